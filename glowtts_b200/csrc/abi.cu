@@ -1,0 +1,181 @@
+// glowtts_b200/csrc/abi.cu -- the extern "C" surface declared in include/glowtts_b200.h.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "ops.h"
+#include "../../include/glowtts_b200.h"
+
+namespace gtk {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+namespace decoder {
+size_t workspace_bytes(const gtk_decoder_desc* d, int train);
+int forward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const float* x, const float* mask, float* z,
+            float* logdet, void* workspace, size_t ws_bytes, int train, cudaStream_t st);
+int reverse(const gtk_decoder_desc* d, const gtk_block_params* blocks, const float* z, const float* mask, float* x,
+            void* workspace, size_t ws_bytes, cudaStream_t st);
+int backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads, const float* mask,
+             const float* dz, const float* dlogdet, float* dx, void* workspace, size_t ws_bytes, cudaStream_t st);
+}  // namespace decoder
+}  // namespace gtk
+
+using namespace gtk;
+#define ST static_cast<cudaStream_t>(stream)
+
+extern "C" {
+
+int gtk_abi_version(void) { return 1; }
+const char* gtk_last_error(void) { return g_err; }
+
+int gtk_mas_lengths_from_mask(const float* mask, int32_t* t_xs, int32_t* t_ys, int B, int T_x, int T_y, void* stream) {
+    return mas::lengths_from_mask(mask, t_xs, t_ys, B, T_x, T_y, ST);
+}
+size_t gtk_mas_workspace_bytes(int B, int T_x, int T_y) { return mas::workspace_bytes(B, T_x, T_y); }
+int gtk_mas_forward(const float* value, const int32_t* t_xs, const int32_t* t_ys, float* path, int32_t* dur_out,
+                    int32_t* idx_out, int B, int T_x, int T_y, void* workspace, size_t workspace_bytes, int force_generic,
+                    void* stream) {
+    return mas::forward(value, t_xs, t_ys, path, dur_out, idx_out, B, T_x, T_y, workspace, workspace_bytes, force_generic, ST);
+}
+
+int gtk_logp(const float* x_m, const float* x_logs, const float* z, float* logp, int B, int D, int T_x, int T_y, void* stream) {
+    return logp::forward(x_m, x_logs, z, logp, B, D, T_x, T_y, ST);
+}
+
+int gtk_squeeze(const float* x, const float* mask, float* out, float* mask_out, int B, int C, int T, int n_sqz, void* stream) {
+    return flow::squeeze(x, mask, out, mask_out, B, C, T, n_sqz, 0, ST);
+}
+int gtk_unsqueeze(const float* x, const float* mask, float* out, float* mask_out, int B, int C, int T, int n_sqz, void* stream) {
+    return flow::unsqueeze(x, mask, out, mask_out, B, C, T, n_sqz, 0, ST);
+}
+int gtk_gate_fwd(const float* a, const float* b, int cond_mode, float* out, int B, int H, int T, void* stream) {
+    return flow::gate_fwd(a, b, cond_mode, 0, out, B, H, T, ST);
+}
+int gtk_gate_bwd(const float* a, const float* b, int cond_mode, const float* dout, float* da, int B, int H, int T, void* stream) {
+    return flow::gate_bwd(a, b, cond_mode, 0, dout, da, B, H, T, ST);
+}
+int gtk_row_sum(const float* in, float* out, int R, int T, int accumulate, void* stream) {
+    return flow::row_sum(in, out, R, T, accumulate, 0, 0, ST);
+}
+int gtk_channel_sum(const float* in, float* out, int B, int M, int T, int accumulate, void* stream) {
+    return flow::channel_sum(in, nullptr, out, B, M, T, accumulate, ST);
+}
+int gtk_mle_loss_fwd(const float* z, const float* m, const float* logs, const float* logdet, const float* mask, float* acc4,
+                     float* loss, int B, int C, int T, void* stream) {
+    return flow::mle_loss_fwd(z, m, logs, logdet, mask, acc4, loss, B, C, T, ST);
+}
+int gtk_mle_loss_bwd(const float* z, const float* m, const float* logs, const float* acc4, const float* gloss, float* dz,
+                     float* dm, float* dlogs, float* dlogdet, int B, int C, int T, void* stream) {
+    return flow::mle_loss_bwd(z, m, logs, acc4, gloss, dz, dm, dlogs, dlogdet, B, C, T, ST);
+}
+int gtk_gather_tokens(const float* src, const int32_t* idx, float* out, int B, int C, int T_x, int T_y, void* stream) {
+    return flow::gather_tokens(src, idx, out, B, C, T_x, T_y, ST);
+}
+int gtk_generate_path(const float* duration, const float* mask, float* path, int B, int T_x, int T_y, void* stream) {
+    return logp::generate_path(duration, mask, path, B, T_x, T_y, ST);
+}
+
+int gtk_mask_len(const float* mask, float* x_len, int B, int T, void* stream) { return flow::mask_len(mask, x_len, B, T, ST); }
+int gtk_invconv_prep(const float* w, int n_split, float* winv, float* logdet_w, void* stream) {
+    return flow::invconv_prep(w, n_split, winv, logdet_w, ST);
+}
+int gtk_flow_mix(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int n_split, float* z,
+                 int B, int C, int T, int reverse, void* stream) {
+    return flow::mix(x, mask, logs, bias, M, n_split, z, B, C, T, reverse, ST);
+}
+int gtk_flow_mix_bwd(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int n_split,
+                     const float* dz, float* dx, float* dlogs, float* dbias, float* dM, int B, int C, int T, void* stream) {
+    return flow::mix_bwd(x, mask, logs, bias, M, n_split, dz, dx, dlogs, dbias, dM, B, C, T, ST);
+}
+int gtk_flow_logdet_const(const float* logs, int C, const float* logdet_w, float group_count, const float* x_len,
+                          float* logdet, int B, int accumulate, void* stream) {
+    return flow::logdet_const(logs, C, logdet_w, group_count, x_len, logdet, B, accumulate, ST);
+}
+int gtk_flow_logdet_const_bwd(const float* dlogdet, const float* x_len, int B, float* dlogs, int C, const float* winv,
+                              int n_split, float group_count, float* dW, void* stream) {
+    return flow::logdet_const_bwd(dlogdet, x_len, B, dlogs, C, winv, n_split, group_count, dW, ST);
+}
+int gtk_actnorm_ddi_stats(const float* x, const float* mask, float* stats, int B, int C, int T, void* stream) {
+    return flow::actnorm_ddi_stats(x, mask, stats, B, C, T, ST);
+}
+int gtk_actnorm_ddi_finalize(const float* stats, float* logs, float* bias, int C, void* stream) {
+    return flow::actnorm_ddi_finalize(stats, logs, bias, C, ST);
+}
+
+int gtk_weightnorm_fwd(const float* g, const float* v, float* w, float* norm_out, int M, int R, void* stream) {
+    return flow::weightnorm_fwd(g, v, w, norm_out, M, R, ST);
+}
+int gtk_weightnorm_bwd(const float* g, const float* v, const float* dw, float* dg, float* dv, int M, int R, int accumulate,
+                       void* stream) {
+    return flow::weightnorm_bwd(g, v, dw, dg, dv, M, R, accumulate, ST);
+}
+int gtk_conv1d_pack_weight(const float* w, float* wp, int M, int Cin, int K, int transpose, void* stream) {
+    return conv::pack_weight(w, wp, M, Cin, K, transpose, ST);
+}
+int gtk_conv1d(const float* in, const float* wp, const float* bias, const float* mask, const float* resid, float* out, int B,
+               int Cin, int M, int T, int K, int dil, int flags, void* stream) {
+    conv::ConvParams p;
+    memset(&p, 0, sizeof(p));
+    p.in = in; p.wp = wp; p.bias = bias; p.mask = mask; p.resid = resid; p.out = out;
+    p.B = B; p.Cin = Cin; p.M = M; p.T = T; p.K = K; p.dil = dil;
+    p.mask_out = flags & 1; p.mask_resid = (flags >> 1) & 1; p.mask_in = (flags >> 2) & 1;
+    return conv::conv1d_f32(p, ST);
+}
+int gtk_conv1d_wgrad(const float* dout, const float* in, const float* mask, float* dw, int B, int Cin, int M, int T, int K,
+                     int dil, int flags, void* stream) {
+    conv::WgradParams p;
+    memset(&p, 0, sizeof(p));
+    p.dout = dout; p.in = in; p.mask = mask; p.dw = dw;
+    p.B = B; p.Cin = Cin; p.M = M; p.T = T; p.dil = dil;
+    p.mask_dout = flags & 1; p.mask_in = (flags >> 1) & 1;
+    return conv::wgrad_f32(p, K, ST);
+}
+int gtk_wn_resskip(const float* rs, const float* x, const float* mask, float* x_out, float* skip, int B, int H, int RS, int T,
+                   int first, int mask_skip, void* stream) {
+    return flow::resskip(rs, x, mask, x_out, skip, B, H, RS, T, first, mask_skip, ST);
+}
+int gtk_coupling_affine(const float* x, const float* end_out, const float* mask, float* z, float* logdet, int B, int C, int T,
+                        int reverse, int sigmoid_scale, void* stream) {
+    return flow::affine(x, end_out, mask, z, logdet, B, C, T, reverse, sigmoid_scale, ST);
+}
+int gtk_coupling_affine_bwd(const float* x, const float* end_out, const float* mask, const float* dz, const float* dlogdet,
+                            float* dend, float* dx, int B, int C, int T, int sigmoid_scale, void* stream) {
+    return flow::affine_bwd(x, end_out, mask, dz, dlogdet, dend, dx, B, C, T, sigmoid_scale, ST);
+}
+
+size_t gtk_decoder_workspace_bytes(const gtk_decoder_desc* d, int train) { return decoder::workspace_bytes(d, train); }
+int gtk_decoder_forward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const float* x, const float* mask, float* z,
+                        float* logdet, void* workspace, size_t workspace_bytes, int train, void* stream) {
+    return decoder::forward(d, blocks, x, mask, z, logdet, workspace, workspace_bytes, train, ST);
+}
+int gtk_decoder_reverse(const gtk_decoder_desc* d, const gtk_block_params* blocks, const float* z, const float* mask, float* x,
+                        void* workspace, size_t workspace_bytes, void* stream) {
+    return decoder::reverse(d, blocks, z, mask, x, workspace, workspace_bytes, ST);
+}
+int gtk_decoder_backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads,
+                         const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace,
+                         size_t workspace_bytes, void* stream) {
+    return decoder::backward(d, blocks, grads, mask, dz, dlogdet, dx, workspace, workspace_bytes, ST);
+}
+
+}  // extern "C"

@@ -1,0 +1,428 @@
+// glowtts_b200/csrc/mas.cu -- monotonic alignment search on sm_100a.
+//
+// Replaces /root/reference/monotonic_align/core.pyx:9-45 (maximum_path_each /
+// maximum_path_c) and the host round trip of monotonic_align/__init__.py:6-21.
+//
+// One CTA per utterance.  Warp 0 is the DP warp: lane l owns text rows
+// x = l*XPT .. l*XPT+XPT-1, keeps the previous DP column Q[x, y-1] in registers,
+// takes the x-1 neighbour of its first row with one warp shuffle per column and
+// sweeps the mel frames y.  For every cell it records ONE bit,
+//     d(x,y) = (x == y) || (Q[x,y-1] < Q[x-1,y-1])      (core.pyx:34, strict <)
+// i.e. "the path at (x,y) came from (x-1,y-1)", packed along y (32 frames per word)
+// in shared memory, so the backtrack never touches HBM and can skip whole runs with
+// one clz per text row.  Warps 1..7 stream `value` tiles (32 frames x t_x rows) from
+// HBM into a shared-memory ring (transposed so the DP warp reads bank-conflict-free)
+// and, in the gaps, zero-fill this utterance's plane of the output, so the memory
+// system works while the latency-bound DP chain runs.  HBM traffic is the algorithmic
+// 8 B per cell (fp32 value read once, fp32 path written once).
+//
+// Bit-exactness (core.pyx): one fp32 add per cell, max() in Cython's select form
+// ((v_prev > v_cur) ? v_prev : v_cur), -1e9 sentinels at x==y and (x==0,y>0), 0 at
+// (0,0), tie => stay.  Cells outside the reference's band are computed but never
+// consumed by an in-band cell, so the lower band clip is not needed.
+#include "common.cuh"
+#include "ops.h"
+
+namespace gtk {
+namespace mas {
+
+constexpr int YT = 32;                   // frames per tile == bits per decision word
+constexpr int NH = 7;                    // helper (load / zero-fill) warps
+constexpr int NT = 32 * (1 + NH);        // threads per CTA
+constexpr int MAX_STAGES = 4;
+constexpr int MAX_XPT = 16;              // fast path covers T_x <= 512
+constexpr float NEG = -1e9f;             // max_neg_val default of maximum_path_c (core.pyx:40)
+
+struct Params {
+    const float* value;   // [B, T_x, T_y] fp32, y fastest
+    float* path;          // [B, T_x, T_y] fp32 out (fully written: zeros + ones)
+    const int* t_xs;      // [B]
+    const int* t_ys;      // [B]
+    int* dur_out;         // [B, T_x] or null: frames per token  (= attn.sum(2), models.py:1085)
+    int* idx_out;         // [B, T_y] or null: token per frame, -1 beyond t_y
+    int B, T_x, T_y;
+    int n_stages;
+    int vec4;             // 1: value rows are 16-byte aligned (T_y % 4 == 0 and base aligned)
+};
+
+template <int XPT>
+__device__ __forceinline__ int phys_col(int x) {   // row x -> column inside a tile / bits row
+    return (x % XPT) * 32 + (x / XPT);             // lane-interleaved: lane = x / XPT, k = x % XPT
+}
+
+template <int XPT, bool DIAG>
+__device__ __forceinline__ void dp_tile(const float* __restrict__ tile, float (&q)[XPT], uint32_t (&bits)[XPT],
+                                        int lane, int y0, int ncols) {
+    constexpr int P = 32 * XPT + 1;
+    const int x0 = lane * XPT;
+#pragma unroll 2
+    for (int yl = 0; yl < ncols; ++yl) {
+        const int y = y0 + yl;
+        float up = __shfl_up_sync(0xffffffffu, q[XPT - 1], 1);
+        if (lane == 0) up = (y == 0) ? 0.0f : NEG;
+        float v[XPT];
+#pragma unroll
+        for (int k = 0; k < XPT; ++k) v[k] = tile[yl * P + k * 32 + lane];
+        const uint32_t bit = 1u << yl;
+#pragma unroll
+        for (int k = XPT - 1; k >= 0; --k) {
+            const float b = (k == 0) ? up : q[k - 1];
+            const float a = q[k];
+            bool d = a < b;
+            float a2 = a;
+            if (DIAG) {
+                const bool diag = (x0 + k == y);
+                d = d || diag;
+                a2 = diag ? NEG : a;
+            }
+            const float m = (b > a2) ? b : a2;
+            q[k] = m + v[k];
+            if (d) bits[k] |= bit;
+        }
+    }
+}
+
+template <int XPT>
+__global__ void __launch_bounds__(NT, 1) mas_kernel(const Params p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int P = 32 * XPT + 1;
+    constexpr int ROWW = 32 * XPT;   // words per decision row-block
+    const int S = p.n_stages;
+    const int NYB = (p.T_y + YT - 1) / YT;
+
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);
+    uint64_t* empty = full + MAX_STAGES;
+    int* ys = reinterpret_cast<int*>(smem_raw + 2 * MAX_STAGES * sizeof(uint64_t));
+    constexpr int YS_WORDS = ((ROWW + 1 + 3) / 4) * 4;
+    uint32_t* bitsT = reinterpret_cast<uint32_t*>(ys + YS_WORDS);
+    float* tiles = reinterpret_cast<float*>(bitsT + (size_t)NYB * ROWW);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.x;
+    int t_x = min(max(p.t_xs[b], 0), p.T_x);
+    int t_y = min(max(p.t_ys[b], 0), p.T_y);
+    const bool valid = (t_x >= 1) && (t_y >= t_x);   // t_x > t_y is undefined in the reference
+    const int n_tiles = valid ? (t_y + YT - 1) / YT : 0;
+    const int n_iter = max(n_tiles, 1);
+    const size_t plane_elems = (size_t)p.T_x * p.T_y;
+    const float* __restrict__ vplane = p.value + (size_t)b * plane_elems;
+    float* __restrict__ pplane = p.path + (size_t)b * plane_elems;
+
+    if (tid == 0) {
+        for (int s = 0; s < MAX_STAGES; ++s) {
+            mbar_init(&full[s], NH * 32);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ DP warp
+        float q[XPT];
+        uint32_t bits[XPT];
+#pragma unroll
+        for (int k = 0; k < XPT; ++k) q[k] = 0.0f;
+        for (int it = 0; it < n_tiles; ++it) {
+            const int s = it % S, use = it / S;
+            mbar_wait(&full[s], use & 1);
+            const float* tile = tiles + (size_t)s * YT * P;
+            const int y0 = it * YT;
+            const int ncols = min(YT, t_y - y0);
+#pragma unroll
+            for (int k = 0; k < XPT; ++k) bits[k] = 0u;
+            if (y0 < 32 * XPT) dp_tile<XPT, true>(tile, q, bits, lane, y0, ncols);
+            else               dp_tile<XPT, false>(tile, q, bits, lane, y0, ncols);
+#pragma unroll
+            for (int k = 0; k < XPT; ++k) bitsT[(size_t)it * ROWW + k * 32 + lane] = bits[k];
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
+        }
+        __syncwarp();
+        // ------------------------------------------------------------ backtrack (run-skipping)
+        if (lane == 0 && valid) {
+            int index = t_x - 1, y = t_y - 1;
+            while (true) {
+                if (index == 0 || y < 0) { ys[0] = 0; break; }
+                const int yb = y >> 5;
+                const uint32_t w = bitsT[(size_t)yb * ROWW + phys_col<XPT>(index)];
+                const uint32_t m = w & (0xffffffffu >> (31 - (y & 31)));
+                if (m) {
+                    const int yp = (yb << 5) + (31 - __clz(m));
+                    ys[index] = yp;       // first frame of token `index`
+                    --index;
+                    y = yp - 1;
+                } else {
+                    y = (yb << 5) - 1;
+                }
+            }
+            // y < 0 with index > 0 cannot happen for valid inputs (diagonal bits force the move);
+            // if it did, make the remaining rows empty rather than reading garbage.
+            for (int x = 1; x <= index; ++x) ys[x] = 0;
+        }
+    } else {
+        // ------------------------------------------------------------ helper warps
+        const int hw = warp - 1;
+        const int ht = tid - 32;
+        constexpr int HT = NH * 32;
+        // zero-fill geometry: [head scalars][nvec float4][tail scalars]
+        const uintptr_t addr = reinterpret_cast<uintptr_t>(pplane);
+        size_t head = ((16 - (addr & 15)) & 15) / 4;
+        if (head > plane_elems) head = plane_elems;
+        const size_t nvec = (plane_elems - head) / 4;
+        const size_t tail0 = head + nvec * 4;
+        float4* pv = reinterpret_cast<float4*>(pplane + head);
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+
+        for (int it = 0; it < n_iter; ++it) {
+            if (it < n_tiles) {
+                const int s = it % S, use = it / S;
+                if (use >= 1) mbar_wait(&empty[s], (use - 1) & 1);
+                float* tile = tiles + (size_t)s * YT * P;
+                const int y0 = it * YT;
+                if (p.vec4) {
+                    // item = (k, group of 4 lanes-of-rows); each lane loads 4 frames of one row.
+                    const int yc = (lane & 7) * 4;
+                    const bool ycol_ok = (y0 + yc) < t_y;
+                    constexpr int U = 4;
+                    for (int item0 = hw; item0 < XPT * 8; item0 += NH * U) {
+                        float4 r[U];
+#pragma unroll
+                        for (int u = 0; u < U; ++u) {
+                            const int item = item0 + u * NH;
+                            const int k = item >> 3, qg = item & 7;
+                            const int x = (4 * qg + (lane >> 3)) * XPT + k;
+                            r[u] = z4;
+                            if (item < XPT * 8 && x < t_x && ycol_ok)
+                                r[u] = __ldg(reinterpret_cast<const float4*>(vplane + (size_t)x * p.T_y + y0 + yc));
+                        }
+#pragma unroll
+                        for (int u = 0; u < U; ++u) {
+                            const int item = item0 + u * NH;
+                            const int k = item >> 3, qg = item & 7;
+                            const int qq = 4 * qg + (lane >> 3);
+                            if (item < XPT * 8 && qq * XPT + k < t_x) {
+                                float* dst = tile + (size_t)yc * P + k * 32 + qq;
+                                dst[0] = r[u].x; dst[P] = r[u].y; dst[2 * P] = r[u].z; dst[3 * P] = r[u].w;
+                            }
+                        }
+                    }
+                } else {
+                    const int y = y0 + lane;
+                    const bool y_ok = y < t_y;
+                    constexpr int U = 8;
+                    for (int x0 = hw; x0 < t_x; x0 += NH * U) {
+                        float r[U];
+#pragma unroll
+                        for (int u = 0; u < U; ++u) {
+                            const int x = x0 + u * NH;
+                            r[u] = (x < t_x && y_ok) ? __ldg(vplane + (size_t)x * p.T_y + y) : 0.f;
+                        }
+#pragma unroll
+                        for (int u = 0; u < U; ++u) {
+                            const int x = x0 + u * NH;
+                            if (x < t_x) tile[(size_t)lane * P + phys_col<XPT>(x)] = r[u];
+                        }
+                    }
+                }
+                mbar_arrive(&full[s]);
+            }
+            // zero-fill share `it` of this utterance's output plane
+            const size_t lo = nvec * (size_t)it / n_iter, hi = nvec * (size_t)(it + 1) / n_iter;
+            for (size_t i = lo + ht; i < hi; i += HT) pv[i] = z4;
+            if (it == 0) {
+                if ((size_t)ht < head) pplane[ht] = 0.f;
+                for (size_t i = tail0 + ht; i < plane_elems; i += HT) pplane[i] = 0.f;
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---------------------------------------------------------------- emit ones / durations / indices
+    for (int x = tid; x < p.T_x; x += NT) {
+        int start = 0, end = 0;
+        if (valid && x < t_x) {
+            start = ys[x];
+            end = (x + 1 < t_x) ? ys[x + 1] : t_y;
+            for (int y = start; y < end; ++y) pplane[(size_t)x * p.T_y + y] = 1.0f;
+            if (p.idx_out)
+                for (int y = start; y < end; ++y) p.idx_out[(size_t)b * p.T_y + y] = x;
+        }
+        if (p.dur_out) p.dur_out[(size_t)b * p.T_x + x] = end - start;
+    }
+    if (p.idx_out)
+        for (int y = (valid ? t_y : 0) + tid; y < p.T_y; y += NT) p.idx_out[(size_t)b * p.T_y + y] = -1;
+}
+
+// -------------------------------------------------------------------------------------------------
+// Generic fallback for shapes the fast path does not cover (T_x > 512, or decision bits that do not
+// fit in shared memory): DP column in shared memory, block barrier per frame, decision words in a
+// global workspace [B][T_y][ceil(T_x/32)].  Same arithmetic, same bits.
+constexpr int GEN_NT = 1024;
+
+__global__ void __launch_bounds__(GEN_NT, 1) mas_generic_kernel(const Params p, uint32_t* __restrict__ ws) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* qa = reinterpret_cast<float*>(smem_raw);
+    float* qb = qa + p.T_x;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int b = blockIdx.x;
+    const int W = (p.T_x + 31) / 32;
+    int t_x = min(max(p.t_xs[b], 0), p.T_x);
+    int t_y = min(max(p.t_ys[b], 0), p.T_y);
+    const bool valid = (t_x >= 1) && (t_y >= t_x);
+    const size_t plane_elems = (size_t)p.T_x * p.T_y;
+    const float* __restrict__ vplane = p.value + (size_t)b * plane_elems;
+    float* __restrict__ pplane = p.path + (size_t)b * plane_elems;
+    uint32_t* wsb = ws + (size_t)b * p.T_y * W;
+
+    for (size_t i = tid; i < plane_elems; i += GEN_NT) pplane[i] = 0.f;
+    if (p.dur_out) for (int x = tid; x < p.T_x; x += GEN_NT) p.dur_out[(size_t)b * p.T_x + x] = 0;
+    if (p.idx_out) for (int y = tid; y < p.T_y; y += GEN_NT) p.idx_out[(size_t)b * p.T_y + y] = -1;
+    for (int x = tid; x < p.T_x; x += GEN_NT) qa[x] = 0.f;
+    __syncthreads();
+    if (!valid) return;
+
+    for (int y = 0; y < t_y; ++y) {
+        for (int xb = 0; xb < t_x; xb += GEN_NT) {
+            const int x = xb + tid;
+            bool d = false;
+            if (x < t_x) {
+                const float a = qa[x];
+                const float bq = (x == 0) ? ((y == 0) ? 0.f : NEG) : qa[x - 1];
+                const bool diag = (x == y);
+                d = (x > 0) && (diag || a < bq);
+                const float a2 = diag ? NEG : a;
+                const float m = (bq > a2) ? bq : a2;
+                qb[x] = m + vplane[(size_t)x * p.T_y + y];
+            }
+            const uint32_t word = __ballot_sync(0xffffffffu, d);
+            if (lane == 0 && (x >> 5) < W) wsb[(size_t)y * W + (x >> 5)] = word;
+        }
+        __syncthreads();
+        float* t = qa; qa = qb; qb = t;
+    }
+    if (tid == 0) {
+        int index = t_x - 1, cnt = 0;
+        for (int y = t_y - 1; y >= 0; --y) {
+            pplane[(size_t)index * p.T_y + y] = 1.0f;
+            if (p.idx_out) p.idx_out[(size_t)b * p.T_y + y] = index;
+            ++cnt;
+            if (index != 0 && ((wsb[(size_t)y * W + (index >> 5)] >> (index & 31)) & 1u)) {
+                if (p.dur_out) p.dur_out[(size_t)b * p.T_x + index] = cnt;
+                cnt = 0;
+                --index;
+            }
+        }
+        if (p.dur_out) p.dur_out[(size_t)b * p.T_x + index] = cnt;
+    }
+}
+
+// monotonic_align/__init__.py:18-19: t_x = mask.sum(1)[:,0], t_y = mask.sum(2)[:,0], on the device.
+__global__ void mas_lengths_kernel(const float* __restrict__ mask, int* __restrict__ t_xs, int* __restrict__ t_ys,
+                                   int T_x, int T_y) {
+    __shared__ float scratch[33];
+    const int b = blockIdx.x;
+    const float* m = mask + (size_t)b * T_x * T_y;
+    float sx = 0.f, sy = 0.f;
+    for (int x = threadIdx.x; x < T_x; x += 256) sx += m[(size_t)x * T_y];
+    for (int y = threadIdx.x; y < T_y; y += 256) sy += m[y];
+    sx = block_sum<256>(sx, scratch);
+    sy = block_sum<256>(sy, scratch);
+    if (threadIdx.x == 0) {
+        t_xs[b] = (int)sx;
+        t_ys[b] = (int)sy;
+    }
+}
+
+// ------------------------------------------------------------------------------------------ host side
+static size_t fast_smem_bytes(int xpt, int T_y, int stages) {
+    const size_t roww = 32 * (size_t)xpt;
+    const size_t ys_words = ((roww + 1 + 3) / 4) * 4;
+    const size_t nyb = (T_y + YT - 1) / YT;
+    return 2 * MAX_STAGES * sizeof(uint64_t) + ys_words * 4 + nyb * roww * 4 + (size_t)stages * YT * (roww + 1) * 4;
+}
+
+static const size_t SMEM_LIMIT = 227 * 1024;
+
+// Picks the fast path configuration; returns stages (0 => use the generic kernel).
+static int plan_fast(int T_x, int T_y, int* xpt_out) {
+    const int xpt = max(1, ceil_div(T_x, 32));
+    *xpt_out = xpt;
+    if (xpt > MAX_XPT) return 0;
+    for (int s = MAX_STAGES; s >= 2; --s)
+        if (fast_smem_bytes(xpt, T_y, s) <= SMEM_LIMIT) return s;
+    return 0;
+}
+
+size_t workspace_bytes(int B, int T_x, int T_y) {
+    int xpt;
+    if (plan_fast(T_x, T_y, &xpt) > 0) return 0;
+    return (size_t)B * T_y * ceil_div(T_x, 32) * sizeof(uint32_t);
+}
+
+template <int XPT>
+static int launch_fast(const Params& p, size_t smem, cudaStream_t stream) {
+    GTK_CUDA(cudaFuncSetAttribute(mas_kernel<XPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mas_kernel<XPT><<<p.B, NT, smem, stream>>>(p);
+    return check_launch("mas_kernel");
+}
+
+int forward(const float* value, const int* t_xs, const int* t_ys, float* path, int* dur_out, int* idx_out, int B,
+            int T_x, int T_y, void* workspace, size_t workspace_bytes_given, int force_generic, cudaStream_t stream) {
+    GTK_REQUIRE(value && t_xs && t_ys && path, "null pointer");
+    GTK_REQUIRE(B >= 0 && T_x >= 0 && T_y >= 0, "negative size");
+    if (B == 0 || T_x == 0 || T_y == 0) {
+        if (dur_out && B * T_x > 0) GTK_CUDA(cudaMemsetAsync(dur_out, 0, sizeof(int) * (size_t)B * T_x, stream));
+        if (idx_out && B * T_y > 0) GTK_CUDA(cudaMemsetAsync(idx_out, 0xff, sizeof(int) * (size_t)B * T_y, stream));
+        return GTK_OK;
+    }
+    Params p;
+    p.value = value; p.path = path; p.t_xs = t_xs; p.t_ys = t_ys; p.dur_out = dur_out; p.idx_out = idx_out;
+    p.B = B; p.T_x = T_x; p.T_y = T_y;
+    p.vec4 = ((T_y % 4) == 0) && ((reinterpret_cast<uintptr_t>(value) & 15) == 0);
+    int xpt = 0;
+    const int stages = force_generic ? 0 : plan_fast(T_x, T_y, &xpt);
+    p.n_stages = stages;
+    if (stages > 0) {
+        const size_t smem = fast_smem_bytes(xpt, T_y, stages);
+        switch (xpt) {
+#define GTK_MAS_CASE(N) case N: return launch_fast<N>(p, smem, stream);
+            GTK_MAS_CASE(1) GTK_MAS_CASE(2) GTK_MAS_CASE(3) GTK_MAS_CASE(4) GTK_MAS_CASE(5) GTK_MAS_CASE(6)
+            GTK_MAS_CASE(7) GTK_MAS_CASE(8) GTK_MAS_CASE(9) GTK_MAS_CASE(10) GTK_MAS_CASE(11) GTK_MAS_CASE(12)
+            GTK_MAS_CASE(13) GTK_MAS_CASE(14) GTK_MAS_CASE(15) GTK_MAS_CASE(16)
+#undef GTK_MAS_CASE
+            default: break;
+        }
+        set_error("mas: internal: no instantiation for XPT=%d", xpt);
+        return GTK_ERR_UNSUPPORTED;
+    }
+    // generic path
+    const size_t need = (size_t)B * T_y * ceil_div(T_x, 32) * sizeof(uint32_t);
+    if (!workspace || workspace_bytes_given < need) {
+        set_error("mas: generic path needs %zu workspace bytes, got %zu", need, workspace_bytes_given);
+        return GTK_ERR_WORKSPACE;
+    }
+    const size_t smem = 2 * (size_t)T_x * sizeof(float);
+    if (smem > SMEM_LIMIT) {
+        set_error("mas: T_x=%d exceeds the generic kernel's shared-memory column buffer", T_x);
+        return GTK_ERR_UNSUPPORTED;
+    }
+    GTK_CUDA(cudaFuncSetAttribute(mas_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mas_generic_kernel<<<B, GEN_NT, smem, stream>>>(p, static_cast<uint32_t*>(workspace));
+    return check_launch("mas_generic_kernel");
+}
+
+int lengths_from_mask(const float* mask, int* t_xs, int* t_ys, int B, int T_x, int T_y, cudaStream_t stream) {
+    GTK_REQUIRE(mask && t_xs && t_ys, "null pointer");
+    if (B == 0) return GTK_OK;
+    if (T_x == 0 || T_y == 0) {
+        GTK_CUDA(cudaMemsetAsync(t_xs, 0, sizeof(int) * B, stream));
+        GTK_CUDA(cudaMemsetAsync(t_ys, 0, sizeof(int) * B, stream));
+        return GTK_OK;
+    }
+    mas_lengths_kernel<<<B, 256, 0, stream>>>(mask, t_xs, t_ys, T_x, T_y);
+    return check_launch("mas_lengths_kernel");
+}
+
+}  // namespace mas
+}  // namespace gtk

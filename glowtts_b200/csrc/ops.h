@@ -1,0 +1,79 @@
+// glowtts_b200/csrc/ops.h -- internal declarations of the launchers (one per kernel family).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace gtk {
+namespace mas {
+size_t workspace_bytes(int B, int T_x, int T_y);
+int forward(const float* value, const int* t_xs, const int* t_ys, float* path, int* dur_out, int* idx_out, int B, int T_x,
+            int T_y, void* workspace, size_t workspace_bytes_given, int force_generic, cudaStream_t stream);
+int lengths_from_mask(const float* mask, int* t_xs, int* t_ys, int B, int T_x, int T_y, cudaStream_t stream);
+}  // namespace mas
+
+namespace logp {
+int forward(const float* x_m, const float* x_logs, const float* z, float* out, int B, int D, int T_x, int T_y, cudaStream_t st);
+int generate_path(const float* dur, const float* mask, float* path, int B, int T_x, int T_y, cudaStream_t st);
+}  // namespace logp
+
+namespace flow {
+int squeeze(const float* x, const float* mask, float* out, float* mask_out, int B, int C, int T, int n, int mask_is_squeezed,
+            cudaStream_t st);
+int unsqueeze(const float* x, const float* mask, float* out, float* mask_out, int B, int C, int T, int n, int out_T,
+              cudaStream_t st);
+int mask_len(const float* mask, float* x_len, int B, int T, cudaStream_t st);
+int invconv_prep(const float* w, int ns, float* winv, float* logdet, cudaStream_t st);
+int mix(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int ns, float* z, int B,
+        int C, int T, int reverse, cudaStream_t st);
+int mix_bwd(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int ns, const float* dz,
+            float* dx, float* dlogs, float* dbias, float* dM, int B, int C, int T, cudaStream_t st);
+int logdet_const(const float* logs, int C, const float* logdetW, float group_count, const float* x_len, float* logdet, int B,
+                 int accumulate, cudaStream_t st);
+int logdet_const_bwd(const float* dlogdet, const float* x_len, int B, float* dlogs, int C, const float* winv, int ns,
+                     float group_count, float* dW, cudaStream_t st);
+int actnorm_ddi_stats(const float* x, const float* mask, float* stats, int B, int C, int T, cudaStream_t st);
+int actnorm_ddi_finalize(const float* stats, float* logs, float* bias, int C, cudaStream_t st);
+int gate_fwd(const float* a, const float* cond, int cond_mode, size_t cond_bstride, float* out, int B, int H, int T,
+             cudaStream_t st);
+int gate_bwd(const float* a, const float* cond, int cond_mode, size_t cond_bstride, const float* dout, float* da, int B, int H,
+             int T, cudaStream_t st);
+int row_sum(const float* in, float* out, int R, int T, int accumulate, int rows_per_group, size_t out_group_stride,
+            cudaStream_t st);
+int channel_sum(const float* in, const float* mask, float* out, int B, int M, int T, int accumulate, cudaStream_t st);
+int affine(const float* x, const float* end_out, const float* mask, float* z, float* logdet, int B, int C, int T, int reverse,
+           int sigmoid_scale, cudaStream_t st);
+int affine_bwd(const float* x, const float* end_out, const float* mask, const float* dz, const float* dlogdet, float* dend,
+               float* dx, int B, int C, int T, int sigmoid_scale, cudaStream_t st);
+int resskip(const float* rs, const float* x, const float* mask, float* x_out, float* skip, int B, int H, int RS, int T,
+            int first, int mask_skip, cudaStream_t st);
+int cat_mask(const float* a, const float* b, const float* mask, float* out, int B, int Ca, int Cb, int T, int mask_b,
+             cudaStream_t st);
+int weightnorm_fwd(const float* g, const float* v, float* w, float* norm_out, int M, int R, cudaStream_t st);
+int weightnorm_bwd(const float* g, const float* v, const float* dw, float* dg, float* dv, int M, int R, int accumulate,
+                   cudaStream_t st);
+int mle_loss_fwd(const float* z, const float* m, const float* logs, const float* logdet, const float* mask, float* acc4,
+                 float* loss, int B, int C, int T, cudaStream_t st);
+int mle_loss_bwd(const float* z, const float* m, const float* logs, const float* acc4, const float* gloss, float* dz,
+                 float* dm, float* dlogs, float* dlogdet, int B, int C, int T, cudaStream_t st);
+int gather_tokens(const float* src, const int* idx, float* out, int B, int C, int T_x, int T_y, cudaStream_t st);
+}  // namespace flow
+
+namespace conv {
+struct ConvParams {
+    const float* in; const float* wp; const float* bias; const float* mask; const float* resid; float* out;
+    int B, Cin, M, T, K, dil;
+    int mask_out, mask_resid, mask_in;
+    size_t in_bstride, out_bstride, resid_bstride;   // elements between batches; 0 = contiguous
+};
+struct WgradParams {
+    const float* dout; const float* in; const float* mask; float* dw;
+    int B, Cin, M, T, dil;
+    int mask_dout, mask_in;
+    size_t dout_bstride, in_bstride;                 // 0 = contiguous
+};
+int pack_weight(const float* w, float* wp, int M, int Cin, int K, int transpose, cudaStream_t st);
+int conv1d_f32(const ConvParams& p, cudaStream_t st);
+int wgrad_f32(const WgradParams& p, int K, cudaStream_t st);
+}  // namespace conv
+}  // namespace gtk

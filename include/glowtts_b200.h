@@ -1,0 +1,197 @@
+/*
+ * glowtts_b200.h -- C ABI of the B200-native Glow-TTS hot path (libglowtts_b200.so).
+ *
+ * Every entry point is stream-ordered on the cudaStream_t passed as `void* stream`, never
+ * synchronises the host, never allocates (workspaces are passed in) and never throws: it
+ * returns 0 on success or a negative GTK_ERR_* code, with a message in gtk_last_error().
+ * All tensors are device pointers, fp32, C-contiguous, laid out as the reference lays them
+ * out ([B, C, T] with t fastest; [B, T_x, T_y] with y fastest) unless stated otherwise.
+ * Masks are the reference's 0/1 float masks; a [B,1,T] mask is passed as [B,T].
+ *
+ * Each function names the reference interface (file:line under /root/reference) it replaces.
+ * The Python host side (glowtts_b200/) binds these with ctypes and registers them as
+ * torch.library ops; INTEGRATION.md shows the binding a reference maintainer would add.
+ */
+#ifndef GLOWTTS_B200_H
+#define GLOWTTS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GTK_OK 0
+#define GTK_ERR_INVALID (-1)
+#define GTK_ERR_LAUNCH (-2)
+#define GTK_ERR_WORKSPACE (-3)
+#define GTK_ERR_UNSUPPORTED (-4)
+
+#define GTK_MAX_LAYERS 8
+
+/* ---- library ---------------------------------------------------------------------------- */
+int gtk_abi_version(void);
+const char* gtk_last_error(void); /* thread-local, valid until the next failing call */
+
+/* ---- monotonic alignment search --------------------------------------------------------- */
+/* Replaces monotonic_align/__init__.py:18-19 (t_x = mask.sum(1)[:,0], t_y = mask.sum(2)[:,0])
+ * without the device->host copy.  mask [B,T_x,T_y]; t_xs, t_ys int32 [B]. */
+int gtk_mas_lengths_from_mask(const float* mask, int32_t* t_xs, int32_t* t_ys, int B, int T_x, int T_y, void* stream);
+
+/* Bytes of workspace gtk_mas_forward needs for this shape (0 when the decision bits fit in
+ * shared memory, which covers T_x <= 512 at the reference's data sizes). */
+size_t gtk_mas_workspace_bytes(int B, int T_x, int T_y);
+
+/* Replaces maximum_path_c / maximum_path_each (monotonic_align/core.pyx:9-45) and the host
+ * round trip of monotonic_align/__init__.py:11-21.  value [B,T_x,T_y] is NOT modified.
+ * path [B,T_x,T_y] is fully written (0/1).  dur_out [B,T_x] (frames per token = attn.sum(2),
+ * models.py:1085) and idx_out [B,T_y] (token per frame, -1 beyond t_y) are optional (NULL).
+ * Bit-exact with core.pyx for the same fp32 value; utterances with t_x > t_y (undefined
+ * behaviour in the reference) or empty lengths produce an all-zero path. */
+int gtk_mas_forward(const float* value, const int32_t* t_xs, const int32_t* t_ys, float* path, int32_t* dur_out,
+                    int32_t* idx_out, int B, int T_x, int T_y, void* workspace, size_t workspace_bytes,
+                    int force_generic, void* stream);
+
+/* ---- logp (models.py:1076-1082) ---------------------------------------------------------- */
+/* logp[b,x,y] = log N(z[b,:,y]; x_m[b,:,x], exp(x_logs[b,:,x])).  x_logs may be NULL (mean_only:
+ * x_logs == 0, models.py:712-713).  x_m,x_logs [B,D,T_x]; z [B,D,T_y]; logp [B,T_x,T_y]. */
+int gtk_logp(const float* x_m, const float* x_logs, const float* z, float* logp, int B, int D, int T_x, int T_y,
+             void* stream);
+
+/* ---- glue (commons.py) ------------------------------------------------------------------- */
+/* commons.squeeze (commons.py:339-351): x [B,C,T] -> out [B,C*n,T/n] (masked), mask_out [B,T/n]. mask/mask_out may be NULL. */
+int gtk_squeeze(const float* x, const float* mask, float* out, float* mask_out, int B, int C, int T, int n_sqz, void* stream);
+/* commons.unsqueeze (commons.py:354-364): x [B,C,T] -> out [B,C/n,T*n] (masked), mask_out [B,T*n]. */
+int gtk_unsqueeze(const float* x, const float* mask, float* out, float* mask_out, int B, int C, int T, int n_sqz, void* stream);
+/* commons.fused_add_tanh_sigmoid_multiply (commons.py:61-68): a [B,2H,T]; cond_mode 0: no b,
+ * 1: b is [B,2H] (broadcast over t, the cond_layer(g) case), 2: b is [B,2H,T]. out [B,H,T]. */
+int gtk_gate_fwd(const float* a, const float* b, int cond_mode, float* out, int B, int H, int T, void* stream);
+/* d(a) [B,2H,T] from d(out); d(b) is d(a) (mode 2) or its sum over t (mode 1, use gtk_row_sum). */
+int gtk_gate_bwd(const float* a, const float* b, int cond_mode, const float* dout, float* da, int B, int H, int T, void* stream);
+int gtk_row_sum(const float* in, float* out, int R, int T, int accumulate, void* stream);
+int gtk_channel_sum(const float* in, float* out, int B, int M, int T, int accumulate, void* stream);
+/* commons.mle_loss (commons.py:28-33).  m/logs may be NULL (= 0).  acc4: 4 floats of scratch that
+ * must be kept for the backward.  loss: 1 float. */
+int gtk_mle_loss_fwd(const float* z, const float* m, const float* logs, const float* logdet, const float* mask, float* acc4,
+                     float* loss, int B, int C, int T, void* stream);
+int gtk_mle_loss_bwd(const float* z, const float* m, const float* logs, const float* acc4, const float* gloss, float* dz,
+                     float* dm, float* dlogs, float* dlogdet, int B, int C, int T, void* stream);
+/* Prior expansion models.py:1118-1119 as the gather it is: out[b,c,y] = src[b,c,idx[b,y]] (0 if idx<0). */
+int gtk_gather_tokens(const float* src, const int32_t* idx, float* out, int B, int C, int T_x, int T_y, void* stream);
+/* commons.generate_path (commons.py:127-143): durations [B,T_x] (float) -> path [B,T_x,T_y] * mask. */
+int gtk_generate_path(const float* duration, const float* mask, float* path, int B, int T_x, int T_y, void* stream);
+
+/* ---- ActNorm / InvConvNear (modules.py:575-668) ------------------------------------------ */
+/* x_len[b] = sum_t mask[b,t]  (modules.py:587,642) */
+int gtk_mask_len(const float* mask, float* x_len, int B, int T, void* stream);
+/* W^-1 (modules.py:651,668) and logdet(W) (modules.py:658) of the n_split x n_split weight, on device. */
+int gtk_invconv_prep(const float* w, int n_split, float* winv, float* logdet_w, void* stream);
+/* Fused ActNorm+InvConvNear.  forward: z = mask * M (bias + exp(logs) x); reverse: z = mask * (M x - bias) exp(-logs).
+ * logs/bias NULL => InvConvNear only (modules.py:635-665; pass M = W or W^-1); M NULL => ActNorm only
+ * (modules.py:584-599; n_split = 1 allows any channel count). */
+int gtk_flow_mix(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int n_split,
+                 float* z, int B, int C, int T, int reverse, void* stream);
+/* Backward of the forward mix; dlogs/dbias [C] and dM [n_split^2] are accumulated into (may be NULL). */
+int gtk_flow_mix_bwd(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int n_split,
+                     const float* dz, float* dx, float* dlogs, float* dbias, float* dM, int B, int C, int T, void* stream);
+/* logdet[b] (+)= (sum_c logs_c + logdet_w * group_count) * x_len[b]; logs / logdet_w may be NULL. */
+int gtk_flow_logdet_const(const float* logs, int C, const float* logdet_w, float group_count, const float* x_len,
+                          float* logdet, int B, int accumulate, void* stream);
+int gtk_flow_logdet_const_bwd(const float* dlogdet, const float* x_len, int B, float* dlogs, int C, const float* winv,
+                              int n_split, float group_count, float* dW, void* stream);
+/* ActNorm.initialize (modules.py:607-619): stats [3,C] = (sum mask, sum x, sum x^2) then finalize.
+ * The split lets a multi-GPU caller all-reduce `stats` in between. */
+int gtk_actnorm_ddi_stats(const float* x, const float* mask, float* stats, int B, int C, int T, void* stream);
+int gtk_actnorm_ddi_finalize(const float* stats, float* logs, float* bias, int C, void* stream);
+
+/* ---- coupling block pieces (attentions.py:132-186, modules.py:144-171) ------------------- */
+/* torch.nn.utils.weight_norm: w[m,:] = g[m] v[m,:] / ||v[m,:]||, R = elements per output channel. */
+int gtk_weightnorm_fwd(const float* g, const float* v, float* w, float* norm_out, int M, int R, void* stream);
+int gtk_weightnorm_bwd(const float* g, const float* v, const float* dw, float* dg, float* dv, int M, int R, int accumulate,
+                       void* stream);
+/* W [M,Cin,K] (torch layout) -> packed operand of gtk_conv1d: transpose=0 forward, 1 data-gradient. */
+int gtk_conv1d_pack_weight(const float* w, float* wp, int M, int Cin, int K, int transpose, void* stream);
+/* F.conv1d(in, W, bias, padding=(K*dil-dil)/2, dilation=dil) with K odd, on a packed weight, plus the fused
+ * tail out = (conv + bias + resid*(mask_resid?mask:1)) * (mask_out?mask:1).  flags: bit0 mask_out,
+ * bit1 mask_resid, bit2 mask_in. */
+int gtk_conv1d(const float* in, const float* wp, const float* bias, const float* mask, const float* resid, float* out,
+               int B, int Cin, int M, int T, int K, int dil, int flags, void* stream);
+/* dW [M,Cin,K] += sum_{b,t} dout[b,m,t] in[b,c,t+(j-(K-1)/2)dil]; flags: bit0 mask dout, bit1 mask in. */
+int gtk_conv1d_wgrad(const float* dout, const float* in, const float* mask, float* dw, int B, int Cin, int M, int T, int K,
+                     int dil, int flags, void* stream);
+/* rs [B,RS,T], RS==2H: x_out=(x+rs[:, :H])*mask, skip(+)=rs[:,H:]; RS==H: skip(+)=rs (modules.py:166-171). */
+int gtk_wn_resskip(const float* rs, const float* x, const float* mask, float* x_out, float* skip, int B, int H, int RS,
+                   int T, int first, int mask_skip, void* stream);
+/* Affine coupling tail (attentions.py:172-183): end_out=[m|logs]; z=[x0 | (m+exp(logs)x1)mask] and
+ * logdet[b] += sum logs*mask (forward), z=[x0 | (x1-m)exp(-logs)mask] (reverse). */
+int gtk_coupling_affine(const float* x, const float* end_out, const float* mask, float* z, float* logdet, int B, int C,
+                        int T, int reverse, int sigmoid_scale, void* stream);
+int gtk_coupling_affine_bwd(const float* x, const float* end_out, const float* mask, const float* dz, const float* dlogdet,
+                            float* dend, float* dx, int B, int C, int T, int sigmoid_scale, void* stream);
+
+/* ---- whole decoder (models.py:719-789) --------------------------------------------------- */
+typedef struct gtk_decoder_desc {
+    int B;              /* batch */
+    int in_channels;    /* mel channels (80) */
+    int T;              /* mel frames of the input tensor (un-squeezed) */
+    int n_sqz;          /* 2 */
+    int hidden;         /* 192 */
+    int kernel_size;    /* 5 */
+    int dilation_rate;  /* 1 */
+    int n_layers;       /* 4 */
+    int n_blocks;       /* 12 */
+    int n_split;        /* 4 */
+    int sigmoid_scale;  /* 0 */
+    int precision;      /* 0: fp32 CUDA-core convolutions (exact-parity path); 1: bf16 tcgen05 path */
+} gtk_decoder_desc;
+
+/* Parameters of one (ActNorm, InvConvNear, CouplingBlock) triple; state_dict names in comments.
+ * Weight-normed convs take (weight_g, weight_v); after remove_weight_norm pass weight as *_v and NULL as *_g. */
+typedef struct gtk_block_params {
+    const float* an_logs;                 /* flows.{3b}.logs   [C]  */
+    const float* an_bias;                 /* flows.{3b}.bias   [C]  */
+    const float* ic_weight;               /* flows.{3b+1}.weight [n_split^2] */
+    const float* start_g;                 /* flows.{3b+2}.start.weight_g [H] */
+    const float* start_v;                 /* ....start.weight_v [H, C/2, 1]  */
+    const float* start_b;                 /* ....start.bias [H] */
+    const float* in_g[GTK_MAX_LAYERS];    /* ....wn.in_layers.{i}.weight_g [2H] */
+    const float* in_v[GTK_MAX_LAYERS];    /* ....wn.in_layers.{i}.weight_v [2H, H, K] */
+    const float* in_b[GTK_MAX_LAYERS];    /* ....wn.in_layers.{i}.bias [2H] */
+    const float* rs_g[GTK_MAX_LAYERS];    /* ....wn.res_skip_layers.{i}.weight_g [RS_i] */
+    const float* rs_v[GTK_MAX_LAYERS];    /* ....wn.res_skip_layers.{i}.weight_v [RS_i, H, 1] */
+    const float* rs_b[GTK_MAX_LAYERS];    /* ....wn.res_skip_layers.{i}.bias [RS_i] */
+    const float* end_w;                   /* ....end.weight [C, H, 1] */
+    const float* end_b;                   /* ....end.bias [C] */
+    const float* cond;                    /* wn.cond_layer(g) output [B, 2H*L] or NULL (modules.py:148-149) */
+} gtk_block_params;
+
+/* Gradient destinations, same shapes as the parameters; ACCUMULATED into (zero them once per step). */
+typedef struct gtk_block_grads {
+    float* an_logs; float* an_bias; float* ic_weight;
+    float* start_g; float* start_v; float* start_b;
+    float* in_g[GTK_MAX_LAYERS]; float* in_v[GTK_MAX_LAYERS]; float* in_b[GTK_MAX_LAYERS];
+    float* rs_g[GTK_MAX_LAYERS]; float* rs_v[GTK_MAX_LAYERS]; float* rs_b[GTK_MAX_LAYERS];
+    float* end_w; float* end_b;
+    float* cond;                          /* [B, 2H*L] or NULL */
+} gtk_block_grads;
+
+/* train != 0: activations are kept in the workspace for gtk_decoder_backward. */
+size_t gtk_decoder_workspace_bytes(const gtk_decoder_desc* d, int train);
+/* FlowSpecDecoder.forward(reverse=False) (models.py:765-785): x [B,in,T], mask [B,T] -> z [B,in,T'] with
+ * T' = (T/n_sqz)*n_sqz, logdet [B]. */
+int gtk_decoder_forward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const float* x, const float* mask,
+                        float* z, float* logdet, void* workspace, size_t workspace_bytes, int train, void* stream);
+/* FlowSpecDecoder.forward(reverse=True): z -> x.  W^-1 is recomputed on device per call (it is a 4x4). */
+int gtk_decoder_reverse(const gtk_decoder_desc* d, const gtk_block_params* blocks, const float* z, const float* mask,
+                        float* x, void* workspace, size_t workspace_bytes, void* stream);
+/* Backward of gtk_decoder_forward(train=1) with the same workspace: dz [B,in,T'], dlogdet [B] -> dx [B,in,T]
+ * and parameter gradients. */
+int gtk_decoder_backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads,
+                         const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace,
+                         size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GLOWTTS_B200_H */
