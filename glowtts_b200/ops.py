@@ -1,0 +1,672 @@
+"""torch.library ops over the C ABI (include/glowtts_b200.h).
+
+Every op here is a thin shim: check dtype/device/contiguity, allocate outputs with torch,
+pass raw device pointers and the current CUDA stream to libglowtts_b200.so.  No op has a CPU
+implementation: calling one with CPU tensors (or without the built library) raises.
+Ops are registered in the ``glowtts_b200`` namespace (``torch.ops.glowtts_b200.*``) with fake
+(meta) implementations and autograd formulas, so they compose with autograd and DDP.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _lib
+from ._lib import BlockParams, DecoderDesc, GTK_MAX_LAYERS
+
+NS = "glowtts_b200"
+
+
+def _stream() -> ctypes.c_void_p:
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t: Optional[Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _chk(t: Tensor, name: str, dtype=torch.float32) -> Tensor:
+    if not t.is_cuda:
+        raise RuntimeError(f"glowtts_b200: {name} must be a CUDA tensor (there is no CPU path)")
+    if t.dtype != dtype:
+        raise RuntimeError(f"glowtts_b200: {name} must be {dtype}, got {t.dtype}")
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _opt(t: Optional[Tensor], name: str) -> Optional[Tensor]:
+    return None if t is None else _chk(t, name)
+
+
+# =============================================================================== MAS
+@torch.library.custom_op(f"{NS}::mas_lengths", mutates_args=(), device_types="cuda")
+def mas_lengths(mask: Tensor) -> Tuple[Tensor, Tensor]:
+    """monotonic_align/__init__.py:18-19 on the device: (t_x, t_y) int32 [B] from a prefix mask."""
+    mask = _chk(mask, "mask")
+    B, T_x, T_y = mask.shape
+    t_xs = torch.empty(B, dtype=torch.int32, device=mask.device)
+    t_ys = torch.empty(B, dtype=torch.int32, device=mask.device)
+    _lib.call("gtk_mas_lengths_from_mask", _p(mask), _p(t_xs), _p(t_ys), B, T_x, T_y, _stream())
+    return t_xs, t_ys
+
+
+@mas_lengths.register_fake
+def _(mask):
+    B = mask.shape[0]
+    return mask.new_empty(B, dtype=torch.int32), mask.new_empty(B, dtype=torch.int32)
+
+
+@torch.library.custom_op(f"{NS}::mas_path", mutates_args=(), device_types="cuda")
+def mas_path(value: Tensor, t_xs: Tensor, t_ys: Tensor, force_generic: bool = False) -> Tuple[Tensor, Tensor, Tensor]:
+    """core.pyx:9-45 on the device.  -> (path f32 [B,T_x,T_y], durations i32 [B,T_x], index i32 [B,T_y])."""
+    value = _chk(value, "value")
+    t_xs = _chk(t_xs, "t_xs", torch.int32)
+    t_ys = _chk(t_ys, "t_ys", torch.int32)
+    B, T_x, T_y = value.shape
+    path = torch.empty_like(value)
+    dur = torch.empty(B, T_x, dtype=torch.int32, device=value.device)
+    idx = torch.empty(B, T_y, dtype=torch.int32, device=value.device)
+    lib = _lib.load()
+    ws_bytes = 0 if not force_generic else B * T_y * ((T_x + 31) // 32) * 4
+    ws_bytes = max(ws_bytes, lib.gtk_mas_workspace_bytes(B, T_x, T_y))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=value.device) if ws_bytes else None
+    _lib.call("gtk_mas_forward", _p(value), _p(t_xs), _p(t_ys), _p(path), _p(dur), _p(idx), B, T_x, T_y,
+              _p(ws), ws_bytes, int(force_generic), _stream())
+    return path, dur, idx
+
+
+@mas_path.register_fake
+def _(value, t_xs, t_ys, force_generic=False):
+    B, T_x, T_y = value.shape
+    return (torch.empty_like(value), value.new_empty((B, T_x), dtype=torch.int32),
+            value.new_empty((B, T_y), dtype=torch.int32))
+
+
+# =============================================================================== logp
+@torch.library.custom_op(f"{NS}::logp", mutates_args=(), device_types="cuda")
+def logp(x_m: Tensor, x_logs: Optional[Tensor], z: Tensor) -> Tensor:
+    """models.py:1076-1082.  x_m, x_logs [B,D,T_x]; z [B,D,T_y] -> [B,T_x,T_y].  x_logs None == 0."""
+    x_m = _chk(x_m, "x_m")
+    x_logs = _opt(x_logs, "x_logs")
+    z = _chk(z, "z")
+    B, D, T_x = x_m.shape
+    T_y = z.shape[2]
+    out = torch.empty(B, T_x, T_y, dtype=torch.float32, device=z.device)
+    _lib.call("gtk_logp", _p(x_m), _p(x_logs), _p(z), _p(out), B, D, T_x, T_y, _stream())
+    return out
+
+
+@logp.register_fake
+def _(x_m, x_logs, z):
+    return z.new_empty((x_m.shape[0], x_m.shape[2], z.shape[2]))
+
+
+# =============================================================================== glue
+@torch.library.custom_op(f"{NS}::squeeze", mutates_args=(), device_types="cuda")
+def squeeze_op(x: Tensor, mask: Optional[Tensor], n_sqz: int) -> Tuple[Tensor, Tensor]:
+    """commons.py:339-351.  x [B,C,T], mask [B,T] -> (x_sqz [B,C*n,T//n], mask_sqz [B,T//n])."""
+    x = _chk(x, "x")
+    mask = _opt(mask, "mask")
+    B, C, T = x.shape
+    Tq = T // n_sqz
+    out = torch.empty(B, C * n_sqz, Tq, dtype=x.dtype, device=x.device)
+    mo = torch.empty(B, Tq, dtype=x.dtype, device=x.device)
+    _lib.call("gtk_squeeze", _p(x), _p(mask), _p(out), _p(mo), B, C, T, n_sqz, _stream())
+    return out, mo
+
+
+@squeeze_op.register_fake
+def _(x, mask, n_sqz):
+    B, C, T = x.shape
+    return x.new_empty((B, C * n_sqz, T // n_sqz)), x.new_empty((B, T // n_sqz))
+
+
+@torch.library.custom_op(f"{NS}::unsqueeze", mutates_args=(), device_types="cuda")
+def unsqueeze_op(x: Tensor, mask: Optional[Tensor], n_sqz: int) -> Tuple[Tensor, Tensor]:
+    """commons.py:354-364.  x [B,C,T], mask [B,T] -> (x_unsqz [B,C//n,T*n], mask [B,T*n])."""
+    x = _chk(x, "x")
+    mask = _opt(mask, "mask")
+    B, C, T = x.shape
+    out = torch.empty(B, C // n_sqz, T * n_sqz, dtype=x.dtype, device=x.device)
+    mo = torch.empty(B, T * n_sqz, dtype=x.dtype, device=x.device)
+    _lib.call("gtk_unsqueeze", _p(x), _p(mask), _p(out), _p(mo), B, C, T, n_sqz, _stream())
+    return out, mo
+
+
+@unsqueeze_op.register_fake
+def _(x, mask, n_sqz):
+    B, C, T = x.shape
+    return x.new_empty((B, C // n_sqz, T * n_sqz)), x.new_empty((B, T * n_sqz))
+
+
+def _squeeze_bwd(ctx, g_out, g_mask):
+    # squeeze and unsqueeze are inverse index maps; the output mask is applied in both.
+    dx, _ = unsqueeze_op(g_out, ctx.mask_out, ctx.n_sqz)
+    if ctx.T != dx.shape[2]:
+        dx = torch.nn.functional.pad(dx, (0, ctx.T - dx.shape[2]))
+    return dx, None, None
+
+
+def _squeeze_setup(ctx, inputs, output):
+    ctx.n_sqz = inputs[2]
+    ctx.T = inputs[0].shape[2]
+    ctx.mask_out = output[1] if inputs[1] is not None else None
+
+
+squeeze_op.register_autograd(_squeeze_bwd, setup_context=_squeeze_setup)
+
+
+def _unsqueeze_bwd(ctx, g_out, g_mask):
+    dx, _ = squeeze_op(g_out, ctx.mask_out, ctx.n_sqz)
+    return dx, None, None
+
+
+def _unsqueeze_setup(ctx, inputs, output):
+    ctx.n_sqz = inputs[2]
+    ctx.mask_out = output[1] if inputs[1] is not None else None
+
+
+unsqueeze_op.register_autograd(_unsqueeze_bwd, setup_context=_unsqueeze_setup)
+
+
+# ---- gate (commons.py:61-68)
+def _cond_mode(a: Tensor, b: Optional[Tensor]) -> int:
+    if b is None:
+        return 0
+    if b.dim() == 3 and b.shape[2] == a.shape[2] and a.shape[2] != 1:
+        return 2
+    if b.shape[-1] == 1 or b.dim() == 2:
+        return 1
+    return 2
+
+
+@torch.library.custom_op(f"{NS}::gate_fwd", mutates_args=(), device_types="cuda")
+def gate_fwd(a: Tensor, b: Optional[Tensor]) -> Tensor:
+    a = _chk(a, "input_a")
+    b = _opt(b, "input_b")
+    B, H2, T = a.shape
+    out = torch.empty(B, H2 // 2, T, dtype=a.dtype, device=a.device)
+    _lib.call("gtk_gate_fwd", _p(a), _p(b), _cond_mode(a, b), _p(out), B, H2 // 2, T, _stream())
+    return out
+
+
+@gate_fwd.register_fake
+def _(a, b):
+    return a.new_empty((a.shape[0], a.shape[1] // 2, a.shape[2]))
+
+
+@torch.library.custom_op(f"{NS}::gate_bwd", mutates_args=(), device_types="cuda")
+def gate_bwd(a: Tensor, b: Optional[Tensor], dout: Tensor) -> Tensor:
+    a = _chk(a, "input_a")
+    b = _opt(b, "input_b")
+    dout = _chk(dout, "dout")
+    B, H2, T = a.shape
+    da = torch.empty_like(a)
+    _lib.call("gtk_gate_bwd", _p(a), _p(b), _cond_mode(a, b), _p(dout), _p(da), B, H2 // 2, T, _stream())
+    return da
+
+
+@gate_bwd.register_fake
+def _(a, b, dout):
+    return torch.empty_like(a)
+
+
+@torch.library.custom_op(f"{NS}::row_sum", mutates_args=(), device_types="cuda")
+def row_sum(x: Tensor) -> Tensor:
+    """Sum over the last dimension of a contiguous tensor (bias / broadcast-conditioner gradients)."""
+    x = _chk(x, "x")
+    T = x.shape[-1]
+    R = x.numel() // max(T, 1)
+    out = torch.empty(x.shape[:-1], dtype=x.dtype, device=x.device)
+    _lib.call("gtk_row_sum", _p(x), _p(out), R, T, 0, _stream())
+    return out
+
+
+@row_sum.register_fake
+def _(x):
+    return x.new_empty(x.shape[:-1])
+
+
+def _gate_setup(ctx, inputs, output):
+    a, b = inputs
+    ctx.save_for_backward(a, b)
+    ctx.b_shape = None if b is None else tuple(b.shape)
+
+
+def _gate_bwd(ctx, dout):
+    a, b = ctx.saved_tensors
+    da = gate_bwd(a, b, dout.contiguous())
+    db = None
+    if b is not None and ctx.needs_input_grad[1]:
+        db = da if _cond_mode(a, b) == 2 else row_sum(da).reshape(ctx.b_shape)
+    return da, db
+
+
+gate_fwd.register_autograd(_gate_bwd, setup_context=_gate_setup)
+
+
+# =============================================================================== ActNorm / InvConvNear
+@torch.library.custom_op(f"{NS}::mask_len", mutates_args=(), device_types="cuda")
+def mask_len(mask: Tensor) -> Tensor:
+    """x_len[b] = sum_t mask[b,t] (modules.py:587,642).  mask [B,T]."""
+    mask = _chk(mask, "mask")
+    B, T = mask.shape
+    out = torch.empty(B, dtype=mask.dtype, device=mask.device)
+    _lib.call("gtk_mask_len", _p(mask), _p(out), B, T, _stream())
+    return out
+
+
+@mask_len.register_fake
+def _(mask):
+    return mask.new_empty((mask.shape[0],))
+
+
+@torch.library.custom_op(f"{NS}::invconv_prep", mutates_args=(), device_types="cuda")
+def invconv_prep(weight: Tensor) -> Tuple[Tensor, Tensor]:
+    """(W^-1, logdet W) of the n_split x n_split InvConvNear weight (modules.py:651,658,668), on device."""
+    weight = _chk(weight, "weight")
+    ns = weight.shape[0]
+    winv = torch.empty_like(weight)
+    ld = torch.empty((), dtype=weight.dtype, device=weight.device)
+    _lib.call("gtk_invconv_prep", _p(weight), ns, _p(winv), _p(ld), _stream())
+    return winv, ld
+
+
+@invconv_prep.register_fake
+def _(weight):
+    return torch.empty_like(weight), weight.new_empty(())
+
+
+@torch.library.custom_op(f"{NS}::flow_mix", mutates_args=(), device_types="cuda")
+def flow_mix(x: Tensor, mask: Optional[Tensor], logs: Optional[Tensor], bias: Optional[Tensor], M: Optional[Tensor],
+             n_split: int, reverse: bool) -> Tensor:
+    """Fused ActNorm (+) InvConvNear (gtk_flow_mix).  x [B,C,T], mask [B,T], logs/bias [C], M [ns,ns]."""
+    x = _chk(x, "x")
+    mask, logs, bias, M = _opt(mask, "mask"), _opt(logs, "logs"), _opt(bias, "bias"), _opt(M, "M")
+    B, C, T = x.shape
+    z = torch.empty_like(x)
+    _lib.call("gtk_flow_mix", _p(x), _p(mask), _p(logs), _p(bias), _p(M), n_split, _p(z), B, C, T, int(reverse), _stream())
+    return z
+
+
+@flow_mix.register_fake
+def _(x, mask, logs, bias, M, n_split, reverse):
+    return torch.empty_like(x)
+
+
+@torch.library.custom_op(f"{NS}::flow_mix_bwd", mutates_args=(), device_types="cuda")
+def flow_mix_bwd(x: Tensor, mask: Optional[Tensor], logs: Optional[Tensor], bias: Optional[Tensor], M: Optional[Tensor],
+                 n_split: int, dz: Tensor) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """-> (dx, dlogs [C], dbias [C], dM [ns,ns]) of the forward mix."""
+    x, dz = _chk(x, "x"), _chk(dz, "dz")
+    mask, logs, bias, M = _opt(mask, "mask"), _opt(logs, "logs"), _opt(bias, "bias"), _opt(M, "M")
+    B, C, T = x.shape
+    dx = torch.empty_like(x)
+    dlogs = torch.zeros(C, dtype=x.dtype, device=x.device)
+    dbias = torch.zeros(C, dtype=x.dtype, device=x.device)
+    dM = torch.zeros(n_split, n_split, dtype=x.dtype, device=x.device)
+    _lib.call("gtk_flow_mix_bwd", _p(x), _p(mask), _p(logs), _p(bias), _p(M), n_split, _p(dz), _p(dx), _p(dlogs), _p(dbias),
+              _p(dM), B, C, T, _stream())
+    return dx, dlogs, dbias, dM
+
+
+@flow_mix_bwd.register_fake
+def _(x, mask, logs, bias, M, n_split, dz):
+    C = x.shape[1]
+    return torch.empty_like(x), x.new_empty((C,)), x.new_empty((C,)), x.new_empty((n_split, n_split))
+
+
+def _mix_setup(ctx, inputs, output):
+    x, mask, logs, bias, M, n_split, reverse = inputs
+    ctx.save_for_backward(x, mask, logs, bias, M)
+    ctx.n_split, ctx.reverse = n_split, reverse
+
+
+def _mix_bwd(ctx, dz):
+    x, mask, logs, bias, M = ctx.saved_tensors
+    if ctx.reverse:
+        raise RuntimeError("glowtts_b200: the reverse flow is inference-only (no backward), as in the reference's use")
+    dx, dlogs, dbias, dM = flow_mix_bwd(x, mask, logs, bias, M, ctx.n_split, dz.contiguous())
+    return (dx, None, dlogs if logs is not None else None, dbias if bias is not None else None,
+            dM if M is not None else None, None, None)
+
+
+flow_mix.register_autograd(_mix_bwd, setup_context=_mix_setup)
+
+
+@torch.library.custom_op(f"{NS}::flow_logdet_const", mutates_args=(), device_types="cuda")
+def flow_logdet_const(logs: Optional[Tensor], logdet_w: Optional[Tensor], group_count: float, x_len: Tensor) -> Tensor:
+    """logdet[b] = (sum_c logs_c + logdet_w * group_count) * x_len[b]  (modules.py:597, 658)."""
+    logs, logdet_w = _opt(logs, "logs"), _opt(logdet_w, "logdet_w")
+    x_len = _chk(x_len, "x_len")
+    B = x_len.shape[0]
+    out = torch.empty(B, dtype=x_len.dtype, device=x_len.device)
+    C = 0 if logs is None else logs.numel()
+    _lib.call("gtk_flow_logdet_const", _p(logs), C, _p(logdet_w), ctypes.c_float(group_count), _p(x_len), _p(out), B, 0,
+              _stream())
+    return out
+
+
+@flow_logdet_const.register_fake
+def _(logs, logdet_w, group_count, x_len):
+    return torch.empty_like(x_len)
+
+
+@torch.library.custom_op(f"{NS}::flow_logdet_const_bwd", mutates_args=(), device_types="cuda")
+def flow_logdet_const_bwd(dlogdet: Tensor, x_len: Tensor, C: int, winv: Optional[Tensor], group_count: float) -> Tuple[Tensor, Tensor]:
+    """-> (dlogs [C] (all equal), dW [ns,ns] = W^-T * group_count * sum_b dlogdet_b x_len_b)."""
+    dlogdet, x_len = _chk(dlogdet, "dlogdet"), _chk(x_len, "x_len")
+    winv = _opt(winv, "winv")
+    B = x_len.shape[0]
+    dlogs = torch.zeros(max(C, 1), dtype=x_len.dtype, device=x_len.device)
+    ns = 1 if winv is None else winv.shape[0]
+    dW = torch.zeros(ns, ns, dtype=x_len.dtype, device=x_len.device)
+    _lib.call("gtk_flow_logdet_const_bwd", _p(dlogdet), _p(x_len), B, _p(dlogs) if C else None, C, _p(winv), ns,
+              ctypes.c_float(group_count), _p(dW) if winv is not None else None, _stream())
+    return dlogs, dW
+
+
+@flow_logdet_const_bwd.register_fake
+def _(dlogdet, x_len, C, winv, group_count):
+    ns = 1 if winv is None else winv.shape[0]
+    return x_len.new_empty((max(C, 1),)), x_len.new_empty((ns, ns))
+
+
+@torch.library.custom_op(f"{NS}::actnorm_ddi", mutates_args=(), device_types="cuda")
+def actnorm_ddi_stats(x: Tensor, mask: Optional[Tensor]) -> Tensor:
+    """ActNorm.initialize statistics (modules.py:609-611): [3,C] = (sum mask, sum x, sum x^2)."""
+    x = _chk(x, "x")
+    mask = _opt(mask, "mask")
+    B, C, T = x.shape
+    stats = torch.zeros(3, C, dtype=x.dtype, device=x.device)
+    _lib.call("gtk_actnorm_ddi_stats", _p(x), _p(mask), _p(stats), B, C, T, _stream())
+    return stats
+
+
+@actnorm_ddi_stats.register_fake
+def _(x, mask):
+    return x.new_empty((3, x.shape[1]))
+
+
+def actnorm_ddi_finalize(stats: Tensor) -> Tuple[Tensor, Tensor]:
+    """modules.py:612-619: stats -> (logs [C], bias [C])."""
+    stats = _chk(stats, "stats")
+    C = stats.shape[1]
+    logs = torch.empty(C, dtype=stats.dtype, device=stats.device)
+    bias = torch.empty(C, dtype=stats.dtype, device=stats.device)
+    _lib.call("gtk_actnorm_ddi_finalize", _p(stats), _p(logs), _p(bias), C, _stream())
+    return logs, bias
+
+
+# =============================================================================== loss / alignment consumers
+@torch.library.custom_op(f"{NS}::mle_loss_fwd", mutates_args=(), device_types="cuda")
+def mle_loss_fwd(z: Tensor, m: Optional[Tensor], logs: Optional[Tensor], logdet: Tensor, mask: Tensor) -> Tuple[Tensor, Tensor]:
+    """commons.py:28-33 -> (loss scalar, acc4 scratch kept for the backward).  mask [B,T]."""
+    z, logdet, mask = _chk(z, "z"), _chk(logdet, "logdet"), _chk(mask, "mask")
+    m, logs = _opt(m, "m"), _opt(logs, "logs")
+    B, C, T = z.shape
+    acc = torch.empty(4, dtype=z.dtype, device=z.device)
+    loss = torch.empty((), dtype=z.dtype, device=z.device)
+    _lib.call("gtk_mle_loss_fwd", _p(z), _p(m), _p(logs), _p(logdet), _p(mask), _p(acc), _p(loss), B, C, T, _stream())
+    return loss, acc
+
+
+@mle_loss_fwd.register_fake
+def _(z, m, logs, logdet, mask):
+    return z.new_empty(()), z.new_empty((4,))
+
+
+@torch.library.custom_op(f"{NS}::mle_loss_bwd", mutates_args=(), device_types="cuda")
+def mle_loss_bwd(z: Tensor, m: Optional[Tensor], logs: Optional[Tensor], acc: Tensor, gloss: Tensor,
+                 n_batch: int) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    z, acc, gloss = _chk(z, "z"), _chk(acc, "acc4"), _chk(gloss, "gloss")
+    m, logs = _opt(m, "m"), _opt(logs, "logs")
+    B, C, T = z.shape
+    dz = torch.empty_like(z)
+    dm = torch.empty_like(z) if m is not None else z.new_empty(0)
+    dlogs = torch.empty_like(z) if logs is not None else z.new_empty(0)
+    dld = torch.empty(n_batch, dtype=z.dtype, device=z.device)
+    _lib.call("gtk_mle_loss_bwd", _p(z), _p(m), _p(logs), _p(acc), _p(gloss), _p(dz), _p(dm) if m is not None else None,
+              _p(dlogs) if logs is not None else None, _p(dld), B, C, T, _stream())
+    return dz, dm, dlogs, dld
+
+
+@mle_loss_bwd.register_fake
+def _(z, m, logs, acc, gloss, n_batch):
+    return (torch.empty_like(z), torch.empty_like(z) if m is not None else z.new_empty(0),
+            torch.empty_like(z) if logs is not None else z.new_empty(0), z.new_empty((n_batch,)))
+
+
+def _mle_setup(ctx, inputs, output):
+    z, m, logs, logdet, mask = inputs
+    ctx.save_for_backward(z, m, logs, output[1])
+    ctx.n_batch = logdet.shape[0]
+
+
+def _mle_bwd(ctx, gloss, gacc):
+    z, m, logs, acc = ctx.saved_tensors
+    dz, dm, dlogs, dld = mle_loss_bwd(z, m, logs, acc, gloss.contiguous(), ctx.n_batch)
+    return dz, (dm if m is not None else None), (dlogs if logs is not None else None), dld, None
+
+
+mle_loss_fwd.register_autograd(_mle_bwd, setup_context=_mle_setup)
+
+
+@torch.library.custom_op(f"{NS}::gather_tokens", mutates_args=(), device_types="cuda")
+def gather_tokens(src: Tensor, idx: Tensor, T_y: int) -> Tensor:
+    """models.py:1118-1119 as a gather: out[b,c,y] = src[b,c,idx[b,y]] (0 where idx < 0).  src [B,C,T_x]."""
+    src, idx = _chk(src, "src"), _chk(idx, "idx", torch.int32)
+    B, C, T_x = src.shape
+    out = torch.empty(B, C, T_y, dtype=src.dtype, device=src.device)
+    _lib.call("gtk_gather_tokens", _p(src), _p(idx), _p(out), B, C, T_x, T_y, _stream())
+    return out
+
+
+@gather_tokens.register_fake
+def _(src, idx, T_y):
+    return src.new_empty((src.shape[0], src.shape[1], T_y))
+
+
+def _gather_setup(ctx, inputs, output):
+    ctx.save_for_backward(inputs[1])
+    ctx.T_x = inputs[0].shape[2]
+
+
+def _gather_bwd(ctx, dout):
+    (idx,) = ctx.saved_tensors
+    # scatter-add of a monotone index map: small ([B,C,T_x]); library op is fine off the hot path
+    B, C, T_y = dout.shape
+    valid = (idx >= 0)
+    ix = idx.clamp(min=0).long().unsqueeze(1).expand(B, C, T_y)
+    dsrc = torch.zeros(B, C, ctx.T_x, dtype=dout.dtype, device=dout.device)
+    dsrc.scatter_add_(2, ix, dout * valid.unsqueeze(1))
+    return dsrc, None, None
+
+
+gather_tokens.register_autograd(_gather_bwd, setup_context=_gather_setup)
+
+
+@torch.library.custom_op(f"{NS}::generate_path", mutates_args=(), device_types="cuda")
+def generate_path(duration: Tensor, mask: Tensor) -> Tensor:
+    """commons.py:127-143.  duration [B,T_x] float, mask [B,T_x,T_y] -> path [B,T_x,T_y]."""
+    duration, mask = _chk(duration, "duration"), _chk(mask, "mask")
+    B, T_x, T_y = mask.shape
+    path = torch.empty_like(mask)
+    _lib.call("gtk_generate_path", _p(duration), _p(mask), _p(path), B, T_x, T_y, _stream())
+    return path
+
+
+@generate_path.register_fake
+def _(duration, mask):
+    return torch.empty_like(mask)
+
+
+# =============================================================================== whole decoder
+# cfg = [in_channels, n_sqz, hidden, kernel_size, dilation_rate, n_layers, n_blocks, n_split, sigmoid_scale,
+#        precision, wn_folded]
+# params: per block, in this order (g entries absent when wn_folded):
+#   an_logs, an_bias, ic_weight, start_g, start_v, start_b, in_g*L, in_v*L, in_b*L, rs_g*L, rs_v*L, rs_b*L, end_w, end_b
+CFG_LEN = 11
+
+
+def params_per_block(n_layers: int, wn_folded: bool) -> int:
+    return (7 + 4 * n_layers) if wn_folded else (8 + 6 * n_layers)
+
+
+def _desc(cfg: Sequence[int], B: int, T: int) -> DecoderDesc:
+    d = DecoderDesc()
+    d.B, d.T = B, T
+    (d.in_channels, d.n_sqz, d.hidden, d.kernel_size, d.dilation_rate, d.n_layers, d.n_blocks, d.n_split,
+     d.sigmoid_scale, d.precision) = [int(v) for v in cfg[:10]]
+    if d.n_layers > GTK_MAX_LAYERS:
+        raise RuntimeError(f"glowtts_b200: n_layers {d.n_layers} > {GTK_MAX_LAYERS}")
+    return d
+
+
+def _blocks(cfg: Sequence[int], tensors: Sequence[Optional[Tensor]], cond: Optional[Tensor]):
+    """Fill an array of gtk_block_params (or gtk_block_grads) from the flat tensor list."""
+    L, NB, folded = int(cfg[5]), int(cfg[6]), bool(cfg[10])
+    per = params_per_block(L, folded)
+    if len(tensors) != per * NB:
+        raise RuntimeError(f"glowtts_b200: expected {per * NB} decoder tensors, got {len(tensors)}")
+    arr = (BlockParams * NB)()
+    ptr = lambda t: None if t is None else t.data_ptr()
+    for b in range(NB):
+        it = iter(tensors[b * per:(b + 1) * per])
+        P = arr[b]
+        P.an_logs, P.an_bias, P.ic_weight = ptr(next(it)), ptr(next(it)), ptr(next(it))
+        P.start_g = None if folded else ptr(next(it))
+        P.start_v, P.start_b = ptr(next(it)), ptr(next(it))
+        for name in ("in_g", "in_v", "in_b", "rs_g", "rs_v", "rs_b"):
+            fld = getattr(P, name)
+            for i in range(L):
+                fld[i] = None if (folded and name.endswith("_g")) else ptr(next(it))
+        P.end_w, P.end_b = ptr(next(it)), ptr(next(it))
+        P.cond = None if cond is None else cond[b].data_ptr()
+    return arr
+
+
+def grad_layout(params: Sequence[Tensor]):
+    """Offsets (16-byte aligned), sizes and total length of the flat gradient buffer of decoder_backward."""
+    offs, sizes, tot = [], [], 0
+    for p in params:
+        n = p.numel()
+        offs.append(tot)
+        sizes.append(n)
+        tot += (n + 3) // 4 * 4
+    return offs, sizes, tot
+
+
+def _chk_list(ts: Sequence[Tensor], name: str) -> List[Tensor]:
+    return [_chk(t, f"{name}[{i}]") for i, t in enumerate(ts)]
+
+
+@torch.library.custom_op(f"{NS}::decoder_forward", mutates_args=(), device_types="cuda")
+def decoder_forward(x: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], cfg: List[int],
+                    train: bool) -> Tuple[Tensor, Tensor, Tensor]:
+    """FlowSpecDecoder.forward(reverse=False) (models.py:765-785).  x [B,in,T], mask [B,T], cond [NB,B,2H*L] or None
+    -> (z [B,in,(T//n)*n], logdet [B], workspace kept for the backward)."""
+    x, mask = _chk(x, "x"), _chk(mask, "mask")
+    params = _chk_list(params, "params")
+    cond = _opt(cond, "cond")
+    B, Cin, T = x.shape
+    d = _desc(cfg, B, T)
+    lib = _lib.load()
+    ws_bytes = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), int(train))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+    Tz = (T // d.n_sqz) * d.n_sqz
+    z = torch.empty(B, Cin, Tz, dtype=x.dtype, device=x.device)
+    logdet = torch.empty(B, dtype=x.dtype, device=x.device)
+    blocks = _blocks(cfg, params, cond)
+    _lib.call("gtk_decoder_forward", ctypes.byref(d), blocks, _p(x), _p(mask), _p(z), _p(logdet), _p(ws), ws_bytes,
+              int(train), _stream())
+    if not train:
+        ws = ws.new_empty(0)
+    return z, logdet, ws
+
+
+@decoder_forward.register_fake
+def _(x, mask, params, cond, cfg, train):
+    B, Cin, T = x.shape
+    n = cfg[1]
+    return x.new_empty((B, Cin, (T // n) * n)), x.new_empty((B,)), x.new_empty((0,), dtype=torch.uint8)
+
+
+@torch.library.custom_op(f"{NS}::decoder_reverse", mutates_args=(), device_types="cuda")
+def decoder_reverse(z: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], cfg: List[int]) -> Tensor:
+    """FlowSpecDecoder.forward(reverse=True) (models.py:765-785)."""
+    z, mask = _chk(z, "z"), _chk(mask, "mask")
+    params = _chk_list(params, "params")
+    cond = _opt(cond, "cond")
+    B, Cin, T = z.shape
+    d = _desc(cfg, B, T)
+    lib = _lib.load()
+    ws_bytes = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), 0)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=z.device)
+    Tz = (T // d.n_sqz) * d.n_sqz
+    x = torch.empty(B, Cin, Tz, dtype=z.dtype, device=z.device)
+    blocks = _blocks(cfg, params, cond)
+    _lib.call("gtk_decoder_reverse", ctypes.byref(d), blocks, _p(z), _p(mask), _p(x), _p(ws), ws_bytes, _stream())
+    return x
+
+
+@decoder_reverse.register_fake
+def _(z, mask, params, cond, cfg):
+    B, Cin, T = z.shape
+    n = cfg[1]
+    return z.new_empty((B, Cin, (T // n) * n))
+
+
+@torch.library.custom_op(f"{NS}::decoder_backward", mutates_args=(), device_types="cuda")
+def decoder_backward(dz: Tensor, dlogdet: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], ws: Tensor,
+                     cfg: List[int], T: int) -> Tuple[Tensor, Tensor, Tensor]:
+    """Backward of decoder_forward(train=True) -> (dx [B,in,T], flat parameter grads (see grad_layout), dcond)."""
+    dz, dlogdet, mask = _chk(dz, "dz"), _chk(dlogdet, "dlogdet"), _chk(mask, "mask")
+    params = _chk_list(params, "params")
+    cond = _opt(cond, "cond")
+    B, Cin = dz.shape[0], dz.shape[1]
+    d = _desc(cfg, B, T)
+    dx = torch.empty(B, Cin, T, dtype=dz.dtype, device=dz.device)
+    # one flat zero-initialised gradient buffer, viewed per parameter (one memset instead of ~430)
+    offs, sizes, tot = grad_layout(params)
+    flat = torch.zeros(tot, dtype=dz.dtype, device=dz.device)
+    grads = [flat[o:o + s].view(p.shape) for o, s, p in zip(offs, sizes, params)]
+    dcond = torch.zeros_like(cond) if cond is not None else dz.new_empty(0)
+    blocks = _blocks(cfg, params, cond)
+    gblocks = _blocks(cfg, grads, dcond if cond is not None else None)
+    _lib.call("gtk_decoder_backward", ctypes.byref(d), blocks, gblocks, _p(mask), _p(dz), _p(dlogdet), _p(dx), _p(ws),
+              ws.numel(), _stream())
+    return dx, flat, dcond
+
+
+@decoder_backward.register_fake
+def _(dz, dlogdet, mask, params, cond, ws, cfg, T):
+    return (dz.new_empty((dz.shape[0], dz.shape[1], T)), dz.new_empty((grad_layout(params)[2],)),
+            torch.empty_like(cond) if cond is not None else dz.new_empty(0))
+
+
+def _dec_setup(ctx, inputs, output):
+    x, mask, params, cond, cfg, train = inputs
+    ctx.save_for_backward(mask, cond, output[2], *params)
+    ctx.cfg, ctx.T, ctx.train, ctx.has_cond = list(cfg), x.shape[2], train, cond is not None
+
+
+def _dec_bwd(ctx, dz, dlogdet, dws):
+    if not ctx.train:
+        raise RuntimeError("glowtts_b200: decoder_forward was run with train=False; no activations were kept")
+    mask, cond, ws, *params = ctx.saved_tensors
+    B = mask.shape[0]
+    if dz is None:
+        Tz = (ctx.T // ctx.cfg[1]) * ctx.cfg[1]
+        dz = torch.zeros(B, ctx.cfg[0], Tz, dtype=mask.dtype, device=mask.device)
+    if dlogdet is None:
+        dlogdet = torch.zeros(B, dtype=mask.dtype, device=mask.device)
+    dx, flat, dcond = decoder_backward(dz.contiguous(), dlogdet.contiguous(), mask, list(params), cond, ws, ctx.cfg, ctx.T)
+    offs, sizes, _ = grad_layout(params)
+    grads = [flat[o:o + n].view(p.shape) for o, n, p in zip(offs, sizes, params)]
+    return dx, None, grads, (dcond if ctx.has_cond else None), None, None
+
+
+decoder_forward.register_autograd(_dec_bwd, setup_context=_dec_setup)
