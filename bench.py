@@ -1,0 +1,419 @@
+#!/usr/bin/env python
+"""bench.py -- the Glow-TTS train-step hot path on B200 (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one pass of the hot path over one synthetic batch (configs/base.json sizes, B=32 per GPU):
+decoder forward -> logp -> MAS -> prior gather -> mle_loss -> decoder backward (+ fused AdamW on the decoder
+parameters; + NCCL all-reduce of the flat decoder gradient when N > 1).  One JSON line is printed by rank 0.
+
+* value      : mel frames/s over all ranks with the batch already resident in HBM.
+* e2e        : the same metric with the step's inputs copied from pinned host memory and the loss read back
+               inside the timed region (through glowtts_b200.hot_path.train_hot_path, the user-facing call).
+* roofline   : the dominant kernel family (the WaveNet convolutions), timed with CUDA events around every
+               launch by the library's own profiler (gtk_prof_*) in a separate pass of the same steps.
+* mas        : the MAS kernel alone on configs[0] (B=32, T_x=180, T_y=860) and its HBM roofline.
+* cpu_baseline: the CPU restatement (oracle/) on a bounded sample, host cores of this box.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+# ---- workload: configs/base.json "model" section (reference configs/base.json:32-51) + BASELINE configs[1]
+CFG = dict(in_channels=80, hidden_channels=192, kernel_size=5, dilation_rate=1, n_blocks=12, n_layers=4,
+           n_split=4, n_sqz=2, gin_channels=0)
+B_PER_GPU, T_TEXT, T_MEL = 32, 180, 860
+FLOP_PER_SQ_FRAME_FWD = 2 * (192 * 80 + 4 * (384 * 192 * 5) + 3 * (384 * 192) + 192 * 192 + 160 * 192)  # one block
+SEED = 1234  # configs/base.json:5
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return dict(hbm=p["hbm_gbs"], tc_burst=p["bf16_tflops"], tc_sustained=p["bf16_tflops_sustained"], src="measured")
+    except Exception:
+        return dict(hbm=6650.0, tc_burst=1590.0, tc_sustained=1400.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc, self.thread = [], None, None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        def pump():
+            for line in self.proc.stdout:
+                self.rows.append(line.strip())
+        self.thread = threading.Thread(target=pump, daemon=True)
+        self.thread.start()
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        # median of the upper half = clocks under load (the sampler also sees the idle gaps)
+        med = sm[len(sm) * 3 // 4] if sm else None
+        return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def synth_batch(B: int, gen: torch.Generator, pin: bool = True):
+    """LJSpeech-shaped synthetic batch (host, pinned)."""
+    y = (torch.randn(B, CFG["in_channels"], T_MEL, generator=gen) - 5.0)
+    y_len = (torch.randint(T_MEL // 2, T_MEL + 1, (B,), generator=gen) // 2) * 2
+    y_len[0] = T_MEL
+    x_m = torch.randn(B, CFG["in_channels"], T_TEXT, generator=gen) * 0.5
+    x_len = torch.randint(T_TEXT // 2, T_TEXT + 1, (B,), generator=gen)
+    x_len[0] = T_TEXT
+    x_len = torch.minimum(x_len, y_len)
+    mask = (torch.arange(T_MEL)[None, :] < y_len[:, None]).float().unsqueeze(1)
+    y = y * mask
+    return [t.pin_memory() if pin else t for t in (y, y_len, x_m, x_len)]
+
+
+def build_decoder(device, precision):
+    from glowtts_b200 import models
+    torch.manual_seed(SEED)
+    dec = models.FlowSpecDecoder(CFG["in_channels"], CFG["hidden_channels"], CFG["kernel_size"], CFG["dilation_rate"],
+                                 CFG["n_blocks"], CFG["n_layers"], p_dropout=0.0, n_split=CFG["n_split"],
+                                 n_sqz=CFG["n_sqz"], gin_channels=CFG["gin_channels"], precision=precision)
+    with torch.no_grad():
+        for b in range(CFG["n_blocks"]):          # non-trivial couplings (the reference starts them at zero)
+            dec.flows[3 * b + 2].end.weight.normal_(0, 0.01)
+    return dec.to(device)
+
+
+class Runner:
+    """Holds the resident model/optimizer and runs one step, device-resident or end to end."""
+
+    def __init__(self, device, world, precision):
+        from glowtts_b200 import ops
+        self.device, self.world = device, world
+        self.dec = build_decoder(device, precision)
+        self.opt = torch.optim.AdamW(self.dec.parameters(), lr=1e-4, fused=True)
+        gen = torch.Generator().manual_seed(SEED + int(os.environ.get("RANK", "0")))
+        self.host = synth_batch(B_PER_GPU, gen)
+        self.dev = [t.to(device) for t in self.host]
+        self.frames = int(self.host[1].sum())
+        self.cells = int((self.host[1] * self.host[3]).sum())
+        self.loss_host = torch.empty((), pin_memory=True)
+        if world > 1:
+            import torch.distributed as dist
+            ops.set_grad_sync(dist.group.WORLD)
+
+    def step(self, batch):
+        from glowtts_b200.hot_path import train_hot_path
+        y, y_len, x_m, x_len = batch
+        self.opt.zero_grad(set_to_none=True)
+        out = train_hot_path(self.dec, y, y_len, x_m, None, x_len)
+        out.loss.backward()
+        self.opt.step()
+        return out.loss
+
+    def step_resident(self):
+        return self.step(self.dev)
+
+    def step_e2e(self):
+        batch = [t.to(self.device, non_blocking=True) for t in self.host]
+        loss = self.step(batch)
+        self.loss_host.copy_(loss.detach(), non_blocking=True)
+        return loss
+
+    @property
+    def h2d_bytes(self):
+        return sum(t.numel() * t.element_size() for t in self.host)
+
+
+def barrier_sync(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def timed(fn, steps, world):
+    """EXACTLY `steps` calls between barrier+synchronize pairs, CUDA events on the current stream,
+    max over ranks -> ms total."""
+    barrier_sync(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    barrier_sync(world)
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def mas_alone(device, steps=20):
+    """configs[0]: maximum_path on synthetic fp32 logp, B=32, T_x=180, T_y=860, full lengths.  Rotates over
+    enough distinct inputs to exceed the 126 MB L2 between repeats."""
+    from glowtts_b200 import _lib, ops
+    B, TX, TY = 32, T_TEXT, T_MEL
+    gen = torch.Generator(device=device).manual_seed(SEED)
+    n_buf = 8                                                  # 8 x 19.8 MB value + 8 x 19.8 MB path > L2
+    vals = [torch.randn(B, TX, TY, device=device, generator=gen) for _ in range(n_buf)]
+    t_xs = torch.full((B,), TX, dtype=torch.int32, device=device)
+    t_ys = torch.full((B,), TY, dtype=torch.int32, device=device)
+    for i in range(3):
+        ops.mas_path(vals[i % n_buf], t_xs, t_ys)
+    torch.cuda.synchronize()
+    _lib.prof_enable(True)
+    for i in range(steps):
+        ops.mas_path(vals[i % n_buf], t_xs, t_ys)
+    torch.cuda.synchronize()
+    prof = _lib.prof_read()
+    _lib.prof_enable(False)
+    n, ms = prof.get("mas", (0, 0.0))
+    cells = B * TX * TY
+    per = ms / max(n, 1) * 1e-3
+    pk = peaks()
+    gbs = cells * 8 / per / 1e9 if per > 0 else 0.0
+    return {"workload": "maximum_path B=32 T_x=180 T_y=860 fp32, full lengths", "cells_per_s": cells / per if per else 0.0,
+            "us_per_call": per * 1e6, "launches_timed": n,
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
+                         "traffic": None, "algorithmic_bytes_per_cell": 8, "peak_source": pk["src"]},
+            "latency_floor_note": "T_y=860 dependent DP columns per utterance; 32 CTAs on 148 SMs"}
+
+
+# ------------------------------------------------------------------------------------------ CPU legs
+def cpu_hot_path_sample(b_sample: int, threads: int, mas_impl: str):
+    """One CPU pass of the same hot path on `b_sample` utterances of the workload, through the oracle
+    (torch CPU fp32 restatement of the reference modules + the C port / compiled reference core for MAS).
+    -> (frames, cells, seconds, seconds spent in MAS)."""
+    from oracle import flow as oflow
+    from oracle import mas as omas
+    import helpers
+
+    torch.set_num_threads(threads)
+    gen = torch.Generator().manual_seed(SEED)
+    y, y_len, x_m, x_len = synth_batch(b_sample, gen, pin=False)
+    sd = helpers.make_state_dict(dict(CFG), SEED, end_std=0.01)
+    sd = {k: v.requires_grad_(True) for k, v in sd.items() if ".wn_pitch." not in k and ".wn_energy." not in k}
+    mask = (torch.arange(T_MEL)[None, :] < y_len[:, None]).float().unsqueeze(1)
+    t0 = time.perf_counter()
+    z, logdet = oflow.decoder(sd, y, mask, hidden=CFG["hidden_channels"], dilation_rate=CFG["dilation_rate"],
+                              n_blocks=CFG["n_blocks"], n_layers=CFG["n_layers"], n_split=CFG["n_split"], n_sqz=CFG["n_sqz"])
+    with torch.no_grad():
+        lp = oflow.logp(x_m, torch.zeros_like(x_m), z)
+        x_mask = (torch.arange(T_TEXT)[None, :] < x_len[:, None]).float()
+        amask = x_mask[:, :, None] * mask
+        tm = time.perf_counter()
+        attn = omas.maximum_path(lp, amask, impl=mas_impl)       # the reference wrapper's steps, CPU tensors
+        t_mas = time.perf_counter() - tm
+        z_m, z_logs = oflow.expand_prior(attn, x_m, torch.zeros_like(x_m))
+    loss = oflow.mle_loss(z, z_m, z_logs, logdet, mask)
+    loss.backward()
+    dt = time.perf_counter() - t0
+    return int(y_len.sum()), int((y_len * x_len).sum()), dt, t_mas
+
+
+def cpu_baseline(budget_s: float = 20.0):
+    from oracle import mas as omas
+    threads = os.cpu_count() or 1
+    mas_impl = "ref" if omas.ref_core() is not None else "c_port"
+    frames, cells, dt, t_mas = cpu_hot_path_sample(1, threads, mas_impl)      # warm-up + calibration
+    b = max(1, min(B_PER_GPU, int(budget_s / max(dt, 1e-3))))
+    frames, cells, dt, t_mas = cpu_hot_path_sample(b, threads, mas_impl)
+    return {"value": frames / dt, "unit": "mel frames/s", "cores": threads,
+            "kind": "port", "sample": f"{b} of {B_PER_GPU} utterances of the same synthetic batch, 1 fwd+bwd pass "
+                                      f"({dt:.1f} s); torch CPU fp32 restatement of the reference modules with "
+                                      f"{threads} threads; MAS = {'the reference core.pyx compiled as shipped (serial)' if mas_impl == 'ref' else 'C port (serial)'}",
+            "mas_cells_per_s": cells / t_mas if t_mas > 0 else None, "mas_cores": 1}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path on this box's host cores.
+    /root/reference cannot travel to the GPU box, so the decoder/logp leg is the oracle port of the reference's
+    PyTorch modules (same torch CPU kernels) and MAS is the reference's own core.pyx compiled into oracle/_ref."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import mas as omas
+    threads = os.cpu_count() or 1
+    mas_impl = "ref" if omas.ref_core() is not None else "c_port"
+    _, _, dt1, _ = cpu_hot_path_sample(1, threads, mas_impl)
+    total = args.steps + args.warmup
+    b = max(1, min(B_PER_GPU, int(120.0 / max(total, 1) / max(dt1, 1e-3))))
+    for _ in range(args.warmup):
+        cpu_hot_path_sample(b, threads, mas_impl)
+    t_sum, frames_sum = 0.0, 0
+    for _ in range(args.steps):
+        frames, cells, dt, t_mas = cpu_hot_path_sample(b, threads, mas_impl)
+        t_sum += dt
+        frames_sum += frames
+    val = frames_sum / t_sum
+    sample = f"each step = {b} of {B_PER_GPU} utterances of the workload batch, fwd+bwd, {threads} threads"
+    print(json.dumps({
+        "impl": "reference", "metric": "train_hot_path_mel_frames_per_s", "value": val, "unit": "mel frames/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_sum / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(1, args.precision),
+        "cpu_baseline": {"value": val, "unit": "mel frames/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "mel frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def workload_config(world, precision):
+    return {"workload": "Glow-TTS configs/base.json train-step hot path: FlowSpecDecoder(80,192,k5,12 blocks,4 layers,"
+                        "n_sqz 2) fwd+bwd + logp + MAS + prior gather + mle_loss + AdamW; synthetic LJSpeech-shaped "
+                        "mels, ragged lengths",
+            "batch_per_gpu": B_PER_GPU, "global_batch": B_PER_GPU * world, "t_text": T_TEXT, "t_mel": T_MEL,
+            "precision": precision, "p_dropout": 0.0,
+            "l2": "per-step working set (activation workspace ~2.4 GB) exceeds the 126 MB L2",
+            "parallelism": f"dp{world} (batch sharded, one flat-gradient NCCL all-reduce per step)" if world > 1 else "single GPU"}
+
+
+# ------------------------------------------------------------------------------------------ main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default=os.environ.get("GTK_PRECISION", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+
+    from glowtts_b200 import _lib
+    _lib.load()
+    run = Runner(device, world, args.precision)
+
+    for _ in range(args.warmup):
+        run.step_e2e()
+    barrier_sync(world)
+
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    n0 = _lib.launch_count()
+    ms_res = timed(run.step_resident, args.steps, world)
+    launches = _lib.launch_count() - n0
+    ms_e2e = timed(run.step_e2e, args.steps, world)
+    clk = clocks.stop() if rank == 0 else None
+
+    # roofline pass: same steps with the library's event profiler on
+    _lib.prof_enable(True)
+    prof_steps = min(args.steps, 3)
+    for _ in range(prof_steps):
+        run.step_resident()
+    torch.cuda.synchronize()
+    prof = _lib.prof_read()
+    _lib.prof_enable(False)
+
+    frames = torch.tensor([run.frames], device=device, dtype=torch.float64)
+    cells = torch.tensor([run.cells], device=device, dtype=torch.float64)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(frames)
+        dist.all_reduce(cells)
+    frames_total, cells_total = float(frames.item()), float(cells.item())
+
+    if rank == 0:
+        pk = peaks()
+        s_res, s_e2e = ms_res / args.steps * 1e-3, ms_e2e / args.steps * 1e-3
+        # dominant kernel family: the k=5 WaveNet convolution (fwd + data-gradient launches share the kernel)
+        sq_frames_padded = B_PER_GPU * (T_MEL // 2)
+        tag = "conv_tc_kN" if "conv_tc_kN" in prof else "conv_f32_kN"
+        n_l, ms_l = prof.get(tag, (0, 0.0))
+        flop_per_launch = 2.0 * 384 * 192 * 5 * sq_frames_padded      # M=384, K=960, N=B*T' (padded frames are computed)
+        ach = (flop_per_launch * n_l / (ms_l * 1e-3) / 1e12) if ms_l > 0 else 0.0
+        step_ms_prof = sum(v[1] for v in prof.values()) / max(prof_steps, 1)
+        roof = {"kernel": tag, "bound": "tensor", "achieved": ach, "peak": pk["tc_sustained"], "unit": "TFLOP/s",
+                "frac": ach / pk["tc_sustained"], "traffic": None, "peak_source": pk["src"] + " bf16 sustained",
+                "launches_per_step": n_l / max(prof_steps, 1), "ms_per_launch": ms_l / max(n_l, 1),
+                "share_of_step": (ms_l / max(prof_steps, 1)) / (s_res * 1e3),
+                "flop_per_launch": flop_per_launch,
+                "how": f"CUDA events around every launch (library profiler), separate pass of {prof_steps} steps",
+                "by_tag_ms_per_step": {k: v[1] / max(prof_steps, 1) for k, v in sorted(prof.items())}}
+        step_flop = 3.0 * FLOP_PER_SQ_FRAME_FWD * CFG["n_blocks"] * sq_frames_padded
+        out = {
+            "metric": "train_hot_path_mel_frames_per_s", "value": frames_total / s_res, "unit": "mel frames/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": s_res * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if args.precision == "fp32" else "bf16 (fp32 accumulate)", "data": "synthetic",
+            "config": workload_config(world, args.precision),
+            "e2e": {"value": frames_total / s_e2e, "unit": "mel frames/s", "ms_per_step": s_e2e * 1e3,
+                    "h2d_bytes_per_step": run.h2d_bytes, "d2h_bytes_per_step": 4},
+            "gpu_launches": int(launches),
+            "mas_cells_per_step": cells_total, "step_tflops": step_flop * world / s_res / 1e12,
+            "roofline": roof, "clocks": clk,
+        }
+        out["mas"] = mas_alone(device)
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                out["cpu_baseline"] = cpu_baseline()
+            except Exception as e:  # the oracle is a checker; its absence must not hide the GPU numbers
+                out["cpu_baseline"] = {"value": None, "error": repr(e)}
+        print(json.dumps(out))
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

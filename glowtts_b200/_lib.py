@@ -41,10 +41,10 @@ BlockGrads = BlockParams
 
 _CTYPES = {
     "int": ctypes.c_int, "size_t": ctypes.c_size_t, "float": ctypes.c_float,
-    "void": None, "const char*": ctypes.c_char_p,
+    "void": None, "const char*": ctypes.c_char_p, "unsigned long long": ctypes.c_ulonglong,
 }
 
-_PROTO = re.compile(r"^\s*(int|size_t|const char\*)\s+(gtk_\w+)\s*\(([^;{]*)\)\s*;", re.M | re.S)
+_PROTO = re.compile(r"^\s*(int|size_t|const char\*|unsigned long long)\s+(gtk_\w+)\s*\(([^;{]*)\)\s*;", re.M | re.S)
 
 
 def parse_header(path: str = HEADER) -> Dict[str, Tuple[object, List[object]]]:
@@ -109,3 +109,26 @@ def call(name: str, *args):
         msg = lib.gtk_last_error()
         raise GtkError("%s failed (%d): %s" % (name, rc, msg.decode() if msg else ""))
     return rc
+
+
+# ---- launch counter / per-kernel timing (used by bench.py) ----------------------------------------
+def launch_count() -> int:
+    return int(load().gtk_launch_count())
+
+
+def prof_enable(on: bool) -> None:
+    call("gtk_prof_reset")
+    call("gtk_prof_enable", int(on))
+
+
+def prof_read() -> Dict[str, Tuple[int, float]]:
+    """-> {tag: (launches, total_ms)}; synchronises on the recorded events."""
+    lib = load()
+    out = {}
+    for i in range(lib.gtk_prof_tag_count()):
+        name = ctypes.create_string_buffer(64)
+        n, ms = ctypes.c_int(0), ctypes.c_float(0.0)
+        call("gtk_prof_read", i, name, 64, ctypes.byref(n), ctypes.byref(ms))
+        if n.value:
+            out[name.value.decode()] = (n.value, ms.value)
+    return out

@@ -1,0 +1,62 @@
+"""Drop-ins for the hot-path helpers of the reference's commons.py, on the CUDA library."""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import ops
+
+
+def fused_add_tanh_sigmoid_multiply(input_a, input_b, n_channels=None):
+    """commons.py:61-68: tanh((a+b)[:, :n]) * sigmoid((a+b)[:, n:]).  ``n_channels`` (the
+    reference passes a 1-element IntTensor) must equal half of a's channels when given."""
+    if n_channels is not None:
+        n = int(n_channels[0]) if hasattr(n_channels, "__getitem__") else int(n_channels)
+        assert 2 * n == input_a.shape[1], "n_channels must be half of input_a's channels"
+    if input_b is not None and input_b.shape != input_a.shape and input_b.shape[-1] != 1:
+        input_b = input_b.expand_as(input_a)
+    return ops.gate_fwd(input_a, input_b)
+
+
+def _mask2d(x_mask: Optional[torch.Tensor]):
+    return None if x_mask is None else x_mask.reshape(x_mask.shape[0], x_mask.shape[-1])
+
+
+def squeeze(x, x_mask=None, n_sqz=2):
+    """commons.py:339-351 -> (x_sqz [b, c*n, t//n], mask [b, 1, t//n])."""
+    out, m = ops.squeeze_op(x, _mask2d(x_mask), n_sqz)
+    if x_mask is None:
+        m = torch.ones_like(m)
+    return out, m.unsqueeze(1)
+
+
+def unsqueeze(x, x_mask=None, n_sqz=2):
+    """commons.py:354-364 -> (x_unsqz [b, c//n, t*n], mask [b, 1, t*n])."""
+    out, m = ops.unsqueeze_op(x, _mask2d(x_mask), n_sqz)
+    if x_mask is None:
+        m = torch.ones_like(m)
+    return out, m.unsqueeze(1)
+
+
+def mle_loss(z, m, logs, logdet, mask):
+    """commons.py:28-33."""
+    loss, _ = ops.mle_loss_fwd(z, m, logs, logdet, _mask2d(mask))
+    return loss
+
+
+def generate_path(duration, mask):
+    """commons.py:127-143: duration [b, t_x], mask [b, t_x, t_y] -> path [b, t_x, t_y]."""
+    return ops.generate_path(duration.to(torch.float32), mask.to(torch.float32)).to(mask.dtype)
+
+
+def logp(x_m, x_logs, z):
+    """The inline block models.py:1076-1082 as a function: -> [b, t_x, t_y]."""
+    with torch.no_grad():
+        return ops.logp(x_m, x_logs, z)
+
+
+def expand_prior(x_m, x_logs, index):
+    """models.py:1118-1119 (attn^T x_m, attn^T x_logs) as a gather by the per-frame token index."""
+    t_y = index.shape[1]
+    return ops.gather_tokens(x_m, index, t_y), ops.gather_tokens(x_logs, index, t_y)

@@ -2,6 +2,11 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <atomic>
+#include <mutex>
+#include <string>
+#include <vector>
+
 #include "common.cuh"
 #include "ops.h"
 #include "../../include/glowtts_b200.h"
@@ -15,6 +20,45 @@ void set_error(const char* fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
+}
+
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+// ---- per-kernel event timing -------------------------------------------------------------------
+struct ProfTag {
+    std::string name;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> spans;
+    size_t used = 0;
+};
+static std::mutex g_prof_mu;
+static std::vector<ProfTag> g_prof;
+static std::atomic<int> g_prof_on{0};
+
+static ProfTag* prof_tag(const char* tag) {
+    for (auto& t : g_prof)
+        if (t.name == tag) return &t;
+    g_prof.emplace_back();
+    g_prof.back().name = tag;
+    return &g_prof.back();
+}
+void prof_begin(const char* tag, cudaStream_t st) {
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    ProfTag* t = prof_tag(tag);
+    if (t->used == t->spans.size()) {
+        cudaEvent_t a, b;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        t->spans.emplace_back(a, b);
+    }
+    cudaEventRecord(t->spans[t->used].first, st);
+}
+void prof_end(const char* tag, cudaStream_t st) {
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    ProfTag* t = prof_tag(tag);
+    if (t->used < t->spans.size()) cudaEventRecord(t->spans[t->used++].second, st);
 }
 
 int sm_count() {
@@ -47,6 +91,37 @@ extern "C" {
 
 int gtk_abi_version(void) { return 1; }
 const char* gtk_last_error(void) { return g_err; }
+unsigned long long gtk_launch_count(void) { return g_launches.load(); }
+
+int gtk_prof_enable(int on) {
+    g_prof_on.store(on ? 1 : 0);
+    return GTK_OK;
+}
+int gtk_prof_reset(void) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    for (auto& t : g_prof) t.used = 0;
+    return GTK_OK;
+}
+int gtk_prof_tag_count(void) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    return (int)g_prof.size();
+}
+int gtk_prof_read(int i, char* name, int name_cap, int* launches, float* total_ms) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    if (i < 0 || i >= (int)g_prof.size() || !name || !launches || !total_ms) return GTK_ERR_INVALID;
+    ProfTag& t = g_prof[i];
+    snprintf(name, name_cap, "%s", t.name.c_str());
+    float tot = 0.f;
+    for (size_t k = 0; k < t.used; ++k) {
+        GTK_CUDA(cudaEventSynchronize(t.spans[k].second));
+        float ms = 0.f;
+        GTK_CUDA(cudaEventElapsedTime(&ms, t.spans[k].first, t.spans[k].second));
+        tot += ms;
+    }
+    *launches = (int)t.used;
+    *total_ms = tot;
+    return GTK_OK;
+}
 
 int gtk_mas_lengths_from_mask(const float* mask, int32_t* t_xs, int32_t* t_ys, int B, int T_x, int T_y, void* stream) {
     return mas::lengths_from_mask(mask, t_xs, t_ys, B, T_x, T_y, ST);

@@ -15,7 +15,20 @@ namespace gtk {
 
 void set_error(const char* fmt, ...);   // thread-local message for gtk_last_error()
 
+void count_launch();                    // bumps the library's kernel-launch counter (gtk_launch_count)
+
+// Optional per-kernel timing (gtk_prof_*): when enabled, a ProfScope around a launch records a CUDA event
+// pair on the launching stream under `tag`; bench.py reads the totals for the roofline numbers.
+void prof_begin(const char* tag, cudaStream_t st);
+void prof_end(const char* tag, cudaStream_t st);
+struct ProfScope {
+    const char* tag; cudaStream_t st;
+    ProfScope(const char* t, cudaStream_t s) : tag(t), st(s) { prof_begin(tag, st); }
+    ~ProfScope() { prof_end(tag, st); }
+};
+
 inline int check_launch(const char* what) {
+    count_launch();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         set_error("%s: %s", what, cudaGetErrorString(e));

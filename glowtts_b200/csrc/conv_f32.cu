@@ -121,6 +121,7 @@ int conv1d_f32(const ConvParams& p, cudaStream_t st) {
     if (smem > 48 * 1024)
         GTK_CUDA(cudaFuncSetAttribute(conv1d_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(ceil_div(p.T, BT), ceil_div(p.M, BM), p.B);
+    ProfScope prof(p.K > 1 ? "conv_f32_kN" : "conv_f32_k1", st);
     conv1d_f32_kernel<<<grid, NT, smem, st>>>(p);
     return check_launch("conv1d_f32");
 }
@@ -202,6 +203,7 @@ static int wgrad_launch(const WgradParams& p, cudaStream_t st) {
     const int gx = ceil_div(p.M, BM), gy = ceil_div(p.Cin, BC);
     const int n_chunks = p.B * ceil_div(p.T, 64);
     int gz = max(1, min(n_chunks, (sm_count() * 4) / max(1, gx * gy)));
+    ProfScope prof(K > 1 ? "wgrad_f32_kN" : "wgrad_f32_k1", st);
     wgrad_f32_kernel<K><<<dim3(gx, gy, gz), NT, smem, st>>>(p);
     return check_launch("wgrad_f32");
 }

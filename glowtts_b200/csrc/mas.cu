@@ -363,6 +363,7 @@ size_t workspace_bytes(int B, int T_x, int T_y) {
 template <int XPT>
 static int launch_fast(const Params& p, size_t smem, cudaStream_t stream) {
     GTK_CUDA(cudaFuncSetAttribute(mas_kernel<XPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ProfScope prof("mas", stream);
     mas_kernel<XPT><<<p.B, NT, smem, stream>>>(p);
     return check_launch("mas_kernel");
 }
@@ -408,6 +409,7 @@ int forward(const float* value, const int* t_xs, const int* t_ys, float* path, i
         return GTK_ERR_UNSUPPORTED;
     }
     GTK_CUDA(cudaFuncSetAttribute(mas_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ProfScope prof("mas_generic", stream);
     mas_generic_kernel<<<B, GEN_NT, smem, stream>>>(p, static_cast<uint32_t*>(workspace));
     return check_launch("mas_generic_kernel");
 }

@@ -1,0 +1,56 @@
+"""The training-step hot path of FlowGenerator.forward (models.py:1075-1119) + commons.mle_loss
+(train_ms_emo_lang_pitch.py:295) as one host-side function over the library ops.
+
+    z, logdet = decoder(y, z_mask, g)                      models.py:1075
+    logp      = log N(z; x_m, exp(x_logs))                 models.py:1076-1082  (no_grad)
+    attn      = maximum_path(logp, attn_mask)              models.py:1083       (no_grad)
+    z_m,z_logs= attn^T x_m, attn^T x_logs                  models.py:1118-1119  (as a gather)
+    loss      = mle_loss(z, z_m, z_logs, logdet, z_mask)   commons.py:28-33
+
+The text encoder that produces x_m / x_logs is outside the path: they
+arrive as tensors (requires_grad allowed; their gradients flow back through the gather).
+"""
+from __future__ import annotations
+
+from typing import NamedTuple, Optional
+
+import torch
+
+from . import commons, ops
+
+
+class HotPathOut(NamedTuple):
+    loss: torch.Tensor
+    z: torch.Tensor
+    logdet: torch.Tensor
+    attn: Optional[torch.Tensor]      # [B,T_x,T_y] 0/1 (None unless asked for)
+    durations: torch.Tensor           # int32 [B,T_x]  (= attn.sum(2), models.py:1085)
+    index: torch.Tensor               # int32 [B,T_y]  token per frame, -1 in the padding
+
+
+def sequence_mask(length: torch.Tensor, max_length: int) -> torch.Tensor:
+    """commons.py:82-86 -> bool [B, max_length]."""
+    return torch.arange(max_length, device=length.device)[None, :] < length[:, None]
+
+
+def train_hot_path(decoder, y, y_lengths, x_m, x_logs, x_lengths, g=None, return_attn=False) -> HotPathOut:
+    """y [B,80,T_y] mel, y_lengths [B] (multiples of n_sqz, models.py:1052-1053), x_m / x_logs [B,80,T_x]
+    (x_logs None = mean_only), x_lengths [B]."""
+    n = decoder.n_sqz
+    T_y = (y.shape[2] // n) * n
+    y = y[:, :, :T_y]
+    z_mask = sequence_mask(y_lengths, T_y).to(y.dtype).unsqueeze(1)                     # models.py:1054
+    z, logdet = decoder(y, z_mask, g=g)
+    with torch.no_grad():
+        lp = ops.logp(x_m.detach(), None if x_logs is None else x_logs.detach(), z.detach())
+        t_xs = x_lengths.to(torch.int32)
+        t_ys = y_lengths.to(torch.int32)
+        if return_attn:
+            x_mask = sequence_mask(x_lengths, x_m.shape[2]).to(y.dtype)
+            lp = lp * (x_mask[:, :, None] * z_mask)                                      # __init__.py:11
+        # the kernel only reads cells inside [0,t_x) x [0,t_y), so value*mask need not be materialised
+        attn, dur, idx = ops.mas_path(lp, t_xs, t_ys)
+    z_m = ops.gather_tokens(x_m, idx, T_y)
+    z_logs = None if x_logs is None else ops.gather_tokens(x_logs, idx, T_y)
+    loss = commons.mle_loss(z, z_m, z_logs, logdet, z_mask)
+    return HotPathOut(loss, z, logdet, attn if return_attn else None, dur, idx)

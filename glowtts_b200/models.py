@@ -1,0 +1,100 @@
+"""Drop-in for models.FlowSpecDecoder (models.py:719-789) on the CUDA library.
+
+The module tree (``flows.{3b}`` ActNorm, ``flows.{3b+1}`` InvConvNear, ``flows.{3b+2}``
+CouplingBlock) and therefore the state_dict keys match the reference; ``forward`` hands the whole
+stack to ONE library call (gtk_decoder_forward / _reverse; backward through gtk_decoder_backward).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+from torch import nn
+
+from . import attentions, modules, ops
+
+
+class FlowSpecDecoder(nn.Module):
+    def __init__(self, in_channels, hidden_channels, kernel_size, dilation_rate, n_blocks, n_layers, p_dropout=0.,
+                 n_split=4, n_sqz=2, sigmoid_scale=False, gin_channels=0, emoin_channels=0, precision="fp32"):
+        super().__init__()
+        self.in_channels = in_channels
+        self.hidden_channels = hidden_channels
+        self.kernel_size = kernel_size
+        self.dilation_rate = dilation_rate
+        self.n_blocks = n_blocks
+        self.n_layers = n_layers
+        self.p_dropout = p_dropout
+        self.n_split = n_split
+        self.n_sqz = n_sqz
+        self.sigmoid_scale = sigmoid_scale
+        self.gin_channels = gin_channels
+        self.emoin_channels = emoin_channels
+        self.precision = precision      # "fp32" (exact-parity CUDA-core path) | "bf16" (tcgen05 path)
+        self.flows = nn.ModuleList()
+        for _ in range(n_blocks):
+            self.flows.append(modules.ActNorm(channels=in_channels * n_sqz))
+            self.flows.append(modules.InvConvNear(channels=in_channels * n_sqz, n_split=n_split))
+            self.flows.append(attentions.CouplingBlock(
+                in_channels * n_sqz, hidden_channels, kernel_size=kernel_size, dilation_rate=dilation_rate,
+                n_layers=n_layers, gin_channels=gin_channels, emoin_channels=emoin_channels, p_dropout=p_dropout,
+                sigmoid_scale=sigmoid_scale, n_sqz=n_sqz))
+
+    # ---------------------------------------------------------------- fused call plumbing
+    def _cfg(self, folded: bool):
+        return [self.in_channels, self.n_sqz, self.hidden_channels, self.kernel_size, self.dilation_rate,
+                self.n_layers, self.n_blocks, self.n_split, int(bool(self.sigmoid_scale)),
+                {"fp32": 0, "bf16": 1}[self.precision], int(folded)]
+
+    def _params(self):
+        out, folded = [], None
+        for b in range(self.n_blocks):
+            p, f = attentions.block_param_list(self.flows[3 * b], self.flows[3 * b + 1], self.flows[3 * b + 2])
+            assert folded is None or folded == f
+            folded = f
+            out += p
+        return out, bool(folded)
+
+    def _cond(self, g: Optional[torch.Tensor]):
+        if g is None or self.gin_channels == 0:
+            return None
+        return torch.stack([self.flows[3 * b + 2].wn.conditioning(g) for b in range(self.n_blocks)], 0)
+
+    def forward(self, x, x_mask, g=None, emo=None, pitch=None, energy=None, reverse=False):
+        if pitch is not None or energy is not None:
+            raise NotImplementedError("glowtts_b200.FlowSpecDecoder: pitch/energy WaveNets are not built yet")
+        if self.training and self.p_dropout > 0 and not reverse:
+            raise RuntimeError("glowtts_b200.FlowSpecDecoder: p_dropout > 0 in training mode is not implemented")
+        for b in range(self.n_blocks):          # data-dependent init, if requested (init.py:17-23)
+            if not self.flows[3 * b].initialized:
+                return self._forward_unfused(x, x_mask, g, reverse)
+        params, folded = self._params()
+        mask2 = x_mask.reshape(x_mask.shape[0], x_mask.shape[-1]).to(torch.float32)
+        cond = self._cond(g)
+        cfg = self._cfg(folded)
+        if reverse:
+            with torch.no_grad():
+                return ops.decoder_reverse(x, mask2, [p.detach() for p in params], cond, cfg), None
+        train = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params))
+        z, logdet, _ = ops.decoder_forward(x, mask2, params, cond, cfg, train)
+        return z, logdet
+
+    def _forward_unfused(self, x, x_mask, g=None, reverse=False):
+        """Flow by flow through the module-level ops (used for the DDI pass, where ActNorm statistics must be
+        taken between flows)."""
+        from . import commons
+        flows = list(self.flows) if not reverse else list(reversed(self.flows))
+        logdet_tot = 0 if not reverse else None
+        if self.n_sqz > 1:
+            x, x_mask = commons.squeeze(x, x_mask, self.n_sqz)
+        for f in flows:
+            x, logdet = f(x, x_mask, g=g, reverse=reverse)
+            if not reverse:
+                logdet_tot = logdet_tot + logdet
+        if self.n_sqz > 1:
+            x, x_mask = commons.unsqueeze(x, x_mask, self.n_sqz)
+        return x, logdet_tot
+
+    def store_inverse(self):
+        for f in self.flows:
+            f.store_inverse()

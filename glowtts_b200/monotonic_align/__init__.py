@@ -1,0 +1,35 @@
+"""Drop-in for the reference's ``monotonic_align`` package (monotonic_align/__init__.py:6-21).
+
+``maximum_path(value, mask)`` keeps the reference signature and result (0/1 alignment in the
+input dtype on the input device) but never leaves the GPU: lengths come from the mask on the
+device and the DP + backtrack run in one sm_100a kernel (csrc/mas.cu).
+"""
+from __future__ import annotations
+
+import torch
+
+from .. import ops
+
+
+def maximum_path(value: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
+    """value, mask: [b, t_x, t_y] (mask a rectangular 0/1 prefix mask) -> path [b, t_x, t_y]."""
+    path, _, _ = maximum_path_full(value, mask)
+    return path
+
+
+def maximum_path_full(value: torch.Tensor, mask: torch.Tensor):
+    """As maximum_path, plus durations int32 [b, t_x] (= path.sum(2), models.py:1085) and the
+    per-frame token index int32 [b, t_y] (-1 in the padding) straight from the backtrack."""
+    dtype = value.dtype
+    with torch.no_grad():
+        v = (value * mask).to(torch.float32)          # __init__.py:11,14
+        t_xs, t_ys = ops.mas_lengths(mask.to(torch.float32))
+        path, dur, idx = ops.mas_path(v, t_xs, t_ys)
+    return path.to(dtype), dur, idx
+
+
+def maximum_path_lengths(value: torch.Tensor, t_xs: torch.Tensor, t_ys: torch.Tensor):
+    """core.pyx:40-45 entry (maximum_path_c) for callers that already hold the lengths:
+    value fp32 [b,t_x,t_y] (already masked), t_xs / t_ys int32 [b] on the device."""
+    with torch.no_grad():
+        return ops.mas_path(value, t_xs, t_ys)

@@ -559,6 +559,14 @@ def grad_layout(params: Sequence[Tensor]):
     return offs, sizes, tot
 
 
+def _fit_mask(mask: Tensor, T: int) -> Tensor:
+    """The library reads mask rows with the data tensor's row length; a longer mask (the reference squeezes a
+    [B,1,T] mask against a tensor already cut to a multiple of n_sqz, commons.py:342-348) is cut to match."""
+    if mask.shape[-1] < T:
+        raise RuntimeError(f"glowtts_b200: mask has {mask.shape[-1]} frames, data has {T}")
+    return mask if mask.shape[-1] == T else mask[..., :T]
+
+
 def _chk_list(ts: Sequence[Tensor], name: str) -> List[Tensor]:
     return [_chk(t, f"{name}[{i}]") for i, t in enumerate(ts)]
 
@@ -568,10 +576,11 @@ def decoder_forward(x: Tensor, mask: Tensor, params: List[Tensor], cond: Optiona
                     train: bool) -> Tuple[Tensor, Tensor, Tensor]:
     """FlowSpecDecoder.forward(reverse=False) (models.py:765-785).  x [B,in,T], mask [B,T], cond [NB,B,2H*L] or None
     -> (z [B,in,(T//n)*n], logdet [B], workspace kept for the backward)."""
-    x, mask = _chk(x, "x"), _chk(mask, "mask")
+    x = _chk(x, "x")
+    B, Cin, T = x.shape
+    mask = _chk(_fit_mask(mask, T), "mask")
     params = _chk_list(params, "params")
     cond = _opt(cond, "cond")
-    B, Cin, T = x.shape
     d = _desc(cfg, B, T)
     lib = _lib.load()
     ws_bytes = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), int(train))
@@ -597,10 +606,11 @@ def _(x, mask, params, cond, cfg, train):
 @torch.library.custom_op(f"{NS}::decoder_reverse", mutates_args=(), device_types="cuda")
 def decoder_reverse(z: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], cfg: List[int]) -> Tensor:
     """FlowSpecDecoder.forward(reverse=True) (models.py:765-785)."""
-    z, mask = _chk(z, "z"), _chk(mask, "mask")
+    z = _chk(z, "z")
+    B, Cin, T = z.shape
+    mask = _chk(_fit_mask(mask, T), "mask")
     params = _chk_list(params, "params")
     cond = _opt(cond, "cond")
-    B, Cin, T = z.shape
     d = _desc(cfg, B, T)
     lib = _lib.load()
     ws_bytes = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), 0)
@@ -623,7 +633,7 @@ def _(z, mask, params, cond, cfg):
 def decoder_backward(dz: Tensor, dlogdet: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], ws: Tensor,
                      cfg: List[int], T: int) -> Tuple[Tensor, Tensor, Tensor]:
     """Backward of decoder_forward(train=True) -> (dx [B,in,T], flat parameter grads (see grad_layout), dcond)."""
-    dz, dlogdet, mask = _chk(dz, "dz"), _chk(dlogdet, "dlogdet"), _chk(mask, "mask")
+    dz, dlogdet, mask = _chk(dz, "dz"), _chk(dlogdet, "dlogdet"), _chk(_fit_mask(mask, T), "mask")
     params = _chk_list(params, "params")
     cond = _opt(cond, "cond")
     B, Cin = dz.shape[0], dz.shape[1]
@@ -647,6 +657,15 @@ def _(dz, dlogdet, mask, params, cond, ws, cfg, T):
             torch.empty_like(cond) if cond is not None else dz.new_empty(0))
 
 
+_GRAD_SYNC = {"group": None}
+
+
+def set_grad_sync(group) -> None:
+    """Enable (group = a torch.distributed process group, or dist.group.WORLD) or disable (None) the
+    all-reduce of the decoder's flat gradient buffer inside the backward."""
+    _GRAD_SYNC["group"] = group
+
+
 def _dec_setup(ctx, inputs, output):
     x, mask, params, cond, cfg, train = inputs
     ctx.save_for_backward(mask, cond, output[2], *params)
@@ -664,9 +683,177 @@ def _dec_bwd(ctx, dz, dlogdet, dws):
     if dlogdet is None:
         dlogdet = torch.zeros(B, dtype=mask.dtype, device=mask.device)
     dx, flat, dcond = decoder_backward(dz.contiguous(), dlogdet.contiguous(), mask, list(params), cond, ws, ctx.cfg, ctx.T)
+    if _GRAD_SYNC["group"] is not None:
+        # data-parallel training (train_ms_emo_lang_pitch.py:166 DDP): ONE NCCL all-reduce over the flat
+        # gradient buffer the backward kernels wrote, averaged over ranks as DDP does.
+        import torch.distributed as dist
+        dist.all_reduce(flat, group=_GRAD_SYNC["group"])
+        flat.div_(dist.get_world_size(_GRAD_SYNC["group"]))
     offs, sizes, _ = grad_layout(params)
     grads = [flat[o:o + n].view(p.shape) for o, n, p in zip(offs, sizes, params)]
     return dx, None, grads, (dcond if ctx.has_cond else None), None, None
 
 
 decoder_forward.register_autograd(_dec_bwd, setup_context=_dec_setup)
+
+
+# =============================================================================== coupling-block pieces
+@torch.library.custom_op(f"{NS}::weightnorm_fwd", mutates_args=(), device_types="cuda")
+def weightnorm_fwd(g: Tensor, v: Tensor) -> Tensor:
+    """torch.nn.utils.weight_norm (dim=0): w[m] = g[m] v[m] / ||v[m]||  (modules.py:124,131,141)."""
+    g, v = _chk(g, "weight_g"), _chk(v, "weight_v")
+    M = v.shape[0]
+    w = torch.empty_like(v)
+    _lib.call("gtk_weightnorm_fwd", _p(g), _p(v), _p(w), None, M, v.numel() // M, _stream())
+    return w
+
+
+@weightnorm_fwd.register_fake
+def _(g, v):
+    return torch.empty_like(v)
+
+
+@torch.library.custom_op(f"{NS}::weightnorm_bwd", mutates_args=(), device_types="cuda")
+def weightnorm_bwd(g: Tensor, v: Tensor, dw: Tensor) -> Tuple[Tensor, Tensor]:
+    g, v, dw = _chk(g, "weight_g"), _chk(v, "weight_v"), _chk(dw, "dw")
+    M = v.shape[0]
+    dg, dv = torch.empty_like(g), torch.empty_like(v)
+    _lib.call("gtk_weightnorm_bwd", _p(g), _p(v), _p(dw), _p(dg), _p(dv), M, v.numel() // M, 0, _stream())
+    return dg, dv
+
+
+@weightnorm_bwd.register_fake
+def _(g, v, dw):
+    return torch.empty_like(g), torch.empty_like(v)
+
+
+def _wn_setup(ctx, inputs, output):
+    ctx.save_for_backward(*inputs)
+
+
+def _wn_bwd(ctx, dw):
+    g, v = ctx.saved_tensors
+    return weightnorm_bwd(g, v, dw.contiguous())
+
+
+weightnorm_fwd.register_autograd(_wn_bwd, setup_context=_wn_setup)
+
+
+def _conv_raw(x: Tensor, w: Tensor, bias: Optional[Tensor], dil: int, transpose: bool) -> Tensor:
+    B, Cin, T = x.shape
+    M, Cw, K = w.shape
+    if transpose:   # data gradient: contract over w's output channels
+        assert Cin == M
+        n_out, n_in = Cw, M
+    else:
+        assert Cin == Cw
+        n_out, n_in = M, Cw
+    wp = torch.empty(w.numel(), dtype=w.dtype, device=w.device)
+    _lib.call("gtk_conv1d_pack_weight", _p(w), _p(wp), M, Cw, K, int(transpose), _stream())
+    out = torch.empty(B, n_out, T, dtype=x.dtype, device=x.device)
+    _lib.call("gtk_conv1d", _p(x), _p(wp), _p(bias), None, None, _p(out), B, n_in, n_out, T, K, dil, 0, _stream())
+    return out
+
+
+@torch.library.custom_op(f"{NS}::conv1d", mutates_args=(), device_types="cuda")
+def conv1d(x: Tensor, w: Tensor, bias: Optional[Tensor], dilation: int) -> Tensor:
+    """F.conv1d(x, w, bias, padding=(K-1)*dil/2, dilation=dil), K odd.  x [B,Cin,T], w [M,Cin,K]."""
+    return _conv_raw(_chk(x, "x"), _chk(w, "weight"), _opt(bias, "bias"), dilation, False)
+
+
+@conv1d.register_fake
+def _(x, w, bias, dilation):
+    return x.new_empty((x.shape[0], w.shape[0], x.shape[2]))
+
+
+@torch.library.custom_op(f"{NS}::conv1d_bwd", mutates_args=(), device_types="cuda")
+def conv1d_bwd(x: Tensor, w: Tensor, dout: Tensor, dilation: int) -> Tuple[Tensor, Tensor, Tensor]:
+    """-> (dx, dw, dbias) of conv1d."""
+    x, w, dout = _chk(x, "x"), _chk(w, "weight"), _chk(dout, "dout")
+    B, Cin, T = x.shape
+    M, _, K = w.shape
+    dx = _conv_raw(dout, w, None, dilation, True)
+    dw = torch.zeros_like(w)
+    _lib.call("gtk_conv1d_wgrad", _p(dout), _p(x), None, _p(dw), B, Cin, M, T, K, dilation, 0, _stream())
+    db = torch.zeros(M, dtype=x.dtype, device=x.device)
+    _lib.call("gtk_channel_sum", _p(dout), _p(db), B, M, T, 0, _stream())
+    return dx, dw, db
+
+
+@conv1d_bwd.register_fake
+def _(x, w, dout, dilation):
+    return torch.empty_like(x), torch.empty_like(w), x.new_empty((w.shape[0],))
+
+
+def _conv_setup(ctx, inputs, output):
+    x, w, bias, dil = inputs
+    ctx.save_for_backward(x, w)
+    ctx.dil, ctx.has_bias = dil, bias is not None
+
+
+def _conv_bwd(ctx, dout):
+    x, w = ctx.saved_tensors
+    dx, dw, db = conv1d_bwd(x, w, dout.contiguous(), ctx.dil)
+    return dx, dw, (db if ctx.has_bias else None), None
+
+
+conv1d.register_autograd(_conv_bwd, setup_context=_conv_setup)
+
+
+@torch.library.custom_op(f"{NS}::coupling_affine", mutates_args=(), device_types="cuda")
+def coupling_affine(x: Tensor, end_out: Tensor, mask: Optional[Tensor], reverse: bool, sigmoid_scale: bool) -> Tuple[Tensor, Tensor]:
+    """attentions.py:172-183: end_out = [m | logs] -> (z = [x0 | affine(x1)], logdet [B] (zeros in reverse))."""
+    x, end_out = _chk(x, "x"), _chk(end_out, "end_out")
+    mask = _opt(mask, "mask")
+    B, C, T = x.shape
+    z = torch.empty_like(x)
+    logdet = torch.zeros(B, dtype=x.dtype, device=x.device)
+    _lib.call("gtk_coupling_affine", _p(x), _p(end_out), _p(mask), _p(z), _p(logdet), B, C, T, int(reverse),
+              int(sigmoid_scale), _stream())
+    return z, logdet
+
+
+@coupling_affine.register_fake
+def _(x, end_out, mask, reverse, sigmoid_scale):
+    return torch.empty_like(x), x.new_empty((x.shape[0],))
+
+
+@torch.library.custom_op(f"{NS}::coupling_affine_bwd", mutates_args=(), device_types="cuda")
+def coupling_affine_bwd(x: Tensor, end_out: Tensor, mask: Optional[Tensor], dz: Tensor, dlogdet: Tensor,
+                        sigmoid_scale: bool) -> Tuple[Tensor, Tensor]:
+    """-> (d end_out, dx) of the forward affine (dx0 = dz0 passthrough, dx1 = dz1 e^logs mask)."""
+    x, end_out, dz, dlogdet = _chk(x, "x"), _chk(end_out, "end_out"), _chk(dz, "dz"), _chk(dlogdet, "dlogdet")
+    mask = _opt(mask, "mask")
+    B, C, T = x.shape
+    dend = torch.empty_like(end_out)
+    dx = torch.empty_like(x)
+    _lib.call("gtk_coupling_affine_bwd", _p(x), _p(end_out), _p(mask), _p(dz), _p(dlogdet), _p(dend), _p(dx), B, C, T,
+              int(sigmoid_scale), _stream())
+    dx[:, : C // 2].copy_(dz[:, : C // 2])
+    return dend, dx
+
+
+@coupling_affine_bwd.register_fake
+def _(x, end_out, mask, dz, dlogdet, sigmoid_scale):
+    return torch.empty_like(end_out), torch.empty_like(x)
+
+
+def _aff_setup(ctx, inputs, output):
+    x, end_out, mask, reverse, sigmoid_scale = inputs
+    ctx.save_for_backward(x, end_out, mask)
+    ctx.reverse, ctx.sigmoid_scale = reverse, sigmoid_scale
+
+
+def _aff_bwd(ctx, dz, dlogdet):
+    if ctx.reverse:
+        raise RuntimeError("glowtts_b200: the reverse flow is inference-only (no backward)")
+    x, end_out, mask = ctx.saved_tensors
+    if dz is None:
+        dz = torch.zeros_like(x)
+    if dlogdet is None:
+        dlogdet = torch.zeros(x.shape[0], dtype=x.dtype, device=x.device)
+    dend, dx = coupling_affine_bwd(x, end_out, mask, dz.contiguous(), dlogdet.contiguous(), ctx.sigmoid_scale)
+    return dx, dend, None, None, None
+
+
+coupling_affine.register_autograd(_aff_bwd, setup_context=_aff_setup)

@@ -33,6 +33,15 @@ extern "C" {
 /* ---- library ---------------------------------------------------------------------------- */
 int gtk_abi_version(void);
 const char* gtk_last_error(void); /* thread-local, valid until the next failing call */
+/* Kernels launched by this library in this process so far (bench.py's gpu_launches). */
+unsigned long long gtk_launch_count(void);
+/* Per-kernel device timing for the roofline report: while enabled, the hot kernels' launches are
+ * bracketed by CUDA events on their stream, grouped under a tag.  gtk_prof_read synchronises on the
+ * recorded events of tag i and returns the number of launches and their summed duration. */
+int gtk_prof_enable(int on);
+int gtk_prof_reset(void);
+int gtk_prof_tag_count(void);
+int gtk_prof_read(int i, char* name, int name_cap, int* launches, float* total_ms);
 
 /* ---- monotonic alignment search --------------------------------------------------------- */
 /* Replaces monotonic_align/__init__.py:18-19 (t_x = mask.sum(1)[:,0], t_y = mask.sum(2)[:,0])

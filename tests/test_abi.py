@@ -1,0 +1,66 @@
+"""CPU-side checks of the boundary: the C-ABI library builds, loads and exports every symbol
+include/glowtts_b200.h declares; the product package refuses to run without CUDA tensors."""
+import ctypes
+import os
+
+import pytest
+import torch
+
+from glowtts_b200 import _lib
+
+
+def test_header_declares_the_expected_surface():
+    syms = _lib.declared_symbols()
+    for must in ("gtk_mas_forward", "gtk_mas_lengths_from_mask", "gtk_logp", "gtk_decoder_forward",
+                 "gtk_decoder_reverse", "gtk_decoder_backward", "gtk_flow_mix", "gtk_gate_fwd",
+                 "gtk_coupling_affine", "gtk_mle_loss_fwd", "gtk_generate_path"):
+        assert must in syms
+    assert len(syms) >= 35
+
+
+def test_library_exports_every_declared_symbol():
+    if not os.path.exists(_lib.LIB_PATH):
+        from glowtts_b200 import build
+        build.build()
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in _lib.declared_symbols():
+        assert hasattr(lib, name), name
+    loaded = _lib.load()
+    assert loaded.gtk_abi_version() >= 1
+
+
+def test_workspace_queries_run_without_a_gpu():
+    lib = _lib.load()
+    assert lib.gtk_mas_workspace_bytes(32, 180, 860) == 0          # decision bits fit in shared memory
+    assert lib.gtk_mas_workspace_bytes(2, 2000, 4000) > 0          # generic path needs a workspace
+    d = _lib.DecoderDesc(B=2, in_channels=80, T=100, n_sqz=2, hidden=192, kernel_size=5, dilation_rate=1,
+                         n_layers=4, n_blocks=12, n_split=4, sigmoid_scale=0, precision=0)
+    infer = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), 0)
+    train = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), 1)
+    assert 0 < infer < train
+
+
+def test_no_cpu_fallback():
+    from glowtts_b200 import monotonic_align, ops
+    v = torch.zeros(1, 3, 5)
+    with pytest.raises((RuntimeError, NotImplementedError)):
+        monotonic_align.maximum_path(v, torch.ones_like(v))
+    with pytest.raises((RuntimeError, NotImplementedError)):
+        ops.gate_fwd(torch.zeros(1, 4, 3), None)
+
+
+def test_state_dict_keys_match_reference_names():
+    import helpers
+    from glowtts_b200 import models
+    dec = models.FlowSpecDecoder(80, 192, 5, 1, 12, 4, p_dropout=0.05, n_split=4, n_sqz=2, gin_channels=256)
+    want = {k for k in helpers.decoder_param_shapes(dict(helpers.BASE_CFG, gin_channels=256))
+            if ".wn_pitch." not in k and ".wn_energy." not in k}
+    got = dict(dec.state_dict())
+    assert set(got) == want
+    shapes = helpers.decoder_param_shapes(dict(helpers.BASE_CFG, gin_channels=256))
+    for k, v in got.items():
+        assert tuple(v.shape) == tuple(shapes[k]), k
+    dec.store_inverse()
+    keys = set(dec.state_dict())
+    assert "flows.2.wn.in_layers.0.weight" in keys and "flows.2.wn.in_layers.0.weight_g" not in keys
+    assert "flows.2.start.weight_g" in keys      # attentions.py:188-194 folds only the WaveNets

@@ -1,0 +1,233 @@
+"""GPU parity of the flow decoder path (fp32 CUDA path through the C ABI) against the committed
+fixtures made by the REFERENCE modules and against the CPU oracle (oracle/flow.py).
+Tolerance (BASELINE.json north_star): fp32, 1e-4 relative (absolute floors stated per check)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import helpers
+from oracle import flow as oflow
+
+pytestmark = pytest.mark.gpu
+
+TOL = dict(rtol=1e-4, atol=2e-5)
+CASES = {
+    "flow_tiny": (helpers.TINY_CFG, False),
+    "flow_tiny_g": (dict(helpers.TINY_CFG, gin_channels=6), True),
+    "flow_tiny_k3_dil2": (dict(helpers.TINY_CFG, kernel_size=3, dilation_rate=2, n_layers=3), False),
+    "flow_base": (helpers.BASE_CFG, False),
+}
+
+
+def _decoder(cfg, sd, precision="fp32"):
+    from glowtts_b200 import models
+    dec = models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"], cfg["dilation_rate"],
+                                 cfg["n_blocks"], cfg["n_layers"], p_dropout=0.0, n_split=cfg["n_split"],
+                                 n_sqz=cfg["n_sqz"], gin_channels=cfg["gin_channels"], precision=precision)
+    res = dec.load_state_dict(sd, strict=False)
+    assert not res.missing_keys
+    assert all(".wn_pitch." in k or ".wn_energy." in k for k in res.unexpected_keys)
+    return dec.cuda()
+
+
+def _kw(cfg):
+    return dict(hidden=cfg["hidden_channels"], dilation_rate=cfg["dilation_rate"], n_blocks=cfg["n_blocks"],
+                n_layers=cfg["n_layers"], n_split=cfg["n_split"], n_sqz=cfg["n_sqz"])
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_decoder_matches_reference_fixture(golden_dir, name):
+    from glowtts_b200 import commons
+    cfg, use_g = CASES[name]
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    sd = helpers.make_state_dict(cfg, int(g["sd_seed"]), end_std=float(g["end_std"]))
+    dec = _decoder(cfg, sd)
+    y, mask, _, cond = helpers.flow_inputs(cfg, int(g["b"]), int(g["t"]), int(g["in_seed"]), use_g)
+    y = y.cuda().requires_grad_(True)
+    mask = mask.cuda()
+    cond = cond.cuda() if cond is not None else None
+    z, logdet = dec(y, mask, g=cond)
+    np.testing.assert_allclose(z.detach().cpu().numpy(), g["z"], **TOL)
+    np.testing.assert_allclose(logdet.detach().cpu().numpy(), g["logdet"], rtol=1e-4, atol=1e-3)
+    loss = commons.mle_loss(z, None, None, logdet, mask)
+    assert abs(loss.item() - float(g["loss"])) < 1e-4 * max(1.0, abs(float(g["loss"])))
+    loss.backward()
+    np.testing.assert_allclose(y.grad.cpu().numpy(), g["dy"], rtol=1e-3, atol=1e-6)
+    params = dict(dec.named_parameters())
+    n_checked = 0
+    for key in g.files:
+        if not key.startswith("grad:"):
+            continue
+        got = params[key[5:]].grad.cpu().numpy()
+        want = g[key]
+        if got.size != want.size:
+            got = got.reshape(-1)[:: max(1, got.size // 2048)]
+        np.testing.assert_allclose(got.reshape(want.shape), want, rtol=2e-3, atol=2e-6, err_msg=key)
+        n_checked += 1
+    assert n_checked > 5
+    y_rev, none = dec(z.detach(), mask, g=cond, reverse=True)
+    assert none is None
+    np.testing.assert_allclose(y_rev.cpu().numpy(), g["y_rev"], rtol=1e-4, atol=5e-5)
+    dec.store_inverse()
+    y_rev2, _ = dec(z.detach(), mask, g=cond, reverse=True)
+    np.testing.assert_allclose(y_rev2.cpu().numpy(), g["y_rev_stored"], rtol=1e-4, atol=5e-5)
+
+
+@pytest.mark.parametrize("b,t,use_g", [(3, 50, False), (2, 97, True), (1, 2, False), (4, 33, False)])
+def test_decoder_matches_oracle_random(b, t, use_g):
+    """Seeded random shapes incl. odd T (last frame dropped by squeeze) and ragged lengths."""
+    cfg = dict(helpers.TINY_CFG, n_blocks=3, n_layers=3, hidden_channels=24, gin_channels=5 if use_g else 0)
+    sd = helpers.make_state_dict(cfg, 900 + t)
+    dec = _decoder(cfg, sd)
+    y, mask, _, cond = helpers.flow_inputs(cfg, b, t, 77 + t, use_g)
+    z_ref, ld_ref = oflow.decoder({k: v for k, v in sd.items()}, y, mask, g=cond, **_kw(cfg))
+    z, ld = dec(y.cuda(), mask.cuda(), g=None if cond is None else cond.cuda())
+    np.testing.assert_allclose(z.detach().cpu().numpy(), z_ref.numpy(), **TOL)
+    np.testing.assert_allclose(ld.detach().cpu().numpy(), ld_ref.numpy(), rtol=1e-4, atol=1e-3)
+    # invertibility: decoder^-1(decoder(y)) == y * mask on the frames squeeze keeps
+    y_back, _ = dec(z.detach(), mask.cuda(), g=None if cond is None else cond.cuda(), reverse=True)
+    te = (t // 2) * 2
+    ms = mask[:, :, 1::2].repeat_interleave(2, dim=2)[:, :, :te]
+    np.testing.assert_allclose(y_back.cpu().numpy(), (y[:, :, :te] * ms).numpy(), rtol=1e-3, atol=2e-4)
+
+
+def test_fresh_decoder_is_identity_with_zero_logdet():
+    """attentions.py:107-110 zero-init + ActNorm zeros + orthogonal W."""
+    from glowtts_b200 import models
+    torch.manual_seed(0)
+    dec = models.FlowSpecDecoder(8, 16, 5, 1, 3, 2, n_split=4, n_sqz=2).cuda()
+    y, mask, _, _ = helpers.flow_inputs(helpers.TINY_CFG, 2, 20, 3, False)
+    z, ld = dec(y.cuda(), mask.cuda())
+    assert ld.abs().max().item() < 1e-3
+    # with identity couplings/ActNorm the flow is a product of orthogonal mixes: norms are preserved
+    np.testing.assert_allclose(z.detach().pow(2).sum().item(), (y * mask[:, :, 1::2].repeat_interleave(2, 2)).pow(2).sum().item(), rtol=1e-4)
+
+
+def test_modules_match_reference_fixture(golden_dir):
+    from glowtts_b200 import commons, modules
+    g = np.load(os.path.join(golden_dir, "modules_small.npz"))
+    x = torch.from_numpy(g["x"]).cuda()
+    lengths = torch.from_numpy(g["lengths"])
+    mask = oflow.sequence_mask(lengths, x.shape[2]).float().unsqueeze(1).cuda()
+    an = modules.ActNorm(16).cuda()
+    an.logs.data.copy_(torch.from_numpy(g["an_logs"]))
+    an.bias.data.copy_(torch.from_numpy(g["an_bias"]))
+    z, ld = an(x, mask)
+    np.testing.assert_allclose(z.detach().cpu().numpy(), g["an_z"], **TOL)
+    np.testing.assert_allclose(ld.detach().cpu().numpy(), g["an_logdet"], **TOL)
+    zr, none = an(x, mask, reverse=True)
+    assert none is None
+    np.testing.assert_allclose(zr.detach().cpu().numpy(), g["an_zrev"], **TOL)
+    ddi = modules.ActNorm(16, ddi=True).cuda()
+    zd, _ = ddi(x, mask)
+    np.testing.assert_allclose(ddi.logs.detach().cpu().numpy(), g["ddi_logs"], **TOL)
+    np.testing.assert_allclose(ddi.bias.detach().cpu().numpy(), g["ddi_bias"], **TOL)
+    np.testing.assert_allclose(zd.detach().cpu().numpy(), g["ddi_z"], rtol=1e-4, atol=1e-4)
+    ic = modules.InvConvNear(16, n_split=4).cuda()
+    ic.weight.data.copy_(torch.from_numpy(g["ic_w"]))
+    z, ld = ic(x, mask)
+    np.testing.assert_allclose(z.detach().cpu().numpy(), g["ic_z"], **TOL)
+    np.testing.assert_allclose(ld.detach().cpu().numpy(), g["ic_logdet"], **TOL)
+    zr, _ = ic(x, mask, reverse=True)
+    np.testing.assert_allclose(zr.detach().cpu().numpy(), g["ic_zrev"], **TOL)
+    ic.store_inverse()
+    zr2, _ = ic(x, mask, reverse=True)
+    np.testing.assert_allclose(zr2.detach().cpu().numpy(), g["ic_zrev"], **TOL)
+    out = commons.fused_add_tanh_sigmoid_multiply(torch.from_numpy(g["gate_a"]).cuda(), torch.from_numpy(g["gate_b"]).cuda(),
+                                                  torch.IntTensor([16]))
+    np.testing.assert_allclose(out.cpu().numpy(), g["gate_out"], **TOL)
+    xs, ms = commons.squeeze(x, mask, 2)
+    assert np.array_equal(xs.cpu().numpy(), g["sq_x"]) and np.array_equal(ms.cpu().numpy(), g["sq_mask"])
+    xu, mu = commons.unsqueeze(xs, ms, 2)
+    assert np.array_equal(xu.cpu().numpy(), g["unsq_x"]) and np.array_equal(mu.cpu().numpy(), g["unsq_mask"])
+    gp = commons.generate_path(torch.from_numpy(g["gp_dur"]).cuda(), torch.from_numpy(g["gp_mask"]).cuda())
+    assert np.array_equal(gp.cpu().numpy(), g["gp_path"])
+
+
+def test_logp_matches_reference_fixture(golden_dir):
+    from glowtts_b200 import commons
+    g = np.load(os.path.join(golden_dir, "logp_small.npz"))
+    lp = commons.logp(torch.from_numpy(g["x_m"]).cuda(), torch.from_numpy(g["x_logs"]).cuda(), torch.from_numpy(g["z"]).cuda())
+    np.testing.assert_allclose(lp.cpu().numpy(), g["logp"], rtol=1e-5, atol=1e-4)
+
+
+@pytest.mark.parametrize("mean_only", [True, False])
+def test_logp_matches_oracle_and_feeds_mas(mean_only):
+    from glowtts_b200 import commons, monotonic_align
+    from oracle import mas as omas
+    gen = torch.Generator().manual_seed(8)
+    B, D, TX, TY = 3, 80, 37, 101
+    x_m = torch.randn(B, D, TX, generator=gen) * 0.5
+    x_logs = torch.zeros(B, D, TX) if mean_only else torch.randn(B, D, TX, generator=gen) * 0.1
+    z = torch.randn(B, D, TY, generator=gen)
+    want = oflow.logp(x_m, x_logs, z)
+    got = commons.logp(x_m.cuda(), None if mean_only else x_logs.cuda(), z.cuda())
+    np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=1e-5, atol=2e-4)
+    mask = torch.ones(B, TX, TY)
+    path = monotonic_align.maximum_path(got, mask.cuda())
+    ref = omas.maximum_path_np(got.cpu().numpy(), mask.numpy())      # bit-exact given the same fp32 value
+    assert (path.cpu().numpy() == ref).all()
+    ref2 = omas.maximum_path_np(want.numpy(), mask.numpy())
+    agree = (path.cpu().numpy().argmax(1) == ref2.argmax(1)).mean()
+    assert agree > 0.97                                              # path agreement under 1e-4 logp noise
+
+
+def test_standalone_coupling_block_and_wn_match_oracle():
+    from glowtts_b200 import attentions
+    cfg = dict(helpers.TINY_CFG, n_blocks=1, gin_channels=4, kernel_size=3, dilation_rate=2, n_layers=3)
+    sd = helpers.make_state_dict(cfg, 55)
+    cb = attentions.CouplingBlock(16, 16, 3, 2, 3, gin_channels=4).cuda()
+    cb.load_state_dict({k[len("flows.2."):]: v for k, v in sd.items() if k.startswith("flows.2.")
+                        and ".wn_pitch." not in k and ".wn_energy." not in k})
+    gen = torch.Generator().manual_seed(3)
+    x = torch.randn(2, 16, 19, generator=gen)
+    mask = oflow.sequence_mask(torch.tensor([19, 11]), 19).float().unsqueeze(1)
+    g = torch.randn(2, 4, 1, generator=gen)
+    xr = x.clone().requires_grad_(True)
+    sdr = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    z_ref, ld_ref = oflow.coupling(sdr, "flows.2", xr, mask, hidden=16, dilation_rate=2, n_layers=3, g=g)
+    (z_ref.pow(2).sum() + ld_ref.sum()).backward()
+    xc = x.cuda().requires_grad_(True)
+    z, ld = cb(xc, mask.cuda(), g=g.cuda())
+    np.testing.assert_allclose(z.detach().cpu().numpy(), z_ref.detach().numpy(), **TOL)
+    np.testing.assert_allclose(ld.detach().cpu().numpy(), ld_ref.detach().numpy(), rtol=1e-4, atol=1e-4)
+    (z.pow(2).sum() + ld.sum()).backward()
+    np.testing.assert_allclose(xc.grad.cpu().numpy(), xr.grad.numpy(), rtol=1e-3, atol=1e-5)
+    for name, p in cb.named_parameters():
+        np.testing.assert_allclose(p.grad.cpu().numpy(), sdr["flows.2." + name].grad.numpy(), rtol=2e-3, atol=2e-5,
+                                   err_msg=name)
+    zr, _ = cb(z.detach(), mask.cuda(), g=g.cuda(), reverse=True)
+    np.testing.assert_allclose(zr.cpu().numpy(), (x * 1).numpy() * np.concatenate(
+        [np.ones((2, 8, 19), np.float32), mask.expand(2, 8, 19).numpy()], 1), rtol=1e-3, atol=1e-4)
+
+
+def test_mle_loss_and_prior_expansion_match_oracle():
+    from glowtts_b200 import commons, ops
+    gen = torch.Generator().manual_seed(4)
+    B, C, T, TX = 3, 8, 30, 7
+    lengths = torch.tensor([30, 22, 16])
+    mask = oflow.sequence_mask(lengths, T).float().unsqueeze(1)
+    z = torch.randn(B, C, T, generator=gen) * mask
+    m = torch.randn(B, C, T, generator=gen) * mask
+    logs = torch.randn(B, C, T, generator=gen) * 0.1 * mask
+    ld = torch.randn(B, generator=gen)
+    ins = [t.clone().requires_grad_(True) for t in (z, m, logs, ld)]
+    want = oflow.mle_loss(*ins, mask)
+    want.backward()
+    gins = [t.cuda().requires_grad_(True) for t in (z, m, logs, ld)]
+    got = commons.mle_loss(*gins, mask.cuda())
+    got.backward()
+    assert abs(got.item() - want.item()) < 1e-5 * max(1, abs(want.item()))
+    for a, b in zip(gins, ins):
+        np.testing.assert_allclose(a.grad.cpu().numpy(), b.grad.numpy(), rtol=1e-4, atol=1e-7)
+    # prior expansion as a gather == attn^T matmul (models.py:1118-1119)
+    value, amask, _, _ = helpers.mas_case(B, TX, T, 3)
+    v, am = torch.from_numpy(value * amask).cuda(), torch.from_numpy(amask).cuda()
+    t_xs, t_ys = ops.mas_lengths(am)
+    attn, dur, idx = ops.mas_path(v, t_xs, t_ys)
+    x_m = torch.randn(B, C, TX, generator=gen)
+    z_m_ref, z_l_ref = oflow.expand_prior(attn.cpu(), x_m, x_m * 2)
+    z_m, z_l = commons.expand_prior(x_m.cuda(), (x_m * 2).cuda(), idx)
+    assert torch.equal(z_m.cpu(), z_m_ref) and torch.equal(z_l.cpu(), z_l_ref)
