@@ -370,9 +370,11 @@ static int launch_fast(const Params& p, size_t smem, cudaStream_t stream) {
 
 int forward(const float* value, const int* t_xs, const int* t_ys, float* path, int* dur_out, int* idx_out, int B,
             int T_x, int T_y, void* workspace, size_t workspace_bytes_given, int force_generic, cudaStream_t stream) {
-    GTK_REQUIRE(value && t_xs && t_ys && path, "null pointer");
     GTK_REQUIRE(B >= 0 && T_x >= 0 && T_y >= 0, "negative size");
-    if (B == 0 || T_x == 0 || T_y == 0) {
+    if (B == 0) return GTK_OK;
+    GTK_REQUIRE(t_xs && t_ys, "null pointer");
+    GTK_REQUIRE((value && path) || T_x == 0 || T_y == 0, "null pointer");
+    if (T_x == 0 || T_y == 0) {
         if (dur_out && B * T_x > 0) GTK_CUDA(cudaMemsetAsync(dur_out, 0, sizeof(int) * (size_t)B * T_x, stream));
         if (idx_out && B * T_y > 0) GTK_CUDA(cudaMemsetAsync(idx_out, 0xff, sizeof(int) * (size_t)B * T_y, stream));
         return GTK_OK;
