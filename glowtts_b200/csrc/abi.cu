@@ -73,6 +73,15 @@ int sm_count() {
     return cached[dev];
 }
 
+namespace tc {
+struct ConvTcParams;
+int pack_weight_bf16(const float* w, __nv_bfloat16* out, int M, int Cin, int K, int transpose, int rows, int cols, cudaStream_t st);
+int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, int c0, int nc, int ld, cudaStream_t st);
+int conv1d_plain(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, const float* bias, const float* mask, int B, int T,
+                 int K, int dil, int N, float* out_f32, int ld_f32, __nv_bfloat16* out_bf16, int ld_bf16, int mask_out,
+                 cudaStream_t st);
+}  // namespace tc
+
 namespace decoder {
 size_t workspace_bytes(const gtk_decoder_desc* d, int train);
 int forward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const float* x, const float* mask, float* z,
@@ -236,6 +245,18 @@ int gtk_coupling_affine(const float* x, const float* end_out, const float* mask,
 int gtk_coupling_affine_bwd(const float* x, const float* end_out, const float* mask, const float* dz, const float* dlogdet,
                             float* dend, float* dx, int B, int C, int T, int sigmoid_scale, void* stream) {
     return flow::affine_bwd(x, end_out, mask, dz, dlogdet, dend, dx, B, C, T, sigmoid_scale, ST);
+}
+
+int gtk_tc_frames_from_tmajor(const float* x, void* frames_bf16, int B, int C, int T, int c0, int nc, int ld, void* stream) {
+    return tc::frames_from_tmajor(x, static_cast<__nv_bfloat16*>(frames_bf16), B, C, T, c0, nc, ld, ST);
+}
+int gtk_tc_pack_weight(const float* w, void* wp_bf16, int M, int Cin, int K, int transpose, int rows, int cols, void* stream) {
+    return tc::pack_weight_bf16(w, static_cast<__nv_bfloat16*>(wp_bf16), M, Cin, K, transpose, rows, cols, ST);
+}
+int gtk_tc_conv1d(const void* in_bf16, int ld_in, const void* wp_bf16, const float* bias, const float* mask, int B, int T,
+                  int K, int dil, int N, float* out_f32, int ld_f32, void* out_bf16, int ld_bf16, int flags, void* stream) {
+    return tc::conv1d_plain(static_cast<const __nv_bfloat16*>(in_bf16), ld_in, static_cast<const __nv_bfloat16*>(wp_bf16), bias,
+                            mask, B, T, K, dil, N, out_f32, ld_f32, static_cast<__nv_bfloat16*>(out_bf16), ld_bf16, flags & 1, ST);
 }
 
 size_t gtk_decoder_workspace_bytes(const gtk_decoder_desc* d, int train) { return decoder::workspace_bytes(d, train); }

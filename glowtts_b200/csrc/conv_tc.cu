@@ -1,0 +1,317 @@
+// glowtts_b200/csrc/conv_tc.cu -- bf16 tcgen05 implicit-GEMM conv1d on "frame-major" activations.
+//
+// The WaveNet / 1x1 contractions of the coupling block (modules.py:129-142,152,165; attentions.py:102-110,151,170)
+// as D[t, n] = sum_{j, c} X[t + (j - K/2) dil, c] * W[j][n][c]:
+//   * activations are kept frame-major ([B, T, C], channel fastest) in bf16, so a tile of 128 frames x 64 channels
+//     is a K-major UMMA operand that TMA writes straight into the canonical SWIZZLE_128B layout; the conv taps are
+//     just shifted TMA boxes (out-of-range frames are zero-filled by TMA = the conv's zero padding, and the batch
+//     index is a separate tensor-map dimension so a halo never crosses utterances);
+//   * weights are packed [tap][n][c] bf16 (K-major B operand);
+//   * the accumulator D (128 frames x N <= 512 fp32 columns) lives in TMEM: lane = frame, column = out channel.
+//     An epilogue thread therefore owns one frame and sees all of its channels, which is what lets the
+//     gate / residual / affine-coupling epilogues (later in this file) run without any cross-thread exchange.
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warp 2 = TMEM allocator,
+// warps 4..7 = epilogue (TMEM lane quarter = warp % 4).
+#include <string.h>
+
+#include "tc.cuh"
+#include "ops.h"
+
+namespace gtk {
+namespace tc {
+
+// ---------------------------------------------------------------------------------- host: tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                   const uint32_t* box, bool swizzle128) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return GTK_ERR_LAUNCH; }
+    cuuint64_t gdim[5], gstr[5];
+    cuuint32_t bx[5], estr[5];
+    for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; estr[i] = 1; }
+    for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];   // stride of dim i+1
+    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return GTK_ERR_LAUNCH; }
+    return GTK_OK;
+}
+
+// ---------------------------------------------------------------------------------- kernel
+constexpr int BT = 128;            // frames per CTA tile (UMMA M)
+constexpr int KC = 64;             // channels per k-chunk (128 B of bf16 = one swizzle row)
+constexpr int A_BYTES = BT * KC * 2;
+constexpr int NTHREADS = 256;
+
+struct ConvTcParams {
+    int B, T, taps, dil, n_k;      // n_k = padded input channels / 64
+    int N, NW, NCH;                // N = NW * NCH output columns, NW % 16 == 0, NW <= 256
+    int stages;
+    // ---- plain epilogue: v = acc + bias[n] (+ resid) ; optional mask ; stores
+    const float* bias;             // [N] or null
+    const float* mask;             // [B, T] or null
+    int mask_out, mask_resid;
+    const float* resid_f32;        // frame-major [B, T, ld_resid] or null
+    int ld_resid;
+    float* out_f32;                // frame-major [B, T, ld_f32] or null
+    int ld_f32;
+    __nv_bfloat16* out_bf16;       // frame-major [B, T, ld_bf16] or null (columns N..ld_bf16 are left untouched)
+    int ld_bf16;
+    float* out_tm;                 // t-major [B, tm_C, T]: channel tm_c0 + n, or null
+    const float* resid_tm;         // t-major residual added before the store (same indexing), or null
+    int tm_C, tm_c0;
+};
+
+struct SmemCtl {
+    uint64_t full[4], empty[4], acc_full;
+    uint32_t tmem_base;
+};
+
+template <int TMEM_COLS>
+__global__ void __launch_bounds__(NTHREADS, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    // 1024-byte alignment of the operand tiles (SWIZZLE_128B atoms)
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int stage_bytes = A_BYTES + p.N * KC * 2;
+    SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + (size_t)p.stages * stage_bytes);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int t0 = blockIdx.x * BT, b = blockIdx.y;
+    const int n_iter = p.taps * p.n_k;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.stages; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
+        mbar_init(&ctl->acc_full, 1);
+        mbar_fence_init();
+    }
+    if (warp == 2) tmem_alloc<TMEM_COLS>(&ctl->tmem_base);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = ctl->tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            tma_prefetch_desc(&tmA);
+            tma_prefetch_desc(&tmB);
+            for (int it = 0; it < n_iter; ++it) {
+                const int s = it % p.stages, use = it / p.stages;
+                if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
+                const int j = it / p.n_k, kc = it % p.n_k;
+                unsigned char* sa = smem + (size_t)s * stage_bytes;
+                unsigned char* sb = sa + A_BYTES;
+                mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)stage_bytes);
+                tma_load_3d(sa, &tmA, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
+                for (int ch = 0; ch < p.NCH; ++ch)
+                    tma_load_3d(sb + (size_t)ch * p.NW * KC * 2, &tmB, &ctl->full[s], kc * KC, ch * p.NW, j);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_bf16(BT, p.NW);
+            for (int it = 0; it < n_iter; ++it) {
+                const int s = it % p.stages, use = it / p.stages;
+                mbar_wait(&ctl->full[s], use & 1);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+                const uint32_t sb = sa + A_BYTES;
+                const uint64_t adesc = umma_desc_kmajor_sw128(sa);
+#pragma unroll
+                for (int k = 0; k < KC / 16; ++k) {
+                    for (int ch = 0; ch < p.NCH; ++ch) {
+                        const uint64_t bdesc = umma_desc_kmajor_sw128(sb + ch * p.NW * KC * 2);
+                        umma_bf16(tmem + ch * p.NW, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0);
+                    }
+                }
+                umma_commit(&ctl->empty[s]);
+            }
+            umma_commit(&ctl->acc_full);
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------------ plain epilogue
+        mbar_wait(&ctl->acc_full, 0);
+        tc_fence_after();
+        const int q = warp & 3;
+        const int t = t0 + q * 32 + lane;
+        const bool t_ok = t < p.T;
+        const float mk = (p.mask && t_ok) ? p.mask[(size_t)b * p.T + t] : 1.f;
+        const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
+        for (int c0 = 0; c0 < p.N; c0 += 16) {
+            float v[16];
+            tmem_ld16(tmem + ((uint32_t)(q * 32) << 16) + c0, v);
+            if (!t_ok) continue;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                if (p.bias) v[i] += __ldg(p.bias + c0 + i);
+            }
+            if (p.resid_f32) {
+                const float4* r4 = reinterpret_cast<const float4*>(p.resid_f32 + frame * p.ld_resid + c0);
+                const float rm = p.mask_resid ? mk : 1.f;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float4 r = r4[i];
+                    v[4 * i] += r.x * rm; v[4 * i + 1] += r.y * rm; v[4 * i + 2] += r.z * rm; v[4 * i + 3] += r.w * rm;
+                }
+            }
+            if (p.resid_tm) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] += p.resid_tm[((size_t)b * p.tm_C + p.tm_c0 + c0 + i) * p.T + t];
+            }
+            if (p.mask_out) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] *= mk;
+            }
+            if (p.out_f32) {
+                float4* o4 = reinterpret_cast<float4*>(p.out_f32 + frame * p.ld_f32 + c0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            }
+            if (p.out_bf16) {
+                uint32_t w[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+                    w[i] = *reinterpret_cast<uint32_t*>(&h);
+                }
+                uint4* o = reinterpret_cast<uint4*>(p.out_bf16 + frame * p.ld_bf16 + c0);
+                o[0] = make_uint4(w[0], w[1], w[2], w[3]);
+                o[1] = make_uint4(w[4], w[5], w[6], w[7]);
+            }
+            if (p.out_tm) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) p.out_tm[((size_t)b * p.tm_C + p.tm_c0 + c0 + i) * p.T + t] = v[i];
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<TMEM_COLS>(tmem);
+    }
+}
+
+// ---------------------------------------------------------------------------------- helpers: packing / layout
+// W fp32 [M][Cin][K] (torch) -> bf16 [K][rows][cols] zero padded.
+//   transpose = 0 (forward operand):        out[j][m][c] = W[m][c][j]            rows >= M,   cols >= Cin
+//   transpose = 1 (data-gradient operand):  out[j][c][m] = W[m][c][K-1-j]        rows >= Cin, cols >= M
+__global__ void pack_weight_bf16_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int M, int Cin, int K,
+                                        int transpose, int rows, int cols) {
+    const long long total = (long long)K * rows * cols;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cols);
+        long long r = i / cols;
+        const int row = (int)(r % rows), j = (int)(r / rows);
+        float v = 0.f;
+        if (!transpose) { if (row < M && c < Cin) v = w[((size_t)row * Cin + c) * K + j]; }
+        else            { if (row < Cin && c < M) v = w[((size_t)c * Cin + row) * K + (K - 1 - j)]; }
+        out[i] = __float2bfloat16_rn(v);
+    }
+}
+int pack_weight_bf16(const float* w, __nv_bfloat16* out, int M, int Cin, int K, int transpose, int rows, int cols, cudaStream_t st) {
+    GTK_REQUIRE(w && out, "null");
+    const long long total = (long long)K * rows * cols;
+    if (total == 0) return GTK_OK;
+    long long g = ceil_div_ll(total, 256);
+    pack_weight_bf16_kernel<<<(int)(g > 2048 ? 2048 : g), 256, 0, st>>>(w, out, M, Cin, K, transpose, rows, cols);
+    return check_launch("pack_weight_bf16");
+}
+
+// x fp32 t-major [B, C, T] channels [c0, c0+nc) -> bf16 frame-major out[b][t][0..ld): columns >= nc are zero.
+__global__ void frames_from_tmajor_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int C, int T, int c0,
+                                          int nc, int ld) {
+    __shared__ float tile[32][33];
+    const int b = blockIdx.z, tt = blockIdx.x * 32, cc = blockIdx.y * 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
+    for (int i = ty; i < 32; i += 8) {
+        const int c = cc + i, t = tt + tx;
+        tile[i][tx] = (c < nc && t < T) ? x[((size_t)b * C + c0 + c) * T + t] : 0.f;
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+        const int t = tt + i, c = cc + tx;
+        if (t < T && c < ld) out[((size_t)b * T + t) * ld + c] = __float2bfloat16_rn(tile[tx][i]);
+    }
+}
+int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, int c0, int nc, int ld, cudaStream_t st) {
+    GTK_REQUIRE(x && out && c0 >= 0 && c0 + nc <= C && ld >= nc, "bad args");
+    if ((long long)B * T * ld == 0) return GTK_OK;
+    dim3 grid(ceil_div(T, 32), ceil_div(ld, 32), B);
+    frames_from_tmajor_kernel<<<grid, dim3(32, 8), 0, st>>>(x, out, C, T, c0, nc, ld);
+    return check_launch("frames_from_tmajor");
+}
+
+// ---------------------------------------------------------------------------------- launcher
+static size_t conv_tc_smem(int N, int stages) { return (size_t)stages * (A_BYTES + (size_t)N * KC * 2) + sizeof(SmemCtl) + 1024; }
+
+int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, ConvTcParams p, cudaStream_t st) {
+    GTK_REQUIRE(in && wp, "null");
+    GTK_REQUIRE(p.taps >= 1 && (p.taps & 1) && p.dil >= 1 && p.n_k >= 1, "bad conv shape");
+    GTK_REQUIRE(ld_in == p.n_k * KC, "input frames must be padded to a multiple of 64 channels");
+    GTK_REQUIRE(p.N >= 16 && p.N % 16 == 0 && p.N <= 512, "N must be a multiple of 16, <= 512");
+    if (p.B == 0 || p.T == 0) return GTK_OK;
+    p.NCH = (p.N > 256) ? 2 : 1;
+    p.NW = p.N / p.NCH;
+    GTK_REQUIRE(p.NW % 16 == 0 && p.NW <= 256, "N chunk must be a multiple of 16");
+    int stages = 4;
+    while (stages > 2 && conv_tc_smem(p.N, stages) > 200 * 1024) --stages;
+    p.stages = stages;
+    const size_t smem = conv_tc_smem(p.N, stages);
+    GTK_REQUIRE(smem <= 227 * 1024, "tile does not fit in shared memory");
+
+    CUtensorMap tmA, tmB;
+    {
+        const uint64_t dims[3] = {(uint64_t)ld_in, (uint64_t)p.T, (uint64_t)p.B};
+        const uint64_t strides[2] = {(uint64_t)ld_in * 2, (uint64_t)ld_in * 2 * p.T};
+        const uint32_t box[3] = {KC, BT, 1};
+        int rc = make_tmap_bf16(&tmA, in, 3, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    {
+        const uint64_t dims[3] = {(uint64_t)ld_in, (uint64_t)p.N, (uint64_t)p.taps};
+        const uint64_t strides[2] = {(uint64_t)ld_in * 2, (uint64_t)ld_in * 2 * p.N};
+        const uint32_t box[3] = {KC, (uint32_t)p.NW, 1};
+        int rc = make_tmap_bf16(&tmB, wp, 3, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    dim3 grid(ceil_div(p.T, BT), p.B);
+    ProfScope prof(p.taps > 1 ? "conv_tc_kN" : "conv_tc_k1", st);
+    if (p.N > 256) {
+        GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        conv_tc_kernel<512><<<grid, NTHREADS, smem, st>>>(tmA, tmB, p);
+    } else {
+        GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        conv_tc_kernel<256><<<grid, NTHREADS, smem, st>>>(tmA, tmB, p);
+    }
+    return check_launch("conv_tc");
+}
+
+int conv1d_plain(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, const float* bias, const float* mask, int B, int T,
+                 int K, int dil, int N, float* out_f32, int ld_f32, __nv_bfloat16* out_bf16, int ld_bf16, int mask_out,
+                 cudaStream_t st) {
+    ConvTcParams p;
+    memset(&p, 0, sizeof(p));
+    p.B = B; p.T = T; p.taps = K; p.dil = dil; p.n_k = ld_in / KC; p.N = N;
+    p.bias = bias; p.mask = mask; p.mask_out = mask_out;
+    p.out_f32 = out_f32; p.ld_f32 = ld_f32; p.out_bf16 = out_bf16; p.ld_bf16 = ld_bf16;
+    return conv_tc_launch(in, ld_in, wp, p, st);
+}
+
+}  // namespace tc
+}  // namespace gtk

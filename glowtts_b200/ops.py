@@ -857,3 +857,45 @@ def _aff_bwd(ctx, dz, dlogdet):
 
 
 coupling_affine.register_autograd(_aff_bwd, setup_context=_aff_setup)
+
+
+# =============================================================================== bf16 tensor-core conv (frames)
+def _pad64(n: int) -> int:
+    return (n + 63) // 64 * 64
+
+
+def tc_frames(x: Tensor, c0: int = 0, nc: Optional[int] = None) -> Tensor:
+    """x fp32 [B,C,T] -> bf16 frames [B,T,pad64(nc)] (gtk_tc_frames_from_tmajor)."""
+    x = _chk(x, "x")
+    B, C, T = x.shape
+    nc = C - c0 if nc is None else nc
+    ld = _pad64(nc)
+    out = torch.empty(B, T, ld, dtype=torch.bfloat16, device=x.device)
+    _lib.call("gtk_tc_frames_from_tmajor", _p(x), _p(out), B, C, T, c0, nc, ld, _stream())
+    return out
+
+
+def tc_pack_weight(w: Tensor, transpose: bool = False) -> Tensor:
+    """w fp32 [M,Cin,K] -> bf16 [K, rows, pad64(cols)] operand of tc_conv1d (forward or data-gradient form)."""
+    w = _chk(w, "weight")
+    M, Cin, K = w.shape
+    rows, cols = (Cin, _pad64(M)) if transpose else (M, _pad64(Cin))
+    rows = (rows + 15) // 16 * 16
+    out = torch.empty(K, rows, cols, dtype=torch.bfloat16, device=w.device)
+    _lib.call("gtk_tc_pack_weight", _p(w), _p(out), M, Cin, K, int(transpose), rows, cols, _stream())
+    return out
+
+
+def tc_conv1d(frames: Tensor, wp: Tensor, bias: Optional[Tensor], dilation: int = 1, mask: Optional[Tensor] = None,
+              want_f32: bool = True, want_bf16: bool = False):
+    """Frame-major conv on the tensor cores: frames bf16 [B,T,ld], wp bf16 [K,N,ld] -> fp32 [B,T,N] and/or
+    bf16 frames [B,T,pad64(N)]."""
+    B, T, ld = frames.shape
+    K, N, ldw = wp.shape
+    assert ld == ldw and frames.dtype == torch.bfloat16 and wp.dtype == torch.bfloat16
+    out32 = torch.empty(B, T, N, dtype=torch.float32, device=frames.device) if want_f32 else None
+    ldb = _pad64(N)
+    out16 = torch.zeros(B, T, ldb, dtype=torch.bfloat16, device=frames.device) if want_bf16 else None
+    _lib.call("gtk_tc_conv1d", _p(frames), ld, _p(wp), _p(_opt(bias, "bias")), _p(_opt(mask, "mask")), B, T, K, dilation, N,
+              _p(out32), N, _p(out16), ldb, 1 if mask is not None else 0, _stream())
+    return out32, out16

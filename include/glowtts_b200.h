@@ -139,6 +139,20 @@ int gtk_coupling_affine(const float* x, const float* end_out, const float* mask,
 int gtk_coupling_affine_bwd(const float* x, const float* end_out, const float* mask, const float* dz, const float* dlogdet,
                             float* dend, float* dx, int B, int C, int T, int sigmoid_scale, void* stream);
 
+/* ---- bf16 tensor-core path (tcgen05 + TMA), frame-major activations ----------------------- */
+/* "Frames" are bf16 [B, T, ld] tensors with the channel fastest and ld a multiple of 64 (zero padded);
+ * they are the K-major UMMA operands of the tensor-core convolutions. */
+/* x fp32 [B,C,T] channels [c0, c0+nc) -> frames bf16 [B,T,ld] (columns nc..ld zeroed). */
+int gtk_tc_frames_from_tmajor(const float* x, void* frames_bf16, int B, int C, int T, int c0, int nc, int ld, void* stream);
+/* W fp32 [M,Cin,K] (torch) -> bf16 [K][rows][cols], zero padded; transpose=0: out[j][m][c] (forward operand, rows>=M,
+ * cols>=Cin); transpose=1: out[j][c][m] = W[m][c][K-1-j] (data-gradient operand, rows>=Cin, cols>=M). */
+int gtk_tc_pack_weight(const float* w, void* wp_bf16, int M, int Cin, int K, int transpose, int rows, int cols, void* stream);
+/* out[b,t,n] = bias[n] + sum_{j,c} in[b, t+(j-K/2)dil, c] wp[j][n][c]  (F.conv1d of modules.py:152,165 /
+ * attentions.py:151,170 on frames).  in: frames [B,T,ld_in]; wp: [K][N][ld_in]; N % 16 == 0, N <= 512.
+ * flags bit0: multiply the output by mask[b,t].  out_f32 (ld_f32) and out_bf16 (ld_bf16) frame-major, either may be NULL. */
+int gtk_tc_conv1d(const void* in_bf16, int ld_in, const void* wp_bf16, const float* bias, const float* mask, int B, int T,
+                  int K, int dil, int N, float* out_f32, int ld_f32, void* out_bf16, int ld_bf16, int flags, void* stream);
+
 /* ---- whole decoder (models.py:719-789) --------------------------------------------------- */
 typedef struct gtk_decoder_desc {
     int B;              /* batch */
