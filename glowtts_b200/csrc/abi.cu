@@ -7,7 +7,7 @@
 #include <string>
 #include <vector>
 
-#include "common.cuh"
+#include "tc.cuh"
 #include "ops.h"
 #include "../../include/glowtts_b200.h"
 
@@ -74,9 +74,6 @@ int sm_count() {
 }
 
 namespace tc {
-struct ConvTcParams;
-int pack_weight_bf16(const float* w, __nv_bfloat16* out, int M, int Cin, int K, int transpose, int rows, int cols, cudaStream_t st);
-int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, int c0, int nc, int ld, cudaStream_t st);
 int conv1d_plain(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, const float* bias, const float* mask, int B, int T,
                  int K, int dil, int N, float* out_f32, int ld_f32, __nv_bfloat16* out_bf16, int ld_bf16, int mask_out,
                  cudaStream_t st);
@@ -257,6 +254,23 @@ int gtk_tc_conv1d(const void* in_bf16, int ld_in, const void* wp_bf16, const flo
                   int K, int dil, int N, float* out_f32, int ld_f32, void* out_bf16, int ld_bf16, int flags, void* stream) {
     return tc::conv1d_plain(static_cast<const __nv_bfloat16*>(in_bf16), ld_in, static_cast<const __nv_bfloat16*>(wp_bf16), bias,
                             mask, B, T, K, dil, N, out_f32, ld_f32, static_cast<__nv_bfloat16*>(out_bf16), ld_bf16, flags & 1, ST);
+}
+
+int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, const void* wrs_p, const float* bias_in,
+                    const float* bias_rs, const float* cond, size_t cond_bstride, const float* mask, int B, int T, int H,
+                    int RS, int K, int dil, int first, int last, float drop_p, unsigned long long drop_seed,
+                    float* h_out_f32, void* h_out_bf16, float* skip_f32, void* skip_out_bf16, void* ts_save,
+                    void* acts_save, void* stream) {
+    tc::WnLayerParams p;
+    memset(&p, 0, sizeof(p));
+    p.B = B; p.T = T; p.H = H; p.RS = RS; p.taps = K; p.dil = dil; p.first = first; p.last = last;
+    p.bias_in = bias_in; p.bias_rs = bias_rs; p.cond = cond; p.cond_bstride = cond_bstride; p.mask = mask;
+    p.drop_p = drop_p; p.drop_seed = drop_seed;
+    p.h_f32 = h_f32; p.h_out_f32 = h_out_f32; p.h_out_bf16 = static_cast<__nv_bfloat16*>(h_out_bf16);
+    p.skip_f32 = skip_f32; p.skip_out_bf16 = static_cast<__nv_bfloat16*>(skip_out_bf16);
+    p.ts_save = static_cast<__nv_bfloat16*>(ts_save); p.acts_save = static_cast<__nv_bfloat16*>(acts_save);
+    return tc::wn_layer_launch(static_cast<const __nv_bfloat16*>(h_bf16), static_cast<const __nv_bfloat16*>(win_p),
+                               static_cast<const __nv_bfloat16*>(wrs_p), p, ST);
 }
 
 size_t gtk_decoder_workspace_bytes(const gtk_decoder_desc* d, int train) { return decoder::workspace_bytes(d, train); }

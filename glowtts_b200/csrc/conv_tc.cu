@@ -53,36 +53,12 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t*
 }
 
 // ---------------------------------------------------------------------------------- kernel
-constexpr int BT = 128;            // frames per CTA tile (UMMA M)
-constexpr int KC = 64;             // channels per k-chunk (128 B of bf16 = one swizzle row)
-constexpr int A_BYTES = BT * KC * 2;
-constexpr int NTHREADS = 256;
-
-struct ConvTcParams {
-    int B, T, taps, dil, n_k;      // n_k = padded input channels / 64
-    int N, NW, NCH;                // N = NW * NCH output columns, NW % 16 == 0, NW <= 256
-    int stages;
-    // ---- plain epilogue: v = acc + bias[n] (+ resid) ; optional mask ; stores
-    const float* bias;             // [N] or null
-    const float* mask;             // [B, T] or null
-    int mask_out, mask_resid;
-    const float* resid_f32;        // frame-major [B, T, ld_resid] or null
-    int ld_resid;
-    float* out_f32;                // frame-major [B, T, ld_f32] or null
-    int ld_f32;
-    __nv_bfloat16* out_bf16;       // frame-major [B, T, ld_bf16] or null (columns N..ld_bf16 are left untouched)
-    int ld_bf16;
-    float* out_tm;                 // t-major [B, tm_C, T]: channel tm_c0 + n, or null
-    const float* resid_tm;         // t-major residual added before the store (same indexing), or null
-    int tm_C, tm_c0;
-};
-
 struct SmemCtl {
     uint64_t full[4], empty[4], acc_full;
     uint32_t tmem_base;
 };
 
-template <int TMEM_COLS>
+template <int TMEM_COLS, int EPI>
 __global__ void __launch_bounds__(NTHREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -144,7 +120,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             umma_commit(&ctl->acc_full);
         }
     } else if (warp >= 4) {
-        // ------------------------------------------------------------------ plain epilogue
         mbar_wait(&ctl->acc_full, 0);
         tc_fence_after();
         const int q = warp & 3;
@@ -152,50 +127,107 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const bool t_ok = t < p.T;
         const float mk = (p.mask && t_ok) ? p.mask[(size_t)b * p.T + t] : 1.f;
         const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
-        for (int c0 = 0; c0 < p.N; c0 += 16) {
-            float v[16];
-            tmem_ld16(tmem + ((uint32_t)(q * 32) << 16) + c0, v);
-            if (!t_ok) continue;
+        const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+        if constexpr (EPI == EPI_PLAIN) {
+            for (int c0 = 0; c0 < p.N; c0 += 16) {
+                float v[16];
+                tmem_ld16(trow + c0, v);
+                if (!t_ok) continue;
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                if (p.bias) v[i] += __ldg(p.bias + c0 + i);
-            }
-            if (p.resid_f32) {
-                const float4* r4 = reinterpret_cast<const float4*>(p.resid_f32 + frame * p.ld_resid + c0);
-                const float rm = p.mask_resid ? mk : 1.f;
+                for (int i = 0; i < 16; ++i) {
+                    if (p.bias) v[i] += __ldg(p.bias + c0 + i);
+                }
+                if (p.resid_f32) {
+                    const float4* r4 = reinterpret_cast<const float4*>(p.resid_f32 + frame * p.ld_resid + c0);
+                    const float rm = p.mask_resid ? mk : 1.f;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float4 r = r4[i];
-                    v[4 * i] += r.x * rm; v[4 * i + 1] += r.y * rm; v[4 * i + 2] += r.z * rm; v[4 * i + 3] += r.w * rm;
+                    for (int i = 0; i < 4; ++i) {
+                        const float4 r = r4[i];
+                        v[4 * i] += r.x * rm; v[4 * i + 1] += r.y * rm; v[4 * i + 2] += r.z * rm; v[4 * i + 3] += r.w * rm;
+                    }
+                }
+                if (p.resid_tm) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] += p.resid_tm[((size_t)b * p.tm_C + p.tm_c0 + c0 + i) * p.T + t];
+                }
+                if (p.mask_out) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] *= mk;
+                }
+                if (p.out_f32) {
+                    float4* o4 = reinterpret_cast<float4*>(p.out_f32 + frame * p.ld_f32 + c0);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                }
+                if (p.out_bf16) store_bf16x16(p.out_bf16 + frame * p.ld_bf16 + c0, v);
+                if (p.out_tm) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) p.out_tm[((size_t)b * p.tm_C + p.tm_c0 + c0 + i) * p.T + t] = v[i];
                 }
             }
-            if (p.resid_tm) {
+        } else if constexpr (EPI == EPI_GATE_BWD) {
+            const int H = p.N;
+            for (int c0 = 0; c0 < H; c0 += 16) {
+                float d[16];
+                tmem_ld16(trow + c0, d);
+                if (!t_ok) continue;
+                float tt[16], ss[16], dt[16], ds[16];
+                load_bf16x16(p.ts + frame * (2 * H) + c0, tt);
+                load_bf16x16(p.ts + frame * (2 * H) + H + c0, ss);
 #pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] += p.resid_tm[((size_t)b * p.tm_C + p.tm_c0 + c0 + i) * p.T + t];
-            }
-            if (p.mask_out) {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] *= mk;
-            }
-            if (p.out_f32) {
-                float4* o4 = reinterpret_cast<float4*>(p.out_f32 + frame * p.ld_f32 + c0);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-            }
-            if (p.out_bf16) {
-                uint32_t w[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-                    w[i] = *reinterpret_cast<uint32_t*>(&h);
+                for (int i = 0; i < 16; ++i) {
+                    dt[i] = d[i] * ss[i] * (1.f - tt[i] * tt[i]);
+                    ds[i] = d[i] * tt[i] * ss[i] * (1.f - ss[i]);
                 }
-                uint4* o = reinterpret_cast<uint4*>(p.out_bf16 + frame * p.ld_bf16 + c0);
-                o[0] = make_uint4(w[0], w[1], w[2], w[3]);
-                o[1] = make_uint4(w[4], w[5], w[6], w[7]);
-            }
-            if (p.out_tm) {
+                if (p.out2_bf16) {
+                    store_bf16x16(p.out2_bf16 + frame * (2 * H) + c0, dt);
+                    store_bf16x16(p.out2_bf16 + frame * (2 * H) + H + c0, ds);
+                }
+                if (p.drop_p > 0.f) {
 #pragma unroll
-                for (int i = 0; i < 16; ++i) p.out_tm[((size_t)b * p.tm_C + p.tm_c0 + c0 + i) * p.T + t] = v[i];
+                    for (int i = 0; i < 16; ++i) {
+                        dt[i] *= dropout_scale(p.drop_seed, frame * (2 * H) + c0 + i, p.drop_p);
+                        ds[i] *= dropout_scale(p.drop_seed, frame * (2 * H) + H + c0 + i, p.drop_p);
+                    }
+                }
+                store_bf16x16(p.out_bf16 + frame * p.ld_bf16 + c0, dt);
+                store_bf16x16(p.out_bf16 + frame * p.ld_bf16 + H + c0, ds);
+            }
+        } else {   // EPI_AFFINE
+            const int Ch = p.N / 2, C = p.N;
+            float ld_sum = 0.f;
+            for (int c0 = 0; c0 < Ch; c0 += 16) {
+                float m[16], lg[16];
+                tmem_ld16(trow + c0, m);
+                tmem_ld16(trow + Ch + c0, lg);
+                if (!t_ok) continue;
+                float lsave[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int c = c0 + i;
+                    float mm = m[i] + (p.bias ? __ldg(p.bias + c) : 0.f);
+                    float ll = lg[i] + (p.bias ? __ldg(p.bias + Ch + c) : 0.f);
+                    lsave[i] = ll;     // raw end-conv output (pre sigmoid_scale), as the fp32 path keeps it
+                    if (p.aff_sigmoid_scale) ll = __logf(1e-6f + sigmoid_f(ll + 2.f));
+                    const size_t o0 = ((size_t)b * C + c) * p.T + t, o1 = o0 + (size_t)Ch * p.T;
+                    const float x1 = p.aff_x[o1];
+                    p.aff_z[o0] = p.aff_x[o0];
+                    if (p.aff_reverse) {
+                        p.aff_z[o1] = (x1 - mm) * __expf(-ll) * mk;
+                    } else {
+                        p.aff_z[o1] = (mm + __expf(ll) * x1) * mk;
+                        ld_sum += ll * mk;
+                    }
+                }
+                if (p.aff_logs_save) {
+                    float4* o4 = reinterpret_cast<float4*>(p.aff_logs_save + frame * Ch + c0);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) o4[i] = make_float4(lsave[4 * i], lsave[4 * i + 1], lsave[4 * i + 2], lsave[4 * i + 3]);
+                }
+            }
+            if (!p.aff_reverse && p.aff_logdet) {
+                ld_sum = warp_sum(t_ok ? ld_sum : 0.f);
+                if (lane == 0) atomicAdd(p.aff_logdet + b, ld_sum);
             }
         }
         tc_fence_before();
@@ -260,10 +292,12 @@ int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, 
 // ---------------------------------------------------------------------------------- launcher
 static size_t conv_tc_smem(int N, int stages) { return (size_t)stages * (A_BYTES + (size_t)N * KC * 2) + sizeof(SmemCtl) + 1024; }
 
-int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, ConvTcParams p, cudaStream_t st) {
+// in: frames with row pitch ld_in elements, of which the first p.n_k * 64 columns are the conv's input channels
+// (the weights are packed with exactly that many columns).
+int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, ConvTcParams p, int epi, cudaStream_t st) {
     GTK_REQUIRE(in && wp, "null");
     GTK_REQUIRE(p.taps >= 1 && (p.taps & 1) && p.dil >= 1 && p.n_k >= 1, "bad conv shape");
-    GTK_REQUIRE(ld_in == p.n_k * KC, "input frames must be padded to a multiple of 64 channels");
+    GTK_REQUIRE(ld_in >= p.n_k * KC && ld_in % 8 == 0, "input frames: row pitch must cover n_k * 64 channels, 16-byte aligned");
     GTK_REQUIRE(p.N >= 16 && p.N % 16 == 0 && p.N <= 512, "N must be a multiple of 16, <= 512");
     if (p.B == 0 || p.T == 0) return GTK_OK;
     p.NCH = (p.N > 256) ? 2 : 1;
@@ -277,28 +311,31 @@ int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, 
 
     CUtensorMap tmA, tmB;
     {
-        const uint64_t dims[3] = {(uint64_t)ld_in, (uint64_t)p.T, (uint64_t)p.B};
+        const uint64_t dims[3] = {(uint64_t)p.n_k * KC, (uint64_t)p.T, (uint64_t)p.B};
         const uint64_t strides[2] = {(uint64_t)ld_in * 2, (uint64_t)ld_in * 2 * p.T};
         const uint32_t box[3] = {KC, BT, 1};
         int rc = make_tmap_bf16(&tmA, in, 3, dims, strides, box, true);
         if (rc) return rc;
     }
     {
-        const uint64_t dims[3] = {(uint64_t)ld_in, (uint64_t)p.N, (uint64_t)p.taps};
-        const uint64_t strides[2] = {(uint64_t)ld_in * 2, (uint64_t)ld_in * 2 * p.N};
+        const uint64_t kcols = (uint64_t)p.n_k * KC;
+        const uint64_t dims[3] = {kcols, (uint64_t)p.N, (uint64_t)p.taps};
+        const uint64_t strides[2] = {kcols * 2, kcols * 2 * p.N};
         const uint32_t box[3] = {KC, (uint32_t)p.NW, 1};
         int rc = make_tmap_bf16(&tmB, wp, 3, dims, strides, box, true);
         if (rc) return rc;
     }
     dim3 grid(ceil_div(p.T, BT), p.B);
     ProfScope prof(p.taps > 1 ? "conv_tc_kN" : "conv_tc_k1", st);
-    if (p.N > 256) {
-        GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        conv_tc_kernel<512><<<grid, NTHREADS, smem, st>>>(tmA, tmB, p);
-    } else {
-        GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        conv_tc_kernel<256><<<grid, NTHREADS, smem, st>>>(tmA, tmB, p);
-    }
+#define GTK_TC_LAUNCH(COLS, E)                                                                                       \
+    do {                                                                                                             \
+        GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<COLS, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        conv_tc_kernel<COLS, E><<<grid, NTHREADS, smem, st>>>(tmA, tmB, p);                                          \
+    } while (0)
+    if (epi == EPI_PLAIN) { if (p.N > 256) GTK_TC_LAUNCH(512, EPI_PLAIN); else GTK_TC_LAUNCH(256, EPI_PLAIN); }
+    else if (epi == EPI_GATE_BWD) { GTK_REQUIRE(p.N <= 256 && p.ts && p.out_bf16, "gate_bwd epilogue arguments"); GTK_TC_LAUNCH(256, EPI_GATE_BWD); }
+    else { GTK_REQUIRE(p.N <= 256 && p.N % 32 == 0 && p.aff_x && p.aff_z, "affine epilogue arguments"); GTK_TC_LAUNCH(256, EPI_AFFINE); }
+#undef GTK_TC_LAUNCH
     return check_launch("conv_tc");
 }
 
@@ -310,7 +347,7 @@ int conv1d_plain(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, co
     p.B = B; p.T = T; p.taps = K; p.dil = dil; p.n_k = ld_in / KC; p.N = N;
     p.bias = bias; p.mask = mask; p.mask_out = mask_out;
     p.out_f32 = out_f32; p.ld_f32 = ld_f32; p.out_bf16 = out_bf16; p.ld_bf16 = ld_bf16;
-    return conv_tc_launch(in, ld_in, wp, p, st);
+    return conv_tc_launch(in, ld_in, wp, p, EPI_PLAIN, st);
 }
 
 }  // namespace tc

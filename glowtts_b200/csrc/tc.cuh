@@ -13,6 +13,70 @@ namespace tc {
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                    const uint32_t* box, bool swizzle128);
 
+constexpr int BT = 128;            // frames per CTA tile (UMMA M)
+constexpr int KC = 64;             // channels per k-chunk (128 B of bf16 = one swizzle row)
+constexpr int A_BYTES = BT * KC * 2;
+constexpr int NTHREADS = 256;
+
+struct ConvTcParams {
+    int B, T, taps, dil, n_k;      // n_k = padded input channels / 64
+    int N, NW, NCH;                // N = NW * NCH output columns, NW % 16 == 0, NW <= 256
+    int stages;
+    // ---- plain epilogue: v = acc + bias[n] (+ resid) ; optional mask ; stores
+    const float* bias;             // [N] or null
+    const float* mask;             // [B, T] or null
+    int mask_out, mask_resid;
+    const float* resid_f32;        // frame-major [B, T, ld_resid] or null
+    int ld_resid;
+    float* out_f32;                // frame-major [B, T, ld_f32] or null
+    int ld_f32;
+    __nv_bfloat16* out_bf16;       // frame-major [B, T, ld_bf16] or null (columns N..ld_bf16 are left untouched)
+    int ld_bf16;
+    float* out_tm;                 // t-major [B, tm_C, T]: channel tm_c0 + n, or null
+    const float* resid_tm;         // t-major residual added before the store (same indexing), or null
+    int tm_C, tm_c0;
+    // ---- EPI_GATE_BWD (N = H): acc = d(acts); ts = saved [tanh | sigmoid] frames [B,T,2H] ->
+    //      out_bf16[.., 0:2H] = d(conv output) (dropout-scaled), out2_bf16 = d(gate input) (pre-dropout; may be null)
+    const __nv_bfloat16* ts;
+    __nv_bfloat16* out2_bf16;
+    float drop_p;                  // dropout probability on the conv output (modules.py:153); 0 = off
+    unsigned long long drop_seed;  // element (b, t, n) of this layer keeps iff hash(seed, index) >= p
+    // ---- EPI_AFFINE (N = C, attentions.py:172-183): acc = [m | logs]; x / z t-major [B, C, T]
+    const float* aff_x;
+    float* aff_z;
+    float* aff_logdet;             // [B], accumulated with atomicAdd (forward only)
+    float* aff_logs_save;          // frame-major [B, T, C/2] or null: logs kept for the backward
+    int aff_reverse, aff_sigmoid_scale;
+};
+
+enum { EPI_PLAIN = 0, EPI_GATE_BWD = 1, EPI_AFFINE = 2 };
+
+// One fused WaveNet layer (wn_tc.cu).  All activations frame-major [B, T, H].
+struct WnLayerParams {
+    int B, T, H, RS, taps, dil;
+    int first, last;               // first: skip is written, not accumulated; last: RS == H, skip*mask -> skip_out_bf16
+    const float* bias_in;          // [2H]
+    const float* bias_rs;          // [RS]
+    const float* cond;             // this layer's slice of cond_layer(g): cond[b * cond_bstride + n], n < 2H; or null
+    size_t cond_bstride;
+    const float* mask;             // [B, T]
+    float drop_p;
+    unsigned long long drop_seed;
+    const float* h_f32;            // layer input (fp32 master copy) -- the bf16 copy is the TMA operand
+    float* h_out_f32;              // next layer's input (not last)
+    __nv_bfloat16* h_out_bf16;
+    float* skip_f32;               // running skip sum (fp32)
+    __nv_bfloat16* skip_out_bf16;  // last layer: masked WN output, operand of the `end` conv
+    __nv_bfloat16* ts_save;        // [B,T,2H] tanh | sigmoid outputs for the backward, or null
+    __nv_bfloat16* acts_save;      // [B,T,H] gate output for the res_skip weight gradient, or null
+};
+int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, const __nv_bfloat16* wrs_p, WnLayerParams p,
+                    cudaStream_t st);
+
+int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, ConvTcParams p, int epi, cudaStream_t st);
+int pack_weight_bf16(const float* w, __nv_bfloat16* out, int M, int Cin, int K, int transpose, int rows, int cols, cudaStream_t st);
+int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, int c0, int nc, int ld, cudaStream_t st);
+
 #ifdef __CUDACC__
 // ---------------------------------------------------------------------------------- device: TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
@@ -109,6 +173,39 @@ __device__ __forceinline__ bool elect_one() {
         : "=r"(pred));
     return pred != 0;
 }
+// Counter-based dropout mask shared by the forward and backward kernels: keep iff u >= p.
+__device__ __forceinline__ float dropout_scale(unsigned long long seed, unsigned long long idx, float p) {
+    unsigned long long z = seed + idx * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    const float u = (float)(uint32_t)(z >> 40) * (1.0f / 16777216.0f);
+    return (u >= p) ? 1.0f / (1.0f - p) : 0.0f;
+}
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + __expf(-x)); }
+__device__ __forceinline__ void store_bf16x16(__nv_bfloat16* dst, const float (&v)[16]) {
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+        w[i] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    uint4* o = reinterpret_cast<uint4*>(dst);
+    o[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    o[1] = make_uint4(w[4], w[5], w[6], w[7]);
+}
+__device__ __forceinline__ void load_bf16x16(const __nv_bfloat16* src, float (&v)[16]) {
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    const uint4 a = s4[0], b = s4[1];
+    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
+        v[2 * i] = __low2float(h);
+        v[2 * i + 1] = __high2float(h);
+    }
+}
+
 #endif  // __CUDACC__
 
 }  // namespace tc

@@ -1,0 +1,258 @@
+// glowtts_b200/csrc/wn_tc.cu -- one WaveNet layer (modules.py:151-170) as ONE tcgen05 kernel per 128-frame tile:
+//
+//   GEMM 1   xin[t, 0:2H]  = sum_{j,c} h[t + (j-K/2) dil, c] * Win[j][n][c]          (dilated conv, TMA-shifted taps)
+//   epilogue acts[t, 0:H]  = tanh(drop(xin[:, :H] + b) + g) * sigmoid(drop(xin[:, H:] + b) + g)   (commons.py:61-68)
+//            -> written as bf16 straight into the shared-memory A-operand slots (canonical SWIZZLE_128B layout)
+//   GEMM 2   rs[t, 0:RS]   = acts[t, :] * Wrs[n][c]                                   (1x1 res/skip conv)
+//   epilogue h' = (h + rs[:, :H] + b) * mask ;  skip (+)= rs[:, H:] + b               (modules.py:166-170)
+//
+// The 2H-channel pre-activation and the gate output never touch HBM (except the bf16 copies the backward needs,
+// written only when training).  TMEM: the same 2H fp32 columns hold xin, then rs.  Thread <-> frame ownership
+// (TMEM lane = frame) makes every epilogue step thread-local.
+#include <string.h>
+
+#include "tc.cuh"
+#include "ops.h"
+
+namespace gtk {
+namespace tc {
+
+struct WnCtl {
+    uint64_t full[3], empty[3], acc_full, acts_ready;
+    uint32_t tmem_base;
+};
+
+constexpr int WN_STAGES = 3;
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmWin,
+                const __grid_constant__ CUtensorMap tmWrs, const WnLayerParams p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int H = p.H, H2 = 2 * p.H, RS = p.RS;
+    const int n_kh = H / KC;                            // k-chunks of the hidden dimension (<= 3)
+    const int stage_bytes = A_BYTES + H2 * KC * 2;      // A tile + up to 2H weight rows of one k-chunk
+    WnCtl* ctl = reinterpret_cast<WnCtl*>(smem + (size_t)WN_STAGES * stage_bytes);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int t0 = blockIdx.x * BT, b = blockIdx.y;
+    const int n1 = p.taps * n_kh;                       // GEMM-1 iterations
+    const int n_all = n1 + n_kh;                        // + GEMM-2 iterations
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < WN_STAGES; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
+        mbar_init(&ctl->acc_full, 1);
+        mbar_init(&ctl->acts_ready, 128);
+        mbar_fence_init();
+    }
+    if (warp == 2) tmem_alloc<512>(&ctl->tmem_base);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = ctl->tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            tma_prefetch_desc(&tmH);
+            tma_prefetch_desc(&tmWin);
+            tma_prefetch_desc(&tmWrs);
+            for (int it = 0; it < n_all; ++it) {
+                const int s = it % WN_STAGES, use = it / WN_STAGES;
+                if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
+                unsigned char* sa = smem + (size_t)s * stage_bytes;
+                unsigned char* sb = sa + A_BYTES;
+                if (it < n1) {
+                    const int j = it / n_kh, kc = it % n_kh;
+                    mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(A_BYTES + H2 * KC * 2));
+                    tma_load_3d(sa, &tmH, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
+                    tma_load_3d(sb, &tmWin, &ctl->full[s], kc * KC, 0, j);
+                    tma_load_3d(sb + (size_t)H * KC * 2, &tmWin, &ctl->full[s], kc * KC, H, j);
+                } else {
+                    const int kc = it - n1;             // A slot of this stage is written by the epilogue warps
+                    mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(RS * KC * 2));
+                    tma_load_2d(sb, &tmWrs, &ctl->full[s], kc * KC, 0);
+                    if (RS > H) tma_load_2d(sb + (size_t)H * KC * 2, &tmWrs, &ctl->full[s], kc * KC, H);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_bf16(BT, H);
+            for (int it = 0; it < n_all; ++it) {
+                const int s = it % WN_STAGES, use = it / WN_STAGES;
+                if (it == n1) {                          // GEMM 1 done -> epilogue 1 may read TMEM
+                    umma_commit(&ctl->acc_full);
+                    mbar_wait(&ctl->acts_ready, 0);      // acts are in the A slots, xin columns are free again
+                    tc_fence_after();
+                }
+                mbar_wait(&ctl->full[s], use & 1);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+                const uint32_t sb = sa + A_BYTES;
+                const uint64_t adesc = umma_desc_kmajor_sw128(sa);
+                const int nch = (it < n1) ? 2 : (RS > H ? 2 : 1);
+                const bool first = (it == 0) || (it == n1);
+#pragma unroll
+                for (int k = 0; k < KC / 16; ++k) {
+                    for (int ch = 0; ch < nch; ++ch) {
+                        const uint64_t bdesc = umma_desc_kmajor_sw128(sb + ch * H * KC * 2);
+                        umma_bf16(tmem + ch * H, adesc + 2 * k, bdesc + 2 * k, idesc, !(first && k == 0));
+                    }
+                }
+                umma_commit(&ctl->empty[s]);
+            }
+            umma_commit(&ctl->acc_full);
+        }
+    } else if (warp >= 4) {
+        const int q = warp & 3;
+        const int r = q * 32 + lane;                     // row of the tile == TMEM lane
+        const int t = t0 + r;
+        const bool t_ok = t < p.T;
+        const float mk = (p.mask && t_ok) ? p.mask[(size_t)b * p.T + t] : 1.f;
+        const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
+        const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+        const float* cond = p.cond ? p.cond + (size_t)b * p.cond_bstride : nullptr;
+
+        // ---------------------------------------------------------------- epilogue 1: gate -> A operand of GEMM 2
+        mbar_wait(&ctl->acc_full, 0);
+        tc_fence_after();
+        for (int c0 = 0; c0 < H; c0 += 16) {
+            float a[16], g[16];
+            tmem_ld16(trow + c0, a);
+            tmem_ld16(trow + H + c0, g);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                float xa = a[i] + __ldg(p.bias_in + c0 + i);
+                float xg = g[i] + __ldg(p.bias_in + H + c0 + i);
+                if (p.drop_p > 0.f) {
+                    xa *= dropout_scale(p.drop_seed, frame * H2 + c0 + i, p.drop_p);
+                    xg *= dropout_scale(p.drop_seed, frame * H2 + H + c0 + i, p.drop_p);
+                }
+                if (cond) { xa += __ldg(cond + c0 + i); xg += __ldg(cond + H + c0 + i); }
+                a[i] = tanhf(xa);
+                g[i] = sigmoid_f(xg);
+            }
+            if (p.ts_save && t_ok) {
+                store_bf16x16(p.ts_save + frame * H2 + c0, a);
+                store_bf16x16(p.ts_save + frame * H2 + H + c0, g);
+            }
+#pragma unroll
+            for (int i = 0; i < 16; ++i) a[i] *= g[i];
+            if (p.acts_save && t_ok) store_bf16x16(p.acts_save + frame * H + c0, a);
+            // canonical K-major SWIZZLE_128B: row r at r*128 B, 16-byte chunk index XOR (r % 8)
+            const int kc = c0 / KC, ci = (c0 % KC) / 8;
+            unsigned char* slot = smem + (size_t)((n1 + kc) % WN_STAGES) * stage_bytes + (size_t)r * 128;
+            uint32_t w[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                __nv_bfloat162 h2 = __floats2bfloat162_rn(a[2 * i], a[2 * i + 1]);
+                w[i] = *reinterpret_cast<uint32_t*>(&h2);
+            }
+            *reinterpret_cast<uint4*>(slot + ((ci ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+            *reinterpret_cast<uint4*>(slot + (((ci + 1) ^ (r & 7)) << 4)) = make_uint4(w[4], w[5], w[6], w[7]);
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        mbar_arrive(&ctl->acts_ready);
+
+        // ---------------------------------------------------------------- epilogue 2: residual / skip
+        mbar_wait(&ctl->acc_full, 1);
+        tc_fence_after();
+        for (int c0 = 0; c0 < H; c0 += 16) {
+            float v[16], sk[16];
+            if (RS > H) {
+                tmem_ld16(trow + c0, v);
+                tmem_ld16(trow + H + c0, sk);
+            } else {
+                tmem_ld16(trow + c0, sk);
+            }
+            if (!t_ok) continue;
+            if (RS > H) {
+                const float4* x4 = reinterpret_cast<const float4*>(p.h_f32 + frame * H + c0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float4 x = x4[i];
+                    v[4 * i] = (v[4 * i] + __ldg(p.bias_rs + c0 + 4 * i) + x.x) * mk;
+                    v[4 * i + 1] = (v[4 * i + 1] + __ldg(p.bias_rs + c0 + 4 * i + 1) + x.y) * mk;
+                    v[4 * i + 2] = (v[4 * i + 2] + __ldg(p.bias_rs + c0 + 4 * i + 2) + x.z) * mk;
+                    v[4 * i + 3] = (v[4 * i + 3] + __ldg(p.bias_rs + c0 + 4 * i + 3) + x.w) * mk;
+                }
+                float4* o4 = reinterpret_cast<float4*>(p.h_out_f32 + frame * H + c0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                store_bf16x16(p.h_out_bf16 + frame * H + c0, v);
+            }
+            const int bo = (RS > H) ? H : 0;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) sk[i] += __ldg(p.bias_rs + bo + c0 + i);
+            if (!p.first) {
+                const float4* s4 = reinterpret_cast<const float4*>(p.skip_f32 + frame * H + c0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float4 x = s4[i];
+                    sk[4 * i] += x.x; sk[4 * i + 1] += x.y; sk[4 * i + 2] += x.z; sk[4 * i + 3] += x.w;
+                }
+            }
+            if (p.last) {                                 // WN output = skip * mask (modules.py:171), operand of `end`
+#pragma unroll
+                for (int i = 0; i < 16; ++i) sk[i] *= mk;
+                store_bf16x16(p.skip_out_bf16 + frame * H + c0, sk);
+            } else {
+                float4* o4 = reinterpret_cast<float4*>(p.skip_f32 + frame * H + c0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) o4[i] = make_float4(sk[4 * i], sk[4 * i + 1], sk[4 * i + 2], sk[4 * i + 3]);
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem);
+    }
+}
+
+int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, const __nv_bfloat16* wrs_p, WnLayerParams p,
+                    cudaStream_t st) {
+    GTK_REQUIRE(h_bf16 && win_p && wrs_p && p.bias_in && p.bias_rs, "null");
+    GTK_REQUIRE(p.H % KC == 0 && p.H / KC <= WN_STAGES && p.H <= 256, "fused WN layer needs hidden in {64,128,192}");
+    GTK_REQUIRE(p.RS == p.H || p.RS == 2 * p.H, "res_skip channels");
+    GTK_REQUIRE(p.taps >= 1 && (p.taps & 1) && p.dil >= 1, "bad conv shape");
+    GTK_REQUIRE(p.last ? (p.RS == p.H && p.skip_out_bf16) : (p.RS == 2 * p.H && p.h_f32 && p.h_out_f32 && p.h_out_bf16), "layer outputs");
+    GTK_REQUIRE(p.first || p.skip_f32, "skip accumulator");
+    GTK_REQUIRE(p.last || p.skip_f32, "skip accumulator");
+    if (p.B == 0 || p.T == 0) return GTK_OK;
+    const int H = p.H;
+    CUtensorMap tmH, tmWin, tmWrs;
+    {
+        const uint64_t dims[3] = {(uint64_t)H, (uint64_t)p.T, (uint64_t)p.B};
+        const uint64_t strides[2] = {(uint64_t)H * 2, (uint64_t)H * 2 * p.T};
+        const uint32_t box[3] = {KC, BT, 1};
+        int rc = make_tmap_bf16(&tmH, h_bf16, 3, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    {
+        const uint64_t dims[3] = {(uint64_t)H, (uint64_t)2 * H, (uint64_t)p.taps};
+        const uint64_t strides[2] = {(uint64_t)H * 2, (uint64_t)H * 2 * 2 * H};
+        const uint32_t box[3] = {KC, (uint32_t)H, 1};
+        int rc = make_tmap_bf16(&tmWin, win_p, 3, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    {
+        const uint64_t dims[2] = {(uint64_t)H, (uint64_t)p.RS};
+        const uint64_t strides[1] = {(uint64_t)H * 2};
+        const uint32_t box[2] = {KC, (uint32_t)H};
+        int rc = make_tmap_bf16(&tmWrs, wrs_p, 2, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    const size_t smem = (size_t)WN_STAGES * (A_BYTES + (size_t)2 * H * KC * 2) + sizeof(WnCtl) + 1024;
+    GTK_REQUIRE(smem <= 227 * 1024, "tile does not fit in shared memory");
+    GTK_CUDA(cudaFuncSetAttribute(wn_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid(ceil_div(p.T, BT), p.B);
+    ProfScope prof("wn_layer_tc", st);
+    wn_layer_kernel<<<grid, NTHREADS, smem, st>>>(tmH, tmWin, tmWrs, p);
+    return check_launch("wn_layer_tc");
+}
+
+}  // namespace tc
+}  // namespace gtk

@@ -152,6 +152,17 @@ int gtk_tc_pack_weight(const float* w, void* wp_bf16, int M, int Cin, int K, int
  * flags bit0: multiply the output by mask[b,t].  out_f32 (ld_f32) and out_bf16 (ld_bf16) frame-major, either may be NULL. */
 int gtk_tc_conv1d(const void* in_bf16, int ld_in, const void* wp_bf16, const float* bias, const float* mask, int B, int T,
                   int K, int dil, int N, float* out_f32, int ld_f32, void* out_bf16, int ld_bf16, int flags, void* stream);
+/* One fused WaveNet layer (modules.py:151-170) on frames: dilated conv -> (dropout) -> +cond -> tanh*sigmoid ->
+ * res/skip 1x1 -> residual / skip update, in one tcgen05 kernel.  h: layer input as bf16 frames [B,T,H] (operand)
+ * and fp32 frames (residual master).  win_p = gtk_tc_pack_weight(in_layers[i].weight) [K][2H][H]; wrs_p =
+ * gtk_tc_pack_weight(res_skip_layers[i].weight) [1][RS][H].  cond: this layer's 2H slice of cond_layer(g), batch
+ * stride cond_bstride floats, or NULL.  first: skip is overwritten; last (RS == H): skip*mask -> skip_out_bf16 and no
+ * h_out.  ts_save [B,T,2H] / acts_save [B,T,H] (bf16) are the activations the backward needs, or NULL. */
+int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, const void* wrs_p, const float* bias_in,
+                    const float* bias_rs, const float* cond, size_t cond_bstride, const float* mask, int B, int T, int H,
+                    int RS, int K, int dil, int first, int last, float drop_p, unsigned long long drop_seed,
+                    float* h_out_f32, void* h_out_bf16, float* skip_f32, void* skip_out_bf16, void* ts_save,
+                    void* acts_save, void* stream);
 
 /* ---- whole decoder (models.py:719-789) --------------------------------------------------- */
 typedef struct gtk_decoder_desc {

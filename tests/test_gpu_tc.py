@@ -47,3 +47,58 @@ def test_tc_conv1d_data_gradient_form():
     wpt = ops.tc_pack_weight(w, transpose=True)
     dx, _ = ops.tc_conv1d(ops.tc_frames(dout), wpt, None, dil)
     np.testing.assert_allclose(dx.cpu().numpy(), x.grad.permute(0, 2, 1).cpu().numpy(), rtol=2e-3, atol=2e-3)
+
+
+@pytest.mark.parametrize("last,use_cond", [(False, True), (True, False), (False, False)])
+def test_fused_wn_layer_matches_torch(last, use_cond):
+    """One WaveNet layer (modules.py:151-170) in the fused tcgen05 kernel vs torch on bf16-rounded operands."""
+    import ctypes
+    from glowtts_b200 import _lib, ops
+    gen = torch.Generator(device="cuda").manual_seed(11 + int(last))
+    B, H, T, K, dil = 3, 192, 301, 5, 1
+    RS = H if last else 2 * H
+    h = torch.randn(B, H, T, device="cuda", generator=gen)
+    lengths = torch.tensor([T, T - 40, T // 2], device="cuda")
+    mask = (torch.arange(T, device="cuda")[None, :] < lengths[:, None]).float()
+    h = h * mask[:, None]
+    win = torch.randn(2 * H, H, K, device="cuda", generator=gen) / (H * K) ** 0.5
+    wrs = torch.randn(RS, H, 1, device="cuda", generator=gen) / H ** 0.5
+    b_in = torch.randn(2 * H, device="cuda", generator=gen) * 0.1
+    b_rs = torch.randn(RS, device="cuda", generator=gen) * 0.1
+    cond = torch.randn(B, 2 * H, device="cuda", generator=gen) * 0.3 if use_cond else None
+    skip_prev = torch.randn(B, T, H, device="cuda", generator=gen)
+    # reference
+    xin = F.conv1d(_bf(h), _bf(win), b_in, padding=(K - 1) * dil // 2, dilation=dil)
+    if cond is not None:
+        xin = xin + cond[:, :, None]
+    tt, ss = torch.tanh(xin[:, :H]), torch.sigmoid(xin[:, H:])
+    acts = tt * ss
+    rs = F.conv1d(_bf(acts), _bf(wrs), b_rs)
+    # kernel
+    hf = h.permute(0, 2, 1).contiguous()
+    hb = hf.to(torch.bfloat16)
+    win_p, wrs_p = ops.tc_pack_weight(win), ops.tc_pack_weight(wrs)
+    h_out32 = torch.zeros(B, T, H, device="cuda")
+    h_out16 = torch.zeros(B, T, H, device="cuda", dtype=torch.bfloat16)
+    skip32 = skip_prev.clone()
+    skip16 = torch.zeros(B, T, H, device="cuda", dtype=torch.bfloat16)
+    ts = torch.zeros(B, T, 2 * H, device="cuda", dtype=torch.bfloat16)
+    ac = torch.zeros(B, T, H, device="cuda", dtype=torch.bfloat16)
+    P = lambda t: None if t is None else ctypes.c_void_p(t.data_ptr())
+    _lib.call("gtk_tc_wn_layer", P(hb), P(hf), P(win_p), P(wrs_p), P(b_in), P(b_rs), P(cond), 2 * H, P(mask), B, T, H, RS, K, dil,
+              0, int(last), ctypes.c_float(0.0), 0, P(h_out32), P(h_out16), P(skip32), P(skip16), P(ts), P(ac),
+              ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    tol = dict(rtol=1e-2, atol=1e-2)
+    np.testing.assert_allclose(ts[:, :, :H].float().cpu().numpy(), tt.permute(0, 2, 1).cpu().numpy(), **tol)
+    np.testing.assert_allclose(ts[:, :, H:].float().cpu().numpy(), ss.permute(0, 2, 1).cpu().numpy(), **tol)
+    np.testing.assert_allclose(ac.float().cpu().numpy(), acts.permute(0, 2, 1).cpu().numpy(), **tol)
+    if last:
+        want = (skip_prev + rs.permute(0, 2, 1)) * mask[:, :, None]
+        np.testing.assert_allclose(skip16.float().cpu().numpy(), want.cpu().numpy(), rtol=2e-2, atol=2e-2)
+    else:
+        want_h = (h + rs[:, :H]).permute(0, 2, 1) * mask[:, :, None]
+        np.testing.assert_allclose(h_out32.cpu().numpy(), want_h.cpu().numpy(), rtol=5e-3, atol=5e-3)
+        np.testing.assert_allclose(h_out16.float().cpu().numpy(), want_h.cpu().numpy(), rtol=2e-2, atol=2e-2)
+        want_s = skip_prev + rs[:, H:].permute(0, 2, 1)
+        np.testing.assert_allclose(skip32.cpu().numpy(), want_s.cpu().numpy(), rtol=5e-3, atol=5e-3)
