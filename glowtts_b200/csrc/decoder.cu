@@ -7,7 +7,9 @@
 //  * Weight norm is folded on device once per call; its backward is fused behind each weight gradient.
 //  * precision 0 runs every contraction in fp32 on CUDA cores (exact-parity path);
 //    precision 1 routes the WN / start / end contractions to the bf16 tcgen05 kernels (conv_tc.cu).
-#include "common.cuh"
+#include <string.h>
+
+#include "tc.cuh"
 #include "ops.h"
 #include "../../include/glowtts_b200.h"
 
@@ -100,9 +102,13 @@ static void make_layout(const Dims& D, int train, Layout* L) {
     L->total = off;
 }
 
+struct TcLayout;
+static size_t tc_workspace_bytes(const Dims& D, int train);
+
 size_t workspace_bytes(const gtk_decoder_desc* d, int train) {
     Dims D;
     if (make_dims(d, &D) != GTK_OK) return 0;
+    if (d->precision == 1) return tc_workspace_bytes(D, train);
     Layout L;
     make_layout(D, train, &L);
     return L.total * sizeof(float) + 256;
@@ -178,11 +184,22 @@ static int coupling_net(const Dims& D, const Layout& L, const gtk_block_params& 
     return GTK_OK;
 }
 
+#include "decoder_tc.inl"
+
+static size_t tc_workspace_bytes(const Dims& D, int train) {
+    Layout L32;
+    make_layout(D, 0, &L32);
+    TcLayout L;
+    make_tc_layout(D, L32, train, &L);
+    return L.total + 1024;
+}
+
 int forward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const float* x, const float* mask, float* z,
             float* logdet, void* workspace, size_t ws_bytes, int train, cudaStream_t st) {
     Dims D;
     GTK_TRY(make_dims(d, &D));
     GTK_REQUIRE(blocks && x && mask && z && logdet && workspace, "null pointer");
+    if (d->precision == 1) return tc_forward(d, D, blocks, x, mask, z, logdet, workspace, ws_bytes, train, st);
     if (d->precision != 0) { set_error("decoder: precision %d not available in this build", d->precision); return GTK_ERR_UNSUPPORTED; }
     Layout L;
     make_layout(D, train, &L);
@@ -221,6 +238,7 @@ int reverse(const gtk_decoder_desc* d, const gtk_block_params* blocks, const flo
     Dims D;
     GTK_TRY(make_dims(d, &D));
     GTK_REQUIRE(blocks && z && mask && x && workspace, "null pointer");
+    if (d->precision == 1) return tc_reverse(d, D, blocks, z, mask, x, workspace, ws_bytes, st);
     if (d->precision != 0) { set_error("decoder: precision %d not available in this build", d->precision); return GTK_ERR_UNSUPPORTED; }
     Layout L;
     make_layout(D, 0, &L);

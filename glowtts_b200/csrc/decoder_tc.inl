@@ -1,0 +1,243 @@
+// glowtts_b200/csrc/decoder_tc.inl -- precision 1: the coupling networks on the bf16 tcgen05 kernels
+// (conv_tc.cu, wn_tc.cu); ActNorm / InvConvNear / logdet bookkeeping stay fp32.  Included by decoder.cu.
+//
+// Per block:  mix (fp32, t-major) -> frames(x0) -> start 1x1 [plain epilogue, mask] -> L fused WN layers ->
+//             end 1x1 [affine-coupling epilogue: z1, logdet, x0 copy].  Activations inside the coupling network are
+//             frame-major ([B, T', H], channel fastest): bf16 operand copies + an fp32 master of the residual stream.
+
+typedef __nv_bfloat16 bf16;
+
+static inline int pad64(int n) { return (n + 63) / 64 * 64; }
+
+struct TcPack {            // bf16 element offsets inside one block's packed-weight set
+    size_t start, in[GTK_MAX_LAYERS], rs[GTK_MAX_LAYERS], end;          // forward operands
+    size_t t_start, t_in[GTK_MAX_LAYERS], t_rs[GTK_MAX_LAYERS], t_end;  // data-gradient operands
+    size_t total;
+};
+struct TcAct {             // byte offsets inside one block's activation set
+    size_t xmix, a0, h[GTK_MAX_LAYERS], ts[GTK_MAX_LAYERS], acts[GTK_MAX_LAYERS], skip_bf, logs, total;
+};
+struct TcLayout {          // byte offsets in the workspace
+    size_t mask_sq, x_len, winv, icld, we, pack, X, act, hf[2], skipf, bwd, total;
+    size_t we_floats, x_bytes;
+    int n_pack, n_act, n_x;
+    TcPack P;
+    TcAct A;
+    // backward temporaries
+    size_t b_dZ, b_dM, b_dend, b_drs, b_dxin, b_dgate, b_dhf[2], b_dh0, b_dweff;
+};
+
+static int tc_supported(const Dims& D) {
+    if (D.H % 64 != 0 || D.H > 192) { set_error("bf16 path: hidden_channels must be 64, 128 or 192 (got %d)", D.H); return GTK_ERR_UNSUPPORTED; }
+    if ((D.C / 2) % 16 != 0) { set_error("bf16 path: in_channels*n_sqz/2 must be a multiple of 16 (got %d)", D.C / 2); return GTK_ERR_UNSUPPORTED; }
+    return GTK_OK;
+}
+
+static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout* L) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 1024); return o; };
+    const size_t nq = D.nq;
+    const int H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
+    L->mask_sq = take(nq * 4);
+    L->x_len = take((size_t)D.B * 4);
+    L->winv = take((size_t)D.NB * 64 * 4);
+    L->icld = take((size_t)D.NB * 4);
+    L->we_floats = L32.weff_block;
+    L->we = take(L32.weff_block * 4);
+    // packed weights
+    size_t w = 0;
+    auto wtake = [&](size_t n) { size_t o = w; w = align_up(w + n, 512); return o; };
+    TcPack& P = L->P;
+    P.start = wtake((size_t)H * pad64(Ch));
+    for (int i = 0; i < D.L; ++i) P.in[i] = wtake((size_t)K * 2 * H * H);
+    for (int i = 0; i < D.L; ++i) P.rs[i] = wtake((size_t)((i < D.L - 1) ? 2 * H : H) * H);
+    P.end = wtake((size_t)C * H);
+    P.t_start = wtake((size_t)Ch * H);
+    for (int i = 0; i < D.L; ++i) P.t_in[i] = wtake((size_t)K * H * 2 * H);
+    for (int i = 0; i < D.L; ++i) P.t_rs[i] = wtake((size_t)H * pad64((i < D.L - 1) ? 2 * H : H));
+    P.t_end = wtake((size_t)H * pad64(C));
+    P.total = w;
+    L->n_pack = train ? D.NB : 1;
+    L->pack = take(w * 2 * L->n_pack);
+    // block inputs / outputs (fp32, t-major)
+    L->x_bytes = (size_t)C * nq * 4;
+    L->n_x = train ? D.NB + 1 : 2;
+    L->X = take(L->x_bytes * L->n_x);
+    // activations
+    size_t a = 0;
+    auto atake = [&](size_t bytes) { size_t o = a; a = align_up(a + bytes, 1024); return o; };
+    TcAct& A = L->A;
+    A.xmix = atake((size_t)C * nq * 4);
+    A.a0 = atake((size_t)pad64(Ch) * nq * 2);
+    for (int i = 0; i < D.L; ++i) A.h[i] = atake((size_t)H * nq * 2);
+    for (int i = 0; i < D.L; ++i) A.ts[i] = atake((size_t)2 * H * nq * 2);
+    for (int i = 0; i < D.L; ++i) A.acts[i] = atake((size_t)H * nq * 2);
+    A.skip_bf = atake((size_t)H * nq * 2);
+    A.logs = atake((size_t)Ch * nq * 4);
+    A.total = a;
+    L->n_act = train ? D.NB : 1;
+    L->act = take(a * L->n_act);
+    L->hf[0] = take((size_t)H * nq * 4);
+    L->hf[1] = take((size_t)H * nq * 4);
+    L->skipf = take((size_t)H * nq * 4);
+    L->bwd = off;
+    if (train) {
+        L->b_dZ = take((size_t)C * nq * 4);
+        L->b_dM = take((size_t)C * nq * 4);
+        L->b_dend = take((size_t)pad64(C) * nq * 2);
+        L->b_drs = take((size_t)2 * H * nq * 2);
+        L->b_dxin = take((size_t)2 * H * nq * 2);
+        L->b_dgate = take((size_t)2 * H * nq * 2);
+        L->b_dhf[0] = take((size_t)H * nq * 4);
+        L->b_dhf[1] = take((size_t)H * nq * 4);
+        L->b_dh0 = take((size_t)H * nq * 2);
+        size_t wmax = (size_t)2 * H * H * K;
+        if ((size_t)C * H > wmax) wmax = (size_t)C * H;
+        L->b_dweff = take(wmax * 4);
+    }
+    L->total = off;
+}
+
+// fp32 effective weights (we) -> bf16 operand packs of one block
+static int tc_pack_block(const Dims& D, const Layout& L32, const TcLayout& L, const gtk_block_params& P, const float* we,
+                         bf16* pk, int with_transposed, cudaStream_t st) {
+    const int H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
+    const TcPack& Q = L.P;
+    GTK_TRY(tc::pack_weight_bf16(w_start(L32, P, we), pk + Q.start, H, Ch, 1, 0, H, pad64(Ch), st));
+    for (int i = 0; i < D.L; ++i) {
+        const int RS = (i < D.L - 1) ? 2 * H : H;
+        GTK_TRY(tc::pack_weight_bf16(w_in(L32, P, we, i), pk + Q.in[i], 2 * H, H, K, 0, 2 * H, H, st));
+        GTK_TRY(tc::pack_weight_bf16(w_rs(L32, P, we, i), pk + Q.rs[i], RS, H, 1, 0, RS, H, st));
+    }
+    GTK_TRY(tc::pack_weight_bf16(P.end_w, pk + Q.end, C, H, 1, 0, C, H, st));
+    if (with_transposed) {
+        GTK_TRY(tc::pack_weight_bf16(w_start(L32, P, we), pk + Q.t_start, H, Ch, 1, 1, Ch, H, st));
+        for (int i = 0; i < D.L; ++i) {
+            const int RS = (i < D.L - 1) ? 2 * H : H;
+            GTK_TRY(tc::pack_weight_bf16(w_in(L32, P, we, i), pk + Q.t_in[i], 2 * H, H, K, 1, H, 2 * H, st));
+            GTK_TRY(tc::pack_weight_bf16(w_rs(L32, P, we, i), pk + Q.t_rs[i], RS, H, 1, 1, H, pad64(RS), st));
+        }
+        GTK_TRY(tc::pack_weight_bf16(P.end_w, pk + Q.t_end, C, H, 1, 1, H, pad64(C), st));
+    }
+    return GTK_OK;
+}
+
+// start -> WN -> end(+affine) of one block.  xc = mixed block input (t-major fp32), zout = block output.
+static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout& L, const gtk_block_params& P, const bf16* pk,
+                       const float* xc, float* zout, float* logdet, const float* mask, unsigned char* act, unsigned char* ws,
+                       int reverse, int save, unsigned long long seed_base, cudaStream_t st) {
+    const int B = D.B, T = D.Tq, H = D.H, C = D.C, Ch = D.C / 2;
+    const TcPack& Q = L.P;
+    const TcAct& A = L.A;
+    bf16* a0 = reinterpret_cast<bf16*>(act + A.a0);
+    float* hf[2] = {reinterpret_cast<float*>(ws + L.hf[0]), reinterpret_cast<float*>(ws + L.hf[1])};
+    float* skipf = reinterpret_cast<float*>(ws + L.skipf);
+    GTK_TRY(tc::frames_from_tmajor(xc, a0, B, C, T, 0, Ch, pad64(Ch), st));
+    {
+        tc::ConvTcParams p;
+        memset(&p, 0, sizeof(p));
+        p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = pad64(Ch) / 64; p.N = H;
+        p.bias = P.start_b; p.mask = mask; p.mask_out = 1;
+        p.out_f32 = hf[0]; p.ld_f32 = H;
+        p.out_bf16 = reinterpret_cast<bf16*>(act + A.h[0]); p.ld_bf16 = H;
+        GTK_TRY(tc::conv_tc_launch(a0, pad64(Ch), pk + Q.start, p, tc::EPI_PLAIN, st));
+    }
+    for (int i = 0; i < D.L; ++i) {
+        tc::WnLayerParams p;
+        memset(&p, 0, sizeof(p));
+        p.B = B; p.T = T; p.H = H; p.RS = (i < D.L - 1) ? 2 * H : H; p.taps = D.K; p.dil = ipow(D.dr, i);
+        p.first = (i == 0); p.last = (i == D.L - 1);
+        p.bias_in = P.in_b[i]; p.bias_rs = P.rs_b[i];
+        p.cond = P.cond ? P.cond + (size_t)i * 2 * H : nullptr; p.cond_bstride = (size_t)2 * H * D.L;
+        p.mask = mask;
+        p.drop_p = 0.f; p.drop_seed = seed_base + i;
+        p.h_f32 = hf[i & 1]; p.h_out_f32 = hf[(i + 1) & 1];
+        p.h_out_bf16 = (i < D.L - 1) ? reinterpret_cast<bf16*>(act + A.h[i + 1]) : nullptr;
+        p.skip_f32 = skipf;
+        p.skip_out_bf16 = reinterpret_cast<bf16*>(act + A.skip_bf);
+        p.ts_save = save ? reinterpret_cast<bf16*>(act + A.ts[i]) : nullptr;
+        p.acts_save = save ? reinterpret_cast<bf16*>(act + A.acts[i]) : nullptr;
+        GTK_TRY(tc::wn_layer_launch(reinterpret_cast<const bf16*>(act + A.h[i]), pk + Q.in[i], pk + Q.rs[i], p, st));
+    }
+    {
+        tc::ConvTcParams p;
+        memset(&p, 0, sizeof(p));
+        p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = H / 64; p.N = C;
+        p.bias = P.end_b; p.mask = mask;
+        p.aff_x = xc; p.aff_z = zout; p.aff_logdet = reverse ? nullptr : logdet;
+        p.aff_logs_save = save ? reinterpret_cast<float*>(act + A.logs) : nullptr;
+        p.aff_reverse = reverse; p.aff_sigmoid_scale = d->sigmoid_scale;
+        GTK_TRY(tc::conv_tc_launch(reinterpret_cast<const bf16*>(act + A.skip_bf), H, pk + Q.end, p, tc::EPI_AFFINE, st));
+    }
+    return GTK_OK;
+}
+
+static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_params* blocks, const float* x, const float* mask,
+                      float* z, float* logdet, void* workspace, size_t ws_bytes, int train, cudaStream_t st) {
+    GTK_TRY(tc_supported(D));
+    Layout L32;
+    make_layout(D, 0, &L32);
+    TcLayout L;
+    make_tc_layout(D, L32, train, &L);
+    if (ws_bytes < L.total) { set_error("decoder_forward(bf16): workspace %zu < %zu", ws_bytes, L.total); return GTK_ERR_WORKSPACE; }
+    if (D.B == 0) return GTK_OK;
+    GTK_CUDA(cudaMemsetAsync(logdet, 0, sizeof(float) * D.B, st));
+    if (D.Tq == 0) return GTK_OK;
+    unsigned char* ws = static_cast<unsigned char*>(workspace);
+    float* msq = reinterpret_cast<float*>(ws + L.mask_sq);
+    float* x_len = reinterpret_cast<float*>(ws + L.x_len);
+    float* we = reinterpret_cast<float*>(ws + L.we);
+    GTK_TRY(flow::squeeze(x, mask, reinterpret_cast<float*>(ws + L.X), msq, D.B, D.Cin, D.T, D.n, 0, st));
+    GTK_TRY(flow::mask_len(msq, x_len, D.B, D.Tq, st));
+    for (int blk = 0; blk < D.NB; ++blk) {
+        const gtk_block_params& P = blocks[blk];
+        GTK_TRY(check_block(D, P));
+        unsigned char* act = ws + L.act + (size_t)(train ? blk : 0) * L.A.total;
+        bf16* pk = reinterpret_cast<bf16*>(ws + L.pack) + (size_t)(train ? blk : 0) * L.P.total;
+        const float* xin = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? blk : (blk & 1)) * L.x_bytes);
+        float* xout = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? blk + 1 : ((blk + 1) & 1)) * L.x_bytes);
+        float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
+        float* icld = reinterpret_cast<float*>(ws + L.icld) + blk;
+        float* xmix = reinterpret_cast<float*>(act + L.A.xmix);
+        GTK_TRY(fold_weights(D, L32, P, we, st));
+        GTK_TRY(tc_pack_block(D, L32, L, P, we, pk, train, st));
+        GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, icld, st));
+        GTK_TRY(flow::mix(xin, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, xmix, D.B, D.C, D.Tq, 0, st));
+        GTK_TRY(flow::logdet_const(P.an_logs, D.C, icld, (float)(D.C / D.NS), x_len, logdet, D.B, 1, st));
+        GTK_TRY(tc_coupling(d, D, L, P, pk, xmix, xout, logdet, msq, act, ws, 0, train, 0x1000ull * blk, st));
+    }
+    const float* xfin = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? D.NB : (D.NB & 1)) * L.x_bytes);
+    GTK_TRY(flow::unsqueeze(xfin, msq, z, nullptr, D.B, D.C, D.Tq, D.n, 0, st));
+    return GTK_OK;
+}
+
+static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_params* blocks, const float* z, const float* mask,
+                      float* x, void* workspace, size_t ws_bytes, cudaStream_t st) {
+    GTK_TRY(tc_supported(D));
+    Layout L32;
+    make_layout(D, 0, &L32);
+    TcLayout L;
+    make_tc_layout(D, L32, 0, &L);
+    if (ws_bytes < L.total) { set_error("decoder_reverse(bf16): workspace %zu < %zu", ws_bytes, L.total); return GTK_ERR_WORKSPACE; }
+    if (D.B == 0 || D.Tq == 0) return GTK_OK;
+    unsigned char* ws = static_cast<unsigned char*>(workspace);
+    float* msq = reinterpret_cast<float*>(ws + L.mask_sq);
+    float* we = reinterpret_cast<float*>(ws + L.we);
+    float* xa = reinterpret_cast<float*>(ws + L.X);
+    float* xb = reinterpret_cast<float*>(ws + L.X + L.x_bytes);
+    unsigned char* act = ws + L.act;
+    bf16* pk = reinterpret_cast<bf16*>(ws + L.pack);
+    GTK_TRY(flow::squeeze(z, mask, xa, msq, D.B, D.Cin, D.T, D.n, 0, st));
+    for (int blk = D.NB - 1; blk >= 0; --blk) {
+        const gtk_block_params& P = blocks[blk];
+        GTK_TRY(check_block(D, P));
+        float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
+        GTK_TRY(fold_weights(D, L32, P, we, st));
+        GTK_TRY(tc_pack_block(D, L32, L, P, we, pk, 0, st));
+        GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, nullptr, st));
+        GTK_TRY(tc_coupling(d, D, L, P, pk, xa, xb, nullptr, msq, act, ws, 1, 0, 0, st));
+        GTK_TRY(flow::mix(xb, msq, P.an_logs, P.an_bias, winv, D.NS, xa, D.B, D.C, D.Tq, 1, st));
+    }
+    GTK_TRY(flow::unsqueeze(xa, msq, x, nullptr, D.B, D.C, D.Tq, D.n, 0, st));
+    return GTK_OK;
+}

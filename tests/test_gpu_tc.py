@@ -102,3 +102,52 @@ def test_fused_wn_layer_matches_torch(last, use_cond):
         np.testing.assert_allclose(h_out16.float().cpu().numpy(), want_h.cpu().numpy(), rtol=2e-2, atol=2e-2)
         want_s = skip_prev + rs[:, H:].permute(0, 2, 1)
         np.testing.assert_allclose(skip32.cpu().numpy(), want_s.cpu().numpy(), rtol=5e-3, atol=5e-3)
+
+
+def _decoders(cfg, seed, end_std=0.05):
+    import helpers
+    from glowtts_b200 import models
+    sd = helpers.make_state_dict(cfg, seed, end_std=end_std)
+    out = []
+    for prec in ("fp32", "bf16"):
+        dec = models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"], cfg["dilation_rate"],
+                                     cfg["n_blocks"], cfg["n_layers"], n_split=cfg["n_split"], n_sqz=cfg["n_sqz"],
+                                     gin_channels=cfg["gin_channels"], precision=prec)
+        dec.load_state_dict(sd, strict=False)
+        out.append(dec.cuda())
+    return out
+
+
+TC_CFGS = {
+    "h64": dict(in_channels=16, hidden_channels=64, kernel_size=5, dilation_rate=1, n_blocks=3, n_layers=3, n_split=4,
+                n_sqz=2, gin_channels=0),
+    "h128_g_dil2": dict(in_channels=16, hidden_channels=128, kernel_size=3, dilation_rate=2, n_blocks=2, n_layers=2,
+                        n_split=4, n_sqz=2, gin_channels=8),
+    "base": dict(in_channels=80, hidden_channels=192, kernel_size=5, dilation_rate=1, n_blocks=12, n_layers=4, n_split=4,
+                 n_sqz=2, gin_channels=0),
+}
+
+
+@pytest.mark.parametrize("name", list(TC_CFGS))
+def test_bf16_decoder_forward_and_reverse_track_fp32(name):
+    """Stated bound for the bf16 WN path (BASELINE.json): max |dz| <= 2e-2 * max|z|, |d logdet| <= 2e-2 * |logdet| + 0.5,
+    |d mle_loss| <= 5e-3, and reverse(forward(y)) == y within 5e-2 * max|y|."""
+    import helpers
+    from glowtts_b200 import commons
+    cfg = TC_CFGS[name]
+    f32, b16 = _decoders(cfg, 77, end_std=0.01 if name == "base" else 0.05)
+    B, T = (4, 300) if name != "base" else (3, 214)
+    y, mask, _, g = helpers.flow_inputs(cfg, B, T, 5, cfg["gin_channels"] > 0)
+    y, mask = y.cuda(), mask.cuda()
+    g = g.cuda() if g is not None else None
+    with torch.no_grad():
+        z0, ld0 = f32(y, mask, g=g)
+        z1, ld1 = b16(y, mask, g=g)
+        l0 = commons.mle_loss(z0, None, None, ld0, mask).item()
+        l1 = commons.mle_loss(z1, None, None, ld1, mask).item()
+        yb, _ = b16(z1, mask, g=g, reverse=True)
+    zerr = (z1 - z0).abs().max().item() / z0.abs().max().item()
+    lderr = ((ld1 - ld0).abs() / (ld0.abs() * 2e-2 + 0.5)).max().item()
+    rerr = (yb - y).abs().max().item() / y.abs().max().item()
+    print(f"{name}: rel|dz|={zerr:.2e} logdet={lderr:.2e} dloss={abs(l1 - l0):.2e} roundtrip={rerr:.2e}")
+    assert zerr < 2e-2 and lderr < 1.0 and abs(l1 - l0) < 5e-3 and rerr < 5e-2
