@@ -42,6 +42,7 @@ BlockGrads = BlockParams
 _CTYPES = {
     "int": ctypes.c_int, "size_t": ctypes.c_size_t, "float": ctypes.c_float,
     "void": None, "const char*": ctypes.c_char_p, "unsigned long long": ctypes.c_ulonglong,
+    "long long": ctypes.c_longlong,
 }
 
 _PROTO = re.compile(r"^\s*(int|size_t|const char\*|unsigned long long)\s+(gtk_\w+)\s*\(([^;{]*)\)\s*;", re.M | re.S)

@@ -256,6 +256,15 @@ int gtk_tc_conv1d(const void* in_bf16, int ld_in, const void* wp_bf16, const flo
                             mask, B, T, K, dil, N, out_f32, ld_f32, static_cast<__nv_bfloat16*>(out_bf16), ld_bf16, flags & 1, ST);
 }
 
+int gtk_tc_wgrad(const void* dy_bf16, int ld_y, const void* x_bf16, int ld_x, float* dw, int B, int T, int M, int Cin, int K,
+                 int dil, void* stream) {
+    return tc::wgrad_tc_launch(static_cast<const __nv_bfloat16*>(dy_bf16), ld_y, ld_y, static_cast<const __nv_bfloat16*>(x_bf16),
+                               ld_x, ld_x, dw, B, T, M, Cin, K, dil, ST);
+}
+int gtk_tc_colsum(const void* in_bf16, int ld, int n_cols, int groups, long long rows_per_group, float* out,
+                  size_t out_gstride, void* stream) {
+    return tc::colsum_frames(static_cast<const __nv_bfloat16*>(in_bf16), ld, n_cols, groups, rows_per_group, out, out_gstride, ST);
+}
 int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, const void* wrs_p, const float* bias_in,
                     const float* bias_rs, const float* cond, size_t cond_bstride, const float* mask, int B, int T, int H,
                     int RS, int K, int dil, int first, int last, float drop_p, unsigned long long drop_seed,

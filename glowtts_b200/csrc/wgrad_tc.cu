@@ -1,0 +1,192 @@
+// glowtts_b200/csrc/wgrad_tc.cu -- weight gradients of the frame-major convolutions on tcgen05.
+//
+//   dW[m][c][j] += sum_{b,t} dY[b, t, m] * X[b, t + (j - K/2) dil, c]
+//
+// Both operands are frame-major bf16 ([B, T, channels]), i.e. the reduction dimension (t) is the ROW index and the
+// M / N dimension is contiguous: "MN-major" UMMA operands.  A TMA box {64 channels, 64 frames} lands as 64 rows of
+// 128 B in the SWIZZLE_128B layout; 8 rows form one 1024-byte atom (SBO), successive 64-channel blocks are one box
+// (8192 B) apart (LBO).  The conv tap is again a shifted TMA box of X (zero-filled outside the utterance).
+// Grid = (M tiles of 128, taps, split-K); each CTA reduces its share of the (b, 64-frame chunk) steps into a
+// [128 x N] fp32 TMEM accumulator and adds it to dW with red.global.add.f32.
+#include <string.h>
+
+#include "tc.cuh"
+#include "ops.h"
+
+namespace gtk {
+namespace tc {
+
+constexpr int WG_TK = 64;                       // frames per k-step
+constexpr int WG_BOX = WG_TK * 128;             // bytes of one {64 ch, 64 frames} box
+constexpr int WG_STAGES = 4;
+
+struct WgCtl {
+    uint64_t full[WG_STAGES], empty[WG_STAGES], acc_full;
+    uint32_t tmem_base;
+};
+
+struct WgradTcParams {
+    int B, T, M, Cin, taps, dil;
+    int n_blk;                 // N = 64 * n_blk columns of X are reduced (>= Cin, zero padded)
+    int steps_total, splits;
+    float* dw;                 // [M][Cin][taps] fp32, accumulated
+};
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmX, const WgradTcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int a_bytes = 2 * WG_BOX, b_bytes = p.n_blk * WG_BOX;
+    const int stage_bytes = a_bytes + b_bytes;
+    WgCtl* ctl = reinterpret_cast<WgCtl*>(smem + (size_t)WG_STAGES * stage_bytes);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * 128, j = blockIdx.y, split = blockIdx.z;
+    const int chunks_t = (p.T + WG_TK - 1) / WG_TK;
+    const int s_lo = (int)((long long)p.steps_total * split / p.splits);
+    const int s_hi = (int)((long long)p.steps_total * (split + 1) / p.splits);
+    const int n_iter = s_hi - s_lo;
+    const int N = p.n_blk * 64;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < WG_STAGES; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
+        mbar_init(&ctl->acc_full, 1);
+        mbar_fence_init();
+    }
+    if (warp == 2) tmem_alloc<256>(&ctl->tmem_base);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = ctl->tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            tma_prefetch_desc(&tmY);
+            tma_prefetch_desc(&tmX);
+            for (int it = 0; it < n_iter; ++it) {
+                const int s = it % WG_STAGES, use = it / WG_STAGES;
+                if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
+                const int step = s_lo + it;
+                const int b = step / chunks_t, t0 = (step % chunks_t) * WG_TK;
+                unsigned char* sa = smem + (size_t)s * stage_bytes;
+                unsigned char* sb = sa + a_bytes;
+                mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)stage_bytes);
+                tma_load_3d(sa, &tmY, &ctl->full[s], m0, t0, b);
+                tma_load_3d(sa + WG_BOX, &tmY, &ctl->full[s], m0 + 64, t0, b);
+                for (int nb = 0; nb < p.n_blk; ++nb)
+                    tma_load_3d(sb + (size_t)nb * WG_BOX, &tmX, &ctl->full[s], nb * 64, t0 + (j - p.taps / 2) * p.dil, b);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_bf16(128, N, 1, 1);
+            for (int it = 0; it < n_iter; ++it) {
+                const int s = it % WG_STAGES, use = it / WG_STAGES;
+                mbar_wait(&ctl->full[s], use & 1);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+                const uint32_t sb = sa + a_bytes;
+#pragma unroll
+                for (int k = 0; k < WG_TK / 16; ++k) {
+                    const uint64_t adesc = umma_desc_mnmajor_sw128(sa + k * 2048, WG_BOX, 1024);
+                    const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + k * 2048, WG_BOX, 1024);
+                    umma_bf16(tmem, adesc, bdesc, idesc, (it | k) != 0);
+                }
+                umma_commit(&ctl->empty[s]);
+            }
+            umma_commit(&ctl->acc_full);
+        }
+    } else if (warp >= 4 && n_iter > 0) {
+        mbar_wait(&ctl->acc_full, 0);
+        tc_fence_after();
+        const int q = warp & 3;
+        const int m = m0 + q * 32 + lane;
+        const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+        for (int c0 = 0; c0 < N; c0 += 16) {
+            float v[16];
+            tmem_ld16(trow + c0, v);
+            if (m >= p.M) continue;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const int c = c0 + i;
+                if (c < p.Cin) atomicAdd(p.dw + ((size_t)m * p.Cin + c) * p.taps + j, v[i]);
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<256>(tmem);
+    }
+}
+
+// dy: frames [B, T, ld_y] (columns [0, M) used; M may exceed... columns >= M read as zero must exist or be OOB);
+// x: frames [B, T, ld_x] with at least Cin valid columns (the rest zero or OOB).
+int wgrad_tc_launch(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, float* dw, int B,
+                    int T, int M, int Cin, int K, int dil, cudaStream_t st) {
+    GTK_REQUIRE(dy && x && dw, "null");
+    GTK_REQUIRE(K >= 1 && (K & 1) && dil >= 1, "bad conv shape");
+    GTK_REQUIRE(ld_y % 8 == 0 && ld_x % 8 == 0 && cols_y >= M && cols_x >= Cin, "frame pitch");
+    if ((long long)B * T == 0 || M == 0 || Cin == 0) return GTK_OK;
+    WgradTcParams p;
+    memset(&p, 0, sizeof(p));
+    p.B = B; p.T = T; p.M = M; p.Cin = Cin; p.taps = K; p.dil = dil; p.dw = dw;
+    p.n_blk = ceil_div(Cin, 64);
+    GTK_REQUIRE(p.n_blk * 64 <= 256, "Cin <= 256");
+    p.steps_total = B * ceil_div(T, WG_TK);
+    const int m_tiles = ceil_div(M, 128);
+    int splits = max(1, sm_count() / max(1, m_tiles * K));
+    if (splits > p.steps_total) splits = p.steps_total;
+    p.splits = splits;
+    CUtensorMap tmY, tmX;
+    {
+        const uint64_t dims[3] = {(uint64_t)cols_y, (uint64_t)T, (uint64_t)B};
+        const uint64_t strides[2] = {(uint64_t)ld_y * 2, (uint64_t)ld_y * 2 * T};
+        const uint32_t box[3] = {64, WG_TK, 1};
+        int rc = make_tmap_bf16(&tmY, dy, 3, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    {
+        const uint64_t dims[3] = {(uint64_t)cols_x, (uint64_t)T, (uint64_t)B};
+        const uint64_t strides[2] = {(uint64_t)ld_x * 2, (uint64_t)ld_x * 2 * T};
+        const uint32_t box[3] = {64, WG_TK, 1};
+        int rc = make_tmap_bf16(&tmX, x, 3, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    const size_t smem = (size_t)WG_STAGES * (2 + p.n_blk) * WG_BOX + sizeof(WgCtl) + 1024;
+    GTK_REQUIRE(smem <= 227 * 1024, "tile does not fit in shared memory");
+    GTK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid(m_tiles, K, splits);
+    ProfScope prof(K > 1 ? "wgrad_tc_kN" : "wgrad_tc_k1", st);
+    wgrad_tc_kernel<<<grid, NTHREADS, smem, st>>>(tmY, tmX, p);
+    return check_launch("wgrad_tc");
+}
+
+// out[g][n] (+)= sum over the rows of group g of in[row][n]   (bias / conditioning gradients from bf16 frames)
+// rows_per_group = T for a per-utterance sum (groups = B), or B*T for a whole-batch sum (groups = 1).
+__global__ void colsum_frames_kernel(const __nv_bfloat16* __restrict__ in, int ld, int n_cols, long long rows_per_group,
+                                     float* __restrict__ out, size_t out_gstride, int row_splits) {
+    const int g = blockIdx.y / row_splits, rs = blockIdx.y % row_splits;
+    const int n = blockIdx.x * 64 + (threadIdx.x & 63);
+    const int rl = threadIdx.x >> 6;                                // 4 row lanes
+    const long long r_lo = rows_per_group * rs / row_splits, r_hi = rows_per_group * (rs + 1) / row_splits;
+    float acc = 0.f;
+    if (n < n_cols)
+        for (long long r = r_lo + rl; r < r_hi; r += 4) acc += __bfloat162float(in[((size_t)g * rows_per_group + r) * ld + n]);
+    __shared__ float red[256];
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    if (rl == 0 && n < n_cols) atomicAdd(out + (size_t)g * out_gstride + n, red[threadIdx.x] + red[threadIdx.x + 64] + red[threadIdx.x + 128] + red[threadIdx.x + 192]);
+}
+int colsum_frames(const __nv_bfloat16* in, int ld, int n_cols, int groups, long long rows_per_group, float* out, size_t out_gstride,
+                  cudaStream_t st) {
+    GTK_REQUIRE(in && out, "null");
+    if (groups == 0 || rows_per_group == 0 || n_cols == 0) return GTK_OK;
+    int row_splits = (int)max(1LL, min((long long)64, rows_per_group / 256));
+    dim3 grid(ceil_div(n_cols, 64), groups * row_splits);
+    colsum_frames_kernel<<<grid, 256, 0, st>>>(in, ld, n_cols, rows_per_group, out, out_gstride, row_splits);
+    return check_launch("colsum_frames");
+}
+
+}  // namespace tc
+}  // namespace gtk

@@ -152,6 +152,15 @@ int gtk_tc_pack_weight(const float* w, void* wp_bf16, int M, int Cin, int K, int
  * flags bit0: multiply the output by mask[b,t].  out_f32 (ld_f32) and out_bf16 (ld_bf16) frame-major, either may be NULL. */
 int gtk_tc_conv1d(const void* in_bf16, int ld_in, const void* wp_bf16, const float* bias, const float* mask, int B, int T,
                   int K, int dil, int N, float* out_f32, int ld_f32, void* out_bf16, int ld_bf16, int flags, void* stream);
+/* Weight gradient of gtk_tc_conv1d: dw[m][c][j] += sum_{b,t} dy[b,t,m] x[b, t+(j-K/2)dil, c]; dy frames [B,T,ld_y]
+ * (M <= ld_y valid columns), x frames [B,T,ld_x] (Cin <= ld_x valid columns, Cin <= 256); dw fp32 [M,Cin,K] (torch
+ * layout), ACCUMULATED into with atomics. */
+int gtk_tc_wgrad(const void* dy_bf16, int ld_y, const void* x_bf16, int ld_x, float* dw, int B, int T, int M, int Cin, int K,
+                 int dil, void* stream);
+/* out[g*out_gstride + n] += sum of rows [g*rows_per_group, (g+1)*rows_per_group) of frames in[.., n], n < n_cols
+ * (bias gradients: groups=1, rows=B*T; conditioning gradients: groups=B, rows=T). */
+int gtk_tc_colsum(const void* in_bf16, int ld, int n_cols, int groups, long long rows_per_group, float* out,
+                  size_t out_gstride, void* stream);
 /* One fused WaveNet layer (modules.py:151-170) on frames: dilated conv -> (dropout) -> +cond -> tanh*sigmoid ->
  * res/skip 1x1 -> residual / skip update, in one tcgen05 kernel.  h: layer input as bf16 frames [B,T,H] (operand)
  * and fp32 frames (residual master).  win_p = gtk_tc_pack_weight(in_layers[i].weight) [K][2H][H]; wrs_p =

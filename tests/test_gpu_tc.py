@@ -151,3 +151,29 @@ def test_bf16_decoder_forward_and_reverse_track_fp32(name):
     rerr = (yb - y).abs().max().item() / y.abs().max().item()
     print(f"{name}: rel|dz|={zerr:.2e} logdet={lderr:.2e} dloss={abs(l1 - l0):.2e} roundtrip={rerr:.2e}")
     assert zerr < 2e-2 and lderr < 1.0 and abs(l1 - l0) < 5e-3 and rerr < 5e-2
+
+
+@pytest.mark.parametrize("B,T,M,Cin,K,dil", [(4, 300, 384, 192, 5, 1), (2, 100, 192, 80, 1, 1), (3, 77, 160, 192, 1, 1),
+                                              (2, 215, 128, 64, 3, 2)])
+def test_tc_wgrad_and_colsum_match_torch(B, T, M, Cin, K, dil):
+    import ctypes
+    from glowtts_b200 import _lib, ops
+    gen = torch.Generator(device="cuda").manual_seed(T)
+    x = torch.randn(B, Cin, T, device="cuda", generator=gen, requires_grad=False)
+    dy = torch.randn(B, M, T, device="cuda", generator=gen)
+    w = torch.zeros(M, Cin, K, device="cuda", requires_grad=True)
+    F.conv1d(_bf(x), w, None, padding=(K - 1) * dil // 2, dilation=dil).backward(_bf(dy))
+    xf, dyf = ops.tc_frames(x), ops.tc_frames(dy)
+    dw = torch.zeros(M, Cin, K, device="cuda")
+    P = lambda t: ctypes.c_void_p(t.data_ptr())
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib.call("gtk_tc_wgrad", P(dyf), dyf.shape[2], P(xf), xf.shape[2], P(dw), B, T, M, Cin, K, dil, st)
+    torch.cuda.synchronize()
+    scale = w.grad.abs().max().item()
+    np.testing.assert_allclose(dw.cpu().numpy(), w.grad.cpu().numpy(), rtol=2e-3, atol=2e-3 * scale)
+    out = torch.zeros(B, M, device="cuda")
+    _lib.call("gtk_tc_colsum", P(dyf), dyf.shape[2], M, B, T, P(out), M, st)
+    np.testing.assert_allclose(out.cpu().numpy(), _bf(dy).sum(2).cpu().numpy(), rtol=1e-3, atol=1e-3)
+    tot = torch.zeros(M, device="cuda")
+    _lib.call("gtk_tc_colsum", P(dyf), dyf.shape[2], M, 1, B * T, P(tot), 0, st)
+    np.testing.assert_allclose(tot.cpu().numpy(), _bf(dy).sum((0, 2)).cpu().numpy(), rtol=1e-3, atol=2e-3)
