@@ -289,6 +289,61 @@ int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, 
     return check_launch("frames_from_tmajor");
 }
 
+// ---------------------------------------------------------------------------------- affine coupling backward
+// attentions.py:172-183 backward, one thread per frame: g = dz1 * mask; d(end_out) = [g | (g e^logs x1 + dlogdet mask) ds]
+// as bf16 frames (operand of the `end` data/weight gradients), dx1 = g e^logs (t-major fp32).
+__global__ void affine_bwd_frames_kernel(const float* __restrict__ x, const float* __restrict__ logs_raw,
+                                         const float* __restrict__ mask, const float* __restrict__ dz,
+                                         const float* __restrict__ dlogdet, __nv_bfloat16* __restrict__ dend, int ld,
+                                         float* __restrict__ dx, int B, int C, int T, int sigmoid_scale) {
+    const int Ch = C / 2;
+    const long long total = (long long)B * T;
+    for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < total; f += (long long)gridDim.x * blockDim.x) {
+        const int b = (int)(f / T), t = (int)(f % T);
+        const float mk = mask ? mask[f] : 1.f;
+        const float dl = dlogdet ? dlogdet[b] * mk : 0.f;
+        __nv_bfloat16* row = dend + (size_t)f * ld;
+        for (int c0 = 0; c0 < Ch; c0 += 8) {
+            float gm[8], gl[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int c = c0 + i;
+                gm[i] = gl[i] = 0.f;
+                if (c < Ch) {
+                    const size_t o1 = ((size_t)b * C + Ch + c) * T + t;
+                    const float raw = logs_raw[(size_t)f * Ch + c];
+                    float lg = raw, dscale = 1.f;
+                    if (sigmoid_scale) {
+                        const float sg = sigmoid_f(raw + 2.f);
+                        lg = __logf(1e-6f + sg);
+                        dscale = sg * (1.f - sg) / (1e-6f + sg);
+                    }
+                    const float e = __expf(lg);
+                    const float g = dz[o1] * mk;
+                    gm[i] = g;
+                    gl[i] = (g * e * x[o1] + dl) * dscale;
+                    dx[o1] = g * e;
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int c = c0 + i;
+                if (c < Ch) { row[c] = __float2bfloat16_rn(gm[i]); row[Ch + c] = __float2bfloat16_rn(gl[i]); }
+            }
+        }
+        for (int c = C; c < ld; ++c) row[c] = __float2bfloat16_rn(0.f);
+    }
+}
+int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, const float* dz, const float* dlogdet,
+                      __nv_bfloat16* dend, int ld, float* dx, int B, int C, int T, int sigmoid_scale, cudaStream_t st) {
+    GTK_REQUIRE(x && logs_raw && dz && dend && dx && C % 2 == 0 && ld >= C, "bad args");
+    const long long total = (long long)B * T;
+    if (total == 0) return GTK_OK;
+    affine_bwd_frames_kernel<<<(int)ceil_div_ll(total, 128), 128, 0, st>>>(x, logs_raw, mask, dz, dlogdet, dend, ld, dx, B, C, T,
+                                                                           sigmoid_scale);
+    return check_launch("affine_bwd_frames");
+}
+
 // ---------------------------------------------------------------------------------- launcher
 static size_t conv_tc_smem(int N, int stages) { return (size_t)stages * (A_BYTES + (size_t)N * KC * 2) + sizeof(SmemCtl) + 1024; }
 

@@ -40,6 +40,7 @@ int backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gt
     Dims D;
     GTK_TRY(make_dims(d, &D));
     GTK_REQUIRE(blocks && grads && mask && dz && dlogdet && dx && workspace, "null pointer");
+    if (d->precision == 1) return tc_backward(d, D, blocks, grads, mask, dz, dlogdet, dx, workspace, ws_bytes, st);
     if (d->precision != 0) { set_error("decoder: precision %d not available in this build", d->precision); return GTK_ERR_UNSUPPORTED; }
     Layout L;
     make_layout(D, 1, &L);

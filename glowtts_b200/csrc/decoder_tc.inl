@@ -241,3 +241,129 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     GTK_TRY(flow::unsqueeze(xa, msq, x, nullptr, D.B, D.C, D.Tq, D.n, 0, st));
     return GTK_OK;
 }
+
+// ------------------------------------------------------------------------------------------ backward
+// Weight gradient of a (possibly weight-normed) conv from frame operands: into (dg, dv) through the dweff scratch, or
+// straight into the plain weight's gradient.
+static int tc_wgrad_param(const float* g, const float* v, float* dg, float* dv, float* dweff, const bf16* dy, int ld_y, int cols_y,
+                          const bf16* x, int ld_x, int cols_x, int B, int T, int M, int Cin, int K, int dil, cudaStream_t st) {
+    if (!dv) return GTK_OK;
+    if (g) {
+        GTK_REQUIRE(dg != nullptr, "weight_g gradient pointer missing");
+        GTK_CUDA(cudaMemsetAsync(dweff, 0, sizeof(float) * (size_t)M * Cin * K, st));
+        GTK_TRY(tc::wgrad_tc_launch(dy, ld_y, cols_y, x, ld_x, cols_x, dweff, B, T, M, Cin, K, dil, st));
+        return flow::weightnorm_bwd(g, v, dweff, dg, dv, M, Cin * K, 1, st);
+    }
+    return tc::wgrad_tc_launch(dy, ld_y, cols_y, x, ld_x, cols_x, dv, B, T, M, Cin, K, dil, st);
+}
+
+static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_params* blocks, const gtk_block_grads* grads,
+                       const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace, size_t ws_bytes,
+                       cudaStream_t st) {
+    GTK_TRY(tc_supported(D));
+    Layout L32;
+    make_layout(D, 0, &L32);
+    TcLayout L;
+    make_tc_layout(D, L32, 1, &L);
+    if (ws_bytes < L.total) { set_error("decoder_backward(bf16): workspace %zu < %zu", ws_bytes, L.total); return GTK_ERR_WORKSPACE; }
+    if (D.B == 0 || D.T == 0) return GTK_OK;
+    if (D.Tq * D.n != D.T || D.Tq == 0) GTK_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)D.B * D.Cin * D.T, st));
+    if (D.Tq == 0) return GTK_OK;
+
+    unsigned char* ws = static_cast<unsigned char*>(workspace);
+    const float* msq = reinterpret_cast<const float*>(ws + L.mask_sq);
+    const float* x_len = reinterpret_cast<const float*>(ws + L.x_len);
+    const int B = D.B, T = D.Tq, H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
+    const int ldC = pad64(C), ldCh = pad64(Ch);
+    const long long rows = (long long)B * T;
+    float* dZ = reinterpret_cast<float*>(ws + L.b_dZ);
+    float* dM = reinterpret_cast<float*>(ws + L.b_dM);
+    bf16* dend = reinterpret_cast<bf16*>(ws + L.b_dend);
+    bf16* drs = reinterpret_cast<bf16*>(ws + L.b_drs);
+    bf16* dxin = reinterpret_cast<bf16*>(ws + L.b_dxin);
+    float* dhf[2] = {reinterpret_cast<float*>(ws + L.b_dhf[0]), reinterpret_cast<float*>(ws + L.b_dhf[1])};
+    bf16* dh0 = reinterpret_cast<bf16*>(ws + L.b_dh0);
+    float* dweff = reinterpret_cast<float*>(ws + L.b_dweff);
+
+    GTK_TRY(flow::squeeze(dz, msq, dZ, nullptr, B, D.Cin, D.Tq * D.n, D.n, 1, st));
+
+    for (int blk = D.NB - 1; blk >= 0; --blk) {
+        const gtk_block_params& P = blocks[blk];
+        const gtk_block_grads& G = grads[blk];
+        unsigned char* act = ws + L.act + (size_t)blk * L.A.total;
+        const bf16* pk = reinterpret_cast<const bf16*>(ws + L.pack) + (size_t)blk * L.P.total;
+        const TcPack& Q = L.P;
+        const TcAct& A = L.A;
+        const float* xin_blk = reinterpret_cast<const float*>(ws + L.X + (size_t)blk * L.x_bytes);
+        const float* winv = reinterpret_cast<const float*>(ws + L.winv) + (size_t)blk * 64;
+        const float* xmix = reinterpret_cast<const float*>(act + A.xmix);
+        const bf16* a0 = reinterpret_cast<const bf16*>(act + A.a0);
+        const bf16* skip_bf = reinterpret_cast<const bf16*>(act + A.skip_bf);
+
+        // affine coupling + end conv
+        GTK_TRY(tc::affine_bwd_frames(xmix, reinterpret_cast<const float*>(act + A.logs), msq, dZ, dlogdet, dend, ldC, dM, B, C, T,
+                                      d->sigmoid_scale, st));
+        if (G.end_w) GTK_TRY(tc::wgrad_tc_launch(dend, ldC, ldC, skip_bf, H, H, G.end_w, B, T, C, H, 1, 1, st));
+        if (G.end_b) GTK_TRY(tc::colsum_frames(dend, ldC, C, 1, rows, G.end_b, 0, st));
+        {
+            tc::ConvTcParams p;
+            memset(&p, 0, sizeof(p));
+            p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = ldC / 64; p.N = H;
+            p.mask = msq; p.mask_out = 1;
+            p.out_bf16 = drs + H; p.ld_bf16 = 2 * H;
+            GTK_TRY(tc::conv_tc_launch(dend, ldC, pk + Q.t_end, p, tc::EPI_PLAIN, st));
+        }
+        for (int i = D.L - 1; i >= 0; --i) {
+            const int RS = (i < D.L - 1) ? 2 * H : H;
+            const int dil = ipow(D.dr, i);
+            const bf16* drs_i = (i < D.L - 1) ? drs : drs + H;          // [dh_{i+1} mask | dskip]  or  dskip
+            const bf16* ts = reinterpret_cast<const bf16*>(act + A.ts[i]);
+            const bf16* acts = reinterpret_cast<const bf16*>(act + A.acts[i]);
+            const bf16* h_i = reinterpret_cast<const bf16*>(act + A.h[i]);
+            // res_skip 1x1: parameter gradients, then data gradient fused with the gate backward
+            GTK_TRY(tc_wgrad_param(P.rs_g[i], P.rs_v[i], G.rs_g[i], G.rs_v[i], dweff, drs_i, 2 * H, RS, acts, H, H, B, T, RS, H, 1, 1, st));
+            if (G.rs_b[i]) GTK_TRY(tc::colsum_frames(drs_i, 2 * H, RS, 1, rows, G.rs_b[i], 0, st));
+            {
+                tc::ConvTcParams p;
+                memset(&p, 0, sizeof(p));
+                p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = pad64(RS) / 64; p.N = H;
+                p.mask = msq;
+                p.ts = ts; p.out_bf16 = dxin; p.ld_bf16 = 2 * H;
+                GTK_TRY(tc::conv_tc_launch(drs_i, 2 * H, pk + Q.t_rs[i], p, tc::EPI_GATE_BWD, st));
+            }
+            if (P.cond && G.cond)
+                GTK_TRY(tc::colsum_frames(dxin, 2 * H, 2 * H, B, T, G.cond + (size_t)i * 2 * H, (size_t)2 * H * D.L, st));
+            // in_layer dilated conv
+            GTK_TRY(tc_wgrad_param(P.in_g[i], P.in_v[i], G.in_g[i], G.in_v[i], dweff, dxin, 2 * H, 2 * H, h_i, H, H, B, T, 2 * H, H, K,
+                                   dil, st));
+            if (G.in_b[i]) GTK_TRY(tc::colsum_frames(dxin, 2 * H, 2 * H, 1, rows, G.in_b[i], 0, st));
+            {
+                tc::ConvTcParams p;
+                memset(&p, 0, sizeof(p));
+                p.B = B; p.T = T; p.taps = K; p.dil = dil; p.n_k = 2 * H / 64; p.N = H;
+                p.mask = msq; p.mask_out = 1;
+                if (i < D.L - 1) { p.resid_f32 = dhf[(i + 1) & 1]; p.ld_resid = H; p.mask_resid = 1; }
+                p.out_f32 = dhf[i & 1]; p.ld_f32 = H;
+                if (i > 0) { p.out_bf16 = drs; p.ld_bf16 = 2 * H; }
+                else       { p.out_bf16 = dh0; p.ld_bf16 = H; }
+                GTK_TRY(tc::conv_tc_launch(dxin, 2 * H, pk + Q.t_in[i], p, tc::EPI_PLAIN, st));
+            }
+        }
+        // start conv: h0 = (W x0 + b) * mask   (dh0 is already masked)
+        GTK_TRY(tc_wgrad_param(P.start_g, P.start_v, G.start_g, G.start_v, dweff, dh0, H, H, a0, ldCh, ldCh, B, T, H, Ch, 1, 1, st));
+        if (G.start_b) GTK_TRY(tc::colsum_frames(dh0, H, H, 1, rows, G.start_b, 0, st));
+        {
+            tc::ConvTcParams p;
+            memset(&p, 0, sizeof(p));
+            p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = H / 64; p.N = Ch;
+            p.resid_tm = dZ; p.out_tm = dM; p.tm_C = C; p.tm_c0 = 0;
+            GTK_TRY(tc::conv_tc_launch(dh0, H, pk + Q.t_start, p, tc::EPI_PLAIN, st));
+        }
+        // ActNorm + InvConvNear (fp32)
+        GTK_TRY(flow::mix_bwd(xin_blk, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, dM, dZ, G.an_logs, G.an_bias, G.ic_weight, B,
+                              C, T, st));
+        GTK_TRY(flow::logdet_const_bwd(dlogdet, x_len, B, G.an_logs, C, winv, D.NS, (float)(C / D.NS), G.ic_weight, st));
+    }
+    GTK_TRY(flow::unsqueeze(dZ, msq, dx, nullptr, B, C, T, D.n, D.T, st));
+    return GTK_OK;
+}

@@ -77,6 +77,8 @@ int wgrad_tc_launch(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bf
                     int T, int M, int Cin, int K, int dil, cudaStream_t st);
 int colsum_frames(const __nv_bfloat16* in, int ld, int n_cols, int groups, long long rows_per_group, float* out, size_t out_gstride,
                   cudaStream_t st);
+int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, const float* dz, const float* dlogdet,
+                      __nv_bfloat16* dend, int ld, float* dx, int B, int C, int T, int sigmoid_scale, cudaStream_t st);
 int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, ConvTcParams p, int epi, cudaStream_t st);
 int pack_weight_bf16(const float* w, __nv_bfloat16* out, int M, int Cin, int K, int transpose, int rows, int cols, cudaStream_t st);
 int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, int c0, int nc, int ld, cudaStream_t st);

@@ -177,3 +177,38 @@ def test_tc_wgrad_and_colsum_match_torch(B, T, M, Cin, K, dil):
     tot = torch.zeros(M, device="cuda")
     _lib.call("gtk_tc_colsum", P(dyf), dyf.shape[2], M, 1, B * T, P(tot), 0, st)
     np.testing.assert_allclose(tot.cpu().numpy(), _bf(dy).sum((0, 2)).cpu().numpy(), rtol=1e-3, atol=2e-3)
+
+
+@pytest.mark.parametrize("name", list(TC_CFGS))
+def test_bf16_decoder_backward_tracks_fp32(name):
+    """Gradients of the bf16 path vs the fp32 path (same loss): per-tensor relative L2 error <= 3e-2
+    (bf16 operand rounding through up to 48 layers), dy relative L2 error <= 2e-2."""
+    import helpers
+    from glowtts_b200 import commons
+    cfg = TC_CFGS[name]
+    f32, b16 = _decoders(cfg, 78, end_std=0.01 if name == "base" else 0.05)
+    B, T = (4, 300) if name != "base" else (3, 214)
+    y, mask, _, g = helpers.flow_inputs(cfg, B, T, 6, cfg["gin_channels"] > 0)
+    mask = mask.cuda()
+    g = g.cuda() if g is not None else None
+    grads = []
+    for dec in (f32, b16):
+        yy = y.cuda().requires_grad_(True)
+        gg = g.clone().requires_grad_(True) if g is not None else None
+        z, ld = dec(yy, mask, g=gg)
+        loss = commons.mle_loss(z, None, None, ld, mask)
+        loss.backward()
+        d = {k: p.grad.clone() for k, p in dec.named_parameters()}
+        d["__dy"] = yy.grad.clone()
+        if gg is not None:
+            d["__dg"] = gg.grad.clone()
+        grads.append(d)
+    worst = ("", 0.0)
+    for k, a in grads[0].items():
+        b = grads[1][k]
+        assert torch.isfinite(b).all(), k
+        err = ((a - b).norm() / (a.norm() + 1e-12)).item()
+        if a.norm().item() > 1e-7 and err > worst[1]:
+            worst = (k, err)
+    print(f"{name}: worst relative L2 grad error {worst[1]:.3e} at {worst[0]}; dy {((grads[0]['__dy'] - grads[1]['__dy']).norm() / grads[0]['__dy'].norm()).item():.3e}")
+    assert worst[1] < 3e-2
