@@ -289,6 +289,47 @@ int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, 
     return check_launch("frames_from_tmajor");
 }
 
+// ---------------------------------------------------------------------------------- fold + pack, one launch per block
+// Every conv weight of one coupling block: weight-norm fold (w = g v / ||v||, modules.py:124,131,141) and bf16 packing
+// into the forward ([j][m][c]) and data-gradient ([j][c][m], taps flipped) operand layouts in ONE kernel.
+// One CTA per (weight, output row m).
+__global__ void __launch_bounds__(128) fold_pack_kernel(const FoldPackJobs jobs) {
+    __shared__ float scratch[33];
+    int row = blockIdx.x, w = 0;
+    while (w < jobs.n && row >= jobs.job[w].M) { row -= jobs.job[w].M; ++w; }
+    if (w >= jobs.n) return;
+    const FoldPackJob J = jobs.job[w];
+    const int m = row, R = J.Cin * J.K;
+    const float* vrow = J.v + (size_t)m * R;
+    float sc = 1.f;
+    if (J.g) {
+        float ss = 0.f;
+        for (int e = threadIdx.x; e < R; e += 128) { const float t = vrow[e]; ss += t * t; }
+        ss = block_sum<128>(ss, scratch);
+        sc = J.g[m] / sqrtf(ss);
+    }
+    // forward operand: out[j][m][c], c < cols_f (zero padded)
+    for (int e = threadIdx.x; e < J.K * J.cols_f; e += 128) {
+        const int j = e / J.cols_f, c = e % J.cols_f;
+        const float val = (c < J.Cin) ? vrow[c * J.K + j] * sc : 0.f;
+        J.fwd[((size_t)j * J.rows_f + m) * J.cols_f + c] = __float2bfloat16_rn(val);
+    }
+    // data-gradient operand: out[j][c][m] = W[m][c][K-1-j], c < rows_t
+    if (J.tr) {
+        for (int e = threadIdx.x; e < J.K * J.Cin; e += 128) {
+            const int j = e / J.Cin, c = e % J.Cin;
+            J.tr[((size_t)j * J.rows_t + c) * J.cols_t + m] = __float2bfloat16_rn(vrow[c * J.K + (J.K - 1 - j)] * sc);
+        }
+    }
+}
+int fold_pack(const FoldPackJobs& jobs, cudaStream_t st) {
+    int rows = 0;
+    for (int i = 0; i < jobs.n; ++i) rows += jobs.job[i].M;
+    if (rows == 0) return GTK_OK;
+    fold_pack_kernel<<<rows, 128, 0, st>>>(jobs);
+    return check_launch("fold_pack");
+}
+
 // ---------------------------------------------------------------------------------- affine coupling backward
 // attentions.py:172-183 backward, one thread per frame: g = dz1 * mask; d(end_out) = [g | (g e^logs x1 + dlogdet mask) ds]
 // as bf16 frames (operand of the `end` data/weight gradients), dx1 = g e^logs (t-major fp32).
@@ -297,47 +338,53 @@ __global__ void affine_bwd_frames_kernel(const float* __restrict__ x, const floa
                                          const float* __restrict__ dlogdet, __nv_bfloat16* __restrict__ dend, int ld,
                                          float* __restrict__ dx, int B, int C, int T, int sigmoid_scale) {
     const int Ch = C / 2;
-    const long long total = (long long)B * T;
-    for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < total; f += (long long)gridDim.x * blockDim.x) {
+    const int n_chunk = (Ch + 7) / 8, n_pad = (ld - C + 7) / 8;      // channel chunks + zero-padding chunks
+    const long long frames = (long long)B * T, total = frames * (n_chunk + n_pad);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long f = i % frames;
+        const int chunk = (int)(i / frames);
         const int b = (int)(f / T), t = (int)(f % T);
+        __nv_bfloat16* row = dend + (size_t)f * ld;
+        if (chunk >= n_chunk) {
+            const int c0 = C + (chunk - n_chunk) * 8;
+            for (int c = c0; c < min(c0 + 8, ld); ++c) row[c] = __float2bfloat16_rn(0.f);
+            continue;
+        }
         const float mk = mask ? mask[f] : 1.f;
         const float dl = dlogdet ? dlogdet[b] * mk : 0.f;
-        __nv_bfloat16* row = dend + (size_t)f * ld;
-        for (int c0 = 0; c0 < Ch; c0 += 8) {
-            float gm[8], gl[8];
+        const int c0 = chunk * 8;
+        float gm[8], gl[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int c = c0 + i;
-                gm[i] = gl[i] = 0.f;
-                if (c < Ch) {
-                    const size_t o1 = ((size_t)b * C + Ch + c) * T + t;
-                    const float raw = logs_raw[(size_t)f * Ch + c];
-                    float lg = raw, dscale = 1.f;
-                    if (sigmoid_scale) {
-                        const float sg = sigmoid_f(raw + 2.f);
-                        lg = __logf(1e-6f + sg);
-                        dscale = sg * (1.f - sg) / (1e-6f + sg);
-                    }
-                    const float e = __expf(lg);
-                    const float g = dz[o1] * mk;
-                    gm[i] = g;
-                    gl[i] = (g * e * x[o1] + dl) * dscale;
-                    dx[o1] = g * e;
+        for (int k = 0; k < 8; ++k) {
+            const int c = c0 + k;
+            gm[k] = gl[k] = 0.f;
+            if (c < Ch) {
+                const size_t o1 = ((size_t)b * C + Ch + c) * T + t;
+                const float raw = logs_raw[(size_t)f * Ch + c];
+                float lg = raw, dscale = 1.f;
+                if (sigmoid_scale) {
+                    const float sg = sigmoid_f(raw + 2.f);
+                    lg = __logf(1e-6f + sg);
+                    dscale = sg * (1.f - sg) / (1e-6f + sg);
                 }
-            }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int c = c0 + i;
-                if (c < Ch) { row[c] = __float2bfloat16_rn(gm[i]); row[Ch + c] = __float2bfloat16_rn(gl[i]); }
+                const float e = __expf(lg);
+                const float g = dz[o1] * mk;
+                gm[k] = g;
+                gl[k] = (g * e * x[o1] + dl) * dscale;
+                dx[o1] = g * e;
             }
         }
-        for (int c = C; c < ld; ++c) row[c] = __float2bfloat16_rn(0.f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int c = c0 + k;
+            if (c < Ch) { row[c] = __float2bfloat16_rn(gm[k]); row[Ch + c] = __float2bfloat16_rn(gl[k]); }
+        }
     }
 }
 int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, const float* dz, const float* dlogdet,
                       __nv_bfloat16* dend, int ld, float* dx, int B, int C, int T, int sigmoid_scale, cudaStream_t st) {
     GTK_REQUIRE(x && logs_raw && dz && dend && dx && C % 2 == 0 && ld >= C, "bad args");
-    const long long total = (long long)B * T;
+    const long long total = (long long)B * T * ((C / 2 + 7) / 8 + (ld - C + 7) / 8);
     if (total == 0) return GTK_OK;
     affine_bwd_frames_kernel<<<(int)ceil_div_ll(total, 128), 128, 0, st>>>(x, logs_raw, mask, dz, dlogdet, dend, ld, dx, B, C, T,
                                                                            sigmoid_scale);

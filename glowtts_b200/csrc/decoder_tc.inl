@@ -24,7 +24,7 @@ struct TcLayout {          // byte offsets in the workspace
     TcPack P;
     TcAct A;
     // backward temporaries
-    size_t b_dZ, b_dM, b_dend, b_drs, b_dxin, b_dgate, b_dhf[2], b_dh0, b_dweff;
+    size_t b_dZ, b_dM, b_dend, b_drs, b_dxin, b_dgate, b_dhf[2], b_dh0, b_wpart;
 };
 
 static int tc_supported(const Dims& D) {
@@ -91,35 +91,33 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
         L->b_dhf[0] = take((size_t)H * nq * 4);
         L->b_dhf[1] = take((size_t)H * nq * 4);
         L->b_dh0 = take((size_t)H * nq * 2);
-        size_t wmax = (size_t)2 * H * H * K;
-        if ((size_t)C * H > wmax) wmax = (size_t)C * H;
-        L->b_dweff = take(wmax * 4);
+        L->b_wpart = take(tc::wgrad_tc_workspace_bytes());
     }
     L->total = off;
 }
 
-// fp32 effective weights (we) -> bf16 operand packs of one block
-static int tc_pack_block(const Dims& D, const Layout& L32, const TcLayout& L, const gtk_block_params& P, const float* we,
-                         bf16* pk, int with_transposed, cudaStream_t st) {
+// weight-norm fold + bf16 operand packs of one block, one launch.  The padding columns/rows of the packs are zeroed
+// once per forward call (tc_forward / tc_reverse memset the pack region).
+static int tc_pack_block(const Dims& D, const TcLayout& L, const gtk_block_params& P, bf16* pk, int with_transposed,
+                         cudaStream_t st) {
     const int H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
     const TcPack& Q = L.P;
-    GTK_TRY(tc::pack_weight_bf16(w_start(L32, P, we), pk + Q.start, H, Ch, 1, 0, H, pad64(Ch), st));
+    tc::FoldPackJobs J;
+    memset(&J, 0, sizeof(J));
+    auto add = [&](const float* g, const float* v, size_t fwd, size_t tr, int M, int Cin, int Kk, int cols_f, int cols_t) {
+        tc::FoldPackJob& j = J.job[J.n++];
+        j.g = g; j.v = v; j.fwd = pk + fwd; j.tr = with_transposed ? pk + tr : nullptr;
+        j.M = M; j.Cin = Cin; j.K = Kk; j.rows_f = M; j.cols_f = cols_f; j.rows_t = Cin; j.cols_t = cols_t;
+    };
+    if (2 + 2 * D.L > 16) { set_error("bf16 path: n_layers <= 7"); return GTK_ERR_UNSUPPORTED; }
+    add(P.start_g, P.start_v, Q.start, Q.t_start, H, Ch, 1, pad64(Ch), H);
     for (int i = 0; i < D.L; ++i) {
         const int RS = (i < D.L - 1) ? 2 * H : H;
-        GTK_TRY(tc::pack_weight_bf16(w_in(L32, P, we, i), pk + Q.in[i], 2 * H, H, K, 0, 2 * H, H, st));
-        GTK_TRY(tc::pack_weight_bf16(w_rs(L32, P, we, i), pk + Q.rs[i], RS, H, 1, 0, RS, H, st));
+        add(P.in_g[i], P.in_v[i], Q.in[i], Q.t_in[i], 2 * H, H, K, H, 2 * H);
+        add(P.rs_g[i], P.rs_v[i], Q.rs[i], Q.t_rs[i], RS, H, 1, H, pad64(RS));
     }
-    GTK_TRY(tc::pack_weight_bf16(P.end_w, pk + Q.end, C, H, 1, 0, C, H, st));
-    if (with_transposed) {
-        GTK_TRY(tc::pack_weight_bf16(w_start(L32, P, we), pk + Q.t_start, H, Ch, 1, 1, Ch, H, st));
-        for (int i = 0; i < D.L; ++i) {
-            const int RS = (i < D.L - 1) ? 2 * H : H;
-            GTK_TRY(tc::pack_weight_bf16(w_in(L32, P, we, i), pk + Q.t_in[i], 2 * H, H, K, 1, H, 2 * H, st));
-            GTK_TRY(tc::pack_weight_bf16(w_rs(L32, P, we, i), pk + Q.t_rs[i], RS, H, 1, 1, H, pad64(RS), st));
-        }
-        GTK_TRY(tc::pack_weight_bf16(P.end_w, pk + Q.t_end, C, H, 1, 1, H, pad64(C), st));
-    }
-    return GTK_OK;
+    add(nullptr, P.end_w, Q.end, Q.t_end, C, H, 1, H, pad64(C));
+    return tc::fold_pack(J, st);
 }
 
 // start -> WN -> end(+affine) of one block.  xc = mixed block input (t-major fp32), zout = block output.
@@ -187,6 +185,7 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     float* msq = reinterpret_cast<float*>(ws + L.mask_sq);
     float* x_len = reinterpret_cast<float*>(ws + L.x_len);
     float* we = reinterpret_cast<float*>(ws + L.we);
+    GTK_CUDA(cudaMemsetAsync(ws + L.pack, 0, L.P.total * 2 * L.n_pack, st));   // zero padding of the packed weights
     GTK_TRY(flow::squeeze(x, mask, reinterpret_cast<float*>(ws + L.X), msq, D.B, D.Cin, D.T, D.n, 0, st));
     GTK_TRY(flow::mask_len(msq, x_len, D.B, D.Tq, st));
     for (int blk = 0; blk < D.NB; ++blk) {
@@ -199,8 +198,7 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
         float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
         float* icld = reinterpret_cast<float*>(ws + L.icld) + blk;
         float* xmix = reinterpret_cast<float*>(act + L.A.xmix);
-        GTK_TRY(fold_weights(D, L32, P, we, st));
-        GTK_TRY(tc_pack_block(D, L32, L, P, we, pk, train, st));
+        GTK_TRY(tc_pack_block(D, L, P, pk, train, st));
         GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, icld, st));
         GTK_TRY(flow::mix(xin, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, xmix, D.B, D.C, D.Tq, 0, st));
         GTK_TRY(flow::logdet_const(P.an_logs, D.C, icld, (float)(D.C / D.NS), x_len, logdet, D.B, 1, st));
@@ -227,13 +225,13 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     float* xb = reinterpret_cast<float*>(ws + L.X + L.x_bytes);
     unsigned char* act = ws + L.act;
     bf16* pk = reinterpret_cast<bf16*>(ws + L.pack);
+    GTK_CUDA(cudaMemsetAsync(ws + L.pack, 0, L.P.total * 2, st));
     GTK_TRY(flow::squeeze(z, mask, xa, msq, D.B, D.Cin, D.T, D.n, 0, st));
     for (int blk = D.NB - 1; blk >= 0; --blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
         float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
-        GTK_TRY(fold_weights(D, L32, P, we, st));
-        GTK_TRY(tc_pack_block(D, L32, L, P, we, pk, 0, st));
+        GTK_TRY(tc_pack_block(D, L, P, pk, 0, st));
         GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, nullptr, st));
         GTK_TRY(tc_coupling(d, D, L, P, pk, xa, xb, nullptr, msq, act, ws, 1, 0, 0, st));
         GTK_TRY(flow::mix(xb, msq, P.an_logs, P.an_bias, winv, D.NS, xa, D.B, D.C, D.Tq, 1, st));
@@ -243,18 +241,12 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
 }
 
 // ------------------------------------------------------------------------------------------ backward
-// Weight gradient of a (possibly weight-normed) conv from frame operands: into (dg, dv) through the dweff scratch, or
-// straight into the plain weight's gradient.
-static int tc_wgrad_param(const float* g, const float* v, float* dg, float* dv, float* dweff, const bf16* dy, int ld_y, int cols_y,
+// Weight gradient of a (possibly weight-normed) conv from frame operands, accumulated into (dg, dv) or dv alone.
+static int tc_wgrad_param(const float* g, const float* v, float* dg, float* dv, float* part, const bf16* dy, int ld_y, int cols_y,
                           const bf16* x, int ld_x, int cols_x, int B, int T, int M, int Cin, int K, int dil, cudaStream_t st) {
     if (!dv) return GTK_OK;
-    if (g) {
-        GTK_REQUIRE(dg != nullptr, "weight_g gradient pointer missing");
-        GTK_CUDA(cudaMemsetAsync(dweff, 0, sizeof(float) * (size_t)M * Cin * K, st));
-        GTK_TRY(tc::wgrad_tc_launch(dy, ld_y, cols_y, x, ld_x, cols_x, dweff, B, T, M, Cin, K, dil, st));
-        return flow::weightnorm_bwd(g, v, dweff, dg, dv, M, Cin * K, 1, st);
-    }
-    return tc::wgrad_tc_launch(dy, ld_y, cols_y, x, ld_x, cols_x, dv, B, T, M, Cin, K, dil, st);
+    if (g) GTK_REQUIRE(dg != nullptr, "weight_g gradient pointer missing");
+    return tc::wgrad_tc_param(dy, ld_y, cols_y, x, ld_x, cols_x, g, v, dg, dv, part, B, T, M, Cin, K, dil, st);
 }
 
 static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_params* blocks, const gtk_block_grads* grads,
@@ -283,7 +275,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     bf16* dxin = reinterpret_cast<bf16*>(ws + L.b_dxin);
     float* dhf[2] = {reinterpret_cast<float*>(ws + L.b_dhf[0]), reinterpret_cast<float*>(ws + L.b_dhf[1])};
     bf16* dh0 = reinterpret_cast<bf16*>(ws + L.b_dh0);
-    float* dweff = reinterpret_cast<float*>(ws + L.b_dweff);
+    float* dweff = reinterpret_cast<float*>(ws + L.b_wpart);   // split-K partial tiles of the weight gradients
 
     GTK_TRY(flow::squeeze(dz, msq, dZ, nullptr, B, D.Cin, D.Tq * D.n, D.n, 1, st));
 
@@ -303,7 +295,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         // affine coupling + end conv
         GTK_TRY(tc::affine_bwd_frames(xmix, reinterpret_cast<const float*>(act + A.logs), msq, dZ, dlogdet, dend, ldC, dM, B, C, T,
                                       d->sigmoid_scale, st));
-        if (G.end_w) GTK_TRY(tc::wgrad_tc_launch(dend, ldC, ldC, skip_bf, H, H, G.end_w, B, T, C, H, 1, 1, st));
+        GTK_TRY(tc_wgrad_param(nullptr, nullptr, nullptr, G.end_w, dweff, dend, ldC, ldC, skip_bf, H, H, B, T, C, H, 1, 1, st));
         if (G.end_b) GTK_TRY(tc::colsum_frames(dend, ldC, C, 1, rows, G.end_b, 0, st));
         {
             tc::ConvTcParams p;

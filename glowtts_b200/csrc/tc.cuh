@@ -75,10 +75,24 @@ int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, con
 
 int wgrad_tc_launch(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, float* dw, int B,
                     int T, int M, int Cin, int K, int dil, cudaStream_t st);
+size_t wgrad_tc_workspace_bytes();
+int wgrad_tc_param(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, const float* g,
+                   const float* v, float* dg, float* dv, float* part_ws, int B, int T, int M, int Cin, int K, int dil,
+                   cudaStream_t st);
 int colsum_frames(const __nv_bfloat16* in, int ld, int n_cols, int groups, long long rows_per_group, float* out, size_t out_gstride,
                   cudaStream_t st);
 int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, const float* dz, const float* dlogdet,
                       __nv_bfloat16* dend, int ld, float* dx, int B, int C, int T, int sigmoid_scale, cudaStream_t st);
+// Fold (weight norm) + bf16 pack of up to 16 conv weights in one launch (conv_tc.cu).
+struct FoldPackJob {
+    const float* g;            // weight_g [M] or null (plain weight)
+    const float* v;            // weight_v / weight [M][Cin][K]
+    __nv_bfloat16* fwd;        // [K][rows_f][cols_f]
+    __nv_bfloat16* tr;         // [K][rows_t][cols_t] or null
+    int M, Cin, K, rows_f, cols_f, rows_t, cols_t;
+};
+struct FoldPackJobs { FoldPackJob job[16]; int n; };
+int fold_pack(const FoldPackJobs& jobs, cudaStream_t st);
 int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, ConvTcParams p, int epi, cudaStream_t st);
 int pack_weight_bf16(const float* w, __nv_bfloat16* out, int M, int Cin, int K, int transpose, int rows, int cols, cudaStream_t st);
 int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, int c0, int nc, int ld, cudaStream_t st);

@@ -29,7 +29,8 @@ struct WgradTcParams {
     int B, T, M, Cin, taps, dil;
     int n_blk;                 // N = 64 * n_blk columns of X are reduced (>= Cin, zero padded)
     int steps_total, splits;
-    float* dw;                 // [M][Cin][taps] fp32, accumulated
+    float* dw;                 // [M][Cin][taps] fp32, accumulated with atomics (part == null)
+    float* part;               // or: partial tiles [split][tap][m_tiles*128][N] fp32, plain stores (reduced by wgrad_reduce)
 };
 
 __global__ void __launch_bounds__(NTHREADS, 1)
@@ -101,9 +102,16 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         const int q = warp & 3;
         const int m = m0 + q * 32 + lane;
         const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+        float* prow = p.part ? p.part + (((size_t)split * p.taps + j) * (gridDim.x * 128) + (m - 0)) * N : nullptr;
         for (int c0 = 0; c0 < N; c0 += 16) {
             float v[16];
             tmem_ld16(trow + c0, v);
+            if (prow) {
+                float4* o4 = reinterpret_cast<float4*>(prow + c0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                continue;
+            }
             if (m >= p.M) continue;
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
@@ -122,15 +130,81 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 
 // dy: frames [B, T, ld_y] (columns [0, M) used; M may exceed... columns >= M read as zero must exist or be OOB);
 // x: frames [B, T, ld_x] with at least Cin valid columns (the rest zero or OOB).
+// Sum the split-K partial tiles of one weight and finish the parameter gradient in the same pass: one block per output
+// row m (R = Cin*taps elements).  Plain weight: dv[m][c][j] += sum.  Weight-normed (g != null; torch.nn.utils.weight_norm,
+// modules.py:124,131,141):  dg[m] += <dW_m, v_m>/||v_m||,  dv_m += g_m/||v_m|| (dW_m - v_m <dW_m, v_m>/||v_m||^2).
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ part, int splits, int m_pad, int N, int M, int Cin,
+                                                           int taps, const float* __restrict__ g, const float* __restrict__ v,
+                                                           float* __restrict__ dg, float* __restrict__ dv) {
+    extern __shared__ float row[];                 // [Cin * taps] reduced dW row, torch order (c, j)
+    __shared__ float scratch[33];
+    const int m = blockIdx.x, R = Cin * taps;
+    float ss = 0.f, dd = 0.f;
+    for (int e = threadIdx.x; e < taps * Cin; e += 256) {
+        const int j = e / Cin, c = e % Cin;        // c fastest: coalesced reads of the partial tiles
+        float acc = 0.f;
+        for (int s = 0; s < splits; ++s) acc += part[(((size_t)s * taps + j) * m_pad + m) * N + c];
+        row[c * taps + j] = acc;
+        if (g) {
+            const float t = v[(size_t)m * R + c * taps + j];
+            ss += t * t;
+            dd += t * acc;
+        }
+    }
+    __syncthreads();
+    if (!g) {
+        for (int e = threadIdx.x; e < R; e += 256) dv[(size_t)m * R + e] += row[e];
+        return;
+    }
+    ss = block_sum<256>(ss, scratch);
+    dd = block_sum<256>(dd, scratch);
+    const float nrm = sqrtf(ss);
+    const float sc = g[m] / nrm, proj = dd / ss;
+    for (int e = threadIdx.x; e < R; e += 256) dv[(size_t)m * R + e] += sc * (row[e] - v[(size_t)m * R + e] * proj);
+    if (threadIdx.x == 0) dg[m] += dd / nrm;
+}
+
+size_t wgrad_tc_workspace_bytes() { return (size_t)(sm_count() + 16) * 128 * 256 * sizeof(float); }
+
+// Weight gradient straight into the parameter gradients (dg, dv) -- or dv alone for a plain weight (g == null) --
+// through split-K partial tiles in `part_ws` (wgrad_tc_workspace_bytes()).
+int wgrad_tc_param(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, const float* g,
+                   const float* v, float* dg, float* dv, float* part_ws, int B, int T, int M, int Cin, int K, int dil,
+                   cudaStream_t st);
+
+static int wgrad_tc_run(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, float* dw,
+                        float* part, int* splits_out, int B, int T, int M, int Cin, int K, int dil, cudaStream_t st);
+
 int wgrad_tc_launch(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, float* dw, int B,
                     int T, int M, int Cin, int K, int dil, cudaStream_t st) {
-    GTK_REQUIRE(dy && x && dw, "null");
+    GTK_REQUIRE(dw, "null");
+    return wgrad_tc_run(dy, ld_y, cols_y, x, ld_x, cols_x, dw, nullptr, nullptr, B, T, M, Cin, K, dil, st);
+}
+
+int wgrad_tc_param(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, const float* g,
+                   const float* v, float* dg, float* dv, float* part_ws, int B, int T, int M, int Cin, int K, int dil,
+                   cudaStream_t st) {
+    GTK_REQUIRE(dv && part_ws && (!g || (v && dg)), "null");
+    if ((long long)B * T == 0 || M == 0 || Cin == 0) return GTK_OK;
+    int splits = 0;
+    int rc = wgrad_tc_run(dy, ld_y, cols_y, x, ld_x, cols_x, nullptr, part_ws, &splits, B, T, M, Cin, K, dil, st);
+    if (rc) return rc;
+    const int m_pad = ceil_div(M, 128) * 128, N = ceil_div(Cin, 64) * 64;
+    const size_t smem = (size_t)Cin * K * sizeof(float);
+    GTK_REQUIRE(smem <= 48 * 1024, "weight row too long for the reduce kernel");
+    wgrad_reduce_kernel<<<M, 256, smem, st>>>(part_ws, splits, m_pad, N, M, Cin, K, g, v, dg, dv);
+    return check_launch("wgrad_reduce");
+}
+
+static int wgrad_tc_run(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, float* dw,
+                        float* part, int* splits_out, int B, int T, int M, int Cin, int K, int dil, cudaStream_t st) {
+    GTK_REQUIRE(dy && x && (dw || part), "null");
     GTK_REQUIRE(K >= 1 && (K & 1) && dil >= 1, "bad conv shape");
     GTK_REQUIRE(ld_y % 8 == 0 && ld_x % 8 == 0 && cols_y >= M && cols_x >= Cin, "frame pitch");
     if ((long long)B * T == 0 || M == 0 || Cin == 0) return GTK_OK;
     WgradTcParams p;
     memset(&p, 0, sizeof(p));
-    p.B = B; p.T = T; p.M = M; p.Cin = Cin; p.taps = K; p.dil = dil; p.dw = dw;
+    p.B = B; p.T = T; p.M = M; p.Cin = Cin; p.taps = K; p.dil = dil; p.dw = dw; p.part = part;
     p.n_blk = ceil_div(Cin, 64);
     GTK_REQUIRE(p.n_blk * 64 <= 256, "Cin <= 256");
     p.steps_total = B * ceil_div(T, WG_TK);
@@ -138,6 +212,7 @@ int wgrad_tc_launch(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bf
     int splits = max(1, sm_count() / max(1, m_tiles * K));
     if (splits > p.steps_total) splits = p.steps_total;
     p.splits = splits;
+    if (splits_out) *splits_out = splits;
     CUtensorMap tmY, tmX;
     {
         const uint64_t dims[3] = {(uint64_t)cols_y, (uint64_t)T, (uint64_t)B};

@@ -76,8 +76,60 @@ class FlowSpecDecoder(nn.Module):
             with torch.no_grad():
                 return ops.decoder_reverse(x, mask2, [p.detach() for p in params], cond, cfg), None
         train = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params))
-        z, logdet, _ = ops.decoder_forward(x, mask2, params, cond, cfg, train)
+        if train and not folded and all(p.requires_grad for p in params):
+            flat, offsets = self._ensure_flat(params)
+            z, logdet, _ = ops.decoder_forward_flat(x, mask2, flat, offsets, cond, cfg, True)
+        else:
+            z, logdet, _ = ops.decoder_forward(x, mask2, params, cond, cfg, train)
         return z, logdet
+
+    # ---------------------------------------------------------------- flat parameter storage (training)
+    def _ensure_flat(self, params):
+        """Keep every decoder parameter as a view into ONE fp32 buffer (like DDP/FSDP flat buffers): the fused call
+        takes the buffer, autograd returns ONE gradient tensor, and `p.grad` of the named parameters become views of
+        it (no per-parameter copies).  Rebuilt lazily if the module was moved (.to()/.cuda()) or reloaded."""
+        offs, sizes, total = ops.grad_layout(params)
+        flat = getattr(self, "_flat", None)
+        ok = flat is not None and flat.numel() == total and flat.device == params[0].device
+        if ok:
+            base = flat.data_ptr()
+            ok = all(p.data_ptr() == base + 4 * o for p, o in zip(params, offs))
+        if not ok:
+            with torch.no_grad():
+                buf = torch.zeros(total, dtype=torch.float32, device=params[0].device)
+                owners = self._param_owners()
+                for p, o, n in zip(params, offs, sizes):
+                    buf[o:o + n].copy_(p.detach().reshape(-1))
+                    owners[p.data_ptr()].data = buf[o:o + n].view(owners[p.data_ptr()].shape)
+            flat = buf.requires_grad_(True)
+            flat.register_post_accumulate_grad_hook(self._scatter_flat_grad)
+            self._flat, self._flat_offs, self._flat_sizes = flat, offs, sizes
+            self._flat_params = [owners_p for owners_p in self._ordered_owners()]
+        return self._flat, self._flat_offs
+
+    def _ordered_owners(self):
+        """nn.Parameters in decoder_forward order (ActNorm logs/bias are [1,C,1] parameters passed as [C] views)."""
+        out = []
+        for b in range(self.n_blocks):
+            an, ic, cb = self.flows[3 * b], self.flows[3 * b + 1], self.flows[3 * b + 2]
+            out += [an.logs, an.bias, ic.weight, cb.start.weight_g, cb.start.weight_v, cb.start.bias]
+            for grp in (cb.wn.in_layers, cb.wn.res_skip_layers):
+                out += [l.weight_g for l in grp] + [l.weight_v for l in grp] + [l.bias for l in grp]
+            out += [cb.end.weight, cb.end.bias]
+        return out
+
+    def _param_owners(self):
+        return {p.data_ptr(): p for p in self._ordered_owners()}
+
+    def _scatter_flat_grad(self, flat):
+        g = flat.grad
+        flat.grad = None
+        for p, o, n in zip(self._flat_params, self._flat_offs, self._flat_sizes):
+            v = g[o:o + n].view(p.shape)
+            if p.grad is None:
+                p.grad = v
+            else:
+                p.grad.add_(v)
 
     def _forward_unfused(self, x, x_mask, g=None, reverse=False):
         """Flow by flow through the module-level ops (used for the DDI pass, where ActNorm statistics must be

@@ -532,7 +532,7 @@ def _blocks(cfg: Sequence[int], tensors: Sequence[Optional[Tensor]], cond: Optio
     if len(tensors) != per * NB:
         raise RuntimeError(f"glowtts_b200: expected {per * NB} decoder tensors, got {len(tensors)}")
     arr = (BlockParams * NB)()
-    ptr = lambda t: None if t is None else t.data_ptr()
+    ptr = lambda t: None if t is None else (t if isinstance(t, int) else t.data_ptr())
     for b in range(NB):
         it = iter(tensors[b * per:(b + 1) * per])
         P = arr[b]
@@ -659,6 +659,95 @@ def _(dz, dlogdet, mask, params, cond, ws, cfg, T):
 
 _GRAD_SYNC = {"group": None}
 
+# ---- flat-parameter variant: all decoder parameters live in ONE fp32 buffer (offsets in elements, 16-byte aligned),
+# so autograd moves ONE gradient tensor instead of ~400 and the optimizer / NCCL see a single bucket.
+def _flat_ptrs(flat: Tensor, offsets: Sequence[int]) -> List[int]:
+    base = flat.data_ptr()
+    return [base + 4 * int(o) for o in offsets]
+
+
+@torch.library.custom_op(f"{NS}::decoder_forward_flat", mutates_args=(), device_types="cuda")
+def decoder_forward_flat(x: Tensor, mask: Tensor, flat: Tensor, offsets: List[int], cond: Optional[Tensor], cfg: List[int],
+                         train: bool) -> Tuple[Tensor, Tensor, Tensor]:
+    """decoder_forward with the parameters given as one flat buffer + element offsets (same order as `params`)."""
+    x = _chk(x, "x")
+    B, Cin, T = x.shape
+    mask = _chk(_fit_mask(mask, T), "mask")
+    flat = _chk(flat, "flat")
+    cond = _opt(cond, "cond")
+    d = _desc(cfg, B, T)
+    lib = _lib.load()
+    ws_bytes = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), int(train))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+    Tz = (T // d.n_sqz) * d.n_sqz
+    z = torch.empty(B, Cin, Tz, dtype=x.dtype, device=x.device)
+    logdet = torch.empty(B, dtype=x.dtype, device=x.device)
+    blocks = _blocks(cfg, _flat_ptrs(flat, offsets), cond)
+    _lib.call("gtk_decoder_forward", ctypes.byref(d), blocks, _p(x), _p(mask), _p(z), _p(logdet), _p(ws), ws_bytes,
+              int(train), _stream())
+    if not train:
+        ws = ws.new_empty(0)
+    return z, logdet, ws
+
+
+@decoder_forward_flat.register_fake
+def _(x, mask, flat, offsets, cond, cfg, train):
+    B, Cin, T = x.shape
+    n = cfg[1]
+    return x.new_empty((B, Cin, (T // n) * n)), x.new_empty((B,)), x.new_empty((0,), dtype=torch.uint8)
+
+
+@torch.library.custom_op(f"{NS}::decoder_backward_flat", mutates_args=(), device_types="cuda")
+def decoder_backward_flat(dz: Tensor, dlogdet: Tensor, mask: Tensor, flat: Tensor, offsets: List[int], cond: Optional[Tensor],
+                          ws: Tensor, cfg: List[int], T: int) -> Tuple[Tensor, Tensor, Tensor]:
+    """-> (dx, d flat (same layout as flat), dcond)."""
+    dz, dlogdet, mask = _chk(dz, "dz"), _chk(dlogdet, "dlogdet"), _chk(_fit_mask(mask, T), "mask")
+    flat = _chk(flat, "flat")
+    cond = _opt(cond, "cond")
+    B, Cin = dz.shape[0], dz.shape[1]
+    d = _desc(cfg, B, T)
+    dx = torch.empty(B, Cin, T, dtype=dz.dtype, device=dz.device)
+    dflat = torch.zeros_like(flat)
+    dcond = torch.zeros_like(cond) if cond is not None else dz.new_empty(0)
+    blocks = _blocks(cfg, _flat_ptrs(flat, offsets), cond)
+    gblocks = _blocks(cfg, _flat_ptrs(dflat, offsets), dcond if cond is not None else None)
+    _lib.call("gtk_decoder_backward", ctypes.byref(d), blocks, gblocks, _p(mask), _p(dz), _p(dlogdet), _p(dx), _p(ws),
+              ws.numel(), _stream())
+    return dx, dflat, dcond
+
+
+@decoder_backward_flat.register_fake
+def _(dz, dlogdet, mask, flat, offsets, cond, ws, cfg, T):
+    return (dz.new_empty((dz.shape[0], dz.shape[1], T)), torch.empty_like(flat),
+            torch.empty_like(cond) if cond is not None else dz.new_empty(0))
+
+
+def _decf_setup(ctx, inputs, output):
+    x, mask, flat, offsets, cond, cfg, train = inputs
+    ctx.save_for_backward(mask, cond, output[2], flat)
+    ctx.cfg, ctx.T, ctx.train, ctx.has_cond, ctx.offsets = list(cfg), x.shape[2], train, cond is not None, list(offsets)
+
+
+def _decf_bwd(ctx, dz, dlogdet, dws):
+    if not ctx.train:
+        raise RuntimeError("glowtts_b200: decoder_forward was run with train=False; no activations were kept")
+    mask, cond, ws, flat = ctx.saved_tensors
+    B = mask.shape[0]
+    if dz is None:
+        Tz = (ctx.T // ctx.cfg[1]) * ctx.cfg[1]
+        dz = torch.zeros(B, ctx.cfg[0], Tz, dtype=mask.dtype, device=mask.device)
+    if dlogdet is None:
+        dlogdet = torch.zeros(B, dtype=mask.dtype, device=mask.device)
+    dx, dflat, dcond = decoder_backward_flat(dz.contiguous(), dlogdet.contiguous(), mask, flat, ctx.offsets, cond, ws, ctx.cfg,
+                                             ctx.T)
+    if _GRAD_SYNC["group"] is not None:
+        import torch.distributed as dist
+        dist.all_reduce(dflat, group=_GRAD_SYNC["group"])
+        dflat.div_(dist.get_world_size(_GRAD_SYNC["group"]))
+    return dx, None, dflat, None, (dcond if ctx.has_cond else None), None, None
+
+
+
 
 def set_grad_sync(group) -> None:
     """Enable (group = a torch.distributed process group, or dist.group.WORLD) or disable (None) the
@@ -695,6 +784,7 @@ def _dec_bwd(ctx, dz, dlogdet, dws):
 
 
 decoder_forward.register_autograd(_dec_bwd, setup_context=_dec_setup)
+decoder_forward_flat.register_autograd(_decf_bwd, setup_context=_decf_setup)
 
 
 # =============================================================================== coupling-block pieces
