@@ -56,6 +56,7 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t*
 struct SmemCtl {
     uint64_t full[4], empty[4], acc_full;
     uint32_t tmem_base;
+    alignas(16) float bias[512];        // [N] (zeros when there is none)
 };
 
 template <int TMEM_COLS, int EPI>
@@ -76,6 +77,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_init(&ctl->acc_full, 1);
         mbar_fence_init();
     }
+    for (int i = threadIdx.x; i < p.N; i += NTHREADS) ctl->bias[i] = p.bias ? p.bias[i] : 0.f;
     if (warp == 2) tmem_alloc<TMEM_COLS>(&ctl->tmem_base);
     tc_fence_before();
     __syncthreads();
@@ -119,24 +121,26 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             umma_commit(&ctl->acc_full);
         }
-    } else if (warp >= 4) {
+    }
+    __syncwarp();
+    {   // epilogue: ALL 8 warps; warp w owns TMEM lane quarter w % 4 (frames) and column half w / 4
         mbar_wait(&ctl->acc_full, 0);
         tc_fence_after();
-        const int q = warp & 3;
+        const int q = warp & 3, half = warp >> 2;
         const int t = t0 + q * 32 + lane;
         const bool t_ok = t < p.T;
         const float mk = (p.mask && t_ok) ? p.mask[(size_t)b * p.T + t] : 1.f;
         const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
         const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
         if constexpr (EPI == EPI_PLAIN) {
-            for (int c0 = 0; c0 < p.N; c0 += 16) {
+            const int nck = p.N / 16;
+            for (int cc = half ? (nck + 1) / 2 : 0; cc < (half ? nck : (nck + 1) / 2); ++cc) {
+                const int c0 = cc * 16;
                 float v[16];
                 tmem_ld16(trow + c0, v);
                 if (!t_ok) continue;
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    if (p.bias) v[i] += __ldg(p.bias + c0 + i);
-                }
+                for (int i = 0; i < 16; ++i) v[i] += ctl->bias[c0 + i];
                 if (p.resid_f32) {
                     const float4* r4 = reinterpret_cast<const float4*>(p.resid_f32 + frame * p.ld_resid + c0);
                     const float rm = p.mask_resid ? mk : 1.f;
@@ -166,8 +170,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
             }
         } else if constexpr (EPI == EPI_GATE_BWD) {
-            const int H = p.N;
-            for (int c0 = 0; c0 < H; c0 += 16) {
+            const int H = p.N, nck = H / 16;
+            for (int cc = half ? (nck + 1) / 2 : 0; cc < (half ? nck : (nck + 1) / 2); ++cc) {
+                const int c0 = cc * 16;
                 float d[16];
                 tmem_ld16(trow + c0, d);
                 if (!t_ok) continue;
@@ -196,7 +201,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         } else {   // EPI_AFFINE
             const int Ch = p.N / 2, C = p.N;
             float ld_sum = 0.f;
-            for (int c0 = 0; c0 < Ch; c0 += 16) {
+            const int nck = Ch / 16;
+            for (int cc = half ? (nck + 1) / 2 : 0; cc < (half ? nck : (nck + 1) / 2); ++cc) {
+                const int c0 = cc * 16;
                 float m[16], lg[16];
                 tmem_ld16(trow + c0, m);
                 tmem_ld16(trow + Ch + c0, lg);
@@ -205,8 +212,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
                     const int c = c0 + i;
-                    float mm = m[i] + (p.bias ? __ldg(p.bias + c) : 0.f);
-                    float ll = lg[i] + (p.bias ? __ldg(p.bias + Ch + c) : 0.f);
+                    float mm = m[i] + ctl->bias[c];
+                    float ll = lg[i] + ctl->bias[Ch + c];
                     lsave[i] = ll;     // raw end-conv output (pre sigmoid_scale), as the fp32 path keeps it
                     if (p.aff_sigmoid_scale) ll = __logf(1e-6f + sigmoid_f(ll + 2.f));
                     const size_t o0 = ((size_t)b * C + c) * p.T + t, o1 = o0 + (size_t)Ch * p.T;

@@ -203,6 +203,13 @@ __device__ __forceinline__ float dropout_scale(unsigned long long seed, unsigned
     return (u >= p) ? 1.0f / (1.0f - p) : 0.0f;
 }
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + __expf(-x)); }
+// single-MUFU forms used by the bf16 path (results are rounded to bf16 anyway; abs error ~5e-4)
+__device__ __forceinline__ float tanh_fast(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
 __device__ __forceinline__ void store_bf16x16(__nv_bfloat16* dst, const float (&v)[16]) {
     uint32_t w[8];
 #pragma unroll

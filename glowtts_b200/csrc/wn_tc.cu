@@ -20,6 +20,9 @@ namespace tc {
 struct WnCtl {
     uint64_t full[3], empty[3], acc_full, acts_ready;
     uint32_t tmem_base;
+    alignas(16) float bias_in[512];     // [2H]
+    alignas(16) float cond[512];        // this utterance's conditioning slice [2H] (zeros when there is none)
+    alignas(16) float bias_rs[512];     // [RS]
 };
 
 constexpr int WN_STAGES = 3;
@@ -42,169 +45,210 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     if (threadIdx.x == 0) {
         for (int s = 0; s < WN_STAGES; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
         mbar_init(&ctl->acc_full, 1);
-        mbar_init(&ctl->acts_ready, 128);
+        mbar_init(&ctl->acts_ready, NTHREADS);
         mbar_fence_init();
+    }
+    {
+        const float* cond = p.cond ? p.cond + (size_t)b * p.cond_bstride : nullptr;
+        for (int i = threadIdx.x; i < H2; i += NTHREADS) {
+            ctl->bias_in[i] = p.bias_in[i];
+            ctl->cond[i] = cond ? cond[i] : 0.f;
+        }
+        for (int i = threadIdx.x; i < RS; i += NTHREADS) ctl->bias_rs[i] = p.bias_rs[i];
     }
     if (warp == 2) tmem_alloc<512>(&ctl->tmem_base);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = ctl->tmem_base;
+    const uint32_t idesc = umma_idesc_bf16(BT, H);
 
-    if (warp == 0) {
-        if (lane == 0) {
-            tma_prefetch_desc(&tmH);
-            tma_prefetch_desc(&tmWin);
-            tma_prefetch_desc(&tmWrs);
-            for (int it = 0; it < n_all; ++it) {
-                const int s = it % WN_STAGES, use = it / WN_STAGES;
-                if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
-                unsigned char* sa = smem + (size_t)s * stage_bytes;
-                unsigned char* sb = sa + A_BYTES;
-                if (it < n1) {
-                    const int j = it / n_kh, kc = it % n_kh;
-                    mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(A_BYTES + H2 * KC * 2));
-                    tma_load_3d(sa, &tmH, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
-                    tma_load_3d(sb, &tmWin, &ctl->full[s], kc * KC, 0, j);
-                    tma_load_3d(sb + (size_t)H * KC * 2, &tmWin, &ctl->full[s], kc * KC, H, j);
-                } else {
-                    const int kc = it - n1;             // A slot of this stage is written by the epilogue warps
-                    mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(RS * KC * 2));
-                    tma_load_2d(sb, &tmWrs, &ctl->full[s], kc * KC, 0);
-                    if (RS > H) tma_load_2d(sb + (size_t)H * KC * 2, &tmWrs, &ctl->full[s], kc * KC, H);
-                }
+    // ---------------------------------------------------------------- roles during GEMM 1 (one lane each)
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmH);
+        tma_prefetch_desc(&tmWin);
+        tma_prefetch_desc(&tmWrs);
+        for (int it = 0; it < n_all; ++it) {
+            const int s = it % WN_STAGES, use = it / WN_STAGES;
+            if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
+            unsigned char* sa = smem + (size_t)s * stage_bytes;
+            unsigned char* sb = sa + A_BYTES;
+            if (it < n1) {
+                const int j = it / n_kh, kc = it % n_kh;
+                mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(A_BYTES + H2 * KC * 2));
+                tma_load_3d(sa, &tmH, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
+                tma_load_3d(sb, &tmWin, &ctl->full[s], kc * KC, 0, j);
+                tma_load_3d(sb + (size_t)H * KC * 2, &tmWin, &ctl->full[s], kc * KC, H, j);
+            } else {
+                const int kc = it - n1;                 // the A slot of this stage is written by epilogue 1
+                mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(RS * KC * 2));
+                tma_load_2d(sb, &tmWrs, &ctl->full[s], kc * KC, 0);
+                if (RS > H) tma_load_2d(sb + (size_t)H * KC * 2, &tmWrs, &ctl->full[s], kc * KC, H);
             }
         }
-    } else if (warp == 1) {
-        if (lane == 0) {
-            const uint32_t idesc = umma_idesc_bf16(BT, H);
-            for (int it = 0; it < n_all; ++it) {
-                const int s = it % WN_STAGES, use = it / WN_STAGES;
-                if (it == n1) {                          // GEMM 1 done -> epilogue 1 may read TMEM
-                    umma_commit(&ctl->acc_full);
-                    mbar_wait(&ctl->acts_ready, 0);      // acts are in the A slots, xin columns are free again
-                    tc_fence_after();
-                }
-                mbar_wait(&ctl->full[s], use & 1);
-                tc_fence_after();
-                const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
-                const uint32_t sb = sa + A_BYTES;
-                const uint64_t adesc = umma_desc_kmajor_sw128(sa);
-                const int nch = (it < n1) ? 2 : (RS > H ? 2 : 1);
-                const bool first = (it == 0) || (it == n1);
+    } else if (warp == 1 && lane == 0) {
+        for (int it = 0; it < n1; ++it) {
+            const int s = it % WN_STAGES, use = it / WN_STAGES;
+            mbar_wait(&ctl->full[s], use & 1);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+            const uint32_t sb = sa + A_BYTES;
+            const uint64_t adesc = umma_desc_kmajor_sw128(sa);
 #pragma unroll
-                for (int k = 0; k < KC / 16; ++k) {
-                    for (int ch = 0; ch < nch; ++ch) {
-                        const uint64_t bdesc = umma_desc_kmajor_sw128(sb + ch * H * KC * 2);
-                        umma_bf16(tmem + ch * H, adesc + 2 * k, bdesc + 2 * k, idesc, !(first && k == 0));
-                    }
+            for (int k = 0; k < KC / 16; ++k) {
+#pragma unroll
+                for (int ch = 0; ch < 2; ++ch) {
+                    const uint64_t bdesc = umma_desc_kmajor_sw128(sb + ch * H * KC * 2);
+                    umma_bf16(tmem + ch * H, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0);
                 }
-                umma_commit(&ctl->empty[s]);
             }
-            umma_commit(&ctl->acc_full);
+            umma_commit(&ctl->empty[s]);
         }
-    } else if (warp >= 4) {
-        const int q = warp & 3;
-        const int r = q * 32 + lane;                     // row of the tile == TMEM lane
-        const int t = t0 + r;
-        const bool t_ok = t < p.T;
-        const float mk = (p.mask && t_ok) ? p.mask[(size_t)b * p.T + t] : 1.f;
-        const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
-        const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
-        const float* cond = p.cond ? p.cond + (size_t)b * p.cond_bstride : nullptr;
+        umma_commit(&ctl->acc_full);                     // GEMM 1 done -> epilogue 1 may read TMEM
+    }
+    __syncwarp();
 
-        // ---------------------------------------------------------------- epilogue 1: gate -> A operand of GEMM 2
-        mbar_wait(&ctl->acc_full, 0);
-        tc_fence_after();
-        for (int c0 = 0; c0 < H; c0 += 16) {
-            float a[16], g[16];
-            tmem_ld16(trow + c0, a);
-            tmem_ld16(trow + H + c0, g);
+    // ---------------------------------------------------------------- epilogues: ALL 8 warps.  Warp w owns TMEM lane
+    // quarter w % 4 (frames) and column half w / 4.
+    const int q = warp & 3, half = warp >> 2;
+    const int r = q * 32 + lane;                         // row of the tile == TMEM lane
+    const int t = t0 + r;
+    const bool t_ok = t < p.T;
+    const float mk = (p.mask && t_ok) ? p.mask[(size_t)b * p.T + t] : 1.f;
+    const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
+    const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+    const int n_chunks = H / 16;
+    const int ch_lo = half ? (n_chunks + 1) / 2 : 0, ch_hi = half ? n_chunks : (n_chunks + 1) / 2;
+
+    // ---- epilogue 1: gate -> A operand of GEMM 2
+    mbar_wait(&ctl->acc_full, 0);
+    tc_fence_after();
+    for (int cc = ch_lo; cc < ch_hi; ++cc) {
+        const int c0 = cc * 16;
+        float a[16], g[16];
+        tmem_ld16(trow + c0, a);
+        tmem_ld16(trow + H + c0, g);
+#pragma unroll
+        for (int i = 0; i < 16; i += 4) {
+            const float4 ba = *reinterpret_cast<const float4*>(&ctl->bias_in[c0 + i]);
+            const float4 bg = *reinterpret_cast<const float4*>(&ctl->bias_in[H + c0 + i]);
+            a[i] += ba.x; a[i + 1] += ba.y; a[i + 2] += ba.z; a[i + 3] += ba.w;
+            g[i] += bg.x; g[i + 1] += bg.y; g[i + 2] += bg.z; g[i + 3] += bg.w;
+        }
+        if (p.drop_p > 0.f) {
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-                float xa = a[i] + __ldg(p.bias_in + c0 + i);
-                float xg = g[i] + __ldg(p.bias_in + H + c0 + i);
-                if (p.drop_p > 0.f) {
-                    xa *= dropout_scale(p.drop_seed, frame * H2 + c0 + i, p.drop_p);
-                    xg *= dropout_scale(p.drop_seed, frame * H2 + H + c0 + i, p.drop_p);
-                }
-                if (cond) { xa += __ldg(cond + c0 + i); xg += __ldg(cond + H + c0 + i); }
-                a[i] = tanhf(xa);
-                g[i] = sigmoid_f(xg);
-            }
-            if (p.ts_save && t_ok) {
-                store_bf16x16(p.ts_save + frame * H2 + c0, a);
-                store_bf16x16(p.ts_save + frame * H2 + H + c0, g);
-            }
-#pragma unroll
-            for (int i = 0; i < 16; ++i) a[i] *= g[i];
-            if (p.acts_save && t_ok) store_bf16x16(p.acts_save + frame * H + c0, a);
-            // canonical K-major SWIZZLE_128B: row r at r*128 B, 16-byte chunk index XOR (r % 8)
-            const int kc = c0 / KC, ci = (c0 % KC) / 8;
-            unsigned char* slot = smem + (size_t)((n1 + kc) % WN_STAGES) * stage_bytes + (size_t)r * 128;
-            uint32_t w[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                __nv_bfloat162 h2 = __floats2bfloat162_rn(a[2 * i], a[2 * i + 1]);
-                w[i] = *reinterpret_cast<uint32_t*>(&h2);
-            }
-            *reinterpret_cast<uint4*>(slot + ((ci ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-            *reinterpret_cast<uint4*>(slot + (((ci + 1) ^ (r & 7)) << 4)) = make_uint4(w[4], w[5], w[6], w[7]);
-        }
-        fence_proxy_async_smem();
-        tc_fence_before();
-        mbar_arrive(&ctl->acts_ready);
-
-        // ---------------------------------------------------------------- epilogue 2: residual / skip
-        mbar_wait(&ctl->acc_full, 1);
-        tc_fence_after();
-        for (int c0 = 0; c0 < H; c0 += 16) {
-            float v[16], sk[16];
-            if (RS > H) {
-                tmem_ld16(trow + c0, v);
-                tmem_ld16(trow + H + c0, sk);
-            } else {
-                tmem_ld16(trow + c0, sk);
-            }
-            if (!t_ok) continue;
-            if (RS > H) {
-                const float4* x4 = reinterpret_cast<const float4*>(p.h_f32 + frame * H + c0);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float4 x = x4[i];
-                    v[4 * i] = (v[4 * i] + __ldg(p.bias_rs + c0 + 4 * i) + x.x) * mk;
-                    v[4 * i + 1] = (v[4 * i + 1] + __ldg(p.bias_rs + c0 + 4 * i + 1) + x.y) * mk;
-                    v[4 * i + 2] = (v[4 * i + 2] + __ldg(p.bias_rs + c0 + 4 * i + 2) + x.z) * mk;
-                    v[4 * i + 3] = (v[4 * i + 3] + __ldg(p.bias_rs + c0 + 4 * i + 3) + x.w) * mk;
-                }
-                float4* o4 = reinterpret_cast<float4*>(p.h_out_f32 + frame * H + c0);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                store_bf16x16(p.h_out_bf16 + frame * H + c0, v);
-            }
-            const int bo = (RS > H) ? H : 0;
-#pragma unroll
-            for (int i = 0; i < 16; ++i) sk[i] += __ldg(p.bias_rs + bo + c0 + i);
-            if (!p.first) {
-                const float4* s4 = reinterpret_cast<const float4*>(p.skip_f32 + frame * H + c0);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float4 x = s4[i];
-                    sk[4 * i] += x.x; sk[4 * i + 1] += x.y; sk[4 * i + 2] += x.z; sk[4 * i + 3] += x.w;
-                }
-            }
-            if (p.last) {                                 // WN output = skip * mask (modules.py:171), operand of `end`
-#pragma unroll
-                for (int i = 0; i < 16; ++i) sk[i] *= mk;
-                store_bf16x16(p.skip_out_bf16 + frame * H + c0, sk);
-            } else {
-                float4* o4 = reinterpret_cast<float4*>(p.skip_f32 + frame * H + c0);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) o4[i] = make_float4(sk[4 * i], sk[4 * i + 1], sk[4 * i + 2], sk[4 * i + 3]);
+                a[i] *= dropout_scale(p.drop_seed, frame * H2 + c0 + i, p.drop_p);
+                g[i] *= dropout_scale(p.drop_seed, frame * H2 + H + c0 + i, p.drop_p);
             }
         }
-        tc_fence_before();
+#pragma unroll
+        for (int i = 0; i < 16; i += 4) {
+            const float4 ca = *reinterpret_cast<const float4*>(&ctl->cond[c0 + i]);
+            const float4 cg = *reinterpret_cast<const float4*>(&ctl->cond[H + c0 + i]);
+            a[i] = tanh_fast(a[i] + ca.x); a[i + 1] = tanh_fast(a[i + 1] + ca.y);
+            a[i + 2] = tanh_fast(a[i + 2] + ca.z); a[i + 3] = tanh_fast(a[i + 3] + ca.w);
+            g[i] = sigmoid_fast(g[i] + cg.x); g[i + 1] = sigmoid_fast(g[i + 1] + cg.y);
+            g[i + 2] = sigmoid_fast(g[i + 2] + cg.z); g[i + 3] = sigmoid_fast(g[i + 3] + cg.w);
+        }
+        if (p.ts_save && t_ok) {
+            store_bf16x16(p.ts_save + frame * H2 + c0, a);
+            store_bf16x16(p.ts_save + frame * H2 + H + c0, g);
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) a[i] *= g[i];
+        if (p.acts_save && t_ok) store_bf16x16(p.acts_save + frame * H + c0, a);
+        // canonical K-major SWIZZLE_128B: row r at r*128 B, 16-byte chunk index XOR (r % 8)
+        const int kc = c0 / KC, ci = (c0 % KC) / 8;
+        unsigned char* slot = smem + (size_t)((n1 + kc) % WN_STAGES) * stage_bytes + (size_t)r * 128;
+        uint32_t w[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(a[2 * i], a[2 * i + 1]);
+            w[i] = *reinterpret_cast<uint32_t*>(&h2);
+        }
+        *reinterpret_cast<uint4*>(slot + ((ci ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+        *reinterpret_cast<uint4*>(slot + (((ci + 1) ^ (r & 7)) << 4)) = make_uint4(w[4], w[5], w[6], w[7]);
     }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    mbar_arrive(&ctl->acts_ready);
+
+    // ---- GEMM 2 (res_skip 1x1): issued by warp 1 once every thread has delivered its gate outputs
+    if (warp == 1 && lane == 0) {
+        mbar_wait(&ctl->acts_ready, 0);                  // acts are in the A slots, the xin columns are free again
+        tc_fence_after();
+        for (int it = n1; it < n_all; ++it) {
+            const int s = it % WN_STAGES, use = it / WN_STAGES;
+            mbar_wait(&ctl->full[s], use & 1);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+            const uint32_t sb = sa + A_BYTES;
+            const uint64_t adesc = umma_desc_kmajor_sw128(sa);
+            const int nch = RS > H ? 2 : 1;
+#pragma unroll
+            for (int k = 0; k < KC / 16; ++k) {
+                for (int ch = 0; ch < nch; ++ch) {
+                    const uint64_t bdesc = umma_desc_kmajor_sw128(sb + ch * H * KC * 2);
+                    umma_bf16(tmem + ch * H, adesc + 2 * k, bdesc + 2 * k, idesc, (it != n1) || (k != 0));
+                }
+            }
+        }
+        umma_commit(&ctl->acc_full);
+    }
+    __syncwarp();
+
+    // ---- epilogue 2: residual / skip
+    mbar_wait(&ctl->acc_full, 1);
+    tc_fence_after();
+    for (int cc = ch_lo; cc < ch_hi; ++cc) {
+        const int c0 = cc * 16;
+        float v[16], sk[16];
+        if (RS > H) {
+            tmem_ld16(trow + c0, v);
+            tmem_ld16(trow + H + c0, sk);
+        } else {
+            tmem_ld16(trow + c0, sk);
+        }
+        if (!t_ok) continue;
+        if (RS > H) {
+            const float4* x4 = reinterpret_cast<const float4*>(p.h_f32 + frame * H + c0);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float4 x = x4[i];
+                const float4 bb = *reinterpret_cast<const float4*>(&ctl->bias_rs[c0 + 4 * i]);
+                v[4 * i] = (v[4 * i] + bb.x + x.x) * mk;
+                v[4 * i + 1] = (v[4 * i + 1] + bb.y + x.y) * mk;
+                v[4 * i + 2] = (v[4 * i + 2] + bb.z + x.z) * mk;
+                v[4 * i + 3] = (v[4 * i + 3] + bb.w + x.w) * mk;
+            }
+            float4* o4 = reinterpret_cast<float4*>(p.h_out_f32 + frame * H + c0);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            store_bf16x16(p.h_out_bf16 + frame * H + c0, v);
+        }
+        const int bo = (RS > H) ? H : 0;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) sk[i] += ctl->bias_rs[bo + c0 + i];
+        if (!p.first) {
+            const float4* s4 = reinterpret_cast<const float4*>(p.skip_f32 + frame * H + c0);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float4 x = s4[i];
+                sk[4 * i] += x.x; sk[4 * i + 1] += x.y; sk[4 * i + 2] += x.z; sk[4 * i + 3] += x.w;
+            }
+        }
+        if (p.last) {                                     // WN output = skip * mask (modules.py:171), operand of `end`
+#pragma unroll
+            for (int i = 0; i < 16; ++i) sk[i] *= mk;
+            store_bf16x16(p.skip_out_bf16 + frame * H + c0, sk);
+        } else {
+            float4* o4 = reinterpret_cast<float4*>(p.skip_f32 + frame * H + c0);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o4[i] = make_float4(sk[4 * i], sk[4 * i + 1], sk[4 * i + 2], sk[4 * i + 3]);
+        }
+    }
+    tc_fence_before();
     __syncthreads();
     if (warp == 2) {
         tc_fence_after();

@@ -1,0 +1,24 @@
+"""Aggregate an `ncu --metrics gpu__time_duration.sum --csv` launch list by kernel for the LAST full step in it.
+usage: python profiles/summarize_launches.py gpurun_out/launches.csv"""
+import collections
+import csv
+import re
+import sys
+
+lines = [l for l in open(sys.argv[1]) if not l.startswith("==")]
+rows = list(csv.DictReader(lines))
+names = [r["Kernel Name"] for r in rows]
+sq = [i for i, n in enumerate(names) if "squeeze_kernel" in n and "unsqueeze" not in n]
+start = sq[-2] if len(sq) >= 2 else 0          # each step has a forward squeeze and a backward one
+sel = rows[start:]
+agg = collections.defaultdict(lambda: [0, 0.0])
+for r in sel:
+    n = re.sub(r"[(<].*", "", r["Kernel Name"]).replace("void ", "")
+    v = float(r["Metric Value"].replace(",", ""))
+    v = v / 1e3 if r["Metric Unit"] == "ns" else (v * 1e3 if r["Metric Unit"] == "ms" else v)
+    agg[n][0] += 1
+    agg[n][1] += v
+tot = sum(v[1] for v in agg.values())
+print(f"launches {len(sel)}  total {tot:.1f} us (cold-cache, serialised: compare shares)")
+for n, (c, t) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:28]:
+    print(f"{t:10.1f} us {100 * t / tot:5.1f}% {c:5d}  {n}")
