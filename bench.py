@@ -35,7 +35,7 @@ import torch  # noqa: E402
 
 # ---- workload: configs/base.json "model" section (reference configs/base.json:32-51) + BASELINE configs[1]
 CFG = dict(in_channels=80, hidden_channels=192, kernel_size=5, dilation_rate=1, n_blocks=12, n_layers=4,
-           n_split=4, n_sqz=2, gin_channels=0)
+           n_split=4, n_sqz=2, gin_channels=0, p_dropout_dec=0.05)
 B_PER_GPU, T_TEXT, T_MEL = 32, 180, 860
 FLOP_PER_SQ_FRAME_FWD = 2 * (192 * 80 + 4 * (384 * 192 * 5) + 3 * (384 * 192) + 192 * 192 + 160 * 192)  # one block
 SEED = 1234  # configs/base.json:5
@@ -119,7 +119,7 @@ def build_decoder(device, precision):
     from glowtts_b200 import models
     torch.manual_seed(SEED)
     dec = models.FlowSpecDecoder(CFG["in_channels"], CFG["hidden_channels"], CFG["kernel_size"], CFG["dilation_rate"],
-                                 CFG["n_blocks"], CFG["n_layers"], p_dropout=0.0, n_split=CFG["n_split"],
+                                 CFG["n_blocks"], CFG["n_layers"], p_dropout=CFG["p_dropout_dec"], n_split=CFG["n_split"],
                                  n_sqz=CFG["n_sqz"], gin_channels=CFG["gin_channels"], precision=precision)
     with torch.no_grad():
         for b in range(CFG["n_blocks"]):          # non-trivial couplings (the reference starts them at zero)
@@ -240,7 +240,8 @@ def cpu_hot_path_sample(b_sample: int, threads: int, mas_impl: str):
     mask = (torch.arange(T_MEL)[None, :] < y_len[:, None]).float().unsqueeze(1)
     t0 = time.perf_counter()
     z, logdet = oflow.decoder(sd, y, mask, hidden=CFG["hidden_channels"], dilation_rate=CFG["dilation_rate"],
-                              n_blocks=CFG["n_blocks"], n_layers=CFG["n_layers"], n_split=CFG["n_split"], n_sqz=CFG["n_sqz"])
+                              n_blocks=CFG["n_blocks"], n_layers=CFG["n_layers"], n_split=CFG["n_split"], n_sqz=CFG["n_sqz"],
+                              drop=lambda blk, i, v: torch.nn.functional.dropout(v, CFG["p_dropout_dec"]))
     with torch.no_grad():
         lp = oflow.logp(x_m, torch.zeros_like(x_m), z)
         x_mask = (torch.arange(T_TEXT)[None, :] < x_len[:, None]).float()
@@ -306,7 +307,7 @@ def workload_config(world, precision):
                         "n_sqz 2) fwd+bwd + logp + MAS + prior gather + mle_loss + AdamW; synthetic LJSpeech-shaped "
                         "mels, ragged lengths",
             "batch_per_gpu": B_PER_GPU, "global_batch": B_PER_GPU * world, "t_text": T_TEXT, "t_mel": T_MEL,
-            "precision": precision, "p_dropout": 0.0,
+            "precision": precision, "p_dropout_dec": CFG["p_dropout_dec"],
             "l2": "per-step working set (activation workspace ~2.4 GB) exceeds the 126 MB L2",
             "parallelism": f"dp{world} (batch sharded, one flat-gradient NCCL all-reduce per step)" if world > 1 else "single GPU"}
 
@@ -318,7 +319,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default=os.environ.get("GTK_PRECISION", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--precision", default=os.environ.get("GTK_PRECISION", "bf16"), choices=["fp32", "bf16"],
+                    help="bf16 = tcgen05 tensor-core WN path (north_star); fp32 = exact-parity CUDA-core path")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

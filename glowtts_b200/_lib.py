@@ -24,7 +24,8 @@ class DecoderDesc(ctypes.Structure):
     """gtk_decoder_desc (include/glowtts_b200.h)."""
     _fields_ = [(n, ctypes.c_int) for n in (
         "B", "in_channels", "T", "n_sqz", "hidden", "kernel_size", "dilation_rate", "n_layers",
-        "n_blocks", "n_split", "sigmoid_scale", "precision")]
+        "n_blocks", "n_split", "sigmoid_scale", "precision")] + [("p_dropout", ctypes.c_float),
+                                                                 ("seed", ctypes.c_ulonglong)]
 
 
 _BLOCK_FIELDS = ("an_logs", "an_bias", "ic_weight", "start_g", "start_v", "start_b",

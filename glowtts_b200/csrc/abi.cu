@@ -150,10 +150,16 @@ int gtk_unsqueeze(const float* x, const float* mask, float* out, float* mask_out
     return flow::unsqueeze(x, mask, out, mask_out, B, C, T, n_sqz, 0, ST);
 }
 int gtk_gate_fwd(const float* a, const float* b, int cond_mode, float* out, int B, int H, int T, void* stream) {
-    return flow::gate_fwd(a, b, cond_mode, 0, out, B, H, T, ST);
+    return flow::gate_fwd(a, b, cond_mode, 0, out, B, H, T, 0.f, 0ull, ST);
 }
 int gtk_gate_bwd(const float* a, const float* b, int cond_mode, const float* dout, float* da, int B, int H, int T, void* stream) {
-    return flow::gate_bwd(a, b, cond_mode, 0, dout, da, B, H, T, ST);
+    return flow::gate_bwd(a, b, cond_mode, 0, dout, da, B, H, T, 0.f, 0ull, 1, ST);
+}
+int gtk_dropout_scale(unsigned long long seed, float p, long long n, float* out, void* stream) {
+    return flow::dropout_scale(seed, p, n, out, ST);
+}
+unsigned long long gtk_decoder_layer_seed(unsigned long long seed, int block, int layer) {
+    return drop_layer_seed(seed, block, layer);
 }
 int gtk_row_sum(const float* in, float* out, int R, int T, int accumulate, void* stream) {
     return flow::row_sum(in, out, R, T, accumulate, 0, 0, ST);
@@ -265,6 +271,7 @@ int gtk_tc_colsum(const void* in_bf16, int ld, int n_cols, int groups, long long
                   size_t out_gstride, void* stream) {
     return tc::colsum_frames(static_cast<const __nv_bfloat16*>(in_bf16), ld, n_cols, groups, rows_per_group, out, out_gstride, ST);
 }
+int gtk_debug_wn_trace(unsigned long long* out, int n_ctas) { return tc::wn_trace_read(out, n_ctas); }
 int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, const void* wrs_p, const float* bias_in,
                     const float* bias_rs, const float* cond, size_t cond_bstride, const float* mask, int B, int T, int H,
                     int RS, int K, int dil, int first, int last, float drop_p, unsigned long long drop_seed,

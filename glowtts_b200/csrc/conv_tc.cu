@@ -189,11 +189,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     store_bf16x16(p.out2_bf16 + frame * (2 * H) + H + c0, ds);
                 }
                 if (p.drop_p > 0.f) {
+                    float sc[16];
+                    dropout_scale16(p.drop_seed, (unsigned long long)frame * (2 * H) + c0, p.drop_p, sc);
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        dt[i] *= dropout_scale(p.drop_seed, frame * (2 * H) + c0 + i, p.drop_p);
-                        ds[i] *= dropout_scale(p.drop_seed, frame * (2 * H) + H + c0 + i, p.drop_p);
-                    }
+                    for (int i = 0; i < 16; ++i) dt[i] *= sc[i];
+                    dropout_scale16(p.drop_seed, (unsigned long long)frame * (2 * H) + H + c0, p.drop_p, sc);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) ds[i] *= sc[i];
                 }
                 store_bf16x16(p.out_bf16 + frame * p.ld_bf16 + c0, dt);
                 store_bf16x16(p.out_bf16 + frame * p.ld_bf16 + H + c0, ds);

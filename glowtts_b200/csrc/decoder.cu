@@ -31,6 +31,7 @@ static int make_dims(const gtk_decoder_desc* d, Dims* o) {
     GTK_REQUIRE(d->kernel_size % 2 == 1, "kernel_size must be odd (modules.py:108)");
     GTK_REQUIRE(d->hidden % 2 == 0, "hidden_channels must be even (modules.py:109)");
     GTK_REQUIRE(d->n_split == 2 || d->n_split == 4 || d->n_split == 8, "n_split must be 2, 4 or 8");
+    GTK_REQUIRE(d->p_dropout >= 0.f && d->p_dropout < 1.f, "p_dropout must be in [0, 1)");
     o->B = d->B; o->Cin = d->in_channels; o->T = d->T; o->n = d->n_sqz;
     o->C = d->in_channels * d->n_sqz; o->Tq = d->T / d->n_sqz;
     o->H = d->hidden; o->K = d->kernel_size; o->L = d->n_layers; o->NB = d->n_blocks; o->NS = d->n_split;
@@ -162,7 +163,8 @@ static int check_block(const Dims& D, const gtk_block_params& P) {
 
 // start -> WN -> end of one coupling block on xc[:, :C/2]; leaves end_out in act.a_end (attentions.py:151-170).
 static int coupling_net(const Dims& D, const Layout& L, const gtk_block_params& P, const float* we, const float* xc,
-                        const float* mask, float* act, float* rs, float* wp, cudaStream_t st) {
+                        const float* mask, float* act, float* rs, float* wp, float drop_p, unsigned long long seed, int blk,
+                        cudaStream_t st) {
     const int B = D.B, T = D.Tq, H = D.H, C = D.C, Ch = D.C / 2;
     const size_t cbs = (size_t)C * T;
     GTK_TRY(conv::pack_weight(w_start(L, P, we), wp, H, Ch, 1, 0, st));
@@ -173,7 +175,7 @@ static int coupling_net(const Dims& D, const Layout& L, const gtk_block_params& 
         GTK_TRY(conv(act + L.a_h[i], 0, wp, P.in_b[i], mask, nullptr, 0, act + L.a_xin[i], 0, B, H, 2 * H, T, D.K,
                      ipow(D.dr, i), 0, 0, 0, st));
         GTK_TRY(flow::gate_fwd(act + L.a_xin[i], P.cond ? P.cond + (size_t)i * 2 * H : nullptr, P.cond ? 1 : 0,
-                               (size_t)2 * H * D.L, act + L.a_acts[i], B, H, T, st));
+                               (size_t)2 * H * D.L, act + L.a_acts[i], B, H, T, drop_p, drop_layer_seed(seed, blk, i), st));
         GTK_TRY(conv::pack_weight(w_rs(L, P, we, i), wp, RS, H, 1, 0, st));
         GTK_TRY(conv(act + L.a_acts[i], 0, wp, P.rs_b[i], mask, nullptr, 0, rs, 0, B, H, RS, T, 1, 1, 0, 0, 0, st));
         GTK_TRY(flow::resskip(rs, act + L.a_h[i], mask, (i < D.L - 1) ? act + L.a_h[i + 1] : nullptr, act + L.a_skip, B, H, RS,
@@ -225,7 +227,7 @@ int forward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const flo
         GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, icld, st));
         GTK_TRY(flow::mix(xin, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, act + L.a_xmix, D.B, D.C, D.Tq, 0, st));
         GTK_TRY(flow::logdet_const(P.an_logs, D.C, icld, (float)(D.C / D.NS), ws + L.x_len, logdet, D.B, 1, st));
-        GTK_TRY(coupling_net(D, L, P, we, act + L.a_xmix, msq, act, ws + L.rs, ws + L.wp, st));
+        GTK_TRY(coupling_net(D, L, P, we, act + L.a_xmix, msq, act, ws + L.rs, ws + L.wp, d->p_dropout, d->seed, blk, st));
         GTK_TRY(flow::affine(act + L.a_xmix, act + L.a_end, msq, xout, logdet, D.B, D.C, D.Tq, 0, d->sigmoid_scale, st));
     }
     const float* xfin = ws + L.X + (size_t)(train ? D.NB : (D.NB & 1)) * xsz;
@@ -258,7 +260,7 @@ int reverse(const gtk_decoder_desc* d, const gtk_block_params* blocks, const flo
         float* winv = ws + L.winv + (size_t)blk * 64;
         GTK_TRY(fold_weights(D, L, P, we, st));
         GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, nullptr, st));
-        GTK_TRY(coupling_net(D, L, P, we, xa, msq, act, ws + L.rs, ws + L.wp, st));
+        GTK_TRY(coupling_net(D, L, P, we, xa, msq, act, ws + L.rs, ws + L.wp, d->p_dropout, d->seed, blk, st));
         GTK_TRY(flow::affine(xa, act + L.a_end, msq, xb, nullptr, D.B, D.C, D.Tq, 1, d->sigmoid_scale, st));
         GTK_TRY(flow::mix(xb, msq, P.an_logs, P.an_bias, winv, D.NS, xa, D.B, D.C, D.Tq, 1, st));
     }

@@ -123,7 +123,7 @@ static int tc_pack_block(const Dims& D, const TcLayout& L, const gtk_block_param
 // start -> WN -> end(+affine) of one block.  xc = mixed block input (t-major fp32), zout = block output.
 static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout& L, const gtk_block_params& P, const bf16* pk,
                        const float* xc, float* zout, float* logdet, const float* mask, unsigned char* act, unsigned char* ws,
-                       int reverse, int save, unsigned long long seed_base, cudaStream_t st) {
+                       int reverse, int save, int blk, cudaStream_t st) {
     const int B = D.B, T = D.Tq, H = D.H, C = D.C, Ch = D.C / 2;
     const TcPack& Q = L.P;
     const TcAct& A = L.A;
@@ -148,7 +148,7 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
         p.bias_in = P.in_b[i]; p.bias_rs = P.rs_b[i];
         p.cond = P.cond ? P.cond + (size_t)i * 2 * H : nullptr; p.cond_bstride = (size_t)2 * H * D.L;
         p.mask = mask;
-        p.drop_p = 0.f; p.drop_seed = seed_base + i;
+        p.drop_p = d->p_dropout; p.drop_seed = drop_layer_seed(d->seed, blk, i);
         p.h_f32 = hf[i & 1]; p.h_out_f32 = hf[(i + 1) & 1];
         p.h_out_bf16 = (i < D.L - 1) ? reinterpret_cast<bf16*>(act + A.h[i + 1]) : nullptr;
         p.skip_f32 = skipf;
@@ -202,7 +202,7 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
         GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, icld, st));
         GTK_TRY(flow::mix(xin, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, xmix, D.B, D.C, D.Tq, 0, st));
         GTK_TRY(flow::logdet_const(P.an_logs, D.C, icld, (float)(D.C / D.NS), x_len, logdet, D.B, 1, st));
-        GTK_TRY(tc_coupling(d, D, L, P, pk, xmix, xout, logdet, msq, act, ws, 0, train, 0x1000ull * blk, st));
+        GTK_TRY(tc_coupling(d, D, L, P, pk, xmix, xout, logdet, msq, act, ws, 0, train, blk, st));
     }
     const float* xfin = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? D.NB : (D.NB & 1)) * L.x_bytes);
     GTK_TRY(flow::unsqueeze(xfin, msq, z, nullptr, D.B, D.C, D.Tq, D.n, 0, st));
@@ -233,7 +233,7 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
         float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
         GTK_TRY(tc_pack_block(D, L, P, pk, 0, st));
         GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, nullptr, st));
-        GTK_TRY(tc_coupling(d, D, L, P, pk, xa, xb, nullptr, msq, act, ws, 1, 0, 0, st));
+        GTK_TRY(tc_coupling(d, D, L, P, pk, xa, xb, nullptr, msq, act, ws, 1, 0, blk, st));
         GTK_TRY(flow::mix(xb, msq, P.an_logs, P.an_bias, winv, D.NS, xa, D.B, D.C, D.Tq, 1, st));
     }
     GTK_TRY(flow::unsqueeze(xa, msq, x, nullptr, D.B, D.C, D.Tq, D.n, 0, st));
@@ -273,6 +273,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     bf16* dend = reinterpret_cast<bf16*>(ws + L.b_dend);
     bf16* drs = reinterpret_cast<bf16*>(ws + L.b_drs);
     bf16* dxin = reinterpret_cast<bf16*>(ws + L.b_dxin);
+    bf16* dgate = reinterpret_cast<bf16*>(ws + L.b_dgate);
     float* dhf[2] = {reinterpret_cast<float*>(ws + L.b_dhf[0]), reinterpret_cast<float*>(ws + L.b_dhf[1])};
     bf16* dh0 = reinterpret_cast<bf16*>(ws + L.b_dh0);
     float* dweff = reinterpret_cast<float*>(ws + L.b_wpart);   // split-K partial tiles of the weight gradients
@@ -312,6 +313,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
             const bf16* ts = reinterpret_cast<const bf16*>(act + A.ts[i]);
             const bf16* acts = reinterpret_cast<const bf16*>(act + A.acts[i]);
             const bf16* h_i = reinterpret_cast<const bf16*>(act + A.h[i]);
+            const bool want_dcond = P.cond && G.cond;
             // res_skip 1x1: parameter gradients, then data gradient fused with the gate backward
             GTK_TRY(tc_wgrad_param(P.rs_g[i], P.rs_v[i], G.rs_g[i], G.rs_v[i], dweff, drs_i, 2 * H, RS, acts, H, H, B, T, RS, H, 1, 1, st));
             if (G.rs_b[i]) GTK_TRY(tc::colsum_frames(drs_i, 2 * H, RS, 1, rows, G.rs_b[i], 0, st));
@@ -321,10 +323,14 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = pad64(RS) / 64; p.N = H;
                 p.mask = msq;
                 p.ts = ts; p.out_bf16 = dxin; p.ld_bf16 = 2 * H;
+                p.drop_p = d->p_dropout; p.drop_seed = drop_layer_seed(d->seed, blk, i);
+                // the conditioning enters after the dropout: with both active keep the un-scaled gate gradient too
+                if (want_dcond && d->p_dropout > 0.f) p.out2_bf16 = dgate;
                 GTK_TRY(tc::conv_tc_launch(drs_i, 2 * H, pk + Q.t_rs[i], p, tc::EPI_GATE_BWD, st));
             }
-            if (P.cond && G.cond)
-                GTK_TRY(tc::colsum_frames(dxin, 2 * H, 2 * H, B, T, G.cond + (size_t)i * 2 * H, (size_t)2 * H * D.L, st));
+            if (want_dcond)
+                GTK_TRY(tc::colsum_frames(d->p_dropout > 0.f ? dgate : dxin, 2 * H, 2 * H, B, T, G.cond + (size_t)i * 2 * H,
+                                          (size_t)2 * H * D.L, st));
             // in_layer dilated conv
             GTK_TRY(tc_wgrad_param(P.in_g[i], P.in_v[i], G.in_g[i], G.in_v[i], dweff, dxin, 2 * H, 2 * H, h_i, H, H, B, T, 2 * H, H, K,
                                    dil, st));

@@ -60,7 +60,7 @@ int actnorm_ddi_finalize(const float* stats, float* logs, float* bias, int C, cu
 // ------------------------------------------------------------------------------------------ gate
 // cond_mode: 0 none, 1 cond[B,2H] broadcast over t, 2 cond[B,2H,T]
 __global__ void gate_fwd_kernel(const float* __restrict__ a, const float* __restrict__ cond, int cond_mode, size_t cbs,
-                                float* __restrict__ out, int B, int H, int T) {
+                                float* __restrict__ out, int B, int H, int T, float drop_p, unsigned long long seed) {
     const long long total = (long long)B * H * T;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int t = (int)(i % T);
@@ -68,13 +68,20 @@ __global__ void gate_fwd_kernel(const float* __restrict__ a, const float* __rest
         const int h = (int)(r % H), b = (int)(r / H);
         const size_t o1 = ((size_t)b * 2 * H + h) * T + t, o2 = o1 + (size_t)H * T;
         float s1 = a[o1], s2 = a[o2];
+        if (drop_p > 0.f) {                                  // nn.Dropout on the in_layer output (modules.py:153)
+            const unsigned long long e = ((unsigned long long)b * T + t) * (2ull * H) + h;
+            s1 *= dropout_scale1(seed, e, drop_p);
+            s2 *= dropout_scale1(seed, e + H, drop_p);
+        }
         if (cond_mode == 1) { s1 += cond[(size_t)b * cbs + h]; s2 += cond[(size_t)b * cbs + H + h]; }
         else if (cond_mode == 2) { s1 += cond[o1]; s2 += cond[o2]; }
         out[i] = tanhf(s1) * sigmoidf_(s2);
     }
 }
+// scale_out = 1: da = d(in_layer output) (dropout-scaled); 0: da = d(gate pre-activation) (what the conditioning sees).
 __global__ void gate_bwd_kernel(const float* __restrict__ a, const float* __restrict__ cond, int cond_mode, size_t cbs,
-                                const float* __restrict__ dout, float* __restrict__ da, int B, int H, int T) {
+                                const float* __restrict__ dout, float* __restrict__ da, int B, int H, int T, float drop_p,
+                                unsigned long long seed, int scale_out) {
     const long long total = (long long)B * H * T;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int t = (int)(i % T);
@@ -82,30 +89,52 @@ __global__ void gate_bwd_kernel(const float* __restrict__ a, const float* __rest
         const int h = (int)(r % H), b = (int)(r / H);
         const size_t o1 = ((size_t)b * 2 * H + h) * T + t, o2 = o1 + (size_t)H * T;
         float s1 = a[o1], s2 = a[o2];
+        float k1 = 1.f, k2 = 1.f;
+        if (drop_p > 0.f) {
+            const unsigned long long e = ((unsigned long long)b * T + t) * (2ull * H) + h;
+            k1 = dropout_scale1(seed, e, drop_p);
+            k2 = dropout_scale1(seed, e + H, drop_p);
+            s1 *= k1; s2 *= k2;
+            if (!scale_out) k1 = k2 = 1.f;
+        }
         if (cond_mode == 1) { s1 += cond[(size_t)b * cbs + h]; s2 += cond[(size_t)b * cbs + H + h]; }
         else if (cond_mode == 2) { s1 += cond[o1]; s2 += cond[o2]; }
         const float th = tanhf(s1), sg = sigmoidf_(s2), g = dout[i];
-        da[o1] = g * sg * (1.f - th * th);
-        da[o2] = g * th * sg * (1.f - sg);
+        da[o1] = g * sg * (1.f - th * th) * k1;
+        da[o2] = g * th * sg * (1.f - sg) * k2;
     }
 }
 int gate_fwd(const float* a, const float* cond, int cond_mode, size_t cond_bstride, float* out, int B, int H, int T,
-             cudaStream_t st) {
+             float drop_p, unsigned long long seed, cudaStream_t st) {
     if (cond_bstride == 0) cond_bstride = 2 * (size_t)H;
     GTK_REQUIRE(a && out && (cond_mode == 0 || cond), "bad args");
+    GTK_REQUIRE(drop_p >= 0.f && drop_p < 1.f, "dropout probability");
     const long long total = (long long)B * H * T;
     if (total == 0) return GTK_OK;
-    gate_fwd_kernel<<<pw_grid(total), PW_NT, 0, st>>>(a, cond, cond_mode, cond_bstride, out, B, H, T);
+    gate_fwd_kernel<<<pw_grid(total), PW_NT, 0, st>>>(a, cond, cond_mode, cond_bstride, out, B, H, T, drop_p, seed);
     return check_launch("gate_fwd");
 }
 int gate_bwd(const float* a, const float* cond, int cond_mode, size_t cond_bstride, const float* dout, float* da, int B, int H,
-             int T, cudaStream_t st) {
+             int T, float drop_p, unsigned long long seed, int scale_out, cudaStream_t st) {
     if (cond_bstride == 0) cond_bstride = 2 * (size_t)H;
     GTK_REQUIRE(a && dout && da && (cond_mode == 0 || cond), "bad args");
+    GTK_REQUIRE(drop_p >= 0.f && drop_p < 1.f, "dropout probability");
     const long long total = (long long)B * H * T;
     if (total == 0) return GTK_OK;
-    gate_bwd_kernel<<<pw_grid(total), PW_NT, 0, st>>>(a, cond, cond_mode, cond_bstride, dout, da, B, H, T);
+    gate_bwd_kernel<<<pw_grid(total), PW_NT, 0, st>>>(a, cond, cond_mode, cond_bstride, dout, da, B, H, T, drop_p, seed,
+                                                       scale_out);
     return check_launch("gate_bwd");
+}
+// scale[i] = dropout keep-scale of element i (0 or 1/(1-p)) for i in [0, n): the mask the decoder kernels apply.
+__global__ void dropout_scale_kernel(unsigned long long seed, float p, long long n, float* __restrict__ out) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = dropout_scale1(seed, (unsigned long long)i, p);
+}
+int dropout_scale(unsigned long long seed, float p, long long n, float* out, cudaStream_t st) {
+    GTK_REQUIRE(n >= 0 && (n == 0 || out) && p >= 0.f && p < 1.f, "bad args");
+    if (n == 0) return GTK_OK;
+    dropout_scale_kernel<<<pw_grid(n), PW_NT, 0, st>>>(seed, p, n, out);
+    return check_launch("dropout_scale");
 }
 
 // ------------------------------------------------------------------------------------------ reductions

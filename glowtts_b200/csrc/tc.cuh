@@ -73,6 +73,8 @@ struct WnLayerParams {
 int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, const __nv_bfloat16* wrs_p, WnLayerParams p,
                     cudaStream_t st);
 
+int wn_trace_read(unsigned long long* out, int n_ctas);
+
 int wgrad_tc_launch(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, float* dw, int B,
                     int T, int M, int Cin, int K, int dil, cudaStream_t st);
 size_t wgrad_tc_workspace_bytes();
@@ -192,15 +194,6 @@ __device__ __forceinline__ bool elect_one() {
         "{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(pred));
     return pred != 0;
-}
-// Counter-based dropout mask shared by the forward and backward kernels: keep iff u >= p.
-__device__ __forceinline__ float dropout_scale(unsigned long long seed, unsigned long long idx, float p) {
-    unsigned long long z = seed + idx * 0x9E3779B97F4A7C15ull;
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-    z ^= z >> 31;
-    const float u = (float)(uint32_t)(z >> 40) * (1.0f / 16777216.0f);
-    return (u >= p) ? 1.0f / (1.0f - p) : 0.0f;
 }
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + __expf(-x)); }
 // single-MUFU forms used by the bf16 path (results are rounded to bf16 anyway; abs error ~5e-4)

@@ -27,6 +27,22 @@ struct WnCtl {
 
 constexpr int WN_STAGES = 3;
 
+// Phase timestamps (globaltimer, ns) of every CTA: g_wn_trace[cta][start, setup done, GEMM1 done, epilogue1 done,
+// GEMM2 done, end], cta = blockIdx.y * gridDim.x + blockIdx.x (first WN_TRACE_CTAS only).  Always written (6 stores by
+// one thread per CTA); read with gtk_debug_wn_trace for the per-phase breakdown in profiles/.
+constexpr int WN_TRACE_CTAS = 512;
+__device__ unsigned long long g_wn_trace[WN_TRACE_CTAS * 6];
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define WN_TRACE(i)                                                                     \
+    do {                                                                                \
+        const int cta_ = blockIdx.y * gridDim.x + blockIdx.x;                           \
+        if (threadIdx.x == 128 && cta_ < WN_TRACE_CTAS) g_wn_trace[cta_ * 6 + (i)] = gtimer(); \
+    } while (0)
+
 __global__ void __launch_bounds__(NTHREADS, 1)
 wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmWin,
                 const __grid_constant__ CUtensorMap tmWrs, const WnLayerParams p) {
@@ -39,6 +55,7 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int t0 = blockIdx.x * BT, b = blockIdx.y;
+    WN_TRACE(0);
     const int n1 = p.taps * n_kh;                       // GEMM-1 iterations
     const int n_all = n1 + n_kh;                        // + GEMM-2 iterations
 
@@ -62,6 +79,7 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     tc_fence_after();
     const uint32_t tmem = ctl->tmem_base;
     const uint32_t idesc = umma_idesc_bf16(BT, H);
+    WN_TRACE(1);
 
     // ---------------------------------------------------------------- roles during GEMM 1 (one lane each)
     if (warp == 0 && lane == 0) {
@@ -123,6 +141,7 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     // ---- epilogue 1: gate -> A operand of GEMM 2
     mbar_wait(&ctl->acc_full, 0);
     tc_fence_after();
+    WN_TRACE(2);
     for (int cc = ch_lo; cc < ch_hi; ++cc) {
         const int c0 = cc * 16;
         float a[16], g[16];
@@ -136,11 +155,13 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
             g[i] += bg.x; g[i + 1] += bg.y; g[i + 2] += bg.z; g[i + 3] += bg.w;
         }
         if (p.drop_p > 0.f) {
+            float sc[16];
+            dropout_scale16(p.drop_seed, (unsigned long long)frame * H2 + c0, p.drop_p, sc);
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                a[i] *= dropout_scale(p.drop_seed, frame * H2 + c0 + i, p.drop_p);
-                g[i] *= dropout_scale(p.drop_seed, frame * H2 + H + c0 + i, p.drop_p);
-            }
+            for (int i = 0; i < 16; ++i) a[i] *= sc[i];
+            dropout_scale16(p.drop_seed, (unsigned long long)frame * H2 + H + c0, p.drop_p, sc);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) g[i] *= sc[i];
         }
 #pragma unroll
         for (int i = 0; i < 16; i += 4) {
@@ -173,6 +194,7 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     fence_proxy_async_smem();
     tc_fence_before();
     mbar_arrive(&ctl->acts_ready);
+    WN_TRACE(3);
 
     // ---- GEMM 2 (res_skip 1x1): issued by warp 1 once every thread has delivered its gate outputs
     if (warp == 1 && lane == 0) {
@@ -201,6 +223,7 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     // ---- epilogue 2: residual / skip
     mbar_wait(&ctl->acc_full, 1);
     tc_fence_after();
+    WN_TRACE(4);
     for (int cc = ch_lo; cc < ch_hi; ++cc) {
         const int c0 = cc * 16;
         float v[16], sk[16];
@@ -249,11 +272,18 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
         }
     }
     tc_fence_before();
+    WN_TRACE(5);
     __syncthreads();
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc<512>(tmem);
     }
+}
+
+int wn_trace_read(unsigned long long* out, int n_ctas) {
+    GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= WN_TRACE_CTAS, "n_ctas");
+    GTK_CUDA(cudaMemcpyFromSymbol(out, g_wn_trace, size_t(n_ctas) * 6 * sizeof(unsigned long long)));
+    return GTK_OK;
 }
 
 int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, const __nv_bfloat16* wrs_p, WnLayerParams p,

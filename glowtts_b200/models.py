@@ -42,9 +42,13 @@ class FlowSpecDecoder(nn.Module):
 
     # ---------------------------------------------------------------- fused call plumbing
     def _cfg(self, folded: bool):
+        # nn.Dropout(p_dropout) on the WN in_layer outputs (modules.py:120,153) is active in training mode only; the
+        # per-call seed comes from torch's CPU generator, so torch.manual_seed makes runs reproducible.
+        drop = self.training and self.p_dropout > 0
         return [self.in_channels, self.n_sqz, self.hidden_channels, self.kernel_size, self.dilation_rate,
                 self.n_layers, self.n_blocks, self.n_split, int(bool(self.sigmoid_scale)),
-                {"fp32": 0, "bf16": 1}[self.precision], int(folded)]
+                {"fp32": 0, "bf16": 1}[self.precision], int(folded),
+                int(round(self.p_dropout * 1e6)) if drop else 0, ops.draw_seed() if drop else 0]
 
     def _params(self):
         out, folded = [], None
@@ -63,8 +67,6 @@ class FlowSpecDecoder(nn.Module):
     def forward(self, x, x_mask, g=None, emo=None, pitch=None, energy=None, reverse=False):
         if pitch is not None or energy is not None:
             raise NotImplementedError("glowtts_b200.FlowSpecDecoder: pitch/energy WaveNets are not built yet")
-        if self.training and self.p_dropout > 0 and not reverse:
-            raise RuntimeError("glowtts_b200.FlowSpecDecoder: p_dropout > 0 in training mode is not implemented")
         for b in range(self.n_blocks):          # data-dependent init, if requested (init.py:17-23)
             if not self.flows[3 * b].initialized:
                 return self._forward_unfused(x, x_mask, g, reverse)

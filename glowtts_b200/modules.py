@@ -208,14 +208,15 @@ class WN(nn.Module):
 
     def forward(self, x, x_mask=None, g=None, **kwargs):
         H = self.hidden_channels
-        if self.training and self.p_dropout > 0:
-            raise RuntimeError("glowtts_b200.WN: dropout inside the fused stack is not implemented; "
-                               "use p_dropout=0 or eval() (documented deviation, DESIGN.md)")
+        drop = self.training and self.p_dropout > 0
+        seed = ops.draw_seed() if drop else 0
         mask = 1 if x_mask is None else x_mask
         cond = self.conditioning(g)
         output = None
         for i in range(self.n_layers):
             x_in = self.in_layers[i](x)
+            if drop:                          # modules.py:153, with the library's counter-based mask
+                x_in = x_in * ops.dropout_scale(seed, 0, i, self.p_dropout, x_in.shape[0], x_in.shape[2], 2 * H, x_in.device)
             g_l = None if cond is None else cond[:, 2 * H * i: 2 * H * (i + 1)].contiguous()
             acts = ops.gate_fwd(x_in, g_l)
             rs = self.res_skip_layers[i](acts)

@@ -520,9 +520,26 @@ def _desc(cfg: Sequence[int], B: int, T: int) -> DecoderDesc:
     d.B, d.T = B, T
     (d.in_channels, d.n_sqz, d.hidden, d.kernel_size, d.dilation_rate, d.n_layers, d.n_blocks, d.n_split,
      d.sigmoid_scale, d.precision) = [int(v) for v in cfg[:10]]
+    if len(cfg) > 12:                      # cfg[11] = dropout probability in ppm, cfg[12] = per-call seed
+        d.p_dropout, d.seed = int(cfg[11]) * 1e-6, int(cfg[12])
     if d.n_layers > GTK_MAX_LAYERS:
         raise RuntimeError(f"glowtts_b200: n_layers {d.n_layers} > {GTK_MAX_LAYERS}")
     return d
+
+
+def draw_seed() -> int:
+    """A fresh dropout seed from torch's CPU generator (reproducible under torch.manual_seed, no device sync)."""
+    return int(torch.randint(0, 2 ** 62, (1,)).item())
+
+
+def dropout_scale(seed: int, block: int, layer: int, p: float, B: int, T: int, C2: int, device) -> Tensor:
+    """The dropout keep-scale (0 or 1/(1-p)) the decoder kernels apply to the in_layer output of (block, layer)
+    (modules.py:153) for per-call seed `seed`, as a [B, C2, T] tensor."""
+    lib = _lib.load()
+    lseed = int(lib.gtk_decoder_layer_seed(int(seed), int(block), int(layer)))
+    out = torch.empty(B, T, C2, dtype=torch.float32, device=device)
+    _lib.call("gtk_dropout_scale", lseed, float(p), out.numel(), _p(out), _stream())
+    return out.transpose(1, 2)
 
 
 def _blocks(cfg: Sequence[int], tensors: Sequence[Optional[Tensor]], cond: Optional[Tensor]):
@@ -724,6 +741,7 @@ def _(dz, dlogdet, mask, flat, offsets, cond, ws, cfg, T):
 
 def _decf_setup(ctx, inputs, output):
     x, mask, flat, offsets, cond, cfg, train = inputs
+    ctx.set_materialize_grads(False)       # the activation workspace output has no gradient: do not zero-fill GBs for it
     ctx.save_for_backward(mask, cond, output[2], flat)
     ctx.cfg, ctx.T, ctx.train, ctx.has_cond, ctx.offsets = list(cfg), x.shape[2], train, cond is not None, list(offsets)
 
@@ -757,6 +775,7 @@ def set_grad_sync(group) -> None:
 
 def _dec_setup(ctx, inputs, output):
     x, mask, params, cond, cfg, train = inputs
+    ctx.set_materialize_grads(False)
     ctx.save_for_backward(mask, cond, output[2], *params)
     ctx.cfg, ctx.T, ctx.train, ctx.has_cond = list(cfg), x.shape[2], train, cond is not None
 

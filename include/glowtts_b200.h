@@ -78,6 +78,11 @@ int gtk_unsqueeze(const float* x, const float* mask, float* out, float* mask_out
 int gtk_gate_fwd(const float* a, const float* b, int cond_mode, float* out, int B, int H, int T, void* stream);
 /* d(a) [B,2H,T] from d(out); d(b) is d(a) (mode 2) or its sum over t (mode 1, use gtk_row_sum). */
 int gtk_gate_bwd(const float* a, const float* b, int cond_mode, const float* dout, float* da, int B, int H, int T, void* stream);
+/* Dropout mask of the decoder kernels (modules.py:120,153): out[i] = keep-scale (0 or 1/(1-p)) of element i of a
+ * [B, T', 2H] frame-major in_layer output for layer seed `seed`; gtk_decoder_layer_seed maps the per-call seed of
+ * gtk_decoder_desc to the seed of (block, layer).  For tests and for the module-level (unfused) WN. */
+int gtk_dropout_scale(unsigned long long seed, float p, long long n, float* out, void* stream);
+unsigned long long gtk_decoder_layer_seed(unsigned long long seed, int block, int layer);
 int gtk_row_sum(const float* in, float* out, int R, int T, int accumulate, void* stream);
 int gtk_channel_sum(const float* in, float* out, int B, int M, int T, int accumulate, void* stream);
 /* commons.mle_loss (commons.py:28-33).  m/logs may be NULL (= 0).  acc4: 4 floats of scratch that
@@ -173,6 +178,11 @@ int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, c
                     float* h_out_f32, void* h_out_bf16, float* skip_f32, void* skip_out_bf16, void* ts_save,
                     void* acts_save, void* stream);
 
+/* Debug: phase timestamps (ns) of the first n_ctas (<= 512) CTAs of the last fused WN-layer launch:
+ * out[cta * 6 + {start, setup done, GEMM1 done, epilogue-1 done, GEMM2 done, end}], cta = batch * tiles + tile.
+ * Synchronises the device. */
+int gtk_debug_wn_trace(unsigned long long* out, int n_ctas);
+
 /* ---- whole decoder (models.py:719-789) --------------------------------------------------- */
 typedef struct gtk_decoder_desc {
     int B;              /* batch */
@@ -187,6 +197,8 @@ typedef struct gtk_decoder_desc {
     int n_split;        /* 4 */
     int sigmoid_scale;  /* 0 */
     int precision;      /* 0: fp32 CUDA-core convolutions (exact-parity path); 1: bf16 tcgen05 path */
+    float p_dropout;    /* nn.Dropout on every WN in_layer output (modules.py:120,153); 0 = off (eval) */
+    unsigned long long seed;   /* per-call dropout seed; decoder_backward must be given the forward's value */
 } gtk_decoder_desc;
 
 /* Parameters of one (ActNorm, InvConvNear, CouplingBlock) triple; state_dict names in comments.

@@ -158,13 +158,17 @@ def invconvnear(x: Tensor, x_mask: Tensor, weight: Tensor, reverse: bool = False
 
 
 def wn(sd: SD, prefix: str, x: Tensor, x_mask: Tensor, g: Optional[Tensor], hidden: int,
-       dilation_rate: int, n_layers: int) -> Tensor:
-    """modules.py:144-171 (dropout inactive: eval / p=0)."""
+       dilation_rate: int, n_layers: int, drop=None) -> Tensor:
+    """modules.py:144-171.  `drop(layer, x_in) -> x_in` stands for self.drop (modules.py:153); None = eval / p=0.
+    The tests pass the keep-mask of the implementation under test, since nn.Dropout's RNG stream is not part of
+    the contract."""
     out = torch.zeros_like(x)
     if g is not None:
         g = _conv(sd, prefix + ".cond_layer", g)
     for i in range(n_layers):
         x_in = _conv(sd, f"{prefix}.in_layers.{i}", x, dilation=dilation_rate**i)
+        if drop is not None:
+            x_in = drop(i, x_in)
         if g is not None:
             g_l = g[:, 2 * hidden * i : 2 * hidden * (i + 1)]
         else:
@@ -204,7 +208,7 @@ def wnp(sd: SD, prefix: str, x: Tensor, x_mask: Tensor, g1: Optional[Tensor], hi
 def coupling(sd: SD, prefix: str, x: Tensor, x_mask: Tensor, *, hidden: int, dilation_rate: int,
              n_layers: int, g: Optional[Tensor] = None, pitch: Optional[Tensor] = None,
              energy: Optional[Tensor] = None, reverse: bool = False, sigmoid_scale: bool = False,
-             n_sqz: int = 2):
+             n_sqz: int = 2, drop=None):
     """attentions.py:132-186."""
     c = x.shape[1]
     x0, x1 = x[:, : c // 2], x[:, c // 2 :]
@@ -213,7 +217,7 @@ def coupling(sd: SD, prefix: str, x: Tensor, x_mask: Tensor, *, hidden: int, dil
     if energy is not None and energy.dim() == 2:
         energy = energy.unsqueeze(1)
     h = _conv(sd, prefix + ".start", x0) * x_mask
-    h = wn(sd, prefix + ".wn", h, x_mask, g, hidden, dilation_rate, n_layers)
+    h = wn(sd, prefix + ".wn", h, x_mask, g, hidden, dilation_rate, n_layers, drop)
     h = wnp(sd, prefix + ".wn_energy", h, x_mask, energy, hidden, dilation_rate, n_layers, n_sqz)
     h = wnp(sd, prefix + ".wn_pitch", h, x_mask, pitch, hidden, dilation_rate, n_layers, n_sqz)
     out = _conv(sd, prefix + ".end", h)
@@ -232,7 +236,7 @@ def coupling(sd: SD, prefix: str, x: Tensor, x_mask: Tensor, *, hidden: int, dil
 def decoder(sd: SD, x: Tensor, x_mask: Tensor, *, hidden: int = 192, dilation_rate: int = 1,
             n_blocks: int = 12, n_layers: int = 4, n_split: int = 4, n_sqz: int = 2,
             sigmoid_scale: bool = False, g: Optional[Tensor] = None, pitch: Optional[Tensor] = None,
-            energy: Optional[Tensor] = None, reverse: bool = False, prefix: str = ""):
+            energy: Optional[Tensor] = None, reverse: bool = False, prefix: str = "", drop=None):
     """models.py:765-785: squeeze -> (ActNorm, InvConvNear, CouplingBlock) x n_blocks ->
     unsqueeze; reversed order with inverse maps and no logdet when reverse=True."""
     if n_sqz > 1:
@@ -246,7 +250,8 @@ def decoder(sd: SD, x: Tensor, x_mask: Tensor, *, hidden: int = 192, dilation_ra
             lambda t: invconvnear(t, x_mask, sd[ic + ".weight"], reverse, n_split),
             lambda t: coupling(sd, cb, t, x_mask, hidden=hidden, dilation_rate=dilation_rate,
                                n_layers=n_layers, g=g, pitch=pitch, energy=energy, reverse=reverse,
-                               sigmoid_scale=sigmoid_scale, n_sqz=n_sqz),
+                               sigmoid_scale=sigmoid_scale, n_sqz=n_sqz,
+                               drop=None if drop is None else (lambda i, v, _b=blk: drop(_b, i, v))),
         ]
         if reverse:
             steps.reverse()

@@ -232,3 +232,82 @@ def test_mle_loss_and_prior_expansion_match_oracle():
     z_m_ref, z_l_ref = oflow.expand_prior(attn.cpu(), x_m, x_m * 2)
     z_m, z_l = commons.expand_prior(x_m.cuda(), (x_m * 2).cuda(), idx)
     assert torch.equal(z_m.cpu(), z_m_ref) and torch.equal(z_l.cpu(), z_l_ref)
+
+
+# ----------------------------------------------------------------------------------------- dropout (modules.py:120,153)
+def _dropout_decoder(cfg, sd, p, precision="fp32"):
+    from glowtts_b200 import models
+    dec = models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"], cfg["dilation_rate"],
+                                 cfg["n_blocks"], cfg["n_layers"], p_dropout=p, n_split=cfg["n_split"],
+                                 n_sqz=cfg["n_sqz"], gin_channels=cfg["gin_channels"], precision=precision)
+    dec.load_state_dict(sd, strict=False)
+    return dec.cuda().train()
+
+
+def test_dropout_mask_statistics_and_determinism():
+    from glowtts_b200 import ops
+    p = 0.05
+    m = ops.dropout_scale(1234, 2, 1, p, 8, 500, 384, "cuda")
+    m2 = ops.dropout_scale(1234, 2, 1, p, 8, 500, 384, "cuda")
+    other = ops.dropout_scale(1234, 2, 2, p, 8, 500, 384, "cuda")
+    assert torch.equal(m, m2)
+    assert not torch.equal(m, other)
+    vals = torch.unique(m).cpu().numpy()
+    thr = round(p * 65536)
+    np.testing.assert_allclose(vals, [0.0, 65536.0 / (65536.0 - thr)], rtol=1e-6)
+    drop_rate = (m == 0).float().mean().item()
+    assert abs(drop_rate - p) < 4 * (p * (1 - p) / m.numel()) ** 0.5 + 1e-5       # 4 sigma
+    assert abs(m.mean().item() - 1.0) < 2e-3                                        # unbiased scaling
+    # per-channel and per-frame rates are flat (no structure along either axis)
+    assert ((m == 0).float().mean(dim=(0, 2)) - p).abs().max().item() < 0.03
+    assert ((m == 0).float().mean(dim=(0, 1)) - p).abs().max().item() < 0.03
+
+
+@pytest.mark.parametrize("use_g", [False, True])
+def test_decoder_dropout_matches_oracle_given_the_mask(use_g):
+    """Training-mode forward/backward with p_dropout > 0 equals the oracle run with the SAME keep-mask (the mask the
+    kernels derive from the per-call seed); eval mode ignores p_dropout."""
+    from glowtts_b200 import ops
+    p = 0.2
+    cfg = dict(helpers.TINY_CFG, n_blocks=2, n_layers=3, hidden_channels=32, gin_channels=5 if use_g else 0)
+    sd = helpers.make_state_dict(cfg, 4242)
+    dec = _dropout_decoder(cfg, sd, p)
+    b, t = 3, 42
+    y, mask, _, cond = helpers.flow_inputs(cfg, b, t, 99, use_g)
+    torch.manual_seed(777)
+    seed = ops.draw_seed()                     # the seed the module will draw next
+    torch.manual_seed(777)
+    yc = y.cuda().requires_grad_(True)
+    condc = None if cond is None else cond.cuda().requires_grad_(True)
+    z, ld = dec(yc, mask.cuda(), g=condc)
+    (z.pow(2).sum() + ld.sum()).backward()
+
+    H2 = 2 * cfg["hidden_channels"]
+    masks = {(blk, i): ops.dropout_scale(seed, blk, i, p, b, t // 2, H2, "cuda").cpu()
+             for blk in range(cfg["n_blocks"]) for i in range(cfg["n_layers"])}
+    assert all((m == 0).any() for m in masks.values())
+    yr = y.clone().requires_grad_(True)
+    condr = None if cond is None else cond.clone().requires_grad_(True)
+    sdr = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    z_ref, ld_ref = oflow.decoder(sdr, yr, mask, g=condr, drop=lambda blk, i, v: v * masks[(blk, i)], **_kw(cfg))
+    (z_ref.pow(2).sum() + ld_ref.sum()).backward()
+    np.testing.assert_allclose(z.detach().cpu().numpy(), z_ref.detach().numpy(), **TOL)
+    np.testing.assert_allclose(ld.detach().cpu().numpy(), ld_ref.detach().numpy(), rtol=1e-4, atol=1e-3)
+    np.testing.assert_allclose(yc.grad.cpu().numpy(), yr.grad.numpy(), rtol=1e-3, atol=1e-5)
+    if use_g:
+        np.testing.assert_allclose(condc.grad.cpu().numpy(), condr.grad.numpy(), rtol=2e-3, atol=2e-5)
+    n = 0
+    for name, prm in dec.named_parameters():
+        if name in sdr and sdr[name].grad is not None:
+            np.testing.assert_allclose(prm.grad.cpu().numpy().reshape(-1), sdr[name].grad.numpy().reshape(-1), rtol=2e-3,
+                                       atol=3e-5, err_msg=name)
+            n += 1
+    assert n > 20
+    # a different call draws a different mask; eval() switches dropout off
+    z2, _ = dec(yc.detach(), mask.cuda(), g=None if condc is None else condc.detach())
+    assert not torch.allclose(z2, z.detach())
+    dec.eval()
+    with torch.no_grad():
+        z_eval, _ = dec(y.cuda(), mask.cuda(), g=None if cond is None else cond.cuda())
+        z_plain, _ = oflow.decoder(sd, y, mask, g=cond, **_kw(cfg))
+    np.testing.assert_allclose(z_eval.cpu().numpy(), z_plain.numpy(), **TOL)

@@ -212,3 +212,47 @@ def test_bf16_decoder_backward_tracks_fp32(name):
             worst = (k, err)
     print(f"{name}: worst relative L2 grad error {worst[1]:.3e} at {worst[0]}; dy {((grads[0]['__dy'] - grads[1]['__dy']).norm() / grads[0]['__dy'].norm()).item():.3e}")
     assert worst[1] < 3e-2
+
+
+@pytest.mark.parametrize("use_g", [False, True])
+def test_bf16_decoder_dropout_matches_fp32_path_with_the_same_seed(use_g):
+    """p_dropout > 0: the tcgen05 path and the fp32 path draw the same keep-mask from the same seed, so forward and
+    gradients agree within the bf16 bound (the dropped elements are exactly the same ones)."""
+    import helpers
+    from glowtts_b200 import models
+    cfg = dict(helpers.TINY_CFG, in_channels=16, n_blocks=2, n_layers=2, hidden_channels=64, gin_channels=4 if use_g else 0)
+    sd = helpers.make_state_dict(cfg, 31)
+    decs = {}
+    for prec in ("fp32", "bf16"):
+        d = models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"], cfg["dilation_rate"],
+                                   cfg["n_blocks"], cfg["n_layers"], p_dropout=0.25, n_split=cfg["n_split"],
+                                   n_sqz=cfg["n_sqz"], gin_channels=cfg["gin_channels"], precision=prec)
+        d.load_state_dict(sd, strict=False)
+        decs[prec] = d.cuda().train()
+    y, mask, _, cond = helpers.flow_inputs(cfg, 3, 300, 5, use_g)
+    res = {}
+    for prec, d in decs.items():
+        torch.manual_seed(2024)
+        yc = y.cuda().requires_grad_(True)
+        cc = None if cond is None else cond.cuda().requires_grad_(True)
+        z, ld = d(yc, mask.cuda(), g=cc)
+        (z.pow(2).mean() + ld.mean() * 1e-3).backward()
+        grads = {n: p.grad.detach().clone() for n, p in d.named_parameters() if p.grad is not None}
+        res[prec] = (z.detach(), ld.detach(), yc.grad.clone(), None if cc is None else cc.grad.clone(), grads)
+    zf, ldf, dyf, dcf, gf = res["fp32"]
+    zb, ldb, dyb, dcb, gb = res["bf16"]
+
+    def rel(a, b):
+        return ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
+    assert rel(zb, zf) < 2e-2, rel(zb, zf)
+    assert rel(ldb, ldf) < 2e-2
+    assert rel(dyb, dyf) < 3e-2, rel(dyb, dyf)
+    if use_g:
+        assert rel(dcb, dcf) < 5e-2, rel(dcb, dcf)
+    worst = max(rel(gb[n], gf[n]) for n in gf if gf[n].norm() > 1e-6)
+    assert worst < 6e-2, worst
+    # the un-dropped forward differs by far more than the bf16 bound: the masks really were applied and shared
+    decs["bf16"].eval()
+    with torch.no_grad():
+        z_eval, _ = decs["bf16"](y.cuda(), mask.cuda(), g=None if cond is None else cond.cuda())
+    assert rel(z_eval, zf) > 3 * rel(zb, zf)
