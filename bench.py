@@ -185,11 +185,8 @@ def timed(fn, steps, world):
         fn()
     e1.record()
     barrier_sync(world)
-    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
-    if world > 1:
-        import torch.distributed as dist
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    return float(ms.item())
+    from glowtts_b200.distributed import max_over_ranks
+    return max_over_ranks(e0.elapsed_time(e1), torch.device("cuda", torch.cuda.current_device()))
 
 
 def mas_alone(device, steps=20):
@@ -366,13 +363,8 @@ def main():
     prof = _lib.prof_read()
     _lib.prof_enable(False)
 
-    frames = torch.tensor([run.frames], device=device, dtype=torch.float64)
-    cells = torch.tensor([run.cells], device=device, dtype=torch.float64)
-    if world > 1:
-        import torch.distributed as dist
-        dist.all_reduce(frames)
-        dist.all_reduce(cells)
-    frames_total, cells_total = float(frames.item()), float(cells.item())
+    from glowtts_b200.distributed import sum_over_ranks
+    frames_total, cells_total = sum_over_ranks(run.frames, device), sum_over_ranks(run.cells, device)
 
     if rank == 0:
         pk = peaks()

@@ -759,9 +759,9 @@ def _decf_bwd(ctx, dz, dlogdet, dws):
     dx, dflat, dcond = decoder_backward_flat(dz.contiguous(), dlogdet.contiguous(), mask, flat, ctx.offsets, cond, ws, ctx.cfg,
                                              ctx.T)
     if _GRAD_SYNC["group"] is not None:
-        import torch.distributed as dist
-        dist.all_reduce(dflat, group=_GRAD_SYNC["group"])
-        dflat.div_(dist.get_world_size(_GRAD_SYNC["group"]))
+        # data-parallel training (train_ms_emo_lang_pitch.py:166 DDP): ONE all-reduce over the flat gradient buffer
+        from .distributed import sync_flat_grad
+        sync_flat_grad(dflat, _GRAD_SYNC["group"])
     return dx, None, dflat, None, (dcond if ctx.has_cond else None), None, None
 
 
@@ -794,9 +794,8 @@ def _dec_bwd(ctx, dz, dlogdet, dws):
     if _GRAD_SYNC["group"] is not None:
         # data-parallel training (train_ms_emo_lang_pitch.py:166 DDP): ONE NCCL all-reduce over the flat
         # gradient buffer the backward kernels wrote, averaged over ranks as DDP does.
-        import torch.distributed as dist
-        dist.all_reduce(flat, group=_GRAD_SYNC["group"])
-        flat.div_(dist.get_world_size(_GRAD_SYNC["group"]))
+        from .distributed import sync_flat_grad
+        sync_flat_grad(flat, _GRAD_SYNC["group"])
     offs, sizes, _ = grad_layout(params)
     grads = [flat[o:o + n].view(p.shape) for o, n, p in zip(offs, sizes, params)]
     return dx, None, grads, (dcond if ctx.has_cond else None), None, None
