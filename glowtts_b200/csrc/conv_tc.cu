@@ -163,7 +163,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                     for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
                 }
-                if (p.out_bf16) store_bf16x16(p.out_bf16 + frame * p.ld_bf16 + c0, v);
+                if (p.out_bf16) {
+                    store_bf16x16(p.out_bf16 + frame * p.ld_bf16 + c0, v);
+                    for (int rp = 1; rp < p.rep_bf16; ++rp)
+                        store_bf16x16(p.out_bf16 + (size_t)rp * p.rep_stride + frame * p.ld_bf16 + c0, v);
+                }
                 if (p.out_tm) {
 #pragma unroll
                     for (int i = 0; i < 16; ++i) p.out_tm[((size_t)b * p.tm_C + p.tm_c0 + c0 + i) * p.T + t] = v[i];

@@ -24,7 +24,7 @@ struct TcLayout {          // byte offsets in the workspace
     TcPack P;
     TcAct A;
     // backward temporaries
-    size_t b_dZ, b_dM, b_dend, b_drs, b_dxin, b_dgate, b_dhf[2], b_dh0, b_wpart;
+    size_t b_dZ, b_dM, b_dend, b_drs, b_dxin, b_lstride, b_dgate, b_dhf[2], b_dh0, b_wpart;   // b_drs / b_dxin: one per layer, b_lstride apart
 };
 
 static int tc_supported(const Dims& D) {
@@ -85,13 +85,14 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
         L->b_dZ = take((size_t)C * nq * 4);
         L->b_dM = take((size_t)C * nq * 4);
         L->b_dend = take((size_t)pad64(C) * nq * 2);
-        L->b_drs = take((size_t)2 * H * nq * 2);
-        L->b_dxin = take((size_t)2 * H * nq * 2);
+        L->b_lstride = align_up((size_t)2 * H * nq * 2, 1024);      // per-layer copies: the grouped weight-gradient
+        L->b_drs = take(L->b_lstride * D.L);                         // launch at the end of the block reads them all
+        L->b_dxin = take(L->b_lstride * D.L);
         L->b_dgate = take((size_t)2 * H * nq * 2);
         L->b_dhf[0] = take((size_t)H * nq * 4);
         L->b_dhf[1] = take((size_t)H * nq * 4);
         L->b_dh0 = take((size_t)H * nq * 2);
-        L->b_wpart = take(tc::wgrad_tc_workspace_bytes());
+        L->b_wpart = take(tc::wgrad_group_workspace_bytes());
     }
     L->total = off;
 }
@@ -271,12 +272,12 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     float* dZ = reinterpret_cast<float*>(ws + L.b_dZ);
     float* dM = reinterpret_cast<float*>(ws + L.b_dM);
     bf16* dend = reinterpret_cast<bf16*>(ws + L.b_dend);
-    bf16* drs = reinterpret_cast<bf16*>(ws + L.b_drs);
-    bf16* dxin = reinterpret_cast<bf16*>(ws + L.b_dxin);
+    auto drs_of = [&](int i) { return reinterpret_cast<bf16*>(ws + L.b_drs + (size_t)i * L.b_lstride); };
+    auto dxin_of = [&](int i) { return reinterpret_cast<bf16*>(ws + L.b_dxin + (size_t)i * L.b_lstride); };
     bf16* dgate = reinterpret_cast<bf16*>(ws + L.b_dgate);
     float* dhf[2] = {reinterpret_cast<float*>(ws + L.b_dhf[0]), reinterpret_cast<float*>(ws + L.b_dhf[1])};
     bf16* dh0 = reinterpret_cast<bf16*>(ws + L.b_dh0);
-    float* dweff = reinterpret_cast<float*>(ws + L.b_wpart);   // split-K partial tiles of the weight gradients
+    float* wpart = reinterpret_cast<float*>(ws + L.b_wpart);   // stream-K partial tiles of the weight gradients
 
     GTK_TRY(flow::squeeze(dz, msq, dZ, nullptr, B, D.Cin, D.Tq * D.n, D.n, 1, st));
 
@@ -293,30 +294,53 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         const bf16* a0 = reinterpret_cast<const bf16*>(act + A.a0);
         const bf16* skip_bf = reinterpret_cast<const bf16*>(act + A.skip_bf);
 
+        // Weight / bias gradients of the whole block are queued here and run as ONE stream-K launch after the
+        // data-gradient chain (which is the critical path and keeps every dY it produced).
+        tc::WgradGroupJob jobs[tc::WGG_MAX_JOBS];
+        int n_jobs = 0, n_tiles = 0;
+        auto flush = [&]() -> int {
+            int rc = n_jobs ? tc::wgrad_group_launch(jobs, n_jobs, B, T, wpart, st) : GTK_OK;
+            n_jobs = 0; n_tiles = 0;
+            return rc;
+        };
+        auto queue = [&](const float* g, const float* v, float* dg, float* dv, float* db, const bf16* dy, int ld_y, int cols_y,
+                         const bf16* x, int ld_x, int cols_x, int M, int Cin, int Kk, int dil) -> int {
+            if (!dv) return db ? tc::colsum_frames(dy, ld_y, M, 1, rows, db, 0, st) : GTK_OK;
+            if (g && !dg) { set_error("decoder_backward(bf16): weight_g gradient pointer missing"); return GTK_ERR_INVALID; }
+            const int tiles = ((M + 127) / 128) * Kk;
+            if (n_jobs == tc::WGG_MAX_JOBS || n_tiles + tiles > tc::WGG_MAX_TILES) GTK_TRY(flush());
+            tc::WgradGroupJob& J = jobs[n_jobs++];
+            n_tiles += tiles;
+            J.dy = dy; J.ld_y = ld_y; J.cols_y = cols_y; J.x = x; J.ld_x = ld_x; J.cols_x = cols_x;
+            J.g = g; J.v = v; J.dg = dg; J.dv = dv; J.db = db; J.M = M; J.Cin = Cin; J.K = Kk; J.dil = dil;
+            return GTK_OK;
+        };
+
         // affine coupling + end conv
         GTK_TRY(tc::affine_bwd_frames(xmix, reinterpret_cast<const float*>(act + A.logs), msq, dZ, dlogdet, dend, ldC, dM, B, C, T,
                                       d->sigmoid_scale, st));
-        GTK_TRY(tc_wgrad_param(nullptr, nullptr, nullptr, G.end_w, dweff, dend, ldC, ldC, skip_bf, H, H, B, T, C, H, 1, 1, st));
-        if (G.end_b) GTK_TRY(tc::colsum_frames(dend, ldC, C, 1, rows, G.end_b, 0, st));
+        GTK_TRY(queue(nullptr, P.end_w, nullptr, G.end_w, G.end_b, dend, ldC, ldC, skip_bf, H, H, C, H, 1, 1));
         {
+            // d(skip) feeds the res_skip gradient of EVERY layer: written into columns [H, 2H) of all per-layer buffers
             tc::ConvTcParams p;
             memset(&p, 0, sizeof(p));
             p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = ldC / 64; p.N = H;
             p.mask = msq; p.mask_out = 1;
-            p.out_bf16 = drs + H; p.ld_bf16 = 2 * H;
+            p.out_bf16 = drs_of(0) + H; p.ld_bf16 = 2 * H;
+            p.rep_bf16 = D.L; p.rep_stride = L.b_lstride / 2;
             GTK_TRY(tc::conv_tc_launch(dend, ldC, pk + Q.t_end, p, tc::EPI_PLAIN, st));
         }
         for (int i = D.L - 1; i >= 0; --i) {
             const int RS = (i < D.L - 1) ? 2 * H : H;
             const int dil = ipow(D.dr, i);
-            const bf16* drs_i = (i < D.L - 1) ? drs : drs + H;          // [dh_{i+1} mask | dskip]  or  dskip
+            const bf16* drs_i = (i < D.L - 1) ? drs_of(i) : drs_of(i) + H;     // [dh_{i+1} mask | dskip]  or  dskip
+            bf16* dxin = dxin_of(i);
             const bf16* ts = reinterpret_cast<const bf16*>(act + A.ts[i]);
             const bf16* acts = reinterpret_cast<const bf16*>(act + A.acts[i]);
             const bf16* h_i = reinterpret_cast<const bf16*>(act + A.h[i]);
             const bool want_dcond = P.cond && G.cond;
-            // res_skip 1x1: parameter gradients, then data gradient fused with the gate backward
-            GTK_TRY(tc_wgrad_param(P.rs_g[i], P.rs_v[i], G.rs_g[i], G.rs_v[i], dweff, drs_i, 2 * H, RS, acts, H, H, B, T, RS, H, 1, 1, st));
-            if (G.rs_b[i]) GTK_TRY(tc::colsum_frames(drs_i, 2 * H, RS, 1, rows, G.rs_b[i], 0, st));
+            // res_skip 1x1: data gradient fused with the gate backward
+            GTK_TRY(queue(P.rs_g[i], P.rs_v[i], G.rs_g[i], G.rs_v[i], G.rs_b[i], drs_i, 2 * H, RS, acts, H, H, RS, H, 1, 1));
             {
                 tc::ConvTcParams p;
                 memset(&p, 0, sizeof(p));
@@ -332,9 +356,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 GTK_TRY(tc::colsum_frames(d->p_dropout > 0.f ? dgate : dxin, 2 * H, 2 * H, B, T, G.cond + (size_t)i * 2 * H,
                                           (size_t)2 * H * D.L, st));
             // in_layer dilated conv
-            GTK_TRY(tc_wgrad_param(P.in_g[i], P.in_v[i], G.in_g[i], G.in_v[i], dweff, dxin, 2 * H, 2 * H, h_i, H, H, B, T, 2 * H, H, K,
-                                   dil, st));
-            if (G.in_b[i]) GTK_TRY(tc::colsum_frames(dxin, 2 * H, 2 * H, 1, rows, G.in_b[i], 0, st));
+            GTK_TRY(queue(P.in_g[i], P.in_v[i], G.in_g[i], G.in_v[i], G.in_b[i], dxin, 2 * H, 2 * H, h_i, H, H, 2 * H, H, K, dil));
             {
                 tc::ConvTcParams p;
                 memset(&p, 0, sizeof(p));
@@ -342,14 +364,13 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 p.mask = msq; p.mask_out = 1;
                 if (i < D.L - 1) { p.resid_f32 = dhf[(i + 1) & 1]; p.ld_resid = H; p.mask_resid = 1; }
                 p.out_f32 = dhf[i & 1]; p.ld_f32 = H;
-                if (i > 0) { p.out_bf16 = drs; p.ld_bf16 = 2 * H; }
+                if (i > 0) { p.out_bf16 = drs_of(i - 1); p.ld_bf16 = 2 * H; }
                 else       { p.out_bf16 = dh0; p.ld_bf16 = H; }
                 GTK_TRY(tc::conv_tc_launch(dxin, 2 * H, pk + Q.t_in[i], p, tc::EPI_PLAIN, st));
             }
         }
         // start conv: h0 = (W x0 + b) * mask   (dh0 is already masked)
-        GTK_TRY(tc_wgrad_param(P.start_g, P.start_v, G.start_g, G.start_v, dweff, dh0, H, H, a0, ldCh, ldCh, B, T, H, Ch, 1, 1, st));
-        if (G.start_b) GTK_TRY(tc::colsum_frames(dh0, H, H, 1, rows, G.start_b, 0, st));
+        GTK_TRY(queue(P.start_g, P.start_v, G.start_g, G.start_v, G.start_b, dh0, H, H, a0, ldCh, ldCh, H, Ch, 1, 1));
         {
             tc::ConvTcParams p;
             memset(&p, 0, sizeof(p));
@@ -357,6 +378,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
             p.resid_tm = dZ; p.out_tm = dM; p.tm_C = C; p.tm_c0 = 0;
             GTK_TRY(tc::conv_tc_launch(dh0, H, pk + Q.t_start, p, tc::EPI_PLAIN, st));
         }
+        GTK_TRY(flush());
         // ActNorm + InvConvNear (fp32)
         GTK_TRY(flow::mix_bwd(xin_blk, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, dM, dZ, G.an_logs, G.an_bias, G.ic_weight, B,
                               C, T, st));

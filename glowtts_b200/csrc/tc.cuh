@@ -32,6 +32,8 @@ struct ConvTcParams {
     int ld_f32;
     __nv_bfloat16* out_bf16;       // frame-major [B, T, ld_bf16] or null (columns N..ld_bf16 are left untouched)
     int ld_bf16;
+    int rep_bf16;                  // > 1: the bf16 output is also written to rep_bf16 - 1 more buffers,
+    size_t rep_stride;             //      rep_stride elements apart (plain epilogue only)
     float* out_tm;                 // t-major [B, tm_C, T]: channel tm_c0 + n, or null
     const float* resid_tm;         // t-major residual added before the store (same indexing), or null
     int tm_C, tm_c0;
@@ -81,6 +83,22 @@ size_t wgrad_tc_workspace_bytes();
 int wgrad_tc_param(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, const float* g,
                    const float* v, float* dg, float* dv, float* part_ws, int B, int T, int M, int Cin, int K, int dil,
                    cudaStream_t st);
+// All weight / bias gradients of one coupling block in one stream-K launch + one reduce launch (wgrad_group.cu).
+constexpr int WGG_MAX_JOBS = 16, WGG_MAX_TILES = 160, WGG_MAX_SEGS = 320, WGG_MAX_CTAS = 160;
+struct WgradGroupJob {
+    const __nv_bfloat16* dy;   // output-gradient frames [B, T, ld_y], columns [0, cols_y) exist, [0, M) are used
+    int ld_y, cols_y;
+    const __nv_bfloat16* x;    // input frames [B, T, ld_x], columns [0, cols_x) exist, [0, Cin) are used
+    int ld_x, cols_x;
+    const float* g;            // weight_g [M] or null (plain weight)
+    const float* v;            // weight_v / weight [M][Cin][K]
+    float* dg;                 // += (weight-normed only)
+    float* dv;                 // +=
+    float* db;                 // += bias gradient [M], or null
+    int M, Cin, K, dil;
+};
+size_t wgrad_group_workspace_bytes();
+int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, cudaStream_t st);
 int colsum_frames(const __nv_bfloat16* in, int ld, int n_cols, int groups, long long rows_per_group, float* out, size_t out_gstride,
                   cudaStream_t st);
 int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, const float* dz, const float* dlogdet,

@@ -1,0 +1,341 @@
+// glowtts_b200/csrc/wgrad_group.cu -- ALL weight and bias gradients of one coupling block in one persistent,
+// stream-K tcgen05 launch + one reduce launch.
+//
+//   dW_q[m][c][j] = sum_{b,t} dY_q[b, t, m] * X_q[b, t + (j - K_q/2) dil_q, c]          for every conv q of the block
+//   db_q[m]       = sum_{b,t} dY_q[b, t, m]                                             (a column of ones appended to X_q)
+//
+// Work = (conv, 128-row M tile, tap) tiles x (utterance, 64-frame chunk) k-steps.  All tiles of all convs are laid
+// end to end (weighted by the bytes one k-step stages) and cut into `grid` equal contiguous shares, one per SM
+// ("stream-K"): no wave quantisation, no per-conv launch, and each CTA writes at most a few partial tiles.  A CTA
+// walks its segments with one TMA producer thread, one MMA thread and four epilogue warps; the two 256-column TMEM
+// accumulators alternate so the drain of one segment overlaps the MMAs of the next.
+//
+// Operands are frame-major bf16 ([B, T, channels]; reduction dim = rows), i.e. MN-major UMMA operands fetched as
+// {64 channels x 64 frames} SWIZZLE_128B boxes, the conv tap being a shifted (zero-filled) box of X -- as in
+// wgrad_tc.cu.  The bias gradient rides along as X block 3 = [1, 0, 0, ...] written once to shared memory.
+// The reduce kernel sums a tile's partial slots and finishes weight norm (dg, dv) and the bias gradient per row.
+#include <string.h>
+
+#include "tc.cuh"
+#include "ops.h"
+
+namespace gtk {
+namespace tc {
+
+constexpr int GG_TK = 64;                        // frames per k-step
+constexpr int GG_BOX = GG_TK * 128;              // bytes of one {64 ch, 64 frames} box
+constexpr int GG_STAGES = 4;
+constexpr int GG_STAGE_BYTES = 6 * GG_BOX;       // 2 dY boxes (128 rows of M) + up to 4 X boxes (N <= 256)
+constexpr int GG_ONES_BLK = 3;                   // X block that holds the ones column (never written by TMA)
+constexpr int GG_SLOT_FLOATS = 128 * 256;        // one partial tile
+
+struct GgJobDev {
+    int taps, dil, n_blk, ones;                  // n_blk = real 64-column blocks of X; ones: bias gradient wanted
+};
+struct GgTile { unsigned char job, m_tile, tap, pad; };
+struct GgSeg { unsigned short tile, s_lo, s_hi, slot; };
+struct GgCta { unsigned short seg0, nseg; };
+
+struct GgParams {
+    int B, T, chunks_t;
+    float* part;                                 // [slots][128][256] fp32
+    GgJobDev job[WGG_MAX_JOBS];
+    GgTile tile[WGG_MAX_TILES];
+    GgSeg seg[WGG_MAX_SEGS];
+    GgCta cta[WGG_MAX_CTAS];
+    CUtensorMap tmY[WGG_MAX_JOBS], tmX[WGG_MAX_JOBS];
+};
+
+struct GgCtl {
+    uint64_t full[GG_STAGES], empty[GG_STAGES], acc_full[2], acc_empty[2];
+    uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_constant__ GgParams p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    GgCtl* ctl = reinterpret_cast<GgCtl*>(smem + (size_t)GG_STAGES * GG_STAGE_BYTES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const GgCta me = p.cta[blockIdx.x];
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < GG_STAGES; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&ctl->acc_full[a], 1); mbar_init(&ctl->acc_empty[a], 4); }
+        mbar_fence_init();
+    }
+    if (warp == 2) tmem_alloc<512>(&ctl->tmem_base);
+    // ones block of every stage: row r (frame) is 128 B = 64 channels, channel 0 sits in 16-byte chunk (0 ^ (r & 7))
+    for (int i = threadIdx.x; i < GG_STAGES * GG_TK * 8; i += NTHREADS) {
+        const int s = i / (GG_TK * 8), r = (i / 8) % GG_TK, ch = i % 8;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (ch == (r & 7)) v.x = 0x3F80u;        // bf16 1.0 in the low half-word = channel 0
+        *reinterpret_cast<uint4*>(smem + (size_t)s * GG_STAGE_BYTES + (2 + GG_ONES_BLK) * GG_BOX + r * 128 + ch * 16) = v;
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = ctl->tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int it = 0;
+            for (int sg = 0; sg < me.nseg; ++sg) {
+                const GgSeg S = p.seg[me.seg0 + sg];
+                const GgTile Tl = p.tile[S.tile];
+                const GgJobDev J = p.job[Tl.job];
+                const CUtensorMap* tmX = &p.tmX[Tl.job];
+                const CUtensorMap* tmY = &p.tmY[Tl.job];
+                const int m0 = Tl.m_tile * 128;
+                const int shift = ((int)Tl.tap - J.taps / 2) * J.dil;
+                const uint32_t bytes = (uint32_t)(2 + J.n_blk) * GG_BOX;
+                for (int step = S.s_lo; step < S.s_hi; ++step, ++it) {
+                    const int s = it % GG_STAGES, use = it / GG_STAGES;
+                    if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
+                    const int b = step / p.chunks_t, t0 = (step % p.chunks_t) * GG_TK;
+                    unsigned char* sa = smem + (size_t)s * GG_STAGE_BYTES;
+                    unsigned char* sb = sa + 2 * GG_BOX;
+                    mbar_arrive_expect_tx(&ctl->full[s], bytes);
+                    tma_load_3d(sa, tmY, &ctl->full[s], m0, t0, b);
+                    tma_load_3d(sa + GG_BOX, tmY, &ctl->full[s], m0 + 64, t0, b);
+                    for (int nb = 0; nb < J.n_blk; ++nb)
+                        tma_load_3d(sb + (size_t)nb * GG_BOX, tmX, &ctl->full[s], nb * 64, t0 + shift, b);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            int it = 0;
+            for (int sg = 0; sg < me.nseg; ++sg) {
+                const GgSeg S = p.seg[me.seg0 + sg];
+                const GgTile Tl = p.tile[S.tile];
+                const GgJobDev J = p.job[Tl.job];
+                const int N = (J.ones && Tl.tap == 0) ? (GG_ONES_BLK + 1) * 64 : J.n_blk * 64;
+                const uint32_t idesc = umma_idesc_bf16(128, N, 1, 1);
+                const int a = sg & 1, ause = sg >> 1;
+                if (ause > 0) { mbar_wait(&ctl->acc_empty[a], (ause - 1) & 1); tc_fence_after(); }
+                const uint32_t acc = tmem + a * 256;
+                for (int step = S.s_lo; step < S.s_hi; ++step, ++it) {
+                    const int s = it % GG_STAGES, use = it / GG_STAGES;
+                    mbar_wait(&ctl->full[s], use & 1);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + (size_t)s * GG_STAGE_BYTES);
+                    const uint32_t sb = sa + 2 * GG_BOX;
+#pragma unroll
+                    for (int k = 0; k < GG_TK / 16; ++k) {
+                        const uint64_t adesc = umma_desc_mnmajor_sw128(sa + k * 2048, GG_BOX, 1024);
+                        const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + k * 2048, GG_BOX, 1024);
+                        umma_bf16(acc, adesc, bdesc, idesc, (step != S.s_lo) || k != 0);
+                    }
+                    umma_commit(&ctl->empty[s]);
+                }
+                umma_commit(&ctl->acc_full[a]);
+            }
+        }
+    } else if (warp >= 4) {
+        const int q = warp & 3;
+        for (int sg = 0; sg < me.nseg; ++sg) {
+            const GgSeg S = p.seg[me.seg0 + sg];
+            const GgTile Tl = p.tile[S.tile];
+            const GgJobDev J = p.job[Tl.job];
+            const int a = sg & 1, ause = sg >> 1;
+            mbar_wait(&ctl->acc_full[a], ause & 1);
+            tc_fence_after();
+            const uint32_t trow = tmem + a * 256 + ((uint32_t)(q * 32) << 16);
+            float* prow = p.part + (size_t)S.slot * GG_SLOT_FLOATS + (size_t)(q * 32 + lane) * 256;
+            for (int c0 = 0; c0 < J.n_blk * 64; c0 += 16) {
+                float v[16];
+                tmem_ld16(trow + c0, v);
+                float4* o4 = reinterpret_cast<float4*>(prow + c0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            }
+            if (J.ones && Tl.tap == 0) {
+                float v[16];
+                tmem_ld16(trow + GG_ONES_BLK * 64, v);
+                prow[GG_ONES_BLK * 64] = v[0];
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ctl->acc_empty[a]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem);
+    }
+}
+
+// ------------------------------------------------------------------------------------------ reduce
+struct GgRedJob {
+    const float* g;            // weight_g [M] or null (plain weight)
+    const float* v;            // weight_v / weight [M][Cin][taps]
+    float* dg;
+    float* dv;
+    float* db;                 // bias gradient [M] or null
+    int M, Cin, taps, tile0, row0, ones;
+};
+struct GgRedParams {
+    const float* part;
+    int n_jobs;
+    GgRedJob job[WGG_MAX_JOBS];
+    unsigned short slot0[WGG_MAX_TILES], nslot[WGG_MAX_TILES];
+};
+
+// One block per output row m of one conv.  Plain weight: dv[m][c][j] += sum.  Weight-normed (torch.nn.utils.weight_norm,
+// modules.py:124,131,141):  dg[m] += <dW_m, v_m>/||v_m||,  dv_m += g_m/||v_m|| (dW_m - v_m <dW_m, v_m>/||v_m||^2).
+__global__ void __launch_bounds__(256) wgrad_group_reduce_kernel(const __grid_constant__ GgRedParams p) {
+    extern __shared__ float row[];                 // [Cin * taps] reduced dW row, torch order (c, j)
+    __shared__ float scratch[33];
+    int q = 0;
+    while (q + 1 < p.n_jobs && (int)blockIdx.x >= p.job[q + 1].row0) ++q;
+    const GgRedJob J = p.job[q];
+    const int m = blockIdx.x - J.row0, R = J.Cin * J.taps;
+    const int m_tile = m >> 7, r = m & 127;
+    float ss = 0.f, dd = 0.f;
+    for (int e = threadIdx.x; e < R; e += 256) {
+        const int j = e / J.Cin, c = e % J.Cin;    // c fastest: coalesced reads of the partial tiles
+        const int tile = J.tile0 + m_tile * J.taps + j;
+        const float* src = p.part + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + (size_t)r * 256 + c;
+        float acc = 0.f;
+        for (int s = 0; s < p.nslot[tile]; ++s) acc += src[(size_t)s * GG_SLOT_FLOATS];
+        row[c * J.taps + j] = acc;
+        if (J.g) {
+            const float t = J.v[(size_t)m * R + c * J.taps + j];
+            ss += t * t;
+            dd += t * acc;
+        }
+    }
+    if (J.db && J.ones && threadIdx.x == 0) {
+        const int tile = J.tile0 + m_tile * J.taps;
+        const float* src = p.part + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + (size_t)r * 256 + GG_ONES_BLK * 64;
+        float acc = 0.f;
+        for (int s = 0; s < p.nslot[tile]; ++s) acc += src[(size_t)s * GG_SLOT_FLOATS];
+        J.db[m] += acc;
+    }
+    __syncthreads();
+    if (!J.g) {
+        for (int e = threadIdx.x; e < R; e += 256) J.dv[(size_t)m * R + e] += row[e];
+        return;
+    }
+    ss = block_sum<256>(ss, scratch);
+    dd = block_sum<256>(dd, scratch);
+    const float nrm = sqrtf(ss);
+    const float sc = J.g[m] / nrm, proj = dd / ss;
+    for (int e = threadIdx.x; e < R; e += 256) J.dv[(size_t)m * R + e] += sc * (row[e] - J.v[(size_t)m * R + e] * proj);
+    if (threadIdx.x == 0) J.dg[m] += dd / nrm;
+}
+
+// ------------------------------------------------------------------------------------------ host
+size_t wgrad_group_workspace_bytes() { return (size_t)(WGG_MAX_CTAS + WGG_MAX_TILES) * GG_SLOT_FLOATS * sizeof(float); }
+
+static int tmap_frames(CUtensorMap* out, const __nv_bfloat16* base, int ld, int cols, int T, int B) {
+    const uint64_t dims[3] = {(uint64_t)cols, (uint64_t)T, (uint64_t)B};
+    const uint64_t strides[2] = {(uint64_t)ld * 2, (uint64_t)ld * 2 * T};
+    const uint32_t box[3] = {64, GG_TK, 1};
+    return make_tmap_bf16(out, base, 3, dims, strides, box, true);
+}
+
+int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, cudaStream_t st) {
+    GTK_REQUIRE(jobs && n_jobs >= 1 && n_jobs <= WGG_MAX_JOBS && part_ws, "bad job list");
+    if ((long long)B * T == 0) return GTK_OK;
+    static thread_local GgParams P;                 // ~12 KB of kernel parameters, rebuilt per launch
+    static thread_local GgRedParams R;
+    memset(&P, 0, sizeof(P));
+    memset(&R, 0, sizeof(R));
+    P.B = B; P.T = T; P.chunks_t = ceil_div(T, GG_TK); P.part = part_ws;
+    R.part = part_ws; R.n_jobs = n_jobs;
+    const int S = B * P.chunks_t;
+    GTK_REQUIRE(S <= 65535, "too many k-steps for the segment table");
+
+    bool ones_ok = true;
+    for (int q = 0; q < n_jobs; ++q) ones_ok = ones_ok && ceil_div(jobs[q].Cin, 64) <= GG_ONES_BLK;
+    int n_tiles = 0, rows = 0;
+    size_t max_row = 0;
+    long long w_tile[WGG_MAX_TILES];
+    for (int q = 0; q < n_jobs; ++q) {
+        const WgradGroupJob& J = jobs[q];
+        GTK_REQUIRE(J.dy && J.x && J.dv && (!J.g || (J.v && J.dg)), "null");
+        GTK_REQUIRE(J.K >= 1 && (J.K & 1) && J.dil >= 1 && J.M >= 1 && J.Cin >= 1 && J.Cin <= 256, "bad conv shape");
+        GTK_REQUIRE(J.ld_y % 8 == 0 && J.ld_x % 8 == 0 && J.cols_x >= J.Cin, "frame pitch");
+        GTK_REQUIRE(J.cols_y >= J.M, "dY columns");
+        GgJobDev& D = P.job[q];
+        D.taps = J.K; D.dil = J.dil; D.n_blk = ceil_div(J.Cin, 64);
+        D.ones = (J.db && ones_ok) ? 1 : 0;
+        int rc = tmap_frames(&P.tmY[q], J.dy, J.ld_y, J.cols_y, T, B);
+        if (rc) return rc;
+        rc = tmap_frames(&P.tmX[q], J.x, J.ld_x, J.cols_x, T, B);
+        if (rc) return rc;
+        GgRedJob& Q = R.job[q];
+        Q.g = J.g; Q.v = J.v; Q.dg = J.dg; Q.dv = J.dv; Q.db = J.db;
+        Q.M = J.M; Q.Cin = J.Cin; Q.taps = J.K; Q.tile0 = n_tiles; Q.row0 = rows; Q.ones = D.ones;
+        rows += J.M;
+        max_row = max(max_row, (size_t)J.Cin * J.K * sizeof(float));
+        const int m_tiles = ceil_div(J.M, 128);
+        GTK_REQUIRE(n_tiles + m_tiles * J.K <= WGG_MAX_TILES && m_tiles <= 255 && J.K <= 255, "too many tiles in one group");
+        for (int mt = 0; mt < m_tiles; ++mt)
+            for (int j = 0; j < J.K; ++j) {
+                GgTile& Tl = P.tile[n_tiles];
+                Tl.job = (unsigned char)q; Tl.m_tile = (unsigned char)mt; Tl.tap = (unsigned char)j;
+                w_tile[n_tiles] = 2 + ((D.ones && j == 0) ? GG_ONES_BLK + 1 : D.n_blk);    // boxes staged per k-step
+                ++n_tiles;
+            }
+    }
+    GTK_REQUIRE(max_row <= 48 * 1024, "weight row too long for the reduce kernel");
+
+    // stream-K cut: tile i covers [pos_i, pos_i + w_i S) on a line of length U; CTA c owns [c U / G, (c+1) U / G)
+    long long U = 0;
+    for (int i = 0; i < n_tiles; ++i) U += w_tile[i] * S;
+    const int G = (int)min((long long)min(sm_count(), WGG_MAX_CTAS), (long long)n_tiles * S);
+    int n_seg = 0, slot = 0, c = 0;
+    long long pos = 0;
+    for (int i = 0; i < n_tiles; ++i) {
+        const long long w = w_tile[i];
+        R.slot0[i] = (unsigned short)slot;
+        int s = 0;
+        while (s < S) {
+            while (c + 1 < G && pos + w * s >= (long long)(c + 1) * U / G) ++c;       // CTA that owns k-step s
+            const long long hi = (c + 1 < G) ? (long long)(c + 1) * U / G : U + w;     // first position it does not own
+            int s_hi = (int)min((long long)S, (hi - pos + w - 1) / w);
+            if (s_hi <= s) s_hi = s + 1;
+            GTK_REQUIRE(n_seg < WGG_MAX_SEGS, "segment table overflow");
+            GgSeg& Sg = P.seg[n_seg];
+            Sg.tile = (unsigned short)i; Sg.s_lo = (unsigned short)s; Sg.s_hi = (unsigned short)s_hi; Sg.slot = (unsigned short)slot;
+            if (P.cta[c].nseg == 0) P.cta[c].seg0 = (unsigned short)n_seg;
+            ++P.cta[c].nseg;
+            ++n_seg; ++slot;
+            s = s_hi;
+        }
+        R.nslot[i] = (unsigned short)(slot - R.slot0[i]);
+        pos += w * S;
+    }
+    GTK_REQUIRE((size_t)slot * GG_SLOT_FLOATS * sizeof(float) <= wgrad_group_workspace_bytes(), "partial workspace");
+
+    const size_t smem = (size_t)GG_STAGES * GG_STAGE_BYTES + sizeof(GgCtl) + 1024;
+    GTK_CUDA(cudaFuncSetAttribute(wgrad_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        ProfScope prof("wgrad_group", st);
+        wgrad_group_kernel<<<G, NTHREADS, smem, st>>>(P);
+        int rc = check_launch("wgrad_group");
+        if (rc) return rc;
+    }
+    {
+        ProfScope prof("wgrad_group_reduce", st);
+        wgrad_group_reduce_kernel<<<rows, 256, max_row, st>>>(R);
+        int rc = check_launch("wgrad_group_reduce");
+        if (rc) return rc;
+    }
+    // bias gradients that could not ride along (Cin > 192): plain column sums
+    for (int q = 0; q < n_jobs; ++q) {
+        const WgradGroupJob& J = jobs[q];
+        if (!J.db || P.job[q].ones) continue;
+        int rc = colsum_frames(J.dy, J.ld_y, J.M, 1, (long long)B * T, J.db, 0, st);
+        if (rc) return rc;
+    }
+    return GTK_OK;
+}
+
+}  // namespace tc
+}  // namespace gtk
