@@ -61,15 +61,17 @@ struct SmemCtl {
 
 template <int TMEM_COLS, int EPI>
 __global__ void __launch_bounds__(NTHREADS, 1)
-conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const ConvTcParams p) {
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmO, const ConvTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     // 1024-byte alignment of the operand tiles (SWIZZLE_128B atoms)
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int stage_bytes = A_BYTES + p.N * KC * 2;
-    SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + (size_t)p.stages * stage_bytes);
+    SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + p.ctl_off);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int t0 = blockIdx.x * BT, b = blockIdx.y;
+    int out_chunks = 0;                                  // staged [128 x 64] bf16 output tiles to TMA-store at the end
     const int n_iter = p.taps * p.n_k;
 
     if (threadIdx.x == 0) {
@@ -132,6 +134,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const float mk = (p.mask && t_ok) ? p.mask[(size_t)b * p.T + t] : 1.f;
         const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
         const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+        RowIo io;
+        io.tp = p.tile_layout; io.tile_id = b * gridDim.x + blockIdx.x; io.r = q * 32 + lane; io.frame = frame;
+        // The operand stages are idle once the accumulator is complete: bf16 outputs that the next kernel reads as TMA
+        // operands are staged there in the SWIZZLE_128B layout and leave as bulk tensor stores (no row-strided stores).
         if constexpr (EPI == EPI_PLAIN) {
             const int nck = p.N / 16;
             for (int cc = half ? (nck + 1) / 2 : 0; cc < (half ? nck : (nck + 1) / 2); ++cc) {
@@ -142,13 +148,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                 for (int i = 0; i < 16; ++i) v[i] += ctl->bias[c0 + i];
                 if (p.resid_f32) {
-                    const float4* r4 = reinterpret_cast<const float4*>(p.resid_f32 + frame * p.ld_resid + c0);
+                    float x[16];
+                    row_load_f32x16(p.resid_f32, p.ld_resid, c0, io, x);
                     const float rm = p.mask_resid ? mk : 1.f;
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const float4 r = r4[i];
-                        v[4 * i] += r.x * rm; v[4 * i + 1] += r.y * rm; v[4 * i + 2] += r.z * rm; v[4 * i + 3] += r.w * rm;
-                    }
+                    for (int i = 0; i < 16; ++i) v[i] += x[i] * rm;
                 }
                 if (p.resid_tm) {
 #pragma unroll
@@ -158,21 +162,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                     for (int i = 0; i < 16; ++i) v[i] *= mk;
                 }
-                if (p.out_f32) {
-                    float4* o4 = reinterpret_cast<float4*>(p.out_f32 + frame * p.ld_f32 + c0);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                }
-                if (p.out_bf16) {
-                    store_bf16x16(p.out_bf16 + frame * p.ld_bf16 + c0, v);
-                    for (int rp = 1; rp < p.rep_bf16; ++rp)
-                        store_bf16x16(p.out_bf16 + (size_t)rp * p.rep_stride + frame * p.ld_bf16 + c0, v);
-                }
+                if (p.out_f32) row_store_f32x16(p.out_f32, p.ld_f32, c0, io, v);
+                if (p.out_bf16) stage_bf16x16_sw128(smem, A_BYTES, io.r, c0, v);
                 if (p.out_tm) {
 #pragma unroll
                     for (int i = 0; i < 16; ++i) p.out_tm[((size_t)b * p.tm_C + p.tm_c0 + c0 + i) * p.T + t] = v[i];
                 }
             }
+            if (p.out_bf16) out_chunks = (p.N + KC - 1) / KC;
         } else if constexpr (EPI == EPI_GATE_BWD) {
             const int H = p.N, nck = H / 16;
             for (int cc = half ? (nck + 1) / 2 : 0; cc < (half ? nck : (nck + 1) / 2); ++cc) {
@@ -181,8 +178,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 tmem_ld16(trow + c0, d);
                 if (!t_ok) continue;
                 float tt[16], ss[16], dt[16], ds[16];
-                load_bf16x16(p.ts + frame * (2 * H) + c0, tt);
-                load_bf16x16(p.ts + frame * (2 * H) + H + c0, ss);
+                row_load_bf16x16(p.ts, 2 * H, c0, io, tt);
+                row_load_bf16x16(p.ts, 2 * H, H + c0, io, ss);
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
                     dt[i] = d[i] * ss[i] * (1.f - tt[i] * tt[i]);
@@ -201,9 +198,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                     for (int i = 0; i < 16; ++i) ds[i] *= sc[i];
                 }
-                store_bf16x16(p.out_bf16 + frame * p.ld_bf16 + c0, dt);
-                store_bf16x16(p.out_bf16 + frame * p.ld_bf16 + H + c0, ds);
+                stage_bf16x16_sw128(smem, A_BYTES, io.r, c0, dt);
+                stage_bf16x16_sw128(smem, A_BYTES, io.r, H + c0, ds);
             }
+            out_chunks = 2 * H / KC;
         } else {   // EPI_AFFINE
             const int Ch = p.N / 2, C = p.N;
             float ld_sum = 0.f;
@@ -243,9 +241,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (lane == 0) atomicAdd(p.aff_logdet + b, ld_sum);
             }
         }
+        if (out_chunks) fence_proxy_async_smem();
         tc_fence_before();
     }
     __syncthreads();
+    if (out_chunks && warp == 1 && lane == 0) {
+        const int reps = p.rep_bf16 > 1 ? p.rep_bf16 : 1;
+        for (int rp = 0; rp < reps; ++rp)
+            for (int ch = 0; ch < out_chunks; ++ch) tma_store_4d(&tmO, smem + (size_t)ch * A_BYTES, ch * KC, t0, b, rp);
+        tma_store_commit();
+        tma_store_wait_read();                           // shared memory must outlive the bulk reads
+    }
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc<TMEM_COLS>(tmem);
@@ -405,7 +411,12 @@ int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, 
 }
 
 // ---------------------------------------------------------------------------------- launcher
-static size_t conv_tc_smem(int N, int stages) { return (size_t)stages * (A_BYTES + (size_t)N * KC * 2) + sizeof(SmemCtl) + 1024; }
+static size_t conv_tc_stage_area(int N, int stages, int out_cols) {
+    const size_t ops = (size_t)stages * (A_BYTES + (size_t)N * KC * 2);
+    const size_t staging = (size_t)ceil_div(out_cols, KC) * A_BYTES;      // bf16 output tiles staged for the TMA stores
+    return ops > staging ? ops : staging;
+}
+static size_t conv_tc_smem(int N, int stages, int out_cols) { return conv_tc_stage_area(N, stages, out_cols) + sizeof(SmemCtl) + 1024; }
 
 // in: frames with row pitch ld_in elements, of which the first p.n_k * 64 columns are the conv's input channels
 // (the weights are packed with exactly that many columns).
@@ -418,13 +429,29 @@ int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, 
     p.NCH = (p.N > 256) ? 2 : 1;
     p.NW = p.N / p.NCH;
     GTK_REQUIRE(p.NW % 16 == 0 && p.NW <= 256, "N chunk must be a multiple of 16");
+    const int out_cols = (epi == EPI_GATE_BWD) ? 2 * p.N : ((epi == EPI_PLAIN && p.out_bf16) ? p.N : 0);
     int stages = 4;
-    while (stages > 2 && conv_tc_smem(p.N, stages) > 200 * 1024) --stages;
+    while (stages > 2 && conv_tc_smem(p.N, stages, out_cols) > 200 * 1024) --stages;
     p.stages = stages;
-    const size_t smem = conv_tc_smem(p.N, stages);
+    p.ctl_off = (int)conv_tc_stage_area(p.N, stages, out_cols);
+    const size_t smem = conv_tc_smem(p.N, stages, out_cols);
     GTK_REQUIRE(smem <= 227 * 1024, "tile does not fit in shared memory");
+    GTK_REQUIRE(!p.tile_layout || ((!p.out_f32 || p.ld_f32 == p.N) && (!p.resid_f32 || p.ld_resid == p.N)),
+                "tile-private layout: row pitch must equal the column count");
 
-    CUtensorMap tmA, tmB;
+    CUtensorMap tmA, tmB, tmO;
+    if (out_cols) {
+        GTK_REQUIRE(p.out_bf16 && p.ld_bf16 % 8 == 0 && p.ld_bf16 >= out_cols, "bf16 output frames: row pitch");
+        const int reps = p.rep_bf16 > 1 ? p.rep_bf16 : 1;
+        const uint64_t dims[4] = {(uint64_t)out_cols, (uint64_t)p.T, (uint64_t)p.B, (uint64_t)reps};
+        const uint64_t strides[3] = {(uint64_t)p.ld_bf16 * 2, (uint64_t)p.ld_bf16 * 2 * p.T,
+                                     reps > 1 ? (uint64_t)p.rep_stride * 2 : (uint64_t)p.ld_bf16 * 2 * p.T * p.B};
+        const uint32_t box[4] = {KC, BT, 1, 1};
+        int rc = make_tmap_bf16(&tmO, p.out_bf16, 4, dims, strides, box, true);
+        if (rc) return rc;
+    } else {
+        memset(&tmO, 0, sizeof(tmO));
+    }
     {
         const uint64_t dims[3] = {(uint64_t)p.n_k * KC, (uint64_t)p.T, (uint64_t)p.B};
         const uint64_t strides[2] = {(uint64_t)ld_in * 2, (uint64_t)ld_in * 2 * p.T};
@@ -445,7 +472,7 @@ int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, 
 #define GTK_TC_LAUNCH(COLS, E)                                                                                       \
     do {                                                                                                             \
         GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<COLS, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        conv_tc_kernel<COLS, E><<<grid, NTHREADS, smem, st>>>(tmA, tmB, p);                                          \
+        conv_tc_kernel<COLS, E><<<grid, NTHREADS, smem, st>>>(tmA, tmB, tmO, p);                                          \
     } while (0)
     if (epi == EPI_PLAIN) { if (p.N > 256) GTK_TC_LAUNCH(512, EPI_PLAIN); else GTK_TC_LAUNCH(256, EPI_PLAIN); }
     else if (epi == EPI_GATE_BWD) { GTK_REQUIRE(p.N <= 256 && p.ts && p.out_bf16, "gate_bwd epilogue arguments"); GTK_TC_LAUNCH(256, EPI_GATE_BWD); }

@@ -37,6 +37,7 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 1024); return o; };
     const size_t nq = D.nq;
+    const size_t nqp = (size_t)D.B * ((D.Tq + 127) / 128) * 128;     // rows of the tile-private buffers (whole 128-frame tiles)
     const int H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
     L->mask_sq = take(nq * 4);
     L->x_len = take((size_t)D.B * 4);
@@ -70,16 +71,16 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     A.xmix = atake((size_t)C * nq * 4);
     A.a0 = atake((size_t)pad64(Ch) * nq * 2);
     for (int i = 0; i < D.L; ++i) A.h[i] = atake((size_t)H * nq * 2);
-    for (int i = 0; i < D.L; ++i) A.ts[i] = atake((size_t)2 * H * nq * 2);
+    for (int i = 0; i < D.L; ++i) A.ts[i] = atake((size_t)2 * H * nqp * 2);     // tile-private layout: whole tiles
     for (int i = 0; i < D.L; ++i) A.acts[i] = atake((size_t)H * nq * 2);
     A.skip_bf = atake((size_t)H * nq * 2);
     A.logs = atake((size_t)Ch * nq * 4);
     A.total = a;
     L->n_act = train ? D.NB : 1;
     L->act = take(a * L->n_act);
-    L->hf[0] = take((size_t)H * nq * 4);
-    L->hf[1] = take((size_t)H * nq * 4);
-    L->skipf = take((size_t)H * nq * 4);
+    L->hf[0] = take((size_t)H * nqp * 4);
+    L->hf[1] = take((size_t)H * nqp * 4);
+    L->skipf = take((size_t)H * nqp * 4);
     L->bwd = off;
     if (train) {
         L->b_dZ = take((size_t)C * nq * 4);
@@ -89,8 +90,8 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
         L->b_drs = take(L->b_lstride * D.L);                         // launch at the end of the block reads them all
         L->b_dxin = take(L->b_lstride * D.L);
         L->b_dgate = take((size_t)2 * H * nq * 2);
-        L->b_dhf[0] = take((size_t)H * nq * 4);
-        L->b_dhf[1] = take((size_t)H * nq * 4);
+        L->b_dhf[0] = take((size_t)H * nqp * 4);
+        L->b_dhf[1] = take((size_t)H * nqp * 4);
         L->b_dh0 = take((size_t)H * nq * 2);
         L->b_wpart = take(tc::wgrad_group_workspace_bytes());
     }
@@ -137,6 +138,7 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
         memset(&p, 0, sizeof(p));
         p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = pad64(Ch) / 64; p.N = H;
         p.bias = P.start_b; p.mask = mask; p.mask_out = 1;
+        p.tile_layout = 1;
         p.out_f32 = hf[0]; p.ld_f32 = H;
         p.out_bf16 = reinterpret_cast<bf16*>(act + A.h[0]); p.ld_bf16 = H;
         GTK_TRY(tc::conv_tc_launch(a0, pad64(Ch), pk + Q.start, p, tc::EPI_PLAIN, st));
@@ -146,6 +148,7 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
         memset(&p, 0, sizeof(p));
         p.B = B; p.T = T; p.H = H; p.RS = (i < D.L - 1) ? 2 * H : H; p.taps = D.K; p.dil = ipow(D.dr, i);
         p.first = (i == 0); p.last = (i == D.L - 1);
+        p.tile_layout = 1;
         p.bias_in = P.in_b[i]; p.bias_rs = P.rs_b[i];
         p.cond = P.cond ? P.cond + (size_t)i * 2 * H : nullptr; p.cond_bstride = (size_t)2 * H * D.L;
         p.mask = mask;
@@ -346,6 +349,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 memset(&p, 0, sizeof(p));
                 p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = pad64(RS) / 64; p.N = H;
                 p.mask = msq;
+                p.tile_layout = 1;
                 p.ts = ts; p.out_bf16 = dxin; p.ld_bf16 = 2 * H;
                 p.drop_p = d->p_dropout; p.drop_seed = drop_layer_seed(d->seed, blk, i);
                 // the conditioning enters after the dropout: with both active keep the un-scaled gate gradient too
@@ -362,6 +366,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 memset(&p, 0, sizeof(p));
                 p.B = B; p.T = T; p.taps = K; p.dil = dil; p.n_k = 2 * H / 64; p.N = H;
                 p.mask = msq; p.mask_out = 1;
+                p.tile_layout = 1;
                 if (i < D.L - 1) { p.resid_f32 = dhf[(i + 1) & 1]; p.ld_resid = H; p.mask_resid = 1; }
                 p.out_f32 = dhf[i & 1]; p.ld_f32 = H;
                 if (i > 0) { p.out_bf16 = drs_of(i - 1); p.ld_bf16 = 2 * H; }

@@ -20,8 +20,10 @@ constexpr int NTHREADS = 256;
 
 struct ConvTcParams {
     int B, T, taps, dil, n_k;      // n_k = padded input channels / 64
+    int tile_layout;               // 1: out_f32 / resid_f32 / ts use the tile-private layout (RowIo); ld = column count
     int N, NW, NCH;                // N = NW * NCH output columns, NW % 16 == 0, NW <= 256
     int stages;
+    int ctl_off;                   // byte offset of the control block behind the operand stages / output staging area
     // ---- plain epilogue: v = acc + bias[n] (+ resid) ; optional mask ; stores
     const float* bias;             // [N] or null
     const float* mask;             // [B, T] or null
@@ -56,6 +58,7 @@ enum { EPI_PLAIN = 0, EPI_GATE_BWD = 1, EPI_AFFINE = 2 };
 // One fused WaveNet layer (wn_tc.cu).  All activations frame-major [B, T, H].
 struct WnLayerParams {
     int B, T, H, RS, taps, dil;
+    int tile_layout;               // 1: h_f32 / h_out_f32 / skip_f32 / ts_save use the tile-private layout (RowIo)
     int first, last;               // first: skip is written, not accumulated; last: RS == H, skip*mask -> skip_out_bf16
     const float* bias_in;          // [2H]
     const float* bias_rs;          // [RS]
@@ -243,6 +246,94 @@ __device__ __forceinline__ void load_bf16x16(const __nv_bfloat16* src, float (&v
         v[2 * i + 1] = __high2float(h);
     }
 }
+
+// ---------------------------------------------------------------------------------- device: epilogue row I/O
+// Tensors that only ever travel between epilogues (fp32 residual / skip masters, the saved tanh|sigmoid pairs, the
+// fp32 data-gradient carry) need no particular layout, only that the thread that owns (tile, row) finds its data.
+// "Tile-private" layout: 16-byte vector v of row r of tile `tile_id` lives at ((tile_id * n_vec + v) * 128 + r) * 16
+// bytes, so the 32 lanes of a warp (32 consecutive rows) move 512 contiguous bytes per instruction instead of 32
+// row-strided 16-byte pieces.  tp == 0 keeps the plain frame-major addressing (standalone C-ABI entry points).
+struct RowIo {
+    int tp;            // 1: tile-private layout, 0: frame-major
+    int tile_id;       // b * tiles_per_utterance + tile
+    int r;             // row inside the tile (== TMEM lane)
+    size_t frame;      // b * T + t (frame-major row)
+};
+__device__ __forceinline__ void row_load_f32x16(const float* base, int ld, int c0, const RowIo& io, float (&v)[16]) {
+    const float4* s;
+    size_t step;
+    if (io.tp) { s = reinterpret_cast<const float4*>(base) + ((size_t)io.tile_id * (ld >> 2) + (c0 >> 2)) * 128 + io.r; step = 128; }
+    else       { s = reinterpret_cast<const float4*>(base + io.frame * ld + c0); step = 1; }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float4 x = s[i * step];
+        v[4 * i] = x.x; v[4 * i + 1] = x.y; v[4 * i + 2] = x.z; v[4 * i + 3] = x.w;
+    }
+}
+__device__ __forceinline__ void row_store_f32x16(float* base, int ld, int c0, const RowIo& io, const float (&v)[16]) {
+    float4* d;
+    size_t step;
+    if (io.tp) { d = reinterpret_cast<float4*>(base) + ((size_t)io.tile_id * (ld >> 2) + (c0 >> 2)) * 128 + io.r; step = 128; }
+    else       { d = reinterpret_cast<float4*>(base + io.frame * ld + c0); step = 1; }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) d[i * step] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+}
+__device__ __forceinline__ void row_load_bf16x16(const __nv_bfloat16* base, int ld, int c0, const RowIo& io, float (&v)[16]) {
+    const uint4* s;
+    size_t step;
+    if (io.tp) { s = reinterpret_cast<const uint4*>(base) + ((size_t)io.tile_id * (ld >> 3) + (c0 >> 3)) * 128 + io.r; step = 128; }
+    else       { s = reinterpret_cast<const uint4*>(base + io.frame * ld + c0); step = 1; }
+    const uint4 a = s[0], b = s[step];
+    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
+        v[2 * i] = __low2float(h);
+        v[2 * i + 1] = __high2float(h);
+    }
+}
+__device__ __forceinline__ void row_store_bf16x16(__nv_bfloat16* base, int ld, int c0, const RowIo& io, const float (&v)[16]) {
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+        w[i] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    uint4* d;
+    size_t step;
+    if (io.tp) { d = reinterpret_cast<uint4*>(base) + ((size_t)io.tile_id * (ld >> 3) + (c0 >> 3)) * 128 + io.r; step = 128; }
+    else       { d = reinterpret_cast<uint4*>(base + io.frame * ld + c0); step = 1; }
+    d[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    d[step] = make_uint4(w[4], w[5], w[6], w[7]);
+}
+// 16 bf16 columns [c0, c0 + 16) of tile row r into a staging area laid out as consecutive [128 rows x 64 columns]
+// SWIZZLE_128B tiles of `tile_stride` bytes (the canonical K-major operand layout == what a TMA store expects).
+__device__ __forceinline__ void stage_bf16x16_sw128(unsigned char* area, size_t tile_stride, int r, int c0, const float (&v)[16]) {
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+        w[i] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    unsigned char* row = area + (size_t)(c0 >> 6) * tile_stride + (size_t)r * 128;
+    const int ci = (c0 & 63) >> 3;
+    *reinterpret_cast<uint4*>(row + ((ci ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+    *reinterpret_cast<uint4*>(row + (((ci + 1) ^ (r & 7)) << 4)) = make_uint4(w[4], w[5], w[6], w[7]);
+}
+// TMA store of one staged [128 x 64] bf16 tile to frames [.., t0 .. t0+128, c0 .. c0+64) of utterance b; rows past the
+// tensor's T extent are clipped by the hardware.
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 
 #endif  // __CUDACC__
 

@@ -186,45 +186,76 @@ struct GgRedParams {
 
 // One block per output row m of one conv.  Plain weight: dv[m][c][j] += sum.  Weight-normed (torch.nn.utils.weight_norm,
 // modules.py:124,131,141):  dg[m] += <dW_m, v_m>/||v_m||,  dv_m += g_m/||v_m|| (dW_m - v_m <dW_m, v_m>/||v_m||^2).
-__global__ void __launch_bounds__(256) wgrad_group_reduce_kernel(const __grid_constant__ GgRedParams p) {
+// The kernel is latency-bound (a few dependent L2 round trips per block), so every thread issues all the loads of its
+// (up to four) row elements -- partial slots four at a time, plus v -- before consuming any of them.
+constexpr int GG_RED_NT = 256;
+__global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __grid_constant__ GgRedParams p) {
     extern __shared__ float row[];                 // [Cin * taps] reduced dW row, torch order (c, j)
-    __shared__ float scratch[33];
+    __shared__ float red[2][GG_RED_NT / 32];
     int q = 0;
     while (q + 1 < p.n_jobs && (int)blockIdx.x >= p.job[q + 1].row0) ++q;
-    const GgRedJob J = p.job[q];
-    const int m = blockIdx.x - J.row0, R = J.Cin * J.taps;
+    const GgRedJob& J = p.job[q];
+    const int m = blockIdx.x - J.row0, Cin = J.Cin, taps = J.taps, R = Cin * taps;
     const int m_tile = m >> 7, r = m & 127;
+    const float* __restrict__ vrow = J.v + (size_t)m * R;
+    float* __restrict__ dvrow = J.dv + (size_t)m * R;
+    const bool wn = J.g != nullptr;
+    const float* part_row = p.part + (size_t)r * 256;
     float ss = 0.f, dd = 0.f;
-    for (int e = threadIdx.x; e < R; e += 256) {
-        const int j = e / J.Cin, c = e % J.Cin;    // c fastest: coalesced reads of the partial tiles
-        const int tile = J.tile0 + m_tile * J.taps + j;
-        const float* src = p.part + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + (size_t)r * 256 + c;
-        float acc = 0.f;
-        for (int s = 0; s < p.nslot[tile]; ++s) acc += src[(size_t)s * GG_SLOT_FLOATS];
-        row[c * J.taps + j] = acc;
-        if (J.g) {
-            const float t = J.v[(size_t)m * R + c * J.taps + j];
-            ss += t * t;
-            dd += t * acc;
+    for (int e0 = threadIdx.x; e0 < R; e0 += 4 * GG_RED_NT) {
+        float acc[4], vv[4];
+        int idx[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int e = e0 + u * GG_RED_NT;
+            acc[u] = 0.f; vv[u] = 0.f; idx[u] = -1;
+            if (e < R) {
+                const int j = e / Cin, c = e - j * Cin;        // c fastest: coalesced reads of the partial tiles
+                const int tile = J.tile0 + m_tile * taps + j;
+                const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + c;
+                const int ns = p.nslot[tile];
+                idx[u] = c * taps + j;
+                if (wn) vv[u] = vrow[idx[u]];
+                for (int s = 0; s < ns; s += 4) {
+                    const float a0 = src[(size_t)s * GG_SLOT_FLOATS];
+                    const float a1 = (s + 1 < ns) ? src[(size_t)(s + 1) * GG_SLOT_FLOATS] : 0.f;
+                    const float a2 = (s + 2 < ns) ? src[(size_t)(s + 2) * GG_SLOT_FLOATS] : 0.f;
+                    const float a3 = (s + 3 < ns) ? src[(size_t)(s + 3) * GG_SLOT_FLOATS] : 0.f;
+                    acc[u] += (a0 + a1) + (a2 + a3);
+                }
+            }
         }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (idx[u] >= 0) {
+                row[idx[u]] = acc[u];
+                ss += vv[u] * vv[u];
+                dd += vv[u] * acc[u];
+            }
     }
-    if (J.db && J.ones && threadIdx.x == 0) {
-        const int tile = J.tile0 + m_tile * J.taps;
-        const float* src = p.part + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + (size_t)r * 256 + GG_ONES_BLK * 64;
+    if (J.db && J.ones && threadIdx.x == GG_RED_NT - 1) {
+        const int tile = J.tile0 + m_tile * taps;
+        const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + GG_ONES_BLK * 64;
         float acc = 0.f;
         for (int s = 0; s < p.nslot[tile]; ++s) acc += src[(size_t)s * GG_SLOT_FLOATS];
         J.db[m] += acc;
     }
+    if (wn) {                                       // both row sums with one barrier pair
+        ss = warp_sum(ss);
+        dd = warp_sum(dd);
+        if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = ss; red[1][threadIdx.x >> 5] = dd; }
+    }
     __syncthreads();
-    if (!J.g) {
-        for (int e = threadIdx.x; e < R; e += 256) J.dv[(size_t)m * R + e] += row[e];
+    if (!wn) {
+        for (int e = threadIdx.x; e < R; e += GG_RED_NT) dvrow[e] += row[e];
         return;
     }
-    ss = block_sum<256>(ss, scratch);
-    dd = block_sum<256>(dd, scratch);
+    ss = 0.f; dd = 0.f;
+#pragma unroll
+    for (int w = 0; w < GG_RED_NT / 32; ++w) { ss += red[0][w]; dd += red[1][w]; }
     const float nrm = sqrtf(ss);
     const float sc = J.g[m] / nrm, proj = dd / ss;
-    for (int e = threadIdx.x; e < R; e += 256) J.dv[(size_t)m * R + e] += sc * (row[e] - J.v[(size_t)m * R + e] * proj);
+    for (int e = threadIdx.x; e < R; e += GG_RED_NT) dvrow[e] += sc * (row[e] - vrow[e] * proj);
     if (threadIdx.x == 0) J.dg[m] += dd / nrm;
 }
 
@@ -323,7 +354,7 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     }
     {
         ProfScope prof("wgrad_group_reduce", st);
-        wgrad_group_reduce_kernel<<<rows, 256, max_row, st>>>(R);
+        wgrad_group_reduce_kernel<<<rows, GG_RED_NT, max_row, st>>>(R);
         int rc = check_launch("wgrad_group_reduce");
         if (rc) return rc;
     }

@@ -45,7 +45,8 @@ __device__ __forceinline__ unsigned long long gtimer() {
 
 __global__ void __launch_bounds__(NTHREADS, 1)
 wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmWin,
-                const __grid_constant__ CUtensorMap tmWrs, const WnLayerParams p) {
+                const __grid_constant__ CUtensorMap tmWrs, const __grid_constant__ CUtensorMap tmActs,
+                const __grid_constant__ CUtensorMap tmOut, const WnLayerParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int H = p.H, H2 = 2 * p.H, RS = p.RS;
@@ -135,6 +136,8 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     const float mk = (p.mask && t_ok) ? p.mask[(size_t)b * p.T + t] : 1.f;
     const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
     const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+    RowIo io;
+    io.tp = p.tile_layout; io.tile_id = b * gridDim.x + blockIdx.x; io.r = r; io.frame = frame;
     const int n_chunks = H / 16;
     const int ch_lo = half ? (n_chunks + 1) / 2 : 0, ch_hi = half ? n_chunks : (n_chunks + 1) / 2;
 
@@ -173,23 +176,13 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
             g[i + 2] = sigmoid_fast(g[i + 2] + cg.z); g[i + 3] = sigmoid_fast(g[i + 3] + cg.w);
         }
         if (p.ts_save && t_ok) {
-            store_bf16x16(p.ts_save + frame * H2 + c0, a);
-            store_bf16x16(p.ts_save + frame * H2 + H + c0, g);
+            row_store_bf16x16(p.ts_save, H2, c0, io, a);
+            row_store_bf16x16(p.ts_save, H2, H + c0, io, g);
         }
 #pragma unroll
         for (int i = 0; i < 16; ++i) a[i] *= g[i];
-        if (p.acts_save && t_ok) store_bf16x16(p.acts_save + frame * H + c0, a);
-        // canonical K-major SWIZZLE_128B: row r at r*128 B, 16-byte chunk index XOR (r % 8)
-        const int kc = c0 / KC, ci = (c0 % KC) / 8;
-        unsigned char* slot = smem + (size_t)((n1 + kc) % WN_STAGES) * stage_bytes + (size_t)r * 128;
-        uint32_t w[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(a[2 * i], a[2 * i + 1]);
-            w[i] = *reinterpret_cast<uint32_t*>(&h2);
-        }
-        *reinterpret_cast<uint4*>(slot + ((ci ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-        *reinterpret_cast<uint4*>(slot + (((ci + 1) ^ (r & 7)) << 4)) = make_uint4(w[4], w[5], w[6], w[7]);
+        // gate output -> A slot of GEMM 2 (canonical K-major SWIZZLE_128B); the same tile is TMA-stored to acts_save
+        stage_bf16x16_sw128(smem + (size_t)((n1 + c0 / KC) % WN_STAGES) * stage_bytes, 0, r, c0 % KC, a);
     }
     fence_proxy_async_smem();
     tc_fence_before();
@@ -217,10 +210,17 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
             }
         }
         umma_commit(&ctl->acc_full);
+        if (p.acts_save) {                               // bf16 gate output for the res_skip weight gradient
+            for (int kc = 0; kc < n_kh; ++kc)
+                tma_store_3d(&tmActs, smem + (size_t)((n1 + kc) % WN_STAGES) * stage_bytes, kc * KC, t0, b);
+            tma_store_commit();
+        }
     }
     __syncwarp();
 
-    // ---- epilogue 2: residual / skip
+    // ---- epilogue 2: residual / skip.  The bf16 operand copy of the result (next layer's input, or the masked WN
+    // output for `end`) is staged in the now idle weight slots and leaves as TMA stores.
+    unsigned char* stage_out = smem + A_BYTES;
     mbar_wait(&ctl->acc_full, 1);
     tc_fence_after();
     WN_TRACE(4);
@@ -235,45 +235,45 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
         }
         if (!t_ok) continue;
         if (RS > H) {
-            const float4* x4 = reinterpret_cast<const float4*>(p.h_f32 + frame * H + c0);
+            float x[16];
+            row_load_f32x16(p.h_f32, H, c0, io, x);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const float4 x = x4[i];
                 const float4 bb = *reinterpret_cast<const float4*>(&ctl->bias_rs[c0 + 4 * i]);
-                v[4 * i] = (v[4 * i] + bb.x + x.x) * mk;
-                v[4 * i + 1] = (v[4 * i + 1] + bb.y + x.y) * mk;
-                v[4 * i + 2] = (v[4 * i + 2] + bb.z + x.z) * mk;
-                v[4 * i + 3] = (v[4 * i + 3] + bb.w + x.w) * mk;
+                v[4 * i] = (v[4 * i] + bb.x + x[4 * i]) * mk;
+                v[4 * i + 1] = (v[4 * i + 1] + bb.y + x[4 * i + 1]) * mk;
+                v[4 * i + 2] = (v[4 * i + 2] + bb.z + x[4 * i + 2]) * mk;
+                v[4 * i + 3] = (v[4 * i + 3] + bb.w + x[4 * i + 3]) * mk;
             }
-            float4* o4 = reinterpret_cast<float4*>(p.h_out_f32 + frame * H + c0);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-            store_bf16x16(p.h_out_bf16 + frame * H + c0, v);
+            row_store_f32x16(p.h_out_f32, H, c0, io, v);
+            stage_bf16x16_sw128(stage_out, stage_bytes, r, c0, v);
         }
         const int bo = (RS > H) ? H : 0;
 #pragma unroll
         for (int i = 0; i < 16; ++i) sk[i] += ctl->bias_rs[bo + c0 + i];
         if (!p.first) {
-            const float4* s4 = reinterpret_cast<const float4*>(p.skip_f32 + frame * H + c0);
+            float x[16];
+            row_load_f32x16(p.skip_f32, H, c0, io, x);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float4 x = s4[i];
-                sk[4 * i] += x.x; sk[4 * i + 1] += x.y; sk[4 * i + 2] += x.z; sk[4 * i + 3] += x.w;
-            }
+            for (int i = 0; i < 16; ++i) sk[i] += x[i];
         }
         if (p.last) {                                     // WN output = skip * mask (modules.py:171), operand of `end`
 #pragma unroll
             for (int i = 0; i < 16; ++i) sk[i] *= mk;
-            store_bf16x16(p.skip_out_bf16 + frame * H + c0, sk);
+            stage_bf16x16_sw128(stage_out, stage_bytes, r, c0, sk);
         } else {
-            float4* o4 = reinterpret_cast<float4*>(p.skip_f32 + frame * H + c0);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) o4[i] = make_float4(sk[4 * i], sk[4 * i + 1], sk[4 * i + 2], sk[4 * i + 3]);
+            row_store_f32x16(p.skip_f32, H, c0, io, sk);
         }
     }
+    fence_proxy_async_smem();
     tc_fence_before();
     WN_TRACE(5);
     __syncthreads();
+    if (warp == 1 && lane == 0) {                         // the thread that also issued the acts stores
+        for (int kc = 0; kc < n_kh; ++kc) tma_store_3d(&tmOut, stage_out + (size_t)kc * stage_bytes, kc * KC, t0, b);
+        tma_store_commit();
+        tma_store_wait_read();                            // shared memory must outlive the bulk reads
+    }
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc<512>(tmem);
@@ -319,12 +319,23 @@ int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, con
         int rc = make_tmap_bf16(&tmWrs, wrs_p, 2, dims, strides, box, true);
         if (rc) return rc;
     }
+    CUtensorMap tmActs, tmOut;
+    {
+        const uint64_t dims[3] = {(uint64_t)H, (uint64_t)p.T, (uint64_t)p.B};
+        const uint64_t strides[2] = {(uint64_t)H * 2, (uint64_t)H * 2 * p.T};
+        const uint32_t box[3] = {KC, BT, 1};
+        __nv_bfloat16* out = p.last ? p.skip_out_bf16 : p.h_out_bf16;
+        int rc = make_tmap_bf16(&tmOut, out, 3, dims, strides, box, true);
+        if (rc) return rc;
+        rc = make_tmap_bf16(&tmActs, p.acts_save ? p.acts_save : out, 3, dims, strides, box, true);
+        if (rc) return rc;
+    }
     const size_t smem = (size_t)WN_STAGES * (A_BYTES + (size_t)2 * H * KC * 2) + sizeof(WnCtl) + 1024;
     GTK_REQUIRE(smem <= 227 * 1024, "tile does not fit in shared memory");
     GTK_CUDA(cudaFuncSetAttribute(wn_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(ceil_div(p.T, BT), p.B);
     ProfScope prof("wn_layer_tc", st);
-    wn_layer_kernel<<<grid, NTHREADS, smem, st>>>(tmH, tmWin, tmWrs, p);
+    wn_layer_kernel<<<grid, NTHREADS, smem, st>>>(tmH, tmWin, tmWrs, tmActs, tmOut, p);
     return check_launch("wn_layer_tc");
 }
 
