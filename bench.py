@@ -130,11 +130,12 @@ def build_decoder(device, precision):
 class Runner:
     """Holds the resident model/optimizer and runs one step, device-resident or end to end."""
 
-    def __init__(self, device, world, precision):
+    def __init__(self, device, world, precision, graph=False):
         from glowtts_b200 import ops
         self.device, self.world = device, world
         self.dec = build_decoder(device, precision)
-        self.opt = torch.optim.AdamW(self.dec.parameters(), lr=1e-4, fused=True)
+        self.opt = torch.optim.AdamW(self.dec.parameters(), lr=1e-4, fused=True, capturable=graph)
+        self.graphed = None
         gen = torch.Generator().manual_seed(SEED + int(os.environ.get("RANK", "0")))
         self.host = synth_batch(B_PER_GPU, gen)
         self.dev = [t.to(device) for t in self.host]
@@ -144,6 +145,13 @@ class Runner:
         if world > 1:
             import torch.distributed as dist
             ops.set_grad_sync(dist.group.WORLD)
+        if graph:
+            from glowtts_b200.hot_path import GraphedTrainStep
+            try:
+                self.graphed = GraphedTrainStep(self.dec, self.opt, self.dev)
+            except Exception as e:                          # e.g. a collective that cannot be captured: launch eagerly
+                print(f"bench.py: CUDA-graph capture failed ({e!r}); falling back to eager launches", file=sys.stderr)
+                self.graphed = None
 
     def step(self, batch):
         from glowtts_b200.hot_path import train_hot_path
@@ -155,11 +163,16 @@ class Runner:
         return out.loss
 
     def step_resident(self):
+        if self.graphed is not None:
+            return self.graphed.step()                     # inputs already in the static device buffers
         return self.step(self.dev)
 
     def step_e2e(self):
-        batch = [t.to(self.device, non_blocking=True) for t in self.host]
-        loss = self.step(batch)
+        if self.graphed is not None:
+            loss = self.graphed.step(self.host)            # pinned host -> static device buffers, then one graph launch
+        else:
+            batch = [t.to(self.device, non_blocking=True) for t in self.host]
+            loss = self.step(batch)
         self.loss_host.copy_(loss.detach(), non_blocking=True)
         return loss
 
@@ -299,12 +312,12 @@ def run_reference(args):
     }))
 
 
-def workload_config(world, precision):
+def workload_config(world, precision, launch="cuda_graph"):
     return {"workload": "Glow-TTS configs/base.json train-step hot path: FlowSpecDecoder(80,192,k5,12 blocks,4 layers,"
                         "n_sqz 2) fwd+bwd + logp + MAS + prior gather + mle_loss + AdamW; synthetic LJSpeech-shaped "
                         "mels, ragged lengths",
             "batch_per_gpu": B_PER_GPU, "global_batch": B_PER_GPU * world, "t_text": T_TEXT, "t_mel": T_MEL,
-            "precision": precision, "p_dropout_dec": CFG["p_dropout_dec"],
+            "precision": precision, "p_dropout_dec": CFG["p_dropout_dec"], "launch": launch,
             "l2": "per-step working set (activation workspace ~2.4 GB) exceeds the 126 MB L2",
             "parallelism": f"dp{world} (batch sharded, one flat-gradient NCCL all-reduce per step)" if world > 1 else "single GPU"}
 
@@ -319,6 +332,8 @@ def main():
     ap.add_argument("--precision", default=os.environ.get("GTK_PRECISION", "bf16"), choices=["fp32", "bf16"],
                     help="bf16 = tcgen05 tensor-core WN path (north_star); fp32 = exact-parity CUDA-core path")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying "
+                    "the captured CUDA graph of the step (hot_path.GraphedTrainStep)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -339,7 +354,7 @@ def main():
 
     from glowtts_b200 import _lib
     _lib.load()
-    run = Runner(device, world, args.precision)
+    run = Runner(device, world, args.precision, graph=not args.no_graph)
 
     for _ in range(args.warmup):
         run.step_e2e()
@@ -351,6 +366,8 @@ def main():
     n0 = _lib.launch_count()
     ms_res = timed(run.step_resident, args.steps, world)
     launches = _lib.launch_count() - n0
+    if run.graphed is not None:                            # replays do not pass through the library's host counter
+        launches = run.graphed.launches * args.steps
     ms_e2e = timed(run.step_e2e, args.steps, world)
     clk = clocks.stop() if rank == 0 else None
 
@@ -358,7 +375,7 @@ def main():
     _lib.prof_enable(True)
     prof_steps = min(args.steps, 3)
     for _ in range(prof_steps):
-        run.step_resident()
+        run.step(run.dev)                                  # eager launches: the event profiler brackets each one
     torch.cuda.synchronize()
     prof = _lib.prof_read()
     _lib.prof_enable(False)
@@ -389,7 +406,7 @@ def main():
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": s_res * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if args.precision == "fp32" else "bf16 (fp32 accumulate)", "data": "synthetic",
-            "config": workload_config(world, args.precision),
+            "config": workload_config(world, args.precision, "cuda_graph" if run.graphed is not None else "eager"),
             "e2e": {"value": frames_total / s_e2e, "unit": "mel frames/s", "ms_per_step": s_e2e * 1e3,
                     "h2d_bytes_per_step": run.h2d_bytes, "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches),

@@ -25,7 +25,8 @@ class DecoderDesc(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int) for n in (
         "B", "in_channels", "T", "n_sqz", "hidden", "kernel_size", "dilation_rate", "n_layers",
         "n_blocks", "n_split", "sigmoid_scale", "precision")] + [("p_dropout", ctypes.c_float),
-                                                                 ("seed", ctypes.c_ulonglong)]
+                                                                 ("seed", ctypes.c_ulonglong),
+                                                                 ("seed_dev", ctypes.c_void_p)]
 
 
 _BLOCK_FIELDS = ("an_logs", "an_bias", "ic_weight", "start_g", "start_v", "start_b",

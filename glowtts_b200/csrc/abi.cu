@@ -150,10 +150,10 @@ int gtk_unsqueeze(const float* x, const float* mask, float* out, float* mask_out
     return flow::unsqueeze(x, mask, out, mask_out, B, C, T, n_sqz, 0, ST);
 }
 int gtk_gate_fwd(const float* a, const float* b, int cond_mode, float* out, int B, int H, int T, void* stream) {
-    return flow::gate_fwd(a, b, cond_mode, 0, out, B, H, T, 0.f, 0ull, ST);
+    return flow::gate_fwd(a, b, cond_mode, 0, out, B, H, T, 0.f, DropSeed{0ull, nullptr}, ST);
 }
 int gtk_gate_bwd(const float* a, const float* b, int cond_mode, const float* dout, float* da, int B, int H, int T, void* stream) {
-    return flow::gate_bwd(a, b, cond_mode, 0, dout, da, B, H, T, 0.f, 0ull, 1, ST);
+    return flow::gate_bwd(a, b, cond_mode, 0, dout, da, B, H, T, 0.f, DropSeed{0ull, nullptr}, 1, ST);
 }
 int gtk_dropout_scale(unsigned long long seed, float p, long long n, float* out, void* stream) {
     return flow::dropout_scale(seed, p, n, out, ST);
@@ -272,6 +272,8 @@ int gtk_tc_colsum(const void* in_bf16, int ld, int n_cols, int groups, long long
     return tc::colsum_frames(static_cast<const __nv_bfloat16*>(in_bf16), ld, n_cols, groups, rows_per_group, out, out_gstride, ST);
 }
 int gtk_debug_wn_trace(unsigned long long* out, int n_ctas) { return tc::wn_trace_read(out, n_ctas); }
+int gtk_debug_conv_trace_select(int epilogue, int taps) { tc::conv_trace_select(epilogue, taps); return GTK_OK; }
+int gtk_debug_conv_trace(unsigned long long* out, int n_ctas) { return tc::conv_trace_read(out, n_ctas); }
 int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, const void* wrs_p, const float* bias_in,
                     const float* bias_rs, const float* cond, size_t cond_bstride, const float* mask, int B, int T, int H,
                     int RS, int K, int dil, int first, int last, float drop_p, unsigned long long drop_seed,
@@ -281,7 +283,7 @@ int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, c
     memset(&p, 0, sizeof(p));
     p.B = B; p.T = T; p.H = H; p.RS = RS; p.taps = K; p.dil = dil; p.first = first; p.last = last;
     p.bias_in = bias_in; p.bias_rs = bias_rs; p.cond = cond; p.cond_bstride = cond_bstride; p.mask = mask;
-    p.drop_p = drop_p; p.drop_seed = drop_seed;
+    p.drop_p = drop_p; p.drop_seed.value = drop_seed; p.drop_seed.dev = nullptr;
     p.h_f32 = h_f32; p.h_out_f32 = h_out_f32; p.h_out_bf16 = static_cast<__nv_bfloat16*>(h_out_bf16);
     p.skip_f32 = skip_f32; p.skip_out_bf16 = static_cast<__nv_bfloat16*>(skip_out_bf16);
     p.ts_save = static_cast<__nv_bfloat16*>(ts_save); p.acts_save = static_cast<__nv_bfloat16*>(acts_save);

@@ -160,5 +160,21 @@ __device__ __forceinline__ void dropout_scale16(unsigned long long seed, unsigne
 __host__ __device__ __forceinline__ unsigned long long drop_layer_seed(unsigned long long seed, int blk, int layer) {
     return drop_hash(seed ^ 0xD6E8FEB86659FD93ull, (unsigned long long)blk * 64ull + (unsigned long long)layer);
 }
+// The per-call seed may live in device memory (gtk_decoder_desc.seed_dev: CUDA-graph replays then see a fresh seed
+// without re-capturing).  Kernels take (value, dev): dev == null -> value is the layer seed; otherwise value is the
+// layer's salt blk * 64 + layer and the layer seed is derived on the device from *dev.
+struct DropSeed {
+    unsigned long long value;
+    const unsigned long long* dev;
+};
+inline DropSeed make_drop_seed(unsigned long long call_seed, const unsigned long long* dev, int blk, int layer) {
+    DropSeed s;
+    s.dev = dev;
+    s.value = dev ? (unsigned long long)blk * 64ull + (unsigned long long)layer : drop_layer_seed(call_seed, blk, layer);
+    return s;
+}
+__device__ __forceinline__ unsigned long long drop_resolve(const DropSeed& s) {
+    return s.dev ? drop_hash(*s.dev ^ 0xD6E8FEB86659FD93ull, s.value) : s.value;
+}
 
 }  // namespace gtk

@@ -59,6 +59,22 @@ struct SmemCtl {
     alignas(16) float bias[512];        // [N] (zeros when there is none)
 };
 
+// Phase timestamps (globaltimer, ns) per CTA of the last launch selected with conv_trace_select():
+// [start, setup done, accumulator complete, epilogue math done, stores issued].  Read with gtk_debug_conv_trace.
+constexpr int CONV_TRACE_CTAS = 512;
+__device__ unsigned long long g_conv_trace[CONV_TRACE_CTAS * 5];
+static int g_trace_epi = -1, g_trace_taps = -1;
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define CONV_TRACE(i)                                                                                       \
+    do {                                                                                                    \
+        const int cta_ = blockIdx.y * gridDim.x + blockIdx.x;                                               \
+        if (p.trace && threadIdx.x == 128 && cta_ < CONV_TRACE_CTAS) g_conv_trace[cta_ * 5 + (i)] = gtimer(); \
+    } while (0)
+
 template <int TMEM_COLS, int EPI>
 __global__ void __launch_bounds__(NTHREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -72,6 +88,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int t0 = blockIdx.x * BT, b = blockIdx.y;
     int out_chunks = 0;                                  // staged [128 x 64] bf16 output tiles to TMA-store at the end
+    CONV_TRACE(0);
     const int n_iter = p.taps * p.n_k;
 
     if (threadIdx.x == 0) {
@@ -85,6 +102,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = ctl->tmem_base;
+    CONV_TRACE(1);
 
     if (warp == 0) {
         if (lane == 0) {
@@ -128,6 +146,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     {   // epilogue: ALL 8 warps; warp w owns TMEM lane quarter w % 4 (frames) and column half w / 4
         mbar_wait(&ctl->acc_full, 0);
         tc_fence_after();
+        CONV_TRACE(2);
         const int q = warp & 3, half = warp >> 2;
         const int t = t0 + q * 32 + lane;
         const bool t_ok = t < p.T;
@@ -172,6 +191,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (p.out_bf16) out_chunks = (p.N + KC - 1) / KC;
         } else if constexpr (EPI == EPI_GATE_BWD) {
             const int H = p.N, nck = H / 16;
+            const unsigned long long dseed = p.drop_p > 0.f ? drop_resolve(p.drop_seed) : 0ull;
             for (int cc = half ? (nck + 1) / 2 : 0; cc < (half ? nck : (nck + 1) / 2); ++cc) {
                 const int c0 = cc * 16;
                 float d[16];
@@ -191,10 +211,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
                 if (p.drop_p > 0.f) {
                     float sc[16];
-                    dropout_scale16(p.drop_seed, (unsigned long long)frame * (2 * H) + c0, p.drop_p, sc);
+                    dropout_scale16(dseed, (unsigned long long)frame * (2 * H) + c0, p.drop_p, sc);
 #pragma unroll
                     for (int i = 0; i < 16; ++i) dt[i] *= sc[i];
-                    dropout_scale16(p.drop_seed, (unsigned long long)frame * (2 * H) + H + c0, p.drop_p, sc);
+                    dropout_scale16(dseed, (unsigned long long)frame * (2 * H) + H + c0, p.drop_p, sc);
 #pragma unroll
                     for (int i = 0; i < 16; ++i) ds[i] *= sc[i];
                 }
@@ -244,6 +264,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (out_chunks) fence_proxy_async_smem();
         tc_fence_before();
     }
+    CONV_TRACE(3);
     __syncthreads();
     if (out_chunks && warp == 1 && lane == 0) {
         const int reps = p.rep_bf16 > 1 ? p.rep_bf16 : 1;
@@ -252,10 +273,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tma_store_commit();
         tma_store_wait_read();                           // shared memory must outlive the bulk reads
     }
+    CONV_TRACE(4);
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc<TMEM_COLS>(tmem);
     }
+}
+
+void conv_trace_select(int epi, int taps) { g_trace_epi = epi; g_trace_taps = taps; }
+int conv_trace_read(unsigned long long* out, int n_ctas) {
+    GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= CONV_TRACE_CTAS, "n_ctas");
+    GTK_CUDA(cudaMemcpyFromSymbol(out, g_conv_trace, size_t(n_ctas) * 5 * sizeof(unsigned long long)));
+    return GTK_OK;
 }
 
 // ---------------------------------------------------------------------------------- helpers: packing / layout
@@ -468,6 +497,7 @@ int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, 
         if (rc) return rc;
     }
     dim3 grid(ceil_div(p.T, BT), p.B);
+    p.trace = (epi == g_trace_epi && p.taps == g_trace_taps) ? 1 : 0;
     ProfScope prof(p.taps > 1 ? "conv_tc_kN" : "conv_tc_k1", st);
 #define GTK_TC_LAUNCH(COLS, E)                                                                                       \
     do {                                                                                                             \

@@ -163,7 +163,7 @@ static int check_block(const Dims& D, const gtk_block_params& P) {
 
 // start -> WN -> end of one coupling block on xc[:, :C/2]; leaves end_out in act.a_end (attentions.py:151-170).
 static int coupling_net(const Dims& D, const Layout& L, const gtk_block_params& P, const float* we, const float* xc,
-                        const float* mask, float* act, float* rs, float* wp, float drop_p, unsigned long long seed, int blk,
+                        const float* mask, float* act, float* rs, float* wp, const gtk_decoder_desc* d, int blk,
                         cudaStream_t st) {
     const int B = D.B, T = D.Tq, H = D.H, C = D.C, Ch = D.C / 2;
     const size_t cbs = (size_t)C * T;
@@ -175,7 +175,7 @@ static int coupling_net(const Dims& D, const Layout& L, const gtk_block_params& 
         GTK_TRY(conv(act + L.a_h[i], 0, wp, P.in_b[i], mask, nullptr, 0, act + L.a_xin[i], 0, B, H, 2 * H, T, D.K,
                      ipow(D.dr, i), 0, 0, 0, st));
         GTK_TRY(flow::gate_fwd(act + L.a_xin[i], P.cond ? P.cond + (size_t)i * 2 * H : nullptr, P.cond ? 1 : 0,
-                               (size_t)2 * H * D.L, act + L.a_acts[i], B, H, T, drop_p, drop_layer_seed(seed, blk, i), st));
+                               (size_t)2 * H * D.L, act + L.a_acts[i], B, H, T, d->p_dropout, make_drop_seed(d->seed, d->seed_dev, blk, i), st));
         GTK_TRY(conv::pack_weight(w_rs(L, P, we, i), wp, RS, H, 1, 0, st));
         GTK_TRY(conv(act + L.a_acts[i], 0, wp, P.rs_b[i], mask, nullptr, 0, rs, 0, B, H, RS, T, 1, 1, 0, 0, 0, st));
         GTK_TRY(flow::resskip(rs, act + L.a_h[i], mask, (i < D.L - 1) ? act + L.a_h[i + 1] : nullptr, act + L.a_skip, B, H, RS,
@@ -227,7 +227,7 @@ int forward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const flo
         GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, icld, st));
         GTK_TRY(flow::mix(xin, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, act + L.a_xmix, D.B, D.C, D.Tq, 0, st));
         GTK_TRY(flow::logdet_const(P.an_logs, D.C, icld, (float)(D.C / D.NS), ws + L.x_len, logdet, D.B, 1, st));
-        GTK_TRY(coupling_net(D, L, P, we, act + L.a_xmix, msq, act, ws + L.rs, ws + L.wp, d->p_dropout, d->seed, blk, st));
+        GTK_TRY(coupling_net(D, L, P, we, act + L.a_xmix, msq, act, ws + L.rs, ws + L.wp, d, blk, st));
         GTK_TRY(flow::affine(act + L.a_xmix, act + L.a_end, msq, xout, logdet, D.B, D.C, D.Tq, 0, d->sigmoid_scale, st));
     }
     const float* xfin = ws + L.X + (size_t)(train ? D.NB : (D.NB & 1)) * xsz;
@@ -260,7 +260,7 @@ int reverse(const gtk_decoder_desc* d, const gtk_block_params* blocks, const flo
         float* winv = ws + L.winv + (size_t)blk * 64;
         GTK_TRY(fold_weights(D, L, P, we, st));
         GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, nullptr, st));
-        GTK_TRY(coupling_net(D, L, P, we, xa, msq, act, ws + L.rs, ws + L.wp, d->p_dropout, d->seed, blk, st));
+        GTK_TRY(coupling_net(D, L, P, we, xa, msq, act, ws + L.rs, ws + L.wp, d, blk, st));
         GTK_TRY(flow::affine(xa, act + L.a_end, msq, xb, nullptr, D.B, D.C, D.Tq, 1, d->sigmoid_scale, st));
         GTK_TRY(flow::mix(xb, msq, P.an_logs, P.an_bias, winv, D.NS, xa, D.B, D.C, D.Tq, 1, st));
     }

@@ -100,14 +100,14 @@ int backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gt
             GTK_TRY(conv::pack_weight(w_rs(L, P, we, i), wp, RS, H, 1, 1, st));
             GTK_TRY(conv(drs, 0, wp, nullptr, msq, nullptr, 0, dacts, 0, B, RS, H, T, 1, 1, 0, 0, 0, st));
             const float* cond_i = P.cond ? P.cond + (size_t)i * 2 * H : nullptr;
-            const unsigned long long lseed = drop_layer_seed(d->seed, blk, i);
+            const DropSeed lseed = make_drop_seed(d->seed, d->seed_dev, blk, i);
             if (P.cond && G.cond) {
                 // the conditioning enters after the dropout: its gradient is the un-scaled gate gradient
                 if (d->p_dropout > 0.f)
                     GTK_TRY(flow::gate_bwd(act + L.a_xin[i], cond_i, 1, (size_t)2 * H * D.L, dacts, dxin, B, H, T, d->p_dropout,
                                            lseed, 0, st));
                 else
-                    GTK_TRY(flow::gate_bwd(act + L.a_xin[i], cond_i, 1, (size_t)2 * H * D.L, dacts, dxin, B, H, T, 0.f, 0ull, 1, st));
+                    GTK_TRY(flow::gate_bwd(act + L.a_xin[i], cond_i, 1, (size_t)2 * H * D.L, dacts, dxin, B, H, T, 0.f, DropSeed{0ull, nullptr}, 1, st));
                 GTK_TRY(flow::row_sum(dxin, G.cond + (size_t)i * 2 * H, B * 2 * H, T, 1, 2 * H, (size_t)2 * H * D.L, st));
             }
             if (!(P.cond && G.cond) || d->p_dropout > 0.f)

@@ -152,7 +152,7 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
         p.bias_in = P.in_b[i]; p.bias_rs = P.rs_b[i];
         p.cond = P.cond ? P.cond + (size_t)i * 2 * H : nullptr; p.cond_bstride = (size_t)2 * H * D.L;
         p.mask = mask;
-        p.drop_p = d->p_dropout; p.drop_seed = drop_layer_seed(d->seed, blk, i);
+        p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, i);
         p.h_f32 = hf[i & 1]; p.h_out_f32 = hf[(i + 1) & 1];
         p.h_out_bf16 = (i < D.L - 1) ? reinterpret_cast<bf16*>(act + A.h[i + 1]) : nullptr;
         p.skip_f32 = skipf;
@@ -351,7 +351,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 p.mask = msq;
                 p.tile_layout = 1;
                 p.ts = ts; p.out_bf16 = dxin; p.ld_bf16 = 2 * H;
-                p.drop_p = d->p_dropout; p.drop_seed = drop_layer_seed(d->seed, blk, i);
+                p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, i);
                 // the conditioning enters after the dropout: with both active keep the un-scaled gate gradient too
                 if (want_dcond && d->p_dropout > 0.f) p.out2_bf16 = dgate;
                 GTK_TRY(tc::conv_tc_launch(drs_i, 2 * H, pk + Q.t_rs[i], p, tc::EPI_GATE_BWD, st));

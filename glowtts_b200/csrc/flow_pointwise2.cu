@@ -60,7 +60,8 @@ int actnorm_ddi_finalize(const float* stats, float* logs, float* bias, int C, cu
 // ------------------------------------------------------------------------------------------ gate
 // cond_mode: 0 none, 1 cond[B,2H] broadcast over t, 2 cond[B,2H,T]
 __global__ void gate_fwd_kernel(const float* __restrict__ a, const float* __restrict__ cond, int cond_mode, size_t cbs,
-                                float* __restrict__ out, int B, int H, int T, float drop_p, unsigned long long seed) {
+                                float* __restrict__ out, int B, int H, int T, float drop_p, DropSeed dseed) {
+    const unsigned long long seed = drop_p > 0.f ? drop_resolve(dseed) : 0ull;
     const long long total = (long long)B * H * T;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int t = (int)(i % T);
@@ -81,7 +82,8 @@ __global__ void gate_fwd_kernel(const float* __restrict__ a, const float* __rest
 // scale_out = 1: da = d(in_layer output) (dropout-scaled); 0: da = d(gate pre-activation) (what the conditioning sees).
 __global__ void gate_bwd_kernel(const float* __restrict__ a, const float* __restrict__ cond, int cond_mode, size_t cbs,
                                 const float* __restrict__ dout, float* __restrict__ da, int B, int H, int T, float drop_p,
-                                unsigned long long seed, int scale_out) {
+                                DropSeed dseed, int scale_out) {
+    const unsigned long long seed = drop_p > 0.f ? drop_resolve(dseed) : 0ull;
     const long long total = (long long)B * H * T;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int t = (int)(i % T);
@@ -105,7 +107,7 @@ __global__ void gate_bwd_kernel(const float* __restrict__ a, const float* __rest
     }
 }
 int gate_fwd(const float* a, const float* cond, int cond_mode, size_t cond_bstride, float* out, int B, int H, int T,
-             float drop_p, unsigned long long seed, cudaStream_t st) {
+             float drop_p, DropSeed seed, cudaStream_t st) {
     if (cond_bstride == 0) cond_bstride = 2 * (size_t)H;
     GTK_REQUIRE(a && out && (cond_mode == 0 || cond), "bad args");
     GTK_REQUIRE(drop_p >= 0.f && drop_p < 1.f, "dropout probability");
@@ -115,7 +117,7 @@ int gate_fwd(const float* a, const float* cond, int cond_mode, size_t cond_bstri
     return check_launch("gate_fwd");
 }
 int gate_bwd(const float* a, const float* cond, int cond_mode, size_t cond_bstride, const float* dout, float* da, int B, int H,
-             int T, float drop_p, unsigned long long seed, int scale_out, cudaStream_t st) {
+             int T, float drop_p, DropSeed seed, int scale_out, cudaStream_t st) {
     if (cond_bstride == 0) cond_bstride = 2 * (size_t)H;
     GTK_REQUIRE(a && dout && da && (cond_mode == 0 || cond), "bad args");
     GTK_REQUIRE(drop_p >= 0.f && drop_p < 1.f, "dropout probability");

@@ -35,9 +35,9 @@ int logdet_const_bwd(const float* dlogdet, const float* x_len, int B, float* dlo
 int actnorm_ddi_stats(const float* x, const float* mask, float* stats, int B, int C, int T, cudaStream_t st);
 int actnorm_ddi_finalize(const float* stats, float* logs, float* bias, int C, cudaStream_t st);
 int gate_fwd(const float* a, const float* cond, int cond_mode, size_t cond_bstride, float* out, int B, int H, int T,
-             float drop_p, unsigned long long seed, cudaStream_t st);
+             float drop_p, DropSeed seed, cudaStream_t st);
 int gate_bwd(const float* a, const float* cond, int cond_mode, size_t cond_bstride, const float* dout, float* da, int B, int H,
-             int T, float drop_p, unsigned long long seed, int scale_out, cudaStream_t st);
+             int T, float drop_p, DropSeed seed, int scale_out, cudaStream_t st);
 int dropout_scale(unsigned long long seed, float p, long long n, float* out, cudaStream_t st);
 int row_sum(const float* in, float* out, int R, int T, int accumulate, int rows_per_group, size_t out_group_stride,
             cudaStream_t st);

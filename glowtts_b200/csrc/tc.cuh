@@ -23,6 +23,7 @@ struct ConvTcParams {
     int tile_layout;               // 1: out_f32 / resid_f32 / ts use the tile-private layout (RowIo); ld = column count
     int N, NW, NCH;                // N = NW * NCH output columns, NW % 16 == 0, NW <= 256
     int stages;
+    int trace;                     // 1: record per-CTA phase timestamps (conv_trace_select)
     int ctl_off;                   // byte offset of the control block behind the operand stages / output staging area
     // ---- plain epilogue: v = acc + bias[n] (+ resid) ; optional mask ; stores
     const float* bias;             // [N] or null
@@ -44,7 +45,7 @@ struct ConvTcParams {
     const __nv_bfloat16* ts;
     __nv_bfloat16* out2_bf16;
     float drop_p;                  // dropout probability on the conv output (modules.py:153); 0 = off
-    unsigned long long drop_seed;  // element (b, t, n) of this layer keeps iff hash(seed, index) >= p
+    DropSeed drop_seed;            // layer seed (or its salt + the device address of the call seed), common.cuh
     // ---- EPI_AFFINE (N = C, attentions.py:172-183): acc = [m | logs]; x / z t-major [B, C, T]
     const float* aff_x;
     float* aff_z;
@@ -66,7 +67,7 @@ struct WnLayerParams {
     size_t cond_bstride;
     const float* mask;             // [B, T]
     float drop_p;
-    unsigned long long drop_seed;
+    DropSeed drop_seed;
     const float* h_f32;            // layer input (fp32 master copy) -- the bf16 copy is the TMA operand
     float* h_out_f32;              // next layer's input (not last)
     __nv_bfloat16* h_out_bf16;
@@ -79,6 +80,8 @@ int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, con
                     cudaStream_t st);
 
 int wn_trace_read(unsigned long long* out, int n_ctas);
+void conv_trace_select(int epi, int taps);
+int conv_trace_read(unsigned long long* out, int n_ctas);
 
 int wgrad_tc_launch(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, float* dw, int B,
                     int T, int M, int Cin, int K, int dil, cudaStream_t st);

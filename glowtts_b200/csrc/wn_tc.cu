@@ -142,6 +142,7 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     const int ch_lo = half ? (n_chunks + 1) / 2 : 0, ch_hi = half ? n_chunks : (n_chunks + 1) / 2;
 
     // ---- epilogue 1: gate -> A operand of GEMM 2
+    const unsigned long long dseed = p.drop_p > 0.f ? drop_resolve(p.drop_seed) : 0ull;
     mbar_wait(&ctl->acc_full, 0);
     tc_fence_after();
     WN_TRACE(2);
@@ -159,10 +160,10 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
         }
         if (p.drop_p > 0.f) {
             float sc[16];
-            dropout_scale16(p.drop_seed, (unsigned long long)frame * H2 + c0, p.drop_p, sc);
+            dropout_scale16(dseed, (unsigned long long)frame * H2 + c0, p.drop_p, sc);
 #pragma unroll
             for (int i = 0; i < 16; ++i) a[i] *= sc[i];
-            dropout_scale16(p.drop_seed, (unsigned long long)frame * H2 + H + c0, p.drop_p, sc);
+            dropout_scale16(dseed, (unsigned long long)frame * H2 + H + c0, p.drop_p, sc);
 #pragma unroll
             for (int i = 0; i < 16; ++i) g[i] *= sc[i];
         }

@@ -16,7 +16,7 @@ from typing import NamedTuple, Optional
 
 import torch
 
-from . import commons, ops
+from . import _lib, commons, ops
 
 
 class HotPathOut(NamedTuple):
@@ -54,3 +54,58 @@ def train_hot_path(decoder, y, y_lengths, x_m, x_logs, x_lengths, g=None, return
     z_logs = None if x_logs is None else ops.gather_tokens(x_logs, idx, T_y)
     loss = commons.mle_loss(z, z_m, z_logs, logdet, z_mask)
     return HotPathOut(loss, z, logdet, attn if return_attn else None, dur, idx)
+
+
+class GraphedTrainStep:
+    """One training step of the hot path (forward, backward, optimizer) captured as a CUDA graph for fixed shapes.
+
+    The step is ~330 kernel launches of 5-70 us each: replayed as one graph the host cost is a single launch, so
+    the GPU never waits for the Python / driver launch path.  Everything the step needs is graph-safe by
+    construction: no host synchronisation anywhere on the path, the dropout seed lives (and advances) on the
+    device, the flat parameter / gradient buffers keep their addresses.  Inputs are copied into static device
+    buffers before each replay (`step(batch)`), so any batch of the captured shape can be fed.
+
+        stepper = GraphedTrainStep(decoder, optimizer, example_batch)   # optimizer: capturable (e.g. fused AdamW)
+        loss = stepper.step((y, y_lengths, x_m, x_lengths))             # host (pinned) or device tensors
+
+    Batches of another shape need another instance (bucket by padded length, as the reference's bucket sampler
+    already does: data_utils.py DistributedBucketSampler).
+    """
+
+    def __init__(self, decoder, optimizer, example_batch, x_logs=None, g=None, warmup: int = 3):
+        dev = next(decoder.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("glowtts_b200.GraphedTrainStep: the decoder must live on a CUDA device")
+        self.decoder, self.optimizer = decoder, optimizer
+        self.static = [t.to(dev, copy=True) for t in example_batch]
+        self.x_logs = None if x_logs is None else x_logs.to(dev, copy=True)
+        self.g = None if g is None else g.to(dev, copy=True)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):                      # warm-up off the capture: allocations, flat buffers, seed state
+            for _ in range(max(1, warmup)):
+                self._eager()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        self.optimizer.zero_grad(set_to_none=True)
+        n0 = _lib.launch_count()
+        with torch.cuda.graph(self.graph):
+            self.out = self._eager()
+        self.launches = _lib.launch_count() - n0           # library kernels per replay
+
+    def _eager(self) -> HotPathOut:
+        y, y_len, x_m, x_len = self.static
+        self.optimizer.zero_grad(set_to_none=True)
+        out = train_hot_path(self.decoder, y, y_len, x_m, self.x_logs, x_len, self.g)
+        out.loss.backward()
+        self.optimizer.step()
+        return out
+
+    def step(self, batch=None) -> torch.Tensor:
+        """Copy `batch` (same shapes as the example) into the static buffers, replay, return the (static) loss tensor."""
+        if batch is not None:
+            for dst, src in zip(self.static, batch):
+                dst.copy_(src, non_blocking=True)
+        self.graph.replay()
+        return self.out.loss

@@ -42,13 +42,37 @@ class FlowSpecDecoder(nn.Module):
 
     # ---------------------------------------------------------------- fused call plumbing
     def _cfg(self, folded: bool):
-        # nn.Dropout(p_dropout) on the WN in_layer outputs (modules.py:120,153) is active in training mode only; the
-        # per-call seed comes from torch's CPU generator, so torch.manual_seed makes runs reproducible.
+        # nn.Dropout(p_dropout) on the WN in_layer outputs (modules.py:120,153) is active in training mode only.
         drop = self.training and self.p_dropout > 0
         return [self.in_channels, self.n_sqz, self.hidden_channels, self.kernel_size, self.dilation_rate,
                 self.n_layers, self.n_blocks, self.n_split, int(bool(self.sigmoid_scale)),
                 {"fp32": 0, "bf16": 1}[self.precision], int(folded),
-                int(round(self.p_dropout * 1e6)) if drop else 0, ops.draw_seed() if drop else 0]
+                int(round(self.p_dropout * 1e6)) if drop else 0, 0]
+
+    _SEED_STEP = 0x9E3779B97F4A7C15 - (1 << 64)      # odd 64-bit increment (as a signed int64)
+
+    def _next_seed(self, device):
+        """Per-call dropout seed as a one-element int64 DEVICE tensor.  The state starts from torch's CPU generator
+        (torch.manual_seed reproducibility) and advances on the device, so no call synchronises the host and a
+        captured CUDA graph of the step draws a fresh mask at every replay."""
+        if not (self.training and self.p_dropout > 0):
+            return None
+        st = getattr(self, "_drop_state", None)
+        if st is None or st.device != device:
+            st = torch.tensor([ops.draw_seed()], dtype=torch.int64).to(device)
+            self._drop_state = st
+        seed = st.clone()
+        st.add_(self._SEED_STEP)
+        return seed
+
+    def peek_dropout_seed(self, device=None) -> int:
+        """The seed the next training forward will use (synchronises; for tests and debugging)."""
+        st = getattr(self, "_drop_state", None)
+        if st is None:
+            dev = device or next(self.parameters()).device
+            st = torch.tensor([ops.draw_seed()], dtype=torch.int64).to(dev)
+            self._drop_state = st
+        return int(st.item()) & 0xFFFFFFFFFFFFFFFF
 
     def _params(self):
         out, folded = [], None
@@ -74,15 +98,16 @@ class FlowSpecDecoder(nn.Module):
         mask2 = x_mask.reshape(x_mask.shape[0], x_mask.shape[-1]).to(torch.float32)
         cond = self._cond(g)
         cfg = self._cfg(folded)
+        seed = self._next_seed(x.device)
         if reverse:
             with torch.no_grad():
-                return ops.decoder_reverse(x, mask2, [p.detach() for p in params], cond, cfg), None
+                return ops.decoder_reverse(x, mask2, [p.detach() for p in params], cond, cfg, seed), None
         train = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params))
         if train and not folded and all(p.requires_grad for p in params):
             flat, offsets = self._ensure_flat(params)
-            z, logdet, _ = ops.decoder_forward_flat(x, mask2, flat, offsets, cond, cfg, True)
+            z, logdet, _ = ops.decoder_forward_flat(x, mask2, flat, offsets, cond, cfg, True, seed)
         else:
-            z, logdet, _ = ops.decoder_forward(x, mask2, params, cond, cfg, train)
+            z, logdet, _ = ops.decoder_forward(x, mask2, params, cond, cfg, train, seed)
         return z, logdet
 
     # ---------------------------------------------------------------- flat parameter storage (training)

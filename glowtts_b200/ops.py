@@ -515,13 +515,17 @@ def params_per_block(n_layers: int, wn_folded: bool) -> int:
     return (7 + 4 * n_layers) if wn_folded else (8 + 6 * n_layers)
 
 
-def _desc(cfg: Sequence[int], B: int, T: int) -> DecoderDesc:
+def _desc(cfg: Sequence[int], B: int, T: int, seed: Optional[Tensor] = None) -> DecoderDesc:
     d = DecoderDesc()
     d.B, d.T = B, T
     (d.in_channels, d.n_sqz, d.hidden, d.kernel_size, d.dilation_rate, d.n_layers, d.n_blocks, d.n_split,
      d.sigmoid_scale, d.precision) = [int(v) for v in cfg[:10]]
-    if len(cfg) > 12:                      # cfg[11] = dropout probability in ppm, cfg[12] = per-call seed
-        d.p_dropout, d.seed = int(cfg[11]) * 1e-6, int(cfg[12])
+    if len(cfg) > 12:                      # cfg[11] = dropout probability in ppm, cfg[12] = per-call seed (host value)
+        d.p_dropout, d.seed = int(cfg[11]) * 1e-6, int(cfg[12]) & 0xFFFFFFFFFFFFFFFF
+    if seed is not None:                   # device-resident per-call seed (CUDA-graph friendly); overrides cfg[12]
+        if seed.dtype != torch.int64 or seed.numel() != 1 or not seed.is_cuda:
+            raise RuntimeError("glowtts_b200: dropout seed must be a one-element int64 CUDA tensor")
+        d.seed_dev = seed.data_ptr()
     if d.n_layers > GTK_MAX_LAYERS:
         raise RuntimeError(f"glowtts_b200: n_layers {d.n_layers} > {GTK_MAX_LAYERS}")
     return d
@@ -536,7 +540,7 @@ def dropout_scale(seed: int, block: int, layer: int, p: float, B: int, T: int, C
     """The dropout keep-scale (0 or 1/(1-p)) the decoder kernels apply to the in_layer output of (block, layer)
     (modules.py:153) for per-call seed `seed`, as a [B, C2, T] tensor."""
     lib = _lib.load()
-    lseed = int(lib.gtk_decoder_layer_seed(int(seed), int(block), int(layer)))
+    lseed = int(lib.gtk_decoder_layer_seed(int(seed) & 0xFFFFFFFFFFFFFFFF, int(block), int(layer)))
     out = torch.empty(B, T, C2, dtype=torch.float32, device=device)
     _lib.call("gtk_dropout_scale", lseed, float(p), out.numel(), _p(out), _stream())
     return out.transpose(1, 2)
@@ -590,7 +594,7 @@ def _chk_list(ts: Sequence[Tensor], name: str) -> List[Tensor]:
 
 @torch.library.custom_op(f"{NS}::decoder_forward", mutates_args=(), device_types="cuda")
 def decoder_forward(x: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], cfg: List[int],
-                    train: bool) -> Tuple[Tensor, Tensor, Tensor]:
+                    train: bool, seed: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
     """FlowSpecDecoder.forward(reverse=False) (models.py:765-785).  x [B,in,T], mask [B,T], cond [NB,B,2H*L] or None
     -> (z [B,in,(T//n)*n], logdet [B], workspace kept for the backward)."""
     x = _chk(x, "x")
@@ -598,7 +602,7 @@ def decoder_forward(x: Tensor, mask: Tensor, params: List[Tensor], cond: Optiona
     mask = _chk(_fit_mask(mask, T), "mask")
     params = _chk_list(params, "params")
     cond = _opt(cond, "cond")
-    d = _desc(cfg, B, T)
+    d = _desc(cfg, B, T, seed)
     lib = _lib.load()
     ws_bytes = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), int(train))
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
@@ -614,21 +618,22 @@ def decoder_forward(x: Tensor, mask: Tensor, params: List[Tensor], cond: Optiona
 
 
 @decoder_forward.register_fake
-def _(x, mask, params, cond, cfg, train):
+def _(x, mask, params, cond, cfg, train, seed=None):
     B, Cin, T = x.shape
     n = cfg[1]
     return x.new_empty((B, Cin, (T // n) * n)), x.new_empty((B,)), x.new_empty((0,), dtype=torch.uint8)
 
 
 @torch.library.custom_op(f"{NS}::decoder_reverse", mutates_args=(), device_types="cuda")
-def decoder_reverse(z: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], cfg: List[int]) -> Tensor:
+def decoder_reverse(z: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], cfg: List[int],
+                    seed: Optional[Tensor] = None) -> Tensor:
     """FlowSpecDecoder.forward(reverse=True) (models.py:765-785)."""
     z = _chk(z, "z")
     B, Cin, T = z.shape
     mask = _chk(_fit_mask(mask, T), "mask")
     params = _chk_list(params, "params")
     cond = _opt(cond, "cond")
-    d = _desc(cfg, B, T)
+    d = _desc(cfg, B, T, seed)
     lib = _lib.load()
     ws_bytes = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), 0)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=z.device)
@@ -640,7 +645,7 @@ def decoder_reverse(z: Tensor, mask: Tensor, params: List[Tensor], cond: Optiona
 
 
 @decoder_reverse.register_fake
-def _(z, mask, params, cond, cfg):
+def _(z, mask, params, cond, cfg, seed=None):
     B, Cin, T = z.shape
     n = cfg[1]
     return z.new_empty((B, Cin, (T // n) * n))
@@ -648,13 +653,13 @@ def _(z, mask, params, cond, cfg):
 
 @torch.library.custom_op(f"{NS}::decoder_backward", mutates_args=(), device_types="cuda")
 def decoder_backward(dz: Tensor, dlogdet: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], ws: Tensor,
-                     cfg: List[int], T: int) -> Tuple[Tensor, Tensor, Tensor]:
+                     cfg: List[int], T: int, seed: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
     """Backward of decoder_forward(train=True) -> (dx [B,in,T], flat parameter grads (see grad_layout), dcond)."""
     dz, dlogdet, mask = _chk(dz, "dz"), _chk(dlogdet, "dlogdet"), _chk(_fit_mask(mask, T), "mask")
     params = _chk_list(params, "params")
     cond = _opt(cond, "cond")
     B, Cin = dz.shape[0], dz.shape[1]
-    d = _desc(cfg, B, T)
+    d = _desc(cfg, B, T, seed)
     dx = torch.empty(B, Cin, T, dtype=dz.dtype, device=dz.device)
     # one flat zero-initialised gradient buffer, viewed per parameter (one memset instead of ~430)
     offs, sizes, tot = grad_layout(params)
@@ -669,7 +674,7 @@ def decoder_backward(dz: Tensor, dlogdet: Tensor, mask: Tensor, params: List[Ten
 
 
 @decoder_backward.register_fake
-def _(dz, dlogdet, mask, params, cond, ws, cfg, T):
+def _(dz, dlogdet, mask, params, cond, ws, cfg, T, seed=None):
     return (dz.new_empty((dz.shape[0], dz.shape[1], T)), dz.new_empty((grad_layout(params)[2],)),
             torch.empty_like(cond) if cond is not None else dz.new_empty(0))
 
@@ -685,14 +690,14 @@ def _flat_ptrs(flat: Tensor, offsets: Sequence[int]) -> List[int]:
 
 @torch.library.custom_op(f"{NS}::decoder_forward_flat", mutates_args=(), device_types="cuda")
 def decoder_forward_flat(x: Tensor, mask: Tensor, flat: Tensor, offsets: List[int], cond: Optional[Tensor], cfg: List[int],
-                         train: bool) -> Tuple[Tensor, Tensor, Tensor]:
+                         train: bool, seed: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
     """decoder_forward with the parameters given as one flat buffer + element offsets (same order as `params`)."""
     x = _chk(x, "x")
     B, Cin, T = x.shape
     mask = _chk(_fit_mask(mask, T), "mask")
     flat = _chk(flat, "flat")
     cond = _opt(cond, "cond")
-    d = _desc(cfg, B, T)
+    d = _desc(cfg, B, T, seed)
     lib = _lib.load()
     ws_bytes = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), int(train))
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
@@ -708,7 +713,7 @@ def decoder_forward_flat(x: Tensor, mask: Tensor, flat: Tensor, offsets: List[in
 
 
 @decoder_forward_flat.register_fake
-def _(x, mask, flat, offsets, cond, cfg, train):
+def _(x, mask, flat, offsets, cond, cfg, train, seed=None):
     B, Cin, T = x.shape
     n = cfg[1]
     return x.new_empty((B, Cin, (T // n) * n)), x.new_empty((B,)), x.new_empty((0,), dtype=torch.uint8)
@@ -716,13 +721,13 @@ def _(x, mask, flat, offsets, cond, cfg, train):
 
 @torch.library.custom_op(f"{NS}::decoder_backward_flat", mutates_args=(), device_types="cuda")
 def decoder_backward_flat(dz: Tensor, dlogdet: Tensor, mask: Tensor, flat: Tensor, offsets: List[int], cond: Optional[Tensor],
-                          ws: Tensor, cfg: List[int], T: int) -> Tuple[Tensor, Tensor, Tensor]:
+                          ws: Tensor, cfg: List[int], T: int, seed: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
     """-> (dx, d flat (same layout as flat), dcond)."""
     dz, dlogdet, mask = _chk(dz, "dz"), _chk(dlogdet, "dlogdet"), _chk(_fit_mask(mask, T), "mask")
     flat = _chk(flat, "flat")
     cond = _opt(cond, "cond")
     B, Cin = dz.shape[0], dz.shape[1]
-    d = _desc(cfg, B, T)
+    d = _desc(cfg, B, T, seed)
     dx = torch.empty(B, Cin, T, dtype=dz.dtype, device=dz.device)
     dflat = torch.zeros_like(flat)
     dcond = torch.zeros_like(cond) if cond is not None else dz.new_empty(0)
@@ -734,22 +739,22 @@ def decoder_backward_flat(dz: Tensor, dlogdet: Tensor, mask: Tensor, flat: Tenso
 
 
 @decoder_backward_flat.register_fake
-def _(dz, dlogdet, mask, flat, offsets, cond, ws, cfg, T):
+def _(dz, dlogdet, mask, flat, offsets, cond, ws, cfg, T, seed=None):
     return (dz.new_empty((dz.shape[0], dz.shape[1], T)), torch.empty_like(flat),
             torch.empty_like(cond) if cond is not None else dz.new_empty(0))
 
 
 def _decf_setup(ctx, inputs, output):
-    x, mask, flat, offsets, cond, cfg, train = inputs
+    x, mask, flat, offsets, cond, cfg, train, seed = inputs
     ctx.set_materialize_grads(False)       # the activation workspace output has no gradient: do not zero-fill GBs for it
-    ctx.save_for_backward(mask, cond, output[2], flat)
+    ctx.save_for_backward(mask, cond, output[2], flat, seed)
     ctx.cfg, ctx.T, ctx.train, ctx.has_cond, ctx.offsets = list(cfg), x.shape[2], train, cond is not None, list(offsets)
 
 
 def _decf_bwd(ctx, dz, dlogdet, dws):
     if not ctx.train:
         raise RuntimeError("glowtts_b200: decoder_forward was run with train=False; no activations were kept")
-    mask, cond, ws, flat = ctx.saved_tensors
+    mask, cond, ws, flat, seed = ctx.saved_tensors
     B = mask.shape[0]
     if dz is None:
         Tz = (ctx.T // ctx.cfg[1]) * ctx.cfg[1]
@@ -757,12 +762,12 @@ def _decf_bwd(ctx, dz, dlogdet, dws):
     if dlogdet is None:
         dlogdet = torch.zeros(B, dtype=mask.dtype, device=mask.device)
     dx, dflat, dcond = decoder_backward_flat(dz.contiguous(), dlogdet.contiguous(), mask, flat, ctx.offsets, cond, ws, ctx.cfg,
-                                             ctx.T)
+                                             ctx.T, seed)
     if _GRAD_SYNC["group"] is not None:
         # data-parallel training (train_ms_emo_lang_pitch.py:166 DDP): ONE all-reduce over the flat gradient buffer
         from .distributed import sync_flat_grad
         sync_flat_grad(dflat, _GRAD_SYNC["group"])
-    return dx, None, dflat, None, (dcond if ctx.has_cond else None), None, None
+    return dx, None, dflat, None, (dcond if ctx.has_cond else None), None, None, None
 
 
 
@@ -774,23 +779,23 @@ def set_grad_sync(group) -> None:
 
 
 def _dec_setup(ctx, inputs, output):
-    x, mask, params, cond, cfg, train = inputs
+    x, mask, params, cond, cfg, train, seed = inputs
     ctx.set_materialize_grads(False)
-    ctx.save_for_backward(mask, cond, output[2], *params)
+    ctx.save_for_backward(mask, cond, output[2], seed, *params)
     ctx.cfg, ctx.T, ctx.train, ctx.has_cond = list(cfg), x.shape[2], train, cond is not None
 
 
 def _dec_bwd(ctx, dz, dlogdet, dws):
     if not ctx.train:
         raise RuntimeError("glowtts_b200: decoder_forward was run with train=False; no activations were kept")
-    mask, cond, ws, *params = ctx.saved_tensors
+    mask, cond, ws, seed, *params = ctx.saved_tensors
     B = mask.shape[0]
     if dz is None:
         Tz = (ctx.T // ctx.cfg[1]) * ctx.cfg[1]
         dz = torch.zeros(B, ctx.cfg[0], Tz, dtype=mask.dtype, device=mask.device)
     if dlogdet is None:
         dlogdet = torch.zeros(B, dtype=mask.dtype, device=mask.device)
-    dx, flat, dcond = decoder_backward(dz.contiguous(), dlogdet.contiguous(), mask, list(params), cond, ws, ctx.cfg, ctx.T)
+    dx, flat, dcond = decoder_backward(dz.contiguous(), dlogdet.contiguous(), mask, list(params), cond, ws, ctx.cfg, ctx.T, seed)
     if _GRAD_SYNC["group"] is not None:
         # data-parallel training (train_ms_emo_lang_pitch.py:166 DDP): ONE NCCL all-reduce over the flat
         # gradient buffer the backward kernels wrote, averaged over ranks as DDP does.
@@ -798,7 +803,7 @@ def _dec_bwd(ctx, dz, dlogdet, dws):
         sync_flat_grad(flat, _GRAD_SYNC["group"])
     offs, sizes, _ = grad_layout(params)
     grads = [flat[o:o + n].view(p.shape) for o, n, p in zip(offs, sizes, params)]
-    return dx, None, grads, (dcond if ctx.has_cond else None), None, None
+    return dx, None, grads, (dcond if ctx.has_cond else None), None, None, None
 
 
 decoder_forward.register_autograd(_dec_bwd, setup_context=_dec_setup)

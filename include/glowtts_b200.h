@@ -182,6 +182,11 @@ int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, c
  * out[cta * 6 + {start, setup done, GEMM1 done, epilogue-1 done, GEMM2 done, end}], cta = batch * tiles + tile.
  * Synchronises the device. */
 int gtk_debug_wn_trace(unsigned long long* out, int n_ctas);
+/* Debug: the same for the plain tcgen05 conv kernel.  Select which launches record (epilogue 0 plain / 1 gate-bwd /
+ * 2 affine, and the tap count; -1 = none), run, then read out[cta * 5 + {start, setup done, accumulator complete,
+ * epilogue math done, stores issued}] of the last selected launch.  Synchronises the device. */
+int gtk_debug_conv_trace_select(int epilogue, int taps);
+int gtk_debug_conv_trace(unsigned long long* out, int n_ctas);
 
 /* ---- whole decoder (models.py:719-789) --------------------------------------------------- */
 typedef struct gtk_decoder_desc {
@@ -199,6 +204,9 @@ typedef struct gtk_decoder_desc {
     int precision;      /* 0: fp32 CUDA-core convolutions (exact-parity path); 1: bf16 tcgen05 path */
     float p_dropout;    /* nn.Dropout on every WN in_layer output (modules.py:120,153); 0 = off (eval) */
     unsigned long long seed;   /* per-call dropout seed; decoder_backward must be given the forward's value */
+    const unsigned long long* seed_dev;   /* if not NULL the per-call seed is read from this DEVICE address by the
+                                           * kernels instead (`seed` is ignored): a captured CUDA graph then picks up a
+                                           * fresh seed on every replay */
 } gtk_decoder_desc;
 
 /* Parameters of one (ActNorm, InvConvNear, CouplingBlock) triple; state_dict names in comments.

@@ -275,8 +275,7 @@ def test_decoder_dropout_matches_oracle_given_the_mask(use_g):
     b, t = 3, 42
     y, mask, _, cond = helpers.flow_inputs(cfg, b, t, 99, use_g)
     torch.manual_seed(777)
-    seed = ops.draw_seed()                     # the seed the module will draw next
-    torch.manual_seed(777)
+    seed = dec.peek_dropout_seed()             # the seed the next training forward uses (device-resident state)
     yc = y.cuda().requires_grad_(True)
     condc = None if cond is None else cond.cuda().requires_grad_(True)
     z, ld = dec(yc, mask.cuda(), g=condc)

@@ -232,7 +232,7 @@ def test_bf16_decoder_dropout_matches_fp32_path_with_the_same_seed(use_g):
     y, mask, _, cond = helpers.flow_inputs(cfg, 3, 300, 5, use_g)
     res = {}
     for prec, d in decs.items():
-        torch.manual_seed(2024)
+        torch.manual_seed(2024)                # both decoders start their dropout state from the same draw
         yc = y.cuda().requires_grad_(True)
         cc = None if cond is None else cond.cuda().requires_grad_(True)
         z, ld = d(yc, mask.cuda(), g=cc)
