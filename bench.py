@@ -134,7 +134,8 @@ class Runner:
         from glowtts_b200 import ops
         self.device, self.world = device, world
         self.dec = build_decoder(device, precision)
-        self.opt = torch.optim.AdamW(self.dec.parameters(), lr=1e-4, fused=True, capturable=graph)
+        # train_ms_emo_lang_pitch.py:126-130 AdamW; the decoder hands its weights over as one flat tensor
+        self.opt = torch.optim.AdamW(self.dec.flat_parameters(), lr=1e-4, fused=True, capturable=graph)
         self.graphed = None
         gen = torch.Generator().manual_seed(SEED + int(os.environ.get("RANK", "0")))
         self.host = synth_batch(B_PER_GPU, gen)

@@ -232,7 +232,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 tmem_ld16(trow + c0, m);
                 tmem_ld16(trow + Ch + c0, lg);
                 if (!t_ok) continue;
-                float lsave[16];
+                // all loads of the chunk first (x and z may alias as far as the compiler knows: loads behind stores
+                // would serialise into one L2 round trip per channel)
+                const float* __restrict__ ax = p.aff_x;
+                float* __restrict__ az = p.aff_z;
+                const size_t o0 = ((size_t)b * C + c0) * p.T + t, o1 = o0 + (size_t)Ch * p.T;
+                float x0[16], x1[16], lsave[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) { x0[i] = ax[o0 + (size_t)i * p.T]; x1[i] = ax[o1 + (size_t)i * p.T]; }
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
                     const int c = c0 + i;
@@ -240,13 +247,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     float ll = lg[i] + ctl->bias[Ch + c];
                     lsave[i] = ll;     // raw end-conv output (pre sigmoid_scale), as the fp32 path keeps it
                     if (p.aff_sigmoid_scale) ll = __logf(1e-6f + sigmoid_f(ll + 2.f));
-                    const size_t o0 = ((size_t)b * C + c) * p.T + t, o1 = o0 + (size_t)Ch * p.T;
-                    const float x1 = p.aff_x[o1];
-                    p.aff_z[o0] = p.aff_x[o0];
+                    az[o0 + (size_t)i * p.T] = x0[i];
                     if (p.aff_reverse) {
-                        p.aff_z[o1] = (x1 - mm) * __expf(-ll) * mk;
+                        az[o1 + (size_t)i * p.T] = (x1[i] - mm) * __expf(-ll) * mk;
                     } else {
-                        p.aff_z[o1] = (mm + __expf(ll) * x1) * mk;
+                        az[o1 + (size_t)i * p.T] = (mm + __expf(ll) * x1[i]) * mk;
                         ld_sum += ll * mk;
                     }
                 }
@@ -338,43 +343,84 @@ int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, 
 }
 
 // ---------------------------------------------------------------------------------- fold + pack, one launch per block
-// Every conv weight of one coupling block: weight-norm fold (w = g v / ||v||, modules.py:124,131,141) and bf16 packing
-// into the forward ([j][m][c]) and data-gradient ([j][c][m], taps flipped) operand layouts in ONE kernel.
-// One CTA per (weight, output row m).
-__global__ void __launch_bounds__(128) fold_pack_kernel(const FoldPackJobs jobs) {
-    __shared__ float scratch[33];
-    int row = blockIdx.x, w = 0;
-    while (w < jobs.n && row >= jobs.job[w].M) { row -= jobs.job[w].M; ++w; }
+// Every conv weight of the decoder: weight-norm fold (w = g v / ||v||, modules.py:124,131,141) and bf16 packing into the
+// forward ([j][m][c]) and data-gradient ([j][c][m], taps flipped) operand layouts, zero padding included, in ONE launch.
+// One CTA per (weight, group of 32 output rows m): row norms first, then 64-channel slabs of the 32 rows go through
+// shared memory so that both layouts are written with contiguous runs (c fastest for fwd, m fastest for tr).
+constexpr int FP_ROWS = 32, FP_CH = 64, FP_NT = 256;
+__global__ void __launch_bounds__(FP_NT) fold_pack_kernel(const __grid_constant__ FoldPackJobs jobs) {
+    extern __shared__ float fp_tile[];               // [FP_ROWS][FP_CH * K + 1]
+    __shared__ float sc_sm[FP_ROWS];
+    int grp = blockIdx.x, w = 0;
+    while (w < jobs.n && grp >= jobs.job[w].groups) { grp -= jobs.job[w].groups; ++w; }
     if (w >= jobs.n) return;
-    const FoldPackJob J = jobs.job[w];
-    const int m = row, R = J.Cin * J.K;
-    const float* vrow = J.v + (size_t)m * R;
-    float sc = 1.f;
-    if (J.g) {
-        float ss = 0.f;
-        for (int e = threadIdx.x; e < R; e += 128) { const float t = vrow[e]; ss += t * t; }
-        ss = block_sum<128>(ss, scratch);
-        sc = J.g[m] / sqrtf(ss);
-    }
-    // forward operand: out[j][m][c], c < cols_f (zero padded)
-    for (int e = threadIdx.x; e < J.K * J.cols_f; e += 128) {
-        const int j = e / J.cols_f, c = e % J.cols_f;
-        const float val = (c < J.Cin) ? vrow[c * J.K + j] * sc : 0.f;
-        J.fwd[((size_t)j * J.rows_f + m) * J.cols_f + c] = __float2bfloat16_rn(val);
-    }
-    // data-gradient operand: out[j][c][m] = W[m][c][K-1-j], c < rows_t
-    if (J.tr) {
-        for (int e = threadIdx.x; e < J.K * J.Cin; e += 128) {
-            const int j = e / J.Cin, c = e % J.Cin;
-            J.tr[((size_t)j * J.rows_t + c) * J.cols_t + m] = __float2bfloat16_rn(vrow[c * J.K + (J.K - 1 - j)] * sc);
+    const FoldPackJob& J = jobs.job[w];
+    const int K = J.K, Cin = J.Cin, R = Cin * K, m0 = grp * FP_ROWS;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // row scales (rows >= M are padding rows of the transposed pack: scale 0)
+    for (int rl = warp; rl < FP_ROWS; rl += FP_NT / 32) {
+        const int m = m0 + rl;
+        float sc = 0.f;
+        if (m < J.M) {
+            sc = 1.f;
+            if (J.g) {
+                const float* vrow = J.v + (size_t)m * R;
+                float ss = 0.f;
+                for (int e = lane; e < R; e += 32) { const float t = vrow[e]; ss += t * t; }
+                ss = warp_sum(ss);
+                sc = J.g[m] / sqrtf(ss);
+            }
         }
+        if (lane == 0) sc_sm[rl] = sc;
+    }
+    __syncthreads();
+    const int pitch = FP_CH * K + 1;
+    const int c_end = J.cols_f > Cin ? J.cols_f : Cin;               // fwd columns include the zero padding
+    for (int cb = 0; cb < c_end; cb += FP_CH) {
+        const int nc = min(FP_CH, Cin - cb);                          // real channels in this slab (may be <= 0)
+        // load: rows contiguous (nc * K floats each), scaled
+        for (int rl = warp; rl < FP_ROWS; rl += FP_NT / 32) {
+            const int m = m0 + rl;
+            const float sc = sc_sm[rl];
+            const float* src = J.v + (size_t)m * R + (size_t)cb * K;
+            for (int e = lane; e < FP_CH * K; e += 32) fp_tile[rl * pitch + e] = (m < J.M && e < nc * K) ? src[e] * sc : 0.f;
+        }
+        __syncthreads();
+        // forward operand: out[j][m][c], c fastest
+        const int ncf = min(FP_CH, J.cols_f - cb);
+        if (ncf > 0) {
+            for (int i = threadIdx.x; i < K * FP_ROWS * ncf; i += FP_NT) {
+                const int cl = i % ncf, rl = (i / ncf) % FP_ROWS, j = i / (ncf * FP_ROWS);
+                const int m = m0 + rl;
+                if (m < J.rows_f) J.fwd[((size_t)j * J.rows_f + m) * J.cols_f + cb + cl] = __float2bfloat16_rn(fp_tile[rl * pitch + cl * K + j]);
+            }
+        }
+        // data-gradient operand: out[j][c][m] = W[m][c][K-1-j], m fastest (columns M..cols_t are zero padding)
+        if (J.tr && nc > 0) {
+            for (int i = threadIdx.x; i < K * nc * FP_ROWS; i += FP_NT) {
+                const int rl = i % FP_ROWS, cl = (i / FP_ROWS) % nc, j = i / (FP_ROWS * nc);
+                const int m = m0 + rl;
+                if (m < J.cols_t) J.tr[((size_t)j * J.rows_t + cb + cl) * J.cols_t + m] = __float2bfloat16_rn(fp_tile[rl * pitch + cl * K + (K - 1 - j)]);
+            }
+        }
+        __syncthreads();
     }
 }
-int fold_pack(const FoldPackJobs& jobs, cudaStream_t st) {
-    int rows = 0;
-    for (int i = 0; i < jobs.n; ++i) rows += jobs.job[i].M;
-    if (rows == 0) return GTK_OK;
-    fold_pack_kernel<<<rows, 128, 0, st>>>(jobs);
+int fold_pack(FoldPackJobs& jobs, cudaStream_t st) {
+    int groups = 0, kmax = 1;
+    for (int i = 0; i < jobs.n; ++i) {
+        FoldPackJob& J = jobs.job[i];
+        GTK_REQUIRE(J.rows_f == J.M && J.rows_t == J.Cin, "pack shapes");
+        const int rows = J.tr ? (J.cols_t > J.M ? J.cols_t : J.M) : J.M;
+        J.groups = ceil_div(rows, FP_ROWS);
+        groups += J.groups;
+        kmax = max(kmax, J.K);
+    }
+    if (groups == 0) return GTK_OK;
+    const size_t smem = (size_t)FP_ROWS * (FP_CH * kmax + 1) * sizeof(float);
+    GTK_REQUIRE(smem <= 200 * 1024, "kernel_size too large for the pack kernel");
+    GTK_CUDA(cudaFuncSetAttribute(fold_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    fold_pack_kernel<<<groups, FP_NT, smem, st>>>(jobs);
     return check_launch("fold_pack");
 }
 
@@ -395,37 +441,69 @@ __global__ void affine_bwd_frames_kernel(const float* __restrict__ x, const floa
         __nv_bfloat16* row = dend + (size_t)f * ld;
         if (chunk >= n_chunk) {
             const int c0 = C + (chunk - n_chunk) * 8;
-            for (int c = c0; c < min(c0 + 8, ld); ++c) row[c] = __float2bfloat16_rn(0.f);
+            if (c0 + 8 <= ld && (C % 8 == 0) && (ld % 8 == 0)) *reinterpret_cast<uint4*>(row + c0) = make_uint4(0u, 0u, 0u, 0u);
+            else for (int c = c0; c < min(c0 + 8, ld); ++c) row[c] = __float2bfloat16_rn(0.f);
             continue;
         }
         const float mk = mask ? mask[f] : 1.f;
         const float dl = dlogdet ? dlogdet[b] * mk : 0.f;
         const int c0 = chunk * 8;
-        float gm[8], gl[8];
+        const bool vec = (Ch % 8 == 0) && (ld % 8 == 0);          // 16-byte aligned 8-channel groups
+        float gm[8], gl[8], raw8[8], dz8[8], x8[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { raw8[k] = 0.f; dz8[k] = 0.f; x8[k] = 0.f; }
+        if (vec) {
+            const float4* r4 = reinterpret_cast<const float4*>(logs_raw + (size_t)f * Ch + c0);
+            const float4 a = r4[0], bq = r4[1];
+            raw8[0] = a.x; raw8[1] = a.y; raw8[2] = a.z; raw8[3] = a.w;
+            raw8[4] = bq.x; raw8[5] = bq.y; raw8[6] = bq.z; raw8[7] = bq.w;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {                              // all loads before any store
+            const int c = c0 + k;
+            if (c < Ch) {
+                const size_t o1 = ((size_t)b * C + Ch + c) * T + t;
+                if (!vec) raw8[k] = logs_raw[(size_t)f * Ch + c];
+                dz8[k] = dz[o1];
+                x8[k] = x[o1];
+            }
+        }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             const int c = c0 + k;
             gm[k] = gl[k] = 0.f;
             if (c < Ch) {
                 const size_t o1 = ((size_t)b * C + Ch + c) * T + t;
-                const float raw = logs_raw[(size_t)f * Ch + c];
-                float lg = raw, dscale = 1.f;
+                float lg = raw8[k], dscale = 1.f;
                 if (sigmoid_scale) {
-                    const float sg = sigmoid_f(raw + 2.f);
+                    const float sg = sigmoid_f(raw8[k] + 2.f);
                     lg = __logf(1e-6f + sg);
                     dscale = sg * (1.f - sg) / (1e-6f + sg);
                 }
                 const float e = __expf(lg);
-                const float g = dz[o1] * mk;
+                const float g = dz8[k] * mk;
                 gm[k] = g;
-                gl[k] = (g * e * x[o1] + dl) * dscale;
+                gl[k] = (g * e * x8[k] + dl) * dscale;
                 dx[o1] = g * e;
             }
         }
+        if (vec) {
+            uint32_t wm[4], wl[4];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const int c = c0 + k;
-            if (c < Ch) { row[c] = __float2bfloat16_rn(gm[k]); row[Ch + c] = __float2bfloat16_rn(gl[k]); }
+            for (int k = 0; k < 4; ++k) {
+                __nv_bfloat162 hm = __floats2bfloat162_rn(gm[2 * k], gm[2 * k + 1]);
+                __nv_bfloat162 hl = __floats2bfloat162_rn(gl[2 * k], gl[2 * k + 1]);
+                wm[k] = *reinterpret_cast<uint32_t*>(&hm);
+                wl[k] = *reinterpret_cast<uint32_t*>(&hl);
+            }
+            *reinterpret_cast<uint4*>(row + c0) = make_uint4(wm[0], wm[1], wm[2], wm[3]);
+            *reinterpret_cast<uint4*>(row + Ch + c0) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int c = c0 + k;
+                if (c < Ch) { row[c] = __float2bfloat16_rn(gm[k]); row[Ch + c] = __float2bfloat16_rn(gl[k]); }
+            }
         }
     }
 }

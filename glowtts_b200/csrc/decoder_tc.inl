@@ -58,7 +58,7 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     for (int i = 0; i < D.L; ++i) P.t_rs[i] = wtake((size_t)H * pad64((i < D.L - 1) ? 2 * H : H));
     P.t_end = wtake((size_t)H * pad64(C));
     P.total = w;
-    L->n_pack = train ? D.NB : 1;
+    L->n_pack = D.NB;            // all blocks are packed by one launch up front
     L->pack = take(w * 2 * L->n_pack);
     // block inputs / outputs (fp32, t-major)
     L->x_bytes = (size_t)C * nq * 4;
@@ -98,27 +98,33 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     L->total = off;
 }
 
-// weight-norm fold + bf16 operand packs of one block, one launch.  The padding columns/rows of the packs are zeroed
-// once per forward call (tc_forward / tc_reverse memset the pack region).
-static int tc_pack_block(const Dims& D, const TcLayout& L, const gtk_block_params& P, bf16* pk, int with_transposed,
-                         cudaStream_t st) {
+// weight-norm fold + bf16 operand packs (zero padding included) of EVERY block in one launch (a second one only
+// if the model has more than FOLD_PACK_MAX_JOBS conv weights).
+static int tc_pack_all(const Dims& D, const TcLayout& L, const gtk_block_params* blocks, bf16* pk_base, int with_transposed,
+                       cudaStream_t st) {
     const int H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
     const TcPack& Q = L.P;
-    tc::FoldPackJobs J;
-    memset(&J, 0, sizeof(J));
+    static thread_local tc::FoldPackJobs J;
+    J.n = 0;
+    bf16* pk = pk_base;
     auto add = [&](const float* g, const float* v, size_t fwd, size_t tr, int M, int Cin, int Kk, int cols_f, int cols_t) {
         tc::FoldPackJob& j = J.job[J.n++];
         j.g = g; j.v = v; j.fwd = pk + fwd; j.tr = with_transposed ? pk + tr : nullptr;
-        j.M = M; j.Cin = Cin; j.K = Kk; j.rows_f = M; j.cols_f = cols_f; j.rows_t = Cin; j.cols_t = cols_t;
+        j.M = M; j.Cin = Cin; j.K = Kk; j.rows_f = M; j.cols_f = cols_f; j.rows_t = Cin; j.cols_t = cols_t; j.groups = 0;
     };
-    if (2 + 2 * D.L > 16) { set_error("bf16 path: n_layers <= 7"); return GTK_ERR_UNSUPPORTED; }
-    add(P.start_g, P.start_v, Q.start, Q.t_start, H, Ch, 1, pad64(Ch), H);
-    for (int i = 0; i < D.L; ++i) {
-        const int RS = (i < D.L - 1) ? 2 * H : H;
-        add(P.in_g[i], P.in_v[i], Q.in[i], Q.t_in[i], 2 * H, H, K, H, 2 * H);
-        add(P.rs_g[i], P.rs_v[i], Q.rs[i], Q.t_rs[i], RS, H, 1, H, pad64(RS));
+    for (int blk = 0; blk < D.NB; ++blk) {
+        const gtk_block_params& P = blocks[blk];
+        GTK_TRY(check_block(D, P));
+        if (J.n + 2 + 2 * D.L > tc::FOLD_PACK_MAX_JOBS) { GTK_TRY(tc::fold_pack(J, st)); J.n = 0; }
+        pk = pk_base + (size_t)blk * Q.total;
+        add(P.start_g, P.start_v, Q.start, Q.t_start, H, Ch, 1, pad64(Ch), H);
+        for (int i = 0; i < D.L; ++i) {
+            const int RS = (i < D.L - 1) ? 2 * H : H;
+            add(P.in_g[i], P.in_v[i], Q.in[i], Q.t_in[i], 2 * H, H, K, H, 2 * H);
+            add(P.rs_g[i], P.rs_v[i], Q.rs[i], Q.t_rs[i], RS, H, 1, H, pad64(RS));
+        }
+        add(nullptr, P.end_w, Q.end, Q.t_end, C, H, 1, H, pad64(C));
     }
-    add(nullptr, P.end_w, Q.end, Q.t_end, C, H, 1, H, pad64(C));
     return tc::fold_pack(J, st);
 }
 
@@ -189,20 +195,19 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     float* msq = reinterpret_cast<float*>(ws + L.mask_sq);
     float* x_len = reinterpret_cast<float*>(ws + L.x_len);
     float* we = reinterpret_cast<float*>(ws + L.we);
-    GTK_CUDA(cudaMemsetAsync(ws + L.pack, 0, L.P.total * 2 * L.n_pack, st));   // zero padding of the packed weights
+    GTK_TRY(tc_pack_all(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), train, st));
     GTK_TRY(flow::squeeze(x, mask, reinterpret_cast<float*>(ws + L.X), msq, D.B, D.Cin, D.T, D.n, 0, st));
     GTK_TRY(flow::mask_len(msq, x_len, D.B, D.Tq, st));
     for (int blk = 0; blk < D.NB; ++blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
         unsigned char* act = ws + L.act + (size_t)(train ? blk : 0) * L.A.total;
-        bf16* pk = reinterpret_cast<bf16*>(ws + L.pack) + (size_t)(train ? blk : 0) * L.P.total;
+        bf16* pk = reinterpret_cast<bf16*>(ws + L.pack) + (size_t)blk * L.P.total;
         const float* xin = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? blk : (blk & 1)) * L.x_bytes);
         float* xout = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? blk + 1 : ((blk + 1) & 1)) * L.x_bytes);
         float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
         float* icld = reinterpret_cast<float*>(ws + L.icld) + blk;
         float* xmix = reinterpret_cast<float*>(act + L.A.xmix);
-        GTK_TRY(tc_pack_block(D, L, P, pk, train, st));
         GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, icld, st));
         GTK_TRY(flow::mix(xin, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, xmix, D.B, D.C, D.Tq, 0, st));
         GTK_TRY(flow::logdet_const(P.an_logs, D.C, icld, (float)(D.C / D.NS), x_len, logdet, D.B, 1, st));
@@ -228,14 +233,13 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     float* xa = reinterpret_cast<float*>(ws + L.X);
     float* xb = reinterpret_cast<float*>(ws + L.X + L.x_bytes);
     unsigned char* act = ws + L.act;
-    bf16* pk = reinterpret_cast<bf16*>(ws + L.pack);
-    GTK_CUDA(cudaMemsetAsync(ws + L.pack, 0, L.P.total * 2, st));
+    GTK_TRY(tc_pack_all(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), 0, st));
     GTK_TRY(flow::squeeze(z, mask, xa, msq, D.B, D.Cin, D.T, D.n, 0, st));
     for (int blk = D.NB - 1; blk >= 0; --blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
         float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
-        GTK_TRY(tc_pack_block(D, L, P, pk, 0, st));
+        const bf16* pk = reinterpret_cast<const bf16*>(ws + L.pack) + (size_t)blk * L.P.total;
         GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, nullptr, st));
         GTK_TRY(tc_coupling(d, D, L, P, pk, xa, xb, nullptr, msq, act, ws, 1, 0, blk, st));
         GTK_TRY(flow::mix(xb, msq, P.an_logs, P.an_bias, winv, D.NS, xa, D.B, D.C, D.Tq, 1, st));

@@ -109,16 +109,18 @@ int colsum_frames(const __nv_bfloat16* in, int ld, int n_cols, int groups, long 
                   cudaStream_t st);
 int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, const float* dz, const float* dlogdet,
                       __nv_bfloat16* dend, int ld, float* dx, int B, int C, int T, int sigmoid_scale, cudaStream_t st);
-// Fold (weight norm) + bf16 pack of up to 16 conv weights in one launch (conv_tc.cu).
+// Fold (weight norm) + bf16 pack of up to FOLD_PACK_MAX_JOBS conv weights in one launch (conv_tc.cu).
+constexpr int FOLD_PACK_MAX_JOBS = 320;
 struct FoldPackJob {
     const float* g;            // weight_g [M] or null (plain weight)
     const float* v;            // weight_v / weight [M][Cin][K]
     __nv_bfloat16* fwd;        // [K][rows_f][cols_f]
     __nv_bfloat16* tr;         // [K][rows_t][cols_t] or null
     int M, Cin, K, rows_f, cols_f, rows_t, cols_t;
+    int groups;                // filled by fold_pack: CTAs (32-row groups) of this job
 };
-struct FoldPackJobs { FoldPackJob job[16]; int n; };
-int fold_pack(const FoldPackJobs& jobs, cudaStream_t st);
+struct FoldPackJobs { FoldPackJob job[FOLD_PACK_MAX_JOBS]; int n; };
+int fold_pack(FoldPackJobs& jobs, cudaStream_t st);
 int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, ConvTcParams p, int epi, cudaStream_t st);
 int pack_weight_bf16(const float* w, __nv_bfloat16* out, int M, int Cin, int K, int transpose, int rows, int cols, cudaStream_t st);
 int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, int c0, int nc, int ld, cudaStream_t st);

@@ -134,6 +134,19 @@ class FlowSpecDecoder(nn.Module):
             self._flat_params = [owners_p for owners_p in self._ordered_owners()]
         return self._flat, self._flat_offs
 
+    def flat_parameters(self):
+        """Parameters for the optimizer with the fused decoder weights as ONE tensor: [flat buffer] + every parameter
+        that is not part of it (e.g. the WN cond_layers).  The named parameters stay views of the buffer, so
+        state_dict()/checkpoints are unchanged; an elementwise optimizer (Adam, AdamW, SGD) then runs one multi-tensor
+        launch instead of ~40 and reads the gradient the backward kernels wrote in place (no scatter)."""
+        params, folded = self._params()
+        if folded:
+            raise RuntimeError("glowtts_b200: weight norm was removed (store_inverse/remove_weight_norm); nothing to train")
+        flat, _ = self._ensure_flat(params)
+        self._keep_flat_grad = True
+        inside = {id(p) for p in self._ordered_owners()}
+        return [flat] + [p for p in self.parameters() if id(p) not in inside]
+
     def _ordered_owners(self):
         """nn.Parameters in decoder_forward order (ActNorm logs/bias are [1,C,1] parameters passed as [C] views)."""
         out = []
@@ -149,6 +162,8 @@ class FlowSpecDecoder(nn.Module):
         return {p.data_ptr(): p for p in self._ordered_owners()}
 
     def _scatter_flat_grad(self, flat):
+        if getattr(self, "_keep_flat_grad", False):      # the optimizer owns the flat tensor (flat_parameters())
+            return
         g = flat.grad
         flat.grad = None
         for p, o, n in zip(self._flat_params, self._flat_offs, self._flat_sizes):
