@@ -129,31 +129,39 @@ __device__ __forceinline__ float block_sum(float v, float* scratch /* >= 33 floa
 #endif  // __CUDACC__
 // ---------------------------------------------------------------------------------------------- dropout
 // Counter-based dropout shared by every kernel that applies or back-propagates nn.Dropout on the WaveNet in_layer
-// output (modules.py:153).  Element (row = b*T + t, col in [0, 2H)) has index idx = row * 2H + col; one splitmix64
-// hash of (seed, idx >> 2) yields four 16-bit uniforms, element idx keeps iff its field >= thr = round(p * 65536),
-// and kept values are scaled by 1 / (1 - thr/65536) (so the estimator is exactly unbiased for the quantised p).
+// output (modules.py:153).  Element (row = b*T + t, col in [0, 2H)) has index idx = row * 2H + col (< 2^32); one 32-bit
+// hash (two multiplies) of (layer seed, idx >> 1) yields two 16-bit uniforms, element idx keeps iff its field >= thr =
+// round(p * 65536), and kept values are scaled by 1 / (1 - thr/65536) (exactly unbiased for the quantised p).  The
+// epilogues that apply it are instruction-bound, hence the cheap 32-bit mixer instead of a 64-bit one.
 __host__ __device__ __forceinline__ unsigned long long drop_hash(unsigned long long seed, unsigned long long ctr) {
-    unsigned long long z = seed + (ctr + 1ull) * 0x9E3779B97F4A7C15ull;
+    unsigned long long z = seed + (ctr + 1ull) * 0x9E3779B97F4A7C15ull;      // splitmix64: seed derivation only
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
     return z ^ (z >> 31);
 }
+__host__ __device__ __forceinline__ unsigned drop_bits32(unsigned long long seed, unsigned pair) {
+    unsigned x = pair * 0x9E3779B1u + (unsigned)seed;
+    x ^= x >> 16; x *= 0x7FEB352Du;
+    x ^= x >> 15; x ^= (unsigned)(seed >> 32); x *= 0x846CA68Bu;
+    return x ^ (x >> 16);
+}
 __host__ __device__ __forceinline__ unsigned drop_threshold(float p) { return (unsigned)(p * 65536.f + 0.5f); }
 __host__ __device__ __forceinline__ float drop_inv_keep(float p) { return 65536.f / (65536.f - (float)drop_threshold(p)); }
 __host__ __device__ __forceinline__ float dropout_scale1(unsigned long long seed, unsigned long long idx, float p) {
-    const unsigned long long h = drop_hash(seed, idx >> 2);
-    const unsigned u = (unsigned)(h >> (16 * (unsigned)(idx & 3))) & 0xffffu;
+    const unsigned h = drop_bits32(seed, (unsigned)(idx >> 1));
+    const unsigned u = (h >> (16 * (unsigned)(idx & 1))) & 0xffffu;
     return u >= drop_threshold(p) ? drop_inv_keep(p) : 0.f;
 }
-// 16 consecutive elements starting at idx0 (a multiple of 16): four hashes.
+// 16 consecutive elements starting at idx0 (a multiple of 16): eight hashes.
 __device__ __forceinline__ void dropout_scale16(unsigned long long seed, unsigned long long idx0, float p, float (&s)[16]) {
     const unsigned thr = drop_threshold(p);
     const float keep = drop_inv_keep(p);
+    const unsigned pair0 = (unsigned)(idx0 >> 1);
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const unsigned long long h = drop_hash(seed, (idx0 >> 2) + q);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) s[4 * q + j] = (((unsigned)(h >> (16 * j)) & 0xffffu) >= thr) ? keep : 0.f;
+    for (int q = 0; q < 8; ++q) {
+        const unsigned h = drop_bits32(seed, pair0 + q);
+        s[2 * q] = ((h & 0xffffu) >= thr) ? keep : 0.f;
+        s[2 * q + 1] = ((h >> 16) >= thr) ? keep : 0.f;
     }
 }
 // Seed of layer `layer` of block `blk` derived from the per-call seed in gtk_decoder_desc.

@@ -75,8 +75,11 @@ __device__ __forceinline__ unsigned long long gtimer() {
         if (p.trace && threadIdx.x == 128 && cta_ < CONV_TRACE_CTAS) g_conv_trace[cta_ * 5 + (i)] = gtimer(); \
     } while (0)
 
-template <int TMEM_COLS, int EPI>
-__global__ void __launch_bounds__(NTHREADS, 1)
+// CL = CTAs per cluster.  CL == 2: two neighbouring frame tiles share every weight tile -- each CTA fetches half of
+// its rows and the TMA multicasts them into both shared memories, so the L2 -> SM traffic of the weights (60 % of the
+// bytes of the k = 5 data gradient, which is L2-latency bound, not MMA bound) is halved.
+template <int TMEM_COLS, int EPI, int CL>
+__global__ void __launch_bounds__(EPI_NT, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmO, const ConvTcParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -91,15 +94,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     CONV_TRACE(0);
     const int n_iter = p.taps * p.n_k;
 
+    const uint32_t cta_rank = CL > 1 ? cluster_ctarank() : 0u;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.stages; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
+        for (int s = 0; s < p.stages; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], CL); }
         mbar_init(&ctl->acc_full, 1);
         mbar_fence_init();
     }
-    for (int i = threadIdx.x; i < p.N; i += NTHREADS) ctl->bias[i] = p.bias ? p.bias[i] : 0.f;
+    for (int i = threadIdx.x; i < p.N; i += EPI_NT) ctl->bias[i] = p.bias ? p.bias[i] : 0.f;
     if (warp == 2) tmem_alloc<TMEM_COLS>(&ctl->tmem_base);
     tc_fence_before();
-    __syncthreads();
+    if constexpr (CL > 1) cluster_sync_all();             // the peer's barriers exist before anything is multicast
+    else __syncthreads();
     tc_fence_after();
     const uint32_t tmem = ctl->tmem_base;
     CONV_TRACE(1);
@@ -116,8 +121,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 unsigned char* sb = sa + A_BYTES;
                 mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)stage_bytes);
                 tma_load_3d(sa, &tmA, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
-                for (int ch = 0; ch < p.NCH; ++ch)
-                    tma_load_3d(sb + (size_t)ch * p.NW * KC * 2, &tmB, &ctl->full[s], kc * KC, ch * p.NW, j);
+                if constexpr (CL > 1) {
+                    const int rows = p.NW / CL;            // this CTA's share of the weight rows, delivered to the whole cluster
+                    for (int ch = 0; ch < p.NCH; ++ch)
+                        tma_load_3d_multicast(sb + ((size_t)ch * p.NW + cta_rank * rows) * KC * 2, &tmB, &ctl->full[s], kc * KC,
+                                              ch * p.NW + cta_rank * rows, j, (uint16_t)((1u << CL) - 1));
+                } else {
+                    for (int ch = 0; ch < p.NCH; ++ch)
+                        tma_load_3d(sb + (size_t)ch * p.NW * KC * 2, &tmB, &ctl->full[s], kc * KC, ch * p.NW, j);
+                }
             }
         }
     } else if (warp == 1) {
@@ -137,29 +149,30 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         umma_bf16(tmem + ch * p.NW, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0);
                     }
                 }
-                umma_commit(&ctl->empty[s]);
+                if constexpr (CL > 1) umma_commit_multicast(&ctl->empty[s], (uint16_t)((1u << CL) - 1));
+                else umma_commit(&ctl->empty[s]);
             }
             umma_commit(&ctl->acc_full);
         }
     }
     __syncwarp();
-    {   // epilogue: ALL 8 warps; warp w owns TMEM lane quarter w % 4 (frames) and column half w / 4
+    {   // epilogue: ALL warps; warp w owns TMEM lane quarter w % 4 (frames) and column part w / 4 of EPI_PARTS
         mbar_wait(&ctl->acc_full, 0);
         tc_fence_after();
         CONV_TRACE(2);
-        const int q = warp & 3, half = warp >> 2;
+        const int q = warp & 3, part = warp >> 2;
         const int t = t0 + q * 32 + lane;
         const bool t_ok = t < p.T;
         const float mk = (p.mask && t_ok) ? p.mask[(size_t)b * p.T + t] : 1.f;
         const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
         const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
         RowIo io;
-        io.tp = p.tile_layout; io.tile_id = b * gridDim.x + blockIdx.x; io.r = q * 32 + lane; io.frame = frame;
+        io.tp = p.tile_layout; io.tile_id = b * ((p.T + BT - 1) / BT) + blockIdx.x; io.r = q * 32 + lane; io.frame = frame;
         // The operand stages are idle once the accumulator is complete: bf16 outputs that the next kernel reads as TMA
         // operands are staged there in the SWIZZLE_128B layout and leave as bulk tensor stores (no row-strided stores).
         if constexpr (EPI == EPI_PLAIN) {
             const int nck = p.N / 16;
-            for (int cc = half ? (nck + 1) / 2 : 0; cc < (half ? nck : (nck + 1) / 2); ++cc) {
+            for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
                 const int c0 = cc * 16;
                 float v[16];
                 tmem_ld16(trow + c0, v);
@@ -192,7 +205,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         } else if constexpr (EPI == EPI_GATE_BWD) {
             const int H = p.N, nck = H / 16;
             const unsigned long long dseed = p.drop_p > 0.f ? drop_resolve(p.drop_seed) : 0ull;
-            for (int cc = half ? (nck + 1) / 2 : 0; cc < (half ? nck : (nck + 1) / 2); ++cc) {
+            for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
                 const int c0 = cc * 16;
                 float d[16];
                 tmem_ld16(trow + c0, d);
@@ -226,7 +239,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int Ch = p.N / 2, C = p.N;
             float ld_sum = 0.f;
             const int nck = Ch / 16;
-            for (int cc = half ? (nck + 1) / 2 : 0; cc < (half ? nck : (nck + 1) / 2); ++cc) {
+            for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
                 const int c0 = cc * 16;
                 float m[16], lg[16];
                 tmem_ld16(trow + c0, m);
@@ -279,6 +292,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tma_store_wait_read();                           // shared memory must outlive the bulk reads
     }
     CONV_TRACE(4);
+    if constexpr (CL > 1) cluster_sync_all();             // no CTA leaves while the peer's commits may still arrive here
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc<TMEM_COLS>(tmem);
@@ -536,6 +550,8 @@ int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, 
     p.NCH = (p.N > 256) ? 2 : 1;
     p.NW = p.N / p.NCH;
     GTK_REQUIRE(p.NW % 16 == 0 && p.NW <= 256, "N chunk must be a multiple of 16");
+    // weight-tile sharing between two frame tiles pays when the mainloop is long (k > 1 taps)
+    p.cluster = (epi == EPI_PLAIN && p.taps > 1 && p.N <= 256 && (p.NW / 2) % 8 == 0 && ceil_div(p.T, BT) > 1) ? 2 : 1;
     const int out_cols = (epi == EPI_GATE_BWD) ? 2 * p.N : ((epi == EPI_PLAIN && p.out_bf16) ? p.N : 0);
     int stages = 4;
     while (stages > 2 && conv_tc_smem(p.N, stages, out_cols) > 200 * 1024) --stages;
@@ -570,19 +586,30 @@ int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, 
         const uint64_t kcols = (uint64_t)p.n_k * KC;
         const uint64_t dims[3] = {kcols, (uint64_t)p.N, (uint64_t)p.taps};
         const uint64_t strides[2] = {kcols * 2, kcols * 2 * p.N};
-        const uint32_t box[3] = {KC, (uint32_t)p.NW, 1};
+        const uint32_t box[3] = {KC, (uint32_t)(p.NW / p.cluster), 1};
         int rc = make_tmap_bf16(&tmB, wp, 3, dims, strides, box, true);
         if (rc) return rc;
     }
-    dim3 grid(ceil_div(p.T, BT), p.B);
+    dim3 grid(ceil_div(ceil_div(p.T, BT), p.cluster) * p.cluster, p.B);   // an out-of-range tile only feeds its peer
     p.trace = (epi == g_trace_epi && p.taps == g_trace_taps) ? 1 : 0;
     ProfScope prof(p.taps > 1 ? "conv_tc_kN" : "conv_tc_k1", st);
 #define GTK_TC_LAUNCH(COLS, E)                                                                                       \
     do {                                                                                                             \
-        GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<COLS, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        conv_tc_kernel<COLS, E><<<grid, NTHREADS, smem, st>>>(tmA, tmB, tmO, p);                                          \
+        GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<COLS, E, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        conv_tc_kernel<COLS, E, 1><<<grid, EPI_NT, smem, st>>>(tmA, tmB, tmO, p);                                  \
     } while (0)
-    if (epi == EPI_PLAIN) { if (p.N > 256) GTK_TC_LAUNCH(512, EPI_PLAIN); else GTK_TC_LAUNCH(256, EPI_PLAIN); }
+    if (epi == EPI_PLAIN && p.cluster == 2) {
+        GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<256, EPI_PLAIN, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = grid; cfg.blockDim = dim3(EPI_NT); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        GTK_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<256, EPI_PLAIN, 2>, tmA, tmB, tmO, p));
+    }
+    else if (epi == EPI_PLAIN) { if (p.N > 256) GTK_TC_LAUNCH(512, EPI_PLAIN); else GTK_TC_LAUNCH(256, EPI_PLAIN); }
     else if (epi == EPI_GATE_BWD) { GTK_REQUIRE(p.N <= 256 && p.ts && p.out_bf16, "gate_bwd epilogue arguments"); GTK_TC_LAUNCH(256, EPI_GATE_BWD); }
     else { GTK_REQUIRE(p.N <= 256 && p.N % 32 == 0 && p.aff_x && p.aff_z, "affine epilogue arguments"); GTK_TC_LAUNCH(256, EPI_AFFINE); }
 #undef GTK_TC_LAUNCH

@@ -128,6 +128,24 @@ static int tc_pack_all(const Dims& D, const TcLayout& L, const gtk_block_params*
     return tc::fold_pack(J, st);
 }
 
+// W^-1 / log|det W| of every block (+ the constant part of logdet when logdet != null), one launch per 32 blocks.
+static int tc_flow_consts(const Dims& D, const TcLayout& L, const gtk_block_params* blocks, unsigned char* ws, const float* x_len,
+                          float* logdet, cudaStream_t st) {
+    static thread_local flow::FlowConstJobs J;
+    for (int k0 = 0; k0 < D.NB; k0 += flow::FLOW_CONST_MAX_BLOCKS) {
+        J.n = min(flow::FLOW_CONST_MAX_BLOCKS, D.NB - k0);
+        for (int k = 0; k < J.n; ++k) {
+            GTK_TRY(check_block(D, blocks[k0 + k]));
+            J.w[k] = blocks[k0 + k].ic_weight;
+            J.logs[k] = blocks[k0 + k].an_logs;
+        }
+        J.winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)k0 * 64;
+        J.icld = reinterpret_cast<float*>(ws + L.icld) + k0;
+        GTK_TRY(flow::flow_consts(J, D.NS, D.C, x_len, logdet, D.B, 1, st));
+    }
+    return GTK_OK;
+}
+
 // start -> WN -> end(+affine) of one block.  xc = mixed block input (t-major fp32), zout = block output.
 static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout& L, const gtk_block_params& P, const bf16* pk,
                        const float* xc, float* zout, float* logdet, const float* mask, unsigned char* act, unsigned char* ws,
@@ -198,6 +216,7 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     GTK_TRY(tc_pack_all(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), train, st));
     GTK_TRY(flow::squeeze(x, mask, reinterpret_cast<float*>(ws + L.X), msq, D.B, D.Cin, D.T, D.n, 0, st));
     GTK_TRY(flow::mask_len(msq, x_len, D.B, D.Tq, st));
+    GTK_TRY(tc_flow_consts(D, L, blocks, ws, x_len, logdet, st));      // W^-1, log|det W|, the constant logdet terms
     for (int blk = 0; blk < D.NB; ++blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
@@ -205,12 +224,8 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
         bf16* pk = reinterpret_cast<bf16*>(ws + L.pack) + (size_t)blk * L.P.total;
         const float* xin = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? blk : (blk & 1)) * L.x_bytes);
         float* xout = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? blk + 1 : ((blk + 1) & 1)) * L.x_bytes);
-        float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
-        float* icld = reinterpret_cast<float*>(ws + L.icld) + blk;
         float* xmix = reinterpret_cast<float*>(act + L.A.xmix);
-        GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, icld, st));
         GTK_TRY(flow::mix(xin, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, xmix, D.B, D.C, D.Tq, 0, st));
-        GTK_TRY(flow::logdet_const(P.an_logs, D.C, icld, (float)(D.C / D.NS), x_len, logdet, D.B, 1, st));
         GTK_TRY(tc_coupling(d, D, L, P, pk, xmix, xout, logdet, msq, act, ws, 0, train, blk, st));
     }
     const float* xfin = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? D.NB : (D.NB & 1)) * L.x_bytes);
@@ -235,12 +250,12 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     unsigned char* act = ws + L.act;
     GTK_TRY(tc_pack_all(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), 0, st));
     GTK_TRY(flow::squeeze(z, mask, xa, msq, D.B, D.Cin, D.T, D.n, 0, st));
+    GTK_TRY(tc_flow_consts(D, L, blocks, ws, nullptr, nullptr, st));
     for (int blk = D.NB - 1; blk >= 0; --blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
         float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
         const bf16* pk = reinterpret_cast<const bf16*>(ws + L.pack) + (size_t)blk * L.P.total;
-        GTK_TRY(flow::invconv_prep(P.ic_weight, D.NS, winv, nullptr, st));
         GTK_TRY(tc_coupling(d, D, L, P, pk, xa, xb, nullptr, msq, act, ws, 1, 0, blk, st));
         GTK_TRY(flow::mix(xb, msq, P.an_logs, P.an_bias, winv, D.NS, xa, D.B, D.C, D.Tq, 1, st));
     }
@@ -287,6 +302,15 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     float* wpart = reinterpret_cast<float*>(ws + L.b_wpart);   // stream-K partial tiles of the weight gradients
 
     GTK_TRY(flow::squeeze(dz, msq, dZ, nullptr, B, D.Cin, D.Tq * D.n, D.n, 1, st));
+    {   // gradients of the constant logdet terms of every block, one launch (they only need dlogdet and the saved W^-1)
+        static thread_local flow::FlowConstGrads FG;
+        for (int k0 = 0; k0 < D.NB; k0 += flow::FLOW_CONST_MAX_BLOCKS) {
+            FG.n = min(flow::FLOW_CONST_MAX_BLOCKS, D.NB - k0);
+            for (int k = 0; k < FG.n; ++k) { FG.dlogs[k] = grads[k0 + k].an_logs; FG.dW[k] = grads[k0 + k].ic_weight; }
+            GTK_TRY(flow::logdet_const_bwd_all(dlogdet, x_len, B, FG, C, reinterpret_cast<const float*>(ws + L.winv) + (size_t)k0 * 64,
+                                               D.NS, st));
+        }
+    }
 
     for (int blk = D.NB - 1; blk >= 0; --blk) {
         const gtk_block_params& P = blocks[blk];
@@ -391,7 +415,6 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         // ActNorm + InvConvNear (fp32)
         GTK_TRY(flow::mix_bwd(xin_blk, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, dM, dZ, G.an_logs, G.an_bias, G.ic_weight, B,
                               C, T, st));
-        GTK_TRY(flow::logdet_const_bwd(dlogdet, x_len, B, G.an_logs, C, winv, D.NS, (float)(C / D.NS), G.ic_weight, st));
     }
     GTK_TRY(flow::unsqueeze(dZ, msq, dx, nullptr, B, C, T, D.n, D.T, st));
     return GTK_OK;

@@ -102,9 +102,7 @@ int mask_len(const float* mask, float* x_len, int B, int T, cudaStream_t st) {
 // ------------------------------------------------------------------------------------------ invconv prep
 // Single thread: LU with partial pivoting of the NS x NS weight -> inverse and log(det) (NaN for det<0,
 // like torch.logdet).  winv and logdet may be null.
-__global__ void invconv_prep_kernel(const float* __restrict__ w, int ns, float* __restrict__ winv,
-                                    float* __restrict__ logdet) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+__device__ void invconv_lu(const float* __restrict__ w, int ns, float* __restrict__ winv, float* __restrict__ logdet) {
     float a[8][16];
     for (int i = 0; i < ns; ++i)
         for (int j = 0; j < ns; ++j) {
@@ -135,6 +133,48 @@ __global__ void invconv_prep_kernel(const float* __restrict__ w, int ns, float* 
         for (int i = 0; i < ns; ++i)
             for (int j = 0; j < ns; ++j) winv[i * ns + j] = a[i][ns + j];
     if (logdet) *logdet = logf(det);
+}
+__global__ void invconv_prep_kernel(const float* __restrict__ w, int ns, float* __restrict__ winv,
+                                    float* __restrict__ logdet) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    invconv_lu(w, ns, winv, logdet);
+}
+
+// All flow blocks at once (the decoder's per-call constants): warp k inverts block k's InvConvNear weight and sums its
+// ActNorm logs; then logdet[b] (+)= x_len[b] * sum_k (sum_c logs_kc + logdetW_k * C/NS), blocks added in index order.
+__global__ void __launch_bounds__(1024) flow_consts_kernel(const FlowConstJobs J, int ns, int C, float group_count,
+                                                           const float* __restrict__ x_len, float* __restrict__ logdet, int B,
+                                                           int accumulate) {
+    __shared__ float s_blk[FLOW_CONST_MAX_BLOCKS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int k = warp; k < J.n; k += blockDim.x >> 5) {
+        float ld = 0.f;
+        if (lane == 0) invconv_lu(J.w[k], ns, J.winv ? J.winv + (size_t)k * 64 : nullptr, &ld);
+        float s = 0.f;
+        if (J.logs[k])
+            for (int c = lane; c < C; c += 32) s += J.logs[k][c];
+        s = warp_sum(s);
+        if (lane == 0) {
+            s_blk[k] = s + ld * group_count;
+            if (J.icld) J.icld[k] = ld;
+        }
+    }
+    __syncthreads();
+    if (!logdet) return;
+    float tot = 0.f;
+    for (int k = 0; k < J.n; ++k) tot += s_blk[k];
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+        const float v = tot * x_len[b];
+        logdet[b] = accumulate ? logdet[b] + v : v;
+    }
+}
+int flow_consts(const FlowConstJobs& J, int ns, int C, const float* x_len, float* logdet, int B, int accumulate, cudaStream_t st) {
+    GTK_REQUIRE(ns >= 1 && ns <= 8 && J.n >= 0 && J.n <= FLOW_CONST_MAX_BLOCKS, "bad args");
+    GTK_REQUIRE(!logdet || x_len, "null");
+    if (J.n == 0) return GTK_OK;
+    const int threads = min(1024, max(32, J.n * 32));
+    flow_consts_kernel<<<1, threads, 0, st>>>(J, ns, C, (float)(C / ns), x_len, logdet, B, accumulate);
+    return check_launch("flow_consts");
 }
 int invconv_prep(const float* w, int ns, float* winv, float* logdet, cudaStream_t st) {
     GTK_REQUIRE(w && ns >= 1 && ns <= 8, "n_split must be in [1, 8]");
@@ -354,6 +394,29 @@ __global__ void logdet_const_bwd_kernel(const float* __restrict__ dlogdet, const
         const int i = threadIdx.x / ns, j = threadIdx.x % ns;
         dW[i * ns + j] += s * group_count * winv[j * ns + i];
     }
+}
+// The same for every block in one launch: block k adds to dlogs[k] / dW[k] (winv [k][64]).
+__global__ void logdet_const_bwd_all_kernel(const float* __restrict__ dlogdet, const float* __restrict__ x_len, int B,
+                                            const FlowConstGrads G, int C, const float* __restrict__ winv, int ns,
+                                            float group_count) {
+    __shared__ float scratch[33];
+    const int k = blockIdx.x;
+    float s = 0.f;
+    for (int b = threadIdx.x; b < B; b += PW_NT) s += dlogdet[b] * x_len[b];
+    s = block_sum<PW_NT>(s, scratch);
+    if (G.dlogs[k])
+        for (int c = threadIdx.x; c < C; c += PW_NT) G.dlogs[k][c] += s;
+    if (G.dW[k] && threadIdx.x < ns * ns) {
+        const int i = threadIdx.x / ns, j = threadIdx.x % ns;
+        G.dW[k][i * ns + j] += s * group_count * winv[(size_t)k * 64 + j * ns + i];
+    }
+}
+int logdet_const_bwd_all(const float* dlogdet, const float* x_len, int B, const FlowConstGrads& G, int C, const float* winv, int ns,
+                         cudaStream_t st) {
+    GTK_REQUIRE(dlogdet && x_len && winv && G.n >= 0 && G.n <= FLOW_CONST_MAX_BLOCKS, "bad args");
+    if (G.n == 0) return GTK_OK;
+    logdet_const_bwd_all_kernel<<<G.n, PW_NT, 0, st>>>(dlogdet, x_len, B, G, C, winv, ns, (float)(C / ns));
+    return check_launch("logdet_const_bwd_all");
 }
 int logdet_const_bwd(const float* dlogdet, const float* x_len, int B, float* dlogs, int C, const float* winv, int ns,
                      float group_count, float* dW, cudaStream_t st) {

@@ -24,6 +24,23 @@ int unsqueeze(const float* x, const float* mask, float* out, float* mask_out, in
               cudaStream_t st);
 int mask_len(const float* mask, float* x_len, int B, int T, cudaStream_t st);
 int invconv_prep(const float* w, int ns, float* winv, float* logdet, cudaStream_t st);
+// per-call constants of up to FLOW_CONST_MAX_BLOCKS flow blocks in one launch (flow_pointwise.cu)
+constexpr int FLOW_CONST_MAX_BLOCKS = 32;
+struct FlowConstJobs {
+    const float* w[FLOW_CONST_MAX_BLOCKS];       // InvConvNear weight [ns][ns] of block k
+    const float* logs[FLOW_CONST_MAX_BLOCKS];    // ActNorm logs [C] of block k (or null)
+    float* winv;                                 // [n][64] inverses, or null
+    float* icld;                                 // [n] log|det W_k|, or null
+    int n;
+};
+struct FlowConstGrads {
+    float* dlogs[FLOW_CONST_MAX_BLOCKS];
+    float* dW[FLOW_CONST_MAX_BLOCKS];
+    int n;
+};
+int flow_consts(const FlowConstJobs& J, int ns, int C, const float* x_len, float* logdet, int B, int accumulate, cudaStream_t st);
+int logdet_const_bwd_all(const float* dlogdet, const float* x_len, int B, const FlowConstGrads& G, int C, const float* winv, int ns,
+                         cudaStream_t st);
 int mix(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int ns, float* z, int B,
         int C, int T, int reverse, cudaStream_t st);
 int mix_bwd(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int ns, const float* dz,

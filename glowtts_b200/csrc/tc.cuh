@@ -16,13 +16,16 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t*
 constexpr int BT = 128;            // frames per CTA tile (UMMA M)
 constexpr int KC = 64;             // channels per k-chunk (128 B of bf16 = one swizzle row)
 constexpr int A_BYTES = BT * KC * 2;
-constexpr int NTHREADS = 256;
+constexpr int NTHREADS = 256;          // weight-gradient kernels: 2 issue warps + 4 drain warps
+constexpr int EPI_NT = 512;            // conv / fused-layer kernels: every warp drains TMEM (16 warps = 4 lane quarters x 4 column parts)
+constexpr int EPI_PARTS = EPI_NT / 128;
 
 struct ConvTcParams {
     int B, T, taps, dil, n_k;      // n_k = padded input channels / 64
     int tile_layout;               // 1: out_f32 / resid_f32 / ts use the tile-private layout (RowIo); ld = column count
     int N, NW, NCH;                // N = NW * NCH output columns, NW % 16 == 0, NW <= 256
     int stages;
+    int cluster;                   // 1 or 2 CTAs per cluster (2: the weight tile is fetched once per pair, TMA multicast)
     int trace;                     // 1: record per-CTA phase timestamps (conv_trace_select)
     int ctl_off;                   // byte offset of the control block behind the operand stages / output staging area
     // ---- plain epilogue: v = acc + bias[n] (+ resid) ; optional mask ; stores
@@ -212,6 +215,29 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
 // mbarrier arrive when all MMAs issued so far by this thread have completed (implies fence::before_thread_sync)
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// ... the same, arriving on the barrier at this offset in every CTA of `cta_mask` (cluster multicast)
+__device__ __forceinline__ void umma_commit_multicast(uint64_t* bar, uint16_t cta_mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(cta_mask) : "memory");
+}
+// TMA load delivered to the same shared-memory offset (and signalling the same mbarrier offset) in every CTA of cta_mask
+__device__ __forceinline__ void tma_load_3d_multicast(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
+                                                      uint16_t cta_mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        " [%0], [%1, {%3, %4, %5}], [%2], %6;"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "h"(cta_mask)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 __device__ __forceinline__ bool elect_one() {

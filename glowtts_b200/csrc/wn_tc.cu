@@ -43,7 +43,7 @@ __device__ __forceinline__ unsigned long long gtimer() {
         if (threadIdx.x == 128 && cta_ < WN_TRACE_CTAS) g_wn_trace[cta_ * 6 + (i)] = gtimer(); \
     } while (0)
 
-__global__ void __launch_bounds__(NTHREADS, 1)
+__global__ void __launch_bounds__(EPI_NT, 1)
 wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmWin,
                 const __grid_constant__ CUtensorMap tmWrs, const __grid_constant__ CUtensorMap tmActs,
                 const __grid_constant__ CUtensorMap tmOut, const WnLayerParams p) {
@@ -63,16 +63,16 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     if (threadIdx.x == 0) {
         for (int s = 0; s < WN_STAGES; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
         mbar_init(&ctl->acc_full, 1);
-        mbar_init(&ctl->acts_ready, NTHREADS);
+        mbar_init(&ctl->acts_ready, EPI_NT);
         mbar_fence_init();
     }
     {
         const float* cond = p.cond ? p.cond + (size_t)b * p.cond_bstride : nullptr;
-        for (int i = threadIdx.x; i < H2; i += NTHREADS) {
+        for (int i = threadIdx.x; i < H2; i += EPI_NT) {
             ctl->bias_in[i] = p.bias_in[i];
             ctl->cond[i] = cond ? cond[i] : 0.f;
         }
-        for (int i = threadIdx.x; i < RS; i += NTHREADS) ctl->bias_rs[i] = p.bias_rs[i];
+        for (int i = threadIdx.x; i < RS; i += EPI_NT) ctl->bias_rs[i] = p.bias_rs[i];
     }
     if (warp == 2) tmem_alloc<512>(&ctl->tmem_base);
     tc_fence_before();
@@ -127,9 +127,9 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     }
     __syncwarp();
 
-    // ---------------------------------------------------------------- epilogues: ALL 8 warps.  Warp w owns TMEM lane
-    // quarter w % 4 (frames) and column half w / 4.
-    const int q = warp & 3, half = warp >> 2;
+    // ---------------------------------------------------------------- epilogues: ALL 16 warps.  Warp w owns TMEM lane
+    // quarter w % 4 (frames) and column part w / 4 of EPI_PARTS.
+    const int q = warp & 3, part = warp >> 2;
     const int r = q * 32 + lane;                         // row of the tile == TMEM lane
     const int t = t0 + r;
     const bool t_ok = t < p.T;
@@ -137,9 +137,9 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
     const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
     RowIo io;
-    io.tp = p.tile_layout; io.tile_id = b * gridDim.x + blockIdx.x; io.r = r; io.frame = frame;
+    io.tp = p.tile_layout; io.tile_id = b * ((p.T + BT - 1) / BT) + blockIdx.x; io.r = r; io.frame = frame;
     const int n_chunks = H / 16;
-    const int ch_lo = half ? (n_chunks + 1) / 2 : 0, ch_hi = half ? n_chunks : (n_chunks + 1) / 2;
+    const int ch_lo = n_chunks * part / EPI_PARTS, ch_hi = n_chunks * (part + 1) / EPI_PARTS;
 
     // ---- epilogue 1: gate -> A operand of GEMM 2
     const unsigned long long dseed = p.drop_p > 0.f ? drop_resolve(p.drop_seed) : 0ull;
@@ -336,7 +336,7 @@ int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, con
     GTK_CUDA(cudaFuncSetAttribute(wn_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(ceil_div(p.T, BT), p.B);
     ProfScope prof("wn_layer_tc", st);
-    wn_layer_kernel<<<grid, NTHREADS, smem, st>>>(tmH, tmWin, tmWrs, tmActs, tmOut, p);
+    wn_layer_kernel<<<grid, EPI_NT, smem, st>>>(tmH, tmWin, tmWrs, tmActs, tmOut, p);
     return check_launch("wn_layer_tc");
 }
 
