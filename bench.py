@@ -39,6 +39,9 @@ CFG = dict(in_channels=80, hidden_channels=192, kernel_size=5, dilation_rate=1, 
 B_PER_GPU, T_TEXT, T_MEL = 32, 180, 860
 FLOP_PER_SQ_FRAME_FWD = 2 * (192 * 80 + 4 * (384 * 192 * 5) + 3 * (384 * 192) + 192 * 192 + 160 * 192)  # one block
 SEED = 1234  # configs/base.json:5
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed `ncu --set full`
+# capture (profiles/); bench.py never runs under a profiler, so the figure is carried here and updated per round.
+NCU_TRAFFIC = {"wn_layer_tc": 23.05e6}   # profiles/ncu_wn_layer_r01.txt: (16.89 + 0.82 MB, 27.50 + 0.89 MB) -> mean bytes / launch
 
 
 def peaks():
@@ -387,19 +390,27 @@ def main():
     if rank == 0:
         pk = peaks()
         s_res, s_e2e = ms_res / args.steps * 1e-3, ms_e2e / args.steps * 1e-3
-        # dominant kernel family: the k=5 WaveNet convolution (fwd + data-gradient launches share the kernel)
+        # dominant kernel: the fused WaveNet layer (k=5 dilated conv GEMM + gate + res/skip 1x1 GEMM, wn_tc.cu);
+        # fp32 path: the k=5 CUDA-core convolution.  Algorithmic flops = valid (unpadded) squeezed frames only.
+        sq_frames_valid = run.frames // CFG["n_sqz"]
         sq_frames_padded = B_PER_GPU * (T_MEL // 2)
-        tag = "conv_tc_kN" if "conv_tc_kN" in prof else "conv_f32_kN"
+        H, K, L = CFG["hidden_channels"], CFG["kernel_size"], CFG["n_layers"]
+        if "wn_layer_tc" in prof:
+            tag = "wn_layer_tc"
+            # per frame: 2H x (H K) conv + RS x H res/skip, RS = 2H except the last layer of a block (H); mean over layers
+            flop_per_frame = 2.0 * (2 * H * H * K) + 2.0 * H * H * (2 * (L - 1) + 1) / L
+        else:
+            tag = "conv_f32_kN"
+            flop_per_frame = 2.0 * (2 * H * H * K)
         n_l, ms_l = prof.get(tag, (0, 0.0))
-        flop_per_launch = 2.0 * 384 * 192 * 5 * sq_frames_padded      # M=384, K=960, N=B*T' (padded frames are computed)
+        flop_per_launch = flop_per_frame * sq_frames_valid
         ach = (flop_per_launch * n_l / (ms_l * 1e-3) / 1e12) if ms_l > 0 else 0.0
-        step_ms_prof = sum(v[1] for v in prof.values()) / max(prof_steps, 1)
         roof = {"kernel": tag, "bound": "tensor", "achieved": ach, "peak": pk["tc_sustained"], "unit": "TFLOP/s",
-                "frac": ach / pk["tc_sustained"], "traffic": None, "peak_source": pk["src"] + " bf16 sustained",
+                "frac": ach / pk["tc_sustained"], "traffic": NCU_TRAFFIC.get(tag), "peak_source": pk["src"] + " bf16 sustained",
                 "launches_per_step": n_l / max(prof_steps, 1), "ms_per_launch": ms_l / max(n_l, 1),
                 "share_of_step": (ms_l / max(prof_steps, 1)) / (s_res * 1e3),
-                "flop_per_launch": flop_per_launch,
-                "how": f"CUDA events around every launch (library profiler), separate pass of {prof_steps} steps",
+                "flop_per_launch": flop_per_launch, "frames_valid": sq_frames_valid, "frames_computed": sq_frames_padded,
+                "how": f"CUDA events around every launch (library profiler), separate eager pass of {prof_steps} steps",
                 "by_tag_ms_per_step": {k: v[1] / max(prof_steps, 1) for k, v in sorted(prof.items())}}
         step_flop = 3.0 * FLOP_PER_SQ_FRAME_FWD * CFG["n_blocks"] * sq_frames_padded
         out = {

@@ -592,7 +592,7 @@ int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, 
     }
     dim3 grid(ceil_div(ceil_div(p.T, BT), p.cluster) * p.cluster, p.B);   // an out-of-range tile only feeds its peer
     p.trace = (epi == g_trace_epi && p.taps == g_trace_taps) ? 1 : 0;
-    ProfScope prof(p.taps > 1 ? "conv_tc_kN" : "conv_tc_k1", st);
+    ProfScope prof(epi == EPI_GATE_BWD ? "conv_tc_gate_bwd" : epi == EPI_AFFINE ? "conv_tc_affine" : p.taps > 1 ? "conv_tc_kN" : "conv_tc_k1", st);
 #define GTK_TC_LAUNCH(COLS, E)                                                                                       \
     do {                                                                                                             \
         GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<COLS, E, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
