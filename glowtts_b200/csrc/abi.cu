@@ -274,6 +274,7 @@ int gtk_tc_colsum(const void* in_bf16, int ld, int n_cols, int groups, long long
 int gtk_debug_wn_trace(unsigned long long* out, int n_ctas) { return tc::wn_trace_read(out, n_ctas); }
 int gtk_debug_conv_trace_select(int epilogue, int taps) { tc::conv_trace_select(epilogue, taps); return GTK_OK; }
 int gtk_debug_conv_trace(unsigned long long* out, int n_ctas) { return tc::conv_trace_read(out, n_ctas); }
+int gtk_debug_conv_wait(long long* out, int n_ctas) { return tc::conv_wait_read(out, n_ctas); }
 int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, const void* wrs_p, const float* bias_in,
                     const float* bias_rs, const float* cond, size_t cond_bstride, const float* mask, int B, int T, int H,
                     int RS, int K, int dil, int first, int last, float drop_p, unsigned long long drop_seed,

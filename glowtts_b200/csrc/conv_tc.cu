@@ -63,6 +63,7 @@ struct SmemCtl {
 // [start, setup done, accumulator complete, epilogue math done, stores issued].  Read with gtk_debug_conv_trace.
 constexpr int CONV_TRACE_CTAS = 512;
 __device__ unsigned long long g_conv_trace[CONV_TRACE_CTAS * 5];
+__device__ long long g_conv_wait[CONV_TRACE_CTAS * 2];      // SM cycles the producer waited on `empty` / the MMA thread on `full`
 static int g_trace_epi = -1, g_trace_taps = -1;
 __device__ __forceinline__ unsigned long long gtimer() {
     unsigned long long t;
@@ -93,6 +94,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int out_chunks = 0;                                  // staged [128 x 64] bf16 output tiles to TMA-store at the end
     CONV_TRACE(0);
     const int n_iter = p.taps * p.n_k;
+    const bool dual = (p.NCH == 1);                      // two interleaved accumulators (see the MMA loop)
 
     const uint32_t cta_rank = CL > 1 ? cluster_ctarank() : 0u;
     if (threadIdx.x == 0) {
@@ -101,7 +103,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_fence_init();
     }
     for (int i = threadIdx.x; i < p.N; i += EPI_NT) ctl->bias[i] = p.bias ? p.bias[i] : 0.f;
-    if (warp == 2) tmem_alloc<TMEM_COLS>(&ctl->tmem_base);
+    if (warp == 2) tmem_alloc<512>(&ctl->tmem_base);
     tc_fence_before();
     if constexpr (CL > 1) cluster_sync_all();             // the peer's barriers exist before anything is multicast
     else __syncthreads();
@@ -113,9 +115,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (lane == 0) {
             tma_prefetch_desc(&tmA);
             tma_prefetch_desc(&tmB);
+            long long w_empty = 0;
             for (int it = 0; it < n_iter; ++it) {
                 const int s = it % p.stages, use = it / p.stages;
-                if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
+                if (use > 0) {
+                    const long long c0 = p.trace ? clock64() : 0;
+                    mbar_wait(&ctl->empty[s], (use - 1) & 1);
+                    if (p.trace) w_empty += clock64() - c0;
+                }
                 const int j = it / p.n_k, kc = it % p.n_k;
                 unsigned char* sa = smem + (size_t)s * stage_bytes;
                 unsigned char* sb = sa + A_BYTES;
@@ -131,28 +138,43 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         tma_load_3d(sb + (size_t)ch * p.NW * KC * 2, &tmB, &ctl->full[s], kc * KC, ch * p.NW, j);
                 }
             }
+            if (p.trace) { const int cta_ = blockIdx.y * gridDim.x + blockIdx.x; if (cta_ < CONV_TRACE_CTAS) g_conv_wait[cta_ * 2] = w_empty; }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             const uint32_t idesc = umma_idesc_bf16(BT, p.NW);
+            long long w_full = 0;
             for (int it = 0; it < n_iter; ++it) {
                 const int s = it % p.stages, use = it / p.stages;
+                const long long c0 = p.trace ? clock64() : 0;
                 mbar_wait(&ctl->full[s], use & 1);
+                if (p.trace) w_full += clock64() - c0;
                 tc_fence_after();
                 const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
                 const uint32_t sb = sa + A_BYTES;
                 const uint64_t adesc = umma_desc_kmajor_sw128(sa);
+                // Back-to-back MMAs into ONE accumulator serialise on its read-modify-write latency (measured: 127 ns
+                // instead of 77 ns per 128x192x16 MMA).  With N <= 256 the k16 steps alternate between two accumulators
+                // (TMEM columns 0.. and 256..), which the epilogue adds.
+                if (dual) {
+                    const uint64_t bdesc = umma_desc_kmajor_sw128(sb);
 #pragma unroll
-                for (int k = 0; k < KC / 16; ++k) {
-                    for (int ch = 0; ch < p.NCH; ++ch) {
-                        const uint64_t bdesc = umma_desc_kmajor_sw128(sb + ch * p.NW * KC * 2);
-                        umma_bf16(tmem + ch * p.NW, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0);
+                    for (int k = 0; k < KC / 16; ++k)
+                        umma_bf16(tmem + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, it != 0 || k >= 2);
+                } else {
+#pragma unroll
+                    for (int k = 0; k < KC / 16; ++k) {
+                        for (int ch = 0; ch < p.NCH; ++ch) {
+                            const uint64_t bdesc = umma_desc_kmajor_sw128(sb + ch * p.NW * KC * 2);
+                            umma_bf16(tmem + ch * p.NW, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0);
+                        }
                     }
                 }
                 if constexpr (CL > 1) umma_commit_multicast(&ctl->empty[s], (uint16_t)((1u << CL) - 1));
                 else umma_commit(&ctl->empty[s]);
             }
             umma_commit(&ctl->acc_full);
+            if (p.trace) { const int cta_ = blockIdx.y * gridDim.x + blockIdx.x; if (cta_ < CONV_TRACE_CTAS) g_conv_wait[cta_ * 2 + 1] = w_full; }
         }
     }
     __syncwarp();
@@ -175,7 +197,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
                 const int c0 = cc * 16;
                 float v[16];
-                tmem_ld16(trow + c0, v);
+                tmem_ld16_dual(trow + c0, dual, v);
                 if (!t_ok) continue;
 #pragma unroll
                 for (int i = 0; i < 16; ++i) v[i] += ctl->bias[c0 + i];
@@ -208,7 +230,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
                 const int c0 = cc * 16;
                 float d[16];
-                tmem_ld16(trow + c0, d);
+                tmem_ld16_dual(trow + c0, dual, d);
                 if (!t_ok) continue;
                 float tt[16], ss[16], dt[16], ds[16];
                 row_load_bf16x16(p.ts, 2 * H, c0, io, tt);
@@ -242,8 +264,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
                 const int c0 = cc * 16;
                 float m[16], lg[16];
-                tmem_ld16(trow + c0, m);
-                tmem_ld16(trow + Ch + c0, lg);
+                tmem_ld16_dual(trow + c0, dual, m);
+                tmem_ld16_dual(trow + Ch + c0, dual, lg);
                 if (!t_ok) continue;
                 // all loads of the chunk first (x and z may alias as far as the compiler knows: loads behind stores
                 // would serialise into one L2 round trip per channel)
@@ -295,7 +317,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if constexpr (CL > 1) cluster_sync_all();             // no CTA leaves while the peer's commits may still arrive here
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc<TMEM_COLS>(tmem);
+        tmem_dealloc<512>(tmem);
     }
 }
 
@@ -303,6 +325,11 @@ void conv_trace_select(int epi, int taps) { g_trace_epi = epi; g_trace_taps = ta
 int conv_trace_read(unsigned long long* out, int n_ctas) {
     GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= CONV_TRACE_CTAS, "n_ctas");
     GTK_CUDA(cudaMemcpyFromSymbol(out, g_conv_trace, size_t(n_ctas) * 5 * sizeof(unsigned long long)));
+    return GTK_OK;
+}
+int conv_wait_read(long long* out, int n_ctas) {
+    GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= CONV_TRACE_CTAS, "n_ctas");
+    GTK_CUDA(cudaMemcpyFromSymbol(out, g_conv_wait, size_t(n_ctas) * 2 * sizeof(long long)));
     return GTK_OK;
 }
 

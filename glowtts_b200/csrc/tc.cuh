@@ -85,6 +85,7 @@ int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, con
 int wn_trace_read(unsigned long long* out, int n_ctas);
 void conv_trace_select(int epi, int taps);
 int conv_trace_read(unsigned long long* out, int n_ctas);
+int conv_wait_read(long long* out, int n_ctas);
 
 int wgrad_tc_launch(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, float* dw, int B,
                     int T, int M, int Cin, int K, int dil, cudaStream_t st);
@@ -275,6 +276,17 @@ __device__ __forceinline__ void load_bf16x16(const __nv_bfloat16* src, float (&v
         const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
         v[2 * i] = __low2float(h);
         v[2 * i + 1] = __high2float(h);
+    }
+}
+
+// accumulator split over two TMEM column ranges (base and base + 256): load both halves and add
+__device__ __forceinline__ void tmem_ld16_dual(uint32_t taddr, bool dual, float (&v)[16]) {
+    tmem_ld16(taddr, v);
+    if (dual) {
+        float w[16];
+        tmem_ld16(taddr + 256, w);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] += w[i];
     }
 }
 

@@ -187,6 +187,8 @@ int gtk_debug_wn_trace(unsigned long long* out, int n_ctas);
  * epilogue math done, stores issued}] of the last selected launch.  Synchronises the device. */
 int gtk_debug_conv_trace_select(int epilogue, int taps);
 int gtk_debug_conv_trace(unsigned long long* out, int n_ctas);
+/* out[cta * 2 + {0: SM cycles the TMA producer waited for a free stage, 1: cycles the MMA thread waited for data}] */
+int gtk_debug_conv_wait(long long* out, int n_ctas);
 
 /* ---- whole decoder (models.py:719-789) --------------------------------------------------- */
 typedef struct gtk_decoder_desc {

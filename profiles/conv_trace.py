@@ -28,4 +28,8 @@ for label, epi, taps in (("in_layer data gradient (plain, k=5; last launch = lay
     print(f"{'phase':9s} {'min':>7s} {'median':>7s} {'max':>7s}  (us per CTA)")
     for i, n in enumerate(names):
         print(f"{n:9s} {d[:, i].min():7.2f} {np.median(d[:, i]):7.2f} {d[:, i].max():7.2f}")
+    wbuf = (ctypes.c_longlong * (n_ctas * 2))()
+    _lib.call("gtk_debug_conv_wait", wbuf, n_ctas)
+    w = np.array(list(wbuf), dtype=np.int64).reshape(n_ctas, 2) / 1.965e3      # cycles -> us at 1965 MHz
+    print(f"mainloop waits (median): producer on a free stage {np.median(w[:, 0]):.2f} us, MMA thread on data {np.median(w[:, 1]):.2f} us")
 _lib.call("gtk_debug_conv_trace_select", -1, -1)
