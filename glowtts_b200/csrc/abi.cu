@@ -275,6 +275,9 @@ int gtk_debug_wn_trace(unsigned long long* out, int n_ctas) { return tc::wn_trac
 int gtk_debug_conv_trace_select(int epilogue, int taps) { tc::conv_trace_select(epilogue, taps); return GTK_OK; }
 int gtk_debug_conv_trace(unsigned long long* out, int n_ctas) { return tc::conv_trace_read(out, n_ctas); }
 int gtk_debug_conv_wait(long long* out, int n_ctas) { return tc::conv_wait_read(out, n_ctas); }
+int gtk_debug_shift_probe(const void* a, const void* b, float* out, void* stream) {
+    return tc::shift_probe(static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b), out, ST);
+}
 int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, const void* wrs_p, const float* bias_in,
                     const float* bias_rs, const float* cond, size_t cond_bstride, const float* mask, int B, int T, int H,
                     int RS, int K, int dil, int first, int last, float drop_p, unsigned long long drop_seed,

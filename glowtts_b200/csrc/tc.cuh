@@ -86,6 +86,7 @@ int wn_trace_read(unsigned long long* out, int n_ctas);
 void conv_trace_select(int epi, int taps);
 int conv_trace_read(unsigned long long* out, int n_ctas);
 int conv_wait_read(long long* out, int n_ctas);
+int shift_probe(const __nv_bfloat16* a, const __nv_bfloat16* b, float* out, cudaStream_t st);
 
 int wgrad_tc_launch(const __nv_bfloat16* dy, int ld_y, int cols_y, const __nv_bfloat16* x, int ld_x, int cols_x, float* dw, int B,
                     int T, int M, int Cin, int K, int dil, cudaStream_t st);

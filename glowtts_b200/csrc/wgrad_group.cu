@@ -7,8 +7,8 @@
 // Work = (conv, 128-row M tile, tap) tiles x (utterance, 64-frame chunk) k-steps.  All tiles of all convs are laid
 // end to end (weighted by the bytes one k-step stages) and cut into `grid` equal contiguous shares, one per SM
 // ("stream-K"): no wave quantisation, no per-conv launch, and each CTA writes at most a few partial tiles.  A CTA
-// walks its segments with one TMA producer thread, one MMA thread and four epilogue warps; the two 256-column TMEM
-// accumulators alternate so the drain of one segment overlaps the MMAs of the next.
+// walks its segments with one TMA producer thread, one MMA thread and four epilogue warps; two 256-column TMEM
+// accumulators take alternate k16 steps (independent MMA chains) and are added when a segment is drained.
 //
 // Operands are frame-major bf16 ([B, T, channels]; reduction dim = rows), i.e. MN-major UMMA operands fetched as
 // {64 channels x 64 frames} SWIZZLE_128B boxes, the conv tap being a shifted (zero-filled) box of X -- as in
@@ -112,9 +112,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
                 const GgJobDev J = p.job[Tl.job];
                 const int N = (J.ones && Tl.tap == 0) ? (GG_ONES_BLK + 1) * 64 : J.n_blk * 64;
                 const uint32_t idesc = umma_idesc_bf16(128, N, 1, 1);
-                const int a = sg & 1, ause = sg >> 1;
-                if (ause > 0) { mbar_wait(&ctl->acc_empty[a], (ause - 1) & 1); tc_fence_after(); }
-                const uint32_t acc = tmem + a * 256;
+                // Two accumulators (TMEM columns 0.. and 256..) take alternate k16 steps: back-to-back MMAs into one
+                // accumulator serialise on its read-modify-write latency.  The epilogue adds them; the next segment
+                // starts when it has drained both (segments are ~100 k-steps long, the drain is a few per cent).
+                if (sg > 0) { mbar_wait(&ctl->acc_empty[0], (sg - 1) & 1); tc_fence_after(); }
                 for (int step = S.s_lo; step < S.s_hi; ++step, ++it) {
                     const int s = it % GG_STAGES, use = it / GG_STAGES;
                     mbar_wait(&ctl->full[s], use & 1);
@@ -125,11 +126,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
                     for (int k = 0; k < GG_TK / 16; ++k) {
                         const uint64_t adesc = umma_desc_mnmajor_sw128(sa + k * 2048, GG_BOX, 1024);
                         const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + k * 2048, GG_BOX, 1024);
-                        umma_bf16(acc, adesc, bdesc, idesc, (step != S.s_lo) || k != 0);
+                        umma_bf16(tmem + (k & 1) * 256, adesc, bdesc, idesc, (step != S.s_lo) || k >= 2);
                     }
                     umma_commit(&ctl->empty[s]);
                 }
-                umma_commit(&ctl->acc_full[a]);
+                umma_commit(&ctl->acc_full[0]);
             }
         }
     } else if (warp >= 4) {
@@ -138,26 +139,25 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
             const GgSeg S = p.seg[me.seg0 + sg];
             const GgTile Tl = p.tile[S.tile];
             const GgJobDev J = p.job[Tl.job];
-            const int a = sg & 1, ause = sg >> 1;
-            mbar_wait(&ctl->acc_full[a], ause & 1);
+            mbar_wait(&ctl->acc_full[0], sg & 1);
             tc_fence_after();
-            const uint32_t trow = tmem + a * 256 + ((uint32_t)(q * 32) << 16);
+            const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
             float* prow = p.part + (size_t)S.slot * GG_SLOT_FLOATS + (size_t)(q * 32 + lane) * 256;
             for (int c0 = 0; c0 < J.n_blk * 64; c0 += 16) {
                 float v[16];
-                tmem_ld16(trow + c0, v);
+                tmem_ld16_dual(trow + c0, true, v);
                 float4* o4 = reinterpret_cast<float4*>(prow + c0);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
             }
             if (J.ones && Tl.tap == 0) {
                 float v[16];
-                tmem_ld16(trow + GG_ONES_BLK * 64, v);
+                tmem_ld16_dual(trow + GG_ONES_BLK * 64, true, v);
                 prow[GG_ONES_BLK * 64] = v[0];
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&ctl->acc_empty[a]);
+            if (lane == 0) mbar_arrive(&ctl->acc_empty[0]);
         }
     }
     tc_fence_before();

@@ -189,6 +189,10 @@ int gtk_debug_conv_trace_select(int epilogue, int taps);
 int gtk_debug_conv_trace(unsigned long long* out, int n_ctas);
 /* out[cta * 2 + {0: SM cycles the TMA producer waited for a free stage, 1: cycles the MMA thread waited for data}] */
 int gtk_debug_conv_wait(long long* out, int n_ctas);
+/* Hardware probe (debug_shift.cu): D_s = A[s : s+128] B^T for row shifts s = 1..4 of a K-major SWIZZLE_128B operand,
+ * descriptor base-offset field 0 (mode 0) or (addr >> 7) & 7 (mode 1).  a [136][64] bf16, b [64][64] bf16,
+ * out [(s-1)*2 + mode][128][64] fp32. */
+int gtk_debug_shift_probe(const void* a, const void* b, float* out, void* stream);
 
 /* ---- whole decoder (models.py:719-789) --------------------------------------------------- */
 typedef struct gtk_decoder_desc {
