@@ -370,8 +370,22 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
             const bf16* acts = reinterpret_cast<const bf16*>(act + A.acts[i]);
             const bf16* h_i = reinterpret_cast<const bf16*>(act + A.h[i]);
             const bool want_dcond = P.cond && G.cond;
-            // res_skip 1x1: data gradient fused with the gate backward
             GTK_TRY(queue(P.rs_g[i], P.rs_v[i], G.rs_g[i], G.rs_v[i], G.rs_b[i], drs_i, 2 * H, RS, acts, H, H, RS, H, 1, 1));
+            GTK_TRY(queue(P.in_g[i], P.in_v[i], G.in_g[i], G.in_v[i], G.in_b[i], dxin, 2 * H, 2 * H, h_i, H, H, 2 * H, H, K, dil));
+            if (!want_dcond && tc::wn_bwd_supported(H, K, dil)) {
+                // res_skip data gradient -> gate backward -> in_layer data gradient in ONE kernel (wn_bwd_tc.cu)
+                tc::WnBwdParams p;
+                memset(&p, 0, sizeof(p));
+                p.B = B; p.T = T; p.H = H; p.RS = RS; p.taps = K; p.dil = dil;
+                p.mask = msq; p.ts = ts;
+                p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, i);
+                p.resid_f32 = (i < D.L - 1) ? dhf[(i + 1) & 1] : nullptr;
+                p.out_f32 = dhf[i & 1];
+                GTK_TRY(tc::wn_bwd_layer_launch(drs_i, 2 * H, pk + Q.t_rs[i], pk + Q.t_in[i], dxin, i > 0 ? drs_of(i - 1) : dh0,
+                                                i > 0 ? 2 * H : H, p, st));
+                continue;
+            }
+            // res_skip 1x1: data gradient fused with the gate backward
             {
                 tc::ConvTcParams p;
                 memset(&p, 0, sizeof(p));
@@ -388,7 +402,6 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 GTK_TRY(tc::colsum_frames(d->p_dropout > 0.f ? dgate : dxin, 2 * H, 2 * H, B, T, G.cond + (size_t)i * 2 * H,
                                           (size_t)2 * H * D.L, st));
             // in_layer dilated conv
-            GTK_TRY(queue(P.in_g[i], P.in_v[i], G.in_g[i], G.in_v[i], G.in_b[i], dxin, 2 * H, 2 * H, h_i, H, H, 2 * H, H, K, dil));
             {
                 tc::ConvTcParams p;
                 memset(&p, 0, sizeof(p));
@@ -401,7 +414,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 else       { p.out_bf16 = dh0; p.ld_bf16 = H; }
                 GTK_TRY(tc::conv_tc_launch(dxin, 2 * H, pk + Q.t_in[i], p, tc::EPI_PLAIN, st));
             }
-        }
+                }
         // start conv: h0 = (W x0 + b) * mask   (dh0 is already masked)
         GTK_TRY(queue(P.start_g, P.start_v, G.start_g, G.start_v, G.start_b, dh0, H, H, a0, ldCh, ldCh, H, Ch, 1, 1));
         {

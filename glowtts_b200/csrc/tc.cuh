@@ -82,6 +82,23 @@ struct WnLayerParams {
 int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, const __nv_bfloat16* wrs_p, WnLayerParams p,
                     cudaStream_t st);
 
+// Backward of one WaveNet layer fused into one kernel (wn_bwd_tc.cu).
+struct WnBwdParams {
+    int B, T, H, RS, taps, dil;
+    const float* mask;             // [B, T]
+    const __nv_bfloat16* ts;       // saved tanh | sigmoid of the layer, tile-private layout (ld = 2H)
+    float drop_p;
+    DropSeed drop_seed;
+    const float* resid_f32;        // fp32 carry of d(h) from the layer above (tile-private layout, ld = H) or null
+    float* out_f32;                // fp32 carry written for the layer below (tile-private layout, ld = H)
+    int dbg;
+};
+bool wn_bwd_supported(int H, int taps, int dil);
+// drs: [B,T,ld_drs] frames (columns [0,RS) = [d(h_next) mask | d(skip)]); wrs_t / win_t: data-gradient weight packs;
+// dxin: [B,T,2H] frames out; out_bf16: [B,T,ld_out] frames, columns [0,H) = d(h) mask out.
+int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat16* wrs_t, const __nv_bfloat16* win_t,
+                        __nv_bfloat16* dxin, __nv_bfloat16* out_bf16, int ld_out, WnBwdParams p, cudaStream_t st);
+
 int wn_trace_read(unsigned long long* out, int n_ctas);
 void conv_trace_select(int epi, int taps);
 int conv_trace_read(unsigned long long* out, int n_ctas);

@@ -1,0 +1,300 @@
+// glowtts_b200/csrc/wn_bwd_tc.cu -- backward of one WaveNet layer (modules.py:151-170) as ONE tcgen05 kernel per tile:
+//
+//   GEMM a   d(acts)[t, 0:H] = drs[t, 0:RS] * Wrs                       (data gradient of the 1x1 res/skip conv)
+//   epilogue d(xin)[t, 0:2H] = gate backward of d(acts) with the saved tanh | sigmoid, dropout mask re-applied
+//            -> written as bf16 straight into a shared-memory A operand [128 frames x 2H] (SWIZZLE_128B), and from there
+//               TMA-stored to HBM for the weight-gradient launch
+//   GEMM b   d(h)[t, 0:H]    = sum_j d(xin)[t + j dil - halo, :] * Win_j^T   (data gradient of the dilated conv)
+//            -- every tap reads the SAME shared-memory tile through a row-shifted UMMA descriptor (the swizzle is a
+//               function of the address only, profiles/shift_probe.py), so d(xin) never comes back from L2
+//   epilogue d(h) (+ fp32 carry of the residual path) * mask -> fp32 carry + bf16 operand of the next layer down
+//
+// Tiles overlap: a CTA computes d(xin) for 128 frames [t0 - halo, t0 + 128 - halo) but owns only the 128 - 2 halo output
+// frames [t0, t0 + 128 - 2 halo), halo = (K/2) dil (base config: 124 of 128 frames, no inter-CTA dependency).
+#include <stdlib.h>
+#include <string.h>
+
+#include "tc.cuh"
+#include "ops.h"
+
+namespace gtk {
+namespace tc {
+
+constexpr int WB_RING = 120 * 1024;          // operand ring behind the d(xin) tile: 3 x (16 + 24) KB or 5 x 24 KB
+constexpr int WB_MAX_STAGES = 8;
+
+struct WbCtl {
+    uint64_t full[WB_MAX_STAGES], empty[WB_MAX_STAGES], acc_full, acts_ready;
+    uint32_t tmem_base;
+};
+
+// how many phases barrier slot s completed during GEMM a (slots are re-used, re-cut, by GEMM b: parities continue)
+__device__ __forceinline__ int ctl_uses(int nka, int n_sa, int s) { return (s < nka && s < n_sa) ? (nka - 1 - s) / n_sa + 1 : 0; }
+
+// RowIo of frame f of utterance b for the tile-private tensors (addressed by frame, whatever the tiling of the kernel)
+__device__ __forceinline__ RowIo frame_io(int b, int f, int T) {
+    RowIo io;
+    io.tp = 1;
+    io.tile_id = b * ((T + BT - 1) / BT) + (f >> 7);
+    io.r = f & 127;
+    io.frame = (size_t)b * T + f;
+    return io;
+}
+
+__global__ void __launch_bounds__(EPI_NT, 1)
+wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_constant__ CUtensorMap tmWrs,
+                    const __grid_constant__ CUtensorMap tmWin, const __grid_constant__ CUtensorMap tmDxin,
+                    const __grid_constant__ CUtensorMap tmOut, const WnBwdParams p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int H = p.H, H2 = 2 * p.H;
+    const int nka = (p.RS + KC - 1) / KC, nkb = H2 / KC;       // k-chunks of GEMM a / of one tap of GEMM b
+    const int x_bytes = nkb * A_BYTES;                         // d(xin) tile: nkb chunks of [128 x 64] bf16
+    unsigned char* ring = smem + x_bytes;
+    const int sa_bytes = A_BYTES + H * KC * 2, sb_bytes = H * KC * 2;
+    const int n_sa = min(WB_MAX_STAGES, WB_RING / sa_bytes), n_sb = min(WB_MAX_STAGES, WB_RING / sb_bytes);
+    WbCtl* ctl = reinterpret_cast<WbCtl*>(ring + WB_RING);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int halo = (p.taps / 2) * p.dil, tile_out = BT - 2 * halo;
+    const int t0 = blockIdx.x * tile_out, b = blockIdx.y;
+    const int n_b = p.taps * nkb;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < WB_MAX_STAGES; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
+        mbar_init(&ctl->acc_full, 1);
+        mbar_init(&ctl->acts_ready, EPI_NT);
+        mbar_fence_init();
+    }
+    if (warp == 2) tmem_alloc<512>(&ctl->tmem_base);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = ctl->tmem_base;
+    const uint32_t idesc = umma_idesc_bf16(BT, H);
+
+    // ---------------------------------------------------------------- TMA producer
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmDrs);
+        tma_prefetch_desc(&tmWrs);
+        tma_prefetch_desc(&tmWin);
+        for (int kc = 0; kc < nka; ++kc) {
+            const int s = kc % n_sa, use = kc / n_sa;
+            if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
+            unsigned char* sa = ring + (size_t)s * sa_bytes;
+            mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)sa_bytes);
+            tma_load_3d(sa, &tmDrs, &ctl->full[s], kc * KC, t0 - halo, b);
+            tma_load_2d(sa + A_BYTES, &tmWrs, &ctl->full[s], kc * KC, 0);
+        }
+        // the ring is re-cut into weight-only stages for GEMM b once every GEMM-a MMA has read its operands; the first
+        // n_sb tiles are prefetched now (they land while the gate-backward epilogue runs), the rest follows below --
+        // this thread must first deliver its share of epilogue a, or GEMM b (which frees the stages) never starts
+        mbar_wait(&ctl->acc_full, 0);
+        for (int it = 0; it < min(n_sb, n_b); ++it) {
+            const int j = it / nkb, kc = it % nkb;
+            mbar_arrive_expect_tx(&ctl->full[it], (uint32_t)sb_bytes);
+            tma_load_3d(ring + (size_t)it * sb_bytes, &tmWin, &ctl->full[it], kc * KC, 0, j);
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ---------------------------------------------------------------- GEMM a
+        for (int kc = 0; kc < nka; ++kc) {
+            const int s = kc % n_sa, use = kc / n_sa;
+            mbar_wait(&ctl->full[s], use & 1);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(ring + (size_t)s * sa_bytes);
+            const uint64_t adesc = umma_desc_kmajor_sw128(sa), bdesc = umma_desc_kmajor_sw128(sa + A_BYTES);
+#pragma unroll
+            for (int k = 0; k < KC / 16; ++k)                  // two accumulators take alternate k16 steps (conv_tc.cu)
+                umma_bf16(tmem + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, kc != 0 || k >= 2);
+            umma_commit(&ctl->empty[s]);
+        }
+        umma_commit(&ctl->acc_full);
+    }
+    __syncwarp();
+
+    // ---------------------------------------------------------------- epilogue a: gate backward -> d(xin) tile in smem
+    const int q = warp & 3, part = warp >> 2;
+    const int r = q * 32 + lane;
+    const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+    const int nck = H / 16;
+    {
+        const int f = t0 - halo + r;
+        const bool ok = f >= 0 && f < p.T;
+        const RowIo io = frame_io(b, ok ? f : 0, p.T);
+        const unsigned long long dseed = p.drop_p > 0.f ? drop_resolve(p.drop_seed) : 0ull;
+        mbar_wait(&ctl->acc_full, 0);
+        tc_fence_after();
+        for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
+            const int c0 = cc * 16;
+            float d[16], dt[16], ds[16];
+            tmem_ld16_dual(trow + c0, true, d);
+            if (ok) {
+                float tt[16], ss[16];
+                row_load_bf16x16(p.ts, H2, c0, io, tt);
+                row_load_bf16x16(p.ts, H2, H + c0, io, ss);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    dt[i] = d[i] * ss[i] * (1.f - tt[i] * tt[i]);
+                    ds[i] = d[i] * tt[i] * ss[i] * (1.f - ss[i]);
+                }
+                if (p.drop_p > 0.f) {
+                    float sc[16];
+                    dropout_scale16(dseed, (unsigned long long)io.frame * H2 + c0, p.drop_p, sc);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) dt[i] *= sc[i];
+                    dropout_scale16(dseed, (unsigned long long)io.frame * H2 + H + c0, p.drop_p, sc);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) ds[i] *= sc[i];
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) { dt[i] = 0.f; ds[i] = 0.f; }   // outside the utterance: the taps read zeros
+            }
+            stage_bf16x16_sw128(smem, A_BYTES, r, c0, dt);
+            stage_bf16x16_sw128(smem, A_BYTES, r, H + c0, ds);
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        mbar_arrive(&ctl->acts_ready);
+    }
+
+    // ---------------------------------------------------------------- GEMM b: taps = row-shifted views of the smem tile
+    if (warp == 0 && lane == 0) {
+        for (int it = n_sb; it < n_b; ++it) {
+            const int s = it % n_sb, use = it / n_sb;
+            mbar_wait(&ctl->empty[s], (ctl_uses(nka, n_sa, s) + use - 1) & 1);
+            const int j = it / nkb, kc = it % nkb;
+            mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)sb_bytes);
+            tma_load_3d(ring + (size_t)s * sb_bytes, &tmWin, &ctl->full[s], kc * KC, 0, j);
+        }
+    } else if (warp == 1 && lane == 0) {
+        mbar_wait(&ctl->acts_ready, 0);
+        tc_fence_after();
+        if (!(p.dbg & 1)) {
+        // d(xin) of the OWNED frames [t0, t0 + tile_out) for the weight-gradient launch: rows halo.. of the tile (a TMA
+        // store must not start at a negative coordinate; the swizzle is address-based, so a row-offset source is fine)
+        for (int kc = 0; kc < nkb; ++kc) tma_store_3d(&tmDxin, smem + (size_t)kc * A_BYTES + halo * 128, kc * KC, t0, b);
+        tma_store_commit();
+        }
+        for (int it = 0; it < n_b; ++it) {
+            const int s = it % n_sb, use = it / n_sb;
+            mbar_wait(&ctl->full[s], (ctl_uses(nka, n_sa, s) + use) & 1);
+            tc_fence_after();
+            const int j = it / nkb, kc = it % nkb;
+            const uint64_t adesc = umma_desc_kmajor_sw128(smem_u32(smem + (size_t)kc * A_BYTES) + ((p.dbg & 4) ? 0u : (uint32_t)(j * p.dil) * 128u));
+            const uint64_t bdesc = umma_desc_kmajor_sw128(smem_u32(ring + (size_t)s * sb_bytes));
+#pragma unroll
+            for (int k = 0; k < KC / 16; ++k)
+                umma_bf16(tmem + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, it != 0 || k >= 2);
+            umma_commit(&ctl->empty[s]);
+        }
+        umma_commit(&ctl->acc_full);
+    }
+    __syncwarp();
+
+    // ---------------------------------------------------------------- epilogue b: residual carry, mask, outputs
+    {
+        const int f = t0 + r;
+        const bool ok = r < tile_out && f < p.T;
+        const RowIo io = frame_io(b, ok ? f : 0, p.T);
+        const float mk = (p.mask && ok) ? p.mask[(size_t)b * p.T + f] : 1.f;
+        mbar_wait(&ctl->acc_full, 1);
+        tc_fence_after();
+        for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
+            const int c0 = cc * 16;
+            float v[16];
+            tmem_ld16_dual(trow + c0, true, v);
+            if (!ok) continue;
+            if (p.resid_f32) {
+                float x[16];
+                row_load_f32x16(p.resid_f32, H, c0, io, x);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = (v[i] + x[i] * mk) * mk;      // resid and output both masked (modules.py:166)
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] *= mk;
+            }
+            if (p.out_f32) row_store_f32x16(p.out_f32, H, c0, io, v);
+            stage_bf16x16_sw128(ring, A_BYTES, r, c0, v);
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1 && lane == 0) {
+        if (!(p.dbg & 2)) {
+        for (int kc = 0; kc < H / KC; ++kc) tma_store_3d(&tmOut, ring + (size_t)kc * A_BYTES, kc * KC, t0, b);
+        tma_store_commit();
+        }
+        tma_store_wait_read();
+    }
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem);
+    }
+}
+
+int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat16* wrs_t, const __nv_bfloat16* win_t,
+                        __nv_bfloat16* dxin, __nv_bfloat16* out_bf16, int ld_out, WnBwdParams p, cudaStream_t st) {
+    GTK_REQUIRE(drs && wrs_t && win_t && dxin && out_bf16 && p.ts && p.out_f32, "null");
+    GTK_REQUIRE(p.H % KC == 0 && p.H <= 256 && (p.RS == p.H || p.RS == 2 * p.H), "hidden / res_skip channels");
+    GTK_REQUIRE(p.taps >= 1 && (p.taps & 1) && p.dil >= 1 && wn_bwd_supported(p.H, p.taps, p.dil), "conv shape not supported by the fused backward");
+    GTK_REQUIRE(ld_drs % 8 == 0 && ld_out % 8 == 0 && ld_drs >= p.RS && ld_out >= p.H, "frame pitch");
+    if (p.B == 0 || p.T == 0) return GTK_OK;
+    const int H = p.H, halo = (p.taps / 2) * p.dil, tile_out = BT - 2 * halo;
+    const int rs_pad = ceil_div(p.RS, KC) * KC;
+    CUtensorMap tmDrs, tmWrs, tmWin, tmDxin, tmOut;
+    {
+        const uint64_t dims[3] = {(uint64_t)rs_pad, (uint64_t)p.T, (uint64_t)p.B};
+        const uint64_t strides[2] = {(uint64_t)ld_drs * 2, (uint64_t)ld_drs * 2 * p.T};
+        const uint32_t box[3] = {KC, BT, 1};
+        int rc = make_tmap_bf16(&tmDrs, drs, 3, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    {   // data-gradient pack of the res/skip weight: [H rows (N)][rs_pad columns (K)]
+        const uint64_t dims[2] = {(uint64_t)rs_pad, (uint64_t)H};
+        const uint64_t strides[1] = {(uint64_t)rs_pad * 2};
+        const uint32_t box[2] = {KC, (uint32_t)H};
+        int rc = make_tmap_bf16(&tmWrs, wrs_t, 2, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    {   // data-gradient pack of the in_layer weight: [taps][H rows (N)][2H columns (K)]
+        const uint64_t dims[3] = {(uint64_t)2 * H, (uint64_t)H, (uint64_t)p.taps};
+        const uint64_t strides[2] = {(uint64_t)2 * H * 2, (uint64_t)2 * H * 2 * H};
+        const uint32_t box[3] = {KC, (uint32_t)H, 1};
+        int rc = make_tmap_bf16(&tmWin, win_t, 3, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    {
+        const uint64_t dims[3] = {(uint64_t)2 * H, (uint64_t)p.T, (uint64_t)p.B};
+        const uint64_t strides[2] = {(uint64_t)2 * H * 2, (uint64_t)2 * H * 2 * p.T};
+        const uint32_t box[3] = {KC, (uint32_t)tile_out, 1};
+        int rc = make_tmap_bf16(&tmDxin, dxin, 3, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    {
+        const uint64_t dims[3] = {(uint64_t)H, (uint64_t)p.T, (uint64_t)p.B};
+        const uint64_t strides[2] = {(uint64_t)ld_out * 2, (uint64_t)ld_out * 2 * p.T};
+        const uint32_t box[3] = {KC, (uint32_t)tile_out, 1};
+        int rc = make_tmap_bf16(&tmOut, out_bf16, 3, dims, strides, box, true);
+        if (rc) return rc;
+    }
+    const size_t smem = (size_t)(2 * H / KC) * A_BYTES + WB_RING + sizeof(WbCtl) + 1024;
+    GTK_REQUIRE(smem <= 227 * 1024, "tile does not fit in shared memory");
+    GTK_CUDA(cudaFuncSetAttribute(wn_bwd_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid(ceil_div(p.T, tile_out), p.B);
+    { const char* e = getenv("GTK_WB_DBG"); p.dbg = e ? atoi(e) : 0; }
+    ProfScope prof("wn_bwd_layer_tc", st);
+    wn_bwd_layer_kernel<<<grid, EPI_NT, smem, st>>>(tmDrs, tmWrs, tmWin, tmDxin, tmOut, p);
+    return check_launch("wn_bwd_layer_tc");
+}
+
+// The fused backward needs the whole d(xin) tile (2H columns) plus a useful operand ring in shared memory and a halo
+// that leaves most of the 128-frame tile as output.
+bool wn_bwd_supported(int H, int taps, int dil) {
+    const int halo = (taps / 2) * dil;
+    return H % KC == 0 && (size_t)(2 * H / KC) * A_BYTES + WB_RING + sizeof(WbCtl) + 1024 <= 227 * 1024 && 2 * halo <= 32 &&
+           WB_RING / (A_BYTES + H * KC * 2) >= 2;
+}
+
+}  // namespace tc
+}  // namespace gtk
