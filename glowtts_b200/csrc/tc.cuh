@@ -91,7 +91,6 @@ struct WnBwdParams {
     DropSeed drop_seed;
     const float* resid_f32;        // fp32 carry of d(h) from the layer above (tile-private layout, ld = H) or null
     float* out_f32;                // fp32 carry written for the layer below (tile-private layout, ld = H)
-    int dbg;
 };
 bool wn_bwd_supported(int H, int taps, int dil);
 // drs: [B,T,ld_drs] frames (columns [0,RS) = [d(h_next) mask | d(skip)]); wrs_t / win_t: data-gradient weight packs;
@@ -100,6 +99,7 @@ int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat1
                         __nv_bfloat16* dxin, __nv_bfloat16* out_bf16, int ld_out, WnBwdParams p, cudaStream_t st);
 
 int wn_trace_read(unsigned long long* out, int n_ctas);
+int wb_trace_read(unsigned long long* out, int n_ctas);
 void conv_trace_select(int epi, int taps);
 int conv_trace_read(unsigned long long* out, int n_ctas);
 int conv_wait_read(long long* out, int n_ctas);

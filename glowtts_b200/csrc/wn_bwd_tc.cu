@@ -24,12 +24,27 @@ constexpr int WB_RING = 120 * 1024;          // operand ring behind the d(xin) t
 constexpr int WB_MAX_STAGES = 8;
 
 struct WbCtl {
-    uint64_t full[WB_MAX_STAGES], empty[WB_MAX_STAGES], acc_full, acts_ready;
+    uint64_t full[WB_MAX_STAGES], empty[WB_MAX_STAGES];        // GEMM a ring
+    uint64_t full_b[WB_MAX_STAGES], empty_b[WB_MAX_STAGES];    // GEMM b ring (same memory, re-cut; cluster-wide `empty`)
+    uint64_t acc_full, acts_ready;
     uint32_t tmem_base;
 };
+constexpr int WB_CL = 2;                     // CTAs per cluster: every in_layer weight tile is fetched once per pair
 
-// how many phases barrier slot s completed during GEMM a (slots are re-used, re-cut, by GEMM b: parities continue)
-__device__ __forceinline__ int ctl_uses(int nka, int n_sa, int s) { return (s < nka && s < n_sa) ? (nka - 1 - s) / n_sa + 1 : 0; }
+// Phase timestamps (globaltimer, ns) per CTA of the last launch: [start, setup, GEMM a done, epilogue a done, GEMM b done,
+// epilogue b done, end]; read with gtk_debug_wb_trace.
+constexpr int WB_TRACE_CTAS = 512;
+__device__ unsigned long long g_wb_trace[WB_TRACE_CTAS * 7];
+__device__ __forceinline__ unsigned long long wb_timer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define WB_TRACE(i)                                                                         \
+    do {                                                                                    \
+        const int cta_ = blockIdx.y * gridDim.x + blockIdx.x;                               \
+        if (threadIdx.x == 128 && cta_ < WB_TRACE_CTAS) g_wb_trace[cta_ * 7 + (i)] = wb_timer(); \
+    } while (0)
 
 // RowIo of frame f of utterance b for the tile-private tensors (addressed by frame, whatever the tiling of the kernel)
 __device__ __forceinline__ RowIo frame_io(int b, int f, int T) {
@@ -58,19 +73,26 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
     const int halo = (p.taps / 2) * p.dil, tile_out = BT - 2 * halo;
     const int t0 = blockIdx.x * tile_out, b = blockIdx.y;
     const int n_b = p.taps * nkb;
+    WB_TRACE(0);
 
+    const uint32_t cta_rank = cluster_ctarank();
+    const uint16_t cl_mask = (uint16_t)((1u << WB_CL) - 1);
     if (threadIdx.x == 0) {
-        for (int s = 0; s < WB_MAX_STAGES; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
+        for (int s = 0; s < WB_MAX_STAGES; ++s) {
+            mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1);
+            mbar_init(&ctl->full_b[s], 1); mbar_init(&ctl->empty_b[s], WB_CL);
+        }
         mbar_init(&ctl->acc_full, 1);
         mbar_init(&ctl->acts_ready, EPI_NT);
         mbar_fence_init();
     }
     if (warp == 2) tmem_alloc<512>(&ctl->tmem_base);
     tc_fence_before();
-    __syncthreads();
+    cluster_sync_all();                                        // the peer's barriers exist before anything is multicast
     tc_fence_after();
     const uint32_t tmem = ctl->tmem_base;
     const uint32_t idesc = umma_idesc_bf16(BT, H);
+    WB_TRACE(1);
 
     // ---------------------------------------------------------------- TMA producer
     if (warp == 0 && lane == 0) {
@@ -85,14 +107,17 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
             tma_load_3d(sa, &tmDrs, &ctl->full[s], kc * KC, t0 - halo, b);
             tma_load_2d(sa + A_BYTES, &tmWrs, &ctl->full[s], kc * KC, 0);
         }
-        // the ring is re-cut into weight-only stages for GEMM b once every GEMM-a MMA has read its operands; the first
-        // n_sb tiles are prefetched now (they land while the gate-backward epilogue runs), the rest follows below --
-        // this thread must first deliver its share of epilogue a, or GEMM b (which frees the stages) never starts
-        mbar_wait(&ctl->acc_full, 0);
+        // The ring is re-cut into weight-only stages for GEMM b.  Each CTA of the pair fetches half of the rows of every
+        // weight tile and the TMA multicasts them into both shared memories; a stage may be written once BOTH CTAs have
+        // released it (empty_b counts the pair: first release = each CTA's GEMM a has read all its operands).  The first
+        // n_sb tiles go out now and land during the gate-backward epilogue; the rest follows below, after this thread
+        // has delivered its share of that epilogue (GEMM b, which frees the stages, cannot start before).
         for (int it = 0; it < min(n_sb, n_b); ++it) {
+            mbar_wait(&ctl->empty_b[it], 0);
             const int j = it / nkb, kc = it % nkb;
-            mbar_arrive_expect_tx(&ctl->full[it], (uint32_t)sb_bytes);
-            tma_load_3d(ring + (size_t)it * sb_bytes, &tmWin, &ctl->full[it], kc * KC, 0, j);
+            mbar_arrive_expect_tx(&ctl->full_b[it], (uint32_t)sb_bytes);
+            tma_load_3d_multicast(ring + (size_t)it * sb_bytes + (size_t)cta_rank * (H / WB_CL) * 128, &tmWin, &ctl->full_b[it],
+                                  kc * KC, (int)cta_rank * (H / WB_CL), j, cl_mask);
         }
     } else if (warp == 1 && lane == 0) {
         // ---------------------------------------------------------------- GEMM a
@@ -108,6 +133,7 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
             umma_commit(&ctl->empty[s]);
         }
         umma_commit(&ctl->acc_full);
+        for (int s = 0; s < n_sb; ++s) umma_commit_multicast(&ctl->empty_b[s], cl_mask);   // ring free on this CTA
     }
     __syncwarp();
 
@@ -123,6 +149,7 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
         const unsigned long long dseed = p.drop_p > 0.f ? drop_resolve(p.drop_seed) : 0ull;
         mbar_wait(&ctl->acc_full, 0);
         tc_fence_after();
+        WB_TRACE(2);
         for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
             const int c0 = cc * 16;
             float d[16], dt[16], ds[16];
@@ -155,37 +182,39 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
         fence_proxy_async_smem();
         tc_fence_before();
         mbar_arrive(&ctl->acts_ready);
+        WB_TRACE(3);
     }
 
     // ---------------------------------------------------------------- GEMM b: taps = row-shifted views of the smem tile
     if (warp == 0 && lane == 0) {
         for (int it = n_sb; it < n_b; ++it) {
             const int s = it % n_sb, use = it / n_sb;
-            mbar_wait(&ctl->empty[s], (ctl_uses(nka, n_sa, s) + use - 1) & 1);
+            mbar_wait(&ctl->empty_b[s], use & 1);
             const int j = it / nkb, kc = it % nkb;
-            mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)sb_bytes);
-            tma_load_3d(ring + (size_t)s * sb_bytes, &tmWin, &ctl->full[s], kc * KC, 0, j);
+            mbar_arrive_expect_tx(&ctl->full_b[s], (uint32_t)sb_bytes);
+            tma_load_3d_multicast(ring + (size_t)s * sb_bytes + (size_t)cta_rank * (H / WB_CL) * 128, &tmWin, &ctl->full_b[s],
+                                  kc * KC, (int)cta_rank * (H / WB_CL), j, cl_mask);
         }
     } else if (warp == 1 && lane == 0) {
         mbar_wait(&ctl->acts_ready, 0);
         tc_fence_after();
-        if (!(p.dbg & 1)) {
         // d(xin) of the OWNED frames [t0, t0 + tile_out) for the weight-gradient launch: rows halo.. of the tile (a TMA
         // store must not start at a negative coordinate; the swizzle is address-based, so a row-offset source is fine)
-        for (int kc = 0; kc < nkb; ++kc) tma_store_3d(&tmDxin, smem + (size_t)kc * A_BYTES + halo * 128, kc * KC, t0, b);
-        tma_store_commit();
+        if (t0 < p.T) {
+            for (int kc = 0; kc < nkb; ++kc) tma_store_3d(&tmDxin, smem + (size_t)kc * A_BYTES + halo * 128, kc * KC, t0, b);
+            tma_store_commit();
         }
         for (int it = 0; it < n_b; ++it) {
             const int s = it % n_sb, use = it / n_sb;
-            mbar_wait(&ctl->full[s], (ctl_uses(nka, n_sa, s) + use) & 1);
+            mbar_wait(&ctl->full_b[s], use & 1);
             tc_fence_after();
             const int j = it / nkb, kc = it % nkb;
-            const uint64_t adesc = umma_desc_kmajor_sw128(smem_u32(smem + (size_t)kc * A_BYTES) + ((p.dbg & 4) ? 0u : (uint32_t)(j * p.dil) * 128u));
+            const uint64_t adesc = umma_desc_kmajor_sw128(smem_u32(smem + (size_t)kc * A_BYTES) + (uint32_t)(j * p.dil) * 128u);
             const uint64_t bdesc = umma_desc_kmajor_sw128(smem_u32(ring + (size_t)s * sb_bytes));
 #pragma unroll
             for (int k = 0; k < KC / 16; ++k)
                 umma_bf16(tmem + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, it != 0 || k >= 2);
-            umma_commit(&ctl->empty[s]);
+            umma_commit_multicast(&ctl->empty_b[s], cl_mask);
         }
         umma_commit(&ctl->acc_full);
     }
@@ -199,6 +228,7 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
         const float mk = (p.mask && ok) ? p.mask[(size_t)b * p.T + f] : 1.f;
         mbar_wait(&ctl->acc_full, 1);
         tc_fence_after();
+        WB_TRACE(4);
         for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
             const int c0 = cc * 16;
             float v[16];
@@ -218,19 +248,28 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
         }
         fence_proxy_async_smem();
         tc_fence_before();
+        WB_TRACE(5);
     }
     __syncthreads();
     if (warp == 1 && lane == 0) {
-        if (!(p.dbg & 2)) {
-        for (int kc = 0; kc < H / KC; ++kc) tma_store_3d(&tmOut, ring + (size_t)kc * A_BYTES, kc * KC, t0, b);
-        tma_store_commit();
+        if (t0 < p.T) {
+            for (int kc = 0; kc < H / KC; ++kc) tma_store_3d(&tmOut, ring + (size_t)kc * A_BYTES, kc * KC, t0, b);
+            tma_store_commit();
         }
         tma_store_wait_read();
     }
+    WB_TRACE(6);
+    cluster_sync_all();                                        // the peer's commits may still be arriving on our barriers
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc<512>(tmem);
     }
+}
+
+int wb_trace_read(unsigned long long* out, int n_ctas) {
+    GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= WB_TRACE_CTAS, "n_ctas");
+    GTK_CUDA(cudaMemcpyFromSymbol(out, g_wb_trace, size_t(n_ctas) * 7 * sizeof(unsigned long long)));
+    return GTK_OK;
 }
 
 int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat16* wrs_t, const __nv_bfloat16* win_t,
@@ -260,7 +299,7 @@ int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat1
     {   // data-gradient pack of the in_layer weight: [taps][H rows (N)][2H columns (K)]
         const uint64_t dims[3] = {(uint64_t)2 * H, (uint64_t)H, (uint64_t)p.taps};
         const uint64_t strides[2] = {(uint64_t)2 * H * 2, (uint64_t)2 * H * 2 * H};
-        const uint32_t box[3] = {KC, (uint32_t)H, 1};
+        const uint32_t box[3] = {KC, (uint32_t)(H / WB_CL), 1};
         int rc = make_tmap_bf16(&tmWin, win_t, 3, dims, strides, box, true);
         if (rc) return rc;
     }
@@ -281,10 +320,16 @@ int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat1
     const size_t smem = (size_t)(2 * H / KC) * A_BYTES + WB_RING + sizeof(WbCtl) + 1024;
     GTK_REQUIRE(smem <= 227 * 1024, "tile does not fit in shared memory");
     GTK_CUDA(cudaFuncSetAttribute(wn_bwd_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid(ceil_div(p.T, tile_out), p.B);
-    { const char* e = getenv("GTK_WB_DBG"); p.dbg = e ? atoi(e) : 0; }
+    dim3 grid(ceil_div(ceil_div(p.T, tile_out), WB_CL) * WB_CL, p.B);     // an out-of-range tile only feeds its peer
     ProfScope prof("wn_bwd_layer_tc", st);
-    wn_bwd_layer_kernel<<<grid, EPI_NT, smem, st>>>(tmDrs, tmWrs, tmWin, tmDxin, tmOut, p);
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid; cfg.blockDim = dim3(EPI_NT); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = WB_CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    GTK_CUDA(cudaLaunchKernelEx(&cfg, wn_bwd_layer_kernel, tmDrs, tmWrs, tmWin, tmDxin, tmOut, p));
     return check_launch("wn_bwd_layer_tc");
 }
 
@@ -292,7 +337,7 @@ int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat1
 // that leaves most of the 128-frame tile as output.
 bool wn_bwd_supported(int H, int taps, int dil) {
     const int halo = (taps / 2) * dil;
-    return H % KC == 0 && (size_t)(2 * H / KC) * A_BYTES + WB_RING + sizeof(WbCtl) + 1024 <= 227 * 1024 && 2 * halo <= 32 &&
+    return H % KC == 0 && (H / WB_CL) % 8 == 0 && (size_t)(2 * H / KC) * A_BYTES + WB_RING + sizeof(WbCtl) + 1024 <= 227 * 1024 && 2 * halo <= 32 &&
            WB_RING / (A_BYTES + H * KC * 2) >= 2;
 }
 

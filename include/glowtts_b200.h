@@ -182,6 +182,8 @@ int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, c
  * out[cta * 6 + {start, setup done, GEMM1 done, epilogue-1 done, GEMM2 done, end}], cta = batch * tiles + tile.
  * Synchronises the device. */
 int gtk_debug_wn_trace(unsigned long long* out, int n_ctas);
+/* Debug: the fused layer-backward kernel: out[cta * 7 + {start, setup, GEMM a, epilogue a, GEMM b, epilogue b, end}]. */
+int gtk_debug_wb_trace(unsigned long long* out, int n_ctas);
 /* Debug: the same for the plain tcgen05 conv kernel.  Select which launches record (epilogue 0 plain / 1 gate-bwd /
  * 2 affine, and the tap count; -1 = none), run, then read out[cta * 5 + {start, setup done, accumulator complete,
  * epilogue math done, stores issued}] of the last selected launch.  Synchronises the device. */
