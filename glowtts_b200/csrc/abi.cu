@@ -271,6 +271,8 @@ int gtk_tc_colsum(const void* in_bf16, int ld, int n_cols, int groups, long long
                   size_t out_gstride, void* stream) {
     return tc::colsum_frames(static_cast<const __nv_bfloat16*>(in_bf16), ld, n_cols, groups, rows_per_group, out, out_gstride, ST);
 }
+int gtk_debug_mas_trace(unsigned long long* out, int n_ctas) { return mas::trace_read(out, n_ctas); }
+int gtk_debug_mas_wait(long long* out, int n_ctas) { return mas::wait_read(out, n_ctas); }
 int gtk_debug_wn_trace(unsigned long long* out, int n_ctas) { return tc::wn_trace_read(out, n_ctas); }
 int gtk_debug_wb_trace(unsigned long long* out, int n_ctas) { return tc::wb_trace_read(out, n_ctas); }
 int gtk_debug_conv_trace_select(int epilogue, int taps) { tc::conv_trace_select(epilogue, taps); return GTK_OK; }

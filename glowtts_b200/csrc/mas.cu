@@ -22,6 +22,7 @@
 // consumed by an in-band cell, so the lower band clip is not needed.
 #include "common.cuh"
 #include "ops.h"
+#include "tc.cuh"
 
 namespace gtk {
 namespace mas {
@@ -255,6 +256,257 @@ __global__ void __launch_bounds__(NT, 1) mas_kernel(const Params p) {
 }
 
 // -------------------------------------------------------------------------------------------------
+// TMA variant of the fast path (value rows 16-byte aligned: T_y % 4 == 0).  Same DP, same bits, but
+//   * `value` tiles are streamed by ONE thread with cp.async.bulk.tensor (3-D map [B][T_x][T_y], boxes of 36 frames
+//     x 32 text rows; only ceil(t_x / 32) boxes per tile are issued) into an mbarrier ring, so several whole tiles are
+//     in flight per SM while the latency-bound DP chain runs;
+//   * a tile is kept row-major [row][36 floats] exactly as TMA writes it (pitch 36 words == 4 mod 32): the DP warp
+//     reads one 128-bit word per (text row, 4 frames) and software-pipelines the next 4 frames' loads;
+//   * the six remaining warps only zero-fill the output plane.
+constexpr int TP = 36;                   // tile row pitch in floats (32 frames + 4: conflict-free 128-bit reads)
+constexpr int TBOX = 32;                 // text rows per TMA box
+constexpr int TBOX_BYTES = TBOX * TP * 4;
+constexpr int TMA_MAX_STAGES = 6;
+constexpr int TMA_MAX_XPT = 17;
+
+template <int XPT, bool DIAG>
+__device__ __forceinline__ void dp_col(const float (&v)[XPT], float (&q)[XPT], uint32_t (&bits)[XPT], int lane, int x0, int y,
+                                       uint32_t bit) {
+    float up = __shfl_up_sync(0xffffffffu, q[XPT - 1], 1);
+    if (lane == 0) up = (DIAG && y == 0) ? 0.0f : NEG;
+#pragma unroll
+    for (int k = XPT - 1; k >= 0; --k) {
+        const float b = (k == 0) ? up : q[k - 1];
+        const float a = q[k];
+        bool d = a < b;
+        float a2 = a;
+        if (DIAG) {
+            const bool diag = (x0 + k == y);
+            d = d || diag;
+            a2 = diag ? NEG : a;
+        }
+        const float m = (b > a2) ? b : a2;
+        q[k] = m + v[k];
+        if (d) bits[k] |= bit;
+    }
+}
+
+// All 32 frames of a tile (frames past t_y are computed too: their bits are masked by the backtrack and q is dead).
+__device__ __forceinline__ float4 lds128(uint32_t addr) {      // explicit ld.shared (a generic pointer costs an LD.E)
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
+// `tile` = shared-space byte address of the stage, roff[k] = byte offset of this lane's k-th text row
+template <int XPT, bool DIAG>
+__device__ __forceinline__ void dp_tile4(uint32_t tile, const int (&roff)[XPT], float (&q)[XPT],
+                                         uint32_t (&bits)[XPT], int lane, int y0) {
+    const int x0 = lane * XPT;
+    float4 cur[XPT], nxt[XPT];
+#pragma unroll
+    for (int k = 0; k < XPT; ++k) cur[k] = lds128(tile + roff[k]);
+#pragma unroll
+    for (int g = 0; g < YT / 4; ++g) {
+        if (g + 1 < YT / 4) {
+#pragma unroll
+            for (int k = 0; k < XPT; ++k) nxt[k] = lds128(tile + roff[k] + 16 * (g + 1));
+        }
+        float v[XPT];
+#pragma unroll
+        for (int k = 0; k < XPT; ++k) v[k] = cur[k].x;
+        dp_col<XPT, DIAG>(v, q, bits, lane, x0, y0 + 4 * g + 0, 1u << (4 * g + 0));
+#pragma unroll
+        for (int k = 0; k < XPT; ++k) v[k] = cur[k].y;
+        dp_col<XPT, DIAG>(v, q, bits, lane, x0, y0 + 4 * g + 1, 1u << (4 * g + 1));
+#pragma unroll
+        for (int k = 0; k < XPT; ++k) v[k] = cur[k].z;
+        dp_col<XPT, DIAG>(v, q, bits, lane, x0, y0 + 4 * g + 2, 1u << (4 * g + 2));
+#pragma unroll
+        for (int k = 0; k < XPT; ++k) v[k] = cur[k].w;
+        dp_col<XPT, DIAG>(v, q, bits, lane, x0, y0 + 4 * g + 3, 1u << (4 * g + 3));
+        if (g + 1 < YT / 4) {
+#pragma unroll
+            for (int k = 0; k < XPT; ++k) cur[k] = nxt[k];
+        }
+    }
+}
+
+// Phase stamps (globaltimer, ns) of the DP warp per CTA of the last launch: [start, first tile landed, DP done, backtrack
+// done, all warps past the barrier, end]; read with gtk_debug_mas_trace.
+constexpr int MAS_TRACE_CTAS = 1024;
+__device__ unsigned long long g_mas_trace[MAS_TRACE_CTAS * 6];
+__device__ long long g_mas_wait[MAS_TRACE_CTAS];            // SM cycles the DP warp waited for tiles (after the first)
+__device__ __forceinline__ void mas_stamp(int i) {
+    if (blockIdx.x < MAS_TRACE_CTAS) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        g_mas_trace[blockIdx.x * 6 + i] = t;
+    }
+}
+
+template <int XPT>
+__global__ void __launch_bounds__(NT, 1) mas_tma_kernel(const __grid_constant__ CUtensorMap tmV, const Params p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int ROWW = 32 * XPT;   // words per decision row-block
+    const int S = p.n_stages;
+    const int NYB = (p.T_y + YT - 1) / YT;
+    const int RB = (p.T_x + TBOX - 1) / TBOX;        // row boxes a tile has room for
+    const size_t tile_floats = (size_t)RB * TBOX * TP;
+
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);
+    uint64_t* empty = full + TMA_MAX_STAGES;
+    int* ys = reinterpret_cast<int*>(smem_raw + 2 * TMA_MAX_STAGES * sizeof(uint64_t));
+    constexpr int YS_WORDS = ((ROWW + 1 + 3) / 4) * 4;
+    uint32_t* bitsT = reinterpret_cast<uint32_t*>(ys + YS_WORDS);
+    float* tiles = reinterpret_cast<float*>(
+        (reinterpret_cast<uintptr_t>(bitsT + (size_t)NYB * ROWW) + 127) & ~static_cast<uintptr_t>(127));
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.x;
+    int t_x = min(max(p.t_xs[b], 0), p.T_x);
+    int t_y = min(max(p.t_ys[b], 0), p.T_y);
+    const bool valid = (t_x >= 1) && (t_y >= t_x);   // t_x > t_y is undefined in the reference
+    const int n_tiles = valid ? (t_y + YT - 1) / YT : 0;
+    const size_t plane_elems = (size_t)p.T_x * p.T_y;
+    float* __restrict__ pplane = p.path + (size_t)b * plane_elems;
+
+    if (tid == 0) {
+        for (int s = 0; s < TMA_MAX_STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ DP warp
+        if (lane == 0) mas_stamp(0);
+        long long waited = 0;
+        float q[XPT];
+        uint32_t bits[XPT];
+        int roff[XPT];
+#pragma unroll
+        for (int k = 0; k < XPT; ++k) {
+            q[k] = 0.0f;
+            roff[k] = min(lane * XPT + k, RB * TBOX - 1) * TP * 4;   // rows past the tile are never consumed: clamp the read
+        }
+        for (int it = 0; it < n_tiles; ++it) {
+            const int s = it % S, use = it / S;
+            const long long w0 = clock64();
+            mbar_wait(&full[s], use & 1);
+            if (it > 0) waited += clock64() - w0;
+            if (it == 0 && lane == 0) mas_stamp(1);
+            const uint32_t tile = smem_u32(tiles + (size_t)s * tile_floats);
+            const int y0 = it * YT;
+#pragma unroll
+            for (int k = 0; k < XPT; ++k) bits[k] = 0u;
+            if (y0 < 32 * XPT) dp_tile4<XPT, true>(tile, roff, q, bits, lane, y0);
+            else               dp_tile4<XPT, false>(tile, roff, q, bits, lane, y0);
+#pragma unroll
+            for (int k = 0; k < XPT; ++k) bitsT[(size_t)it * ROWW + k * 32 + lane] = bits[k];
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
+        }
+        __syncwarp();
+        if (lane == 0) { mas_stamp(2); if (blockIdx.x < MAS_TRACE_CTAS) g_mas_wait[blockIdx.x] = waited; }
+        // ------------------------------------------------------------ backtrack (run-skipping, one thread)
+        // Token `index` starts at the highest set bit of its row at or below y.  The loop-carried chain is mask -> clz ->
+        // select: the words the NEXT row can need (same 32-frame block or the one before) are loaded one step ahead.
+        if (lane == 0 && valid) {
+            int index = t_x - 1, y = t_y - 1;
+            int k = index % XPT;
+            const uint32_t* rowp = bitsT + k * 32 + index / XPT;       // word of block yb at rowp[yb * ROWW]
+            int yb = y >> 5;
+            uint32_t w = rowp[(size_t)yb * ROWW];
+            while (index > 0 && y >= 0) {
+                const uint32_t* nrow = (k == 0) ? rowp + (XPT - 1) * 32 - 1 : rowp - 32;
+                const uint32_t n0 = nrow[(size_t)yb * ROWW];
+                const uint32_t n1 = nrow[(size_t)max(yb - 1, 0) * ROWW];
+                const uint32_t m = w & (0xffffffffu >> (31 - (y & 31)));
+                if (m) {
+                    const int yp = (yb << 5) + (31 - __clz(m));
+                    ys[index] = yp;       // first frame of token `index`
+                    --index;
+                    k = (k == 0) ? XPT - 1 : k - 1;
+                    rowp = nrow;
+                    y = yp - 1;
+                    const int nyb = y >> 5;                            // yb or yb - 1 (-1 ends the loop)
+                    w = (nyb == yb) ? n0 : n1;
+                    yb = nyb;
+                } else {
+                    y = (yb << 5) - 1;
+                    --yb;
+                    if (yb >= 0) w = rowp[(size_t)yb * ROWW];
+                }
+            }
+            ys[0] = 0;
+            // y < 0 with index > 0 cannot happen for valid inputs (diagonal bits force the move);
+            // if it did, make the remaining rows empty rather than reading garbage.
+            for (int x = 1; x <= index; ++x) ys[x] = 0;
+        }
+        if (lane == 0) mas_stamp(3);
+    } else if (warp == 1) {
+        // ------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            const int nbox = (t_x + TBOX - 1) / TBOX;
+            for (int it = 0; it < n_tiles; ++it) {
+                const int s = it % S, use = it / S;
+                if (use >= 1) mbar_wait(&empty[s], (use - 1) & 1);
+                float* tile = tiles + (size_t)s * tile_floats;
+                mbar_arrive_expect_tx(&full[s], (uint32_t)(nbox * TBOX_BYTES));
+                for (int j = 0; j < nbox; ++j)
+                    tc::tma_load_3d(tile + (size_t)j * TBOX * TP, &tmV, &full[s], it * YT, j * TBOX, b);
+            }
+        }
+    } else {
+        // ------------------------------------------------------------ zero-fill of this utterance's output plane
+        const int ht = tid - 64;
+        constexpr int HT = NT - 64;
+        const uintptr_t addr = reinterpret_cast<uintptr_t>(pplane);
+        size_t head = ((16 - (addr & 15)) & 15) / 4;
+        if (head > plane_elems) head = plane_elems;
+        const size_t nvec = (plane_elems - head) / 4;
+        const size_t tail0 = head + nvec * 4;
+        float4* pv = reinterpret_cast<float4*>(pplane + head);
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (size_t i = ht; i < nvec; i += HT) pv[i] = z4;
+        if ((size_t)ht < head) pplane[ht] = 0.f;
+        for (size_t i = tail0 + ht; i < plane_elems; i += HT) pplane[i] = 0.f;
+    }
+    __syncthreads();
+    if (tid == 0) mas_stamp(4);
+
+    // ---------------------------------------------------------------- emit ones / durations / indices
+    for (int x = tid; x < p.T_x; x += NT) {
+        int start = 0, end = 0;
+        if (valid && x < t_x) {
+            start = ys[x];
+            end = (x + 1 < t_x) ? ys[x + 1] : t_y;
+            for (int y = start; y < end; ++y) pplane[(size_t)x * p.T_y + y] = 1.0f;
+            if (p.idx_out)
+                for (int y = start; y < end; ++y) p.idx_out[(size_t)b * p.T_y + y] = x;
+        }
+        if (p.dur_out) p.dur_out[(size_t)b * p.T_x + x] = end - start;
+    }
+    if (p.idx_out)
+        for (int y = (valid ? t_y : 0) + tid; y < p.T_y; y += NT) p.idx_out[(size_t)b * p.T_y + y] = -1;
+    if (tid == 0) mas_stamp(5);
+}
+
+int trace_read(unsigned long long* out, int n_ctas) {
+    GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= MAS_TRACE_CTAS, "n_ctas");
+    GTK_CUDA(cudaMemcpyFromSymbol(out, g_mas_trace, size_t(n_ctas) * 6 * sizeof(unsigned long long)));
+    return GTK_OK;
+}
+int wait_read(long long* out, int n_ctas) {
+    GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= MAS_TRACE_CTAS, "n_ctas");
+    GTK_CUDA(cudaMemcpyFromSymbol(out, g_mas_wait, size_t(n_ctas) * sizeof(long long)));
+    return GTK_OK;
+}
+
+// -------------------------------------------------------------------------------------------------
 // Generic fallback for shapes the fast path does not cover (T_x > 512, or decision bits that do not
 // fit in shared memory): DP column in shared memory, block barrier per frame, decision words in a
 // global workspace [B][T_y][ceil(T_x/32)].  Same arithmetic, same bits.
@@ -360,6 +612,37 @@ size_t workspace_bytes(int B, int T_x, int T_y) {
     return (size_t)B * T_y * ceil_div(T_x, 32) * sizeof(uint32_t);
 }
 
+// TMA path: text rows per lane.  A lane stride of XPT * 36 words is conflict-free for odd XPT, 2-way for XPT = 2 mod 4;
+// multiples of 4 (4- / 8-way) take one more row per lane instead.
+static int tma_xpt(int T_x) {
+    int xpt = max(1, ceil_div(T_x, 32));
+    if (xpt % 4 == 0) ++xpt;
+    return xpt;
+}
+static size_t tma_smem_bytes(int xpt, int T_x, int T_y, int stages) {
+    const size_t roww = 32 * (size_t)xpt;
+    const size_t ys_words = ((roww + 1 + 3) / 4) * 4;
+    const size_t nyb = (T_y + YT - 1) / YT;
+    const size_t rb = ceil_div(T_x, TBOX);
+    return 2 * TMA_MAX_STAGES * sizeof(uint64_t) + ys_words * 4 + nyb * roww * 4 + 128 + (size_t)stages * rb * TBOX_BYTES;
+}
+static int plan_tma(int T_x, int T_y, int* xpt_out) {
+    const int xpt = tma_xpt(T_x);
+    *xpt_out = xpt;
+    if (xpt > TMA_MAX_XPT || T_y % 4 != 0) return 0;
+    for (int s = TMA_MAX_STAGES; s >= 2; --s)
+        if (tma_smem_bytes(xpt, T_x, T_y, s) <= SMEM_LIMIT) return s;
+    return 0;
+}
+
+template <int XPT>
+static int launch_tma(const Params& p, const CUtensorMap& tm, size_t smem, cudaStream_t stream) {
+    GTK_CUDA(cudaFuncSetAttribute(mas_tma_kernel<XPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ProfScope prof("mas", stream);
+    mas_tma_kernel<XPT><<<p.B, NT, smem, stream>>>(tm, p);
+    return check_launch("mas_tma_kernel");
+}
+
 template <int XPT>
 static int launch_fast(const Params& p, size_t smem, cudaStream_t stream) {
     GTK_CUDA(cudaFuncSetAttribute(mas_kernel<XPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -384,7 +667,29 @@ int forward(const float* value, const int* t_xs, const int* t_ys, float* path, i
     p.B = B; p.T_x = T_x; p.T_y = T_y;
     p.vec4 = ((T_y % 4) == 0) && ((reinterpret_cast<uintptr_t>(value) & 15) == 0);
     int xpt = 0;
-    const int stages = force_generic ? 0 : plan_fast(T_x, T_y, &xpt);
+    // force_generic: 0 = pick the fastest applicable path, 1 = generic kernel, 2 = helper-warp fast path (no TMA)
+    const int tma_stages = (force_generic == 0 && p.vec4) ? plan_tma(T_x, T_y, &xpt) : 0;
+    if (tma_stages > 0) {
+        p.n_stages = tma_stages;
+        CUtensorMap tm;
+        const uint64_t dims[3] = {(uint64_t)T_y, (uint64_t)T_x, (uint64_t)B};
+        const uint64_t strides[2] = {(uint64_t)T_y * 4, (uint64_t)T_y * 4 * T_x};
+        const uint32_t box[3] = {TP, TBOX, 1};
+        int rc = tc::make_tmap_f32(&tm, value, 3, dims, strides, box);
+        if (rc) return rc;
+        const size_t smem = tma_smem_bytes(xpt, T_x, T_y, tma_stages);
+        switch (xpt) {
+#define GTK_MAS_CASE(N) case N: return launch_tma<N>(p, tm, smem, stream);
+            GTK_MAS_CASE(1) GTK_MAS_CASE(2) GTK_MAS_CASE(3) GTK_MAS_CASE(5) GTK_MAS_CASE(6) GTK_MAS_CASE(7)
+            GTK_MAS_CASE(9) GTK_MAS_CASE(10) GTK_MAS_CASE(11) GTK_MAS_CASE(13) GTK_MAS_CASE(14) GTK_MAS_CASE(15)
+            GTK_MAS_CASE(17)
+#undef GTK_MAS_CASE
+            default: break;
+        }
+        set_error("mas: internal: no TMA instantiation for XPT=%d", xpt);
+        return GTK_ERR_UNSUPPORTED;
+    }
+    const int stages = force_generic == 1 ? 0 : plan_fast(T_x, T_y, &xpt);
     p.n_stages = stages;
     if (stages > 0) {
         const size_t smem = fast_smem_bytes(xpt, T_y, stages);

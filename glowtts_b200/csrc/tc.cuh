@@ -12,6 +12,9 @@ namespace tc {
 // requires box[0] * 2 bytes == 128.
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                    const uint32_t* box, bool swizzle128);
+// fp32 tensor, no swizzle (box[0] * 4 bytes must be a multiple of 16)
+int make_tmap_f32(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                  const uint32_t* box);
 
 constexpr int BT = 128;            // frames per CTA tile (UMMA M)
 constexpr int KC = 64;             // channels per k-chunk (128 B of bf16 = one swizzle row)

@@ -59,8 +59,9 @@ def _(mask):
 
 
 @torch.library.custom_op(f"{NS}::mas_path", mutates_args=(), device_types="cuda")
-def mas_path(value: Tensor, t_xs: Tensor, t_ys: Tensor, force_generic: bool = False) -> Tuple[Tensor, Tensor, Tensor]:
-    """core.pyx:9-45 on the device.  -> (path f32 [B,T_x,T_y], durations i32 [B,T_x], index i32 [B,T_y])."""
+def mas_path(value: Tensor, t_xs: Tensor, t_ys: Tensor, force_generic: int = 0) -> Tuple[Tensor, Tensor, Tensor]:
+    """core.pyx:9-45 on the device.  -> (path f32 [B,T_x,T_y], durations i32 [B,T_x], index i32 [B,T_y]).
+    force_generic: 0 = fastest applicable kernel (TMA ring), 1 = generic kernel, 2 = helper-warp fast path."""
     value = _chk(value, "value")
     t_xs = _chk(t_xs, "t_xs", torch.int32)
     t_ys = _chk(t_ys, "t_ys", torch.int32)
@@ -78,7 +79,7 @@ def mas_path(value: Tensor, t_xs: Tensor, t_ys: Tensor, force_generic: bool = Fa
 
 
 @mas_path.register_fake
-def _(value, t_xs, t_ys, force_generic=False):
+def _(value, t_xs, t_ys, force_generic=0):
     B, T_x, T_y = value.shape
     return (torch.empty_like(value), value.new_empty((B, T_x), dtype=torch.int32),
             value.new_empty((B, T_y), dtype=torch.int32))

@@ -182,6 +182,11 @@ int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, c
  * out[cta * 6 + {start, setup done, GEMM1 done, epilogue-1 done, GEMM2 done, end}], cta = batch * tiles + tile.
  * Synchronises the device. */
 int gtk_debug_wn_trace(unsigned long long* out, int n_ctas);
+/* Debug: DP-warp phase stamps of the last TMA-path MAS launch: out[cta * 6 + {start, first tile landed, DP done,
+ * backtrack done, barrier passed, end}] (globaltimer ns).  Synchronises the device. */
+int gtk_debug_mas_trace(unsigned long long* out, int n_ctas);
+/* Debug: SM cycles the DP warp of each CTA spent waiting for value tiles after the first one (same launch). */
+int gtk_debug_mas_wait(long long* out, int n_ctas);
 /* Debug: the fused layer-backward kernel: out[cta * 7 + {start, setup, GEMM a, epilogue a, GEMM b, epilogue b, end}]. */
 int gtk_debug_wb_trace(unsigned long long* out, int n_ctas);
 /* Debug: the same for the plain tcgen05 conv kernel.  Select which launches record (epilogue 0 plain / 1 gate-bwd /

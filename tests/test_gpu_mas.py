@@ -16,17 +16,17 @@ pytestmark = pytest.mark.gpu
 GOLDEN = ["mas_small_ragged", "mas_ties", "mas_square", "mas_tx1", "mas_medium", "mas_wide"]
 
 
-def _gpu_path(value, mask, force_generic=False):
+def _gpu_path(value, mask, force_generic=0):
     from glowtts_b200 import ops
     v = torch.from_numpy(value * mask).cuda()
     m = torch.from_numpy(mask).cuda()
     t_xs, t_ys = ops.mas_lengths(m)
-    path, dur, idx = ops.mas_path(v, t_xs, t_ys, force_generic)
+    path, dur, idx = ops.mas_path(v, t_xs, t_ys, int(force_generic))
     torch.cuda.synchronize()
     return path.cpu().numpy(), dur.cpu().numpy(), idx.cpu().numpy(), t_xs.cpu().numpy(), t_ys.cpu().numpy()
 
 
-@pytest.mark.parametrize("generic", [False, True])
+@pytest.mark.parametrize("generic", [0, 1, 2])     # TMA ring / generic kernel / helper-warp fast path
 @pytest.mark.parametrize("name", GOLDEN)
 def test_matches_reference_fixture(golden_dir, name, generic):
     g = np.load(os.path.join(golden_dir, name + ".npz"))
@@ -58,13 +58,14 @@ def test_drop_in_wrapper_matches_reference_wrapper_semantics():
 
 
 @pytest.mark.parametrize("shape", [(32, 180, 860), (5, 31, 64), (3, 33, 65), (2, 64, 64), (4, 129, 400),
-                                   (2, 400, 2000), (3, 512, 1001), (2, 7, 2048), (1, 1, 1), (2, 300, 301)])
+                                   (2, 400, 2000), (3, 512, 1001), (2, 7, 2048), (1, 1, 1), (2, 300, 301),
+                                   (3, 128, 400), (2, 256, 512), (2, 512, 1000), (3, 97, 100), (2, 333, 1500)])
 @pytest.mark.parametrize("quant", [False, True])
 def test_matches_oracle(shape, quant):
     b, tx, ty = shape
     value, mask, _, _ = helpers.mas_case(b, tx, ty, 1000 + tx + ty, ragged=True, quantised=quant)
     want = omas.maximum_path_np(value, mask, impl="c_port_omp")
-    for generic in (False, True):
+    for generic in (0, 1, 2):
         path, dur, idx, _, _ = _gpu_path(value, mask, generic)
         assert (path == want).all(), f"generic={generic}"
         assert (dur == want.sum(2)).all()
@@ -147,8 +148,9 @@ def test_full_size_properties_and_sampled_parity():
     want = omas.maximum_path_np(v[sel].cpu().numpy(), mask[sel].cpu().numpy(), impl="c_port_omp")
     assert (path[sel].cpu().numpy() == want).all()
     # generic path agrees with the fast path everywhere
-    path2, dur2, idx2 = ops.mas_path(v, t_xs, t_ys, True)
-    assert torch.equal(path, path2) and torch.equal(dur, dur2) and torch.equal(idx, idx2)
+    for kernel in (1, 2):
+        path2, dur2, idx2 = ops.mas_path(v, t_xs, t_ys, kernel)
+        assert torch.equal(path, path2) and torch.equal(dur, dur2) and torch.equal(idx, idx2)
 
 
 def test_duration_roundtrip_through_generate_path():
