@@ -22,7 +22,7 @@ LIB = os.path.join(LIBDIR, "libglowtts_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 CFLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",
-          "-Xptxas", "-v", "-Wno-deprecated-gpu-targets"]
+          "-Xptxas", "-v", "-Wno-deprecated-gpu-targets"] + os.environ.get("GTK_EXTRA_CFLAGS", "").split()
 
 
 def _sources():

@@ -256,53 +256,88 @@ __global__ void __launch_bounds__(NT, 1) mas_kernel(const Params p) {
 }
 
 // -------------------------------------------------------------------------------------------------
-// TMA variant of the fast path (value rows 16-byte aligned: T_y % 4 == 0).  Same DP, same bits, but
-//   * `value` tiles are streamed by ONE thread with cp.async.bulk.tensor (3-D map [B][T_x][T_y], boxes of 36 frames
-//     x 32 text rows; only ceil(t_x / 32) boxes per tile are issued) into an mbarrier ring, so several whole tiles are
-//     in flight per SM while the latency-bound DP chain runs;
-//   * a tile is kept row-major [row][36 floats] exactly as TMA writes it (pitch 36 words == 4 mod 32): the DP warp
-//     reads one 128-bit word per (text row, 4 frames) and software-pipelines the next 4 frames' loads;
-//   * the six remaining warps only zero-fill the output plane.
+// TMA wavefront kernel: the fast path when value rows are 16-byte aligned (T_y % 4 == 0).  Same DP, same bits, but
+//   * FOUR DP warps (one per SM sub-partition) each own a band of 32 * XPT text rows and run one 32-frame tile apart:
+//     warp w hands the DP value of its last row to warp w + 1 through a 32-float shared-memory mailbox per tile
+//     (mbarrier full/empty), so the per-column critical path is XPT cells instead of T_x / 32;
+//   * `value` is streamed by cp.async.bulk.tensor (3-D map [B][T_x][T_y], boxes of 36 frames x 32 text rows, only the
+//     boxes below t_x are issued) into one mbarrier ring PER DP WARP (the warps are skewed in time), so several tiles
+//     are in flight per SM while the latency-bound DP chain runs;
+//   * a tile is kept row-major [row][36 floats] exactly as TMA writes it (pitch 36 words == 4 mod 32): a lane reads one
+//     128-bit word per (text row, 4 frames) and software-pipelines the next 4 frames' loads;
+//   * off the diagonal a cell is 2 FMA-pipe + 2 ALU-pipe instructions: t = a - b (its sign IS a < b: neither operand
+//     can be -0, see dp_col), the decision bit funnel-shifted out of t's sign, max(a, b), + value;
+//   * the remaining warps zero-fill the output plane; the backtrack prefetches the words its next step can need.
 constexpr int TP = 36;                   // tile row pitch in floats (32 frames + 4: conflict-free 128-bit reads)
 constexpr int TBOX = 32;                 // text rows per TMA box
 constexpr int TBOX_BYTES = TBOX * TP * 4;
+constexpr int NDP = 4;                   // DP warps
+constexpr int NBOX = 4;                  // mailbox slots between neighbouring DP warps (tiles a warp may run ahead)
 constexpr int TMA_MAX_STAGES = 6;
-constexpr int TMA_MAX_XPT = 17;
+constexpr int TMA_MAX_XPT = 8;           // T_x <= 1024 (if the decision bits fit)
 
-template <int XPT, bool DIAG>
-__device__ __forceinline__ void dp_col(const float (&v)[XPT], float (&q)[XPT], uint32_t (&bits)[XPT], int lane, int x0, int y,
-                                       uint32_t bit) {
-    float up = __shfl_up_sync(0xffffffffu, q[XPT - 1], 1);
-    if (lane == 0) up = (DIAG && y == 0) ? 0.0f : NEG;
-#pragma unroll
-    for (int k = XPT - 1; k >= 0; --k) {
-        const float b = (k == 0) ? up : q[k - 1];
-        const float a = q[k];
-        bool d = a < b;
-        float a2 = a;
-        if (DIAG) {
-            const bool diag = (x0 + k == y);
-            d = d || diag;
-            a2 = diag ? NEG : a;
-        }
-        const float m = (b > a2) ? b : a2;
-        q[k] = m + v[k];
-        if (d) bits[k] |= bit;
+struct WaveCtl {
+    uint64_t full[NDP][TMA_MAX_STAGES], empty[NDP][TMA_MAX_STAGES];   // value tiles, one ring per DP warp
+    uint64_t box_full[NDP][NBOX], box_empty[NDP][NBOX];               // mailbox of warp w -> w + 1, NBOX tiles deep
+    uint64_t dp_done;
+    alignas(16) float box[NDP][NBOX][YT];
+};
+
+// Phase stamps (globaltimer, ns) per CTA of the last launch: [start, first tile landed, DP done (all warps), backtrack
+// done, all warps past the barrier, end]; read with gtk_debug_mas_trace.
+constexpr int MAS_TRACE_CTAS = 1024;
+__device__ unsigned long long g_mas_trace[MAS_TRACE_CTAS * 6];
+__device__ long long g_mas_wait[MAS_TRACE_CTAS];            // SM cycles DP warp 0 waited for tiles (after the first)
+__device__ __forceinline__ void mas_stamp(int i) {
+    if (blockIdx.x < MAS_TRACE_CTAS) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        g_mas_trace[blockIdx.x * 6 + i] = t;
     }
 }
 
-// All 32 frames of a tile (frames past t_y are computed too: their bits are masked by the backtrack and q is dead).
 __device__ __forceinline__ float4 lds128(uint32_t addr) {      // explicit ld.shared (a generic pointer costs an LD.E)
     float4 v;
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
     return v;
 }
 
-// `tile` = shared-space byte address of the stage, roff[k] = byte offset of this lane's k-th text row
+// One DP column of one warp.  `up_in` = DP value of the row below this warp's band at column y - 1 (lane 0 only).
+// Decision bits are shifted in MSB-first (frame 0 of the tile ends at bit 31; the caller bit-reverses the word).
+// Off the diagonal: sign(a - b) == (a < b) exactly, because a DP value is never -0 (a sum is -0 only if both addends
+// are; the recursion starts from +0 and the sentinels are non-zero) and fp32 subtraction of unequal finite numbers is
+// never zero (denormals are kept: no -ftz); fmaxf(a, b) == ((b > a) ? b : a) for non-NaN input.
 template <int XPT, bool DIAG>
-__device__ __forceinline__ void dp_tile4(uint32_t tile, const int (&roff)[XPT], float (&q)[XPT],
-                                         uint32_t (&bits)[XPT], int lane, int y0) {
-    const int x0 = lane * XPT;
+__device__ __forceinline__ void dp_col(const float (&v)[XPT], float (&q)[XPT], uint32_t (&bits)[XPT], int lane, int x0, int y,
+                                       float up_in) {
+    float up = __shfl_up_sync(0xffffffffu, q[XPT - 1], 1);
+    if (lane == 0) up = up_in;
+#pragma unroll
+    for (int k = XPT - 1; k >= 0; --k) {
+        const float b = (k == 0) ? up : q[k - 1];
+        const float a = q[k];
+        if (DIAG) {
+            const bool diag = (x0 + k == y);
+            const bool d = (a < b) || diag;
+            const float a2 = diag ? NEG : a;
+            const float m = (b > a2) ? b : a2;
+            q[k] = m + v[k];
+            bits[k] = (bits[k] << 1) | (d ? 1u : 0u);
+        } else {
+            const float t = a - b;
+            bits[k] = __funnelshift_l(__float_as_uint(t), bits[k], 1);
+            q[k] = fmaxf(a, b) + v[k];
+        }
+    }
+}
+
+// All 32 frames of a tile (frames past t_y are computed too: their bits are masked by the backtrack and q is dead).
+// `tile` = shared-space byte address of this warp's rows of the stage, roff[k] = byte offset of the lane's k-th row.
+// FIRST: the warp that owns text row 0 (its lane 0 takes the reference's sentinels); otherwise bv[yl] = DP value of
+// the row below the band at frame y0 + yl - 1.  SEND: publish this warp's last row into `box_out` (shared address).
+template <int XPT, bool DIAG, bool FIRST, bool SEND>
+__device__ __forceinline__ void dp_tile4(uint32_t tile, const int (&roff)[XPT], float (&q)[XPT], uint32_t (&bits)[XPT], int lane,
+                                         int x0, int y0, const float (&bv)[YT], uint32_t box_out) {
     float4 cur[XPT], nxt[XPT];
 #pragma unroll
     for (int k = 0; k < XPT; ++k) cur[k] = lds128(tile + roff[k]);
@@ -312,19 +347,17 @@ __device__ __forceinline__ void dp_tile4(uint32_t tile, const int (&roff)[XPT], 
 #pragma unroll
             for (int k = 0; k < XPT; ++k) nxt[k] = lds128(tile + roff[k] + 16 * (g + 1));
         }
-        float v[XPT];
 #pragma unroll
-        for (int k = 0; k < XPT; ++k) v[k] = cur[k].x;
-        dp_col<XPT, DIAG>(v, q, bits, lane, x0, y0 + 4 * g + 0, 1u << (4 * g + 0));
+        for (int c = 0; c < 4; ++c) {
+            const int yl = 4 * g + c;
+            float v[XPT];
 #pragma unroll
-        for (int k = 0; k < XPT; ++k) v[k] = cur[k].y;
-        dp_col<XPT, DIAG>(v, q, bits, lane, x0, y0 + 4 * g + 1, 1u << (4 * g + 1));
-#pragma unroll
-        for (int k = 0; k < XPT; ++k) v[k] = cur[k].z;
-        dp_col<XPT, DIAG>(v, q, bits, lane, x0, y0 + 4 * g + 2, 1u << (4 * g + 2));
-#pragma unroll
-        for (int k = 0; k < XPT; ++k) v[k] = cur[k].w;
-        dp_col<XPT, DIAG>(v, q, bits, lane, x0, y0 + 4 * g + 3, 1u << (4 * g + 3));
+            for (int k = 0; k < XPT; ++k) v[k] = c == 0 ? cur[k].x : c == 1 ? cur[k].y : c == 2 ? cur[k].z : cur[k].w;
+            const float up_in = FIRST ? ((DIAG && y0 + yl == 0) ? 0.0f : NEG) : bv[yl];
+            dp_col<XPT, DIAG>(v, q, bits, lane, x0, y0 + yl, up_in);
+            if (SEND && lane == 31)
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(box_out + 4 * yl), "f"(q[XPT - 1]) : "memory");
+        }
         if (g + 1 < YT / 4) {
 #pragma unroll
             for (int k = 0; k < XPT; ++k) cur[k] = nxt[k];
@@ -332,33 +365,24 @@ __device__ __forceinline__ void dp_tile4(uint32_t tile, const int (&roff)[XPT], 
     }
 }
 
-// Phase stamps (globaltimer, ns) of the DP warp per CTA of the last launch: [start, first tile landed, DP done, backtrack
-// done, all warps past the barrier, end]; read with gtk_debug_mas_trace.
-constexpr int MAS_TRACE_CTAS = 1024;
-__device__ unsigned long long g_mas_trace[MAS_TRACE_CTAS * 6];
-__device__ long long g_mas_wait[MAS_TRACE_CTAS];            // SM cycles the DP warp waited for tiles (after the first)
-__device__ __forceinline__ void mas_stamp(int i) {
-    if (blockIdx.x < MAS_TRACE_CTAS) {
-        unsigned long long t;
-        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-        g_mas_trace[blockIdx.x * 6 + i] = t;
-    }
+// Probe first (mbarrier.test_wait does not suspend): in steady state the phase a DP warp needs has already completed.
+__device__ __forceinline__ void fast_wait(uint64_t* bar, uint32_t parity) {
+    if (!mbar_test_wait(bar, parity)) mbar_wait(bar, parity);
 }
 
 template <int XPT>
-__global__ void __launch_bounds__(NT, 1) mas_tma_kernel(const __grid_constant__ CUtensorMap tmV, const Params p) {
+__global__ void __launch_bounds__(NT, 1) mas_wave_kernel(const __grid_constant__ CUtensorMap tmV, const Params p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    constexpr int ROWW = 32 * XPT;   // words per decision row-block
+    constexpr int BAND = 32 * XPT;                   // text rows per DP warp
     const int S = p.n_stages;
     const int NYB = (p.T_y + YT - 1) / YT;
-    const int RB = (p.T_x + TBOX - 1) / TBOX;        // row boxes a tile has room for
-    const size_t tile_floats = (size_t)RB * TBOX * TP;
+    const int ROWW = (p.T_x + 3) & ~3;               // decision words per 32-frame block: word [yb][x]
+    const int RB = (p.T_x + TBOX - 1) / TBOX;        // row boxes a stage has room for
+    const size_t stage_floats = (size_t)RB * TBOX * TP;
 
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);
-    uint64_t* empty = full + TMA_MAX_STAGES;
-    int* ys = reinterpret_cast<int*>(smem_raw + 2 * TMA_MAX_STAGES * sizeof(uint64_t));
-    constexpr int YS_WORDS = ((ROWW + 1 + 3) / 4) * 4;
-    uint32_t* bitsT = reinterpret_cast<uint32_t*>(ys + YS_WORDS);
+    WaveCtl* ctl = reinterpret_cast<WaveCtl*>(smem_raw);
+    int* ys = reinterpret_cast<int*>(smem_raw + sizeof(WaveCtl));
+    uint32_t* bitsT = reinterpret_cast<uint32_t*>(ys + ROWW + 4);
     float* tiles = reinterpret_cast<float*>(
         (reinterpret_cast<uintptr_t>(bitsT + (size_t)NYB * ROWW) + 127) & ~static_cast<uintptr_t>(127));
 
@@ -368,102 +392,167 @@ __global__ void __launch_bounds__(NT, 1) mas_tma_kernel(const __grid_constant__ 
     int t_y = min(max(p.t_ys[b], 0), p.T_y);
     const bool valid = (t_x >= 1) && (t_y >= t_x);   // t_x > t_y is undefined in the reference
     const int n_tiles = valid ? (t_y + YT - 1) / YT : 0;
+    const int n_act = valid ? (t_x + BAND - 1) / BAND : 0;      // DP warps with rows below t_x
     const size_t plane_elems = (size_t)p.T_x * p.T_y;
     float* __restrict__ pplane = p.path + (size_t)b * plane_elems;
 
     if (tid == 0) {
-        for (int s = 0; s < TMA_MAX_STAGES; ++s) {
-            mbar_init(&full[s], 1);
-            mbar_init(&empty[s], 1);
+        for (int w = 0; w < NDP; ++w) {
+            for (int s = 0; s < TMA_MAX_STAGES; ++s) {
+                mbar_init(&ctl->full[w][s], 1);
+                mbar_init(&ctl->empty[w][s], 1);
+            }
+            for (int s = 0; s < NBOX; ++s) {
+                mbar_init(&ctl->box_full[w][s], 1);
+                mbar_init(&ctl->box_empty[w][s], 1);
+            }
         }
+        mbar_init(&ctl->dp_done, max(n_act, 1));
         mbar_fence_init();
     }
     __syncthreads();
 
-    if (warp == 0) {
-        // ------------------------------------------------------------ DP warp
-        if (lane == 0) mas_stamp(0);
+    if (warp < NDP) {
+        // ------------------------------------------------------------ DP warps
+        const int w = warp;
+        if (w == 0 && lane == 0) mas_stamp(0);
         long long waited = 0;
-        float q[XPT];
-        uint32_t bits[XPT];
-        int roff[XPT];
+        if (w < n_act) {
+            const int r0 = w * BAND;                 // first text row of the band
+            const int x0 = r0 + lane * XPT;
+            const bool send = (w + 1 < n_act);
+            float q[XPT];
+            uint32_t bits[XPT];
+            int roff[XPT];
 #pragma unroll
-        for (int k = 0; k < XPT; ++k) {
-            q[k] = 0.0f;
-            roff[k] = min(lane * XPT + k, RB * TBOX - 1) * TP * 4;   // rows past the tile are never consumed: clamp the read
-        }
-        for (int it = 0; it < n_tiles; ++it) {
-            const int s = it % S, use = it / S;
-            const long long w0 = clock64();
-            mbar_wait(&full[s], use & 1);
-            if (it > 0) waited += clock64() - w0;
-            if (it == 0 && lane == 0) mas_stamp(1);
-            const uint32_t tile = smem_u32(tiles + (size_t)s * tile_floats);
-            const int y0 = it * YT;
+            for (int k = 0; k < XPT; ++k) {
+                q[k] = 0.0f;
+                roff[k] = min(x0 + k, RB * TBOX - 1) * TP * 4;     // rows past the stage are never consumed: clamp the read
+            }
+            float carry = 0.0f;                      // row r0 - 1 at the last frame of the previous tile
+            for (int it = 0; it < n_tiles; ++it) {
+                const int s = it % S, use = it / S, y0 = it * YT;
+                const long long w0 = clock64();
+                fast_wait(&ctl->full[w][s], use & 1);
+                const long long w1 = clock64();
+                if (w == 0 && it > 0) waited += w1 - w0;
+                if (w == 0 && it == 0 && lane == 0) mas_stamp(1);
+                float bv[YT];
+                if (w > 0) {
+                    fast_wait(&ctl->box_full[w - 1][it % NBOX], (it / NBOX) & 1);
+                    const uint32_t bx = smem_u32(&ctl->box[w - 1][it % NBOX][0]);
+                    float4 r[YT / 4];
 #pragma unroll
-            for (int k = 0; k < XPT; ++k) bits[k] = 0u;
-            if (y0 < 32 * XPT) dp_tile4<XPT, true>(tile, roff, q, bits, lane, y0);
-            else               dp_tile4<XPT, false>(tile, roff, q, bits, lane, y0);
+                    for (int j = 0; j < YT / 4; ++j) r[j] = lds128(bx + 16 * j);
+                    bv[0] = carry;
 #pragma unroll
-            for (int k = 0; k < XPT; ++k) bitsT[(size_t)it * ROWW + k * 32 + lane] = bits[k];
+                    for (int j = 0; j < YT / 4; ++j) {
+                        if (4 * j + 1 < YT) bv[4 * j + 1] = r[j].x;
+                        if (4 * j + 2 < YT) bv[4 * j + 2] = r[j].y;
+                        if (4 * j + 3 < YT) bv[4 * j + 3] = r[j].z;
+                        if (4 * j + 4 < YT) bv[4 * j + 4] = r[j].w;
+                    }
+                    carry = r[YT / 4 - 1].w;
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&ctl->box_empty[w - 1][it % NBOX]);
+                }
+                if (send && it >= NBOX) fast_wait(&ctl->box_empty[w][it % NBOX], (it / NBOX - 1) & 1);
+                const long long w2 = clock64();
+                const uint32_t tile = smem_u32(tiles + (size_t)s * stage_floats);
+                const uint32_t bo = smem_u32(&ctl->box[w][it % NBOX][0]);
+#pragma unroll
+                for (int k = 0; k < XPT; ++k) bits[k] = 0u;
+                const bool diag = (y0 < r0 + BAND) && (y0 + YT > r0);
+                if (w == 0) {
+                    if (diag) { if (send) dp_tile4<XPT, true, true, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
+                                else      dp_tile4<XPT, true, true, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
+                    else      { if (send) dp_tile4<XPT, false, true, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
+                                else      dp_tile4<XPT, false, true, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
+                } else {
+                    if (diag) { if (send) dp_tile4<XPT, true, false, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
+                                else      dp_tile4<XPT, true, false, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
+                    else      { if (send) dp_tile4<XPT, false, false, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
+                                else      dp_tile4<XPT, false, false, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
+                }
+                const long long w3 = clock64();
+#pragma unroll
+                for (int k = 0; k < XPT; ++k)
+                    if (x0 + k < ROWW) bitsT[(size_t)it * ROWW + x0 + k] = __brev(bits[k]);
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(&ctl->empty[w][s]);
+                    if (send) mbar_arrive(&ctl->box_full[w][it % NBOX]);
+                }
+#ifdef GTK_MAS_EXP_TILETIME
+                if (it == 10 && lane == 0 && blockIdx.x == 0 && w < 4) {
+                    g_mas_trace[900 * 6 + w * 6 + 0] = (unsigned long long)(w1 - w0);
+                    g_mas_trace[900 * 6 + w * 6 + 1] = (unsigned long long)(w2 - w1);
+                    g_mas_trace[900 * 6 + w * 6 + 2] = (unsigned long long)(w3 - w2);
+                    g_mas_trace[900 * 6 + w * 6 + 3] = (unsigned long long)(clock64() - w3);
+                    g_mas_trace[900 * 6 + w * 6 + 4] = (unsigned long long)w0;
+                }
+#endif
+            }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[s]);
+            if (lane == 0) mbar_arrive(&ctl->dp_done);
         }
-        __syncwarp();
-        if (lane == 0) { mas_stamp(2); if (blockIdx.x < MAS_TRACE_CTAS) g_mas_wait[blockIdx.x] = waited; }
         // ------------------------------------------------------------ backtrack (run-skipping, one thread)
         // Token `index` starts at the highest set bit of its row at or below y.  The loop-carried chain is mask -> clz ->
         // select: the words the NEXT row can need (same 32-frame block or the one before) are loaded one step ahead.
-        if (lane == 0 && valid) {
-            int index = t_x - 1, y = t_y - 1;
-            int k = index % XPT;
-            const uint32_t* rowp = bitsT + k * 32 + index / XPT;       // word of block yb at rowp[yb * ROWW]
-            int yb = y >> 5;
-            uint32_t w = rowp[(size_t)yb * ROWW];
-            while (index > 0 && y >= 0) {
-                const uint32_t* nrow = (k == 0) ? rowp + (XPT - 1) * 32 - 1 : rowp - 32;
-                const uint32_t n0 = nrow[(size_t)yb * ROWW];
-                const uint32_t n1 = nrow[(size_t)max(yb - 1, 0) * ROWW];
-                const uint32_t m = w & (0xffffffffu >> (31 - (y & 31)));
-                if (m) {
-                    const int yp = (yb << 5) + (31 - __clz(m));
-                    ys[index] = yp;       // first frame of token `index`
-                    --index;
-                    k = (k == 0) ? XPT - 1 : k - 1;
-                    rowp = nrow;
-                    y = yp - 1;
-                    const int nyb = y >> 5;                            // yb or yb - 1 (-1 ends the loop)
-                    w = (nyb == yb) ? n0 : n1;
-                    yb = nyb;
-                } else {
-                    y = (yb << 5) - 1;
-                    --yb;
-                    if (yb >= 0) w = rowp[(size_t)yb * ROWW];
+        if (w == 0 && lane == 0) {
+            if (valid) fast_wait(&ctl->dp_done, 0);
+            mas_stamp(2);
+            if (blockIdx.x < MAS_TRACE_CTAS) g_mas_wait[blockIdx.x] = waited;
+            if (valid) {
+                int index = t_x - 1, y = t_y - 1;
+                int yb = y >> 5;
+                const uint32_t* rowp = bitsT + index;                // word of block yb at rowp[yb * ROWW]
+                uint32_t wd = rowp[(size_t)yb * ROWW];
+                while (index > 0 && y >= 0) {
+                    const uint32_t n0 = rowp[(size_t)yb * ROWW - 1];
+                    const uint32_t n1 = rowp[(size_t)max(yb - 1, 0) * ROWW - 1];
+                    const uint32_t m = wd & (0xffffffffu >> (31 - (y & 31)));
+                    if (m) {
+                        const int yp = (yb << 5) + (31 - __clz(m));
+                        ys[index] = yp;       // first frame of token `index`
+                        --index;
+                        --rowp;
+                        y = yp - 1;
+                        const int nyb = y >> 5;                        // yb or yb - 1 (-1 ends the loop)
+                        wd = (nyb == yb) ? n0 : n1;
+                        yb = nyb;
+                    } else {
+                        y = (yb << 5) - 1;
+                        --yb;
+                        if (yb >= 0) wd = rowp[(size_t)yb * ROWW];
+                    }
                 }
+                ys[0] = 0;
+                // y < 0 with index > 0 cannot happen for valid inputs (diagonal bits force the move);
+                // if it did, make the remaining rows empty rather than reading garbage.
+                for (int x = 1; x <= index; ++x) ys[x] = 0;
             }
-            ys[0] = 0;
-            // y < 0 with index > 0 cannot happen for valid inputs (diagonal bits force the move);
-            // if it did, make the remaining rows empty rather than reading garbage.
-            for (int x = 1; x <= index; ++x) ys[x] = 0;
+            mas_stamp(3);
         }
-        if (lane == 0) mas_stamp(3);
-    } else if (warp == 1) {
-        // ------------------------------------------------------------ TMA producer
-        if (lane == 0) {
-            const int nbox = (t_x + TBOX - 1) / TBOX;
+    } else if (warp == NDP) {
+        // ------------------------------------------------------------ TMA producers: lane w feeds DP warp w
+        if (lane < n_act) {
+            const int w = lane;
+            const int r0 = w * BAND;
+            const int nbox = min(XPT, (t_x - r0 + TBOX - 1) / TBOX);
             for (int it = 0; it < n_tiles; ++it) {
                 const int s = it % S, use = it / S;
-                if (use >= 1) mbar_wait(&empty[s], (use - 1) & 1);
-                float* tile = tiles + (size_t)s * tile_floats;
-                mbar_arrive_expect_tx(&full[s], (uint32_t)(nbox * TBOX_BYTES));
+                if (use >= 1) fast_wait(&ctl->empty[w][s], (use - 1) & 1);
+                float* dst = tiles + (size_t)s * stage_floats + (size_t)r0 * TP;
+                mbar_arrive_expect_tx(&ctl->full[w][s], (uint32_t)(nbox * TBOX_BYTES));
                 for (int j = 0; j < nbox; ++j)
-                    tc::tma_load_3d(tile + (size_t)j * TBOX * TP, &tmV, &full[s], it * YT, j * TBOX, b);
+                    tc::tma_load_3d(dst + (size_t)j * TBOX * TP, &tmV, &ctl->full[w][s], it * YT, r0 + j * TBOX, b);
             }
         }
     } else {
         // ------------------------------------------------------------ zero-fill of this utterance's output plane
-        const int ht = tid - 64;
-        constexpr int HT = NT - 64;
+        const int ht = tid - 32 * (NDP + 1);
+        constexpr int HT = NT - 32 * (NDP + 1);
         const uintptr_t addr = reinterpret_cast<uintptr_t>(pplane);
         size_t head = ((16 - (addr & 15)) & 15) / 4;
         if (head > plane_elems) head = plane_elems;
@@ -612,35 +701,28 @@ size_t workspace_bytes(int B, int T_x, int T_y) {
     return (size_t)B * T_y * ceil_div(T_x, 32) * sizeof(uint32_t);
 }
 
-// TMA path: text rows per lane.  A lane stride of XPT * 36 words is conflict-free for odd XPT, 2-way for XPT = 2 mod 4;
-// multiples of 4 (4- / 8-way) take one more row per lane instead.
-static int tma_xpt(int T_x) {
-    int xpt = max(1, ceil_div(T_x, 32));
-    if (xpt % 4 == 0) ++xpt;
-    return xpt;
-}
-static size_t tma_smem_bytes(int xpt, int T_x, int T_y, int stages) {
-    const size_t roww = 32 * (size_t)xpt;
-    const size_t ys_words = ((roww + 1 + 3) / 4) * 4;
+// TMA wavefront path: text rows per lane of each of the NDP DP warps.
+static size_t wave_smem_bytes(int T_x, int T_y, int stages) {
+    const size_t roww = (size_t)((T_x + 3) & ~3);
     const size_t nyb = (T_y + YT - 1) / YT;
     const size_t rb = ceil_div(T_x, TBOX);
-    return 2 * TMA_MAX_STAGES * sizeof(uint64_t) + ys_words * 4 + nyb * roww * 4 + 128 + (size_t)stages * rb * TBOX_BYTES;
+    return sizeof(WaveCtl) + (roww + 4) * 4 + nyb * roww * 4 + 128 + (size_t)stages * rb * TBOX_BYTES;
 }
-static int plan_tma(int T_x, int T_y, int* xpt_out) {
-    const int xpt = tma_xpt(T_x);
+static int plan_wave(int T_x, int T_y, int* xpt_out) {
+    const int xpt = max(1, ceil_div(T_x, 32 * NDP));
     *xpt_out = xpt;
     if (xpt > TMA_MAX_XPT || T_y % 4 != 0) return 0;
     for (int s = TMA_MAX_STAGES; s >= 2; --s)
-        if (tma_smem_bytes(xpt, T_x, T_y, s) <= SMEM_LIMIT) return s;
+        if (wave_smem_bytes(T_x, T_y, s) <= SMEM_LIMIT) return s;
     return 0;
 }
 
 template <int XPT>
-static int launch_tma(const Params& p, const CUtensorMap& tm, size_t smem, cudaStream_t stream) {
-    GTK_CUDA(cudaFuncSetAttribute(mas_tma_kernel<XPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+static int launch_wave(const Params& p, const CUtensorMap& tm, size_t smem, cudaStream_t stream) {
+    GTK_CUDA(cudaFuncSetAttribute(mas_wave_kernel<XPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ProfScope prof("mas", stream);
-    mas_tma_kernel<XPT><<<p.B, NT, smem, stream>>>(tm, p);
-    return check_launch("mas_tma_kernel");
+    mas_wave_kernel<XPT><<<p.B, NT, smem, stream>>>(tm, p);
+    return check_launch("mas_wave_kernel");
 }
 
 template <int XPT>
@@ -668,7 +750,7 @@ int forward(const float* value, const int* t_xs, const int* t_ys, float* path, i
     p.vec4 = ((T_y % 4) == 0) && ((reinterpret_cast<uintptr_t>(value) & 15) == 0);
     int xpt = 0;
     // force_generic: 0 = pick the fastest applicable path, 1 = generic kernel, 2 = helper-warp fast path (no TMA)
-    const int tma_stages = (force_generic == 0 && p.vec4) ? plan_tma(T_x, T_y, &xpt) : 0;
+    const int tma_stages = (force_generic == 0 && p.vec4) ? plan_wave(T_x, T_y, &xpt) : 0;
     if (tma_stages > 0) {
         p.n_stages = tma_stages;
         CUtensorMap tm;
@@ -677,16 +759,15 @@ int forward(const float* value, const int* t_xs, const int* t_ys, float* path, i
         const uint32_t box[3] = {TP, TBOX, 1};
         int rc = tc::make_tmap_f32(&tm, value, 3, dims, strides, box);
         if (rc) return rc;
-        const size_t smem = tma_smem_bytes(xpt, T_x, T_y, tma_stages);
+        const size_t smem = wave_smem_bytes(T_x, T_y, tma_stages);
         switch (xpt) {
-#define GTK_MAS_CASE(N) case N: return launch_tma<N>(p, tm, smem, stream);
-            GTK_MAS_CASE(1) GTK_MAS_CASE(2) GTK_MAS_CASE(3) GTK_MAS_CASE(5) GTK_MAS_CASE(6) GTK_MAS_CASE(7)
-            GTK_MAS_CASE(9) GTK_MAS_CASE(10) GTK_MAS_CASE(11) GTK_MAS_CASE(13) GTK_MAS_CASE(14) GTK_MAS_CASE(15)
-            GTK_MAS_CASE(17)
+#define GTK_MAS_CASE(N) case N: return launch_wave<N>(p, tm, smem, stream);
+            GTK_MAS_CASE(1) GTK_MAS_CASE(2) GTK_MAS_CASE(3) GTK_MAS_CASE(4) GTK_MAS_CASE(5) GTK_MAS_CASE(6)
+            GTK_MAS_CASE(7) GTK_MAS_CASE(8)
 #undef GTK_MAS_CASE
             default: break;
         }
-        set_error("mas: internal: no TMA instantiation for XPT=%d", xpt);
+        set_error("mas: internal: no wavefront instantiation for XPT=%d", xpt);
         return GTK_ERR_UNSUPPORTED;
     }
     const int stages = force_generic == 1 ? 0 : plan_fast(T_x, T_y, &xpt);
