@@ -303,7 +303,7 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {      // explicit ld.sh
 }
 
 // One DP column of one warp.  `up_in` = DP value of the row below this warp's band at column y - 1 (lane 0 only).
-// Decision bits are shifted in MSB-first (frame 0 of the tile ends at bit 31; the caller bit-reverses the word).
+// Decision bits are shifted in MSB-first (frame 0 of the tile ends at bit 31), the order the backtrack wants.
 // Off the diagonal: sign(a - b) == (a < b) exactly, because a DP value is never -0 (a sum is -0 only if both addends
 // are; the recursion starts from +0 and the sentinels are non-zero) and fp32 subtraction of unequal finite numbers is
 // never zero (denormals are kept: no -ftz); fmaxf(a, b) == ((b > a) ? b : a) for non-NaN input.
@@ -477,7 +477,7 @@ __global__ void __launch_bounds__(NT, 1) mas_wave_kernel(const __grid_constant__
                 const long long w3 = clock64();
 #pragma unroll
                 for (int k = 0; k < XPT; ++k)
-                    if (x0 + k < ROWW) bitsT[(size_t)it * ROWW + x0 + k] = __brev(bits[k]);
+                    if (x0 + k < ROWW) bitsT[(size_t)it * ROWW + x0 + k] = bits[k];      // MSB-first: frame f at bit 31 - f
                 __syncwarp();
                 if (lane == 0) {
                     mbar_arrive(&ctl->empty[w][s]);
@@ -504,28 +504,39 @@ __global__ void __launch_bounds__(NT, 1) mas_wave_kernel(const __grid_constant__
             mas_stamp(2);
             if (blockIdx.x < MAS_TRACE_CTAS) g_mas_wait[blockIdx.x] = waited;
             if (valid) {
-                int index = t_x - 1, y = t_y - 1;
-                int yb = y >> 5;
-                const uint32_t* rowp = bitsT + index;                // word of block yb at rowp[yb * ROWW]
-                uint32_t wd = rowp[(size_t)yb * ROWW];
-                while (index > 0 && y >= 0) {
-                    const uint32_t n0 = rowp[(size_t)yb * ROWW - 1];
-                    const uint32_t n1 = rowp[(size_t)max(yb - 1, 0) * ROWW - 1];
-                    const uint32_t m = wd & (0xffffffffu >> (31 - (y & 31)));
-                    if (m) {
-                        const int yp = (yb << 5) + (31 - __clz(m));
-                        ys[index] = yp;       // first frame of token `index`
-                        --index;
-                        --rowp;
-                        y = yp - 1;
-                        const int nyb = y >> 5;                        // yb or yb - 1 (-1 ends the loop)
-                        wd = (nyb == yb) ? n0 : n1;
-                        yb = nyb;
-                    } else {
-                        y = (yb << 5) - 1;
-                        --yb;
-                        if (yb >= 0) wd = rowp[(size_t)yb * ROWW];
+                // Decision words are MSB-first (frame f of the block at bit 31 - f), so "the last frame <= y whose bit is set"
+                // is the LOWEST set bit of (word & M), M = the bit positions still allowed.  Per token the loop-carried
+                // chain is 4 ALU operations (and, isolate lowest bit b, M = bits above b); the frame number (clz b) is off
+                // the chain.  The words of the next BT_ROWS rows of the current 32-frame block are loaded together; a token
+                // that starts in an earlier block (m == 0) ends the batch and moves one block down with M = all ones.
+                constexpr int BT_ROWS = 8;
+                int index = t_x - 1;
+                int yb = (t_y - 1) >> 5;
+                uint32_t M = 0xffffffffu << (31 - ((t_y - 1) & 31));
+                while (index > 0 && yb >= 0) {
+                    const uint32_t* base = bitsT + (size_t)yb * ROWW + index;      // word of (row index, block yb)
+                    uint32_t W[BT_ROWS];
+#pragma unroll
+                    for (int j = 0; j < BT_ROWS; ++j) W[j] = base[-min(j, index)];
+                    const int f0 = yb << 5;
+                    int done = 0;
+                    bool live = true, cross = false;
+#pragma unroll
+                    for (int j = 0; j < BT_ROWS; ++j) {
+                        const bool act = live && (index - j >= 1);
+                        const uint32_t m = W[j] & M;
+                        const bool hit = act && (m != 0u);
+                        const uint32_t bb = m & (0u - m);
+                        if (hit) {
+                            ys[index - j] = f0 + __clz(bb);                        // first frame of token index - j
+                            M = ~(bb | (bb - 1u));
+                            ++done;
+                        }
+                        cross = cross || (act && !hit);
+                        live = hit;
                     }
+                    index -= done;
+                    if (cross) { --yb; M = 0xffffffffu; }
                 }
                 ys[0] = 0;
                 // y < 0 with index > 0 cannot happen for valid inputs (diagonal bits force the move);
