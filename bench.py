@@ -12,7 +12,8 @@ parameters; + NCCL all-reduce of the flat decoder gradient when N > 1).  One JSO
                inside the timed region (through glowtts_b200.hot_path.train_hot_path, the user-facing call).
 * roofline   : the dominant kernel family (the WaveNet convolutions), timed with CUDA events around every
                launch by the library's own profiler (gtk_prof_*) in a separate pass of the same steps.
-* mas        : the MAS kernel alone on configs[0] (B=32, T_x=180, T_y=860) and its HBM roofline.
+* mas        : the MAS kernel alone on configs[0] (B=32, T_x=180, T_y=860) and its HBM roofline; mas_stress: the same
+               on configs[4]'s per-GPU shape (B=512, T_x=400, T_y=2000); inference: the reverse decoder flow (configs[2]).
 * cpu_baseline: the CPU restatement (oracle/) on a bounded sample, host cores of this box.
 """
 from __future__ import annotations
@@ -41,7 +42,8 @@ FLOP_PER_SQ_FRAME_FWD = 2 * (192 * 80 + 4 * (384 * 192 * 5) + 3 * (384 * 192) + 
 SEED = 1234  # configs/base.json:5
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed `ncu --set full`
 # capture (profiles/); bench.py never runs under a profiler, so the figure is carried here and updated per round.
-NCU_TRAFFIC = {"wn_layer_tc": 23.05e6}   # profiles/ncu_wn_layer_r01.txt: (16.89 + 0.82 MB, 27.50 + 0.89 MB) -> mean bytes / launch
+NCU_TRAFFIC = {"wn_layer_tc": 23.05e6,      # profiles/ncu_wn_layer_r01.txt: (16.89 + 0.82 MB, 27.50 + 0.89 MB) -> mean bytes / launch
+               "wn_bwd_layer_tc": 33.0e6}   # profiles/ncu_wn_bwd_layer_r01.txt: 32.78 MB read + 0.2 MB written per launch
 
 
 def peaks():
@@ -206,13 +208,12 @@ def timed(fn, steps, world):
     return max_over_ranks(e0.elapsed_time(e1), torch.device("cuda", torch.cuda.current_device()))
 
 
-def mas_alone(device, steps=20):
-    """configs[0]: maximum_path on synthetic fp32 logp, B=32, T_x=180, T_y=860, full lengths.  Rotates over
-    enough distinct inputs to exceed the 126 MB L2 between repeats."""
+def mas_alone(device, steps=20, B=32, TX=T_TEXT, TY=T_MEL, n_buf=8, name="configs[0]"):
+    """configs[0]: maximum_path on synthetic fp32 logp, B=32, T_x=180, T_y=860, full lengths (rotating over enough
+    distinct inputs to exceed the 126 MB L2 between repeats); configs[4] per GPU: B=512, T_x=400, T_y=2000 (one
+    3.3 GB input: far larger than L2)."""
     from glowtts_b200 import _lib, ops
-    B, TX, TY = 32, T_TEXT, T_MEL
     gen = torch.Generator(device=device).manual_seed(SEED)
-    n_buf = 8                                                  # 8 x 19.8 MB value + 8 x 19.8 MB path > L2
     vals = [torch.randn(B, TX, TY, device=device, generator=gen) for _ in range(n_buf)]
     t_xs = torch.full((B,), TX, dtype=torch.int32, device=device)
     t_ys = torch.full((B,), TY, dtype=torch.int32, device=device)
@@ -230,11 +231,39 @@ def mas_alone(device, steps=20):
     per = ms / max(n, 1) * 1e-3
     pk = peaks()
     gbs = cells * 8 / per / 1e9 if per > 0 else 0.0
-    return {"workload": "maximum_path B=32 T_x=180 T_y=860 fp32, full lengths", "cells_per_s": cells / per if per else 0.0,
+    del vals
+    return {"workload": f"{name}: maximum_path B={B} T_x={TX} T_y={TY} fp32, full lengths", "cells_per_s": cells / per if per else 0.0,
             "us_per_call": per * 1e6, "launches_timed": n,
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
                          "traffic": None, "algorithmic_bytes_per_cell": 8, "peak_source": pk["src"]},
-            "latency_floor_note": "T_y=860 dependent DP columns per utterance; 32 CTAs on 148 SMs"}
+            "latency_floor_note": f"T_y={TY} dependent DP columns per utterance; {B} CTAs on 148 SMs"}
+
+
+def inference_alone(run, steps=10):
+    """configs[2] at the train-step batch: the reverse decoder flow z -> mel (models.py:1230) after store_inverse(),
+    no_grad, B=32 x T_mel=860 resident in HBM; CUDA events over `steps` calls."""
+    dec = run.dec
+    y, y_len = run.dev[0], run.dev[1]
+    mask = (torch.arange(T_MEL, device=y.device)[None, :] < y_len[:, None]).float().unsqueeze(1)
+    was_training = dec.training
+    dec.eval()
+    with torch.no_grad():
+        z = torch.randn_like(y) * mask
+        for _ in range(3):
+            dec(z, mask, reverse=True)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            dec(z, mask, reverse=True)
+        e1.record()
+        torch.cuda.synchronize()
+    dec.train(was_training)
+    ms = e0.elapsed_time(e1) / steps
+    frames = int(y_len.sum())
+    flop = FLOP_PER_SQ_FRAME_FWD * CFG["n_blocks"] * (frames // CFG["n_sqz"])
+    return {"workload": "reverse decoder flow z -> mel, B=32, T_mel=860 (ragged), no_grad", "mel_frames_per_s": frames / (ms * 1e-3),
+            "ms_per_call": ms, "tflops_valid_frames": flop / (ms * 1e-3) / 1e12}
 
 
 # ------------------------------------------------------------------------------------------ CPU legs
@@ -396,7 +425,9 @@ def main():
         sq_frames_padded = B_PER_GPU * (T_MEL // 2)
         H, K, L = CFG["hidden_channels"], CFG["kernel_size"], CFG["n_layers"]
         if "wn_layer_tc" in prof:
-            tag = "wn_layer_tc"
+            # dominant = the fused WaveNet-layer kernel that takes more of the step: forward (k=5 conv GEMM -> gate ->
+            # res/skip GEMM) or backward (res/skip data gradient -> gate backward -> k=5 data gradient): same GEMM shapes.
+            tag = max(("wn_layer_tc", "wn_bwd_layer_tc"), key=lambda t: prof.get(t, (0, 0.0))[1])
             # per frame: 2H x (H K) conv + RS x H res/skip, RS = 2H except the last layer of a block (H); mean over layers
             flop_per_frame = 2.0 * (2 * H * H * K) + 2.0 * H * H * (2 * (L - 1) + 1) / L
         else:
@@ -426,6 +457,13 @@ def main():
             "roofline": roof, "clocks": clk,
         }
         out["mas"] = mas_alone(device)
+        out["inference"] = inference_alone(run)
+        del run
+        torch.cuda.empty_cache()
+        try:
+            out["mas_stress"] = mas_alone(device, steps=5, B=512, TX=400, TY=2000, n_buf=1, name="configs[4] on one GPU")
+        except Exception as e:                              # 6.6 GB of buffers: report, never hide the main numbers
+            out["mas_stress"] = {"error": repr(e)}
         if world == 1 and not args.no_cpu_baseline:
             try:
                 out["cpu_baseline"] = cpu_baseline()

@@ -60,3 +60,38 @@ def expand_prior(x_m, x_logs, index):
     """models.py:1118-1119 (attn^T x_m, attn^T x_logs) as a gather by the per-frame token index."""
     t_y = index.shape[1]
     return ops.gather_tokens(x_m, index, t_y), ops.gather_tokens(x_logs, index, t_y)
+
+
+def clip_grad_value_(parameters, clip_value, norm_type=2):
+    """commons.py:320-336: total gradient norm (|g|^p summed over all parameters, then ^(1/p)) and, when
+    ``clip_value`` is not None, an in-place clamp of every gradient to [-clip_value, clip_value].
+
+    The reference syncs the host once per parameter (``.item()``, ~300 per step); here gradients that are
+    neighbours in memory (the decoder's flat gradient buffer is ONE range) are merged, each range is one
+    launch, and the norm stays on the device: the return value is a 0-d CUDA tensor (``float()`` it to get
+    the reference's python float)."""
+    if isinstance(parameters, torch.Tensor):
+        parameters = [parameters]
+    grads = [p.grad for p in parameters if p.grad is not None]
+    norm_type = float(norm_type)
+    if not grads:
+        return torch.zeros((), device="cuda")
+    for g in grads:
+        if not (g.is_cuda and g.dtype == torch.float32 and g.is_contiguous()):
+            raise RuntimeError("glowtts_b200: clip_grad_value_ needs contiguous CUDA fp32 gradients (there is no CPU path)")
+    acc = torch.zeros(1, dtype=torch.float32, device=grads[0].device)
+    spans = sorted(((g.data_ptr(), g.numel(), g) for g in grads if g.numel() > 0), key=lambda t: t[0])
+    i = 0
+    while i < len(spans):
+        ptr, n, first = spans[i]
+        j = i + 1
+        while j < len(spans) and spans[j][0] == ptr + 4 * n and spans[j][2].untyped_storage().data_ptr() == first.untyped_storage().data_ptr():
+            n += spans[j][1]
+            j += 1
+        if j == i + 1:
+            rng = first.view(-1)
+        else:                           # neighbours in one storage: a single flat view over all of them
+            rng = first.new_empty(0).set_(first.untyped_storage(), (ptr - first.untyped_storage().data_ptr()) // 4, (n,), (1,))
+        ops.clip_grad_value(rng, 0.0 if clip_value is None else float(clip_value), clip_value is not None, norm_type, acc)
+        i = j
+    return acc[0] ** (1.0 / norm_type)

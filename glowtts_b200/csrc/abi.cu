@@ -167,6 +167,9 @@ int gtk_row_sum(const float* in, float* out, int R, int T, int accumulate, void*
 int gtk_channel_sum(const float* in, float* out, int B, int M, int T, int accumulate, void* stream) {
     return flow::channel_sum(in, nullptr, out, B, M, T, accumulate, ST);
 }
+int gtk_clip_grad_value(float* grad, long long n, float clip_value, int do_clip, float norm_type, float* acc, void* stream) {
+    return flow::clip_grad_value(grad, n, clip_value, do_clip, norm_type, acc, ST);
+}
 int gtk_mle_loss_fwd(const float* z, const float* m, const float* logs, const float* logdet, const float* mask, float* acc4,
                      float* loss, int B, int C, int T, void* stream) {
     return flow::mle_loss_fwd(z, m, logs, logdet, mask, acc4, loss, B, C, T, ST);

@@ -412,6 +412,46 @@ int mle_loss_fwd(const float* z, const float* m, const float* logs, const float*
     mle_finalize_kernel<<<1, PW_NT, 0, st>>>(acc4, logdet, B, C, loss);
     return check_launch("mle_finalize");
 }
+// ------------------------------------------------------------------------------------------ clip_grad_value_
+// commons.clip_grad_value_ (commons.py:320-336) over ONE contiguous range of gradients: acc[0] += sum |g|^p, and
+// g = clamp(g, -clip, clip) in place when do_clip.  The reference loops over parameters with a .item() host sync each;
+// the caller here passes the flat gradient buffer (or merges neighbouring tensors) and takes acc^(1/p) on the device.
+template <int MODE>   // 0: p == 2, 1: p == 1, 2: general p
+__global__ void clip_grad_kernel(float* __restrict__ g, long long n, float clip, int do_clip, float p, float* __restrict__ acc) {
+    __shared__ float scratch[33];
+    float s = 0.f;
+    const long long stride = (long long)gridDim.x * blockDim.x, i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const uintptr_t a = reinterpret_cast<uintptr_t>(g);
+    long long head = (long long)(((16 - (a & 15)) & 15) / 4);
+    if (head > n) head = n;
+    const long long nvec = (n - head) / 4;
+    float4* gv = reinterpret_cast<float4*>(g + head);
+    auto term = [&](float v) { return MODE == 0 ? v * v : MODE == 1 ? fabsf(v) : powf(fabsf(v), p); };
+    auto cl = [&](float v) { return fminf(fmaxf(v, -clip), clip); };
+    for (long long i = i0; i < nvec; i += stride) {
+        float4 v = gv[i];
+        s += term(v.x) + term(v.y) + term(v.z) + term(v.w);
+        if (do_clip) { v.x = cl(v.x); v.y = cl(v.y); v.z = cl(v.z); v.w = cl(v.w); gv[i] = v; }
+    }
+    for (long long i = i0; i < head + (n - head - nvec * 4); i += stride) {      // unaligned head and tail scalars
+        const long long j = i < head ? i : head + nvec * 4 + (i - head);
+        const float v = g[j];
+        s += term(v);
+        if (do_clip) g[j] = cl(v);
+    }
+    s = block_sum<PW_NT>(s, scratch);
+    if (threadIdx.x == 0) atomicAdd(acc, s);
+}
+int clip_grad_value(float* grad, long long n, float clip, int do_clip, float norm_type, float* acc, cudaStream_t st) {
+    GTK_REQUIRE(acc && (grad || n == 0) && n >= 0 && norm_type > 0.f, "clip_grad_value arguments");
+    if (n == 0) return GTK_OK;
+    const int grid = pw_grid(ceil_div_ll(n, 4));
+    if (norm_type == 2.f)      clip_grad_kernel<0><<<grid, PW_NT, 0, st>>>(grad, n, clip, do_clip, norm_type, acc);
+    else if (norm_type == 1.f) clip_grad_kernel<1><<<grid, PW_NT, 0, st>>>(grad, n, clip, do_clip, norm_type, acc);
+    else                       clip_grad_kernel<2><<<grid, PW_NT, 0, st>>>(grad, n, clip, do_clip, norm_type, acc);
+    return check_launch("clip_grad_value");
+}
+
 // gloss: device scalar upstream gradient.  dz, dm, dlogs, dlogdet nullable.
 __global__ void mle_bwd_kernel(const float* __restrict__ z, const float* __restrict__ m, const float* __restrict__ logs,
                                const float* __restrict__ acc4, const float* __restrict__ gloss, float* __restrict__ dz,

@@ -72,6 +72,7 @@ int cat_mask(const float* a, const float* b, const float* mask, float* out, int 
 int weightnorm_fwd(const float* g, const float* v, float* w, float* norm_out, int M, int R, cudaStream_t st);
 int weightnorm_bwd(const float* g, const float* v, const float* dw, float* dg, float* dv, int M, int R, int accumulate,
                    cudaStream_t st);
+int clip_grad_value(float* grad, long long n, float clip, int do_clip, float norm_type, float* acc, cudaStream_t st);
 int mle_loss_fwd(const float* z, const float* m, const float* logs, const float* logdet, const float* mask, float* acc4,
                  float* loss, int B, int C, int T, cudaStream_t st);
 int mle_loss_bwd(const float* z, const float* m, const float* logs, const float* acc4, const float* gloss, float* dz,

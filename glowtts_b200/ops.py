@@ -85,6 +85,17 @@ def _(value, t_xs, t_ys, force_generic=0):
             value.new_empty((B, T_y), dtype=torch.int32))
 
 
+# =============================================================================== clip_grad_value_
+@torch.library.custom_op(f"{NS}::clip_grad_value", mutates_args=("grad", "acc"), device_types="cuda")
+def clip_grad_value(grad: Tensor, clip_value: float, do_clip: bool, norm_type: float, acc: Tensor) -> None:
+    """commons.py:320-336 over one contiguous gradient range: acc += sum |g|^p, clamp in place if do_clip."""
+    if not (grad.is_cuda and grad.dtype == torch.float32 and grad.is_contiguous()):
+        raise RuntimeError("glowtts_b200: clip_grad_value needs a contiguous CUDA fp32 gradient")
+    acc = _chk(acc, "acc")
+    _lib.call("gtk_clip_grad_value", _p(grad), grad.numel(), float(clip_value), int(do_clip), float(norm_type), _p(acc),
+              _stream())
+
+
 # =============================================================================== logp
 @torch.library.custom_op(f"{NS}::logp", mutates_args=(), device_types="cuda")
 def logp(x_m: Tensor, x_logs: Optional[Tensor], z: Tensor) -> Tensor:

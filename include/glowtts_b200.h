@@ -85,6 +85,10 @@ int gtk_dropout_scale(unsigned long long seed, float p, long long n, float* out,
 unsigned long long gtk_decoder_layer_seed(unsigned long long seed, int block, int layer);
 int gtk_row_sum(const float* in, float* out, int R, int T, int accumulate, void* stream);
 int gtk_channel_sum(const float* in, float* out, int B, int M, int T, int accumulate, void* stream);
+/* commons.clip_grad_value_ (commons.py:320-336) over one contiguous range of n gradients: *acc += sum |g|^norm_type and,
+ * when do_clip, g = clamp(g, -clip_value, clip_value) in place.  Stream-ordered, no host sync: the caller zeroes acc,
+ * calls once per contiguous range (once for a flat gradient buffer) and takes acc^(1/norm_type) on the device. */
+int gtk_clip_grad_value(float* grad, long long n, float clip_value, int do_clip, float norm_type, float* acc, void* stream);
 /* commons.mle_loss (commons.py:28-33).  m/logs may be NULL (= 0).  acc4: 4 floats of scratch that
  * must be kept for the backward.  loss: 1 float. */
 int gtk_mle_loss_fwd(const float* z, const float* m, const float* logs, const float* logdet, const float* mask, float* acc4,

@@ -82,6 +82,17 @@ def logp(x_m: Tensor, x_logs: Tensor, z: Tensor) -> Tensor:
     return t1 + t2 + t3 + t4
 
 
+def clip_grad_value_(grads, clip_value, norm_type=2):
+    """commons.py:320-336 on a list of gradient tensors (modified in place) -> total norm (python float)."""
+    norm_type = float(norm_type)
+    total = 0.0
+    for g in grads:
+        total += float(g.norm(norm_type)) ** norm_type
+        if clip_value is not None:
+            g.clamp_(min=-float(clip_value), max=float(clip_value))
+    return total ** (1.0 / norm_type)
+
+
 def generate_path(duration: Tensor, mask: Tensor) -> Tensor:
     """commons.py:127-143: durations [B,T_x] -> hard alignment [B,T_x,T_y]."""
     b, t_x, t_y = mask.shape

@@ -310,3 +310,38 @@ def test_decoder_dropout_matches_oracle_given_the_mask(use_g):
         z_eval, _ = dec(y.cuda(), mask.cuda(), g=None if cond is None else cond.cuda())
         z_plain, _ = oflow.decoder(sd, y, mask, g=cond, **_kw(cfg))
     np.testing.assert_allclose(z_eval.cpu().numpy(), z_plain.numpy(), **TOL)
+
+
+@pytest.mark.parametrize("norm_type,clip", [(2, None), (2, 0.05), (1, 0.1), (3, 0.02)])
+def test_clip_grad_value_matches_oracle(norm_type, clip):
+    """commons.clip_grad_value_ (commons.py:320-336): separate tensors, neighbours in one flat buffer, odd offsets."""
+    from glowtts_b200 import commons
+    gen = torch.Generator().manual_seed(11)
+    flat = torch.randn(10007, generator=gen) * 0.1
+    cuts = [0, 3, 1030, 1031, 5000, 10007]                     # views into one buffer, unaligned starts
+    loose = [torch.randn(257, 3, generator=gen) * 0.1, torch.randn(1, generator=gen)]
+    want_grads = [flat[a:b].clone() for a, b in zip(cuts, cuts[1:])] + [t.clone() for t in loose]
+    want = oflow.clip_grad_value_(want_grads, clip, norm_type)
+    dflat = flat.cuda()
+    params = []
+    for a, b in zip(cuts, cuts[1:]):
+        p = torch.nn.Parameter(torch.zeros(b - a, device="cuda"))
+        p.grad = dflat[a:b]
+        params.append(p)
+    for t in loose:
+        p = torch.nn.Parameter(torch.zeros_like(t, device="cuda"))
+        p.grad = t.cuda()
+        params.append(p)
+    params.append(torch.nn.Parameter(torch.zeros(4, device="cuda")))       # no gradient: skipped
+    n0 = _lib_launches()
+    got = commons.clip_grad_value_(params[::-1], clip, norm_type)          # any order
+    assert _lib_launches() - n0 == 3                                       # one launch for the flat buffer + 2 loose tensors
+    assert got.is_cuda and got.dim() == 0
+    np.testing.assert_allclose(float(got), want, rtol=2e-5)
+    for p, w in zip(params, want_grads):
+        assert torch.equal(p.grad.cpu(), w)
+
+
+def _lib_launches():
+    from glowtts_b200 import _lib
+    return _lib.launch_count()

@@ -125,3 +125,24 @@ def test_coupling_and_wn_against_live_reference():
         zr_ref, _ = cb(z_ref, mask, g=g, reverse=True, **kwargs)
         zr, _ = oflow.coupling(sd, "cb", z, mask, hidden=12, dilation_rate=2, n_layers=3, g=g, reverse=True, **kwargs)
         assert torch.allclose(zr, zr_ref, atol=1e-5)
+
+
+@pytest.mark.parametrize("norm_type,clip", [(2, None), (2, 0.05), (1, 0.1), (3, 0.02)])
+def test_clip_grad_value_restatement_matches_reference(norm_type, clip):
+    """oracle.flow.clip_grad_value_ vs the reference's commons.clip_grad_value_ (commons.py:320-336)."""
+    ref = refimport.load()
+    if ref is None:
+        pytest.skip("/root/reference not present")
+    gen = torch.Generator().manual_seed(3)
+    grads = [torch.randn(n, generator=gen) * 0.1 for n in (5, 1000, 33)]
+    params = []
+    for g in grads:
+        p = torch.nn.Parameter(torch.zeros_like(g))
+        p.grad = g.clone()
+        params.append(p)
+    want = ref.commons.clip_grad_value_(params, clip, norm_type)
+    mine = [g.clone() for g in grads]
+    got = oflow.clip_grad_value_(mine, clip, norm_type)
+    assert abs(got - want) <= 1e-6 * max(1.0, abs(want))
+    for p, m in zip(params, mine):
+        assert torch.equal(p.grad, m)
