@@ -10,9 +10,9 @@ from . import modules, ops
 class CouplingBlock(nn.Module):
     """Affine coupling: start 1x1 -> WN -> end 1x1 -> z1 = (m + e^logs x1) mask, logdet = sum logs mask.
 
-    The fork's extra pitch / energy WaveNets (attentions.py:114-117) are identity when their
-    conditioning is None (modules.py:323-324), which is the path implemented here; passing
-    ``pitch``/``energy`` raises (a "next" row)."""
+    The fork's extra pitch / energy WaveNets (``wn_energy``, ``wn_pitch``: attentions.py:114-117, applied in series
+    after ``wn``, attentions.py:155-160) are modules.WNP: identity when their conditioning is None
+    (modules.py:323-324), a WN with a time-varying conditioner otherwise."""
 
     def __init__(self, in_channels, hidden_channels, kernel_size, dilation_rate, n_layers, gin_channels=0,
                  emoin_channels=0, p_dropout=0, sigmoid_scale=False, n_sqz=2):
@@ -31,22 +31,31 @@ class CouplingBlock(nn.Module):
         end.weight.data.zero_()     # attentions.py:107-110: the block starts as the identity
         end.bias.data.zero_()
         self.end = end
+        # module order as the reference registers them (attentions.py:114-117), so state_dict() iterates alike
+        self.wn_pitch = modules.WNP(hidden_channels, kernel_size, dilation_rate, n_layers, p_dropout, 1, n_sqz)
+        self.wn_energy = modules.WNP(hidden_channels, kernel_size, dilation_rate, n_layers, p_dropout, 1, n_sqz)
         self.wn = modules.WN(in_channels, hidden_channels, kernel_size, dilation_rate, n_layers, gin_channels, p_dropout)
 
     def forward(self, x, x_mask=None, reverse=False, g=None, emo=None, pitch=None, energy=None, **kwargs):
-        if pitch is not None or energy is not None:
-            raise NotImplementedError("glowtts_b200.CouplingBlock: pitch/energy WaveNets are not built yet")
+        if pitch is not None and pitch.dim() == 2:
+            pitch = pitch.unsqueeze(1)          # [B,T] -> [B,1,T] (attentions.py:137-141)
+        if energy is not None and energy.dim() == 2:
+            energy = energy.unsqueeze(1)
         m2 = modules._mask2d(x_mask)
         mask = 1 if x_mask is None else x_mask
         x_0 = x[:, : self.in_channels // 2].contiguous()
         h = self.start(x_0) * mask
         h = self.wn(h, x_mask, g)
+        h = self.wn_energy(h, x_mask, energy)
+        h = self.wn_pitch(h, x_mask, pitch)
         out = self.end(h)
         z, logdet = ops.coupling_affine(x, out, m2, reverse, bool(self.sigmoid_scale))
         return z, (None if reverse else logdet)
 
     def store_inverse(self):
         self.wn.remove_weight_norm()
+        self.wn_energy.remove_weight_norm()
+        self.wn_pitch.remove_weight_norm()
 
 
 def block_param_list(actnorm, invconv, coupling):

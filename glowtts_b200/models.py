@@ -90,7 +90,8 @@ class FlowSpecDecoder(nn.Module):
 
     def forward(self, x, x_mask, g=None, emo=None, pitch=None, energy=None, reverse=False):
         if pitch is not None or energy is not None:
-            raise NotImplementedError("glowtts_b200.FlowSpecDecoder: pitch/energy WaveNets are not built yet")
+            # live-fork configuration (three WaveNets per coupling block): flow by flow through the module-level ops
+            return self._forward_unfused(x, x_mask, g, reverse, pitch=pitch, energy=energy)
         for b in range(self.n_blocks):          # data-dependent init, if requested (init.py:17-23)
             if not self.flows[3 * b].initialized:
                 return self._forward_unfused(x, x_mask, g, reverse)
@@ -173,16 +174,16 @@ class FlowSpecDecoder(nn.Module):
             else:
                 p.grad.add_(v)
 
-    def _forward_unfused(self, x, x_mask, g=None, reverse=False):
+    def _forward_unfused(self, x, x_mask, g=None, reverse=False, pitch=None, energy=None):
         """Flow by flow through the module-level ops (used for the DDI pass, where ActNorm statistics must be
-        taken between flows)."""
+        taken between flows, and for the pitch / energy conditioned blocks of the live fork)."""
         from . import commons
         flows = list(self.flows) if not reverse else list(reversed(self.flows))
         logdet_tot = 0 if not reverse else None
         if self.n_sqz > 1:
             x, x_mask = commons.squeeze(x, x_mask, self.n_sqz)
         for f in flows:
-            x, logdet = f(x, x_mask, g=g, reverse=reverse)
+            x, logdet = f(x, x_mask, g=g, pitch=pitch, energy=energy, reverse=reverse)
             if not reverse:
                 logdet_tot = logdet_tot + logdet
         if self.n_sqz > 1:

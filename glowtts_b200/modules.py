@@ -235,3 +235,70 @@ class WN(nn.Module):
             l.remove_weight_norm()
         for l in self.res_skip_layers:
             l.remove_weight_norm()
+
+
+class WNP(nn.Module):
+    """modules.py:272-362: the fork's pitch / energy WaveNet.  Same body as WN, but the conditioner is
+    ``cond_layer1`` (1x1 conv, gin_channels1 -> 2*H*L/n_sqz) applied to the UN-squeezed [B,gin1,T_y] track and then
+    squeezed to [B,2HL,T'] -- a time-varying conditioner; the module is the identity when ``g1`` is None
+    (modules.py:323-324).  Composes the library's conv, squeeze, gate (cond_mode 2) and weight-norm ops."""
+
+    def __init__(self, hidden_channels, kernel_size, dilation_rate, n_layers, p_dropout=0, gin_channels1=0, n_sqz=2):
+        super().__init__()
+        assert kernel_size % 2 == 1
+        assert hidden_channels % 2 == 0
+        self.hidden_channels = hidden_channels
+        self.kernel_size = kernel_size
+        self.dilation_rate = dilation_rate
+        self.n_layers = n_layers
+        self.p_dropout = p_dropout
+        self.n_sqz = n_sqz
+        self.gin_channels1 = gin_channels1
+        self.in_layers = nn.ModuleList()
+        self.res_skip_layers = nn.ModuleList()
+        if gin_channels1 != 0:
+            self.cond_layer1 = WeightNormConv1d(gin_channels1, 2 * hidden_channels * n_layers // n_sqz, 1)
+        for i in range(n_layers):
+            self.in_layers.append(WeightNormConv1d(hidden_channels, 2 * hidden_channels, kernel_size,
+                                                   dilation=dilation_rate ** i))
+            rs = 2 * hidden_channels if i < n_layers - 1 else hidden_channels
+            self.res_skip_layers.append(WeightNormConv1d(hidden_channels, rs, 1))
+
+    def conditioning(self, g1):
+        """cond_layer1(g1) then WNP.squeeze (modules.py:320-322, 353-362): [B,gin1,T_y] -> [B,2HL,T_y/n_sqz]."""
+        cond = self.cond_layer1(g1.to(torch.float32).contiguous())
+        if self.n_sqz > 1:
+            cond, _ = ops.squeeze_op(cond, None, self.n_sqz)
+        return cond
+
+    def forward(self, x, x_mask=None, g1=None, g2=None, **kwargs):
+        if g1 is None:
+            return x
+        H = self.hidden_channels
+        drop = self.training and self.p_dropout > 0
+        seed = ops.draw_seed() if drop else 0
+        mask = 1 if x_mask is None else x_mask
+        cond = self.conditioning(g1)
+        assert cond.shape[2] == x.shape[2], "pitch/energy track length must be n_sqz x the squeezed frame count"
+        output = None
+        for i in range(self.n_layers):
+            x_in = self.in_layers[i](x)
+            if drop:                          # modules.py:331, with the library's counter-based mask
+                x_in = x_in * ops.dropout_scale(seed, 0, i, self.p_dropout, x_in.shape[0], x_in.shape[2], 2 * H, x_in.device)
+            acts = ops.gate_fwd(x_in, cond[:, 2 * H * i: 2 * H * (i + 1)].contiguous())
+            rs = self.res_skip_layers[i](acts)
+            if i < self.n_layers - 1:
+                x = (x + rs[:, :H]) * mask
+                skip = rs[:, H:]
+            else:
+                skip = rs
+            output = skip if output is None else output + skip
+        return output * mask
+
+    def remove_weight_norm(self):
+        if self.gin_channels1 != 0:
+            self.cond_layer1.remove_weight_norm()
+        for l in self.in_layers:
+            l.remove_weight_norm()
+        for l in self.res_skip_layers:
+            l.remove_weight_norm()

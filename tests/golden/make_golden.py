@@ -101,6 +101,47 @@ def gen_flow(ref):
         print(name, float(loss), float((y_rev - y.detach()).abs().max()))
 
 
+PROSODY_CASES = {
+    # name: (cfg, sd_seed, b, t, in_seed, use_g, use_pitch, use_energy)   -- the live fork's 3-WN coupling blocks
+    "flow_tiny_pe": (dict(helpers.TINY_CFG, gin_channels=6), 25, 3, 14, 35, True, True, True),
+    "flow_tiny_p": (helpers.TINY_CFG, 26, 2, 12, 36, False, True, False),
+}
+
+
+prosody_inputs = helpers.prosody_inputs
+
+
+def gen_flow_prosody(ref):
+    """FlowSpecDecoder with pitch / energy tracks: every coupling block runs wn -> wn_energy -> wn_pitch
+    (attentions.py:155-160, modules.WNP)."""
+    for name, (cfg, sd_seed, b, t, in_seed, use_g, use_p, use_e) in PROSODY_CASES.items():
+        dec = ref.models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"],
+                                         cfg["dilation_rate"], cfg["n_blocks"], cfg["n_layers"], p_dropout=0.0,
+                                         n_split=cfg["n_split"], n_sqz=cfg["n_sqz"], gin_channels=cfg["gin_channels"])
+        sd = helpers.make_state_dict(cfg, sd_seed)
+        dec.load_state_dict(sd, strict=True)
+        dec.eval()
+        y, mask, lengths, g = flow_inputs(cfg, b, t, in_seed, use_g)
+        pitch, energy = prosody_inputs(b, t, in_seed, use_p, use_e)
+        y = y.clone().requires_grad_(True)
+        if pitch is not None:
+            pitch = pitch.clone().requires_grad_(True)
+        z, logdet = dec(y, mask, g=g, pitch=pitch, energy=energy, reverse=False)
+        loss = ref.commons.mle_loss(z, torch.zeros_like(z), torch.zeros_like(z), logdet, mask)
+        loss.backward()
+        sel = {"grad:" + k: p.grad.detach().numpy() for k, p in dec.named_parameters() if p.grad is not None}
+        with torch.no_grad():
+            y_rev, _ = dec(z.detach(), mask, g=g, pitch=pitch, energy=energy, reverse=True)
+            dec.store_inverse()
+            y_rev2, _ = dec(z.detach(), mask, g=g, pitch=pitch, energy=energy, reverse=True)
+        extra = {} if pitch is None else {"dpitch": pitch.grad.numpy()}
+        np.savez_compressed(os.path.join(HERE, name + ".npz"),
+                            sd_seed=sd_seed, b=b, t=t, in_seed=in_seed, use_g=use_g, use_pitch=use_p, use_energy=use_e,
+                            z=z.detach().numpy(), logdet=logdet.detach().numpy(), loss=loss.item(),
+                            dy=y.grad.numpy(), y_rev=y_rev.numpy(), y_rev_stored=y_rev2.numpy(), **extra, **sel)
+        print(name, float(loss), float((y_rev - y.detach()).abs().max()), len(sel))
+
+
 def gen_modules(ref):
     """Module-level fixtures: ActNorm (+DDI), InvConvNear, WN, CouplingBlock, gate, squeeze."""
     gen = torch.Generator().manual_seed(41)
@@ -161,6 +202,10 @@ if __name__ == "__main__":
     torch.manual_seed(0)
     ref = refimport.load()
     assert ref is not None, "needs /root/reference"
+    if "--prosody-only" in sys.argv:       # add the 3-WN fixtures without touching the older files
+        gen_flow_prosody(ref)
+        sys.exit(0)
+    gen_flow_prosody(ref)
     gen_mas()
     gen_modules(ref)
     gen_logp()

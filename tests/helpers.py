@@ -124,3 +124,11 @@ def flow_inputs(cfg, b, t, seed, use_g):
     mask = (torch.arange(t)[None, :] < lengths[:, None]).float().unsqueeze(1)
     g = torch.randn(b, cfg["gin_channels"], 1, generator=gen) if use_g else None
     return y * mask, mask, lengths, g
+
+
+def prosody_inputs(b, t, seed, use_pitch, use_energy):
+    """Pitch [b,1,t] / energy [b,t] tracks of the live fork's coupling blocks (2-D on purpose: attentions.py:137-141)."""
+    gen = torch.Generator().manual_seed(seed + 100)
+    pitch = torch.randn(b, 1, t, generator=gen) if use_pitch else None
+    energy = torch.randn(b, t, generator=gen) if use_energy else None
+    return pitch, energy

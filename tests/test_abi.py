@@ -53,8 +53,7 @@ def test_state_dict_keys_match_reference_names():
     import helpers
     from glowtts_b200 import models
     dec = models.FlowSpecDecoder(80, 192, 5, 1, 12, 4, p_dropout=0.05, n_split=4, n_sqz=2, gin_channels=256)
-    want = {k for k in helpers.decoder_param_shapes(dict(helpers.BASE_CFG, gin_channels=256))
-            if ".wn_pitch." not in k and ".wn_energy." not in k}
+    want = set(helpers.decoder_param_shapes(dict(helpers.BASE_CFG, gin_channels=256)))   # incl. wn_pitch / wn_energy
     got = dict(dec.state_dict())
     assert set(got) == want
     shapes = helpers.decoder_param_shapes(dict(helpers.BASE_CFG, gin_channels=256))

@@ -26,9 +26,7 @@ def _decoder(cfg, sd, precision="fp32"):
     dec = models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"], cfg["dilation_rate"],
                                  cfg["n_blocks"], cfg["n_layers"], p_dropout=0.0, n_split=cfg["n_split"],
                                  n_sqz=cfg["n_sqz"], gin_channels=cfg["gin_channels"], precision=precision)
-    res = dec.load_state_dict(sd, strict=False)
-    assert not res.missing_keys
-    assert all(".wn_pitch." in k or ".wn_energy." in k for k in res.unexpected_keys)
+    dec.load_state_dict(sd, strict=True)      # every reference key, incl. the fork's wn_pitch / wn_energy
     return dec.cuda()
 
 
@@ -72,6 +70,52 @@ def test_decoder_matches_reference_fixture(golden_dir, name):
     np.testing.assert_allclose(y_rev.cpu().numpy(), g["y_rev"], rtol=1e-4, atol=5e-5)
     dec.store_inverse()
     y_rev2, _ = dec(z.detach(), mask, g=cond, reverse=True)
+    np.testing.assert_allclose(y_rev2.cpu().numpy(), g["y_rev_stored"], rtol=1e-4, atol=5e-5)
+
+
+PROSODY = {
+    "flow_tiny_pe": dict(helpers.TINY_CFG, gin_channels=6),
+    "flow_tiny_p": helpers.TINY_CFG,
+}
+
+
+@pytest.mark.parametrize("name", list(PROSODY))
+def test_prosody_decoder_matches_reference_fixture(golden_dir, name):
+    """The live fork's 3-WN coupling blocks (wn -> wn_energy -> wn_pitch, attentions.py:155-160; modules.WNP
+    modules.py:272-362) against fixtures made by the reference modules: z, logdet, loss, every gradient
+    (incl. cond_layer1 and the pitch track itself), reverse before and after store_inverse."""
+    from glowtts_b200 import commons
+    cfg = PROSODY[name]
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    dec = _decoder(cfg, helpers.make_state_dict(cfg, int(g["sd_seed"])))
+    y, mask, _, cond = helpers.flow_inputs(cfg, int(g["b"]), int(g["t"]), int(g["in_seed"]), bool(g["use_g"]))
+    pitch, energy = helpers.prosody_inputs(int(g["b"]), int(g["t"]), int(g["in_seed"]), bool(g["use_pitch"]),
+                                           bool(g["use_energy"]))
+    y = y.cuda().requires_grad_(True)
+    mask = mask.cuda()
+    cond = cond.cuda() if cond is not None else None
+    pitch = pitch.cuda().requires_grad_(True)
+    energy = energy.cuda() if energy is not None else None
+    z, logdet = dec(y, mask, g=cond, pitch=pitch, energy=energy)
+    np.testing.assert_allclose(z.detach().cpu().numpy(), g["z"], **TOL)
+    np.testing.assert_allclose(logdet.detach().cpu().numpy(), g["logdet"], rtol=1e-4, atol=1e-3)
+    loss = commons.mle_loss(z, None, None, logdet, mask)
+    assert abs(loss.item() - float(g["loss"])) < 1e-4 * max(1.0, abs(float(g["loss"])))
+    loss.backward()
+    np.testing.assert_allclose(y.grad.cpu().numpy(), g["dy"], rtol=1e-3, atol=1e-6)
+    np.testing.assert_allclose(pitch.grad.cpu().numpy(), g["dpitch"], rtol=1e-3, atol=1e-6)
+    params = dict(dec.named_parameters())
+    keys = [k for k in g.files if k.startswith("grad:")]
+    assert any(".wn_pitch.cond_layer1." in k for k in keys)
+    for key in keys:
+        np.testing.assert_allclose(params[key[5:]].grad.cpu().numpy(), g[key], rtol=2e-3, atol=2e-6, err_msg=key)
+    with_grad = {"grad:" + k for k, p in params.items() if p.grad is not None}
+    assert with_grad == set(keys)          # an unconditioned WNP is the identity: its parameters get no gradient
+    y_rev, none = dec(z.detach(), mask, g=cond, pitch=pitch.detach(), energy=energy, reverse=True)
+    assert none is None
+    np.testing.assert_allclose(y_rev.cpu().numpy(), g["y_rev"], rtol=1e-4, atol=5e-5)
+    dec.store_inverse()
+    y_rev2, _ = dec(z.detach(), mask, g=cond, pitch=pitch.detach(), energy=energy, reverse=True)
     np.testing.assert_allclose(y_rev2.cpu().numpy(), g["y_rev_stored"], rtol=1e-4, atol=5e-5)
 
 
@@ -179,8 +223,7 @@ def test_standalone_coupling_block_and_wn_match_oracle():
     cfg = dict(helpers.TINY_CFG, n_blocks=1, gin_channels=4, kernel_size=3, dilation_rate=2, n_layers=3)
     sd = helpers.make_state_dict(cfg, 55)
     cb = attentions.CouplingBlock(16, 16, 3, 2, 3, gin_channels=4).cuda()
-    cb.load_state_dict({k[len("flows.2."):]: v for k, v in sd.items() if k.startswith("flows.2.")
-                        and ".wn_pitch." not in k and ".wn_energy." not in k})
+    cb.load_state_dict({k[len("flows.2."):]: v for k, v in sd.items() if k.startswith("flows.2.")})
     gen = torch.Generator().manual_seed(3)
     x = torch.randn(2, 16, 19, generator=gen)
     mask = oflow.sequence_mask(torch.tensor([19, 11]), 19).float().unsqueeze(1)
@@ -196,6 +239,9 @@ def test_standalone_coupling_block_and_wn_match_oracle():
     (z.pow(2).sum() + ld.sum()).backward()
     np.testing.assert_allclose(xc.grad.cpu().numpy(), xr.grad.numpy(), rtol=1e-3, atol=1e-5)
     for name, p in cb.named_parameters():
+        if ".wn_pitch." in name or ".wn_energy." in name or name.startswith(("wn_pitch.", "wn_energy.")):
+            assert p.grad is None       # identity without a pitch / energy track
+            continue
         np.testing.assert_allclose(p.grad.cpu().numpy(), sdr["flows.2." + name].grad.numpy(), rtol=2e-3, atol=2e-5,
                                    err_msg=name)
     with torch.no_grad():
@@ -297,7 +343,7 @@ def test_decoder_dropout_matches_oracle_given_the_mask(use_g):
         np.testing.assert_allclose(condc.grad.cpu().numpy(), condr.grad.numpy(), rtol=2e-3, atol=2e-5)
     n = 0
     for name, prm in dec.named_parameters():
-        if name in sdr and sdr[name].grad is not None:
+        if name in sdr and sdr[name].grad is not None and prm.grad is not None:
             np.testing.assert_allclose(prm.grad.cpu().numpy().reshape(-1), sdr[name].grad.numpy().reshape(-1), rtol=2e-3,
                                        atol=3e-5, err_msg=name)
             n += 1

@@ -198,7 +198,7 @@ def test_bf16_decoder_backward_tracks_fp32(name):
         z, ld = dec(yy, mask, g=gg)
         loss = commons.mle_loss(z, None, None, ld, mask)
         loss.backward()
-        d = {k: p.grad.clone() for k, p in dec.named_parameters()}
+        d = {k: p.grad.clone() for k, p in dec.named_parameters() if p.grad is not None}
         d["__dy"] = yy.grad.clone()
         if gg is not None:
             d["__dg"] = gg.grad.clone()

@@ -59,6 +59,40 @@ def test_decoder_matches_reference_fixture(golden_dir, name):
     np.testing.assert_allclose(y_rev.numpy(), g["y_rev_stored"], rtol=1e-4, atol=5e-5)
 
 
+PROSODY = {
+    "flow_tiny_pe": dict(helpers.TINY_CFG, gin_channels=6),
+    "flow_tiny_p": helpers.TINY_CFG,
+}
+
+
+@pytest.mark.parametrize("name", list(PROSODY))
+def test_prosody_decoder_matches_reference_fixture(golden_dir, name):
+    """3-WN coupling blocks of the live fork (wn -> wn_energy -> wn_pitch, attentions.py:155-160; modules.WNP)."""
+    cfg = PROSODY[name]
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    sd = {k: v.clone().requires_grad_(True) for k, v in helpers.make_state_dict(cfg, int(g["sd_seed"])).items()}
+    y, mask, _, cond = helpers.flow_inputs(cfg, int(g["b"]), int(g["t"]), int(g["in_seed"]), bool(g["use_g"]))
+    pitch, energy = helpers.prosody_inputs(int(g["b"]), int(g["t"]), int(g["in_seed"]), bool(g["use_pitch"]),
+                                           bool(g["use_energy"]))
+    y = y.clone().requires_grad_(True)
+    pitch = pitch.clone().requires_grad_(True)
+    z, logdet = oflow.decoder(sd, y, mask, g=cond, pitch=pitch, energy=energy, **_kw(cfg))
+    np.testing.assert_allclose(z.detach().numpy(), g["z"], **TOL)
+    np.testing.assert_allclose(logdet.detach().numpy(), g["logdet"], rtol=1e-4, atol=1e-3)
+    loss = oflow.mle_loss(z, torch.zeros_like(z), torch.zeros_like(z), logdet, mask)
+    loss.backward()
+    np.testing.assert_allclose(y.grad.numpy(), g["dy"], rtol=1e-3, atol=1e-6)
+    np.testing.assert_allclose(pitch.grad.numpy(), g["dpitch"], rtol=1e-3, atol=1e-6)
+    keys = [k for k in g.files if k.startswith("grad:")]
+    assert any(".wn_pitch.cond_layer1." in k for k in keys)
+    for key in keys:
+        np.testing.assert_allclose(sd[key[5:]].grad.numpy(), g[key], rtol=2e-3, atol=2e-6, err_msg=key)
+    with torch.no_grad():
+        y_rev, _ = oflow.decoder(sd, z.detach(), mask, g=cond, pitch=pitch, energy=energy, reverse=True, **_kw(cfg))
+    np.testing.assert_allclose(y_rev.numpy(), g["y_rev"], rtol=1e-4, atol=5e-5)
+    np.testing.assert_allclose(y_rev.numpy(), g["y_rev_stored"], rtol=1e-4, atol=5e-5)
+
+
 def test_modules_match_reference_fixture(golden_dir):
     g = np.load(os.path.join(golden_dir, "modules_small.npz"))
     x = torch.from_numpy(g["x"])
