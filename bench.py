@@ -456,24 +456,50 @@ def main():
             "mas_cells_per_step": cells_total, "step_tflops": step_flop * world / s_res / 1e12,
             "roofline": roof, "clocks": clk,
         }
-        out["mas"] = mas_alone(device)
-        out["inference"] = inference_alone(run)
-        del run
-        torch.cuda.empty_cache()
-        try:
-            out["mas_stress"] = mas_alone(device, steps=5, B=512, TX=400, TY=2000, n_buf=1, name="configs[4] on one GPU")
-        except Exception as e:                              # 6.6 GB of buffers: report, never hide the main numbers
-            out["mas_stress"] = {"error": repr(e)}
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1:
+            # single-GPU legs (configs[0], [2], [4]); under torchrun the ranks are replicas of these (no collective on the
+            # MAS / inference paths), so the scaling run keeps to the training step
+            out["mas"] = mas_alone(device)
+            out["inference"] = inference_alone(run)
+            del run
+            torch.cuda.empty_cache()
             try:
-                out["cpu_baseline"] = cpu_baseline()
-            except Exception as e:  # the oracle is a checker; its absence must not hide the GPU numbers
-                out["cpu_baseline"] = {"value": None, "error": repr(e)}
+                out["mas_stress"] = mas_alone(device, steps=5, B=512, TX=400, TY=2000, n_buf=1, name="configs[4] on one GPU")
+            except Exception as e:                              # 6.6 GB of buffers: report, never hide the main numbers
+                out["mas_stress"] = {"error": repr(e)}
+            if not args.no_cpu_baseline:
+                try:
+                    out["cpu_baseline"] = cpu_baseline()
+                except Exception as e:  # the oracle is a checker; its absence must not hide the GPU numbers
+                    out["cpu_baseline"] = {"value": None, "error": repr(e)}
         print(json.dumps(out))
+    sys.stdout.flush()
+    sys.stderr.flush()
     if world > 1:
-        import torch.distributed as dist
-        dist.barrier()
-        dist.destroy_process_group()
+        # Every collective of the run is done.  Tearing NCCL down while the captured step graph (which holds the
+        # all-reduce) is alive blocked at N=2 on B200, so: rendezvous once through the c10d store (no NCCL), then leave
+        # without destroy_process_group.
+        torch.cuda.synchronize()
+        try:
+            import datetime
+            import torch.distributed as dist
+            store = dist.distributed_c10d._get_default_store()
+            store.add("bench_done", 1)
+            if rank == 0:
+                deadline = time.time() + 60
+                while store.add("bench_done", 0) < world and time.time() < deadline:
+                    time.sleep(0.05)
+            else:
+                store.wait(["bench_rank0_out"], datetime.timedelta(seconds=60))
+        except Exception:
+            pass
+        try:
+            if rank == 0:
+                store.set("bench_rank0_out", "1")
+                time.sleep(0.2)
+        except Exception:
+            pass
+        os._exit(0)
 
 
 if __name__ == "__main__":

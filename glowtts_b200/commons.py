@@ -28,7 +28,7 @@ def squeeze(x, x_mask=None, n_sqz=2):
     out, m = ops.squeeze_op(x, _mask2d(x_mask), n_sqz)
     if x_mask is None:
         m = torch.ones_like(m)
-    return out, m.unsqueeze(1)
+    return out, m.detach().unsqueeze(1)      # masks carry no gradient
 
 
 def unsqueeze(x, x_mask=None, n_sqz=2):
@@ -36,7 +36,7 @@ def unsqueeze(x, x_mask=None, n_sqz=2):
     out, m = ops.unsqueeze_op(x, _mask2d(x_mask), n_sqz)
     if x_mask is None:
         m = torch.ones_like(m)
-    return out, m.unsqueeze(1)
+    return out, m.detach().unsqueeze(1)      # masks carry no gradient
 
 
 def mle_loss(z, m, logs, logdet, mask):

@@ -14,7 +14,7 @@ from . import ops
 
 
 def _mask2d(x_mask):
-    return None if x_mask is None else x_mask.reshape(x_mask.shape[0], x_mask.shape[-1]).to(torch.float32)
+    return None if x_mask is None else x_mask.detach().reshape(x_mask.shape[0], x_mask.shape[-1]).to(torch.float32)
 
 
 def _x_len(x, m2):

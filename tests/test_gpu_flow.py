@@ -111,11 +111,13 @@ def test_prosody_decoder_matches_reference_fixture(golden_dir, name):
         np.testing.assert_allclose(params[key[5:]].grad.cpu().numpy(), g[key], rtol=2e-3, atol=2e-6, err_msg=key)
     with_grad = {"grad:" + k for k, p in params.items() if p.grad is not None}
     assert with_grad == set(keys)          # an unconditioned WNP is the identity: its parameters get no gradient
-    y_rev, none = dec(z.detach(), mask, g=cond, pitch=pitch.detach(), energy=energy, reverse=True)
+    with torch.no_grad():
+        y_rev, none = dec(z.detach(), mask, g=cond, pitch=pitch.detach(), energy=energy, reverse=True)
     assert none is None
     np.testing.assert_allclose(y_rev.cpu().numpy(), g["y_rev"], rtol=1e-4, atol=5e-5)
     dec.store_inverse()
-    y_rev2, _ = dec(z.detach(), mask, g=cond, pitch=pitch.detach(), energy=energy, reverse=True)
+    with torch.no_grad():
+        y_rev2, _ = dec(z.detach(), mask, g=cond, pitch=pitch.detach(), energy=energy, reverse=True)
     np.testing.assert_allclose(y_rev2.cpu().numpy(), g["y_rev_stored"], rtol=1e-4, atol=5e-5)
 
 
