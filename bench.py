@@ -377,6 +377,11 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE line, the JSON: anything a library writes to fd 1 (NCCL prints its version there)
+    # goes to stderr instead
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
     torch.cuda.set_device(local)
@@ -472,7 +477,7 @@ def main():
                     out["cpu_baseline"] = cpu_baseline()
                 except Exception as e:  # the oracle is a checker; its absence must not hide the GPU numbers
                     out["cpu_baseline"] = {"value": None, "error": repr(e)}
-        print(json.dumps(out))
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
     sys.stdout.flush()
     sys.stderr.flush()
     if world > 1:
