@@ -139,6 +139,17 @@ int gtk_mas_forward(const float* value, const int32_t* t_xs, const int32_t* t_ys
     return mas::forward(value, t_xs, t_ys, path, dur_out, idx_out, B, T_x, T_y, workspace, workspace_bytes, force_generic, ST);
 }
 
+int gtk_mas_fused_supported(int D, int T_x, int T_y, int has_x_logs) { return mas::fused_supported(D, T_x, T_y, has_x_logs); }
+int gtk_mas_fused_logp(const float* z, const float* x_m, const float* x_logs, const int32_t* t_xs, const int32_t* t_ys,
+                       float* path, int32_t* dur_out, int32_t* idx_out, float* logp_out, int B, int D, int T_x, int T_y,
+                       void* stream) {
+    if (x_logs) {
+        set_error("mas_fused_logp: x_logs != NULL (not a mean_only model) is not fused; use gtk_logp + gtk_mas_forward");
+        return GTK_ERR_UNSUPPORTED;
+    }
+    return mas::fused_forward(z, x_m, t_xs, t_ys, path, dur_out, idx_out, logp_out, B, D, T_x, T_y, ST);
+}
+
 int gtk_logp(const float* x_m, const float* x_logs, const float* z, float* logp, int B, int D, int T_x, int T_y, void* stream) {
     return logp::forward(x_m, x_logs, z, logp, B, D, T_x, T_y, ST);
 }

@@ -83,6 +83,24 @@ __device__ __forceinline__ void dp_tile(const float* __restrict__ tile, float (&
     }
 }
 
+// Ones of the path, durations and per-frame token indices from the token start frames ys[] (all threads of the CTA).
+__device__ __forceinline__ void emit_path(const Params& p, float* __restrict__ pplane, const int* ys, bool valid, int t_x, int t_y,
+                                          int b, int tid, int n_threads) {
+    for (int x = tid; x < p.T_x; x += n_threads) {
+        int start = 0, end = 0;
+        if (valid && x < t_x) {
+            start = ys[x];
+            end = (x + 1 < t_x) ? ys[x + 1] : t_y;
+            for (int y = start; y < end; ++y) pplane[(size_t)x * p.T_y + y] = 1.0f;
+            if (p.idx_out)
+                for (int y = start; y < end; ++y) p.idx_out[(size_t)b * p.T_y + y] = x;
+        }
+        if (p.dur_out) p.dur_out[(size_t)b * p.T_x + x] = end - start;
+    }
+    if (p.idx_out)
+        for (int y = (valid ? t_y : 0) + tid; y < p.T_y; y += n_threads) p.idx_out[(size_t)b * p.T_y + y] = -1;
+}
+
 template <int XPT>
 __global__ void __launch_bounds__(NT, 1) mas_kernel(const Params p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -239,20 +257,7 @@ __global__ void __launch_bounds__(NT, 1) mas_kernel(const Params p) {
     }
     __syncthreads();
 
-    // ---------------------------------------------------------------- emit ones / durations / indices
-    for (int x = tid; x < p.T_x; x += NT) {
-        int start = 0, end = 0;
-        if (valid && x < t_x) {
-            start = ys[x];
-            end = (x + 1 < t_x) ? ys[x + 1] : t_y;
-            for (int y = start; y < end; ++y) pplane[(size_t)x * p.T_y + y] = 1.0f;
-            if (p.idx_out)
-                for (int y = start; y < end; ++y) p.idx_out[(size_t)b * p.T_y + y] = x;
-        }
-        if (p.dur_out) p.dur_out[(size_t)b * p.T_x + x] = end - start;
-    }
-    if (p.idx_out)
-        for (int y = (valid ? t_y : 0) + tid; y < p.T_y; y += NT) p.idx_out[(size_t)b * p.T_y + y] = -1;
+    emit_path(p, pplane, ys, valid, t_x, t_y, b, tid, NT);
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -370,6 +375,148 @@ __device__ __forceinline__ void fast_wait(uint64_t* bar, uint32_t parity) {
     if (!mbar_test_wait(bar, parity)) mbar_wait(bar, parity);
 }
 
+// One DP warp of the wavefront (band w = text rows [w * 32 * XPT, (w + 1) * 32 * XPT)) over all tiles of the utterance:
+// waits for its value tiles on ctl->full[w][*], releases them on ctl->empty[w][*], trades the band-boundary row with its
+// neighbours through the mailboxes and leaves the decision words in bitsT.  Returns the cycles warp 0 waited for tiles.
+template <int XPT>
+__device__ __forceinline__ long long wave_dp_warp(WaveCtl* ctl, const float* tiles, size_t stage_floats, uint32_t* bitsT,
+                                                  int ROWW, int RB, int S, int n_tiles, int n_act, int w, int lane) {
+    constexpr int BAND = 32 * XPT;
+    if (w == 0 && lane == 0) mas_stamp(0);
+    long long waited = 0;
+    if (w < n_act) {
+        const int r0 = w * BAND;                 // first text row of the band
+        const int x0 = r0 + lane * XPT;
+        const bool send = (w + 1 < n_act);
+        float q[XPT];
+        uint32_t bits[XPT];
+        int roff[XPT];
+#pragma unroll
+        for (int k = 0; k < XPT; ++k) {
+            q[k] = 0.0f;
+            roff[k] = min(x0 + k, RB * TBOX - 1) * TP * 4;     // rows past the stage are never consumed: clamp the read
+        }
+        float carry = 0.0f;                      // row r0 - 1 at the last frame of the previous tile
+        for (int it = 0; it < n_tiles; ++it) {
+            const int s = it % S, use = it / S, y0 = it * YT;
+            const long long w0 = clock64();
+            fast_wait(&ctl->full[w][s], use & 1);
+            const long long w1 = clock64();
+            if (w == 0 && it > 0) waited += w1 - w0;
+            if (w == 0 && it == 0 && lane == 0) mas_stamp(1);
+            float bv[YT];
+            if (w > 0) {
+                fast_wait(&ctl->box_full[w - 1][it % NBOX], (it / NBOX) & 1);
+                const uint32_t bx = smem_u32(&ctl->box[w - 1][it % NBOX][0]);
+                float4 r[YT / 4];
+#pragma unroll
+                for (int j = 0; j < YT / 4; ++j) r[j] = lds128(bx + 16 * j);
+                bv[0] = carry;
+#pragma unroll
+                for (int j = 0; j < YT / 4; ++j) {
+                    if (4 * j + 1 < YT) bv[4 * j + 1] = r[j].x;
+                    if (4 * j + 2 < YT) bv[4 * j + 2] = r[j].y;
+                    if (4 * j + 3 < YT) bv[4 * j + 3] = r[j].z;
+                    if (4 * j + 4 < YT) bv[4 * j + 4] = r[j].w;
+                }
+                carry = r[YT / 4 - 1].w;
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&ctl->box_empty[w - 1][it % NBOX]);
+            }
+            if (send && it >= NBOX) fast_wait(&ctl->box_empty[w][it % NBOX], (it / NBOX - 1) & 1);
+            const long long w2 = clock64();
+            const uint32_t tile = smem_u32(tiles + (size_t)s * stage_floats);
+            const uint32_t bo = smem_u32(&ctl->box[w][it % NBOX][0]);
+#pragma unroll
+            for (int k = 0; k < XPT; ++k) bits[k] = 0u;
+            const bool diag = (y0 < r0 + BAND) && (y0 + YT > r0);
+            if (w == 0) {
+                if (diag) { if (send) dp_tile4<XPT, true, true, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
+                            else      dp_tile4<XPT, true, true, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
+                else      { if (send) dp_tile4<XPT, false, true, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
+                            else      dp_tile4<XPT, false, true, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
+            } else {
+                if (diag) { if (send) dp_tile4<XPT, true, false, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
+                            else      dp_tile4<XPT, true, false, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
+                else      { if (send) dp_tile4<XPT, false, false, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
+                            else      dp_tile4<XPT, false, false, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
+            }
+            const long long w3 = clock64();
+#pragma unroll
+            for (int k = 0; k < XPT; ++k)
+                if (x0 + k < ROWW) bitsT[(size_t)it * ROWW + x0 + k] = bits[k];      // MSB-first: frame f at bit 31 - f
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&ctl->empty[w][s]);
+                if (send) mbar_arrive(&ctl->box_full[w][it % NBOX]);
+            }
+#ifdef GTK_MAS_EXP_TILETIME
+            if (it == 10 && lane == 0 && blockIdx.x == 0 && w < 4) {
+                g_mas_trace[900 * 6 + w * 6 + 0] = (unsigned long long)(w1 - w0);
+                g_mas_trace[900 * 6 + w * 6 + 1] = (unsigned long long)(w2 - w1);
+                g_mas_trace[900 * 6 + w * 6 + 2] = (unsigned long long)(w3 - w2);
+                g_mas_trace[900 * 6 + w * 6 + 3] = (unsigned long long)(clock64() - w3);
+                g_mas_trace[900 * 6 + w * 6 + 4] = (unsigned long long)w0;
+            }
+#endif
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&ctl->dp_done);
+    }
+    return waited;
+}
+
+// ------------------------------------------------------------ backtrack (run-skipping, one thread)
+// Token `index` starts at the highest set bit of its row at or below y.  The loop-carried chain is mask -> clz ->
+// select: the words the NEXT row can need (same 32-frame block or the one before) are loaded one step ahead.
+__device__ __forceinline__ void wave_backtrack(WaveCtl* ctl, const uint32_t* bitsT, int ROWW, int* ys, bool valid, int t_x,
+                                               int t_y, long long waited) {
+    if (valid) fast_wait(&ctl->dp_done, 0);
+    mas_stamp(2);
+    if (blockIdx.x < MAS_TRACE_CTAS) g_mas_wait[blockIdx.x] = waited;
+    if (valid) {
+        // Decision words are MSB-first (frame f of the block at bit 31 - f), so "the last frame <= y whose bit is set"
+        // is the LOWEST set bit of (word & M), M = the bit positions still allowed.  Per token the loop-carried
+        // chain is 4 ALU operations (and, isolate lowest bit b, M = bits above b); the frame number (clz b) is off
+        // the chain.  The words of the next BT_ROWS rows of the current 32-frame block are loaded together; a token
+        // that starts in an earlier block (m == 0) ends the batch and moves one block down with M = all ones.
+        constexpr int BT_ROWS = 8;
+        int index = t_x - 1;
+        int yb = (t_y - 1) >> 5;
+        uint32_t M = 0xffffffffu << (31 - ((t_y - 1) & 31));
+        while (index > 0 && yb >= 0) {
+            const uint32_t* base = bitsT + (size_t)yb * ROWW + index;      // word of (row index, block yb)
+            uint32_t W[BT_ROWS];
+#pragma unroll
+            for (int j = 0; j < BT_ROWS; ++j) W[j] = base[-min(j, index)];
+            const int f0 = yb << 5;
+            int done = 0;
+            bool live = true, cross = false;
+#pragma unroll
+            for (int j = 0; j < BT_ROWS; ++j) {
+                const bool act = live && (index - j >= 1);
+                const uint32_t m = W[j] & M;
+                const bool hit = act && (m != 0u);
+                const uint32_t bb = m & (0u - m);
+                if (hit) {
+                    ys[index - j] = f0 + __clz(bb);                        // first frame of token index - j
+                    M = ~(bb | (bb - 1u));
+                    ++done;
+                }
+                cross = cross || (act && !hit);
+                live = hit;
+            }
+            index -= done;
+            if (cross) { --yb; M = 0xffffffffu; }
+        }
+        ys[0] = 0;
+        // y < 0 with index > 0 cannot happen for valid inputs (diagonal bits force the move);
+        // if it did, make the remaining rows empty rather than reading garbage.
+        for (int x = 1; x <= index; ++x) ys[x] = 0;
+    }
+    mas_stamp(3);
+}
+
 template <int XPT>
 __global__ void __launch_bounds__(NT, 1) mas_wave_kernel(const __grid_constant__ CUtensorMap tmV, const Params p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -415,136 +562,8 @@ __global__ void __launch_bounds__(NT, 1) mas_wave_kernel(const __grid_constant__
     if (warp < NDP) {
         // ------------------------------------------------------------ DP warps
         const int w = warp;
-        if (w == 0 && lane == 0) mas_stamp(0);
-        long long waited = 0;
-        if (w < n_act) {
-            const int r0 = w * BAND;                 // first text row of the band
-            const int x0 = r0 + lane * XPT;
-            const bool send = (w + 1 < n_act);
-            float q[XPT];
-            uint32_t bits[XPT];
-            int roff[XPT];
-#pragma unroll
-            for (int k = 0; k < XPT; ++k) {
-                q[k] = 0.0f;
-                roff[k] = min(x0 + k, RB * TBOX - 1) * TP * 4;     // rows past the stage are never consumed: clamp the read
-            }
-            float carry = 0.0f;                      // row r0 - 1 at the last frame of the previous tile
-            for (int it = 0; it < n_tiles; ++it) {
-                const int s = it % S, use = it / S, y0 = it * YT;
-                const long long w0 = clock64();
-                fast_wait(&ctl->full[w][s], use & 1);
-                const long long w1 = clock64();
-                if (w == 0 && it > 0) waited += w1 - w0;
-                if (w == 0 && it == 0 && lane == 0) mas_stamp(1);
-                float bv[YT];
-                if (w > 0) {
-                    fast_wait(&ctl->box_full[w - 1][it % NBOX], (it / NBOX) & 1);
-                    const uint32_t bx = smem_u32(&ctl->box[w - 1][it % NBOX][0]);
-                    float4 r[YT / 4];
-#pragma unroll
-                    for (int j = 0; j < YT / 4; ++j) r[j] = lds128(bx + 16 * j);
-                    bv[0] = carry;
-#pragma unroll
-                    for (int j = 0; j < YT / 4; ++j) {
-                        if (4 * j + 1 < YT) bv[4 * j + 1] = r[j].x;
-                        if (4 * j + 2 < YT) bv[4 * j + 2] = r[j].y;
-                        if (4 * j + 3 < YT) bv[4 * j + 3] = r[j].z;
-                        if (4 * j + 4 < YT) bv[4 * j + 4] = r[j].w;
-                    }
-                    carry = r[YT / 4 - 1].w;
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&ctl->box_empty[w - 1][it % NBOX]);
-                }
-                if (send && it >= NBOX) fast_wait(&ctl->box_empty[w][it % NBOX], (it / NBOX - 1) & 1);
-                const long long w2 = clock64();
-                const uint32_t tile = smem_u32(tiles + (size_t)s * stage_floats);
-                const uint32_t bo = smem_u32(&ctl->box[w][it % NBOX][0]);
-#pragma unroll
-                for (int k = 0; k < XPT; ++k) bits[k] = 0u;
-                const bool diag = (y0 < r0 + BAND) && (y0 + YT > r0);
-                if (w == 0) {
-                    if (diag) { if (send) dp_tile4<XPT, true, true, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
-                                else      dp_tile4<XPT, true, true, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
-                    else      { if (send) dp_tile4<XPT, false, true, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
-                                else      dp_tile4<XPT, false, true, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
-                } else {
-                    if (diag) { if (send) dp_tile4<XPT, true, false, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
-                                else      dp_tile4<XPT, true, false, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
-                    else      { if (send) dp_tile4<XPT, false, false, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
-                                else      dp_tile4<XPT, false, false, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
-                }
-                const long long w3 = clock64();
-#pragma unroll
-                for (int k = 0; k < XPT; ++k)
-                    if (x0 + k < ROWW) bitsT[(size_t)it * ROWW + x0 + k] = bits[k];      // MSB-first: frame f at bit 31 - f
-                __syncwarp();
-                if (lane == 0) {
-                    mbar_arrive(&ctl->empty[w][s]);
-                    if (send) mbar_arrive(&ctl->box_full[w][it % NBOX]);
-                }
-#ifdef GTK_MAS_EXP_TILETIME
-                if (it == 10 && lane == 0 && blockIdx.x == 0 && w < 4) {
-                    g_mas_trace[900 * 6 + w * 6 + 0] = (unsigned long long)(w1 - w0);
-                    g_mas_trace[900 * 6 + w * 6 + 1] = (unsigned long long)(w2 - w1);
-                    g_mas_trace[900 * 6 + w * 6 + 2] = (unsigned long long)(w3 - w2);
-                    g_mas_trace[900 * 6 + w * 6 + 3] = (unsigned long long)(clock64() - w3);
-                    g_mas_trace[900 * 6 + w * 6 + 4] = (unsigned long long)w0;
-                }
-#endif
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&ctl->dp_done);
-        }
-        // ------------------------------------------------------------ backtrack (run-skipping, one thread)
-        // Token `index` starts at the highest set bit of its row at or below y.  The loop-carried chain is mask -> clz ->
-        // select: the words the NEXT row can need (same 32-frame block or the one before) are loaded one step ahead.
-        if (w == 0 && lane == 0) {
-            if (valid) fast_wait(&ctl->dp_done, 0);
-            mas_stamp(2);
-            if (blockIdx.x < MAS_TRACE_CTAS) g_mas_wait[blockIdx.x] = waited;
-            if (valid) {
-                // Decision words are MSB-first (frame f of the block at bit 31 - f), so "the last frame <= y whose bit is set"
-                // is the LOWEST set bit of (word & M), M = the bit positions still allowed.  Per token the loop-carried
-                // chain is 4 ALU operations (and, isolate lowest bit b, M = bits above b); the frame number (clz b) is off
-                // the chain.  The words of the next BT_ROWS rows of the current 32-frame block are loaded together; a token
-                // that starts in an earlier block (m == 0) ends the batch and moves one block down with M = all ones.
-                constexpr int BT_ROWS = 8;
-                int index = t_x - 1;
-                int yb = (t_y - 1) >> 5;
-                uint32_t M = 0xffffffffu << (31 - ((t_y - 1) & 31));
-                while (index > 0 && yb >= 0) {
-                    const uint32_t* base = bitsT + (size_t)yb * ROWW + index;      // word of (row index, block yb)
-                    uint32_t W[BT_ROWS];
-#pragma unroll
-                    for (int j = 0; j < BT_ROWS; ++j) W[j] = base[-min(j, index)];
-                    const int f0 = yb << 5;
-                    int done = 0;
-                    bool live = true, cross = false;
-#pragma unroll
-                    for (int j = 0; j < BT_ROWS; ++j) {
-                        const bool act = live && (index - j >= 1);
-                        const uint32_t m = W[j] & M;
-                        const bool hit = act && (m != 0u);
-                        const uint32_t bb = m & (0u - m);
-                        if (hit) {
-                            ys[index - j] = f0 + __clz(bb);                        // first frame of token index - j
-                            M = ~(bb | (bb - 1u));
-                            ++done;
-                        }
-                        cross = cross || (act && !hit);
-                        live = hit;
-                    }
-                    index -= done;
-                    if (cross) { --yb; M = 0xffffffffu; }
-                }
-                ys[0] = 0;
-                // y < 0 with index > 0 cannot happen for valid inputs (diagonal bits force the move);
-                // if it did, make the remaining rows empty rather than reading garbage.
-                for (int x = 1; x <= index; ++x) ys[x] = 0;
-            }
-            mas_stamp(3);
-        }
+        const long long waited = wave_dp_warp<XPT>(ctl, tiles, stage_floats, bitsT, ROWW, RB, S, n_tiles, n_act, w, lane);
+        if (w == 0 && lane == 0) wave_backtrack(ctl, bitsT, ROWW, ys, valid, t_x, t_y, waited);
     } else if (warp == NDP) {
         // ------------------------------------------------------------ TMA producers: lane w feeds DP warp w
         if (lane < n_act) {
@@ -578,20 +597,275 @@ __global__ void __launch_bounds__(NT, 1) mas_wave_kernel(const __grid_constant__
     __syncthreads();
     if (tid == 0) mas_stamp(4);
 
-    // ---------------------------------------------------------------- emit ones / durations / indices
-    for (int x = tid; x < p.T_x; x += NT) {
-        int start = 0, end = 0;
-        if (valid && x < t_x) {
-            start = ys[x];
-            end = (x + 1 < t_x) ? ys[x + 1] : t_y;
-            for (int y = start; y < end; ++y) pplane[(size_t)x * p.T_y + y] = 1.0f;
-            if (p.idx_out)
-                for (int y = start; y < end; ++y) p.idx_out[(size_t)b * p.T_y + y] = x;
+    emit_path(p, pplane, ys, valid, t_x, t_y, b, tid, NT);
+    if (tid == 0) mas_stamp(5);
+}
+
+// -------------------------------------------------------------------------------------------------
+// Fused logp + MAS (mean_only models, D = 80 mel channels, T_x <= 256): the value tiles the DP warps consume are
+// never read from HBM -- they are COMPUTED in the CTA, one 32-frame tile ahead of the DP, from z [80, T_y] and
+// x_m [80, T_x] (models.py:1076-1082 with x_logs == 0):
+//     value[x, y] = c[x] + sum_d x_m[d, x] z[d, y],      c[x] = -80 * 0.5 log 2pi - 0.5 sum_d x_m[d, x]^2.
+// The fourth term of the reference, -0.5 sum_d z[d, y]^2, is the same for every text row of frame y: it shifts the
+// whole DP column Q[., y] by one constant and cannot change any decision Q[x, y-1] < Q[x-1, y-1], so the DP runs
+// without it (and with smaller magnitudes); it is added back only where logp itself is written (logp_out).
+//   * 4 DP warps: unchanged (wave_dp_warp), fed through the same per-band rings of [row][36]-pitch tiles;
+//   * 8 MMA warps, two per DP band: a warp keeps its 16 * XPT rows of x_m as mma.sync A fragments in REGISTERS for
+//     the whole utterance (80 fp32 at XPT = 2) and per tile runs the [16 XPT x 80] x [80 x 32] product on the
+//     tensor cores as 3xTF32 (a_lo b_hi + a_hi b_lo + a_hi b_hi, hi = tf32(v), lo = tf32(v - hi): fp32-level
+//     accuracy from the tf32 pipe), adds c[x] and stores the D fragments into its band's tile stage;
+//   * z tiles (80 x 40-float rows: pitch 40 makes the B-fragment reads conflict-free) arrive by TMA into a
+//     4-deep ring shared by all bands (issued by one lane of MMA warp 0, released by all active MMA warps);
+//   * the MMA warps also zero-fill the output plane between tiles.
+// HBM traffic: 4 B/cell (the path) + the z / x_m operands; no [B,T_x,T_y] value tensor exists.
+constexpr int FD = 80;                   // mel channels = contraction length
+constexpr int ZP = 40;                   // z tile row pitch in floats (TMA box of 40 frames, 32 used)
+constexpr int FZ_STAGES = 4;
+constexpr int FZ_BYTES = FD * ZP * 4;
+constexpr int F_NMMA = 2 * NDP;
+constexpr int F_NT = 32 * (NDP + F_NMMA);     // 384 threads: 170 registers per thread
+constexpr int F_MAX_XPT = 2;             // T_x <= 256: the A fragments of a band half must fit the register file
+
+struct FusedCtl {
+    uint64_t zfull[FZ_STAGES], zempty[FZ_STAGES];
+};
+
+__device__ __forceinline__ uint32_t to_tf32(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return r;
+}
+// volatile: keeps the split of the (loop-invariant) A fragments inside the tile loop -- hoisted, hi and lo of every
+// fragment would have to live in registers (2 x 80) and spill
+__device__ __forceinline__ uint32_t to_tf32_pinned(float v) {
+    uint32_t r;
+    asm volatile("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return r;
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ float lds32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+
+template <int XPT>
+__global__ void __launch_bounds__(F_NT, 1) mas_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const Params p,
+                                                            const float* __restrict__ x_m, float* __restrict__ logp_out) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int BAND = 32 * XPT;                   // text rows per DP warp
+    constexpr int MB = XPT;                          // 16-row MMA blocks per MMA warp (half a band)
+    const int S = p.n_stages;
+    const int NYB = (p.T_y + YT - 1) / YT;
+    const int ROWW = (p.T_x + 3) & ~3;
+    const int RB = (p.T_x + TBOX - 1) / TBOX;
+    const size_t stage_floats = (size_t)RB * TBOX * TP;
+
+    WaveCtl* ctl = reinterpret_cast<WaveCtl*>(smem_raw);
+    FusedCtl* fz = reinterpret_cast<FusedCtl*>(smem_raw + sizeof(WaveCtl));
+    int* ys = reinterpret_cast<int*>(smem_raw + sizeof(WaveCtl) + sizeof(FusedCtl));
+    uint32_t* bitsT = reinterpret_cast<uint32_t*>(ys + ROWW + 4);
+    float* tiles = reinterpret_cast<float*>(
+        (reinterpret_cast<uintptr_t>(bitsT + (size_t)NYB * ROWW) + 127) & ~static_cast<uintptr_t>(127));
+    float* ztiles = tiles + (size_t)S * stage_floats;                  // stage_floats * 4 is a multiple of 128
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.x;
+    int t_x = min(max(p.t_xs[b], 0), p.T_x);
+    int t_y = min(max(p.t_ys[b], 0), p.T_y);
+    const bool valid = (t_x >= 1) && (t_y >= t_x);
+    const int n_tiles = valid ? (t_y + YT - 1) / YT : 0;
+    const int n_iter = max(n_tiles, 1);
+    const int n_act = valid ? (t_x + BAND - 1) / BAND : 0;
+    const size_t plane_elems = (size_t)p.T_x * p.T_y;
+    float* __restrict__ pplane = p.path + (size_t)b * plane_elems;
+
+    if (tid == 0) {
+        for (int w = 0; w < NDP; ++w) {
+            for (int s = 0; s < TMA_MAX_STAGES; ++s) {
+                mbar_init(&ctl->full[w][s], F_NMMA / NDP);     // the two MMA warps of the band
+                mbar_init(&ctl->empty[w][s], 1);
+            }
+            for (int s = 0; s < NBOX; ++s) {
+                mbar_init(&ctl->box_full[w][s], 1);
+                mbar_init(&ctl->box_empty[w][s], 1);
+            }
         }
-        if (p.dur_out) p.dur_out[(size_t)b * p.T_x + x] = end - start;
+        mbar_init(&ctl->dp_done, max(n_act, 1));
+        for (int s = 0; s < FZ_STAGES; ++s) {
+            mbar_init(&fz->zfull[s], 1);
+            mbar_init(&fz->zempty[s], max(2 * n_act, 1));
+        }
+        mbar_fence_init();
     }
-    if (p.idx_out)
-        for (int y = (valid ? t_y : 0) + tid; y < p.T_y; y += NT) p.idx_out[(size_t)b * p.T_y + y] = -1;
+    __syncthreads();
+
+    if (warp < NDP) {
+        // ------------------------------------------------------------ DP warps (same code as the TMA wavefront kernel)
+        const int w = warp;
+        const long long waited = wave_dp_warp<XPT>(ctl, tiles, stage_floats, bitsT, ROWW, RB, S, n_tiles, n_act, w, lane);
+        if (w == 0 && lane == 0) wave_backtrack(ctl, bitsT, ROWW, ys, valid, t_x, t_y, waited);
+    } else {
+        // ------------------------------------------------------------ MMA warps: value tiles from x_m and z
+        const int mw = warp - NDP, w = mw >> 1, h = mw & 1;
+        const int g = lane >> 2, t = lane & 3;            // mma.sync fragment coordinates
+        const bool act = w < n_act;
+        const int rbase = w * BAND + h * (16 * MB);       // first text row of this warp
+        const int ht = tid - 32 * NDP;
+        constexpr int HT = 32 * F_NMMA;
+        const uintptr_t addr = reinterpret_cast<uintptr_t>(pplane);
+        size_t head = ((16 - (addr & 15)) & 15) / 4;
+        if (head > plane_elems) head = plane_elems;
+        const size_t nvec = (plane_elems - head) / 4;
+        const size_t tail0 = head + nvec * 4;
+        float4* pv = reinterpret_cast<float4*>(pplane + head);
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+
+        // A fragments (m16n8k8, row-major): a0 (g, t), a1 (g + 8, t), a2 (g, t + 4), a3 (g + 8, t + 4) of each 16 x 8 block;
+        // rows = text positions, columns = mel channels.  Rows at or beyond t_x are zero (never consumed by a valid row).
+        float a[MB][FD / 8][4];
+        float crow[MB][2];
+#pragma unroll
+        for (int mb = 0; mb < MB; ++mb) {
+            const int r_lo = rbase + 16 * mb + g, r_hi = r_lo + 8;
+            const bool ok_lo = act && r_lo < t_x, ok_hi = act && r_hi < t_x;
+            const float* xb = x_m + (size_t)b * FD * p.T_x;
+            float s_lo = 0.f, s_hi = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < FD / 8; ++ks) {
+                const size_t d0 = (size_t)(8 * ks + t) * p.T_x, d1 = d0 + (size_t)4 * p.T_x;
+                const float a0 = ok_lo ? __ldg(xb + d0 + r_lo) : 0.f;
+                const float a1 = ok_hi ? __ldg(xb + d0 + r_hi) : 0.f;
+                const float a2 = ok_lo ? __ldg(xb + d1 + r_lo) : 0.f;
+                const float a3 = ok_hi ? __ldg(xb + d1 + r_hi) : 0.f;
+                a[mb][ks][0] = a0; a[mb][ks][1] = a1; a[mb][ks][2] = a2; a[mb][ks][3] = a3;
+                s_lo = fmaf(a0, a0, s_lo); s_lo = fmaf(a2, a2, s_lo);
+                s_hi = fmaf(a1, a1, s_hi); s_hi = fmaf(a3, a3, s_hi);
+            }
+            s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 1); s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 2);
+            s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 1); s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 2);
+            crow[mb][0] = -0.5f * s_lo - (float)FD * 0.918938533204672742f;      // logp1 + logp4 (models.py:1078,1081)
+            crow[mb][1] = -0.5f * s_hi - (float)FD * 0.918938533204672742f;
+        }
+
+        int z_next = 0;                                   // (MMA warp 0, lane 0) next z tile to request
+        for (int it = 0; it < n_iter; ++it) {
+            if (act && it < n_tiles) {
+                if (mw == 0 && lane == 0) {
+                    // keep up to FZ_STAGES z tiles requested; block only for the tile needed now
+                    while (z_next < n_tiles && z_next < it + FZ_STAGES) {
+                        const int zs = z_next % FZ_STAGES, zu = z_next / FZ_STAGES;
+                        if (zu >= 1) {
+                            if (z_next > it) { if (!mbar_test_wait(&fz->zempty[zs], (zu - 1) & 1)) break; }
+                            else mbar_wait(&fz->zempty[zs], (zu - 1) & 1);
+                        }
+                        mbar_arrive_expect_tx(&fz->zfull[zs], (uint32_t)FZ_BYTES);
+                        tc::tma_load_3d(ztiles + (size_t)zs * FD * ZP, &tmZ, &fz->zfull[zs], z_next * YT, 0, b);
+                        ++z_next;
+                    }
+                }
+                __syncwarp();
+                const int s = it % S, use = it / S, zs = it % FZ_STAGES, zu = it / FZ_STAGES;
+                if (use >= 1) fast_wait(&ctl->empty[w][s], (use - 1) & 1);
+                fast_wait(&fz->zfull[zs], zu & 1);
+                const uint32_t zb = smem_u32(ztiles + (size_t)zs * FD * ZP);
+
+                float acc[MB][4][4];
+#pragma unroll
+                for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+                    for (int nb = 0; nb < 4; ++nb)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) acc[mb][nb][i] = 0.f;
+#pragma unroll
+                for (int ks = 0; ks < FD / 8; ++ks) {
+                    // B fragments (k x n = channel x frame, "col"): b0 (k = t, n = g), b1 (k = t + 4, n = g)
+                    uint32_t bh[4][2], bl[4][2];
+#pragma unroll
+                    for (int nb = 0; nb < 4; ++nb) {
+                        const float v0 = lds32(zb + 4u * ((8 * ks + t) * ZP + 8 * nb + g));
+                        const float v1 = lds32(zb + 4u * ((8 * ks + t + 4) * ZP + 8 * nb + g));
+                        bh[nb][0] = to_tf32(v0); bl[nb][0] = to_tf32(v0 - __uint_as_float(bh[nb][0]));
+                        bh[nb][1] = to_tf32(v1); bl[nb][1] = to_tf32(v1 - __uint_as_float(bh[nb][1]));
+                    }
+#pragma unroll
+                    for (int mb = 0; mb < MB; ++mb) {
+                        uint32_t ah[4], al[4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            ah[i] = to_tf32_pinned(a[mb][ks][i]);
+                            al[i] = to_tf32_pinned(a[mb][ks][i] - __uint_as_float(ah[i]));
+                        }
+#pragma unroll
+                        for (int nb = 0; nb < 4; ++nb) {          // small terms first
+                            mma_tf32(acc[mb][nb], al, bh[nb][0], bh[nb][1]);
+                            mma_tf32(acc[mb][nb], ah, bl[nb][0], bl[nb][1]);
+                            mma_tf32(acc[mb][nb], ah, bh[nb][0], bh[nb][1]);
+                        }
+                    }
+                }
+                // -0.5 sum_d z^2 per frame: only where logp itself is emitted (see the header comment)
+                float zq[4][2];
+#pragma unroll
+                for (int nb = 0; nb < 4; ++nb) zq[nb][0] = zq[nb][1] = 0.f;
+                if (logp_out) {
+                    float sq = 0.f;
+                    for (int d = 0; d < FD; ++d) {
+                        const float v = lds32(zb + 4u * (d * ZP + lane));
+                        sq = fmaf(v, v, sq);
+                    }
+                    sq *= -0.5f;
+#pragma unroll
+                    for (int nb = 0; nb < 4; ++nb) {
+                        zq[nb][0] = __shfl_sync(0xffffffffu, sq, 8 * nb + 2 * t);
+                        zq[nb][1] = __shfl_sync(0xffffffffu, sq, 8 * nb + 2 * t + 1);
+                    }
+                }
+                // D fragments: c0 (g, 2t), c1 (g, 2t + 1), c2 (g + 8, 2t), c3 (g + 8, 2t + 1) -> tile[row][36-pitch]
+                const uint32_t tile = smem_u32(tiles + (size_t)s * stage_floats);
+                const int y0 = it * YT;
+#pragma unroll
+                for (int mb = 0; mb < MB; ++mb) {
+#pragma unroll
+                    for (int half = 0; half < 2; ++half) {
+                        const int x = rbase + 16 * mb + g + 8 * half;
+                        if (x >= RB * TBOX) continue;              // row beyond the stage (band rounding): never consumed
+#pragma unroll
+                        for (int nb = 0; nb < 4; ++nb) {
+                            const int col = 8 * nb + 2 * t;
+                            const float v0 = acc[mb][nb][2 * half] + crow[mb][half];
+                            const float v1 = acc[mb][nb][2 * half + 1] + crow[mb][half];
+                            asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(tile + 4u * (x * TP + col)), "f"(v0), "f"(v1) : "memory");
+                            if (logp_out && x < t_x) {
+                                float* lp = logp_out + ((size_t)b * p.T_x + x) * p.T_y + y0 + col;
+                                if (y0 + col < t_y) lp[0] = v0 + zq[nb][0];
+                                if (y0 + col + 1 < t_y) lp[1] = v1 + zq[nb][1];
+                            }
+                        }
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(&ctl->full[w][s]);
+                    mbar_arrive(&fz->zempty[zs]);
+                }
+            }
+            // zero-fill share `it` of this utterance's output plane
+            const size_t lo = nvec * (size_t)it / n_iter, hi = nvec * (size_t)(it + 1) / n_iter;
+            for (size_t i = lo + ht; i < hi; i += HT) pv[i] = z4;
+            if (it == 0) {
+                if ((size_t)ht < head) pplane[ht] = 0.f;
+                for (size_t i = tail0 + ht; i < plane_elems; i += HT) pplane[i] = 0.f;
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) mas_stamp(4);
+    emit_path(p, pplane, ys, valid, t_x, t_y, b, tid, F_NT);
     if (tid == 0) mas_stamp(5);
 }
 
@@ -726,6 +1000,61 @@ static int plan_wave(int T_x, int T_y, int* xpt_out) {
     for (int s = TMA_MAX_STAGES; s >= 2; --s)
         if (wave_smem_bytes(T_x, T_y, s) <= SMEM_LIMIT) return s;
     return 0;
+}
+
+// Fused logp + MAS path: smem = wavefront layout + the z ring.
+static size_t fused_smem_bytes(int T_x, int T_y, int stages) {
+    const size_t roww = (size_t)((T_x + 3) & ~3);
+    const size_t nyb = (T_y + YT - 1) / YT;
+    const size_t rb = ceil_div(T_x, TBOX);
+    return sizeof(WaveCtl) + sizeof(FusedCtl) + (roww + 4) * 4 + nyb * roww * 4 + 128 + (size_t)stages * rb * TBOX_BYTES +
+           (size_t)FZ_STAGES * FZ_BYTES;
+}
+static int plan_fused(int D, int T_x, int T_y, int* xpt_out) {
+    const int xpt = max(1, ceil_div(T_x, 32 * NDP));
+    *xpt_out = xpt;
+    if (D != FD || T_x < 1 || T_y < 1 || T_y % 4 != 0 || xpt > F_MAX_XPT) return 0;
+    for (int s = TMA_MAX_STAGES; s >= 2; --s)
+        if (fused_smem_bytes(T_x, T_y, s) <= SMEM_LIMIT) return s;
+    return 0;
+}
+int fused_supported(int D, int T_x, int T_y, int has_logs) {
+    int xpt;
+    return (!has_logs && plan_fused(D, T_x, T_y, &xpt) > 0) ? 1 : 0;
+}
+
+template <int XPT>
+static int launch_fused(const Params& p, const CUtensorMap& tm, const float* x_m, float* logp_out, size_t smem, cudaStream_t stream) {
+    GTK_CUDA(cudaFuncSetAttribute(mas_fused_kernel<XPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ProfScope prof("mas_fused", stream);
+    mas_fused_kernel<XPT><<<p.B, F_NT, smem, stream>>>(tm, p, x_m, logp_out);
+    return check_launch("mas_fused_kernel");
+}
+
+int fused_forward(const float* z, const float* x_m, const int* t_xs, const int* t_ys, float* path, int* dur_out, int* idx_out,
+                  float* logp_out, int B, int D, int T_x, int T_y, cudaStream_t stream) {
+    GTK_REQUIRE(B >= 0 && T_x >= 0 && T_y >= 0 && D >= 0, "negative size");
+    if (B == 0) return GTK_OK;
+    GTK_REQUIRE(z && x_m && t_xs && t_ys && path, "null pointer");
+    int xpt = 0;
+    const int stages = plan_fused(D, T_x, T_y, &xpt);
+    if (stages == 0 || (reinterpret_cast<uintptr_t>(z) & 15) != 0) {
+        set_error("mas_fused_logp: unsupported shape D=%d T_x=%d T_y=%d (needs D == %d, T_x <= %d, T_y %% 4 == 0, 16-byte aligned z); "
+                  "use gtk_logp + gtk_mas_forward", D, T_x, T_y, FD, 32 * NDP * F_MAX_XPT);
+        return GTK_ERR_UNSUPPORTED;
+    }
+    Params p;
+    p.value = nullptr; p.path = path; p.t_xs = t_xs; p.t_ys = t_ys; p.dur_out = dur_out; p.idx_out = idx_out;
+    p.B = B; p.T_x = T_x; p.T_y = T_y; p.n_stages = stages; p.vec4 = 1;
+    CUtensorMap tm;
+    const uint64_t dims[3] = {(uint64_t)T_y, (uint64_t)D, (uint64_t)B};
+    const uint64_t strides[2] = {(uint64_t)T_y * 4, (uint64_t)T_y * 4 * D};
+    const uint32_t box[3] = {ZP, FD, 1};
+    int rc = tc::make_tmap_f32(&tm, z, 3, dims, strides, box);
+    if (rc) return rc;
+    const size_t smem = fused_smem_bytes(T_x, T_y, stages);
+    if (xpt == 1) return launch_fused<1>(p, tm, x_m, logp_out, smem, stream);
+    return launch_fused<2>(p, tm, x_m, logp_out, smem, stream);
 }
 
 template <int XPT>

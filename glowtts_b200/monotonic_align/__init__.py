@@ -33,3 +33,20 @@ def maximum_path_lengths(value: torch.Tensor, t_xs: torch.Tensor, t_ys: torch.Te
     value fp32 [b,t_x,t_y] (already masked), t_xs / t_ys int32 [b] on the device."""
     with torch.no_grad():
         return ops.mas_path(value, t_xs, t_ys)
+
+
+def maximum_path_from_prior(z: torch.Tensor, x_m: torch.Tensor, x_logs, t_xs: torch.Tensor, t_ys: torch.Tensor,
+                            return_logp: bool = False):
+    """models.py:1076-1083 as one call: the alignment of z [b,d,t_y] against the prior means x_m [b,d,t_x]
+    (x_logs [b,d,t_x] or None for mean_only models), lengths int32 [b] on the device.
+    -> (path, durations, index[, logp]).  Mean-only shapes the fused kernel covers (ops.mas_fused_supported) run as ONE
+    launch with logp computed on the tensor cores inside the MAS CTA; everything else runs the logp kernel followed by
+    the MAS kernel -- both are CUDA paths, the result differs only by fp32 summation order."""
+    with torch.no_grad():
+        D, T_x, T_y = x_m.shape[1], x_m.shape[2], z.shape[2]
+        if ops.mas_fused_supported(D, T_x, T_y, x_logs is not None) and z.data_ptr() % 16 == 0:
+            path, dur, idx, lp = ops.mas_fused_logp(z, x_m, t_xs, t_ys, return_logp)
+        else:
+            lp = ops.logp(x_m, x_logs, z)
+            path, dur, idx = ops.mas_path(lp, t_xs, t_ys)
+    return (path, dur, idx, lp) if return_logp else (path, dur, idx)

@@ -85,6 +85,39 @@ def _(value, t_xs, t_ys, force_generic=0):
             value.new_empty((B, T_y), dtype=torch.int32))
 
 
+def mas_fused_supported(D: int, T_x: int, T_y: int, has_x_logs: bool) -> bool:
+    """Whether gtk_mas_fused_logp covers this shape (mean_only, D == 80, T_x <= 256, T_y % 4 == 0)."""
+    return bool(_lib.load().gtk_mas_fused_supported(int(D), int(T_x), int(T_y), int(has_x_logs)))
+
+
+@torch.library.custom_op(f"{NS}::mas_fused_logp", mutates_args=(), device_types="cuda")
+def mas_fused_logp(z: Tensor, x_m: Tensor, t_xs: Tensor, t_ys: Tensor, want_logp: bool = False) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """models.py:1076-1083 in one kernel (mean_only): logp is built tile by tile inside the MAS CTA and never stored.
+    z [B,D,T_y], x_m [B,D,T_x] -> (path, durations, index, logp) -- logp is [B,T_x,T_y] (zero outside the lengths) when
+    want_logp, else an empty tensor.  Raises for shapes the fused kernel does not cover (see mas_fused_supported)."""
+    z = _chk(z, "z")
+    x_m = _chk(x_m, "x_m")
+    t_xs = _chk(t_xs, "t_xs", torch.int32)
+    t_ys = _chk(t_ys, "t_ys", torch.int32)
+    B, D, T_x = x_m.shape
+    T_y = z.shape[2]
+    path = torch.empty(B, T_x, T_y, dtype=torch.float32, device=z.device)
+    dur = torch.empty(B, T_x, dtype=torch.int32, device=z.device)
+    idx = torch.empty(B, T_y, dtype=torch.int32, device=z.device)
+    lp = torch.zeros(B, T_x, T_y, dtype=torch.float32, device=z.device) if want_logp else z.new_empty(0)
+    _lib.call("gtk_mas_fused_logp", _p(z), _p(x_m), None, _p(t_xs), _p(t_ys), _p(path), _p(dur), _p(idx),
+              _p(lp) if want_logp else None, B, D, T_x, T_y, _stream())
+    return path, dur, idx, lp
+
+
+@mas_fused_logp.register_fake
+def _(z, x_m, t_xs, t_ys, want_logp=False):
+    B, D, T_x = x_m.shape
+    T_y = z.shape[2]
+    return (z.new_empty((B, T_x, T_y)), z.new_empty((B, T_x), dtype=torch.int32), z.new_empty((B, T_y), dtype=torch.int32),
+            z.new_empty((B, T_x, T_y)) if want_logp else z.new_empty(0))
+
+
 # =============================================================================== clip_grad_value_
 @torch.library.custom_op(f"{NS}::clip_grad_value", mutates_args=("grad", "acc"), device_types="cuda")
 def clip_grad_value(grad: Tensor, clip_value: float, do_clip: bool, norm_type: float, acc: Tensor) -> None:

@@ -62,6 +62,18 @@ int gtk_mas_forward(const float* value, const int32_t* t_xs, const int32_t* t_ys
                     int32_t* idx_out, int B, int T_x, int T_y, void* workspace, size_t workspace_bytes,
                     int force_generic, void* stream);
 
+/* Fused variant: models.py:1076-1083 (logp construction + maximum_path) in ONE kernel -- the [B,T_x,T_y] value tensor
+ * is computed tile by tile on the tensor cores inside the MAS CTA (3xTF32 mma.sync) and never exists in HBM.
+ * Covers mean_only models (x_logs == NULL; all configs/base*.json) with D == 80, T_x <= 256, T_y % 4 == 0;
+ * gtk_mas_fused_supported() tells, anything else returns GTK_ERR_UNSUPPORTED (use gtk_logp + gtk_mas_forward).
+ * z [B,D,T_y], x_m [B,D,T_x]; path/dur_out/idx_out as gtk_mas_forward; logp_out [B,T_x,T_y] is optional (NULL):
+ * when given, the cells inside [0,t_x) x [0,t_y) receive logp (the rest is left untouched).  Not bit-identical to
+ * logp -> MAS (fp32 summation order differs): reported as path agreement + max |delta logp|. */
+int gtk_mas_fused_supported(int D, int T_x, int T_y, int has_x_logs);
+int gtk_mas_fused_logp(const float* z, const float* x_m, const float* x_logs, const int32_t* t_xs, const int32_t* t_ys,
+                       float* path, int32_t* dur_out, int32_t* idx_out, float* logp_out, int B, int D, int T_x, int T_y,
+                       void* stream);
+
 /* ---- logp (models.py:1076-1082) ---------------------------------------------------------- */
 /* logp[b,x,y] = log N(z[b,:,y]; x_m[b,:,x], exp(x_logs[b,:,x])).  x_logs may be NULL (mean_only:
  * x_logs == 0, models.py:712-713).  x_m,x_logs [B,D,T_x]; z [B,D,T_y]; logp [B,T_x,T_y]. */

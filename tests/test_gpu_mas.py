@@ -162,3 +162,74 @@ def test_duration_roundtrip_through_generate_path():
     path, dur, _ = ops.mas_path(v, t_xs, t_ys)
     again = commons.generate_path(dur.float(), m)
     assert torch.equal(again, path)
+
+
+# ------------------------------------------------------------------------------------------ fused logp + MAS
+def _fused_case(B, TX, TY, seed):
+    gen = torch.Generator().manual_seed(seed)
+    x_m = torch.randn(B, 80, TX, generator=gen) * 0.5
+    z = torch.randn(B, 80, TY, generator=gen)
+    t_xs = torch.randint(max(1, TX // 2), TX + 1, (B,), generator=gen)
+    t_ys = torch.randint(max(TX, TY // 2), TY + 1, (B,), generator=gen)
+    t_xs[0], t_ys[0] = TX, TY
+    t_ys = torch.maximum(t_ys, t_xs)
+    return x_m, z, t_xs.to(torch.int32), t_ys.to(torch.int32)
+
+
+@pytest.mark.parametrize("B,TX,TY", [(3, 37, 100), (2, 128, 256), (3, 130, 300), (2, 200, 64 * 4), (2, 256, 1000),
+                                     (4, 180, 860), (2, 1, 8), (2, 33, 36)])
+def test_fused_logp_mas_agrees_with_logp_then_mas(B, TX, TY):
+    """gtk_mas_fused_logp (north_star: 'fused variant'): reported as max |delta logp| and path agreement, plus the
+    property that makes agreement meaningful -- the fused path is a valid monotonic alignment whose total score under
+    the ORACLE logp equals the oracle path's optimum up to fp32 rounding."""
+    from glowtts_b200 import monotonic_align, ops
+    from oracle import flow as oflow
+    x_m, z, t_xs, t_ys = _fused_case(B, TX, TY, 100 + TX)
+    assert ops.mas_fused_supported(80, TX, TY, False)
+    path, dur, idx, lp = monotonic_align.maximum_path_from_prior(z.cuda(), x_m.cuda(), None, t_xs.cuda(), t_ys.cuda(),
+                                                                 return_logp=True)
+    torch.cuda.synchronize()
+    path, dur, idx, lp = path.cpu().numpy(), dur.cpu().numpy(), idx.cpu().numpy(), lp.cpu().numpy()
+    want_lp = oflow.logp(x_m, torch.zeros_like(x_m), z).numpy()
+    mask = np.zeros((B, TX, TY), np.float32)
+    for i in range(B):
+        mask[i, : t_xs[i], : t_ys[i]] = 1
+    d_logp = np.abs(lp - want_lp * mask).max()
+    assert d_logp < 5e-4, d_logp                                    # |logp| ~ 1e2: fp32-level agreement from 3xTF32
+    ref = omas.maximum_path_np(want_lp * mask, mask)
+    agree, total = 0, 0
+    for i in range(B):
+        tx, ty = int(t_xs[i]), int(t_ys[i])
+        p = path[i]
+        assert set(np.unique(p)) <= {0.0, 1.0}
+        assert p[tx:].sum() == 0 and p[:, ty:].sum() == 0
+        assert (p[:tx, :ty].sum(0) == 1).all()                      # one token per frame
+        tok = p[:tx, :ty].argmax(0)
+        assert tok[0] == 0 and tok[-1] == tx - 1 and ((np.diff(tok) == 0) | (np.diff(tok) == 1)).all()
+        assert (dur[i, :tx] == p[:tx, :ty].sum(1)).all() and (idx[i, :ty] == tok).all() and (idx[i, ty:] == -1).all()
+        score = float((want_lp[i].astype(np.float64) * p).sum())
+        best = float((want_lp[i].astype(np.float64) * ref[i]).sum())
+        assert score >= best - 1e-3 * max(1.0, abs(best)) * 1e-2, (score, best)     # optimal up to rounding (1e-5 rel)
+        agree += int((tok == ref[i, :tx, :ty].argmax(0)).sum())
+        total += ty
+    print(f"fused MAS B={B} T_x={TX} T_y={TY}: max|dlogp|={d_logp:.2e}, path agreement {agree / total:.4f}")
+    assert agree / total > 0.97
+
+
+def test_fused_wrapper_routes_uncovered_shapes_through_logp_then_mas():
+    from glowtts_b200 import monotonic_align, ops
+    gen = torch.Generator().manual_seed(5)
+    B, TX, TY = 2, 300, 640                                          # T_x > 256: not fused
+    assert not ops.mas_fused_supported(80, TX, TY, False)
+    assert not ops.mas_fused_supported(80, 100, 400, True)           # x_logs given: not fused
+    assert not ops.mas_fused_supported(80, 100, 402, False)          # T_y % 4 != 0
+    x_m = torch.randn(B, 80, TX, generator=gen).cuda() * 0.5
+    z = torch.randn(B, 80, TY, generator=gen).cuda()
+    t_xs = torch.tensor([300, 211], dtype=torch.int32).cuda()
+    t_ys = torch.tensor([640, 500], dtype=torch.int32).cuda()
+    path, dur, idx = monotonic_align.maximum_path_from_prior(z, x_m, None, t_xs, t_ys)
+    lp = ops.logp(x_m, None, z)
+    want, _, _ = ops.mas_path(lp, t_xs, t_ys)
+    assert torch.equal(path, want)
+    with pytest.raises(RuntimeError):
+        ops.mas_fused_logp(z, x_m, t_xs, t_ys)
