@@ -239,6 +239,51 @@ def mas_alone(device, steps=20, B=32, TX=T_TEXT, TY=T_MEL, n_buf=8, name="config
             "latency_floor_note": f"T_y={TY} dependent DP columns per utterance; {B} CTAs on 148 SMs"}
 
 
+def mas_fused_alone(device, steps=20, B=32, TX=T_TEXT, TY=T_MEL, n_buf=12):
+    """north_star's fused variant at configs[0]'s shape: logp + MAS as ONE kernel (gtk_mas_fused_logp) against the
+    two-kernel sequence gtk_logp -> gtk_mas_forward on the same z / x_m (rotating over n_buf input sets so that the
+    operands and the 19.8 MB logp tensor do not sit in L2 between repeats).  Algorithmic HBM bytes per cell: fused =
+    4 (path) + operands; unfused = 4 (logp write) + 4 (logp read) + 4 (path) + operands."""
+    from glowtts_b200 import ops
+    gen = torch.Generator(device=device).manual_seed(SEED)
+    zs = [torch.randn(B, 80, TY, device=device, generator=gen) for _ in range(n_buf)]
+    xs = [torch.randn(B, 80, TX, device=device, generator=gen) * 0.5 for _ in range(n_buf)]
+    t_xs = torch.full((B,), TX, dtype=torch.int32, device=device)
+    t_ys = torch.full((B,), TY, dtype=torch.int32, device=device)
+    if not ops.mas_fused_supported(80, TX, TY, False):
+        return {"error": "shape not covered by the fused kernel"}
+
+    def unfused(i):
+        return ops.mas_path(ops.logp(xs[i], None, zs[i]), t_xs, t_ys)
+
+    def fused(i):
+        return ops.mas_fused_logp(zs[i], xs[i], t_xs, t_ys)
+
+    from glowtts_b200 import _lib
+    out = {}
+    for name, fn in (("logp_then_mas", unfused), ("fused", fused)):
+        for i in range(3):
+            fn(i % n_buf)
+        torch.cuda.synchronize()
+        _lib.prof_enable(True)                    # CUDA events around each kernel launch, on the launching stream
+        for i in range(steps):
+            fn(i % n_buf)
+        torch.cuda.synchronize()
+        prof = _lib.prof_read()
+        _lib.prof_enable(False)
+        per = {k: v[1] / max(v[0], 1) * 1e3 for k, v in prof.items()}
+        out[name + "_us"] = sum(per.values())
+        out[name + "_kernels_us"] = per
+    ia = unfused(0)[2]
+    ib = fused(0)[2]
+    cells = B * TX * TY
+    out.update({"workload": f"logp + maximum_path from z [B,80,{TY}] and x_m [B,80,{TX}], B={B}, mean_only, full lengths",
+                "cells_per_s_fused": cells / (out["fused_us"] * 1e-6), "cells_per_s_logp_then_mas": cells / (out["logp_then_mas_us"] * 1e-6),
+                "path_agreement": float((ia == ib).float().mean()),
+                "timing": f"library profiler: CUDA events around each kernel launch, mean of {steps} launches"})
+    return out
+
+
 def inference_alone(run, steps=10):
     """configs[2] at the train-step batch: the reverse decoder flow z -> mel (models.py:1230) after store_inverse(),
     no_grad, B=32 x T_mel=860 resident in HBM; CUDA events over `steps` calls."""
@@ -466,6 +511,10 @@ def main():
             # MAS / inference paths), so the scaling run keeps to the training step
             out["mas"] = mas_alone(device)
             out["inference"] = inference_alone(run)
+            try:
+                out["mas_fused"] = mas_fused_alone(device)
+            except Exception as e:
+                out["mas_fused"] = {"error": repr(e)}
             del run
             torch.cuda.empty_cache()
             try:

@@ -612,7 +612,7 @@ __global__ void __launch_bounds__(NT, 1) mas_wave_kernel(const __grid_constant__
 //   * 4 DP warps: unchanged (wave_dp_warp), fed through the same per-band rings of [row][36]-pitch tiles;
 //   * 8 MMA warps, two per DP band: a warp keeps its 16 * XPT rows of x_m as mma.sync A fragments in REGISTERS for
 //     the whole utterance (80 fp32 at XPT = 2) and per tile runs the [16 XPT x 80] x [80 x 32] product on the
-//     tensor cores as 3xTF32 (a_lo b_hi + a_hi b_lo + a_hi b_hi, hi = tf32(v), lo = tf32(v - hi): fp32-level
+//     tensor cores as 3xTF32 (a_lo b_hi + a_hi b_lo + a_hi b_hi, hi = upper 19 bits of v, lo = v - hi: fp32-level
 //     accuracy from the tf32 pipe), adds c[x] and stores the D fragments into its band's tile stage;
 //   * z tiles (80 x 40-float rows: pitch 40 makes the B-fragment reads conflict-free) arrive by TMA into a
 //     4-deep ring shared by all bands (issued by one lane of MMA warp 0, released by all active MMA warps);
@@ -630,20 +630,19 @@ struct FusedCtl {
     uint64_t zfull[FZ_STAGES], zempty[FZ_STAGES];
 };
 
-__device__ __forceinline__ uint32_t to_tf32(float v) {
+// hi / lo split for 3xTF32 without cvt (cvt.rna.tf32 issues at a quarter of the ALU rate and there are 320 of them per
+// warp and tile): the tf32 tensor-core path reads the upper 19 bits of an fp32 register, so hi = v with the low 13
+// mantissa bits cleared (one LOP) and lo = v - hi (exact in fp32; its own low bits are ignored by the MMA).
+// `pinned` (volatile) keeps the split of the loop-invariant A fragments inside the tile loop -- hoisted, hi and lo of
+// every fragment would have to live in registers (2 x 80) and spill.
+__device__ __forceinline__ uint32_t tf32_hi(float v) { return __float_as_uint(v) & 0xffffe000u; }
+__device__ __forceinline__ uint32_t tf32_hi_pinned(float v) {
     uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
-    return r;
-}
-// volatile: keeps the split of the (loop-invariant) A fragments inside the tile loop -- hoisted, hi and lo of every
-// fragment would have to live in registers (2 x 80) and spill
-__device__ __forceinline__ uint32_t to_tf32_pinned(float v) {
-    uint32_t r;
-    asm volatile("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    asm volatile("and.b32 %0, %1, 0xffffe000;" : "=r"(r) : "r"(__float_as_uint(v)));
     return r;
 }
 __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+    asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
                  : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
@@ -789,24 +788,31 @@ __global__ void __launch_bounds__(F_NT, 1) mas_fused_kernel(const __grid_constan
                     for (int nb = 0; nb < 4; ++nb) {
                         const float v0 = lds32(zb + 4u * ((8 * ks + t) * ZP + 8 * nb + g));
                         const float v1 = lds32(zb + 4u * ((8 * ks + t + 4) * ZP + 8 * nb + g));
-                        bh[nb][0] = to_tf32(v0); bl[nb][0] = to_tf32(v0 - __uint_as_float(bh[nb][0]));
-                        bh[nb][1] = to_tf32(v1); bl[nb][1] = to_tf32(v1 - __uint_as_float(bh[nb][1]));
+                        bh[nb][0] = tf32_hi(v0); bl[nb][0] = __float_as_uint(v0 - __uint_as_float(bh[nb][0]));
+                        bh[nb][1] = tf32_hi(v1); bl[nb][1] = __float_as_uint(v1 - __uint_as_float(bh[nb][1]));
                     }
+                    uint32_t ah[MB][4], al[MB][4];
 #pragma unroll
-                    for (int mb = 0; mb < MB; ++mb) {
-                        uint32_t ah[4], al[4];
+                    for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
-                            ah[i] = to_tf32_pinned(a[mb][ks][i]);
-                            al[i] = to_tf32_pinned(a[mb][ks][i] - __uint_as_float(ah[i]));
+                            ah[mb][i] = tf32_hi_pinned(a[mb][ks][i]);
+                            al[mb][i] = __float_as_uint(a[mb][ks][i] - __uint_as_float(ah[mb][i]));
                         }
+                    // three passes over the 4 * MB independent accumulators (small terms first): the MMAs that depend on each
+                    // other are 4 * MB instructions apart instead of back to back
 #pragma unroll
-                        for (int nb = 0; nb < 4; ++nb) {          // small terms first
-                            mma_tf32(acc[mb][nb], al, bh[nb][0], bh[nb][1]);
-                            mma_tf32(acc[mb][nb], ah, bl[nb][0], bl[nb][1]);
-                            mma_tf32(acc[mb][nb], ah, bh[nb][0], bh[nb][1]);
-                        }
-                    }
+                    for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+                        for (int nb = 0; nb < 4; ++nb) mma_tf32(acc[mb][nb], al[mb], bh[nb][0], bh[nb][1]);
+#pragma unroll
+                    for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+                        for (int nb = 0; nb < 4; ++nb) mma_tf32(acc[mb][nb], ah[mb], bl[nb][0], bl[nb][1]);
+#pragma unroll
+                    for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+                        for (int nb = 0; nb < 4; ++nb) mma_tf32(acc[mb][nb], ah[mb], bh[nb][0], bh[nb][1]);
                 }
                 // -0.5 sum_d z^2 per frame: only where logp itself is emitted (see the header comment)
                 float zq[4][2];
