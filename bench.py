@@ -42,7 +42,9 @@ FLOP_PER_SQ_FRAME_FWD = 2 * (192 * 80 + 4 * (384 * 192 * 5) + 3 * (384 * 192) + 
 SEED = 1234  # configs/base.json:5
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed `ncu --set full`
 # capture (profiles/); bench.py never runs under a profiler, so the figure is carried here and updated per round.
-NCU_TRAFFIC = {"wn_layer_tc": 23.05e6,      # profiles/ncu_wn_layer_r01.txt: (16.89 + 0.82 MB, 27.50 + 0.89 MB) -> mean bytes / launch
+NCU_TRAFFIC = {"mas configs[0]": 19.9e6,    # profiles/ncu_mas_cfg1_r01.csv: 19.89 MB read (value), 0 written (the 19.8 MB path stays in L2)
+               "mas configs[4] on one GPU": 3.383e9,   # profiles/ncu_mas_cfg5_r01.csv: 1.728 GB read + 1.655 GB written (algorithmic 3.277 GB)
+               "wn_layer_tc": 23.05e6,      # profiles/ncu_wn_layer_r01.txt: (16.89 + 0.82 MB, 27.50 + 0.89 MB) -> mean bytes / launch
                "wn_bwd_layer_tc": 33.0e6}   # profiles/ncu_wn_bwd_layer_r01.txt: 32.78 MB read + 0.2 MB written per launch
 
 
@@ -235,7 +237,8 @@ def mas_alone(device, steps=20, B=32, TX=T_TEXT, TY=T_MEL, n_buf=8, name="config
     return {"workload": f"{name}: maximum_path B={B} T_x={TX} T_y={TY} fp32, full lengths", "cells_per_s": cells / per if per else 0.0,
             "us_per_call": per * 1e6, "launches_timed": n,
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
-                         "traffic": None, "algorithmic_bytes_per_cell": 8, "peak_source": pk["src"]},
+                         "traffic": NCU_TRAFFIC.get("mas " + name) if (B, TX, TY) in ((32, 180, 860), (512, 400, 2000)) else None,
+                         "algorithmic_bytes_per_cell": 8, "peak_source": pk["src"]},
             "latency_floor_note": f"T_y={TY} dependent DP columns per utterance; {B} CTAs on 148 SMs"}
 
 

@@ -109,3 +109,44 @@ class GraphedTrainStep:
                 dst.copy_(src, non_blocking=True)
         self.graph.replay()
         return self.out.loss
+
+
+class GraphedReverse:
+    """The inference hot path z -> mel (models.py:1230: decoder(z, mask, g, reverse=True)) captured as a CUDA graph for
+    one (batch, T_mel) shape.  The reverse flow is ~100 short launches; below B*T_mel ~ 16k frames the host launch
+    path, not the GPU, sets the latency (profiles/config_sweeps_r01.json), so replaying them as one graph is what makes
+    small-batch synthesis fast.  Call store_inverse() on the decoder first (as the reference's inference does).
+
+        rev = GraphedReverse(decoder, z_example, mask_example, g=None)
+        mel = rev(z, mask)            # same shapes as the examples; returns the static output tensor
+    """
+
+    def __init__(self, decoder, z, mask, g=None, warmup: int = 2):
+        if z.device.type != "cuda":
+            raise RuntimeError("glowtts_b200.GraphedReverse: tensors must live on a CUDA device")
+        self.decoder = decoder
+        self.z, self.mask = z.clone(), mask.clone()
+        self.g = None if g is None else g.clone()
+        dev = z.device
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(max(1, warmup)):
+                decoder(self.z, self.mask, g=self.g, reverse=True)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        n0 = _lib.launch_count()
+        with torch.cuda.graph(self.graph), torch.no_grad():
+            self.out, _ = decoder(self.z, self.mask, g=self.g, reverse=True)
+        self.launches = _lib.launch_count() - n0
+
+    def __call__(self, z=None, mask=None, g=None) -> torch.Tensor:
+        if z is not None:
+            self.z.copy_(z, non_blocking=True)
+        if mask is not None:
+            self.mask.copy_(mask, non_blocking=True)
+        if g is not None and self.g is not None:
+            self.g.copy_(g, non_blocking=True)
+        self.graph.replay()
+        return self.out

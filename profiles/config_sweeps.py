@@ -18,7 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench  # noqa: E402
 from glowtts_b200 import models  # noqa: E402
-from glowtts_b200.hot_path import train_hot_path  # noqa: E402
+from glowtts_b200.hot_path import GraphedReverse, train_hot_path  # noqa: E402
 
 DEV = torch.device("cuda", 0)
 
@@ -60,8 +60,14 @@ def inference_sweep():
                 mask = torch.ones(B, 1, T, device=DEV)
                 ms = timed(lambda: dec(z, mask, reverse=True), 5 if B * T > 100000 else 10)
                 flop = bench.FLOP_PER_SQ_FRAME_FWD * 12 * (B * T // 2)
-                rows.append({"B": B, "T_mel": T, "ms": ms, "mel_frames_per_s": B * T / (ms * 1e-3),
-                             "tflops": flop / (ms * 1e-3) / 1e12})
+                row = {"B": B, "T_mel": T, "ms": ms, "mel_frames_per_s": B * T / (ms * 1e-3),
+                       "tflops": flop / (ms * 1e-3) / 1e12}
+                if B * T <= 64000:                # launch-bound region: the same call replayed as one CUDA graph
+                    rev = GraphedReverse(dec, z, mask)
+                    row["ms_graphed"] = timed(lambda: rev(), 10)
+                    row["launches"] = int(rev.launches)
+                    del rev
+                rows.append(row)
                 del z, mask
     return rows
 

@@ -307,3 +307,31 @@ def test_flat_parameters_and_graphed_step_match_eager_training():
     for k in weights["eager"]:
         assert torch.allclose(weights["eager"][k], weights["flat"][k], rtol=1e-5, atol=1e-7), k
         assert torch.allclose(weights["eager"][k], weights["graph"][k], rtol=1e-5, atol=1e-7), k
+
+
+def test_graphed_reverse_matches_eager_reverse():
+    """hot_path.GraphedReverse: the inference call z -> mel replayed as one CUDA graph returns what the eager call does."""
+    import helpers
+    from glowtts_b200 import models
+    from glowtts_b200.hot_path import GraphedReverse
+    cfg = dict(helpers.TINY_CFG, in_channels=16, n_blocks=3, n_layers=2, hidden_channels=64, gin_channels=4)
+    sd = helpers.make_state_dict(cfg, 61)
+    for precision in ("fp32", "bf16"):
+        dec = models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"], cfg["dilation_rate"],
+                                     cfg["n_blocks"], cfg["n_layers"], n_split=cfg["n_split"], n_sqz=cfg["n_sqz"],
+                                     gin_channels=4, precision=precision)
+        dec.load_state_dict(sd, strict=True)
+        dec = dec.cuda().eval()
+        dec.store_inverse()
+        y, mask, _, g = helpers.flow_inputs(cfg, 3, 40, 9, True)
+        y, mask, g = y.cuda(), mask.cuda(), g.cuda()
+        with torch.no_grad():
+            want, _ = dec(y, mask, g=g, reverse=True)
+        rev = GraphedReverse(dec, torch.zeros_like(y), mask, g=torch.zeros_like(g))
+        got = rev(y, mask, g).clone()
+        assert rev.launches > 0
+        assert torch.equal(got, want)
+        y2 = torch.randn_like(y) * mask
+        with torch.no_grad():
+            want2, _ = dec(y2, mask, g=g, reverse=True)
+        assert torch.equal(rev(y2).clone(), want2)
