@@ -86,7 +86,8 @@ int forward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const flo
 int reverse(const gtk_decoder_desc* d, const gtk_block_params* blocks, const float* z, const float* mask, float* x,
             void* workspace, size_t ws_bytes, cudaStream_t st);
 int backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads, const float* mask,
-             const float* dz, const float* dlogdet, float* dx, void* workspace, size_t ws_bytes, cudaStream_t st);
+             const float* dz, const float* dlogdet, float* dx, void* workspace, size_t ws_bytes, int blk_hi, int blk_lo,
+             cudaStream_t st);
 }  // namespace decoder
 }  // namespace gtk
 
@@ -324,7 +325,13 @@ int gtk_decoder_reverse(const gtk_decoder_desc* d, const gtk_block_params* block
 int gtk_decoder_backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads,
                          const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace,
                          size_t workspace_bytes, void* stream) {
-    return decoder::backward(d, blocks, grads, mask, dz, dlogdet, dx, workspace, workspace_bytes, ST);
+    GTK_REQUIRE(d != nullptr, "null descriptor");
+    return decoder::backward(d, blocks, grads, mask, dz, dlogdet, dx, workspace, workspace_bytes, d->n_blocks - 1, 0, ST);
+}
+int gtk_decoder_backward_range(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads,
+                               const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace,
+                               size_t workspace_bytes, int blk_hi, int blk_lo, void* stream) {
+    return decoder::backward(d, blocks, grads, mask, dz, dlogdet, dx, workspace, workspace_bytes, blk_hi, blk_lo, ST);
 }
 
 }  // extern "C"

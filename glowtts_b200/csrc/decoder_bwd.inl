@@ -35,18 +35,26 @@ static int wgrad_param(const float* g, const float* v, float* dg, float* dv, flo
     return wgrad(dout, dout_bs, in, in_bs, mask, dv, B, Cin, M, T, K, dil, mask_dout, 0, st);
 }
 
+// Blocks blk_hi .. blk_lo (inclusive, descending).  The running gradient dZ lives in the workspace between calls, so the
+// whole backward may be issued as consecutive ranges (NB-1 .. a, a-1 .. b, ..., .. 0): the gradients of a finished range
+// are final and can be all-reduced while the next range computes.  The first range (blk_hi == NB-1) reads dz, the last
+// (blk_lo == 0) writes dx.
 int backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads, const float* mask,
-             const float* dz, const float* dlogdet, float* dx, void* workspace, size_t ws_bytes, cudaStream_t st) {
+             const float* dz, const float* dlogdet, float* dx, void* workspace, size_t ws_bytes, int blk_hi, int blk_lo,
+             cudaStream_t st) {
     Dims D;
     GTK_TRY(make_dims(d, &D));
     GTK_REQUIRE(blocks && grads && mask && dz && dlogdet && dx && workspace, "null pointer");
-    if (d->precision == 1) return tc_backward(d, D, blocks, grads, mask, dz, dlogdet, dx, workspace, ws_bytes, st);
+    GTK_REQUIRE(blk_lo >= 0 && blk_hi >= blk_lo && blk_hi < D.NB, "block range");
+    const bool first = blk_hi == D.NB - 1, last = blk_lo == 0;
+    if (d->precision == 1)
+        return tc_backward(d, D, blocks, grads, mask, dz, dlogdet, dx, workspace, ws_bytes, blk_hi, blk_lo, st);
     if (d->precision != 0) { set_error("decoder: precision %d not available in this build", d->precision); return GTK_ERR_UNSUPPORTED; }
     Layout L;
     make_layout(D, 1, &L);
     if (ws_bytes < L.total * sizeof(float)) { set_error("decoder_backward: workspace %zu < %zu", ws_bytes, L.total * sizeof(float)); return GTK_ERR_WORKSPACE; }
     if (D.B == 0 || D.T == 0) return GTK_OK;
-    if (D.Tq * D.n != D.T || D.Tq == 0) GTK_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)D.B * D.Cin * D.T, st));
+    if (first && (D.Tq * D.n != D.T || D.Tq == 0)) GTK_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)D.B * D.Cin * D.T, st));
     if (D.Tq == 0) return GTK_OK;
 
     float* ws = static_cast<float*>(workspace);
@@ -67,9 +75,9 @@ int backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gt
     float* wp = ws + L.wp;
 
     // unsqueeze^T: dz [B, Cin, Tq*n] -> dZ [B, C, Tq], masked by the squeezed mask
-    GTK_TRY(flow::squeeze(dz, msq, dZ, nullptr, B, D.Cin, D.Tq * D.n, D.n, 1, st));
+    if (first) GTK_TRY(flow::squeeze(dz, msq, dZ, nullptr, B, D.Cin, D.Tq * D.n, D.n, 1, st));
 
-    for (int blk = D.NB - 1; blk >= 0; --blk) {
+    for (int blk = blk_hi; blk >= blk_lo; --blk) {
         const gtk_block_params& P = blocks[blk];
         const gtk_block_grads& G = grads[blk];
         const float* we = ws + L.weff + (size_t)blk * L.weff_block;
@@ -134,6 +142,6 @@ int backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gt
         GTK_TRY(flow::logdet_const_bwd(dlogdet, x_len, B, G.an_logs, C, winv, D.NS, (float)(C / D.NS), G.ic_weight, st));
     }
     // squeeze^T: dZ [B, C, Tq] -> dx [B, Cin, T] (row length T; an odd tail frame keeps its zero)
-    GTK_TRY(flow::unsqueeze(dZ, msq, dx, nullptr, B, C, T, D.n, D.T, st));
+    if (last) GTK_TRY(flow::unsqueeze(dZ, msq, dx, nullptr, B, C, T, D.n, D.T, st));
     return GTK_OK;
 }

@@ -274,7 +274,8 @@ static int tc_wgrad_param(const float* g, const float* v, float* dg, float* dv, 
 
 static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_params* blocks, const gtk_block_grads* grads,
                        const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace, size_t ws_bytes,
-                       cudaStream_t st) {
+                       int blk_hi, int blk_lo, cudaStream_t st) {
+    const bool first = blk_hi == D.NB - 1, last = blk_lo == 0;
     GTK_TRY(tc_supported(D));
     Layout L32;
     make_layout(D, 0, &L32);
@@ -282,7 +283,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     make_tc_layout(D, L32, 1, &L);
     if (ws_bytes < L.total) { set_error("decoder_backward(bf16): workspace %zu < %zu", ws_bytes, L.total); return GTK_ERR_WORKSPACE; }
     if (D.B == 0 || D.T == 0) return GTK_OK;
-    if (D.Tq * D.n != D.T || D.Tq == 0) GTK_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)D.B * D.Cin * D.T, st));
+    if (first && (D.Tq * D.n != D.T || D.Tq == 0)) GTK_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)D.B * D.Cin * D.T, st));
     if (D.Tq == 0) return GTK_OK;
 
     unsigned char* ws = static_cast<unsigned char*>(workspace);
@@ -301,8 +302,8 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     bf16* dh0 = reinterpret_cast<bf16*>(ws + L.b_dh0);
     float* wpart = reinterpret_cast<float*>(ws + L.b_wpart);   // stream-K partial tiles of the weight gradients
 
-    GTK_TRY(flow::squeeze(dz, msq, dZ, nullptr, B, D.Cin, D.Tq * D.n, D.n, 1, st));
-    {   // gradients of the constant logdet terms of every block, one launch (they only need dlogdet and the saved W^-1)
+    if (first) GTK_TRY(flow::squeeze(dz, msq, dZ, nullptr, B, D.Cin, D.Tq * D.n, D.n, 1, st));
+    if (first) {   // gradients of the constant logdet terms of every block, one launch (they only need dlogdet and the saved W^-1)
         static thread_local flow::FlowConstGrads FG;
         for (int k0 = 0; k0 < D.NB; k0 += flow::FLOW_CONST_MAX_BLOCKS) {
             FG.n = min(flow::FLOW_CONST_MAX_BLOCKS, D.NB - k0);
@@ -312,7 +313,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         }
     }
 
-    for (int blk = D.NB - 1; blk >= 0; --blk) {
+    for (int blk = blk_hi; blk >= blk_lo; --blk) {
         const gtk_block_params& P = blocks[blk];
         const gtk_block_grads& G = grads[blk];
         unsigned char* act = ws + L.act + (size_t)blk * L.A.total;
@@ -429,6 +430,6 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         GTK_TRY(flow::mix_bwd(xin_blk, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, dM, dZ, G.an_logs, G.an_bias, G.ic_weight, B,
                               C, T, st));
     }
-    GTK_TRY(flow::unsqueeze(dZ, msq, dx, nullptr, B, C, T, D.n, D.T, st));
+    if (last) GTK_TRY(flow::unsqueeze(dZ, msq, dx, nullptr, B, C, T, D.n, D.T, st));
     return GTK_OK;
 }

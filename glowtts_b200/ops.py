@@ -9,6 +9,7 @@ Ops are registered in the ``glowtts_b200`` namespace (``torch.ops.glowtts_b200.*
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import List, Optional, Sequence, Tuple
 
 import torch
@@ -724,7 +725,12 @@ def _(dz, dlogdet, mask, params, cond, ws, cfg, T, seed=None):
             torch.empty_like(cond) if cond is not None else dz.new_empty(0))
 
 
-_GRAD_SYNC = {"group": None}
+_GRAD_SYNC = {"group": None, "segments": int(os.environ.get("GTK_GRAD_SYNC_SEGMENTS", "3"))}
+
+
+def _world(group) -> int:
+    import torch.distributed as dist
+    return dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
 
 # ---- flat-parameter variant: all decoder parameters live in ONE fp32 buffer (offsets in elements, 16-byte aligned),
 # so autograd moves ONE gradient tensor instead of ~400 and the optimizer / NCCL see a single bucket.
@@ -789,6 +795,48 @@ def _(dz, dlogdet, mask, flat, offsets, cond, ws, cfg, T, seed=None):
             torch.empty_like(cond) if cond is not None else dz.new_empty(0))
 
 
+def decoder_backward_flat_overlapped(dz: Tensor, dlogdet: Tensor, mask: Tensor, flat: Tensor, offsets: List[int],
+                                     cond: Optional[Tensor], ws: Tensor, cfg: List[int], T: int, seed: Optional[Tensor],
+                                     group, n_segments: int = 3) -> Tuple[Tensor, Tensor, Tensor]:
+    """decoder_backward_flat for data-parallel training: the backward is issued as `n_segments` block ranges
+    (gtk_decoder_backward_range) and the flat-gradient slice of each finished range is all-reduced (averaged, as DDP does:
+    train_ms_emo_lang_pitch.py:166) asynchronously while the next range computes; only the last range's collective is
+    exposed.  The slices are contiguous because the flat buffer is laid out block by block."""
+    import torch.distributed as dist
+    dz, dlogdet, mask = _chk(dz, "dz"), _chk(dlogdet, "dlogdet"), _chk(_fit_mask(mask, T), "mask")
+    flat = _chk(flat, "flat")
+    cond = _opt(cond, "cond")
+    B, Cin = dz.shape[0], dz.shape[1]
+    d = _desc(cfg, B, T, seed)
+    dx = torch.empty(B, Cin, T, dtype=dz.dtype, device=dz.device)
+    dflat = torch.zeros_like(flat)
+    dcond = torch.zeros_like(cond) if cond is not None else dz.new_empty(0)
+    blocks = _blocks(cfg, _flat_ptrs(flat, offsets), cond)
+    gblocks = _blocks(cfg, _flat_ptrs(dflat, offsets), dcond if cond is not None else None)
+    nb, ppb = int(cfg[6]), params_per_block(int(cfg[5]), False)
+    sync = group is not None and _world(group) > 1         # group None: segmentation only (tests)
+    world = dist.get_world_size(group) if sync else 1
+    avg = sync and dist.get_backend(group) == "nccl"
+    n_segments = max(1, min(int(n_segments), nb))
+    bounds = [nb * k // n_segments for k in range(n_segments + 1)]          # block index boundaries, ascending
+    works = []
+    for k in range(n_segments - 1, -1, -1):                                   # ranges from the last block down
+        lo, hi = bounds[k], bounds[k + 1] - 1
+        _lib.call("gtk_decoder_backward_range", ctypes.byref(d), blocks, gblocks, _p(mask), _p(dz), _p(dlogdet), _p(dx),
+                  _p(ws), ws.numel(), hi, lo, _stream())
+        if not sync:
+            continue
+        e0 = int(offsets[lo * ppb])
+        e1 = int(offsets[(hi + 1) * ppb]) if hi + 1 < nb else flat.numel()
+        works.append(dist.all_reduce(dflat[e0:e1], op=dist.ReduceOp.AVG if avg else dist.ReduceOp.SUM, group=group,
+                                     async_op=True))
+    for w in works:
+        w.wait()                  # stream-ordered for NCCL: the current stream waits, the host does not
+    if sync and not avg:
+        dflat.div_(world)
+    return dx, dflat, dcond
+
+
 def _decf_setup(ctx, inputs, output):
     x, mask, flat, offsets, cond, cfg, train, seed = inputs
     ctx.set_materialize_grads(False)       # the activation workspace output has no gradient: do not zero-fill GBs for it
@@ -806,21 +854,27 @@ def _decf_bwd(ctx, dz, dlogdet, dws):
         dz = torch.zeros(B, ctx.cfg[0], Tz, dtype=mask.dtype, device=mask.device)
     if dlogdet is None:
         dlogdet = torch.zeros(B, dtype=mask.dtype, device=mask.device)
-    dx, dflat, dcond = decoder_backward_flat(dz.contiguous(), dlogdet.contiguous(), mask, flat, ctx.offsets, cond, ws, ctx.cfg,
-                                             ctx.T, seed)
-    if _GRAD_SYNC["group"] is not None:
-        # data-parallel training (train_ms_emo_lang_pitch.py:166 DDP): ONE all-reduce over the flat gradient buffer
-        from .distributed import sync_flat_grad
-        sync_flat_grad(dflat, _GRAD_SYNC["group"])
+    group = _GRAD_SYNC["group"]
+    if group is not None and _world(group) > 1:
+        # data-parallel training (train_ms_emo_lang_pitch.py:166 DDP): the flat gradient is all-reduced range by range,
+        # overlapped with the rest of the backward
+        dx, dflat, dcond = decoder_backward_flat_overlapped(dz.contiguous(), dlogdet.contiguous(), mask, flat, ctx.offsets, cond,
+                                                            ws, ctx.cfg, ctx.T, seed, group, _GRAD_SYNC["segments"])
+    else:
+        dx, dflat, dcond = decoder_backward_flat(dz.contiguous(), dlogdet.contiguous(), mask, flat, ctx.offsets, cond, ws,
+                                                 ctx.cfg, ctx.T, seed)
     return dx, None, dflat, None, (dcond if ctx.has_cond else None), None, None, None
 
 
 
 
-def set_grad_sync(group) -> None:
+def set_grad_sync(group, segments: Optional[int] = None) -> None:
     """Enable (group = a torch.distributed process group, or dist.group.WORLD) or disable (None) the
-    all-reduce of the decoder's flat gradient buffer inside the backward."""
+    all-reduce of the decoder's flat gradient buffer inside the backward.  `segments` = number of block ranges the
+    backward is split into so that each range's all-reduce overlaps the next range's kernels (default 3)."""
     _GRAD_SYNC["group"] = group
+    if segments is not None:
+        _GRAD_SYNC["segments"] = int(segments)
 
 
 def _dec_setup(ctx, inputs, output):

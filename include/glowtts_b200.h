@@ -282,6 +282,13 @@ int gtk_decoder_reverse(const gtk_decoder_desc* d, const gtk_block_params* block
 int gtk_decoder_backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads,
                          const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace,
                          size_t workspace_bytes, void* stream);
+/* The same backward issued as block ranges blk_hi .. blk_lo (inclusive, descending; first call blk_hi = n_blocks-1,
+ * last call blk_lo = 0, consecutive ranges in between).  The running gradient stays in the workspace between calls, so
+ * the parameter gradients of a finished range are final: data-parallel training all-reduces them (NCCL, DDP at
+ * train_ms_emo_lang_pitch.py:166) while the next range computes. */
+int gtk_decoder_backward_range(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads,
+                               const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace,
+                               size_t workspace_bytes, int blk_hi, int blk_lo, void* stream);
 
 #ifdef __cplusplus
 }

@@ -335,3 +335,33 @@ def test_graphed_reverse_matches_eager_reverse():
         with torch.no_grad():
             want2, _ = dec(y2, mask, g=g, reverse=True)
         assert torch.equal(rev(y2).clone(), want2)
+
+
+@pytest.mark.parametrize("precision,segments", [("bf16", 3), ("bf16", 5), ("fp32", 2)])
+def test_segmented_backward_equals_one_call_backward(precision, segments):
+    """gtk_decoder_backward_range: the backward issued as consecutive block ranges (what the data-parallel path does to
+    overlap the gradient all-reduce) produces the gradients of the single call."""
+    import helpers
+    from glowtts_b200 import models, ops
+    cfg = dict(helpers.TINY_CFG, in_channels=16, n_blocks=5, n_layers=2, hidden_channels=64)
+    sd = helpers.make_state_dict(cfg, 71)
+    dec = models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"], cfg["dilation_rate"],
+                                 cfg["n_blocks"], cfg["n_layers"], n_split=cfg["n_split"], n_sqz=cfg["n_sqz"], precision=precision)
+    dec.load_state_dict(sd, strict=True)
+    dec = dec.cuda().train()
+    y, mask, _, _ = helpers.flow_inputs(cfg, 3, 42, 5, False)
+    y, mask = y.cuda(), mask.cuda()
+    params, folded = dec._params()
+    flat, offsets = dec._ensure_flat(params)
+    mask2 = mask.reshape(mask.shape[0], mask.shape[-1])
+    c = dec._cfg(folded)
+    with torch.no_grad():
+        z, logdet, ws = ops.decoder_forward_flat(y, mask2, flat, offsets, None, c, True, None)
+        gen = torch.Generator(device="cuda").manual_seed(3)
+        dz = torch.randn(z.shape, device="cuda", generator=gen) * mask
+        dld = torch.randn(logdet.shape, device="cuda", generator=gen)
+        dx0, df0, _ = ops.decoder_backward_flat(dz, dld, mask2, flat, offsets, None, ws, c, y.shape[2], None)
+        dx1, df1, _ = ops.decoder_backward_flat_overlapped(dz, dld, mask2, flat, offsets, None, ws, c, y.shape[2], None, None, segments)
+    assert torch.allclose(dx0, dx1, rtol=1e-5, atol=1e-6)
+    assert torch.allclose(df0, df1, rtol=1e-5, atol=1e-6)
+    assert df0.abs().sum().item() > 0
