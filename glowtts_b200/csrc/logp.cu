@@ -6,6 +6,8 @@
 // i.e. one [T_x, 2D] x [2D, T_y] contraction per utterance plus a per-token constant; D = 80, so the
 // kernel is bound by writing the [B,T_x,T_y] fp32 output (4 B/cell).  fp32 FFMA keeps it within fp32
 // rounding of the reference's two matmuls.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "ops.h"
 
@@ -97,10 +99,212 @@ __global__ void __launch_bounds__(NT) logp_kernel(const float* __restrict__ x_m,
     }
 }
 
+// -------------------------------------------------------------------------------------------------
+// Tensor-core logp (D % 8 == 0, D <= 80): the contraction runs on the legacy tensor path as 3xTF32
+// (a_lo b_hi + a_hi b_lo + a_hi b_hi with hi = upper 19 bits, lo = v - hi: fp32-level accuracy), one 64 (text) x 128
+// (frames) output tile per CTA, operands staged ONCE per CTA in shared memory as fp32 [k][x] / [k][y] rows (pitch = 8
+// mod 32: conflict-free fragment reads).  General models contract over 2 D rows ([m s | -0.5 s] x [z ; z^2]);
+// mean_only models (x_logs == NULL, s == 1) over D rows, the z^2 term being the per-frame constant -0.5 sum z^2.
+// The FFMA kernel above is LDS-bound (76 us at B=32, 180 x 860); this one is bound by HMMA issue (8 clk per
+// HMMA.1688.TF32 per SM sub-partition, profiles/micro/hmma_rate.cu) and by writing the 4 B/cell output.
+constexpr int TX = 64, TY = 128, TNT = 256;
+constexpr int AP = TX + 8, BP = TY + 8;         // row pitches (floats)
+constexpr int TC_MAX_D = 80;
+
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t tf32_hi(float v) { return __float_as_uint(v) & 0xffffe000u; }
+__device__ __forceinline__ uint32_t tf32_lo(float v, uint32_t hi) { return __float_as_uint(v - __uint_as_float(hi)); }
+
+template <bool MEAN_ONLY>
+__global__ void __launch_bounds__(TNT, 2) logp_tc_kernel(const float* __restrict__ x_m, const float* __restrict__ x_logs,
+                                                      const float* __restrict__ z, float* __restrict__ out, int D, int T_x,
+                                                      int T_y, int vec4) {
+    extern __shared__ __align__(16) float sm[];
+    const int KT = MEAN_ONLY ? D : 2 * D;
+    float* As = sm;                              // [KT][AP]
+    float* Bs = As + (size_t)KT * AP;            // [KT][BP]
+    float* Cs = Bs + (size_t)KT * BP;            // general: [D][TX] per-(d, x) constants; then crow[TX], zq[TY]
+    float* crow = Cs + (MEAN_ONLY ? 0 : (size_t)D * TX);
+    float* zq = crow + TX;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int y0 = blockIdx.x * TY, x0 = blockIdx.y * TX, b = blockIdx.z;
+    const float* mb = x_m + (size_t)b * D * T_x;
+    const float* lb = MEAN_ONLY ? nullptr : x_logs + (size_t)b * D * T_x;
+    const float* zb = z + (size_t)b * D * T_y;
+
+    auto put_a = [&](int d, int xx, float m, float l, bool ok) {
+        if (MEAN_ONLY) {
+            As[d * AP + xx] = ok ? m : 0.f;
+        } else {
+            const float sc = expf(-2.f * l);
+            As[d * AP + xx] = ok ? m * sc : 0.f;
+            As[(D + d) * AP + xx] = ok ? -0.5f * sc : 0.f;
+            Cs[d * TX + xx] = ok ? (-0.918938533204672742f - l - 0.5f * m * m * sc) : 0.f;
+        }
+    };
+    auto put_b = [&](int d, int yy, float v) {
+        Bs[d * BP + yy] = v;
+        if (!MEAN_ONLY) Bs[(D + d) * BP + yy] = v * v;
+    };
+    if (vec4) {
+        // every operand load of the CTA is in flight before the first shared-memory store: one memory latency per tile
+        constexpr int NA = TC_MAX_D * (TX / 4) / TNT, NB = TC_MAX_D * (TY / 4) / TNT;      // 5, 10 float4 per thread
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 ra[NA], rl[NA], rb[NB];
+#pragma unroll
+        for (int i = 0; i < NA; ++i) {
+            const int e = tid + i * TNT, d = e / (TX / 4), xx = (e % (TX / 4)) * 4;
+            ra[i] = z4; rl[i] = z4;
+            if (d < D && x0 + xx < T_x) {
+                ra[i] = __ldg(reinterpret_cast<const float4*>(mb + (size_t)d * T_x + x0 + xx));
+                if (!MEAN_ONLY) rl[i] = __ldg(reinterpret_cast<const float4*>(lb + (size_t)d * T_x + x0 + xx));
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < NB; ++i) {
+            const int e = tid + i * TNT, d = e / (TY / 4), yy = (e % (TY / 4)) * 4;
+            rb[i] = z4;
+            if (d < D && y0 + yy < T_y) rb[i] = __ldg(reinterpret_cast<const float4*>(zb + (size_t)d * T_y + y0 + yy));
+        }
+#pragma unroll
+        for (int i = 0; i < NA; ++i) {
+            const int e = tid + i * TNT, d = e / (TX / 4), xx = (e % (TX / 4)) * 4;
+            if (d < D) {
+                const bool ok = x0 + xx < T_x;
+                put_a(d, xx, ra[i].x, rl[i].x, ok); put_a(d, xx + 1, ra[i].y, rl[i].y, ok);
+                put_a(d, xx + 2, ra[i].z, rl[i].z, ok); put_a(d, xx + 3, ra[i].w, rl[i].w, ok);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < NB; ++i) {
+            const int e = tid + i * TNT, d = e / (TY / 4), yy = (e % (TY / 4)) * 4;
+            if (d < D) { put_b(d, yy, rb[i].x); put_b(d, yy + 1, rb[i].y); put_b(d, yy + 2, rb[i].z); put_b(d, yy + 3, rb[i].w); }
+        }
+    } else {
+        for (int e = tid; e < D * TX; e += TNT) {
+            const int d = e / TX, xx = e - d * TX;
+            const bool ok = x0 + xx < T_x;
+            const float m = ok ? mb[(size_t)d * T_x + x0 + xx] : 0.f;
+            const float l = (ok && !MEAN_ONLY) ? lb[(size_t)d * T_x + x0 + xx] : 0.f;
+            put_a(d, xx, m, l, ok);
+        }
+        for (int e = tid; e < D * TY; e += TNT) {
+            const int d = e / TY, yy = e - d * TY;
+            put_b(d, yy, (y0 + yy < T_y) ? zb[(size_t)d * T_y + y0 + yy] : 0.f);
+        }
+    }
+    __syncthreads();
+    if (tid < TX) {                              // per-token constant, summed over d in a fixed order
+        float c = 0.f;
+        if (MEAN_ONLY) {
+            for (int d = 0; d < D; ++d) { const float m = As[d * AP + tid]; c = fmaf(m, m, c); }
+            c = -0.5f * c - (float)D * 0.918938533204672742f;
+        } else {
+            for (int d = 0; d < D; ++d) c += Cs[d * TX + tid];
+        }
+        crow[tid] = c;
+    } else if (tid >= 128) {                     // per-frame constant (mean_only): -0.5 sum_d z^2
+        const int yy = tid - 128;
+        float q = 0.f;
+        if (MEAN_ONLY)
+            for (int d = 0; d < D; ++d) { const float v = Bs[d * BP + yy]; q = fmaf(v, v, q); }
+        zq[yy] = -0.5f * q;
+    }
+
+    // warp tile: 32 text rows x 32 frames = 2 x 4 m16n8k8 blocks
+    const int g = lane >> 2, t = lane & 3;
+    const int wx = (warp & 1) * 32, wy = (warp >> 1) * 32;
+    float acc[2][4][4];
+#pragma unroll
+    for (int mb2 = 0; mb2 < 2; ++mb2)
+#pragma unroll
+        for (int nb = 0; nb < 4; ++nb)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[mb2][nb][i] = 0.f;
+    for (int k0 = 0; k0 < KT; k0 += 8) {
+        uint32_t ah[2][4], al[2][4], bh[4][2], bl[4][2];
+#pragma unroll
+        for (int mb2 = 0; mb2 < 2; ++mb2) {
+            const float* ap = As + (size_t)(k0 + t) * AP + wx + 16 * mb2 + g;     // a0 (g, t) a1 (g+8, t) a2 (g, t+4) a3 (g+8, t+4)
+            const float a0 = ap[0], a1 = ap[8], a2 = ap[4 * AP], a3 = ap[4 * AP + 8];
+            ah[mb2][0] = tf32_hi(a0); al[mb2][0] = tf32_lo(a0, ah[mb2][0]);
+            ah[mb2][1] = tf32_hi(a1); al[mb2][1] = tf32_lo(a1, ah[mb2][1]);
+            ah[mb2][2] = tf32_hi(a2); al[mb2][2] = tf32_lo(a2, ah[mb2][2]);
+            ah[mb2][3] = tf32_hi(a3); al[mb2][3] = tf32_lo(a3, ah[mb2][3]);
+        }
+#pragma unroll
+        for (int nb = 0; nb < 4; ++nb) {
+            const float* bp = Bs + (size_t)(k0 + t) * BP + wy + 8 * nb + g;        // b0 (k = t, n = g) b1 (k = t+4, n = g)
+            const float b0 = bp[0], b1 = bp[4 * BP];
+            bh[nb][0] = tf32_hi(b0); bl[nb][0] = tf32_lo(b0, bh[nb][0]);
+            bh[nb][1] = tf32_hi(b1); bl[nb][1] = tf32_lo(b1, bh[nb][1]);
+        }
+#pragma unroll
+        for (int mb2 = 0; mb2 < 2; ++mb2)
+#pragma unroll
+            for (int nb = 0; nb < 4; ++nb) mma_tf32(acc[mb2][nb], al[mb2], bh[nb][0], bh[nb][1]);
+#pragma unroll
+        for (int mb2 = 0; mb2 < 2; ++mb2)
+#pragma unroll
+            for (int nb = 0; nb < 4; ++nb) mma_tf32(acc[mb2][nb], ah[mb2], bl[nb][0], bl[nb][1]);
+#pragma unroll
+        for (int mb2 = 0; mb2 < 2; ++mb2)
+#pragma unroll
+            for (int nb = 0; nb < 4; ++nb) mma_tf32(acc[mb2][nb], ah[mb2], bh[nb][0], bh[nb][1]);
+    }
+    __syncthreads();                             // crow / zq
+    const bool pair_ok = (T_y & 1) == 0;         // (x T_y + y) even for even y: 8-byte aligned float2 stores
+#pragma unroll
+    for (int mb2 = 0; mb2 < 2; ++mb2)
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const int xx = wx + 16 * mb2 + g + 8 * half, x = x0 + xx;
+            if (x >= T_x) continue;
+            const float c = crow[xx];
+            float* orow = out + ((size_t)b * T_x + x) * T_y;
+#pragma unroll
+            for (int nb = 0; nb < 4; ++nb) {
+                const int yy = wy + 8 * nb + 2 * t, y = y0 + yy;
+                const float v0 = acc[mb2][nb][2 * half] + (c + zq[yy]);
+                const float v1 = acc[mb2][nb][2 * half + 1] + (c + zq[yy + 1]);
+                if (pair_ok && y + 1 < T_y) *reinterpret_cast<float2*>(orow + y) = make_float2(v0, v1);
+                else {
+                    if (y < T_y) orow[y] = v0;
+                    if (y + 1 < T_y) orow[y + 1] = v1;
+                }
+            }
+        }
+}
+
+static size_t logp_tc_smem(int D, bool mean_only) {
+    const int KT = mean_only ? D : 2 * D;
+    return sizeof(float) * ((size_t)KT * AP + (size_t)KT * BP + (mean_only ? 0 : (size_t)D * TX) + TX + TY);
+}
+
 int forward(const float* x_m, const float* x_logs, const float* z, float* out, int B, int D, int T_x, int T_y,
             cudaStream_t st) {
     GTK_REQUIRE(x_m && z && out, "null");
     if ((long long)B * T_x * T_y == 0) return GTK_OK;
+    if (D % 8 == 0 && D >= 8 && D <= TC_MAX_D && !getenv("GTK_LOGP_FFMA")) {
+        const bool mo = x_logs == nullptr;
+        const size_t smem = logp_tc_smem(D, mo);
+        const int vec4 = ((T_x | T_y) & 3) == 0 &&
+                         ((reinterpret_cast<uintptr_t>(x_m) | reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(x_logs)) & 15) == 0;
+        dim3 grid(ceil_div(T_y, TY), ceil_div(T_x, TX), B);
+        ProfScope prof("logp", st);
+        if (mo) {
+            GTK_CUDA(cudaFuncSetAttribute(logp_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            logp_tc_kernel<true><<<grid, TNT, smem, st>>>(x_m, x_logs, z, out, D, T_x, T_y, vec4);
+        } else {
+            GTK_CUDA(cudaFuncSetAttribute(logp_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            logp_tc_kernel<false><<<grid, TNT, smem, st>>>(x_m, x_logs, z, out, D, T_x, T_y, vec4);
+        }
+        return check_launch("logp_tc");
+    }
     dim3 grid(ceil_div(T_y, BY), ceil_div(T_x, BX), B);
     ProfScope prof("logp", st);
     if (x_logs) logp_kernel<false><<<grid, NT, 0, st>>>(x_m, x_logs, z, out, D, T_x, T_y);
