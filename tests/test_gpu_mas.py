@@ -187,7 +187,7 @@ def test_fused_logp_mas_agrees_with_logp_then_mas(B, TX, TY):
     x_m, z, t_xs, t_ys = _fused_case(B, TX, TY, 100 + TX)
     assert ops.mas_fused_supported(80, TX, TY, False)
     path, dur, idx, lp = monotonic_align.maximum_path_from_prior(z.cuda(), x_m.cuda(), None, t_xs.cuda(), t_ys.cuda(),
-                                                                 return_logp=True)
+                                                                 return_logp=True, fused=True)
     torch.cuda.synchronize()
     path, dur, idx, lp = path.cpu().numpy(), dur.cpu().numpy(), idx.cpu().numpy(), lp.cpu().numpy()
     want_lp = oflow.logp(x_m, torch.zeros_like(x_m), z).numpy()
