@@ -103,12 +103,39 @@ class GraphedTrainStep:
         return out
 
     def step(self, batch=None) -> torch.Tensor:
-        """Copy `batch` (same shapes as the example) into the static buffers, replay, return the (static) loss tensor."""
+        """Copy `batch` (same shapes as the example) into the static buffers, replay, return the (static) loss tensor.
+        With batch=None the step consumes the batch staged by prefetch(), if any, else re-runs the resident inputs."""
         if batch is not None:
             for dst, src in zip(self.static, batch):
                 dst.copy_(src, non_blocking=True)
+        elif self._staged:
+            cur = torch.cuda.current_stream()
+            cur.wait_event(self._staged_ready)             # the H2D copies of this batch (copy stream) have landed
+            for dst, src in zip(self.static, self._stage):
+                dst.copy_(src, non_blocking=True)          # device -> device, ~10 MB: microseconds
+            self._stage_free.record(cur)
+            self._staged = False
         self.graph.replay()
         return self.out.loss
+
+    _staged = False
+
+    def prefetch(self, batch) -> None:
+        """Input pipeline: start the host -> device copy of the NEXT batch (pinned host tensors) on a copy stream into
+        staging buffers, so that it overlaps the step that is running; the next step() consumes it.  This is the
+        double buffering a DataLoader with pin_memory + non_blocking gives the reference (data_utils.py / train loop)."""
+        if not hasattr(self, "_stage"):
+            self._stage = [torch.empty_like(t) for t in self.static]
+            self._copy_stream = torch.cuda.Stream(device=self.static[0].device)
+            self._staged_ready = torch.cuda.Event()
+            self._stage_free = torch.cuda.Event()
+            self._stage_free.record(torch.cuda.current_stream())
+        self._copy_stream.wait_event(self._stage_free)     # the previous staged batch has been consumed
+        with torch.cuda.stream(self._copy_stream):
+            for dst, src in zip(self._stage, batch):
+                dst.copy_(src, non_blocking=True)
+            self._staged_ready.record(self._copy_stream)
+        self._staged = True
 
 
 class GraphedReverse:

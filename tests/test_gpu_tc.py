@@ -365,3 +365,41 @@ def test_segmented_backward_equals_one_call_backward(precision, segments):
     assert torch.allclose(dx0, dx1, rtol=1e-5, atol=1e-6)
     assert torch.allclose(df0, df1, rtol=1e-5, atol=1e-6)
     assert df0.abs().sum().item() > 0
+
+
+def test_graphed_step_prefetch_feeds_the_same_batches():
+    """GraphedTrainStep.prefetch (copy-stream double buffering of the pinned host batch) == step(batch)."""
+    import helpers
+    from glowtts_b200 import models
+    from glowtts_b200.hot_path import GraphedTrainStep
+    cfg = dict(helpers.TINY_CFG, in_channels=16, n_blocks=2, n_layers=2, hidden_channels=64)
+    sd = helpers.make_state_dict(cfg, 81)
+    gen = torch.Generator().manual_seed(4)
+    batches = []
+    for _ in range(3):
+        y = torch.randn(3, 16, 40, generator=gen)
+        batches.append([y.pin_memory(), torch.tensor([40, 22, 30]).pin_memory(),
+                        (torch.randn(3, 16, 20, generator=gen) * 0.5).pin_memory(), torch.tensor([20, 11, 15]).pin_memory()])
+    losses = []
+    for mode in ("direct", "prefetch"):
+        dec = models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"], cfg["dilation_rate"],
+                                     cfg["n_blocks"], cfg["n_layers"], n_split=cfg["n_split"], n_sqz=cfg["n_sqz"], precision="bf16")
+        dec.load_state_dict(sd, strict=True)
+        dec = dec.cuda().train()
+        opt = torch.optim.AdamW(dec.flat_parameters(), lr=1e-3, fused=True, capturable=True)
+        st = GraphedTrainStep(dec, opt, [t.cuda() for t in batches[0]], warmup=1)
+        ls = []
+        if mode == "direct":
+            for bt in batches:
+                ls.append(st.step(bt).item())
+        else:
+            st.prefetch(batches[0])
+            for i in range(3):
+                loss = st.step()
+                if i + 1 < 3:
+                    st.prefetch(batches[i + 1])
+                ls.append(loss.item())
+        losses.append(ls)
+    # same batches in the same order -> same losses up to the atomics' summation order in the backward
+    assert all(abs(a - b) < 2e-4 * max(1.0, abs(a)) for a, b in zip(*losses)), losses
+    assert abs(losses[0][0] - losses[0][1]) > 1e-3, losses      # the batches do differ: a stale buffer would show
