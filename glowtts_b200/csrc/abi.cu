@@ -1,4 +1,5 @@
 // glowtts_b200/csrc/abi.cu -- the extern "C" surface declared in include/glowtts_b200.h.
+#include <stdlib.h>
 #include <stdarg.h>
 #include <string.h>
 
@@ -14,6 +15,15 @@
 namespace gtk {
 
 static thread_local char g_err[512] = "";
+
+bool pdl_enabled() {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("GTK_PDL");
+        on = (e && e[0] == '0') ? 0 : 1;
+    }
+    return on == 1;
+}
 
 void set_error(const char* fmt, ...) {
     va_list ap;

@@ -4,6 +4,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 
 #define GTK_OK 0
 #define GTK_ERR_INVALID (-1)      // bad argument (null pointer, negative size, unsupported shape)
@@ -55,6 +56,30 @@ inline int check_launch(const char* what) {
     } while (0)
 
 int sm_count();   // cached multiprocessor count of the current device
+
+// Programmatic dependent launch (PDL).  The decoder step is ~250 dependent launches of 5-30 us; launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization a kernel's CTAs may become resident -- and run their preamble
+// (mbarrier init, TMEM allocation, constant staging) -- while the previous kernel drains, instead of after a full
+// grid drain + launch latency.  Protocol: every PDL kernel executes pdl_trigger() on entry (lets ITS successor
+// start early) and pdl_wait() before its first access to memory an earlier kernel of the stream may have written
+// (griddepcontrol.wait returns once the predecessor grid has completed and flushed).  Nothing before pdl_wait() may
+// write global memory.  GTK_PDL=0 disables the attribute (the instructions are then no-ops).
+bool pdl_enabled();
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
 
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 __host__ __device__ inline long long ceil_div_ll(long long a, long long b) { return (a + b - 1) / b; }

@@ -100,6 +100,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int t0 = blockIdx.x * BT, b = blockIdx.y;
     int out_chunks = 0;                                  // staged [128 x 64] bf16 output tiles to TMA-store at the end
+    pdl_trigger();
     CONV_TRACE(0);
     const int n_iter = p.taps * p.n_k;
     const bool dual = (p.NCH == 1);                      // two interleaved accumulators (see the MMA loop)
@@ -116,6 +117,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if constexpr (CL > 1) cluster_sync_all();             // the peer's barriers exist before anything is multicast
     else __syncthreads();
     tc_fence_after();
+    pdl_wait();                                          // the previous kernel's outputs are complete and visible
     const uint32_t tmem = ctl->tmem_base;
     CONV_TRACE(1);
 
@@ -481,6 +483,8 @@ __global__ void affine_bwd_frames_kernel(const float* __restrict__ x, const floa
                                          const float* __restrict__ dlogdet, __nv_bfloat16* __restrict__ dend, int ld,
                                          float* __restrict__ dx, int B, int C, int T, int sigmoid_scale) {
     const int Ch = C / 2;
+    pdl_trigger();
+    pdl_wait();
     const int n_chunk = (Ch + 7) / 8, n_pad = (ld - C + 7) / 8;      // channel chunks + zero-padding chunks
     const long long frames = (long long)B * T, total = frames * (n_chunk + n_pad);
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -561,8 +565,8 @@ int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, 
     GTK_REQUIRE(x && logs_raw && dz && dend && dx && C % 2 == 0 && ld >= C, "bad args");
     const long long total = (long long)B * T * ((C / 2 + 7) / 8 + (ld - C + 7) / 8);
     if (total == 0) return GTK_OK;
-    affine_bwd_frames_kernel<<<(int)ceil_div_ll(total, 128), 128, 0, st>>>(x, logs_raw, mask, dz, dlogdet, dend, ld, dx, B, C, T,
-                                                                           sigmoid_scale);
+    GTK_CUDA(launch_pdl(affine_bwd_frames_kernel, dim3((unsigned)ceil_div_ll(total, 128)), dim3(128), 0, st, x, logs_raw, mask, dz,
+                        dlogdet, dend, ld, dx, B, C, T, sigmoid_scale));
     return check_launch("affine_bwd_frames");
 }
 
@@ -631,17 +635,19 @@ int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, 
 #define GTK_TC_LAUNCH(COLS, E)                                                                                       \
     do {                                                                                                             \
         GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<COLS, E, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        conv_tc_kernel<COLS, E, 1><<<grid, EPI_NT, smem, st>>>(tmA, tmB, tmO, p);                                  \
+        GTK_CUDA(launch_pdl(conv_tc_kernel<COLS, E, 1>, grid, dim3(EPI_NT), smem, st, tmA, tmB, tmO, p));          \
     } while (0)
     if (epi == EPI_PLAIN && p.cluster == 2) {
         GTK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<256, EPI_PLAIN, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof(cfg));
         cfg.gridDim = grid; cfg.blockDim = dim3(EPI_NT); cfg.dynamicSmemBytes = smem; cfg.stream = st;
-        cudaLaunchAttribute attr[1];
+        cudaLaunchAttribute attr[2];
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr; cfg.numAttrs = 1;
+        attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+        cfg.attrs = attr; cfg.numAttrs = 2;
         GTK_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<256, EPI_PLAIN, 2>, tmA, tmB, tmO, p));
     }
     else if (epi == EPI_PLAIN) { if (p.N > 256) GTK_TC_LAUNCH(512, EPI_PLAIN); else GTK_TC_LAUNCH(256, EPI_PLAIN); }

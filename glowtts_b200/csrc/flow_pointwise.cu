@@ -202,6 +202,8 @@ __global__ void mix_kernel(const float* __restrict__ x, const float* __restrict_
                            const float* __restrict__ bias, const float* __restrict__ M, float* __restrict__ z, int B,
                            int C, int T) {
     __shared__ float sM[NS * NS];
+    pdl_trigger();
+    pdl_wait();
     if (threadIdx.x < NS * NS) sM[threadIdx.x] = M ? M[threadIdx.x] : ((threadIdx.x / NS == threadIdx.x % NS) ? 1.f : 0.f);
     __syncthreads();
     const int G = C / NS;
@@ -238,8 +240,8 @@ static int mix_launch(const float* x, const float* mask, const float* logs, cons
                       int B, int C, int T, int reverse, cudaStream_t st) {
     const long long total = (long long)B * (C / NS) * T;
     if (total == 0) return GTK_OK;
-    if (reverse) mix_kernel<NS, true><<<pw_grid(total), PW_NT, 0, st>>>(x, mask, logs, bias, M, z, B, C, T);
-    else         mix_kernel<NS, false><<<pw_grid(total), PW_NT, 0, st>>>(x, mask, logs, bias, M, z, B, C, T);
+    if (reverse) GTK_CUDA(launch_pdl(mix_kernel<NS, true>, dim3(pw_grid(total)), dim3(PW_NT), 0, st, x, mask, logs, bias, M, z, B, C, T));
+    else         GTK_CUDA(launch_pdl(mix_kernel<NS, false>, dim3(pw_grid(total)), dim3(PW_NT), 0, st, x, mask, logs, bias, M, z, B, C, T));
     return check_launch("mix");
 }
 
@@ -267,6 +269,8 @@ __global__ void mix_bwd_kernel(const float* __restrict__ x, const float* __restr
                                int T) {
     __shared__ float sM[NS * NS];
     __shared__ float red[(2 * NS + NS * NS) * (PW_NT / 32)];
+    pdl_trigger();
+    pdl_wait();
     if (threadIdx.x < NS * NS) sM[threadIdx.x] = M ? M[threadIdx.x] : ((threadIdx.x / NS == threadIdx.x % NS) ? 1.f : 0.f);
     __syncthreads();
     const int g = blockIdx.y;
@@ -348,10 +352,10 @@ int mix_bwd(const float* x, const float* mask, const float* logs, const float* b
     if (gx < 1) gx = 1;
     dim3 grid(gx, G);
     switch (ns) {
-        case 1: mix_bwd_kernel<1><<<grid, PW_NT, 0, st>>>(x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T); break;
-        case 2: mix_bwd_kernel<2><<<grid, PW_NT, 0, st>>>(x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T); break;
-        case 4: mix_bwd_kernel<4><<<grid, PW_NT, 0, st>>>(x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T); break;
-        default: mix_bwd_kernel<8><<<grid, PW_NT, 0, st>>>(x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T); break;
+        case 1: GTK_CUDA(launch_pdl(mix_bwd_kernel<1>, grid, dim3(PW_NT), 0, st, x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T)); break;
+        case 2: GTK_CUDA(launch_pdl(mix_bwd_kernel<2>, grid, dim3(PW_NT), 0, st, x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T)); break;
+        case 4: GTK_CUDA(launch_pdl(mix_bwd_kernel<4>, grid, dim3(PW_NT), 0, st, x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T)); break;
+        default: GTK_CUDA(launch_pdl(mix_bwd_kernel<8>, grid, dim3(PW_NT), 0, st, x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T)); break;
     }
     return check_launch("mix_bwd");
 }

@@ -57,6 +57,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
     GgCtl* ctl = reinterpret_cast<GgCtl*>(smem + (size_t)GG_STAGES * GG_STAGE_BYTES);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const GgCta me = p.cta[blockIdx.x];
+    pdl_trigger();
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < GG_STAGES; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
@@ -75,6 +76,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    pdl_wait();                                          // dY / X of the data-gradient chain are complete and visible
     const uint32_t tmem = ctl->tmem_base;
 
     if (warp == 0) {
@@ -192,6 +194,8 @@ constexpr int GG_RED_NT = 256;
 __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __grid_constant__ GgRedParams p) {
     extern __shared__ float row[];                 // [Cin * taps] reduced dW row, torch order (c, j)
     __shared__ float red[2][GG_RED_NT / 32];
+    pdl_trigger();
+    pdl_wait();                                    // the stream-K partial tiles are complete and visible
     int q = 0;
     while (q + 1 < p.n_jobs && (int)blockIdx.x >= p.job[q + 1].row0) ++q;
     const GgRedJob& J = p.job[q];
@@ -348,13 +352,13 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     GTK_CUDA(cudaFuncSetAttribute(wgrad_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     {
         ProfScope prof("wgrad_group", st);
-        wgrad_group_kernel<<<G, NTHREADS, smem, st>>>(P);
+        GTK_CUDA(launch_pdl(wgrad_group_kernel, dim3(G), dim3(NTHREADS), smem, st, P));
         int rc = check_launch("wgrad_group");
         if (rc) return rc;
     }
     {
         ProfScope prof("wgrad_group_reduce", st);
-        wgrad_group_reduce_kernel<<<rows, GG_RED_NT, max_row, st>>>(R);
+        GTK_CUDA(launch_pdl(wgrad_group_reduce_kernel, dim3(rows), dim3(GG_RED_NT), (size_t)max_row, st, R));
         int rc = check_launch("wgrad_group_reduce");
         if (rc) return rc;
     }

@@ -73,6 +73,7 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
     const int halo = (p.taps / 2) * p.dil, tile_out = BT - 2 * halo;
     const int t0 = blockIdx.x * tile_out, b = blockIdx.y;
     const int n_b = p.taps * nkb;
+    pdl_trigger();
     WB_TRACE(0);
 
     const uint32_t cta_rank = cluster_ctarank();
@@ -90,6 +91,7 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
     tc_fence_before();
     cluster_sync_all();                                        // the peer's barriers exist before anything is multicast
     tc_fence_after();
+    pdl_wait();                                                // the previous kernel's gradients are complete and visible
     const uint32_t tmem = ctl->tmem_base;
     const uint32_t idesc = umma_idesc_bf16(BT, H);
     WB_TRACE(1);
@@ -325,10 +327,12 @@ int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat1
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = grid; cfg.blockDim = dim3(EPI_NT); cfg.dynamicSmemBytes = smem; cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = WB_CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = 2;
     GTK_CUDA(cudaLaunchKernelEx(&cfg, wn_bwd_layer_kernel, tmDrs, tmWrs, tmWin, tmDxin, tmOut, p));
     return check_launch("wn_bwd_layer_tc");
 }

@@ -56,6 +56,7 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int t0 = blockIdx.x * BT, b = blockIdx.y;
+    pdl_trigger();
     WN_TRACE(0);
     const int n1 = p.taps * n_kh;                       // GEMM-1 iterations
     const int n_all = n1 + n_kh;                        // + GEMM-2 iterations
@@ -78,6 +79,7 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    pdl_wait();                                          // the previous kernel's h / skip are complete and visible
     const uint32_t tmem = ctl->tmem_base;
     const uint32_t idesc = umma_idesc_bf16(BT, H);
     WN_TRACE(1);
@@ -336,7 +338,7 @@ int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, con
     GTK_CUDA(cudaFuncSetAttribute(wn_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(ceil_div(p.T, BT), p.B);
     ProfScope prof("wn_layer_tc", st);
-    wn_layer_kernel<<<grid, EPI_NT, smem, st>>>(tmH, tmWin, tmWrs, tmActs, tmOut, p);
+    GTK_CUDA(launch_pdl(wn_layer_kernel, grid, dim3(EPI_NT), smem, st, tmH, tmWin, tmWrs, tmActs, tmOut, p));
     return check_launch("wn_layer_tc");
 }
 
