@@ -117,7 +117,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if constexpr (CL > 1) cluster_sync_all();             // the peer's barriers exist before anything is multicast
     else __syncthreads();
     tc_fence_after();
-    pdl_wait();                                          // the previous kernel's outputs are complete and visible
+    // PDL: the producer thread requests the weight tiles of its first stages before pdl_wait() (see wn_tc.cu)
+    const bool is_producer = (warp == 0 && lane == 0);
+    if (!is_producer) pdl_wait();
     const uint32_t tmem = ctl->tmem_base;
     CONV_TRACE(1);
 
@@ -126,18 +128,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tma_prefetch_desc(&tmA);
             tma_prefetch_desc(&tmB);
             long long w_empty = 0;
-            for (int it = 0; it < n_iter; ++it) {
-                const int s = it % p.stages, use = it / p.stages;
-                if (use > 0) {
-                    const long long c0 = p.trace ? clock64() : 0;
-                    mbar_wait(&ctl->empty[s], (use - 1) & 1);
-                    if (p.trace) w_empty += clock64() - c0;
-                }
-                const int j = it / p.n_k, kc = it % p.n_k;
-                unsigned char* sa = smem + (size_t)s * stage_bytes;
-                unsigned char* sb = sa + A_BYTES;
+            auto load_weights = [&](int s, int j, int kc) {
+                unsigned char* sb = smem + (size_t)s * stage_bytes + A_BYTES;
                 mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)stage_bytes);
-                tma_load_3d(sa, &tmA, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
                 if constexpr (CL > 1) {
                     const int rows = p.NW / CL;            // this CTA's share of the weight rows, delivered to the whole cluster
                     for (int ch = 0; ch < p.NCH; ++ch)
@@ -147,6 +140,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     for (int ch = 0; ch < p.NCH; ++ch)
                         tma_load_3d(sb + (size_t)ch * p.NW * KC * 2, &tmB, &ctl->full[s], kc * KC, ch * p.NW, j);
                 }
+            };
+            const int n_pre = min(p.stages, n_iter);
+            for (int it = 0; it < n_pre; ++it) load_weights(it, it / p.n_k, it % p.n_k);
+            pdl_wait();
+            for (int it = 0; it < n_iter; ++it) {
+                const int s = it % p.stages, use = it / p.stages;
+                if (use > 0) {
+                    const long long c0 = p.trace ? clock64() : 0;
+                    mbar_wait(&ctl->empty[s], (use - 1) & 1);
+                    if (p.trace) w_empty += clock64() - c0;
+                }
+                const int j = it / p.n_k, kc = it % p.n_k;
+                unsigned char* sa = smem + (size_t)s * stage_bytes;
+                if (it >= n_pre) load_weights(s, j, kc);
+                tma_load_3d(sa, &tmA, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
             }
             if (p.trace) { const int cta_ = blockIdx.y * gridDim.x + blockIdx.x; if (cta_ < CONV_TRACE_CTAS) g_conv_wait[cta_ * 2] = w_empty; }
         }

@@ -91,7 +91,9 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
     tc_fence_before();
     cluster_sync_all();                                        // the peer's barriers exist before anything is multicast
     tc_fence_after();
-    pdl_wait();                                                // the previous kernel's gradients are complete and visible
+    // PDL: the producer thread requests the res_skip weight tiles of its first stages before pdl_wait() (see wn_tc.cu)
+    const bool is_producer = (warp == 0 && lane == 0);
+    if (!is_producer) pdl_wait();
     const uint32_t tmem = ctl->tmem_base;
     const uint32_t idesc = umma_idesc_bf16(BT, H);
     WB_TRACE(1);
@@ -101,13 +103,21 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
         tma_prefetch_desc(&tmDrs);
         tma_prefetch_desc(&tmWrs);
         tma_prefetch_desc(&tmWin);
+        const int n_pre = min(n_sa, nka);
+        for (int kc = 0; kc < n_pre; ++kc) {
+            mbar_arrive_expect_tx(&ctl->full[kc], (uint32_t)sa_bytes);
+            tma_load_2d(ring + (size_t)kc * sa_bytes + A_BYTES, &tmWrs, &ctl->full[kc], kc * KC, 0);
+        }
+        pdl_wait();
         for (int kc = 0; kc < nka; ++kc) {
             const int s = kc % n_sa, use = kc / n_sa;
             if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
             unsigned char* sa = ring + (size_t)s * sa_bytes;
-            mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)sa_bytes);
+            if (kc >= n_pre) {
+                mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)sa_bytes);
+                tma_load_2d(sa + A_BYTES, &tmWrs, &ctl->full[s], kc * KC, 0);
+            }
             tma_load_3d(sa, &tmDrs, &ctl->full[s], kc * KC, t0 - halo, b);
-            tma_load_2d(sa + A_BYTES, &tmWrs, &ctl->full[s], kc * KC, 0);
         }
         // The ring is re-cut into weight-only stages for GEMM b.  Each CTA of the pair fetches half of the rows of every
         // weight tile and the TMA multicasts them into both shared memories; a stage may be written once BOTH CTAs have

@@ -79,7 +79,11 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    pdl_wait();                                          // the previous kernel's h / skip are complete and visible
+    // PDL: everything the previous kernel of the stream wrote (h, skip) may be touched only after pdl_wait().  The TMA
+    // producer thread first requests the WEIGHT tiles of its first stages (packed long before the previous kernel
+    // started), so they are in flight while the previous kernel drains, and waits afterwards.
+    const bool is_producer = (warp == 0 && lane == 0);
+    if (!is_producer) pdl_wait();
     const uint32_t tmem = ctl->tmem_base;
     const uint32_t idesc = umma_idesc_bf16(BT, H);
     WN_TRACE(1);
@@ -89,6 +93,15 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
         tma_prefetch_desc(&tmH);
         tma_prefetch_desc(&tmWin);
         tma_prefetch_desc(&tmWrs);
+        const int n_pre = min(WN_STAGES, n1);
+        for (int it = 0; it < n_pre; ++it) {             // weights of the first stages: independent of the previous kernel
+            unsigned char* sb = smem + (size_t)it * stage_bytes + A_BYTES;
+            const int j = it / n_kh, kc = it % n_kh;
+            mbar_arrive_expect_tx(&ctl->full[it], (uint32_t)(A_BYTES + H2 * KC * 2));
+            tma_load_3d(sb, &tmWin, &ctl->full[it], kc * KC, 0, j);
+            tma_load_3d(sb + (size_t)H * KC * 2, &tmWin, &ctl->full[it], kc * KC, H, j);
+        }
+        pdl_wait();
         for (int it = 0; it < n_all; ++it) {
             const int s = it % WN_STAGES, use = it / WN_STAGES;
             if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
@@ -96,10 +109,12 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
             unsigned char* sb = sa + A_BYTES;
             if (it < n1) {
                 const int j = it / n_kh, kc = it % n_kh;
-                mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(A_BYTES + H2 * KC * 2));
+                if (it >= n_pre) {
+                    mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(A_BYTES + H2 * KC * 2));
+                    tma_load_3d(sb, &tmWin, &ctl->full[s], kc * KC, 0, j);
+                    tma_load_3d(sb + (size_t)H * KC * 2, &tmWin, &ctl->full[s], kc * KC, H, j);
+                }
                 tma_load_3d(sa, &tmH, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
-                tma_load_3d(sb, &tmWin, &ctl->full[s], kc * KC, 0, j);
-                tma_load_3d(sb + (size_t)H * KC * 2, &tmWin, &ctl->full[s], kc * KC, H, j);
             } else {
                 const int kc = it - n1;                 // the A slot of this stage is written by epilogue 1
                 mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(RS * KC * 2));
