@@ -404,69 +404,82 @@ int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, 
 // ---------------------------------------------------------------------------------- fold + pack, one launch per block
 // Every conv weight of the decoder: weight-norm fold (w = g v / ||v||, modules.py:124,131,141) and bf16 packing into the
 // forward ([j][m][c]) and data-gradient ([j][c][m], taps flipped) operand layouts, zero padding included, in ONE launch.
-// One CTA per (weight, group of 32 output rows m): row norms first, then 64-channel slabs of the 32 rows go through
-// shared memory so that both layouts are written with contiguous runs (c fastest for fwd, m fastest for tr).
-constexpr int FP_ROWS = 32, FP_CH = 64, FP_NT = 256;
+// One CTA per (weight, group of FP_ROWS output rows m).  The CTA's rows are read from HBM ONCE into shared memory (each
+// warp streams whole rows, 8 independent loads in flight per lane, and reduces the row's sum of squares on the way), then
+// both operand layouts are written from shared memory as bf16 pairs with the row scale applied at the store: contiguous
+// 128-byte runs for fwd (c fastest), 32-byte runs for tr (m fastest).  No per-element integer division.
+constexpr int FP_ROWS = 16, FP_NT = 256;
 __global__ void __launch_bounds__(FP_NT) fold_pack_kernel(const __grid_constant__ FoldPackJobs jobs) {
-    extern __shared__ float fp_tile[];               // [FP_ROWS][FP_CH * K + 1]
+    extern __shared__ float fp_tile[];               // [FP_ROWS][Cin * K + 1]
     __shared__ float sc_sm[FP_ROWS];
     int grp = blockIdx.x, w = 0;
     while (w < jobs.n && grp >= jobs.job[w].groups) { grp -= jobs.job[w].groups; ++w; }
     if (w >= jobs.n) return;
     const FoldPackJob& J = jobs.job[w];
-    const int K = J.K, Cin = J.Cin, R = Cin * K, m0 = grp * FP_ROWS;
+    const int K = J.K, Cin = J.Cin, R = Cin * K, P = R + 1, m0 = grp * FP_ROWS;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // row scales (rows >= M are padding rows of the transposed pack: scale 0)
+    // ---- load + row scales (rows >= M are padding rows of the transposed pack: zeros, scale 0)
     for (int rl = warp; rl < FP_ROWS; rl += FP_NT / 32) {
         const int m = m0 + rl;
-        float sc = 0.f;
+        float* trow = fp_tile + (size_t)rl * P;
+        float ss = 0.f;
         if (m < J.M) {
-            sc = 1.f;
-            if (J.g) {
-                const float* vrow = J.v + (size_t)m * R;
-                float ss = 0.f;
-                for (int e = lane; e < R; e += 32) { const float t = vrow[e]; ss += t * t; }
-                ss = warp_sum(ss);
-                sc = J.g[m] / sqrtf(ss);
+            const float* vrow = J.v + (size_t)m * R;
+            for (int e0 = lane; e0 < R; e0 += 32 * 8) {
+                float t[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) t[u] = (e0 + 32 * u < R) ? __ldg(vrow + e0 + 32 * u) : 0.f;
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (e0 + 32 * u < R) { trow[e0 + 32 * u] = t[u]; ss = fmaf(t[u], t[u], ss); }
             }
+        } else {
+            for (int e = lane; e < R; e += 32) trow[e] = 0.f;
         }
-        if (lane == 0) sc_sm[rl] = sc;
+        ss = warp_sum(ss);
+        if (lane == 0) sc_sm[rl] = (m < J.M) ? (J.g ? J.g[m] / sqrtf(ss) : 1.f) : 0.f;
     }
     __syncthreads();
-    const int pitch = FP_CH * K + 1;
-    const int c_end = J.cols_f > Cin ? J.cols_f : Cin;               // fwd columns include the zero padding
-    for (int cb = 0; cb < c_end; cb += FP_CH) {
-        const int nc = min(FP_CH, Cin - cb);                          // real channels in this slab (may be <= 0)
-        // load: rows contiguous (nc * K floats each), scaled
-        for (int rl = warp; rl < FP_ROWS; rl += FP_NT / 32) {
-            const int m = m0 + rl;
-            const float sc = sc_sm[rl];
-            const float* src = J.v + (size_t)m * R + (size_t)cb * K;
-            for (int e = lane; e < FP_CH * K; e += 32) fp_tile[rl * pitch + e] = (m < J.M && e < nc * K) ? src[e] * sc : 0.f;
-        }
-        __syncthreads();
-        // forward operand: out[j][m][c], c fastest
-        const int ncf = min(FP_CH, J.cols_f - cb);
-        if (ncf > 0) {
-            for (int i = threadIdx.x; i < K * FP_ROWS * ncf; i += FP_NT) {
-                const int cl = i % ncf, rl = (i / ncf) % FP_ROWS, j = i / (ncf * FP_ROWS);
-                const int m = m0 + rl;
-                if (m < J.rows_f) J.fwd[((size_t)j * J.rows_f + m) * J.cols_f + cb + cl] = __float2bfloat16_rn(fp_tile[rl * pitch + cl * K + j]);
+    // ---- forward operand: out[j][m][c], c fastest (columns Cin..cols_f are zero padding)
+    for (int idx = warp; idx < K * FP_ROWS; idx += FP_NT / 32) {
+        const int j = idx / FP_ROWS, rl = idx % FP_ROWS, m = m0 + rl;
+        if (m >= J.rows_f) continue;
+        const float sc = sc_sm[rl];
+        const float* trow = fp_tile + (size_t)rl * P + j;
+        __nv_bfloat16* dst = J.fwd + ((size_t)j * J.rows_f + m) * J.cols_f;
+        for (int c = 2 * lane; c < J.cols_f; c += 64) {
+            const float a = c < Cin ? trow[c * K] * sc : 0.f;
+            const float b = c + 1 < Cin ? trow[(c + 1) * K] * sc : 0.f;
+            if (c + 1 < J.cols_f && (J.cols_f & 1) == 0) *reinterpret_cast<__nv_bfloat162*>(dst + c) = __floats2bfloat162_rn(a, b);
+            else {
+                dst[c] = __float2bfloat16_rn(a);
+                if (c + 1 < J.cols_f) dst[c + 1] = __float2bfloat16_rn(b);
             }
         }
-        // data-gradient operand: out[j][c][m] = W[m][c][K-1-j], m fastest (columns M..cols_t are zero padding)
-        if (J.tr && nc > 0) {
-            for (int i = threadIdx.x; i < K * nc * FP_ROWS; i += FP_NT) {
-                const int rl = i % FP_ROWS, cl = (i / FP_ROWS) % nc, j = i / (FP_ROWS * nc);
-                const int m = m0 + rl;
-                if (m < J.cols_t) J.tr[((size_t)j * J.rows_t + cb + cl) * J.cols_t + m] = __float2bfloat16_rn(fp_tile[rl * pitch + cl * K + (K - 1 - j)]);
+    }
+    // ---- data-gradient operand: out[j][c][m] = W[m][c][K-1-j], m fastest (columns M..cols_t are zero padding)
+    if (J.tr) {
+        const int sub = lane >> 3, rp = (lane & 7) * 2, m = m0 + rp;
+        const float s0 = sc_sm[rp], s1 = sc_sm[rp + 1];
+        const bool pair = (J.cols_t & 1) == 0;
+        for (int j = 0; j < K; ++j) {
+            const float* tj = fp_tile + (K - 1 - j);
+            for (int c = warp * 4 + sub; c < Cin; c += (FP_NT / 32) * 4) {
+                if (m >= J.cols_t) continue;
+                const float a = tj[(size_t)rp * P + c * K] * s0;
+                const float b = tj[(size_t)(rp + 1) * P + c * K] * s1;
+                __nv_bfloat16* dst = J.tr + ((size_t)j * J.rows_t + c) * J.cols_t + m;
+                if (pair) *reinterpret_cast<__nv_bfloat162*>(dst) = __floats2bfloat162_rn(a, b);
+                else {
+                    dst[0] = __float2bfloat16_rn(a);
+                    if (m + 1 < J.cols_t) dst[1] = __float2bfloat16_rn(b);
+                }
             }
         }
-        __syncthreads();
     }
 }
 int fold_pack(FoldPackJobs& jobs, cudaStream_t st) {
-    int groups = 0, kmax = 1;
+    int groups = 0, kmax = 1, rmax = 1;
     for (int i = 0; i < jobs.n; ++i) {
         FoldPackJob& J = jobs.job[i];
         GTK_REQUIRE(J.rows_f == J.M && J.rows_t == J.Cin, "pack shapes");
@@ -474,11 +487,14 @@ int fold_pack(FoldPackJobs& jobs, cudaStream_t st) {
         J.groups = ceil_div(rows, FP_ROWS);
         groups += J.groups;
         kmax = max(kmax, J.K);
+        rmax = max(rmax, J.Cin * J.K);
     }
+    (void)kmax;
     if (groups == 0) return GTK_OK;
-    const size_t smem = (size_t)FP_ROWS * (FP_CH * kmax + 1) * sizeof(float);
-    GTK_REQUIRE(smem <= 200 * 1024, "kernel_size too large for the pack kernel");
+    const size_t smem = (size_t)FP_ROWS * ((size_t)rmax + 1) * sizeof(float);
+    GTK_REQUIRE(smem <= 200 * 1024, "weight rows too long for the pack kernel");
     GTK_CUDA(cudaFuncSetAttribute(fold_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ProfScope prof("fold_pack", st);
     fold_pack_kernel<<<groups, FP_NT, smem, st>>>(jobs);
     return check_launch("fold_pack");
 }
@@ -573,6 +589,7 @@ int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, 
     GTK_REQUIRE(x && logs_raw && dz && dend && dx && C % 2 == 0 && ld >= C, "bad args");
     const long long total = (long long)B * T * ((C / 2 + 7) / 8 + (ld - C + 7) / 8);
     if (total == 0) return GTK_OK;
+    ProfScope prof("affine_bwd_frames", st);
     GTK_CUDA(launch_pdl(affine_bwd_frames_kernel, dim3((unsigned)ceil_div_ll(total, 128)), dim3(128), 0, st, x, logs_raw, mask, dz,
                         dlogdet, dend, ld, dx, B, C, T, sigmoid_scale));
     return check_launch("affine_bwd_frames");

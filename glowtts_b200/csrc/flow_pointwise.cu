@@ -197,51 +197,89 @@ __device__ __forceinline__ int mix_channel(int g, int j, int C) {
     }
 }
 
-template <int NS, bool REVERSE>
-__global__ void mix_kernel(const float* __restrict__ x, const float* __restrict__ mask, const float* __restrict__ logs,
-                           const float* __restrict__ bias, const float* __restrict__ M, float* __restrict__ z, int B,
-                           int C, int T) {
+// VEC consecutive frames per thread (128-bit accesses when T % 4 == 0, 64-bit when T is even -- the squeezed T' = 430
+// of the BASELINE configs -- scalar otherwise); one block row per group g, so the per-channel constants (e^logs, bias)
+// are set up once per thread, and no 64-bit division runs per element.
+template <int VEC> struct VecF;
+template <> struct VecF<1> { float v[1]; };
+template <> struct alignas(8) VecF<2> { float v[2]; };
+template <> struct alignas(16) VecF<4> { float v[4]; };
+
+template <int NS, bool REVERSE, int VEC>
+__global__ void __launch_bounds__(PW_NT) mix_kernel(const float* __restrict__ x, const float* __restrict__ mask,
+                                                    const float* __restrict__ logs, const float* __restrict__ bias,
+                                                    const float* __restrict__ M, float* __restrict__ z, int B, int C, int T) {
     __shared__ float sM[NS * NS];
     pdl_trigger();
     pdl_wait();
     if (threadIdx.x < NS * NS) sM[threadIdx.x] = M ? M[threadIdx.x] : ((threadIdx.x / NS == threadIdx.x % NS) ? 1.f : 0.f);
     __syncthreads();
-    const int G = C / NS;
-    const long long total = (long long)B * G * T;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int t = (int)(i % T);
-        long long r = i / T;
-        const int g = (int)(r % G);
-        const int b = (int)(r / G);
-        const float m = mask ? mask[(size_t)b * T + t] : 1.f;
-        float v[NS], o[NS];
-        int ch[NS];
+    const int g = blockIdx.y;
+    int ch[NS];
+    float e[NS], bs[NS];
 #pragma unroll
-        for (int j = 0; j < NS; ++j) {
-            ch[j] = mix_channel<NS>(g, j, C);
-            v[j] = x[((size_t)b * C + ch[j]) * T + t];
-            if (!REVERSE && logs) v[j] = bias[ch[j]] + expf(logs[ch[j]]) * v[j];
-        }
-#pragma unroll
-        for (int a = 0; a < NS; ++a) {
-            float acc = 0.f;
-#pragma unroll
-            for (int j = 0; j < NS; ++j) acc += sM[a * NS + j] * v[j];
-            if (REVERSE && logs) acc = (acc - bias[ch[a]]) * expf(-logs[ch[a]]);
-            o[a] = acc * m;
-        }
-#pragma unroll
-        for (int a = 0; a < NS; ++a) z[((size_t)b * C + ch[a]) * T + t] = o[a];
+    for (int j = 0; j < NS; ++j) {
+        ch[j] = mix_channel<NS>(g, j, C);
+        e[j] = logs ? expf(REVERSE ? -logs[ch[j]] : logs[ch[j]]) : 1.f;
+        bs[j] = bias ? bias[ch[j]] : 0.f;
     }
+    const int TV = T / VEC;
+    const int total = B * TV;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int b = i / TV, t = (i - b * TV) * VEC;
+        VecF<VEC> m, v[NS], o[NS];
+        if (mask) m = *reinterpret_cast<const VecF<VEC>*>(mask + (size_t)b * T + t);
+        else {
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) m.v[u] = 1.f;
+        }
+#pragma unroll
+        for (int j = 0; j < NS; ++j) v[j] = *reinterpret_cast<const VecF<VEC>*>(x + ((size_t)b * C + ch[j]) * T + t);
+#pragma unroll
+        for (int u = 0; u < VEC; ++u) {
+            float y[NS];
+#pragma unroll
+            for (int j = 0; j < NS; ++j) y[j] = (!REVERSE && logs) ? bs[j] + e[j] * v[j].v[u] : v[j].v[u];
+#pragma unroll
+            for (int a = 0; a < NS; ++a) {
+                float acc = 0.f;
+#pragma unroll
+                for (int j = 0; j < NS; ++j) acc += sM[a * NS + j] * y[j];
+                if (REVERSE && logs) acc = (acc - bs[a]) * e[a];
+                o[a].v[u] = acc * m.v[u];
+            }
+        }
+#pragma unroll
+        for (int a = 0; a < NS; ++a) *reinterpret_cast<VecF<VEC>*>(z + ((size_t)b * C + ch[a]) * T + t) = o[a];
+    }
+}
+
+// widest vector the row pitch and the base pointers allow
+static inline int pw_vec(int T, const void* a, const void* b, const void* c = nullptr, const void* d = nullptr) {
+    const uintptr_t bits = reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(c) |
+                           reinterpret_cast<uintptr_t>(d);
+    if (T % 4 == 0 && (bits & 15) == 0) return 4;
+    if (T % 2 == 0 && (bits & 7) == 0) return 2;
+    return 1;
 }
 
 template <int NS>
 static int mix_launch(const float* x, const float* mask, const float* logs, const float* bias, const float* M, float* z,
                       int B, int C, int T, int reverse, cudaStream_t st) {
-    const long long total = (long long)B * (C / NS) * T;
-    if (total == 0) return GTK_OK;
-    if (reverse) GTK_CUDA(launch_pdl(mix_kernel<NS, true>, dim3(pw_grid(total)), dim3(PW_NT), 0, st, x, mask, logs, bias, M, z, B, C, T));
-    else         GTK_CUDA(launch_pdl(mix_kernel<NS, false>, dim3(pw_grid(total)), dim3(PW_NT), 0, st, x, mask, logs, bias, M, z, B, C, T));
+    const int G = C / NS;
+    if ((long long)B * G * T == 0) return GTK_OK;
+    GTK_REQUIRE((long long)B * T < (1ll << 31), "B * T too large");
+    const int vec = pw_vec(T, x, z, mask);
+    int gx = (int)ceil_div_ll((long long)B * (T / vec), PW_NT * 2);
+    const int cap = max(1, sm_count() * 8 / G);
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    const dim3 grid(gx, G), block(PW_NT);
+    ProfScope prof("mix", st);
+#define GTK_MIX(R, V) GTK_CUDA(launch_pdl(mix_kernel<NS, R, V>, grid, block, 0, st, x, mask, logs, bias, M, z, B, C, T))
+    if (reverse) { if (vec == 4) GTK_MIX(true, 4); else if (vec == 2) GTK_MIX(true, 2); else GTK_MIX(true, 1); }
+    else         { if (vec == 4) GTK_MIX(false, 4); else if (vec == 2) GTK_MIX(false, 2); else GTK_MIX(false, 1); }
+#undef GTK_MIX
     return check_launch("mix");
 }
 
@@ -262,8 +300,8 @@ int mix(const float* x, const float* mask, const float* logs, const float* bias,
 // Backward of the forward mix.  One block row per group g (blockIdx.y) so that the per-channel
 // reductions (dlogs, dbias) and the NS x NS dM stay block-local until one atomicAdd per value.
 // dx may alias dz.  dlogs/dbias/dM are ACCUMULATED into (caller zeroes them once per step).
-template <int NS>
-__global__ void mix_bwd_kernel(const float* __restrict__ x, const float* __restrict__ mask, const float* __restrict__ logs,
+template <int NS, int VEC>
+__global__ void __launch_bounds__(PW_NT) mix_bwd_kernel(const float* __restrict__ x, const float* __restrict__ mask, const float* __restrict__ logs,
                                const float* __restrict__ bias, const float* __restrict__ M, const float* dz, float* dx,
                                float* __restrict__ dlogs, float* __restrict__ dbias, float* __restrict__ dM, int B, int C,
                                int T) {
@@ -287,31 +325,46 @@ __global__ void mix_bwd_kernel(const float* __restrict__ x, const float* __restr
     for (int j = 0; j < NS; ++j) a_logs[j] = a_bias[j] = 0.f;
 #pragma unroll
     for (int j = 0; j < NS * NS; ++j) a_M[j] = 0.f;
-    const long long total = (long long)B * T;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int t = (int)(i % T);
-        const int b = (int)(i / T);
-        const float m = mask ? mask[(size_t)b * T + t] : 1.f;
-        float xv[NS], y[NS], gz[NS];
+    const int TV = T / VEC;
+    const int total = B * TV;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int b = i / TV, t = (i - b * TV) * VEC;
+        VecF<VEC> m, xq[NS], gq[NS], oq[NS];
+        if (mask) m = *reinterpret_cast<const VecF<VEC>*>(mask + (size_t)b * T + t);
+        else {
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) m.v[u] = 1.f;
+        }
 #pragma unroll
         for (int j = 0; j < NS; ++j) {
             const size_t off = ((size_t)b * C + ch[j]) * T + t;
-            xv[j] = x[off];
-            y[j] = bs[j] + e[j] * xv[j];
-            gz[j] = dz[off] * m;
+            xq[j] = *reinterpret_cast<const VecF<VEC>*>(x + off);
+            gq[j] = *reinterpret_cast<const VecF<VEC>*>(dz + off);
         }
 #pragma unroll
-        for (int j = 0; j < NS; ++j) {
-            float dy = 0.f;
+        for (int u = 0; u < VEC; ++u) {
+            float xv[NS], y[NS], gz[NS];
 #pragma unroll
-            for (int a = 0; a < NS; ++a) {
-                dy += sM[a * NS + j] * gz[a];
-                a_M[a * NS + j] += gz[a] * y[j];
+            for (int j = 0; j < NS; ++j) {
+                xv[j] = xq[j].v[u];
+                y[j] = bs[j] + e[j] * xv[j];
+                gz[j] = gq[j].v[u] * m.v[u];
             }
-            a_bias[j] += dy;
-            a_logs[j] += dy * e[j] * xv[j];
-            dx[((size_t)b * C + ch[j]) * T + t] = dy * e[j];
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                float dy = 0.f;
+#pragma unroll
+                for (int a = 0; a < NS; ++a) {
+                    dy += sM[a * NS + j] * gz[a];
+                    a_M[a * NS + j] += gz[a] * y[j];
+                }
+                a_bias[j] += dy;
+                a_logs[j] += dy * e[j] * xv[j];
+                oq[j].v[u] = dy * e[j];
+            }
         }
+#pragma unroll
+        for (int j = 0; j < NS; ++j) *reinterpret_cast<VecF<VEC>*>(dx + ((size_t)b * C + ch[j]) * T + t) = oq[j];
     }
     // block reduction of 2*NS + NS*NS values
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -346,17 +399,24 @@ int mix_bwd(const float* x, const float* mask, const float* logs, const float* b
     GTK_REQUIRE(C % ns == 0, "channels % n_split != 0");
     if ((long long)B * C * T == 0) return GTK_OK;
     const int G = C / ns;
-    int gx = (int)ceil_div_ll((long long)B * T, PW_NT * 4);
+    GTK_REQUIRE((long long)B * T < (1ll << 31), "B * T too large");
+    const int vec = pw_vec(T, x, dz, dx, mask);
+    int gx = (int)ceil_div_ll((long long)B * (T / vec), PW_NT * 2);
     const int cap = max(1, sm_count() * 8 / G);
     if (gx > cap) gx = cap;
     if (gx < 1) gx = 1;
     dim3 grid(gx, G);
+    ProfScope prof("mix_bwd", st);
+#define GTK_MIXB(N, V) GTK_CUDA(launch_pdl(mix_bwd_kernel<N, V>, grid, dim3(PW_NT), 0, st, x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T))
+#define GTK_MIXB_V(N) do { if (vec == 4) GTK_MIXB(N, 4); else if (vec == 2) GTK_MIXB(N, 2); else GTK_MIXB(N, 1); } while (0)
     switch (ns) {
-        case 1: GTK_CUDA(launch_pdl(mix_bwd_kernel<1>, grid, dim3(PW_NT), 0, st, x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T)); break;
-        case 2: GTK_CUDA(launch_pdl(mix_bwd_kernel<2>, grid, dim3(PW_NT), 0, st, x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T)); break;
-        case 4: GTK_CUDA(launch_pdl(mix_bwd_kernel<4>, grid, dim3(PW_NT), 0, st, x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T)); break;
-        default: GTK_CUDA(launch_pdl(mix_bwd_kernel<8>, grid, dim3(PW_NT), 0, st, x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T)); break;
+        case 1: GTK_MIXB_V(1); break;
+        case 2: GTK_MIXB_V(2); break;
+        case 4: GTK_MIXB_V(4); break;
+        default: GTK_MIXB_V(8); break;
     }
+#undef GTK_MIXB_V
+#undef GTK_MIXB
     return check_launch("mix_bwd");
 }
 

@@ -9,8 +9,12 @@ lines = [l for l in open(sys.argv[1]) if not l.startswith("==")]
 rows = list(csv.DictReader(lines))
 names = [r["Kernel Name"] for r in rows]
 sq = [i for i, n in enumerate(names) if "squeeze_kernel" in n and "unsqueeze" not in n]
-start = sq[-2] if len(sq) >= 2 else 0          # each step has a forward squeeze and a backward one
-sel = rows[start:]
+# each step has a forward squeeze and a backward one; argv[2] = k picks the k-th step from the end (0 = last, which
+# may be cut off by ncu's -c limit)
+k = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+start = sq[-2 - 2 * k] if len(sq) >= 2 + 2 * k else 0
+end = sq[-2 * k] if k > 0 else len(rows)
+sel = rows[start:end]
 agg = collections.defaultdict(lambda: [0, 0.0])
 for r in sel:
     n = re.sub(r"[(<].*", "", r["Kernel Name"]).replace("void ", "")
