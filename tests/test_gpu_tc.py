@@ -403,3 +403,32 @@ def test_graphed_step_prefetch_feeds_the_same_batches():
     # same batches in the same order -> same losses up to the atomics' summation order in the backward
     assert all(abs(a - b) < 2e-4 * max(1.0, abs(a)) for a, b in zip(*losses)), losses
     assert abs(losses[0][0] - losses[0][1]) > 1e-3, losses      # the batches do differ: a stale buffer would show
+
+
+def test_pdl_on_off_agree(tmp_path):
+    """Programmatic dependent launch must not change a single forward value: the decoder at the BASELINE batch shape with
+    GTK_PDL=1 (kernels start while their predecessor drains) and GTK_PDL=0 (plain stream order), three repetitions each.
+    Forward / reverse outputs are deterministic -> bit-identical; gradients go through atomics -> 1e-5 relative."""
+    import os
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    res = {}
+    for v in ("1", "0"):
+        path = str(tmp_path / f"pdl{v}.npz")
+        env = dict(os.environ, GTK_PDL=v)
+        subprocess.run([sys.executable, os.path.join(here, "pdl_worker.py"), path], check=True, env=env, timeout=300)
+        res[v] = np.load(path)
+    on, off = res["1"], res["0"]
+    for rep in range(3):
+        for k in ("z", "ld", "yb"):
+            # ld accumulates per-utterance sums with atomics; z / yb are deterministic
+            a, b = on[f"{k}{rep}"], off[f"{k}{rep}"]
+            if k == "ld":
+                np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-3)
+            else:
+                assert np.array_equal(a, b), (k, rep, np.abs(a - b).max())
+        np.testing.assert_allclose(on[f"dy{rep}"], off[f"dy{rep}"], rtol=1e-4, atol=1e-7)
+        ga, gb = on[f"g{rep}"], off[f"g{rep}"]
+        assert np.linalg.norm(ga - gb) <= 1e-5 * np.linalg.norm(gb)
+        assert np.array_equal(on[f"z{rep}"], on["z0"])
