@@ -215,6 +215,29 @@ def timed(fn, steps, world):
     return max_over_ranks(e0.elapsed_time(e1), torch.device("cuda", torch.cuda.current_device()))
 
 
+def kernel_spans():
+    """Busy span (us) of the LAST launch of the fused WaveNet-layer kernels in the step that just ran, from the
+    globaltimer stamps every CTA leaves (first CTA past its preamble / griddepcontrol.wait -> last CTA done).  Unlike the
+    event-bracketed eager pass this is the kernel as it runs inside the replayed graph, overlapped launches included."""
+    import ctypes
+
+    import numpy as np
+    from glowtts_b200 import _lib
+    out = {}
+    n_ctas = B_PER_GPU * ((T_MEL // 2 + 127) // 128)
+    for tag, sym, n in (("wn_layer_tc", "gtk_debug_wn_trace", 6), ("wn_bwd_layer_tc", "gtk_debug_wb_trace", 7)):
+        try:
+            buf = (ctypes.c_ulonglong * (n_ctas * n))()
+            torch.cuda.synchronize()
+            _lib.call(sym, buf, n_ctas)
+            t = np.array(list(buf), dtype=np.int64).reshape(n_ctas, n)
+            t = t[t[:, 0] > 0]
+            out[tag] = float(t[:, n - 1].max() - t[:, 1].min()) / 1e3
+        except Exception as e:                              # debug entry points: never hide the main numbers
+            out[tag] = None
+    return out
+
+
 def mas_alone(device, steps=20, B=32, TX=T_TEXT, TY=T_MEL, n_buf=8, name="configs[0]"):
     """configs[0]: maximum_path on synthetic fp32 logp, B=32, T_x=180, T_y=860, full lengths (rotating over enough
     distinct inputs to exceed the 126 MB L2 between repeats); configs[4] per GPU: B=512, T_x=400, T_y=2000 (one
@@ -459,6 +482,7 @@ def main():
     launches = _lib.launch_count() - n0
     if run.graphed is not None:                            # replays do not pass through the library's host counter
         launches = run.graphed.launches * args.steps
+    spans = kernel_spans() if rank == 0 else {}            # in-kernel stamps of the last graph-replayed launches
     ms_e2e = timed(run.step_e2e, args.steps, world)
     clk = clocks.stop() if rank == 0 else None
 
@@ -500,6 +524,11 @@ def main():
                 "share_of_step": (ms_l / max(prof_steps, 1)) / (s_res * 1e3),
                 "flop_per_launch": flop_per_launch, "frames_valid": sq_frames_valid, "frames_computed": sq_frames_padded,
                 "how": f"CUDA events around every launch (library profiler), separate eager pass of {prof_steps} steps",
+                "kernel_span_us_in_graph": spans.get(tag),
+                "frac_by_span": (flop_per_launch / (spans[tag] * 1e-6) / 1e12 / pk["tc_sustained"]) if spans.get(tag) else None,
+                "span_note": "busy span of the step's last launch of this kernel inside the replayed CUDA graph (PDL-overlapped "
+                             "launches), from per-CTA globaltimer stamps; the event-bracketed figure above includes launch "
+                             "and event overhead of the eager pass",
                 "by_tag_ms_per_step": {k: v[1] / max(prof_steps, 1) for k, v in sorted(prof.items())}}
         step_flop = 3.0 * FLOP_PER_SQ_FRAME_FWD * CFG["n_blocks"] * sq_frames_padded
         out = {

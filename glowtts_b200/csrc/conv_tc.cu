@@ -381,6 +381,8 @@ int pack_weight_bf16(const float* w, __nv_bfloat16* out, int M, int Cin, int K, 
 __global__ void frames_from_tmajor_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int C, int T, int c0,
                                           int nc, int ld) {
     __shared__ float tile[32][33];
+    pdl_trigger();
+    pdl_wait();
     const int b = blockIdx.z, tt = blockIdx.x * 32, cc = blockIdx.y * 32;
     const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
     for (int i = ty; i < 32; i += 8) {
@@ -397,7 +399,7 @@ int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, 
     GTK_REQUIRE(x && out && c0 >= 0 && c0 + nc <= C && ld >= nc, "bad args");
     if ((long long)B * T * ld == 0) return GTK_OK;
     dim3 grid(ceil_div(T, 32), ceil_div(ld, 32), B);
-    frames_from_tmajor_kernel<<<grid, dim3(32, 8), 0, st>>>(x, out, C, T, c0, nc, ld);
+    GTK_CUDA(launch_pdl(frames_from_tmajor_kernel, grid, dim3(32, 8), 0, st, x, out, C, T, c0, nc, ld));
     return check_launch("frames_from_tmajor");
 }
 
