@@ -420,26 +420,40 @@ __global__ void __launch_bounds__(FP_NT) fold_pack_kernel(const __grid_constant_
     const FoldPackJob& J = jobs.job[w];
     const int K = J.K, Cin = J.Cin, R = Cin * K, P = R + 1, m0 = grp * FP_ROWS;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // ---- load + row scales (rows >= M are padding rows of the transposed pack: zeros, scale 0)
-    for (int rl = warp; rl < FP_ROWS; rl += FP_NT / 32) {
-        const int m = m0 + rl;
-        float* trow = fp_tile + (size_t)rl * P;
-        float ss = 0.f;
-        if (m < J.M) {
-            const float* vrow = J.v + (size_t)m * R;
-            for (int e0 = lane; e0 < R; e0 += 32 * 8) {
-                float t[8];
+    // ---- load + row scales (rows >= M are padding rows of the transposed pack: zeros, scale 0).  A warp owns rows
+    // `warp` and `warp + 8` and keeps 2 x 16 loads in flight per lane: a 960-float row arrives in two round trips.
+    {
+        constexpr int NW = FP_NT / 32, U = 16;
+        static_assert(FP_ROWS == 2 * NW, "two rows per warp");
+        const float* vrow[2];
+        float* trow[2];
+        bool live[2];
+        float ss[2] = {0.f, 0.f};
 #pragma unroll
-                for (int u = 0; u < 8; ++u) t[u] = (e0 + 32 * u < R) ? __ldg(vrow + e0 + 32 * u) : 0.f;
-#pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    if (e0 + 32 * u < R) { trow[e0 + 32 * u] = t[u]; ss = fmaf(t[u], t[u], ss); }
-            }
-        } else {
-            for (int e = lane; e < R; e += 32) trow[e] = 0.f;
+        for (int q = 0; q < 2; ++q) {
+            const int rl = warp + q * NW, m = m0 + rl;
+            live[q] = m < J.M;
+            vrow[q] = J.v + (size_t)(live[q] ? m : 0) * R;
+            trow[q] = fp_tile + (size_t)rl * P;
         }
-        ss = warp_sum(ss);
-        if (lane == 0) sc_sm[rl] = (m < J.M) ? (J.g ? J.g[m] / sqrtf(ss) : 1.f) : 0.f;
+        for (int e0 = lane; e0 < R; e0 += 32 * U) {
+            float t[2][U];
+#pragma unroll
+            for (int q = 0; q < 2; ++q)
+#pragma unroll
+                for (int u = 0; u < U; ++u) t[q][u] = (live[q] && e0 + 32 * u < R) ? __ldg(vrow[q] + e0 + 32 * u) : 0.f;
+#pragma unroll
+            for (int q = 0; q < 2; ++q)
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+                    if (e0 + 32 * u < R) { trow[q][e0 + 32 * u] = t[q][u]; ss[q] = fmaf(t[q][u], t[q][u], ss[q]); }
+        }
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int rl = warp + q * NW, m = m0 + rl;
+            const float s2 = warp_sum(ss[q]);
+            if (lane == 0) sc_sm[rl] = live[q] ? (J.g ? J.g[m] / sqrtf(s2) : 1.f) : 0.f;
+        }
     }
     __syncthreads();
     // ---- forward operand: out[j][m][c], c fastest (columns Cin..cols_f are zero padding)
