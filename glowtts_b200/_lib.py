@@ -14,7 +14,7 @@ from typing import Dict, List, Tuple
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 HEADER = os.path.join(ROOT, "include", "glowtts_b200.h")
-LIB_PATH = os.path.join(HERE, "lib", "libglowtts_b200.so")
+LIB_PATH = os.environ.get("GTK_LIB") or os.path.join(HERE, "lib", "libglowtts_b200.so")   # GTK_LIB: diagnostic builds
 
 GTK_MAX_LAYERS = 8
 _f32p = ctypes.c_void_p

@@ -315,7 +315,11 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {      // explicit ld.sh
 template <int XPT, bool DIAG>
 __device__ __forceinline__ void dp_col(const float (&v)[XPT], float (&q)[XPT], uint32_t (&bits)[XPT], int lane, int x0, int y,
                                        float up_in) {
+#if defined(GTK_MAS_DIAGNOSE) && GTK_MAS_DIAGNOSE == 1
+    float up = q[XPT - 1];           // DIAGNOSTIC BUILD (wrong results): no cross-lane shuffle, to time the chain without it
+#else
     float up = __shfl_up_sync(0xffffffffu, q[XPT - 1], 1);
+#endif
     if (lane == 0) up = up_in;
 #pragma unroll
     for (int k = XPT - 1; k >= 0; --k) {
@@ -360,8 +364,10 @@ __device__ __forceinline__ void dp_tile4(uint32_t tile, const int (&roff)[XPT], 
             for (int k = 0; k < XPT; ++k) v[k] = c == 0 ? cur[k].x : c == 1 ? cur[k].y : c == 2 ? cur[k].z : cur[k].w;
             const float up_in = FIRST ? ((DIAG && y0 + yl == 0) ? 0.0f : NEG) : bv[yl];
             dp_col<XPT, DIAG>(v, q, bits, lane, x0, y0 + yl, up_in);
+#if !defined(GTK_MAS_DIAGNOSE) || GTK_MAS_DIAGNOSE != 2      // 2: DIAGNOSTIC BUILD (wrong results) without the mailbox store
             if (SEND && lane == 31)
                 asm volatile("st.shared.f32 [%0], %1;" ::"r"(box_out + 4 * yl), "f"(q[XPT - 1]) : "memory");
+#endif
         }
         if (g + 1 < YT / 4) {
 #pragma unroll
