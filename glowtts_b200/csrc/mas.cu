@@ -482,10 +482,9 @@ __device__ __forceinline__ void wave_backtrack(WaveCtl* ctl, const uint32_t* bit
     if (blockIdx.x < MAS_TRACE_CTAS) g_mas_wait[blockIdx.x] = waited;
     if (valid) {
         // Decision words are MSB-first (frame f of the block at bit 31 - f), so "the last frame <= y whose bit is set"
-        // is the LOWEST set bit of (word & M), M = the bit positions still allowed.  Per token the loop-carried
-        // chain is 4 ALU operations (and, isolate lowest bit b, M = bits above b); the frame number (clz b) is off
-        // the chain.  The words of the next BT_ROWS rows of the current 32-frame block are loaded together; a token
-        // that starts in an earlier block (m == 0) ends the batch and moves one block down with M = all ones.
+        // is the LOWEST set bit of (word & M), M = the bit positions still allowed.  The words of the next BT_ROWS rows
+        // of the current 32-frame block are loaded together; a token that starts in an earlier block (m == 0) ends the
+        // batch and moves one block down with M = all ones.
         constexpr int BT_ROWS = 8;
         int index = t_x - 1;
         int yb = (t_y - 1) >> 5;
@@ -494,24 +493,25 @@ __device__ __forceinline__ void wave_backtrack(WaveCtl* ctl, const uint32_t* bit
             const uint32_t* base = bitsT + (size_t)yb * ROWW + index;      // word of (row index, block yb)
             uint32_t W[BT_ROWS];
 #pragma unroll
-            for (int j = 0; j < BT_ROWS; ++j) W[j] = base[-min(j, index)];
+            for (int j = 0; j < BT_ROWS; ++j) {
+                const uint32_t w = base[-min(j, index)];
+                W[j] = (j < index) ? w : 0u;                               // row 0 never moves down: it cannot "hit"
+            }
             const int f0 = yb << 5;
             int done = 0;
-            bool live = true, cross = false;
+            // Branch-free: per token the loop-carried chain is and -> (m - 1) -> not(m xor (m - 1)) = the bits above
+            // the lowest set bit of m.  A miss (m == 0) leaves M == 0, so every later row of the batch misses too
+            // (exactly the "first miss ends the batch" rule); the frame number (clz) and the store are off the chain.
 #pragma unroll
             for (int j = 0; j < BT_ROWS; ++j) {
-                const bool act = live && (index - j >= 1);
                 const uint32_t m = W[j] & M;
-                const bool hit = act && (m != 0u);
                 const uint32_t bb = m & (0u - m);
-                if (hit) {
-                    ys[index - j] = f0 + __clz(bb);                        // first frame of token index - j
-                    M = ~(bb | (bb - 1u));
-                    ++done;
-                }
-                cross = cross || (act && !hit);
-                live = hit;
+                ys[(m != 0u) ? index - j : ROWW + 2] = f0 + __clz(bb);     // first frame of token index - j (a miss
+                                                                           // writes the padding slot: no branch)
+                done += (m != 0u) ? 1 : 0;
+                M = ~(m ^ (m - 1u));
             }
+            const bool cross = done < min(BT_ROWS, index);                 // an active row started in an earlier block
             index -= done;
             if (cross) { --yb; M = 0xffffffffu; }
         }
