@@ -277,7 +277,7 @@ constexpr int TP = 36;                   // tile row pitch in floats (32 frames 
 constexpr int TBOX = 32;                 // text rows per TMA box
 constexpr int TBOX_BYTES = TBOX * TP * 4;
 constexpr int NDP = 4;                   // DP warps
-constexpr int NBOX = 4;                  // mailbox slots between neighbouring DP warps (tiles a warp may run ahead)
+constexpr int NBOX = 8;                  // mailbox slots between neighbouring DP warps (tiles a warp may run ahead)
 constexpr int TMA_MAX_STAGES = 6;
 constexpr int TMA_MAX_XPT = 8;           // T_x <= 1024 (if the decision bits fit)
 
@@ -381,6 +381,14 @@ __device__ __forceinline__ void fast_wait(uint64_t* bar, uint32_t parity) {
     if (!mbar_test_wait(bar, parity)) mbar_wait(bar, parity);
 }
 
+// Cycle stamps inside the DP loop cost ~25 cycles each, four per tile: only in the instrumented build
+// (-DGTK_MAS_EXP_TILETIME, profiles/mas_tiletime.py); the product build reports 0 waited cycles.
+#ifdef GTK_MAS_EXP_TILETIME
+#define MAS_CLOCK() clock64()
+#else
+#define MAS_CLOCK() 0ll
+#endif
+
 // One DP warp of the wavefront (band w = text rows [w * 32 * XPT, (w + 1) * 32 * XPT)) over all tiles of the utterance:
 // waits for its value tiles on ctl->full[w][*], releases them on ctl->empty[w][*], trades the band-boundary row with its
 // neighbours through the mailboxes and leaves the decision words in bitsT.  Returns the cycles warp 0 waited for tiles.
@@ -405,9 +413,9 @@ __device__ __forceinline__ long long wave_dp_warp(WaveCtl* ctl, const float* til
         float carry = 0.0f;                      // row r0 - 1 at the last frame of the previous tile
         for (int it = 0; it < n_tiles; ++it) {
             const int s = it % S, use = it / S, y0 = it * YT;
-            const long long w0 = clock64();
+            const long long w0 = MAS_CLOCK();
             fast_wait(&ctl->full[w][s], use & 1);
-            const long long w1 = clock64();
+            const long long w1 = MAS_CLOCK();
             if (w == 0 && it > 0) waited += w1 - w0;
             if (w == 0 && it == 0 && lane == 0) mas_stamp(1);
             float bv[YT];
@@ -430,7 +438,7 @@ __device__ __forceinline__ long long wave_dp_warp(WaveCtl* ctl, const float* til
                 if (lane == 0) mbar_arrive(&ctl->box_empty[w - 1][it % NBOX]);
             }
             if (send && it >= NBOX) fast_wait(&ctl->box_empty[w][it % NBOX], (it / NBOX - 1) & 1);
-            const long long w2 = clock64();
+            const long long w2 = MAS_CLOCK();
             const uint32_t tile = smem_u32(tiles + (size_t)s * stage_floats);
             const uint32_t bo = smem_u32(&ctl->box[w][it % NBOX][0]);
 #pragma unroll
@@ -447,7 +455,7 @@ __device__ __forceinline__ long long wave_dp_warp(WaveCtl* ctl, const float* til
                 else      { if (send) dp_tile4<XPT, false, false, true>(tile, roff, q, bits, lane, x0, y0, bv, bo);
                             else      dp_tile4<XPT, false, false, false>(tile, roff, q, bits, lane, x0, y0, bv, bo); }
             }
-            const long long w3 = clock64();
+            const long long w3 = MAS_CLOCK();
 #pragma unroll
             for (int k = 0; k < XPT; ++k)
                 if (x0 + k < ROWW) bitsT[(size_t)it * ROWW + x0 + k] = bits[k];      // MSB-first: frame f at bit 31 - f
