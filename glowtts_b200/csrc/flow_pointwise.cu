@@ -64,11 +64,44 @@ __global__ void unsqueeze_kernel(const float* __restrict__ x, const float* __res
     }
 }
 
+// n_sqz == 2 (every config of the reference): a thread owns the frame pair (2 tq, 2 tq + 1) of one channel -- one 64-bit
+// access on the un-squeezed side, two coalesced 32-bit accesses on the squeezed side -- instead of stride-2 scalars.
+// SQUEEZE: out[b, s*C + c, tq] = x[b, c, 2 tq + s] * m;  otherwise out[b, c, 2 t + s] = x[b, s*Cq + c, t] * m.
+template <bool SQUEEZE>
+__global__ void __launch_bounds__(PW_NT) sqz2_kernel(const float* __restrict__ x, const float* __restrict__ mask,
+                                                     float* __restrict__ out, float* __restrict__ mask_out, int Cq, int Tq,
+                                                     int T_long, int msq) {
+    // Cq = channels on the un-squeezed side, Tq = squeezed frames, T_long = row pitch of the un-squeezed tensor (even)
+    const int c = blockIdx.y, b = blockIdx.z;
+    const float* m_row = mask ? (SQUEEZE && !msq ? mask + (size_t)b * T_long : mask + (size_t)b * Tq) : nullptr;
+    for (int tq = blockIdx.x * blockDim.x + threadIdx.x; tq < Tq; tq += gridDim.x * blockDim.x) {
+        const float m = m_row ? ((SQUEEZE && !msq) ? m_row[2 * tq + 1] : m_row[tq]) : 1.f;
+        if (SQUEEZE) {
+            const float2 v = *reinterpret_cast<const float2*>(x + ((size_t)b * Cq + c) * T_long + 2 * tq);
+            out[((size_t)b * 2 * Cq + c) * Tq + tq] = v.x * m;
+            out[((size_t)b * 2 * Cq + Cq + c) * Tq + tq] = v.y * m;
+            if (mask_out && c == 0) mask_out[(size_t)b * Tq + tq] = m;
+        } else {
+            const float a = x[((size_t)b * 2 * Cq + c) * Tq + tq], d = x[((size_t)b * 2 * Cq + Cq + c) * Tq + tq];
+            *reinterpret_cast<float2*>(out + ((size_t)b * Cq + c) * T_long + 2 * tq) = make_float2(a * m, d * m);
+            if (mask_out && c == 0) *reinterpret_cast<float2*>(mask_out + (size_t)b * 2 * Tq + 2 * tq) = make_float2(m, m);
+        }
+    }
+}
+static inline bool sqz2_ok(int n, int T_long, const void* long_side, int B, int Cq) {
+    return n == 2 && T_long % 2 == 0 && (reinterpret_cast<uintptr_t>(long_side) & 7) == 0 && Cq <= 65535 && B <= 65535;
+}
+
 int squeeze(const float* x, const float* mask, float* out, float* mask_out, int B, int C, int T, int n, int mask_is_squeezed,
             cudaStream_t st) {
     GTK_REQUIRE(x && out && n >= 1, "bad args");
     const long long total = (long long)B * C * n * (T / n);
     if (total == 0) return GTK_OK;
+    if (sqz2_ok(n, T, x, B, C)) {
+        const int Tq = T / 2;
+        sqz2_kernel<true><<<dim3(ceil_div(Tq, PW_NT), C, B), PW_NT, 0, st>>>(x, mask, out, mask_out, C, Tq, T, mask_is_squeezed);
+        return check_launch("squeeze");
+    }
     squeeze_kernel<<<pw_grid(total), PW_NT, 0, st>>>(x, mask, out, mask_out, B, C, T, n, mask_is_squeezed);
     return check_launch("squeeze");
 }
@@ -78,6 +111,10 @@ int unsqueeze(const float* x, const float* mask, float* out, float* mask_out, in
     GTK_REQUIRE(x && out && n >= 1 && C % n == 0, "bad args");
     const long long total = (long long)B * C * T;
     if (total == 0) return GTK_OK;
+    if (sqz2_ok(n, out_T, out, B, C / 2) && out_T == 2 * T && (!mask_out || (reinterpret_cast<uintptr_t>(mask_out) & 7) == 0)) {
+        sqz2_kernel<false><<<dim3(ceil_div(T, PW_NT), C / 2, B), PW_NT, 0, st>>>(x, mask, out, mask_out, C / 2, T, out_T, 1);
+        return check_launch("unsqueeze");
+    }
     unsqueeze_kernel<<<pw_grid(total), PW_NT, 0, st>>>(x, mask, out, mask_out, B, C, T, n, out_T);
     return check_launch("unsqueeze");
 }
