@@ -108,26 +108,29 @@ class ClockSampler:
         return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def synth_batch(B: int, gen: torch.Generator, pin: bool = True):
-    """LJSpeech-shaped synthetic batch (host, pinned)."""
-    y = (torch.randn(B, CFG["in_channels"], T_MEL, generator=gen) - 5.0)
-    y_len = (torch.randint(T_MEL // 2, T_MEL + 1, (B,), generator=gen) // 2) * 2
+def synth_batch(B: int, gen: torch.Generator, pin: bool = True, len_gen: torch.Generator = None):
+    """LJSpeech-shaped synthetic batch (host, pinned).  `len_gen` draws the lengths (the same
+    generator state on every rank, so all ranks do the same amount of work per step and weak-scaling efficiency by
+    value equals efficiency by step time); `gen` draws the values (per-rank seed)."""
+    len_gen = len_gen or gen
+    y_len = (torch.randint(T_MEL // 2, T_MEL + 1, (B,), generator=len_gen) // 2) * 2
     y_len[0] = T_MEL
-    x_m = torch.randn(B, CFG["in_channels"], T_TEXT, generator=gen) * 0.5
-    x_len = torch.randint(T_TEXT // 2, T_TEXT + 1, (B,), generator=gen)
+    x_len = torch.randint(T_TEXT // 2, T_TEXT + 1, (B,), generator=len_gen)
     x_len[0] = T_TEXT
     x_len = torch.minimum(x_len, y_len)
+    y = (torch.randn(B, CFG["in_channels"], T_MEL, generator=gen) - 5.0)
+    x_m = torch.randn(B, CFG["in_channels"], T_TEXT, generator=gen) * 0.5
     mask = (torch.arange(T_MEL)[None, :] < y_len[:, None]).float().unsqueeze(1)
     y = y * mask
     return [t.pin_memory() if pin else t for t in (y, y_len, x_m, x_len)]
 
 
-def build_decoder(device, precision):
+def build_decoder(device, precision, gin=0):
     from glowtts_b200 import models
     torch.manual_seed(SEED)
     dec = models.FlowSpecDecoder(CFG["in_channels"], CFG["hidden_channels"], CFG["kernel_size"], CFG["dilation_rate"],
                                  CFG["n_blocks"], CFG["n_layers"], p_dropout=CFG["p_dropout_dec"], n_split=CFG["n_split"],
-                                 n_sqz=CFG["n_sqz"], gin_channels=CFG["gin_channels"], precision=precision)
+                                 n_sqz=CFG["n_sqz"], gin_channels=gin, precision=precision)
     with torch.no_grad():
         for b in range(CFG["n_blocks"]):          # non-trivial couplings (the reference starts them at zero)
             dec.flows[3 * b + 2].end.weight.normal_(0, 0.01)
@@ -137,16 +140,18 @@ def build_decoder(device, precision):
 class Runner:
     """Holds the resident model/optimizer and runs one step, device-resident or end to end."""
 
-    def __init__(self, device, world, precision, graph=False):
+    def __init__(self, device, world, precision, graph=False, gin=0):
         from glowtts_b200 import ops
         self.device, self.world = device, world
-        self.dec = build_decoder(device, precision)
+        self.dec = build_decoder(device, precision, gin)
         # train_ms_emo_lang_pitch.py:126-130 AdamW; the decoder hands its weights over as one flat tensor
         self.opt = torch.optim.AdamW(self.dec.flat_parameters(), lr=1e-4, fused=True, capturable=graph)
         self.graphed = None
         gen = torch.Generator().manual_seed(SEED + int(os.environ.get("RANK", "0")))
-        self.host = synth_batch(B_PER_GPU, gen)
+        self.host = synth_batch(B_PER_GPU, gen, len_gen=torch.Generator().manual_seed(SEED))
         self.dev = [t.to(device) for t in self.host]
+        # configs[3] (base_blank_ms.json): speaker embedding g [B, gin, 1] (models.py:1040-1041), resident
+        self.g = (torch.randn(B_PER_GPU, gin, 1, generator=gen).to(device) if gin else None)
         self.frames = int(self.host[1].sum())
         self.cells = int((self.host[1] * self.host[3]).sum())
         self.loss_host = torch.empty((), pin_memory=True)
@@ -156,7 +161,7 @@ class Runner:
         if graph:
             from glowtts_b200.hot_path import GraphedTrainStep
             try:
-                self.graphed = GraphedTrainStep(self.dec, self.opt, self.dev)
+                self.graphed = GraphedTrainStep(self.dec, self.opt, self.dev, g=self.g)
             except Exception as e:                          # e.g. a collective that cannot be captured: launch eagerly
                 print(f"bench.py: CUDA-graph capture failed ({e!r}); falling back to eager launches", file=sys.stderr)
                 self.graphed = None
@@ -165,7 +170,7 @@ class Runner:
         from glowtts_b200.hot_path import train_hot_path
         y, y_len, x_m, x_len = batch
         self.opt.zero_grad(set_to_none=True)
-        out = train_hot_path(self.dec, y, y_len, x_m, None, x_len)
+        out = train_hot_path(self.dec, y, y_len, x_m, None, x_len, g=self.g)
         out.loss.backward()
         self.opt.step()
         return out.loss
@@ -238,7 +243,7 @@ def kernel_spans():
     return out
 
 
-def mas_alone(device, steps=20, B=32, TX=T_TEXT, TY=T_MEL, n_buf=8, name="configs[0]"):
+def mas_alone(device, steps=20, B=32, TX=T_TEXT, TY=T_MEL, n_buf=8, name="configs[0]", world=1, want_path=True):
     """configs[0]: maximum_path on synthetic fp32 logp, B=32, T_x=180, T_y=860, full lengths (rotating over enough
     distinct inputs to exceed the 126 MB L2 between repeats); configs[4] per GPU: B=512, T_x=400, T_y=2000 (one
     3.3 GB input: far larger than L2)."""
@@ -247,26 +252,32 @@ def mas_alone(device, steps=20, B=32, TX=T_TEXT, TY=T_MEL, n_buf=8, name="config
     vals = [torch.randn(B, TX, TY, device=device, generator=gen) for _ in range(n_buf)]
     t_xs = torch.full((B,), TX, dtype=torch.int32, device=device)
     t_ys = torch.full((B,), TY, dtype=torch.int32, device=device)
+    call = (lambda v: ops.mas_path(v, t_xs, t_ys)) if want_path else (lambda v: ops.mas_index(v, t_xs, t_ys))
     for i in range(3):
-        ops.mas_path(vals[i % n_buf], t_xs, t_ys)
-    torch.cuda.synchronize()
+        call(vals[i % n_buf])
+    barrier_sync(world)
     _lib.prof_enable(True)
     for i in range(steps):
-        ops.mas_path(vals[i % n_buf], t_xs, t_ys)
+        call(vals[i % n_buf])
     torch.cuda.synchronize()
     prof = _lib.prof_read()
     _lib.prof_enable(False)
     n, ms = prof.get("mas", (0, 0.0))
     cells = B * TX * TY
-    per = ms / max(n, 1) * 1e-3
+    from glowtts_b200.distributed import max_over_ranks
+    per = max_over_ranks(ms / max(n, 1) * 1e-3, device)          # the slowest rank sets the job's time
     pk = peaks()
-    gbs = cells * 8 / per / 1e9 if per > 0 else 0.0
+    bpc = 8 if want_path else 4                                   # fp32 value read (+ fp32 path written: the drop-in)
+    gbs = cells * bpc / per / 1e9 if per > 0 else 0.0
     del vals
-    return {"workload": f"{name}: maximum_path B={B} T_x={TX} T_y={TY} fp32, full lengths", "cells_per_s": cells / per if per else 0.0,
+    return {"workload": f"{name}: maximum_path B={B} per GPU, T_x={TX} T_y={TY} fp32, full lengths"
+                        + ("" if want_path else "; index + durations only (no [B,T_x,T_y] path plane: SURVEY 8f-1 extension)"),
+            "cells_per_s": world * cells / per if per else 0.0, "per_gpu_cells_per_s": cells / per if per else 0.0,
+            "n_gpus": world, "sharding": "replicas only: utterances are independent, no collective",
             "us_per_call": per * 1e6, "launches_timed": n,
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
-                         "traffic": NCU_TRAFFIC.get("mas " + name) if (B, TX, TY) in ((32, 180, 860), (512, 400, 2000)) else None,
-                         "algorithmic_bytes_per_cell": 8, "peak_source": pk["src"]},
+                         "traffic": NCU_TRAFFIC.get("mas " + name) if (want_path and (B, TX, TY) in ((32, 180, 860), (512, 400, 2000))) else None,
+                         "algorithmic_bytes_per_cell": bpc, "peak_source": pk["src"], "per": "GPU"},
             "latency_floor_note": f"T_y={TY} dependent DP columns per utterance; {B} CTAs on 148 SMs"}
 
 
@@ -315,7 +326,7 @@ def mas_fused_alone(device, steps=20, B=32, TX=T_TEXT, TY=T_MEL, n_buf=12):
     return out
 
 
-def inference_alone(run, steps=10):
+def inference_alone(run, steps=10, world=1):
     """configs[2] at the train-step batch: the reverse decoder flow z -> mel (models.py:1230) after store_inverse(),
     no_grad, B=32 x T_mel=860 resident in HBM; CUDA events over `steps` calls."""
     dec = run.dec
@@ -335,55 +346,89 @@ def inference_alone(run, steps=10):
         e1.record()
         torch.cuda.synchronize()
     dec.train(was_training)
-    ms = e0.elapsed_time(e1) / steps
+    from glowtts_b200.distributed import max_over_ranks
+    ms = max_over_ranks(e0.elapsed_time(e1) / steps, y.device)
     frames = int(y_len.sum())
     flop = FLOP_PER_SQ_FRAME_FWD * CFG["n_blocks"] * (frames // CFG["n_sqz"])
-    return {"workload": "reverse decoder flow z -> mel, B=32, T_mel=860 (ragged), no_grad", "mel_frames_per_s": frames / (ms * 1e-3),
-            "ms_per_call": ms, "tflops_valid_frames": flop / (ms * 1e-3) / 1e12}
+    return {"workload": "reverse decoder flow z -> mel, B=32 per GPU, T_mel=860 (ragged), no_grad", "n_gpus": world,
+            "mel_frames_per_s": world * frames / (ms * 1e-3), "ms_per_call": ms,
+            "tflops_valid_frames_per_gpu": flop / (ms * 1e-3) / 1e12}
+
+
+def multispeaker_step(device, world, precision, graph, steps, warmup):
+    """BASELINE configs[3] (configs/base_blank_ms.json: gin_channels=256): the same train step with the speaker
+    conditioner, batch sharded over the ranks, flat-gradient NCCL all-reduce; timed like the headline."""
+    run = Runner(device, world, precision, graph=graph, gin=256)
+    for _ in range(max(warmup, 3)):
+        run.step_resident()
+    ms = timed(run.step_resident, steps, world)
+    from glowtts_b200.distributed import sum_over_ranks
+    frames = sum_over_ranks(run.frames, device)
+    out = {"workload": "configs[3]: base_blank_ms.json train step (gin_channels=256 speaker conditioning), B=32 per GPU",
+           "n_gpus": world, "ms_per_step": ms / steps, "mel_frames_per_s": frames / (ms / steps * 1e-3),
+           "launch": "cuda_graph" if run.graphed is not None else "eager"}
+    del run
+    torch.cuda.empty_cache()
+    return out
 
 
 # ------------------------------------------------------------------------------------------ CPU legs
-def cpu_hot_path_sample(b_sample: int, threads: int, mas_impl: str):
-    """One CPU pass of the same hot path on `b_sample` utterances of the workload, through the oracle
-    (torch CPU fp32 restatement of the reference modules + the C port / compiled reference core for MAS).
-    -> (frames, cells, seconds, seconds spent in MAS)."""
-    from oracle import flow as oflow
-    from oracle import mas as omas
-    import helpers
+class CpuArm:
+    """The CPU side of the same hot path through the oracle (torch CPU fp32 restatement of the reference modules + the
+    reference's compiled core.pyx for MAS, else the C port), with a resident checkpoint and an AdamW step, as the
+    reference's train loop has (train_ms_emo_lang_pitch.py:126-130, 295-312)."""
 
-    torch.set_num_threads(threads)
-    gen = torch.Generator().manual_seed(SEED)
-    y, y_len, x_m, x_len = synth_batch(b_sample, gen, pin=False)
-    sd = helpers.make_state_dict(dict(CFG), SEED, end_std=0.01)
-    sd = {k: v.requires_grad_(True) for k, v in sd.items() if ".wn_pitch." not in k and ".wn_energy." not in k}
-    mask = (torch.arange(T_MEL)[None, :] < y_len[:, None]).float().unsqueeze(1)
-    t0 = time.perf_counter()
-    z, logdet = oflow.decoder(sd, y, mask, hidden=CFG["hidden_channels"], dilation_rate=CFG["dilation_rate"],
-                              n_blocks=CFG["n_blocks"], n_layers=CFG["n_layers"], n_split=CFG["n_split"], n_sqz=CFG["n_sqz"],
-                              drop=lambda blk, i, v: torch.nn.functional.dropout(v, CFG["p_dropout_dec"]))
-    with torch.no_grad():
-        lp = oflow.logp(x_m, torch.zeros_like(x_m), z)
-        x_mask = (torch.arange(T_TEXT)[None, :] < x_len[:, None]).float()
-        amask = x_mask[:, :, None] * mask
-        tm = time.perf_counter()
-        attn = omas.maximum_path(lp, amask, impl=mas_impl)       # the reference wrapper's steps, CPU tensors
-        t_mas = time.perf_counter() - tm
-        z_m, z_logs = oflow.expand_prior(attn, x_m, torch.zeros_like(x_m))
-    loss = oflow.mle_loss(z, z_m, z_logs, logdet, mask)
-    loss.backward()
-    dt = time.perf_counter() - t0
-    return int(y_len.sum()), int((y_len * x_len).sum()), dt, t_mas
+    def __init__(self, threads: int, mas_impl: str):
+        import helpers
+        torch.set_num_threads(threads)
+        self.threads, self.mas_impl = threads, mas_impl
+        sd = helpers.make_state_dict(dict(CFG), SEED, end_std=0.01)
+        self.sd = {k: v.requires_grad_(True) for k, v in sd.items() if ".wn_pitch." not in k and ".wn_energy." not in k}
+        self.opt = torch.optim.AdamW(list(self.sd.values()), lr=1e-4)
+
+    def step(self, b_sample: int):
+        """One fwd + bwd + optimizer pass over `b_sample` utterances of the workload batch.
+        -> (frames, cells, seconds, seconds spent in MAS)."""
+        from oracle import flow as oflow
+        from oracle import mas as omas
+        gen = torch.Generator().manual_seed(SEED)
+        y, y_len, x_m, x_len = synth_batch(B_PER_GPU, gen, pin=False, len_gen=torch.Generator().manual_seed(SEED))
+        y, y_len, x_m, x_len = y[:b_sample], y_len[:b_sample], x_m[:b_sample], x_len[:b_sample]
+        mask = (torch.arange(T_MEL)[None, :] < y_len[:, None]).float().unsqueeze(1)
+        t0 = time.perf_counter()
+        self.opt.zero_grad(set_to_none=True)
+        z, logdet = oflow.decoder(self.sd, y, mask, hidden=CFG["hidden_channels"], dilation_rate=CFG["dilation_rate"],
+                                  n_blocks=CFG["n_blocks"], n_layers=CFG["n_layers"], n_split=CFG["n_split"], n_sqz=CFG["n_sqz"],
+                                  drop=lambda blk, i, v: torch.nn.functional.dropout(v, CFG["p_dropout_dec"]))
+        with torch.no_grad():
+            lp = oflow.logp(x_m, torch.zeros_like(x_m), z)
+            x_mask = (torch.arange(T_TEXT)[None, :] < x_len[:, None]).float()
+            amask = x_mask[:, :, None] * mask
+            tm = time.perf_counter()
+            attn = omas.maximum_path(lp, amask, impl=self.mas_impl)       # the reference wrapper's steps, CPU tensors
+            t_mas = time.perf_counter() - tm
+            z_m, z_logs = oflow.expand_prior(attn, x_m, torch.zeros_like(x_m))
+        loss = oflow.mle_loss(z, z_m, z_logs, logdet, mask)
+        loss.backward()
+        self.opt.step()
+        dt = time.perf_counter() - t0
+        return int(y_len.sum()), int((y_len * x_len).sum()), dt, t_mas
 
 
-def cpu_baseline(budget_s: float = 20.0):
+def _cpu_arm():
     from oracle import mas as omas
     threads = os.cpu_count() or 1
     mas_impl = "ref" if omas.ref_core() is not None else "c_port"
-    frames, cells, dt, t_mas = cpu_hot_path_sample(1, threads, mas_impl)      # warm-up + calibration
+    return CpuArm(threads, mas_impl), threads, mas_impl
+
+
+def cpu_baseline(budget_s: float = 20.0):
+    arm, threads, mas_impl = _cpu_arm()
+    frames, cells, dt, t_mas = arm.step(1)                                    # warm-up + calibration
     b = max(1, min(B_PER_GPU, int(budget_s / max(dt, 1e-3))))
-    frames, cells, dt, t_mas = cpu_hot_path_sample(b, threads, mas_impl)
+    frames, cells, dt, t_mas = arm.step(b)
     return {"value": frames / dt, "unit": "mel frames/s", "cores": threads,
-            "kind": "port", "sample": f"{b} of {B_PER_GPU} utterances of the same synthetic batch, 1 fwd+bwd pass "
+            "kind": "port", "sample": f"{b} of {B_PER_GPU} utterances of the same synthetic batch, 1 fwd+bwd+AdamW pass "
                                       f"({dt:.1f} s); torch CPU fp32 restatement of the reference modules with "
                                       f"{threads} threads; MAS = {'the reference core.pyx compiled as shipped (serial)' if mas_impl == 'ref' else 'C port (serial)'}",
             "mas_cells_per_s": cells / t_mas if t_mas > 0 else None, "mas_cores": 1}
@@ -392,30 +437,35 @@ def cpu_baseline(budget_s: float = 20.0):
 def run_reference(args):
     """--impl reference: the reference's CPU implementation of the path on this box's host cores.
     /root/reference cannot travel to the GPU box, so the decoder/logp leg is the oracle port of the reference's
-    PyTorch modules (same torch CPU kernels) and MAS is the reference's own core.pyx compiled into oracle/_ref."""
+    PyTorch modules (same torch CPU kernels) and MAS is the reference's own core.pyx compiled into oracle/_ref.
+    The line carries ITS OWN config (fp32, eager CPU, the utterances it really ran per step)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from oracle import mas as omas
-    threads = os.cpu_count() or 1
-    mas_impl = "ref" if omas.ref_core() is not None else "c_port"
-    _, _, dt1, _ = cpu_hot_path_sample(1, threads, mas_impl)
+    arm, threads, mas_impl = _cpu_arm()
+    _, _, dt1, _ = arm.step(1)
     total = args.steps + args.warmup
-    b = max(1, min(B_PER_GPU, int(120.0 / max(total, 1) / max(dt1, 1e-3))))
+    # the whole W + K run stays within ~4 minutes: the full 32-utterance batch when the box is fast enough for that
+    b = max(1, min(B_PER_GPU, int(240.0 / max(total, 1) / max(dt1, 1e-3))))
     for _ in range(args.warmup):
-        cpu_hot_path_sample(b, threads, mas_impl)
+        arm.step(b)
     t_sum, frames_sum = 0.0, 0
     for _ in range(args.steps):
-        frames, cells, dt, t_mas = cpu_hot_path_sample(b, threads, mas_impl)
+        frames, cells, dt, t_mas = arm.step(b)
         t_sum += dt
         frames_sum += frames
     val = frames_sum / t_sum
-    sample = f"each step = {b} of {B_PER_GPU} utterances of the workload batch, fwd+bwd, {threads} threads"
+    sample = (f"each step = {b} of {B_PER_GPU} utterances of the workload batch, fwd+bwd+AdamW, {threads} threads; "
+              f"MAS = {'reference core.pyx as shipped (1 core)' if mas_impl == 'ref' else 'C port (1 core)'}")
+    cfg = workload_config(1, "f32", "eager-cpu")
+    cfg.update({"batch_per_step": b, "batch_per_gpu": None, "global_batch": b, "device": "host CPU",
+                "parallelism": f"{threads} CPU threads (torch intra-op); no GPU",
+                "l2": "n/a (CPU arm)", "kind": "oracle port of the reference modules + reference core.pyx"})
     print(json.dumps({
         "impl": "reference", "metric": "train_hot_path_mel_frames_per_s", "value": val, "unit": "mel frames/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_sum / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(1, args.precision),
+        "config": cfg,
         "cpu_baseline": {"value": val, "unit": "mel frames/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "mel frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -497,13 +547,43 @@ def main():
 
     from glowtts_b200.distributed import sum_over_ranks
     frames_total, cells_total = sum_over_ranks(run.frames, device), sum_over_ranks(run.cells, device)
+    run_frames, run_h2d, run_graphed = run.frames, run.h2d_bytes, run.graphed is not None
+
+    # ---- secondary legs, at EVERY N (all ranks run them: the timings are reduced over the ranks).  MAS and the reverse
+    # flow shard by utterance with no collective ("replicas only"), so these curves should be linear; configs[3] is the
+    # multi-speaker train step with the gradient all-reduce.
+    from glowtts_b200 import ops as _ops
+    legs = {}
+
+    def leg(name, fn):
+        try:
+            legs[name] = fn()
+        except Exception as e:                                  # report, never hide the main numbers
+            legs[name] = {"error": repr(e)}
+        torch.cuda.empty_cache()
+
+    leg("mas", lambda: mas_alone(device, world=world))
+    if hasattr(_ops, "mas_index"):
+        leg("mas_index_only", lambda: mas_alone(device, world=world, want_path=False))
+    leg("inference", lambda: inference_alone(run, world=world))
+    if world == 1:
+        leg("mas_fused", lambda: mas_fused_alone(device))
+    del run
+    torch.cuda.empty_cache()
+    b_stress = max(1, 512 // world)
+    leg("mas_stress", lambda: mas_alone(device, steps=5, B=b_stress, TX=400, TY=2000, n_buf=1, world=world,
+                                        name="configs[4] on one GPU" if world == 1 else f"configs[4]: B=512 sharded over {world} GPUs"))
+    if hasattr(_ops, "mas_index"):
+        leg("mas_stress_index_only", lambda: mas_alone(device, steps=5, B=b_stress, TX=400, TY=2000, n_buf=1, world=world,
+                                                       want_path=False, name=f"configs[4]: B=512 over {world} GPU(s)"))
+    leg("multispeaker", lambda: multispeaker_step(device, world, args.precision, not args.no_graph, args.steps, args.warmup))
 
     if rank == 0:
         pk = peaks()
         s_res, s_e2e = ms_res / args.steps * 1e-3, ms_e2e / args.steps * 1e-3
         # dominant kernel: the fused WaveNet layer (k=5 dilated conv GEMM + gate + res/skip 1x1 GEMM, wn_tc.cu);
         # fp32 path: the k=5 CUDA-core convolution.  Algorithmic flops = valid (unpadded) squeezed frames only.
-        sq_frames_valid = run.frames // CFG["n_sqz"]
+        sq_frames_valid = run_frames // CFG["n_sqz"]
         sq_frames_padded = B_PER_GPU * (T_MEL // 2)
         H, K, L = CFG["hidden_channels"], CFG["kernel_size"], CFG["n_layers"]
         if "wn_layer_tc" in prof:
@@ -536,35 +616,21 @@ def main():
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": s_res * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if args.precision == "fp32" else "bf16 (fp32 accumulate)", "data": "synthetic",
-            "config": workload_config(world, args.precision, "cuda_graph" if run.graphed is not None else "eager"),
+            "config": workload_config(world, args.precision, "cuda_graph" if run_graphed else "eager"),
             "e2e": {"value": frames_total / s_e2e, "unit": "mel frames/s", "ms_per_step": s_e2e * 1e3,
-                    "h2d_bytes_per_step": run.h2d_bytes, "d2h_bytes_per_step": 4,
+                    "h2d_bytes_per_step": run_h2d, "d2h_bytes_per_step": 4,
                     "h2d": "pinned host -> device on a copy stream, double-buffered: the copy of step i+1's batch overlaps step i"
-                           if run.graphed is not None else "pinned host -> device on the compute stream before the step"},
+                           if run_graphed else "pinned host -> device on the compute stream before the step"},
             "gpu_launches": int(launches),
             "mas_cells_per_step": cells_total, "step_tflops": step_flop * world / s_res / 1e12,
             "roofline": roof, "clocks": clk,
         }
-        if world == 1:
-            # single-GPU legs (configs[0], [2], [4]); under torchrun the ranks are replicas of these (no collective on the
-            # MAS / inference paths), so the scaling run keeps to the training step
-            out["mas"] = mas_alone(device)
-            out["inference"] = inference_alone(run)
+        out.update(legs)
+        if world == 1 and not args.no_cpu_baseline:
             try:
-                out["mas_fused"] = mas_fused_alone(device)
-            except Exception as e:
-                out["mas_fused"] = {"error": repr(e)}
-            del run
-            torch.cuda.empty_cache()
-            try:
-                out["mas_stress"] = mas_alone(device, steps=5, B=512, TX=400, TY=2000, n_buf=1, name="configs[4] on one GPU")
-            except Exception as e:                              # 6.6 GB of buffers: report, never hide the main numbers
-                out["mas_stress"] = {"error": repr(e)}
-            if not args.no_cpu_baseline:
-                try:
-                    out["cpu_baseline"] = cpu_baseline()
-                except Exception as e:  # the oracle is a checker; its absence must not hide the GPU numbers
-                    out["cpu_baseline"] = {"value": None, "error": repr(e)}
+                out["cpu_baseline"] = cpu_baseline()
+            except Exception as e:  # the oracle is a checker; its absence must not hide the GPU numbers
+                out["cpu_baseline"] = {"value": None, "error": repr(e)}
         os.write(json_fd, (json.dumps(out) + "\n").encode())
     sys.stdout.flush()
     sys.stderr.flush()

@@ -14,6 +14,7 @@ from typing import Dict, List, Tuple
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 HEADER = os.path.join(ROOT, "include", "glowtts_b200.h")
+DEBUG_HEADER = os.path.join(ROOT, "include", "glowtts_b200_debug.h")   # instrumented builds only (-DGTK_INSTRUMENT)
 LIB_PATH = os.environ.get("GTK_LIB") or os.path.join(HERE, "lib", "libglowtts_b200.so")   # GTK_LIB: diagnostic builds
 
 GTK_MAX_LAYERS = 8
@@ -96,6 +97,11 @@ def load() -> ctypes.CDLL:
             raise GtkError("glowtts_b200: library does not export %s declared in %s" % (name, HEADER)) from e
         fn.restype = restype
         fn.argtypes = argtypes
+    if hasattr(lib, "gtk_debug_wn_trace") and os.path.exists(DEBUG_HEADER):     # instrumented build: bind the probes too
+        for name, (restype, argtypes) in parse_header(DEBUG_HEADER).items():
+            fn = getattr(lib, name)
+            fn.restype = restype
+            fn.argtypes = argtypes
     _lib, _protos = lib, protos
     return lib
 

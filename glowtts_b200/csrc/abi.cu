@@ -296,6 +296,7 @@ int gtk_tc_colsum(const void* in_bf16, int ld, int n_cols, int groups, long long
                   size_t out_gstride, void* stream) {
     return tc::colsum_frames(static_cast<const __nv_bfloat16*>(in_bf16), ld, n_cols, groups, rows_per_group, out, out_gstride, ST);
 }
+#ifdef GTK_INSTRUMENT
 int gtk_debug_mas_trace(unsigned long long* out, int n_ctas) { return mas::trace_read(out, n_ctas); }
 int gtk_debug_mas_wait(long long* out, int n_ctas) { return mas::wait_read(out, n_ctas); }
 int gtk_debug_wn_trace(unsigned long long* out, int n_ctas) { return tc::wn_trace_read(out, n_ctas); }
@@ -306,6 +307,7 @@ int gtk_debug_conv_wait(long long* out, int n_ctas) { return tc::conv_wait_read(
 int gtk_debug_shift_probe(const void* a, const void* b, float* out, void* stream) {
     return tc::shift_probe(static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b), out, ST);
 }
+#endif  // GTK_INSTRUMENT
 int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, const void* wrs_p, const float* bias_in,
                     const float* bias_rs, const float* cond, size_t cond_bstride, const float* mask, int B, int T, int H,
                     int RS, int K, int dil, int first, int last, float drop_p, unsigned long long drop_seed,
@@ -321,6 +323,21 @@ int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, c
     p.ts_save = static_cast<__nv_bfloat16*>(ts_save); p.acts_save = static_cast<__nv_bfloat16*>(acts_save);
     return tc::wn_layer_launch(static_cast<const __nv_bfloat16*>(h_bf16), static_cast<const __nv_bfloat16*>(win_p),
                                static_cast<const __nv_bfloat16*>(wrs_p), p, ST);
+}
+
+int gtk_tc_wn_bwd_layer(const void* drs_bf16, int ld_drs, const void* wrs_t, const void* win_t, const void* ts_tp,
+                        const float* mask, const float* resid_tp, float* out_tp, void* dxin_bf16, void* out_bf16,
+                        int ld_out, int B, int T, int H, int RS, int K, int dil, float drop_p,
+                        unsigned long long drop_seed, void* stream) {
+    tc::WnBwdParams p;
+    memset(&p, 0, sizeof(p));
+    p.B = B; p.T = T; p.H = H; p.RS = RS; p.taps = K; p.dil = dil;
+    p.mask = mask; p.ts = static_cast<const __nv_bfloat16*>(ts_tp);
+    p.drop_p = drop_p; p.drop_seed.value = drop_seed; p.drop_seed.dev = nullptr;
+    p.resid_f32 = resid_tp; p.out_f32 = out_tp;
+    return tc::wn_bwd_layer_launch(static_cast<const __nv_bfloat16*>(drs_bf16), ld_drs, static_cast<const __nv_bfloat16*>(wrs_t),
+                                   static_cast<const __nv_bfloat16*>(win_t), static_cast<__nv_bfloat16*>(dxin_bf16),
+                                   static_cast<__nv_bfloat16*>(out_bf16), ld_out, p, ST);
 }
 
 size_t gtk_decoder_workspace_bytes(const gtk_decoder_desc* d, int train) { return decoder::workspace_bytes(d, train); }

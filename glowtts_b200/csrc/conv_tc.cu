@@ -69,6 +69,7 @@ struct SmemCtl {
 
 // Phase timestamps (globaltimer, ns) per CTA of the last launch selected with conv_trace_select():
 // [start, setup done, accumulator complete, epilogue math done, stores issued].  Read with gtk_debug_conv_trace.
+#ifdef GTK_INSTRUMENT
 constexpr int CONV_TRACE_CTAS = 512;
 __device__ unsigned long long g_conv_trace[CONV_TRACE_CTAS * 5];
 __device__ long long g_conv_wait[CONV_TRACE_CTAS * 2];      // SM cycles the producer waited on `empty` / the MMA thread on `full`
@@ -83,6 +84,11 @@ __device__ __forceinline__ unsigned long long gtimer() {
         const int cta_ = blockIdx.y * gridDim.x + blockIdx.x;                                               \
         if (p.trace && threadIdx.x == 128 && cta_ < CONV_TRACE_CTAS) g_conv_trace[cta_ * 5 + (i)] = gtimer(); \
     } while (0)
+#define CONV_TRACING(p) ((p).trace)
+#else
+#define CONV_TRACE(i) do { } while (0)
+#define CONV_TRACING(p) false
+#endif
 
 // CL = CTAs per cluster.  CL == 2: two neighbouring frame tiles share every weight tile -- each CTA fetches half of
 // its rows and the TMA multicasts them into both shared memories, so the L2 -> SM traffic of the weights (60 % of the
@@ -147,16 +153,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int it = 0; it < n_iter; ++it) {
                 const int s = it % p.stages, use = it / p.stages;
                 if (use > 0) {
-                    const long long c0 = p.trace ? clock64() : 0;
+                    const long long c0 = CONV_TRACING(p) ? clock64() : 0;
                     mbar_wait(&ctl->empty[s], (use - 1) & 1);
-                    if (p.trace) w_empty += clock64() - c0;
+                    if (CONV_TRACING(p)) w_empty += clock64() - c0;
                 }
                 const int j = it / p.n_k, kc = it % p.n_k;
                 unsigned char* sa = smem + (size_t)s * stage_bytes;
                 if (it >= n_pre) load_weights(s, j, kc);
                 tma_load_3d(sa, &tmA, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
             }
+            #ifdef GTK_INSTRUMENT
             if (p.trace) { const int cta_ = blockIdx.y * gridDim.x + blockIdx.x; if (cta_ < CONV_TRACE_CTAS) g_conv_wait[cta_ * 2] = w_empty; }
+#endif
         }
     } else if (warp == 1) {
         if (lane == 0) {
@@ -164,9 +172,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             long long w_full = 0;
             for (int it = 0; it < n_iter; ++it) {
                 const int s = it % p.stages, use = it / p.stages;
-                const long long c0 = p.trace ? clock64() : 0;
+                const long long c0 = CONV_TRACING(p) ? clock64() : 0;
                 mbar_wait(&ctl->full[s], use & 1);
-                if (p.trace) w_full += clock64() - c0;
+                if (CONV_TRACING(p)) w_full += clock64() - c0;
                 tc_fence_after();
                 const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
                 const uint32_t sb = sa + A_BYTES;
@@ -192,7 +200,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 else umma_commit(&ctl->empty[s]);
             }
             umma_commit(&ctl->acc_full);
+            #ifdef GTK_INSTRUMENT
             if (p.trace) { const int cta_ = blockIdx.y * gridDim.x + blockIdx.x; if (cta_ < CONV_TRACE_CTAS) g_conv_wait[cta_ * 2 + 1] = w_full; }
+#endif
         }
     }
     __syncwarp();
@@ -339,6 +349,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
 }
 
+#ifdef GTK_INSTRUMENT
 void conv_trace_select(int epi, int taps) { g_trace_epi = epi; g_trace_taps = taps; }
 int conv_trace_read(unsigned long long* out, int n_ctas) {
     GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= CONV_TRACE_CTAS, "n_ctas");
@@ -350,6 +361,7 @@ int conv_wait_read(long long* out, int n_ctas) {
     GTK_CUDA(cudaMemcpyFromSymbol(out, g_conv_wait, size_t(n_ctas) * 2 * sizeof(long long)));
     return GTK_OK;
 }
+#endif
 
 // ---------------------------------------------------------------------------------- helpers: packing / layout
 // W fp32 [M][Cin][K] (torch) -> bf16 [K][rows][cols] zero padded.
@@ -671,7 +683,9 @@ int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, 
         if (rc) return rc;
     }
     dim3 grid(ceil_div(ceil_div(p.T, BT), p.cluster) * p.cluster, p.B);   // an out-of-range tile only feeds its peer
+#ifdef GTK_INSTRUMENT
     p.trace = (epi == g_trace_epi && p.taps == g_trace_taps) ? 1 : 0;
+#endif
     ProfScope prof(epi == EPI_GATE_BWD ? "conv_tc_gate_bwd" : epi == EPI_AFFINE ? "conv_tc_affine" : p.taps > 1 ? "conv_tc_kN" : "conv_tc_k1", st);
 #define GTK_TC_LAUNCH(COLS, E)                                                                                       \
     do {                                                                                                             \

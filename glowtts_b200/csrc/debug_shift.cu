@@ -3,6 +3,7 @@
 // every tap of a dilated convolution (rows shifted by the tap offset), and layer-to-layer fusion in shared memory becomes
 // possible.  Computes D_s = A[s : s + 128, :] * B^T for s = 1..4 with the descriptor's "base offset" field (bits 49-51)
 // either 0 or (start address >> 7) & 7.
+#ifdef GTK_INSTRUMENT
 #include <string.h>
 
 #include "tc.cuh"
@@ -89,3 +90,4 @@ int shift_probe(const __nv_bfloat16* a, const __nv_bfloat16* b, float* out, cuda
 
 }  // namespace tc
 }  // namespace gtk
+#endif  // GTK_INSTRUMENT

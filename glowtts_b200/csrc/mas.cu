@@ -290,6 +290,7 @@ struct WaveCtl {
 
 // Phase stamps (globaltimer, ns) per CTA of the last launch: [start, first tile landed, DP done (all warps), backtrack
 // done, all warps past the barrier, end]; read with gtk_debug_mas_trace.
+#ifdef GTK_INSTRUMENT
 constexpr int MAS_TRACE_CTAS = 1024;
 __device__ unsigned long long g_mas_trace[MAS_TRACE_CTAS * 6];
 __device__ long long g_mas_wait[MAS_TRACE_CTAS];            // SM cycles DP warp 0 waited for tiles (after the first)
@@ -300,6 +301,9 @@ __device__ __forceinline__ void mas_stamp(int i) {
         g_mas_trace[blockIdx.x * 6 + i] = t;
     }
 }
+#else
+__device__ __forceinline__ void mas_stamp(int) {}
+#endif
 
 __device__ __forceinline__ float4 lds128(uint32_t addr) {      // explicit ld.shared (a generic pointer costs an LD.E)
     float4 v;
@@ -464,7 +468,7 @@ __device__ __forceinline__ long long wave_dp_warp(WaveCtl* ctl, const float* til
                 mbar_arrive(&ctl->empty[w][s]);
                 if (send) mbar_arrive(&ctl->box_full[w][it % NBOX]);
             }
-#ifdef GTK_MAS_EXP_TILETIME
+#if defined(GTK_MAS_EXP_TILETIME) && defined(GTK_INSTRUMENT)
             if (it == 10 && lane == 0 && blockIdx.x == 0 && w < 4) {
                 g_mas_trace[900 * 6 + w * 6 + 0] = (unsigned long long)(w1 - w0);
                 g_mas_trace[900 * 6 + w * 6 + 1] = (unsigned long long)(w2 - w1);
@@ -487,7 +491,9 @@ __device__ __forceinline__ void wave_backtrack(WaveCtl* ctl, const uint32_t* bit
                                                int t_y, long long waited) {
     if (valid) fast_wait(&ctl->dp_done, 0);
     mas_stamp(2);
+#ifdef GTK_INSTRUMENT
     if (blockIdx.x < MAS_TRACE_CTAS) g_mas_wait[blockIdx.x] = waited;
+#endif
     if (valid) {
         // Decision words are MSB-first (frame f of the block at bit 31 - f), so "the last frame <= y whose bit is set"
         // is the LOWEST set bit of (word & M), M = the bit positions still allowed.  The words of the next BT_ROWS rows
@@ -889,6 +895,7 @@ __global__ void __launch_bounds__(F_NT, 1) mas_fused_kernel(const __grid_constan
     if (tid == 0) mas_stamp(5);
 }
 
+#ifdef GTK_INSTRUMENT
 int trace_read(unsigned long long* out, int n_ctas) {
     GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= MAS_TRACE_CTAS, "n_ctas");
     GTK_CUDA(cudaMemcpyFromSymbol(out, g_mas_trace, size_t(n_ctas) * 6 * sizeof(unsigned long long)));
@@ -899,6 +906,7 @@ int wait_read(long long* out, int n_ctas) {
     GTK_CUDA(cudaMemcpyFromSymbol(out, g_mas_wait, size_t(n_ctas) * sizeof(long long)));
     return GTK_OK;
 }
+#endif
 
 // -------------------------------------------------------------------------------------------------
 // Generic fallback for shapes the fast path does not cover (T_x > 512, or decision bits that do not

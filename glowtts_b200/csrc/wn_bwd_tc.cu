@@ -33,6 +33,7 @@ constexpr int WB_CL = 2;                     // CTAs per cluster: every in_layer
 
 // Phase timestamps (globaltimer, ns) per CTA of the last launch: [start, setup, GEMM a done, epilogue a done, GEMM b done,
 // epilogue b done, end]; read with gtk_debug_wb_trace.
+#ifdef GTK_INSTRUMENT
 constexpr int WB_TRACE_CTAS = 512;
 __device__ unsigned long long g_wb_trace[WB_TRACE_CTAS * 7];
 __device__ __forceinline__ unsigned long long wb_timer() {
@@ -45,6 +46,9 @@ __device__ __forceinline__ unsigned long long wb_timer() {
         const int cta_ = blockIdx.y * gridDim.x + blockIdx.x;                               \
         if (threadIdx.x == 128 && cta_ < WB_TRACE_CTAS) g_wb_trace[cta_ * 7 + (i)] = wb_timer(); \
     } while (0)
+#else
+#define WB_TRACE(i) do { } while (0)
+#endif
 
 // RowIo of frame f of utterance b for the tile-private tensors (addressed by frame, whatever the tiling of the kernel)
 __device__ __forceinline__ RowIo frame_io(int b, int f, int T) {
@@ -278,11 +282,13 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
     }
 }
 
+#ifdef GTK_INSTRUMENT
 int wb_trace_read(unsigned long long* out, int n_ctas) {
     GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= WB_TRACE_CTAS, "n_ctas");
     GTK_CUDA(cudaMemcpyFromSymbol(out, g_wb_trace, size_t(n_ctas) * 7 * sizeof(unsigned long long)));
     return GTK_OK;
 }
+#endif
 
 int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat16* wrs_t, const __nv_bfloat16* win_t,
                         __nv_bfloat16* dxin, __nv_bfloat16* out_bf16, int ld_out, WnBwdParams p, cudaStream_t st) {

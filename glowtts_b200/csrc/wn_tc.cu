@@ -27,9 +27,10 @@ struct WnCtl {
 
 constexpr int WN_STAGES = 3;
 
-// Phase timestamps (globaltimer, ns) of every CTA: g_wn_trace[cta][start, setup done, GEMM1 done, epilogue1 done,
-// GEMM2 done, end], cta = blockIdx.y * gridDim.x + blockIdx.x (first WN_TRACE_CTAS only).  Always written (6 stores by
-// one thread per CTA); read with gtk_debug_wn_trace for the per-phase breakdown in profiles/.
+// Instrumented builds only (-DGTK_INSTRUMENT): phase timestamps (globaltimer, ns) of every CTA: g_wn_trace[cta][start,
+// setup done, GEMM1 done, epilogue1 done, GEMM2 done, end], cta = blockIdx.y * gridDim.x + blockIdx.x (first
+// WN_TRACE_CTAS only); read with gtk_debug_wn_trace for the per-phase breakdown in profiles/.
+#ifdef GTK_INSTRUMENT
 constexpr int WN_TRACE_CTAS = 512;
 __device__ unsigned long long g_wn_trace[WN_TRACE_CTAS * 6];
 __device__ __forceinline__ unsigned long long gtimer() {
@@ -42,6 +43,9 @@ __device__ __forceinline__ unsigned long long gtimer() {
         const int cta_ = blockIdx.y * gridDim.x + blockIdx.x;                           \
         if (threadIdx.x == 128 && cta_ < WN_TRACE_CTAS) g_wn_trace[cta_ * 6 + (i)] = gtimer(); \
     } while (0)
+#else
+#define WN_TRACE(i) do { } while (0)
+#endif
 
 __global__ void __launch_bounds__(EPI_NT, 1)
 wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmWin,
@@ -298,11 +302,13 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     }
 }
 
+#ifdef GTK_INSTRUMENT
 int wn_trace_read(unsigned long long* out, int n_ctas) {
     GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= WN_TRACE_CTAS, "n_ctas");
     GTK_CUDA(cudaMemcpyFromSymbol(out, g_wn_trace, size_t(n_ctas) * 6 * sizeof(unsigned long long)));
     return GTK_OK;
 }
+#endif
 
 int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, const __nv_bfloat16* wrs_p, WnLayerParams p,
                     cudaStream_t st) {

@@ -12,6 +12,7 @@ arrive as tensors (requires_grad allowed; their gradients flow back through the 
 """
 from __future__ import annotations
 
+import copy
 from typing import NamedTuple, Optional
 
 import torch
@@ -82,9 +83,33 @@ class GraphedTrainStep:
         self.g = None if g is None else g.to(dev, copy=True)
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
-        with torch.cuda.stream(side):                      # warm-up off the capture: allocations, flat buffers, seed state
+        # Warm-up off the capture (allocations, flat buffers, seed state).  Constructing the stepper must not train the
+        # model: parameters, optimizer state and the dropout seed state are snapshotted and restored around it, so step 1
+        # of the stepper is step 1 of the run (exact resume, trajectories comparable with the reference's).
+        with torch.cuda.stream(side):
+            self._eager(dry=True)                          # materialises flat buffers / lazily created state
+            snap_p = [p.detach().clone() for g in optimizer.param_groups for p in g["params"]]
+            snap_o = copy.deepcopy(optimizer.state_dict())
+            seed_state = getattr(decoder, "_drop_state", None)
+            snap_s = None if seed_state is None else seed_state.clone()
             for _ in range(max(1, warmup)):
                 self._eager()
+            with torch.no_grad():
+                for p, q in zip([p for g in optimizer.param_groups for p in g["params"]], snap_p):
+                    p.copy_(q)
+            cur = optimizer.state_dict()
+            for k, st in snap_o["state"].items():          # restore IN PLACE: capturable optimizers keep device tensors
+                for name, v in st.items():
+                    tgt = cur["state"][k][name]
+                    if torch.is_tensor(tgt):
+                        tgt.copy_(v)
+            if not snap_o["state"]:                        # the optimizer had no state yet: reset what warm-up created
+                for st in optimizer.state.values():
+                    for v in st.values():
+                        if torch.is_tensor(v):
+                            v.zero_()
+            if snap_s is not None:                         # the dry pass drew one seed: rewind to the state before it
+                decoder._drop_state.copy_(snap_s - decoder._SEED_STEP)
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         self.graph = torch.cuda.CUDAGraph()
@@ -94,12 +119,13 @@ class GraphedTrainStep:
             self.out = self._eager()
         self.launches = _lib.launch_count() - n0           # library kernels per replay
 
-    def _eager(self) -> HotPathOut:
+    def _eager(self, dry: bool = False) -> HotPathOut:
         y, y_len, x_m, x_len = self.static
         self.optimizer.zero_grad(set_to_none=True)
         out = train_hot_path(self.decoder, y, y_len, x_m, self.x_logs, x_len, self.g)
         out.loss.backward()
-        self.optimizer.step()
+        if not dry:
+            self.optimizer.step()
         return out
 
     def step(self, batch=None) -> torch.Tensor:

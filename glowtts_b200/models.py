@@ -123,6 +123,11 @@ class FlowSpecDecoder(nn.Module):
             base = flat.data_ptr()
             ok = all(p.data_ptr() == base + 4 * o for p, o in zip(params, offs))
         if not ok:
+            if flat is not None and getattr(self, "_keep_flat_grad", False):
+                # an optimizer holds the old flat tensor: rebuilding it here would silently stop the decoder's training
+                raise RuntimeError("glowtts_b200: the decoder was moved or its parameters were re-bound after "
+                                   "flat_parameters() handed the flat buffer to an optimizer; build the optimizer again "
+                                   "from flat_parameters() (or move the module before creating it)")
             with torch.no_grad():
                 buf = torch.zeros(total, dtype=torch.float32, device=params[0].device)
                 owners = self._param_owners()
@@ -163,7 +168,13 @@ class FlowSpecDecoder(nn.Module):
         return {p.data_ptr(): p for p in self._ordered_owners()}
 
     def _scatter_flat_grad(self, flat):
-        if getattr(self, "_keep_flat_grad", False):      # the optimizer owns the flat tensor (flat_parameters())
+        if getattr(self, "_keep_flat_grad", False):
+            # the optimizer owns the flat tensor (flat_parameters()); the named parameters still get `.grad` -- as views
+            # of the flat gradient, no copies -- so that `model.parameters()`-based utilities of the reference's loop
+            # (commons.clip_grad_value_, grad-norm logging, GradScaler inf checks) see all 12 flow blocks
+            g = flat.grad
+            for p, o, n in zip(self._flat_params, self._flat_offs, self._flat_sizes):
+                p.grad = g[o:o + n].view(p.shape)
             return
         g = flat.grad
         flat.grad = None

@@ -39,19 +39,20 @@ FUSED_MIN_BATCH = 96      # measured on B200 (profiles/ncu_mas_fused_r01.txt): b
 
 
 def maximum_path_from_prior(z: torch.Tensor, x_m: torch.Tensor, x_logs, t_xs: torch.Tensor, t_ys: torch.Tensor,
-                            return_logp: bool = False, fused=None):
+                            return_logp: bool = False, fused=False):
     """models.py:1076-1083 as one call: the alignment of z [b,d,t_y] against the prior means x_m [b,d,t_x]
     (x_logs [b,d,t_x] or None for mean_only models), lengths int32 [b] on the device.
     -> (path, durations, index[, logp]).  Mean-only shapes the fused kernel covers (ops.mas_fused_supported) can run as
-    ONE launch with logp computed on the tensor cores inside the MAS CTA (`fused=True`; default: when the batch has at
-    least FUSED_MIN_BATCH utterances, i.e. when one CTA per utterance fills the GPU); everything else runs the logp
-    kernel followed by the MAS kernel -- both are CUDA paths, the results differ only by fp32 summation order."""
+    ONE launch with logp computed on the tensor cores inside the MAS CTA -- OPT-IN (`fused=True`, or `fused="auto"`:
+    when the batch has at least FUSED_MIN_BATCH utterances, i.e. when one CTA per utterance fills the GPU), because that
+    kernel is not bit-exact with logp -> MAS (3xTF32 products, the per-frame z^2 term dropped from the DP): the default
+    is the exact two-kernel path, so alignments never depend on the batch size."""
     with torch.no_grad():
         D, T_x, T_y = x_m.shape[1], x_m.shape[2], z.shape[2]
         can = ops.mas_fused_supported(D, T_x, T_y, x_logs is not None) and z.data_ptr() % 16 == 0
         if fused and not can:
             raise RuntimeError("glowtts_b200: this shape is not covered by the fused logp + MAS kernel")
-        if can and (fused or (fused is None and z.shape[0] >= FUSED_MIN_BATCH)):
+        if can and (fused is True or (fused == "auto" and z.shape[0] >= FUSED_MIN_BATCH)):
             path, dur, idx, lp = ops.mas_fused_logp(z, x_m, t_xs, t_ys, return_logp)
         else:
             lp = ops.logp(x_m, x_logs, z)

@@ -194,28 +194,19 @@ int gtk_tc_wn_layer(const void* h_bf16, const float* h_f32, const void* win_p, c
                     float* h_out_f32, void* h_out_bf16, float* skip_f32, void* skip_out_bf16, void* ts_save,
                     void* acts_save, void* stream);
 
-/* Debug: phase timestamps (ns) of the first n_ctas (<= 512) CTAs of the last fused WN-layer launch:
- * out[cta * 6 + {start, setup done, GEMM1 done, epilogue-1 done, GEMM2 done, end}], cta = batch * tiles + tile.
- * Synchronises the device. */
-int gtk_debug_wn_trace(unsigned long long* out, int n_ctas);
-/* Debug: DP-warp phase stamps of the last TMA-path MAS launch: out[cta * 6 + {start, first tile landed, DP done,
- * backtrack done, barrier passed, end}] (globaltimer ns).  Synchronises the device. */
-int gtk_debug_mas_trace(unsigned long long* out, int n_ctas);
-/* Debug: SM cycles the DP warp of each CTA spent waiting for value tiles after the first one (same launch). */
-int gtk_debug_mas_wait(long long* out, int n_ctas);
-/* Debug: the fused layer-backward kernel: out[cta * 7 + {start, setup, GEMM a, epilogue a, GEMM b, epilogue b, end}]. */
-int gtk_debug_wb_trace(unsigned long long* out, int n_ctas);
-/* Debug: the same for the plain tcgen05 conv kernel.  Select which launches record (epilogue 0 plain / 1 gate-bwd /
- * 2 affine, and the tap count; -1 = none), run, then read out[cta * 5 + {start, setup done, accumulator complete,
- * epilogue math done, stores issued}] of the last selected launch.  Synchronises the device. */
-int gtk_debug_conv_trace_select(int epilogue, int taps);
-int gtk_debug_conv_trace(unsigned long long* out, int n_ctas);
-/* out[cta * 2 + {0: SM cycles the TMA producer waited for a free stage, 1: cycles the MMA thread waited for data}] */
-int gtk_debug_conv_wait(long long* out, int n_ctas);
-/* Hardware probe (debug_shift.cu): D_s = A[s : s+128] B^T for row shifts s = 1..4 of a K-major SWIZZLE_128B operand,
- * descriptor base-offset field 0 (mode 0) or (addr >> 7) & 7 (mode 1).  a [136][64] bf16, b [64][64] bf16,
- * out [(s-1)*2 + mode][128][64] fp32. */
-int gtk_debug_shift_probe(const void* a, const void* b, float* out, void* stream);
+/* Backward of gtk_tc_wn_layer in one tcgen05 kernel (autograd of modules.py:151-170): res/skip data gradient -> gate
+ * backward (from the saved tanh|sigmoid, dropout mask regenerated) -> dilated-conv data gradient.
+ * drs: bf16 frames [B,T,ld_drs], columns [0,RS) = [d(h_next) * mask | d(skip)] (RS == H: d(skip) only);
+ * wrs_t = gtk_tc_pack_weight(res_skip weight, transpose=1) [1][H][pad64(RS)]; win_t = gtk_tc_pack_weight(in_layer
+ * weight, transpose=1) [K][H][2H].  ts_tp / resid_tp / out_tp use the TILE-PRIVATE layout the decoder keeps between
+ * epilogues: 16-byte vector v of frame t of utterance b lives at (((b * ceil(T/128) + t/128) * n_vec + v) * 128 + t%128)
+ * * 16 bytes (n_vec = row bytes / 16).  ts_tp: saved [tanh|sigmoid] bf16 (2H columns); resid_tp: fp32 d(h) carried from
+ * the layer above (H columns) or NULL; out_tp: fp32 d(h) of this layer (H columns).  dxin: bf16 frames [B,T,2H] out
+ * (operand of the weight gradient); out_bf16: bf16 frames [B,T,ld_out], columns [0,H) = d(h) * mask. */
+int gtk_tc_wn_bwd_layer(const void* drs_bf16, int ld_drs, const void* wrs_t, const void* win_t, const void* ts_tp,
+                        const float* mask, const float* resid_tp, float* out_tp, void* dxin_bf16, void* out_bf16,
+                        int ld_out, int B, int T, int H, int RS, int K, int dil, float drop_p,
+                        unsigned long long drop_seed, void* stream);
 
 /* ---- whole decoder (models.py:719-789) --------------------------------------------------- */
 typedef struct gtk_decoder_desc {

@@ -142,6 +142,90 @@ def gen_flow_prosody(ref):
         print(name, float(loss), float((y_rev - y.detach()).abs().max()), len(sel))
 
 
+ROUND2_CASES = {
+    # name: (cfg, sd_seed, b, t, in_seed, use_g, sigmoid_scale)  -- round 2: reference branches the round-1 fixtures missed
+    "flow_tiny_sig": (helpers.TINY_CFG, 27, 3, 14, 37, False, True),                      # attentions.py:175-176
+    "flow_h64": (dict(in_channels=16, hidden_channels=64, kernel_size=5, dilation_rate=1, n_blocks=3, n_layers=3,
+                      n_split=4, n_sqz=2, gin_channels=0), 28, 3, 300, 38, False, False),   # runs on the bf16 tcgen05 path
+    "flow_h64_g_sig": (dict(in_channels=16, hidden_channels=64, kernel_size=3, dilation_rate=2, n_blocks=2, n_layers=3,
+                            n_split=4, n_sqz=2, gin_channels=8), 29, 2, 280, 39, True, True),
+}
+
+
+def gen_round2(ref):
+    """Decoder fixtures with sigmoid_scale=True and tensor-core-capable widths (hidden 64), plus module fixtures with
+    x_mask=None (modules.py:585-586, 639-641; attentions.py:134-135) and no_jacobian=True (modules.py:655-656)."""
+    for name, (cfg, sd_seed, b, t, in_seed, use_g, sig) in ROUND2_CASES.items():
+        dec = ref.models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"],
+                                         cfg["dilation_rate"], cfg["n_blocks"], cfg["n_layers"], p_dropout=0.0,
+                                         n_split=cfg["n_split"], n_sqz=cfg["n_sqz"], sigmoid_scale=sig,
+                                         gin_channels=cfg["gin_channels"])
+        sd = helpers.make_state_dict(cfg, sd_seed)
+        dec.load_state_dict(sd, strict=True)
+        dec.eval()
+        y, mask, lengths, g = flow_inputs(cfg, b, t, in_seed, use_g)
+        y = y.clone().requires_grad_(True)
+        if g is not None:
+            g = g.clone().requires_grad_(True)
+        z, logdet = dec(y, mask, g=g, reverse=False)
+        loss = ref.commons.mle_loss(z, torch.zeros_like(z), torch.zeros_like(z), logdet, mask)
+        loss.backward()
+        sel = {}
+        for k, p in dec.named_parameters():
+            if p.grad is None or ".wn_pitch." in k or ".wn_energy." in k:
+                continue
+            a = p.grad.detach().numpy()
+            if a.size > 4096:
+                a = a.reshape(-1)[:: max(1, a.size // 2048)]
+            sel["grad:" + k] = a
+        with torch.no_grad():
+            y_rev, _ = dec(z.detach(), mask, g=g, reverse=True)
+            dec.store_inverse()
+            y_rev2, _ = dec(z.detach(), mask, g=g, reverse=True)
+        extra = {} if g is None else {"dg": g.grad.numpy()}
+        np.savez_compressed(os.path.join(HERE, name + ".npz"),
+                            sd_seed=sd_seed, b=b, t=t, in_seed=in_seed, use_g=use_g, sigmoid_scale=sig, end_std=0.05,
+                            z=z.detach().numpy().astype(np.float32), logdet=logdet.detach().numpy(), loss=loss.item(),
+                            dy=y.grad.numpy(), y_rev=y_rev.numpy(), y_rev_stored=y_rev2.numpy(), **extra, **sel)
+        print(name, float(loss), float((y_rev - y.detach()).abs().max()), len(sel))
+    # ---- modules with x_mask=None / no_jacobian=True
+    gen = torch.Generator().manual_seed(43)
+    b, c, t, h = 2, 16, 9, 16
+    x = torch.randn(b, c, t, generator=gen)
+    out = {"x": x.numpy()}
+    an = ref.modules.ActNorm(c)
+    an.logs.data = 0.2 * torch.randn(1, c, 1, generator=gen)
+    an.bias.data = 0.2 * torch.randn(1, c, 1, generator=gen)
+    z, ld = an(x)
+    zr, _ = an(x, reverse=True)
+    out.update(an_logs=an.logs.data.numpy(), an_bias=an.bias.data.numpy(), an_z=z.detach().numpy(),
+               an_logdet=ld.detach().numpy(), an_zrev=zr.detach().numpy())
+    ic = ref.modules.InvConvNear(c, n_split=4)
+    ic.weight.data = ic.weight.data + 0.1 * torch.randn(4, 4, generator=gen)
+    z, ld = ic(x)
+    zr, _ = ic(x, reverse=True)
+    out.update(ic_w=ic.weight.data.numpy(), ic_z=z.detach().numpy(), ic_logdet=ld.detach().numpy(), ic_zrev=zr.detach().numpy())
+    ic2 = ref.modules.InvConvNear(c, n_split=4, no_jacobian=True)
+    ic2.weight.data = ic.weight.data.clone()
+    lengths = torch.tensor([9, 5])
+    mask = (torch.arange(t)[None, :] < lengths[:, None]).float().unsqueeze(1)
+    z2, ld2 = ic2(x, mask)
+    assert ld2 == 0
+    out.update(nj_lengths=lengths.numpy(), nj_z=z2.detach().numpy())
+    cfg = dict(helpers.TINY_CFG, n_blocks=1)
+    for sig in (False, True):
+        cb = ref.attentions.CouplingBlock(c, h, kernel_size=5, dilation_rate=1, n_layers=2, sigmoid_scale=sig)
+        sd = {k[len("flows.2."):]: v for k, v in helpers.make_state_dict(cfg, 44).items() if k.startswith("flows.2.")}
+        cb.load_state_dict(sd, strict=True)
+        cb.eval()
+        z, ld = cb(x)
+        zr, _ = cb(x, reverse=True)
+        tag = "cbs" if sig else "cb"
+        out.update({tag + "_z": z.detach().numpy(), tag + "_logdet": ld.detach().numpy(), tag + "_zrev": zr.detach().numpy()})
+    np.savez_compressed(os.path.join(HERE, "modules_nomask.npz"), **out)
+    print("modules_nomask ok")
+
+
 def gen_modules(ref):
     """Module-level fixtures: ActNorm (+DDI), InvConvNear, WN, CouplingBlock, gate, squeeze."""
     gen = torch.Generator().manual_seed(41)
@@ -202,10 +286,14 @@ if __name__ == "__main__":
     torch.manual_seed(0)
     ref = refimport.load()
     assert ref is not None, "needs /root/reference"
+    if "--round2-only" in sys.argv:        # add the round-2 fixtures without touching the older files
+        gen_round2(ref)
+        sys.exit(0)
     if "--prosody-only" in sys.argv:       # add the 3-WN fixtures without touching the older files
         gen_flow_prosody(ref)
         sys.exit(0)
     gen_flow_prosody(ref)
+    gen_round2(ref)
     gen_mas()
     gen_modules(ref)
     gen_logp()

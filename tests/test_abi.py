@@ -29,6 +29,18 @@ def test_library_exports_every_declared_symbol():
     assert loaded.gtk_abi_version() >= 1
 
 
+def test_default_build_exports_no_instrumentation():
+    """The shipped boundary is what a maintainer of the reference would bind: the per-CTA trace probes
+    (include/glowtts_b200_debug.h) exist only in a -DGTK_INSTRUMENT build."""
+    import subprocess
+    assert not any(n.startswith("gtk_debug_") for n in _lib.declared_symbols())
+    if os.environ.get("GTK_LIB") or "GTK_INSTRUMENT" in os.environ.get("GTK_EXTRA_CFLAGS", ""):
+        pytest.skip("instrumented diagnostic build selected")
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "gtk_mas_forward" in out
+    assert "gtk_debug_" not in out
+
+
 def test_workspace_queries_run_without_a_gpu():
     lib = _lib.load()
     assert lib.gtk_mas_workspace_bytes(32, 180, 860) == 0          # decision bits fit in shared memory

@@ -1,0 +1,344 @@
+"""Round-2 parity pins ("Next round" item 1): the bf16 tcgen05 path -- the one bench.py times -- compared
+DIRECTLY with the reference-generated fixtures and with oracle/flow.py, at fixture sizes and at BASELINE configs[1]'s
+exact shape (B=32, T_mel=860, ragged, 12 blocks, G=0 and G=256), plus the reference branches round 1 left untested
+(sigmoid_scale=True, x_mask=None, no_jacobian=True), a kernel-level test of the fused layer backward, and the reverse
+flow at T_mel=2000.
+
+Stated bounds of the bf16 path against the REFERENCE (fp32), printed by each test and copied to DESIGN.md section 2:
+    max|dz|        <= 2e-2 * max|z|
+    |d logdet[b]|  <= 2e-2 * |logdet[b]| + 0.5
+    |d mle_loss|   <= 5e-3 * max(1, |loss|)   (same alignment on both sides; <= 2e-3 relative end to end, alignment included)
+    gradients      relative L2 error per tensor <= 3e-2 (dy <= 2e-2)
+    reverse(forward(y)) == y within 5e-2 * max|y|
+The fp32 path keeps the 1e-4 relative bar of test_gpu_flow.py."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import helpers
+from oracle import flow as oflow
+from oracle import mas as omas
+
+pytestmark = pytest.mark.gpu
+
+H64 = dict(in_channels=16, hidden_channels=64, kernel_size=5, dilation_rate=1, n_blocks=3, n_layers=3, n_split=4, n_sqz=2,
+           gin_channels=0)
+H64_G_SIG = dict(in_channels=16, hidden_channels=64, kernel_size=3, dilation_rate=2, n_blocks=2, n_layers=3, n_split=4,
+                 n_sqz=2, gin_channels=8)
+FIXTURES = {
+    # name: (cfg, sigmoid_scale, precisions that can run it)
+    "flow_base": (helpers.BASE_CFG, False, ("bf16",)),                   # fp32 is covered by test_gpu_flow.py
+    "flow_h64": (H64, False, ("fp32", "bf16")),
+    "flow_h64_g_sig": (H64_G_SIG, True, ("fp32", "bf16")),
+    "flow_tiny_sig": (helpers.TINY_CFG, True, ("fp32",)),               # hidden 16: CUDA-core path only
+}
+
+
+def _bf(x):
+    return x.to(torch.bfloat16).to(torch.float32)
+
+
+def _decoder(cfg, sd, precision, sigmoid_scale=False, p_dropout=0.0):
+    from glowtts_b200 import models
+    dec = models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"], cfg["dilation_rate"],
+                                 cfg["n_blocks"], cfg["n_layers"], p_dropout=p_dropout, n_split=cfg["n_split"],
+                                 n_sqz=cfg["n_sqz"], sigmoid_scale=sigmoid_scale, gin_channels=cfg["gin_channels"],
+                                 precision=precision)
+    dec.load_state_dict(sd, strict=True)
+    return dec.cuda()
+
+
+def _kw(cfg):
+    return dict(hidden=cfg["hidden_channels"], dilation_rate=cfg["dilation_rate"], n_blocks=cfg["n_blocks"],
+                n_layers=cfg["n_layers"], n_split=cfg["n_split"], n_sqz=cfg["n_sqz"])
+
+
+def _rel_l2(a, b):
+    return float((a - b).norm() / (b.norm() + 1e-12))
+
+
+def _check_against(tag, precision, z, ld, loss, dy, grads, want, y_rev=None, y=None):
+    """want: dict with z, logdet, loss, dy, grads {name: array (maybe strided sample)}, y_rev."""
+    z, ld, dy = z.detach().float().cpu(), ld.detach().float().cpu(), dy.detach().float().cpu()
+    wz, wld = torch.as_tensor(want["z"]), torch.as_tensor(want["logdet"])
+    if precision == "fp32":
+        np.testing.assert_allclose(z.numpy(), wz.numpy(), rtol=1e-4, atol=2e-5)
+        np.testing.assert_allclose(ld.numpy(), wld.numpy(), rtol=1e-4, atol=1e-3)
+        assert abs(loss - want["loss"]) < 1e-4 * max(1.0, abs(want["loss"]))
+        np.testing.assert_allclose(dy.numpy(), np.asarray(want["dy"]), rtol=1e-3, atol=1e-6)
+        for k, w in want["grads"].items():
+            g = grads[k].detach().cpu().numpy()
+            if g.size != w.size:
+                g = g.reshape(-1)[:: max(1, g.size // 2048)]
+            np.testing.assert_allclose(g.reshape(w.shape), w, rtol=2e-3, atol=2e-6, err_msg=k)
+        if y_rev is not None:
+            np.testing.assert_allclose(y_rev.cpu().numpy(), np.asarray(want["y_rev"]), rtol=1e-4, atol=5e-5)
+        return
+    zerr = float((z - wz).abs().max() / wz.abs().max())
+    lderr = float(((ld - wld).abs() / (wld.abs() * 2e-2 + 0.5)).max())
+    dloss = abs(loss - want["loss"]) / max(1.0, abs(want["loss"]))
+    dyerr = _rel_l2(dy, torch.as_tensor(want["dy"]))
+    worst = ("", 0.0)
+    for k, w in want["grads"].items():
+        g = grads[k].detach().float().cpu()
+        w = torch.as_tensor(w)
+        if g.numel() != w.numel():
+            g = g.reshape(-1)[:: max(1, g.numel() // 2048)]
+        assert torch.isfinite(g).all(), k
+        if w.norm() > 1e-7:
+            e = _rel_l2(g.reshape(w.shape), w)
+            if e > worst[1]:
+                worst = (k, e)
+    msg = (f"[bf16 vs reference] {tag}: max|dz|/max|z|={zerr:.2e} (<=2e-2)  logdet={lderr:.2e} (<=1, i.e. 2e-2 rel + 0.5)  "
+           f"|dloss|/max(1,|loss|)={dloss:.2e} (<=5e-3)  dy relL2={dyerr:.2e} (<=2e-2)  worst grad relL2={worst[1]:.2e} at {worst[0]} (<=3e-2)")
+    if y_rev is not None:
+        rerr = float((y_rev.cpu() - torch.as_tensor(want["y_rev"])).abs().max() / torch.as_tensor(want["y_rev"]).abs().max())
+        msg += f"  reverse={rerr:.2e} (<=5e-2)"
+        assert rerr < 5e-2, msg
+    print(msg)
+    assert zerr < 2e-2 and lderr < 1.0 and dloss < 5e-3 and dyerr < 2e-2 and worst[1] < 3e-2, msg
+
+
+@pytest.mark.parametrize("name,precision", [(n, p) for n, (_, _, ps) in FIXTURES.items() for p in ps])
+def test_decoder_vs_reference_fixture(golden_dir, name, precision):
+    """(i)+(iv): fixtures made by the reference modules, through the fp32 path (1e-4) and the bf16 tcgen05 path (stated
+    bound): z, logdet, loss, dy, parameter gradients, reverse."""
+    from glowtts_b200 import commons
+    cfg, sig, _ = FIXTURES[name]
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    sd = helpers.make_state_dict(cfg, int(g["sd_seed"]), end_std=float(g["end_std"]))
+    dec = _decoder(cfg, sd, precision, sig)
+    y, mask, _, cond = helpers.flow_inputs(cfg, int(g["b"]), int(g["t"]), int(g["in_seed"]), bool(g["use_g"]))
+    y = y.cuda().requires_grad_(True)
+    mask = mask.cuda()
+    cond = cond.cuda().requires_grad_(True) if cond is not None else None
+    z, ld = dec(y, mask, g=cond)
+    loss = commons.mle_loss(z, None, None, ld, mask)
+    loss.backward()
+    with torch.no_grad():
+        y_rev, none = dec(z.detach(), mask, g=cond, reverse=True)
+    assert none is None
+    grads = {k: p.grad for k, p in dec.named_parameters() if p.grad is not None}
+    want = dict(z=g["z"], logdet=g["logdet"], loss=float(g["loss"]), dy=g["dy"], y_rev=g["y_rev"],
+                grads={k[5:]: g[k] for k in g.files if k.startswith("grad:")})
+    assert len(want["grads"]) > 5
+    _check_against(name, precision, z, ld, loss.item(), y.grad, grads, want, y_rev, y)
+    if cond is not None:
+        e = _rel_l2(cond.grad.cpu(), torch.as_tensor(g["dg"]))
+        assert e < (1e-3 if precision == "fp32" else 5e-2), e
+
+
+@pytest.mark.parametrize("precision,gin", [("fp32", 0), ("bf16", 0), ("bf16", 256), ("fp32", 256)])
+def test_baseline_config1_shape_vs_oracle(precision, gin):
+    """(ii): BASELINE configs[1]'s exact shape -- B=32, T_text=180, T_mel=860, ragged, 12 blocks, hidden 192 -- and
+    configs[3]'s conditioner (G=256): decoder z / logdet / gradients against oracle.flow.decoder on the host, then
+    logp -> MAS -> gather -> mle_loss on both sides (MAS on the oracle's own logp through the reference core)."""
+    from glowtts_b200 import commons, monotonic_align, ops
+    torch.manual_seed(0)
+    cfg = dict(helpers.BASE_CFG, gin_channels=gin)
+    B, T, TX = 32, 860, 180
+    sd = helpers.make_state_dict(cfg, 1234, end_std=0.01)
+    dec = _decoder(cfg, sd, precision)
+    gen = torch.Generator().manual_seed(1234)
+    y = torch.randn(B, 80, T, generator=gen) - 5.0
+    y_len = (torch.randint(T // 2, T + 1, (B,), generator=gen) // 2) * 2
+    y_len[0] = T
+    x_m = torch.randn(B, 80, TX, generator=gen) * 0.5
+    x_len = torch.minimum(torch.randint(TX // 2, TX + 1, (B,), generator=gen), y_len)
+    x_len[0] = TX
+    cond = torch.randn(B, gin, 1, generator=gen) if gin else None
+    mask = (torch.arange(T)[None, :] < y_len[:, None]).float().unsqueeze(1)
+    y = y * mask
+    # ---- oracle on the host
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    sd_o = {k: v.clone().requires_grad_(True) for k, v in sd.items() if ".wn_pitch." not in k and ".wn_energy." not in k}
+    yo = y.clone().requires_grad_(True)
+    z_o, ld_o = oflow.decoder(sd_o, yo, mask, g=cond, **_kw(cfg))
+    with torch.no_grad():
+        lp_o = oflow.logp(x_m, torch.zeros_like(x_m), z_o)
+        amask = (torch.arange(TX)[None, :] < x_len[:, None]).float()[:, :, None] * mask
+        attn_o = torch.from_numpy(omas.maximum_path_np(lp_o.numpy(), amask.numpy())).float()
+        zm_o, zl_o = oflow.expand_prior(attn_o, x_m, torch.zeros_like(x_m))
+    loss_o = oflow.mle_loss(z_o, zm_o, zl_o, ld_o, mask)
+    loss_o.backward()
+    # ---- CUDA path
+    yc = y.cuda().requires_grad_(True)
+    mc = mask.cuda()
+    z, ld = dec(yc, mc, g=None if cond is None else cond.cuda())
+    with torch.no_grad():
+        lp = commons.logp(x_m.cuda(), None, z.detach())
+        attn, dur, idx = monotonic_align.maximum_path_full(lp * amask.cuda(), amask.cuda())
+    # the loss couples to the alignment: evaluate it on the ORACLE's alignment on both sides, so that the bound below is
+    # about the flow's arithmetic; what the bf16 path does to the alignment itself is reported (and bounded) separately
+    idx_o = torch.where(attn_o.sum(1) > 0, attn_o.argmax(1), torch.full((1,), -1, dtype=torch.long)).to(torch.int32).cuda()
+    zm = ops.gather_tokens(x_m.cuda(), idx_o, T)
+    loss = commons.mle_loss(z, zm, None, ld, mc)
+    loss.backward()
+    with torch.no_grad():
+        loss_own = commons.mle_loss(z, ops.gather_tokens(x_m.cuda(), idx, T), None, ld, mc).item()
+    agree = float((attn.cpu() == attn_o).float().mean())
+    # MAS: bit-exact given the same value tensor (checked on the oracle's logp); on its own logp the fp32 path must
+    # reproduce the alignment, the bf16 path may move a few frames
+    attn_same_input = monotonic_align.maximum_path(lp_o.cuda() * amask.cuda(), amask.cuda())
+    assert torch.equal(attn_same_input.cpu(), attn_o)
+    frames_moved = float((attn.cpu() - attn_o).abs().sum() / 2)
+    print(f"[configs[1] shape, {precision}, G={gin}] alignment agreement {agree:.6f}, frames moved {frames_moved:.0f} of "
+          f"{int(y_len.sum())}; loss on own alignment {loss_own:.5f} vs reference {loss_o.item():.5f}")
+    assert abs(loss_own - loss_o.item()) < 2e-3 * abs(loss_o.item())
+    if precision == "fp32":
+        assert frames_moved <= 2
+    else:
+        assert frames_moved <= 0.01 * float(y_len.sum())
+    grads = {k: p.grad for k, p in dec.named_parameters() if p.grad is not None}
+    sample = {}
+    for k, v in sd_o.items():
+        if v.grad is None or not (k.startswith("flows.0.") or k.startswith("flows.1.") or k.startswith("flows.2.")
+                                  or k.startswith("flows.17.") or k.startswith("flows.35.") or k.startswith("flows.34.")
+                                  or k.startswith("flows.33.")):
+            continue
+        sample[k] = v.grad.numpy()
+    # the loss couples to the alignment: compare the flow part on identical alignments when they moved
+    want = dict(z=z_o.detach().numpy(), logdet=ld_o.detach().numpy(), loss=loss_o.item(), dy=yo.grad.numpy(), grads=sample)
+    if precision == "fp32":
+        # fp32 at this size: 36 flows deep, |z| ~ 5: keep the 1e-4 relative bar on z/logdet, gradients at 2e-3
+        np.testing.assert_allclose(z.detach().cpu().numpy(), want["z"], rtol=1e-4, atol=1e-4)
+        np.testing.assert_allclose(ld.detach().cpu().numpy(), want["logdet"], rtol=1e-4, atol=1e-2)
+        assert abs(loss.item() - want["loss"]) < 1e-4 * max(1.0, abs(want["loss"]))
+        if frames_moved == 0:
+            assert _rel_l2(yc.grad.cpu(), yo.grad) < 1e-3
+            for k, w in sample.items():
+                e = _rel_l2(grads[k].cpu().reshape(-1), torch.from_numpy(w).reshape(-1))
+                assert e < 2e-3 or np.abs(w).max() < 1e-7, (k, e)
+    else:
+        _check_against(f"configs[1] shape G={gin}", precision, z, ld, loss.item(), yc.grad, grads, want)
+
+
+@pytest.mark.parametrize("last,use_resid", [(False, True), (True, False), (False, False)])
+def test_fused_wn_layer_backward_matches_torch(last, use_resid):
+    """(iii): gtk_tc_wn_bwd_layer (wn_bwd_tc.cu; the largest kernel of the step) against torch autograd of ONE WaveNet
+    layer evaluated on the same bf16-rounded operands; T=301 crosses two tile boundaries of the 124-frame output tiles,
+    ragged lengths, both res/skip widths."""
+    from glowtts_b200 import _lib, ops
+    gen = torch.Generator(device="cuda").manual_seed(21 + int(last))
+    B, H, T, K, dil = 3, 192, 301, 5, 1
+    RS = H if last else 2 * H
+    lengths = torch.tensor([T, T - 40, T // 2], device="cuda")
+    mask = (torch.arange(T, device="cuda")[None, :] < lengths[:, None]).float()
+    win = torch.randn(2 * H, H, K, device="cuda", generator=gen) / (H * K) ** 0.5
+    wrs = torch.randn(RS, H, 1, device="cuda", generator=gen) / H ** 0.5
+    tt = torch.tanh(torch.randn(B, T, H, device="cuda", generator=gen))
+    ss = torch.sigmoid(torch.randn(B, T, H, device="cuda", generator=gen))
+    ts = torch.cat([tt, ss], 2).to(torch.bfloat16)                              # saved activations [B,T,2H]
+    drs = (torch.randn(B, T, RS, device="cuda", generator=gen) * mask[:, :, None]).to(torch.bfloat16)
+    resid = torch.randn(B, T, H, device="cuda", generator=gen) if use_resid else None
+    # ---- reference: same arithmetic in torch fp32 on the rounded operands
+    dacts = F.conv_transpose1d(drs.float().permute(0, 2, 1), _bf(wrs))           # [B,H,T]
+    t_, s_ = ts[:, :, :H].float().permute(0, 2, 1), ts[:, :, H:].float().permute(0, 2, 1)
+    dxin = torch.cat([dacts * s_ * (1 - t_ * t_), dacts * t_ * s_ * (1 - s_)], 1)        # [B,2H,T]
+    dh = F.conv_transpose1d(_bf(dxin), _bf(win), padding=(K - 1) * dil // 2, dilation=dil)  # [B,H,T]
+    want = dh
+    if resid is not None:
+        want = want + resid.permute(0, 2, 1) * mask[:, None, :]
+    want = (want * mask[:, None, :]).permute(0, 2, 1)
+    # ---- kernel
+    tiles = (T + 127) // 128
+
+    def to_tp(x, vec):                      # [B,T,C] -> tile-private layout (see include/glowtts_b200.h)
+        Bq, Tq, C = x.shape
+        xp = torch.zeros(Bq, tiles * 128, C, device=x.device, dtype=x.dtype)
+        xp[:, :Tq] = x
+        return xp.view(Bq, tiles, 128, C // vec, vec).permute(0, 1, 3, 2, 4).contiguous()
+
+    def from_tp(x, C, vec):
+        return x.view(B, tiles, C // vec, 128, vec).permute(0, 1, 3, 2, 4).reshape(B, tiles * 128, C)[:, :T]
+
+    ts_tp = to_tp(ts, 8)
+    resid_tp = to_tp(resid, 4) if resid is not None else None
+    out_tp = torch.zeros(B, tiles, H // 4, 128, 4, device="cuda")
+    dxin_k = torch.zeros(B, T, 2 * H, device="cuda", dtype=torch.bfloat16)
+    out16 = torch.zeros(B, T, H, device="cuda", dtype=torch.bfloat16)
+    wrs_t, win_t = ops.tc_pack_weight(wrs, transpose=True), ops.tc_pack_weight(win, transpose=True)
+    P = lambda t: None if t is None else ctypes.c_void_p(t.data_ptr())
+    _lib.call("gtk_tc_wn_bwd_layer", P(drs), RS, P(wrs_t), P(win_t), P(ts_tp), P(mask), P(resid_tp), P(out_tp), P(dxin_k),
+              P(out16), H, B, T, H, RS, K, dil, ctypes.c_float(0.0), 0, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    got = from_tp(out_tp, H, 4)
+    scale = want.abs().max().item()
+    np.testing.assert_allclose(dxin_k.float().cpu().numpy(), dxin.permute(0, 2, 1).cpu().numpy(), rtol=2e-2,
+                               atol=2e-2 * dxin.abs().max().item())
+    np.testing.assert_allclose(got.cpu().numpy(), want.cpu().numpy(), rtol=5e-3, atol=5e-3 * scale)
+    np.testing.assert_allclose(out16.float().cpu().numpy(), want.cpu().numpy(), rtol=2e-2, atol=2e-2 * scale)
+
+
+def test_modules_without_mask_and_no_jacobian(golden_dir):
+    """(iv): x_mask=None (modules.py:585-586, 639-641; attentions.py:134-135), InvConvNear(no_jacobian=True)
+    (modules.py:655-656) and CouplingBlock(sigmoid_scale=True) against fixtures made by the reference modules."""
+    from glowtts_b200 import attentions, modules
+    TOL = dict(rtol=1e-4, atol=2e-5)
+    g = np.load(os.path.join(golden_dir, "modules_nomask.npz"))
+    x = torch.from_numpy(g["x"]).cuda()
+    an = modules.ActNorm(16).cuda()
+    an.logs.data.copy_(torch.from_numpy(g["an_logs"]))
+    an.bias.data.copy_(torch.from_numpy(g["an_bias"]))
+    z, ld = an(x)
+    np.testing.assert_allclose(z.detach().cpu().numpy(), g["an_z"], **TOL)
+    np.testing.assert_allclose(ld.detach().cpu().numpy(), g["an_logdet"], **TOL)
+    zr, _ = an(x, reverse=True)
+    np.testing.assert_allclose(zr.detach().cpu().numpy(), g["an_zrev"], **TOL)
+    ic = modules.InvConvNear(16, n_split=4).cuda()
+    ic.weight.data.copy_(torch.from_numpy(g["ic_w"]))
+    z, ld = ic(x)
+    np.testing.assert_allclose(z.detach().cpu().numpy(), g["ic_z"], **TOL)
+    np.testing.assert_allclose(ld.detach().cpu().numpy(), g["ic_logdet"], **TOL)
+    zr, _ = ic(x, reverse=True)
+    np.testing.assert_allclose(zr.detach().cpu().numpy(), g["ic_zrev"], **TOL)
+    nj = modules.InvConvNear(16, n_split=4, no_jacobian=True).cuda()
+    nj.weight.data.copy_(torch.from_numpy(g["ic_w"]))
+    mask = oflow.sequence_mask(torch.from_numpy(g["nj_lengths"]), x.shape[2]).float().unsqueeze(1).cuda()
+    z, ld = nj(x, mask)
+    assert ld == 0
+    np.testing.assert_allclose(z.detach().cpu().numpy(), g["nj_z"], **TOL)
+    cfg = dict(helpers.TINY_CFG, n_blocks=1)
+    sd = {k[len("flows.2."):]: v for k, v in helpers.make_state_dict(cfg, 44).items() if k.startswith("flows.2.")}
+    for tag, sig in (("cb", False), ("cbs", True)):
+        cb = attentions.CouplingBlock(16, 16, kernel_size=5, dilation_rate=1, n_layers=2, sigmoid_scale=sig)
+        cb.load_state_dict(sd, strict=True)
+        cb = cb.cuda()
+        z, ld = cb(x)
+        np.testing.assert_allclose(z.detach().cpu().numpy(), g[tag + "_z"], **TOL)
+        np.testing.assert_allclose(ld.detach().cpu().numpy(), g[tag + "_logdet"], rtol=1e-4, atol=1e-4)
+        zr, none = cb(x, reverse=True)
+        assert none is None
+        np.testing.assert_allclose(zr.detach().cpu().numpy(), g[tag + "_zrev"], **TOL)
+
+
+@pytest.mark.parametrize("B,T", [(4, 2000), (256, 250)])
+def test_bf16_reverse_at_config2_corners_vs_oracle(B, T):
+    """(iv): configs[2] corners (T_mel=2000; batch 256) on the bf16 path after store_inverse(): reverse z -> mel against
+    oracle.flow.decoder(reverse=True) on a sample of the batch, and the round trip on all of it."""
+    cfg = helpers.BASE_CFG
+    sd = helpers.make_state_dict(cfg, 4321, end_std=0.01)
+    dec = _decoder(cfg, sd, "bf16").eval()
+    dec.store_inverse()
+    gen = torch.Generator().manual_seed(7)
+    z = torch.randn(B, 80, T, generator=gen)
+    lens = (torch.randint(T // 2, T + 1, (B,), generator=gen) // 2) * 2
+    lens[0] = T
+    mask = (torch.arange(T)[None, :] < lens[:, None]).float().unsqueeze(1)
+    z = z * mask
+    with torch.no_grad():
+        y, _ = dec(z.cuda(), mask.cuda(), reverse=True)
+        z_back, _ = dec(y, mask.cuda())
+    nb = min(B, 2)
+    sd_o = {k: v for k, v in sd.items() if ".wn_pitch." not in k and ".wn_energy." not in k}
+    with torch.no_grad():
+        y_o, _ = oflow.decoder(sd_o, z[:nb], mask[:nb], reverse=True, **_kw(cfg))
+    err = float((y[:nb].cpu() - y_o).abs().max() / y_o.abs().max())
+    rt = float((z_back.cpu() - z).abs().max() / z.abs().max())
+    print(f"[bf16 reverse B={B} T={T}] max|dy|/max|y| vs oracle {err:.2e} (<=2e-2), round trip {rt:.2e} (<=5e-2)")
+    assert err < 2e-2 and rt < 5e-2
+    assert float(y.cpu()[1, :, int(lens[1]):].abs().max() if lens[1] < T else 0.0) == 0.0     # padding stays zero

@@ -180,3 +180,68 @@ def test_clip_grad_value_restatement_matches_reference(norm_type, clip):
     assert abs(got - want) <= 1e-6 * max(1.0, abs(want))
     for p, m in zip(params, mine):
         assert torch.equal(p.grad, m)
+
+
+# ---------------------------------------------------------------------------------- round-2 fixtures
+ROUND2 = {
+    "flow_tiny_sig": (helpers.TINY_CFG, True),
+    "flow_h64": (dict(in_channels=16, hidden_channels=64, kernel_size=5, dilation_rate=1, n_blocks=3, n_layers=3,
+                      n_split=4, n_sqz=2, gin_channels=0), False),
+    "flow_h64_g_sig": (dict(in_channels=16, hidden_channels=64, kernel_size=3, dilation_rate=2, n_blocks=2, n_layers=3,
+                            n_split=4, n_sqz=2, gin_channels=8), True),
+}
+
+
+@pytest.mark.parametrize("name", list(ROUND2))
+def test_round2_decoder_fixtures_incl_sigmoid_scale(golden_dir, name):
+    """sigmoid_scale=True (attentions.py:175-176) and the hidden-64 shapes the tcgen05 path can run."""
+    cfg, sig = ROUND2[name]
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    assert bool(g["sigmoid_scale"]) == sig
+    sd = {k: v.clone().requires_grad_(True) for k, v in helpers.make_state_dict(cfg, int(g["sd_seed"])).items()}
+    y, mask, _, cond = helpers.flow_inputs(cfg, int(g["b"]), int(g["t"]), int(g["in_seed"]), bool(g["use_g"]))
+    y = y.clone().requires_grad_(True)
+    if cond is not None:
+        cond = cond.clone().requires_grad_(True)
+    z, logdet = oflow.decoder(sd, y, mask, g=cond, sigmoid_scale=sig, **_kw(cfg))
+    np.testing.assert_allclose(z.detach().numpy(), g["z"], **TOL)
+    np.testing.assert_allclose(logdet.detach().numpy(), g["logdet"], rtol=1e-4, atol=1e-3)
+    loss = oflow.mle_loss(z, torch.zeros_like(z), torch.zeros_like(z), logdet, mask)
+    assert abs(loss.item() - float(g["loss"])) < 1e-4 * max(1.0, abs(float(g["loss"])))
+    loss.backward()
+    np.testing.assert_allclose(y.grad.numpy(), g["dy"], rtol=1e-3, atol=1e-6)
+    if cond is not None:
+        np.testing.assert_allclose(cond.grad.numpy(), g["dg"], rtol=1e-3, atol=1e-6)
+    for key in [k for k in g.files if k.startswith("grad:")]:
+        got, want = sd[key[5:]].grad.numpy(), g[key]
+        if got.size != want.size:
+            got = got.reshape(-1)[:: max(1, got.size // 2048)]
+        np.testing.assert_allclose(got.reshape(want.shape), want, rtol=2e-3, atol=2e-6, err_msg=key)
+    with torch.no_grad():
+        y_rev, _ = oflow.decoder(sd, z.detach(), mask, g=cond, sigmoid_scale=sig, reverse=True, **_kw(cfg))
+    np.testing.assert_allclose(y_rev.numpy(), g["y_rev"], rtol=1e-4, atol=5e-5)
+
+
+def test_modules_without_mask_and_no_jacobian(golden_dir):
+    """x_mask=None (modules.py:585-586, 639-641; attentions.py:134-135) and InvConvNear(no_jacobian=True)."""
+    g = np.load(os.path.join(golden_dir, "modules_nomask.npz"))
+    x = torch.from_numpy(g["x"])
+    ones = torch.ones(x.shape[0], 1, x.shape[2])
+    z, ld = oflow.actnorm(x, ones, torch.from_numpy(g["an_logs"]), torch.from_numpy(g["an_bias"]))
+    np.testing.assert_allclose(z.numpy(), g["an_z"], **TOL)
+    np.testing.assert_allclose(ld.numpy(), g["an_logdet"], **TOL)
+    w = torch.from_numpy(g["ic_w"])
+    z, ld = oflow.invconvnear(x, ones, w)
+    np.testing.assert_allclose(z.numpy(), g["ic_z"], **TOL)
+    np.testing.assert_allclose(ld.numpy(), g["ic_logdet"], **TOL)
+    mask = oflow.sequence_mask(torch.from_numpy(g["nj_lengths"]), x.shape[2]).float().unsqueeze(1)
+    z, _ = oflow.invconvnear(x, mask, w)
+    np.testing.assert_allclose(z.numpy(), g["nj_z"], **TOL)
+    cfg = dict(helpers.TINY_CFG, n_blocks=1)
+    sd = helpers.make_state_dict(cfg, 44)
+    for tag, sig in (("cb", False), ("cbs", True)):
+        z, ld = oflow.coupling(sd, "flows.2", x, ones, hidden=16, dilation_rate=1, n_layers=2, sigmoid_scale=sig)
+        np.testing.assert_allclose(z.numpy(), g[tag + "_z"], **TOL)
+        np.testing.assert_allclose(ld.numpy(), g[tag + "_logdet"], rtol=1e-4, atol=1e-4)
+        zr, _ = oflow.coupling(sd, "flows.2", x, ones, hidden=16, dilation_rate=1, n_layers=2, sigmoid_scale=sig, reverse=True)
+        np.testing.assert_allclose(zr.numpy(), g[tag + "_zrev"], **TOL)
