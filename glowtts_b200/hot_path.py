@@ -40,6 +40,7 @@ def train_hot_path(decoder, y, y_lengths, x_m, x_logs, x_lengths, g=None, return
     n = decoder.n_sqz
     T_y = (y.shape[2] // n) * n
     y = y[:, :, :T_y]
+    y_lengths = torch.div(y_lengths, n, rounding_mode="floor") * n                      # models.py:1052 (preprocess), on device
     z_mask = sequence_mask(y_lengths, T_y).to(y.dtype).unsqueeze(1)                     # models.py:1054
     z, logdet = decoder(y, z_mask, g=g)
     with torch.no_grad():
