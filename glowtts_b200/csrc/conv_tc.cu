@@ -107,6 +107,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int t0 = blockIdx.x * BT, b = blockIdx.y;
     int out_chunks = 0;                                  // staged [128 x 64] bf16 output tiles to TMA-store at the end
     pdl_trigger();
+    // varlen packing: tiles (pairs of tiles when clustered) with nothing alive leave at once
+    if (p.n_rows && (int)(blockIdx.x & ~(unsigned)(CL - 1)) * BT >= *p.n_rows) return;
     CONV_TRACE(0);
     const int n_iter = p.taps * p.n_k;
     const bool dual = (p.NCH == 1);                      // two interleaved accumulators (see the MMA loop)
@@ -214,6 +216,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int t = t0 + q * 32 + lane;
         const bool t_ok = t < p.T;
         const float mk = (p.mask && t_ok) ? p.mask[(size_t)b * p.T + t] : 1.f;
+        const bool live = mk != 0.f;                     // masked rows are written as exact zeros (never value * 0)
         const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
         const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
         RowIo io;
@@ -232,9 +235,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (p.resid_f32) {
                     float x[16];
                     row_load_f32x16(p.resid_f32, p.ld_resid, c0, io, x);
-                    const float rm = p.mask_resid ? mk : 1.f;
+                    const bool rl = !p.mask_resid || live;
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] += x[i] * rm;
+                    for (int i = 0; i < 16; ++i) v[i] += rl ? x[i] : 0.f;
                 }
                 if (p.resid_tm) {
 #pragma unroll
@@ -242,7 +245,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
                 if (p.mask_out) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] *= mk;
+                    for (int i = 0; i < 16; ++i) v[i] = live ? v[i] : 0.f;
                 }
                 if (p.out_f32) row_store_f32x16(p.out_f32, p.ld_f32, c0, io, v);
                 if (p.out_bf16) stage_bf16x16_sw128(smem, A_BYTES, io.r, c0, v);
@@ -265,8 +268,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 row_load_bf16x16(p.ts, 2 * H, H + c0, io, ss);
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
-                    dt[i] = d[i] * ss[i] * (1.f - tt[i] * tt[i]);
-                    ds[i] = d[i] * tt[i] * ss[i] * (1.f - ss[i]);
+                    dt[i] = live ? d[i] * ss[i] * (1.f - tt[i] * tt[i]) : 0.f;
+                    ds[i] = live ? d[i] * tt[i] * ss[i] * (1.f - ss[i]) : 0.f;
                 }
                 if (p.out2_bf16) {
                     store_bf16x16(p.out2_bf16 + frame * (2 * H) + c0, dt);
@@ -274,10 +277,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
                 if (p.drop_p > 0.f) {
                     float sc[16];
-                    dropout_scale16(dseed, (unsigned long long)frame * (2 * H) + c0, p.drop_p, sc);
+                    const unsigned long long dframe = p.row_fr ? (unsigned long long)p.row_fr[frame] : (unsigned long long)frame;
+                    dropout_scale16(dseed, dframe * (2 * H) + c0, p.drop_p, sc);
 #pragma unroll
                     for (int i = 0; i < 16; ++i) dt[i] *= sc[i];
-                    dropout_scale16(dseed, (unsigned long long)frame * (2 * H) + H + c0, p.drop_p, sc);
+                    dropout_scale16(dseed, dframe * (2 * H) + H + c0, p.drop_p, sc);
 #pragma unroll
                     for (int i = 0; i < 16; ++i) ds[i] *= sc[i];
                 }
@@ -312,10 +316,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     if (p.aff_sigmoid_scale) ll = __logf(1e-6f + sigmoid_f(ll + 2.f));
                     az[o0 + (size_t)i * p.T] = x0[i];
                     if (p.aff_reverse) {
-                        az[o1 + (size_t)i * p.T] = (x1[i] - mm) * __expf(-ll) * mk;
+                        az[o1 + (size_t)i * p.T] = live ? (x1[i] - mm) * __expf(-ll) : 0.f;
                     } else {
-                        az[o1 + (size_t)i * p.T] = (mm + __expf(ll) * x1[i]) * mk;
-                        ld_sum += ll * mk;
+                        az[o1 + (size_t)i * p.T] = live ? mm + __expf(ll) * x1[i] : 0.f;
+                        ld_sum += live ? ll : 0.f;
                     }
                 }
                 if (p.aff_logs_save) {
@@ -325,8 +329,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
             }
             if (!p.aff_reverse && p.aff_logdet) {
-                ld_sum = warp_sum(t_ok ? ld_sum : 0.f);
-                if (lane == 0) atomicAdd(p.aff_logdet + b, ld_sum);
+                if (!t_ok) ld_sum = 0.f;
+                if (p.row_b) {
+                    // packed rows: a warp's 32 rows usually belong to one utterance; at a boundary each lane adds its own
+                    const int ub = p.row_b[frame];
+                    const int ub0 = __shfl_sync(0xffffffffu, ub, 0);
+                    if (__all_sync(0xffffffffu, ub == ub0)) {
+                        ld_sum = warp_sum(ld_sum);
+                        if (lane == 0 && ld_sum != 0.f) atomicAdd(p.aff_logdet + ub0, ld_sum);
+                    } else if (ld_sum != 0.f) {
+                        atomicAdd(p.aff_logdet + ub, ld_sum);
+                    }
+                } else {
+                    ld_sum = warp_sum(ld_sum);
+                    if (lane == 0) atomicAdd(p.aff_logdet + b, ld_sum);
+                }
             }
         }
         if (out_chunks) fence_proxy_async_smem();
@@ -391,11 +408,12 @@ int pack_weight_bf16(const float* w, __nv_bfloat16* out, int M, int Cin, int K, 
 
 // x fp32 t-major [B, C, T] channels [c0, c0+nc) -> bf16 frame-major out[b][t][0..ld): columns >= nc are zero.
 __global__ void frames_from_tmajor_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int C, int T, int c0,
-                                          int nc, int ld) {
+                                          int nc, int ld, const int* __restrict__ n_rows) {
     __shared__ float tile[32][33];
     pdl_trigger();
     pdl_wait();
     const int b = blockIdx.z, tt = blockIdx.x * 32, cc = blockIdx.y * 32;
+    if (n_rows && tt >= ((*n_rows + 127) & ~127)) return;       // varlen packing: nothing lives behind the last 128-row tile
     const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
     for (int i = ty; i < 32; i += 8) {
         const int c = cc + i, t = tt + tx;
@@ -407,11 +425,12 @@ __global__ void frames_from_tmajor_kernel(const float* __restrict__ x, __nv_bflo
         if (t < T && c < ld) out[((size_t)b * T + t) * ld + c] = __float2bfloat16_rn(tile[tx][i]);
     }
 }
-int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, int c0, int nc, int ld, cudaStream_t st) {
+int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, int c0, int nc, int ld, cudaStream_t st,
+                       const int* n_rows) {
     GTK_REQUIRE(x && out && c0 >= 0 && c0 + nc <= C && ld >= nc, "bad args");
     if ((long long)B * T * ld == 0) return GTK_OK;
     dim3 grid(ceil_div(T, 32), ceil_div(ld, 32), B);
-    GTK_CUDA(launch_pdl(frames_from_tmajor_kernel, grid, dim3(32, 8), 0, st, x, out, C, T, c0, nc, ld));
+    GTK_CUDA(launch_pdl(frames_from_tmajor_kernel, grid, dim3(32, 8), 0, st, x, out, C, T, c0, nc, ld, n_rows));
     return check_launch("frames_from_tmajor");
 }
 
@@ -533,14 +552,17 @@ int fold_pack(FoldPackJobs& jobs, cudaStream_t st) {
 __global__ void affine_bwd_frames_kernel(const float* __restrict__ x, const float* __restrict__ logs_raw,
                                          const float* __restrict__ mask, const float* __restrict__ dz,
                                          const float* __restrict__ dlogdet, __nv_bfloat16* __restrict__ dend, int ld,
-                                         float* __restrict__ dx, int B, int C, int T, int sigmoid_scale) {
+                                         float* __restrict__ dx, int B, int C, int T, int sigmoid_scale,
+                                         const int* __restrict__ row_b, const int* __restrict__ n_rows) {
     const int Ch = C / 2;
     pdl_trigger();
     pdl_wait();
     const int n_chunk = (Ch + 7) / 8, n_pad = (ld - C + 7) / 8;      // channel chunks + zero-padding chunks
     const long long frames = (long long)B * T, total = frames * (n_chunk + n_pad);
+    const long long f_lim = n_rows ? (long long)((*n_rows + 127) & ~127) : frames;      // varlen packing (B == 1)
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const long long f = i % frames;
+        if (f >= f_lim) continue;
         const int chunk = (int)(i / frames);
         const int b = (int)(f / T), t = (int)(f % T);
         __nv_bfloat16* row = dend + (size_t)f * ld;
@@ -551,7 +573,7 @@ __global__ void affine_bwd_frames_kernel(const float* __restrict__ x, const floa
             continue;
         }
         const float mk = mask ? mask[f] : 1.f;
-        const float dl = dlogdet ? dlogdet[b] * mk : 0.f;
+        const float dl = dlogdet ? dlogdet[row_b ? row_b[f] : b] * mk : 0.f;
         const int c0 = chunk * 8;
         const bool vec = (Ch % 8 == 0) && (ld % 8 == 0);          // 16-byte aligned 8-channel groups
         float gm[8], gl[8], raw8[8], dz8[8], x8[8];
@@ -613,13 +635,14 @@ __global__ void affine_bwd_frames_kernel(const float* __restrict__ x, const floa
     }
 }
 int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, const float* dz, const float* dlogdet,
-                      __nv_bfloat16* dend, int ld, float* dx, int B, int C, int T, int sigmoid_scale, cudaStream_t st) {
+                      __nv_bfloat16* dend, int ld, float* dx, int B, int C, int T, int sigmoid_scale, const int* row_b,
+                      const int* n_rows, cudaStream_t st) {
     GTK_REQUIRE(x && logs_raw && dz && dend && dx && C % 2 == 0 && ld >= C, "bad args");
     const long long total = (long long)B * T * ((C / 2 + 7) / 8 + (ld - C + 7) / 8);
     if (total == 0) return GTK_OK;
     ProfScope prof("affine_bwd_frames", st);
     GTK_CUDA(launch_pdl(affine_bwd_frames_kernel, dim3((unsigned)ceil_div_ll(total, 128)), dim3(128), 0, st, x, logs_raw, mask, dz,
-                        dlogdet, dend, ld, dx, B, C, T, sigmoid_scale));
+                        dlogdet, dend, ld, dx, B, C, T, sigmoid_scale, row_b, n_rows));
     return check_launch("affine_bwd_frames");
 }
 

@@ -245,10 +245,13 @@ template <> struct alignas(16) VecF<4> { float v[4]; };
 template <int NS, bool REVERSE, int VEC>
 __global__ void __launch_bounds__(PW_NT) mix_kernel(const float* __restrict__ x, const float* __restrict__ mask,
                                                     const float* __restrict__ logs, const float* __restrict__ bias,
-                                                    const float* __restrict__ M, float* __restrict__ z, int B, int C, int T) {
+                                                    const float* __restrict__ M, float* __restrict__ z, int B, int C, int T,
+                                                    const int* __restrict__ n_rows) {
     __shared__ float sM[NS * NS];
     pdl_trigger();
     pdl_wait();
+    // varlen packing (B == 1): rows at or behind n_rows rounded up to a whole 128-row tile hold nothing
+    const int t_lim = n_rows ? ((*n_rows + 127) & ~127) : T;
     if (threadIdx.x < NS * NS) sM[threadIdx.x] = M ? M[threadIdx.x] : ((threadIdx.x / NS == threadIdx.x % NS) ? 1.f : 0.f);
     __syncthreads();
     const int g = blockIdx.y;
@@ -264,6 +267,7 @@ __global__ void __launch_bounds__(PW_NT) mix_kernel(const float* __restrict__ x,
     const int total = B * TV;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int b = i / TV, t = (i - b * TV) * VEC;
+        if (t >= t_lim) continue;
         VecF<VEC> m, v[NS], o[NS];
         if (mask) m = *reinterpret_cast<const VecF<VEC>*>(mask + (size_t)b * T + t);
         else {
@@ -302,7 +306,7 @@ static inline int pw_vec(int T, const void* a, const void* b, const void* c = nu
 
 template <int NS>
 static int mix_launch(const float* x, const float* mask, const float* logs, const float* bias, const float* M, float* z,
-                      int B, int C, int T, int reverse, cudaStream_t st) {
+                      int B, int C, int T, int reverse, const int* n_rows, cudaStream_t st) {
     const int G = C / NS;
     if ((long long)B * G * T == 0) return GTK_OK;
     GTK_REQUIRE((long long)B * T < (1ll << 31), "B * T too large");
@@ -313,7 +317,7 @@ static int mix_launch(const float* x, const float* mask, const float* logs, cons
     if (gx < 1) gx = 1;
     const dim3 grid(gx, G), block(PW_NT);
     ProfScope prof("mix", st);
-#define GTK_MIX(R, V) GTK_CUDA(launch_pdl(mix_kernel<NS, R, V>, grid, block, 0, st, x, mask, logs, bias, M, z, B, C, T))
+#define GTK_MIX(R, V) GTK_CUDA(launch_pdl(mix_kernel<NS, R, V>, grid, block, 0, st, x, mask, logs, bias, M, z, B, C, T, n_rows))
     if (reverse) { if (vec == 4) GTK_MIX(true, 4); else if (vec == 2) GTK_MIX(true, 2); else GTK_MIX(true, 1); }
     else         { if (vec == 4) GTK_MIX(false, 4); else if (vec == 2) GTK_MIX(false, 2); else GTK_MIX(false, 1); }
 #undef GTK_MIX
@@ -321,16 +325,17 @@ static int mix_launch(const float* x, const float* mask, const float* logs, cons
 }
 
 int mix(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int ns, float* z, int B,
-        int C, int T, int reverse, cudaStream_t st) {
+        int C, int T, int reverse, cudaStream_t st, const int* n_rows) {
+    GTK_REQUIRE(!n_rows || B == 1, "packed rows are one long sequence");
     GTK_REQUIRE(x && z, "null");
     GTK_REQUIRE((logs == nullptr) == (bias == nullptr), "logs and bias go together");
     GTK_REQUIRE(ns == 1 || ns == 2 || ns == 4 || ns == 8, "n_split must be 1 (no mix), 2, 4 or 8");
     GTK_REQUIRE(C % ns == 0, "channels % n_split != 0");
     switch (ns) {
-        case 1: return mix_launch<1>(x, mask, logs, bias, M, z, B, C, T, reverse, st);
-        case 2: return mix_launch<2>(x, mask, logs, bias, M, z, B, C, T, reverse, st);
-        case 4: return mix_launch<4>(x, mask, logs, bias, M, z, B, C, T, reverse, st);
-        default: return mix_launch<8>(x, mask, logs, bias, M, z, B, C, T, reverse, st);
+        case 1: return mix_launch<1>(x, mask, logs, bias, M, z, B, C, T, reverse, n_rows, st);
+        case 2: return mix_launch<2>(x, mask, logs, bias, M, z, B, C, T, reverse, n_rows, st);
+        case 4: return mix_launch<4>(x, mask, logs, bias, M, z, B, C, T, reverse, n_rows, st);
+        default: return mix_launch<8>(x, mask, logs, bias, M, z, B, C, T, reverse, n_rows, st);
     }
 }
 
@@ -341,11 +346,12 @@ template <int NS, int VEC>
 __global__ void __launch_bounds__(PW_NT) mix_bwd_kernel(const float* __restrict__ x, const float* __restrict__ mask, const float* __restrict__ logs,
                                const float* __restrict__ bias, const float* __restrict__ M, const float* dz, float* dx,
                                float* __restrict__ dlogs, float* __restrict__ dbias, float* __restrict__ dM, int B, int C,
-                               int T) {
+                               int T, const int* __restrict__ n_rows) {
     __shared__ float sM[NS * NS];
     __shared__ float red[(2 * NS + NS * NS) * (PW_NT / 32)];
     pdl_trigger();
     pdl_wait();
+    const int t_lim = n_rows ? ((*n_rows + 127) & ~127) : T;      // varlen packing (B == 1): see mix_kernel
     if (threadIdx.x < NS * NS) sM[threadIdx.x] = M ? M[threadIdx.x] : ((threadIdx.x / NS == threadIdx.x % NS) ? 1.f : 0.f);
     __syncthreads();
     const int g = blockIdx.y;
@@ -366,6 +372,7 @@ __global__ void __launch_bounds__(PW_NT) mix_bwd_kernel(const float* __restrict_
     const int total = B * TV;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int b = i / TV, t = (i - b * TV) * VEC;
+        if (t >= t_lim) continue;
         VecF<VEC> m, xq[NS], gq[NS], oq[NS];
         if (mask) m = *reinterpret_cast<const VecF<VEC>*>(mask + (size_t)b * T + t);
         else {
@@ -430,8 +437,10 @@ __global__ void __launch_bounds__(PW_NT) mix_bwd_kernel(const float* __restrict_
 }
 
 int mix_bwd(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int ns,
-            const float* dz, float* dx, float* dlogs, float* dbias, float* dM, int B, int C, int T, cudaStream_t st) {
+            const float* dz, float* dx, float* dlogs, float* dbias, float* dM, int B, int C, int T, cudaStream_t st,
+            const int* n_rows) {
     GTK_REQUIRE(x && dz && dx, "null");
+    GTK_REQUIRE(!n_rows || B == 1, "packed rows are one long sequence");
     GTK_REQUIRE(ns == 1 || ns == 2 || ns == 4 || ns == 8, "n_split must be 1 (no mix), 2, 4 or 8");
     GTK_REQUIRE(C % ns == 0, "channels % n_split != 0");
     if ((long long)B * C * T == 0) return GTK_OK;
@@ -444,7 +453,7 @@ int mix_bwd(const float* x, const float* mask, const float* logs, const float* b
     if (gx < 1) gx = 1;
     dim3 grid(gx, G);
     ProfScope prof("mix_bwd", st);
-#define GTK_MIXB(N, V) GTK_CUDA(launch_pdl(mix_bwd_kernel<N, V>, grid, dim3(PW_NT), 0, st, x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T))
+#define GTK_MIXB(N, V) GTK_CUDA(launch_pdl(mix_bwd_kernel<N, V>, grid, dim3(PW_NT), 0, st, x, mask, logs, bias, M, dz, dx, dlogs, dbias, dM, B, C, T, n_rows))
 #define GTK_MIXB_V(N) do { if (vec == 4) GTK_MIXB(N, 4); else if (vec == 2) GTK_MIXB(N, 2); else GTK_MIXB(N, 1); } while (0)
     switch (ns) {
         case 1: GTK_MIXB_V(1); break;

@@ -28,6 +28,15 @@ int squeeze(const float* x, const float* mask, float* out, float* mask_out, int 
 int unsqueeze(const float* x, const float* mask, float* out, float* mask_out, int B, int C, int T, int n, int out_T,
               cudaStream_t st);
 int mask_len(const float* mask, float* x_len, int B, int T, cudaStream_t st);
+// varlen packing of the decoder's working set (pack.cu)
+int pack_plan(const float* mask, int B, int T, int n, int Tq, int G, int P, int* hdr, int* off, int* row_b, int* row_fr,
+              float* mask_p, float* x_len, cudaStream_t st);
+int squeeze_pack(const float* x, const int* off, const int* row_b, const float* mask_p, float* xp, int C, int T_in, int n, int P,
+                 cudaStream_t st);
+int unsqueeze_unpack(const float* xp, const int* off, float* out, int B, int C, int T_out, int n, int G, int P, cudaStream_t st);
+int pack_track(const float* track, const int* off, const int* row_b, const float* mask_p, float* trk, int T_in, int n, int P,
+               cudaStream_t st);
+int unpack_track(const float* dtrk, const int* off, float* dtrack, int B, int T_out, int n, int G, cudaStream_t st);
 int invconv_prep(const float* w, int ns, float* winv, float* logdet, cudaStream_t st);
 // per-call constants of up to FLOW_CONST_MAX_BLOCKS flow blocks in one launch (flow_pointwise.cu)
 constexpr int FLOW_CONST_MAX_BLOCKS = 32;
@@ -46,10 +55,11 @@ struct FlowConstGrads {
 int flow_consts(const FlowConstJobs& J, int ns, int C, const float* x_len, float* logdet, int B, int accumulate, cudaStream_t st);
 int logdet_const_bwd_all(const float* dlogdet, const float* x_len, int B, const FlowConstGrads& G, int C, const float* winv, int ns,
                          cudaStream_t st);
+// n_rows: null, or (varlen packing, B == 1) device pointer to the number of rows in use: rows behind it are skipped
 int mix(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int ns, float* z, int B,
-        int C, int T, int reverse, cudaStream_t st);
+        int C, int T, int reverse, cudaStream_t st, const int* n_rows = nullptr);
 int mix_bwd(const float* x, const float* mask, const float* logs, const float* bias, const float* M, int ns, const float* dz,
-            float* dx, float* dlogs, float* dbias, float* dM, int B, int C, int T, cudaStream_t st);
+            float* dx, float* dlogs, float* dbias, float* dM, int B, int C, int T, cudaStream_t st, const int* n_rows = nullptr);
 int logdet_const(const float* logs, int C, const float* logdetW, float group_count, const float* x_len, float* logdet, int B,
                  int accumulate, cudaStream_t st);
 int logdet_const_bwd(const float* dlogdet, const float* x_len, int B, float* dlogs, int C, const float* winv, int ns,

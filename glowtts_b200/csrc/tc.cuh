@@ -31,6 +31,10 @@ struct ConvTcParams {
     int cluster;                   // 1 or 2 CTAs per cluster (2: the weight tile is fetched once per pair, TMA multicast)
     int trace;                     // 1: record per-CTA phase timestamps (conv_trace_select)
     int ctl_off;                   // byte offset of the control block behind the operand stages / output staging area
+    // ---- varlen packing (pack.cu; all null for plain [B, T] tensors)
+    const int* n_rows;             // device: rows in use; tiles at or behind it exit at once
+    const int* row_b;              // device [T]: utterance of a packed row (per-utterance logdet / dlogdet)
+    const int* row_fr;             // device [T]: un-packed frame index b * T' + t of a packed row (dropout counter)
     // ---- plain epilogue: v = acc + bias[n] (+ resid) ; optional mask ; stores
     const float* bias;             // [N] or null
     const float* mask;             // [B, T] or null
@@ -71,6 +75,16 @@ struct WnLayerParams {
     const float* bias_rs;          // [RS]
     const float* cond;             // this layer's slice of cond_layer(g): cond[b * cond_bstride + n], n < 2H; or null
     size_t cond_bstride;
+    const int* n_rows;             // varlen packing (pack.cu): rows in use / utterance of a row / un-packed frame of a row
+    const int* row_b;
+    const int* row_fr;
+    // time-varying rank-1 conditioner of WNP (modules.py:320-322, 353-362): pre += cw[n] * trk[row * n_sqz + phase(n)] + cb[n]
+    const float* trk;              // [T, n_sqz] packed pitch / energy samples of each row, or null
+    const float* cw;               // [2H] cond_layer1 effective weight of this layer's channels
+    const float* cb;               // [2H] cond_layer1 bias of this layer's channels
+    int n_sqz, cs_div;             // phase of channel n: (cs_base + n) / cs_div  (cs_div = 2HL / n_sqz)
+    int cs_base;                   // layer * 2H
+    float* h_out_f32_last;         // last layer: masked WN output also as fp32 tile-private master (input of a chained WN)
     const float* mask;             // [B, T]
     float drop_p;
     DropSeed drop_seed;
@@ -94,6 +108,10 @@ struct WnBwdParams {
     DropSeed drop_seed;
     const float* resid_f32;        // fp32 carry of d(h) from the layer above (tile-private layout, ld = H) or null
     float* out_f32;                // fp32 carry written for the layer below (tile-private layout, ld = H)
+    const int* n_rows;             // varlen packing (pack.cu), or null
+    const int* row_fr;
+    __nv_bfloat16* dpre;           // [B,T,2H] frames or null: gate-input gradient BEFORE the dropout scale (what the
+                                   // conditioners' gradients are reduced from when p_dropout > 0; == d(xin) when it is 0)
 };
 bool wn_bwd_supported(int H, int taps, int dil);
 // drs: [B,T,ld_drs] frames (columns [0,RS) = [d(h_next) mask | d(skip)]); wrs_t / win_t: data-gradient weight packs;
@@ -129,11 +147,18 @@ struct WgradGroupJob {
     int M, Cin, K, dil;
 };
 size_t wgrad_group_workspace_bytes();
-int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, cudaStream_t st);
+// n_rows: null, or (varlen packing, B == 1) device pointer to hdr[1] of the packing plan {0, n_rows}: rows in use
+int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, const int* n_rows, cudaStream_t st);
+// out[g * out_gstride + n] += sum of rows [seg[g], seg[g + 1]) (device-resident bounds) of frames in[.., n]
+int colsum_frames_seg(const __nv_bfloat16* in, int ld, int n_cols, int groups, const int* seg, float* out, size_t out_gstride,
+                      cudaStream_t st);
+int zero_guard_rows(__nv_bfloat16* base, size_t stride_bytes, int n_buf, int ld, const int* n_rows, int n_guard, int T,
+                    cudaStream_t st);
 int colsum_frames(const __nv_bfloat16* in, int ld, int n_cols, int groups, long long rows_per_group, float* out, size_t out_gstride,
                   cudaStream_t st);
 int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, const float* dz, const float* dlogdet,
-                      __nv_bfloat16* dend, int ld, float* dx, int B, int C, int T, int sigmoid_scale, cudaStream_t st);
+                      __nv_bfloat16* dend, int ld, float* dx, int B, int C, int T, int sigmoid_scale, const int* row_b,
+                      const int* n_rows, cudaStream_t st);
 // Fold (weight norm) + bf16 pack of up to FOLD_PACK_MAX_JOBS conv weights in one launch (conv_tc.cu).
 constexpr int FOLD_PACK_MAX_JOBS = 320;
 struct FoldPackJob {
@@ -148,7 +173,8 @@ struct FoldPackJobs { FoldPackJob job[FOLD_PACK_MAX_JOBS]; int n; };
 int fold_pack(FoldPackJobs& jobs, cudaStream_t st);
 int conv_tc_launch(const __nv_bfloat16* in, int ld_in, const __nv_bfloat16* wp, ConvTcParams p, int epi, cudaStream_t st);
 int pack_weight_bf16(const float* w, __nv_bfloat16* out, int M, int Cin, int K, int transpose, int rows, int cols, cudaStream_t st);
-int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, int c0, int nc, int ld, cudaStream_t st);
+int frames_from_tmajor(const float* x, __nv_bfloat16* out, int B, int C, int T, int c0, int nc, int ld, cudaStream_t st,
+                       const int* n_rows = nullptr);
 
 #ifdef __CUDACC__
 // ---------------------------------------------------------------------------------- device: TMA

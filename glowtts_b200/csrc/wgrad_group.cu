@@ -38,6 +38,7 @@ struct GgCta { unsigned short seg0, nseg; };
 
 struct GgParams {
     int B, T, chunks_t;
+    const int* n_rows;                           // varlen packing (B == 1): only rows [0, *n_rows) hold data, or null
     float* part;                                 // [slots][128][256] fp32
     GgJobDev job[WGG_MAX_JOBS];
     GgTile tile[WGG_MAX_TILES];
@@ -58,6 +59,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const GgCta me = p.cta[blockIdx.x];
     pdl_trigger();
+    // The host cut every tile's k-steps [0, S_max) into contiguous shares.  With packed rows only the first S_val steps
+    // hold data: every segment boundary is rescaled by S_val / S_max (monotone, so the segments still tile [0, S_val)
+    // and the shares stay balanced).  A segment that becomes empty writes a zero partial tile.
+    const long long S_max = (long long)p.B * p.chunks_t;
+    const long long S_val = p.n_rows ? min(S_max, (long long)ceil_div(*p.n_rows, GG_TK)) : S_max;
+#define GG_SCALE(s) ((int)((long long)(s) * S_val / S_max))
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < GG_STAGES; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
@@ -91,7 +98,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
                 const int m0 = Tl.m_tile * 128;
                 const int shift = ((int)Tl.tap - J.taps / 2) * J.dil;
                 const uint32_t bytes = (uint32_t)(2 + J.n_blk) * GG_BOX;
-                for (int step = S.s_lo; step < S.s_hi; ++step, ++it) {
+                const int s_lo = GG_SCALE(S.s_lo), s_hi = GG_SCALE(S.s_hi);
+                for (int step = s_lo; step < s_hi; ++step, ++it) {
                     const int s = it % GG_STAGES, use = it / GG_STAGES;
                     if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
                     const int b = step / p.chunks_t, t0 = (step % p.chunks_t) * GG_TK;
@@ -107,18 +115,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            int it = 0;
+            int it = 0, ne = 0;                            // ne: non-empty segments so far (accumulator hand-shake parity)
             for (int sg = 0; sg < me.nseg; ++sg) {
                 const GgSeg S = p.seg[me.seg0 + sg];
                 const GgTile Tl = p.tile[S.tile];
                 const GgJobDev J = p.job[Tl.job];
+                const int s_lo = GG_SCALE(S.s_lo), s_hi = GG_SCALE(S.s_hi);
+                if (s_hi <= s_lo) continue;
                 const int N = (J.ones && Tl.tap == 0) ? (GG_ONES_BLK + 1) * 64 : J.n_blk * 64;
                 const uint32_t idesc = umma_idesc_bf16(128, N, 1, 1);
                 // Two accumulators (TMEM columns 0.. and 256..) take alternate k16 steps: back-to-back MMAs into one
                 // accumulator serialise on its read-modify-write latency.  The epilogue adds them; the next segment
                 // starts when it has drained both (segments are ~100 k-steps long, the drain is a few per cent).
-                if (sg > 0) { mbar_wait(&ctl->acc_empty[0], (sg - 1) & 1); tc_fence_after(); }
-                for (int step = S.s_lo; step < S.s_hi; ++step, ++it) {
+                if (ne > 0) { mbar_wait(&ctl->acc_empty[0], (ne - 1) & 1); tc_fence_after(); }
+                for (int step = s_lo; step < s_hi; ++step, ++it) {
                     const int s = it % GG_STAGES, use = it / GG_STAGES;
                     mbar_wait(&ctl->full[s], use & 1);
                     tc_fence_after();
@@ -128,23 +138,31 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
                     for (int k = 0; k < GG_TK / 16; ++k) {
                         const uint64_t adesc = umma_desc_mnmajor_sw128(sa + k * 2048, GG_BOX, 1024);
                         const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + k * 2048, GG_BOX, 1024);
-                        umma_bf16(tmem + (k & 1) * 256, adesc, bdesc, idesc, (step != S.s_lo) || k >= 2);
+                        umma_bf16(tmem + (k & 1) * 256, adesc, bdesc, idesc, (step != s_lo) || k >= 2);
                     }
                     umma_commit(&ctl->empty[s]);
                 }
                 umma_commit(&ctl->acc_full[0]);
+                ++ne;
             }
         }
     } else if (warp >= 4) {
         const int q = warp & 3;
+        int ne = 0;
         for (int sg = 0; sg < me.nseg; ++sg) {
             const GgSeg S = p.seg[me.seg0 + sg];
             const GgTile Tl = p.tile[S.tile];
             const GgJobDev J = p.job[Tl.job];
-            mbar_wait(&ctl->acc_full[0], sg & 1);
+            float* prow = p.part + (size_t)S.slot * GG_SLOT_FLOATS + (size_t)(q * 32 + lane) * 256;
+            if (GG_SCALE(S.s_hi) <= GG_SCALE(S.s_lo)) {              // empty share: its partial tile is zero
+                for (int c0 = 0; c0 < J.n_blk * 64; c0 += 4) *reinterpret_cast<float4*>(prow + c0) = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (J.ones && Tl.tap == 0) prow[GG_ONES_BLK * 64] = 0.f;
+                continue;
+            }
+            mbar_wait(&ctl->acc_full[0], ne & 1);
+            ++ne;
             tc_fence_after();
             const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
-            float* prow = p.part + (size_t)S.slot * GG_SLOT_FLOATS + (size_t)(q * 32 + lane) * 256;
             for (int c0 = 0; c0 < J.n_blk * 64; c0 += 16) {
                 float v[16];
                 tmem_ld16_dual(trow + c0, true, v);
@@ -273,14 +291,15 @@ static int tmap_frames(CUtensorMap* out, const __nv_bfloat16* base, int ld, int 
     return make_tmap_bf16(out, base, 3, dims, strides, box, true);
 }
 
-int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, cudaStream_t st) {
+int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, const int* n_rows, cudaStream_t st) {
     GTK_REQUIRE(jobs && n_jobs >= 1 && n_jobs <= WGG_MAX_JOBS && part_ws, "bad job list");
     if ((long long)B * T == 0) return GTK_OK;
     static thread_local GgParams P;                 // ~12 KB of kernel parameters, rebuilt per launch
     static thread_local GgRedParams R;
     memset(&P, 0, sizeof(P));
     memset(&R, 0, sizeof(R));
-    P.B = B; P.T = T; P.chunks_t = ceil_div(T, GG_TK); P.part = part_ws;
+    GTK_REQUIRE(!n_rows || B == 1, "packed rows are one long sequence");
+    P.B = B; P.T = T; P.chunks_t = ceil_div(T, GG_TK); P.part = part_ws; P.n_rows = n_rows;
     R.part = part_ws; R.n_jobs = n_jobs;
     const int S = B * P.chunks_t;
     GTK_REQUIRE(S <= 65535, "too many k-steps for the segment table");
@@ -366,7 +385,8 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     for (int q = 0; q < n_jobs; ++q) {
         const WgradGroupJob& J = jobs[q];
         if (!J.db || P.job[q].ones) continue;
-        int rc = colsum_frames(J.dy, J.ld_y, J.M, 1, (long long)B * T, J.db, 0, st);
+        int rc = n_rows ? colsum_frames_seg(J.dy, J.ld_y, J.M, 1, n_rows - 1, J.db, 0, st)     // hdr = {0, n_rows}
+                        : colsum_frames(J.dy, J.ld_y, J.M, 1, (long long)B * T, J.db, 0, st);
         if (rc) return rc;
     }
     return GTK_OK;

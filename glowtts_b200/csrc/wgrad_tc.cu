@@ -263,5 +263,56 @@ int colsum_frames(const __nv_bfloat16* in, int ld, int n_cols, int groups, long 
     return check_launch("colsum_frames");
 }
 
+// The same with device-resident group bounds (varlen packing: utterance b = rows [off[b], off[b+1]); whole batch =
+// {0, n_rows}).  grid.y = groups * SEG_SPLITS row slices.
+constexpr int SEG_SPLITS = 8;
+__global__ void colsum_frames_seg_kernel(const __nv_bfloat16* __restrict__ in, int ld, int n_cols, const int* __restrict__ seg,
+                                         float* __restrict__ out, size_t out_gstride) {
+    const int g = blockIdx.y / SEG_SPLITS, rs = blockIdx.y % SEG_SPLITS;
+    const int n = blockIdx.x * 64 + (threadIdx.x & 63);
+    const int rl = threadIdx.x >> 6;
+    const long long lo = seg[g], len = (long long)seg[g + 1] - lo;
+    const long long r_lo = lo + len * rs / SEG_SPLITS, r_hi = lo + len * (rs + 1) / SEG_SPLITS;
+    float acc = 0.f;
+    if (n < n_cols)
+        for (long long r = r_lo + rl; r < r_hi; r += 4) acc += __bfloat162float(in[(size_t)r * ld + n]);
+    __shared__ float red[256];
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    if (rl == 0 && n < n_cols) {
+        const float s = red[threadIdx.x] + red[threadIdx.x + 64] + red[threadIdx.x + 128] + red[threadIdx.x + 192];
+        if (s != 0.f) atomicAdd(out + (size_t)g * out_gstride + n, s);
+    }
+}
+int colsum_frames_seg(const __nv_bfloat16* in, int ld, int n_cols, int groups, const int* seg, float* out, size_t out_gstride,
+                      cudaStream_t st) {
+    GTK_REQUIRE(in && out && seg, "null");
+    if (groups == 0 || n_cols == 0) return GTK_OK;
+    dim3 grid(ceil_div(n_cols, 64), groups * SEG_SPLITS);
+    colsum_frames_seg_kernel<<<grid, 256, 0, st>>>(in, ld, n_cols, seg, out, out_gstride);
+    return check_launch("colsum_frames_seg");
+}
+
+// Zero rows [round_up(n_rows, 128), + n_guard) of `n_buf` bf16 frame buffers (row pitch ld, `stride` bytes apart).
+// Varlen packing: kernels never write behind the last 128-row tile in use, but the weight-gradient GEMM reads the conv
+// input up to (K/2) dil rows past its last k-step; those rows only ever meet zero output-gradient rows, and 0 x garbage
+// must not be 0 x NaN.
+__global__ void zero_guard_rows_kernel(unsigned char* base, size_t stride, int ld, const int* __restrict__ n_rows, int n_guard,
+                                       int T) {
+    const int r0 = (*n_rows + 127) & ~127;
+    const int rows = min(n_guard, T - r0);
+    if (rows <= 0) return;
+    uint4* dst = reinterpret_cast<uint4*>(base + (size_t)blockIdx.x * stride + (size_t)r0 * ld * 2);
+    const int n16 = rows * ld * 2 / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+int zero_guard_rows(__nv_bfloat16* base, size_t stride_bytes, int n_buf, int ld, const int* n_rows, int n_guard, int T,
+                    cudaStream_t st) {
+    GTK_REQUIRE(base && n_rows && ld % 8 == 0, "bad args");
+    if (n_buf == 0 || n_guard == 0) return GTK_OK;
+    zero_guard_rows_kernel<<<n_buf, 256, 0, st>>>(reinterpret_cast<unsigned char*>(base), stride_bytes, ld, n_rows, n_guard, T);
+    return check_launch("zero_guard_rows");
+}
+
 }  // namespace tc
 }  // namespace gtk

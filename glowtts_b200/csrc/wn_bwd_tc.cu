@@ -78,6 +78,9 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
     const int t0 = blockIdx.x * tile_out, b = blockIdx.y;
     const int n_b = p.taps * nkb;
     pdl_trigger();
+    // varlen packing: a pair of tiles with nothing alive leaves at once (pair-uniform: the peer's barriers are involved).
+    // Every kernel uses the same limit, n_rows rounded up to whole 128-row tiles: all rows below it are always written.
+    if (p.n_rows && (int)(blockIdx.x & ~(unsigned)(WB_CL - 1)) * tile_out >= ((*p.n_rows + BT - 1) & ~(BT - 1))) return;
     WB_TRACE(0);
 
     const uint32_t cta_rank = cluster_ctarank();
@@ -160,8 +163,14 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
     const int nck = H / 16;
     {
         const int f = t0 - halo + r;
-        const bool ok = f >= 0 && f < p.T;
+        const bool in_t = f >= 0 && f < p.T;
+        // masked frames carry no gradient (d(skip) and d(h) are masked there): exact zeros, whatever the saved
+        // activations of such a row hold
+        const bool ok = in_t && (!p.mask || p.mask[(size_t)b * p.T + f] != 0.f);
         const RowIo io = frame_io(b, ok ? f : 0, p.T);
+        const unsigned long long dframe = p.row_fr ? (unsigned long long)p.row_fr[io.frame] : (unsigned long long)io.frame;
+        const bool own = in_t && r >= halo && r < halo + tile_out;      // tiles overlap by the halo: owned frames only
+        __nv_bfloat16* dpre_row = (p.dpre && own) ? p.dpre + ((size_t)b * p.T + f) * H2 : nullptr;
         const unsigned long long dseed = p.drop_p > 0.f ? drop_resolve(p.drop_seed) : 0ull;
         mbar_wait(&ctl->acc_full, 0);
         tc_fence_after();
@@ -179,18 +188,20 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
                     dt[i] = d[i] * ss[i] * (1.f - tt[i] * tt[i]);
                     ds[i] = d[i] * tt[i] * ss[i] * (1.f - ss[i]);
                 }
+                if (dpre_row) { store_bf16x16(dpre_row + c0, dt); store_bf16x16(dpre_row + H + c0, ds); }
                 if (p.drop_p > 0.f) {
                     float sc[16];
-                    dropout_scale16(dseed, (unsigned long long)io.frame * H2 + c0, p.drop_p, sc);
+                    dropout_scale16(dseed, dframe * H2 + c0, p.drop_p, sc);
 #pragma unroll
                     for (int i = 0; i < 16; ++i) dt[i] *= sc[i];
-                    dropout_scale16(dseed, (unsigned long long)io.frame * H2 + H + c0, p.drop_p, sc);
+                    dropout_scale16(dseed, dframe * H2 + H + c0, p.drop_p, sc);
 #pragma unroll
                     for (int i = 0; i < 16; ++i) ds[i] *= sc[i];
                 }
             } else {
 #pragma unroll
                 for (int i = 0; i < 16; ++i) { dt[i] = 0.f; ds[i] = 0.f; }   // outside the utterance: the taps read zeros
+                if (dpre_row) { store_bf16x16(dpre_row + c0, dt); store_bf16x16(dpre_row + H + c0, ds); }
             }
             stage_bf16x16_sw128(smem, A_BYTES, r, c0, dt);
             stage_bf16x16_sw128(smem, A_BYTES, r, H + c0, ds);
@@ -242,6 +253,7 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
         const bool ok = r < tile_out && f < p.T;
         const RowIo io = frame_io(b, ok ? f : 0, p.T);
         const float mk = (p.mask && ok) ? p.mask[(size_t)b * p.T + f] : 1.f;
+        const bool live = mk != 0.f;
         mbar_wait(&ctl->acc_full, 1);
         tc_fence_after();
         WB_TRACE(4);
@@ -254,10 +266,10 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
                 float x[16];
                 row_load_f32x16(p.resid_f32, H, c0, io, x);
 #pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] = (v[i] + x[i] * mk) * mk;      // resid and output both masked (modules.py:166)
+                for (int i = 0; i < 16; ++i) v[i] = live ? v[i] + x[i] : 0.f;     // resid and output both masked (modules.py:166)
             } else {
 #pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] *= mk;
+                for (int i = 0; i < 16; ++i) v[i] = live ? v[i] : 0.f;
             }
             if (p.out_f32) row_store_f32x16(p.out_f32, H, c0, io, v);
             stage_bf16x16_sw128(ring, A_BYTES, r, c0, v);

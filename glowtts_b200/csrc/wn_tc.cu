@@ -21,7 +21,8 @@ struct WnCtl {
     uint64_t full[3], empty[3], acc_full, acts_ready;
     uint32_t tmem_base;
     alignas(16) float bias_in[512];     // [2H]
-    alignas(16) float cond[512];        // this utterance's conditioning slice [2H] (zeros when there is none)
+    alignas(16) float cw[512];          // [2H]  WNP conditioner weight / bias per channel (zeros when there is none)
+    alignas(16) float cb[512];
     alignas(16) float bias_rs[512];     // [RS]
 };
 
@@ -61,6 +62,7 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int t0 = blockIdx.x * BT, b = blockIdx.y;
     pdl_trigger();
+    if (p.n_rows && t0 >= *p.n_rows) return;            // varlen packing: nothing lives in this tile
     WN_TRACE(0);
     const int n1 = p.taps * n_kh;                       // GEMM-1 iterations
     const int n_all = n1 + n_kh;                        // + GEMM-2 iterations
@@ -72,10 +74,10 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
         mbar_fence_init();
     }
     {
-        const float* cond = p.cond ? p.cond + (size_t)b * p.cond_bstride : nullptr;
         for (int i = threadIdx.x; i < H2; i += EPI_NT) {
             ctl->bias_in[i] = p.bias_in[i];
-            ctl->cond[i] = cond ? cond[i] : 0.f;
+            ctl->cw[i] = p.trk ? p.cw[i] : 0.f;
+            ctl->cb[i] = p.trk ? p.cb[i] : 0.f;
         }
         for (int i = threadIdx.x; i < RS; i += EPI_NT) ctl->bias_rs[i] = p.bias_rs[i];
     }
@@ -155,7 +157,13 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     const int t = t0 + r;
     const bool t_ok = t < p.T;
     const float mk = (p.mask && t_ok) ? p.mask[(size_t)b * p.T + t] : 1.f;
+    const bool live = t_ok && mk != 0.f;                 // masked rows are written as exact zeros (never value * 0)
     const size_t frame = (size_t)b * p.T + (t_ok ? t : 0);
+    // dropout counter: the un-packed frame index, so that packed and [B, T] runs draw the same mask
+    const unsigned long long dframe = p.row_fr ? (unsigned long long)p.row_fr[frame] : (unsigned long long)frame;
+    // conditioning of this row: speaker embedding projection (per utterance) and / or the WNP pitch-energy track
+    const float* cond_row = p.cond ? p.cond + (size_t)(p.row_b ? p.row_b[frame] : b) * p.cond_bstride : nullptr;
+    const float* trk_row = p.trk ? p.trk + frame * p.n_sqz : nullptr;
     const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
     RowIo io;
     io.tp = p.tile_layout; io.tile_id = b * ((p.T + BT - 1) / BT) + blockIdx.x; io.r = r; io.frame = frame;
@@ -181,21 +189,34 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
         }
         if (p.drop_p > 0.f) {
             float sc[16];
-            dropout_scale16(dseed, (unsigned long long)frame * H2 + c0, p.drop_p, sc);
+            dropout_scale16(dseed, dframe * H2 + c0, p.drop_p, sc);
 #pragma unroll
             for (int i = 0; i < 16; ++i) a[i] *= sc[i];
-            dropout_scale16(dseed, (unsigned long long)frame * H2 + H + c0, p.drop_p, sc);
+            dropout_scale16(dseed, dframe * H2 + H + c0, p.drop_p, sc);
 #pragma unroll
             for (int i = 0; i < 16; ++i) g[i] *= sc[i];
         }
+        if (cond_row) {                                  // cond_layer(g) slice of this utterance (modules.py:148-157)
 #pragma unroll
-        for (int i = 0; i < 16; i += 4) {
-            const float4 ca = *reinterpret_cast<const float4*>(&ctl->cond[c0 + i]);
-            const float4 cg = *reinterpret_cast<const float4*>(&ctl->cond[H + c0 + i]);
-            a[i] = tanh_fast(a[i] + ca.x); a[i + 1] = tanh_fast(a[i + 1] + ca.y);
-            a[i + 2] = tanh_fast(a[i + 2] + ca.z); a[i + 3] = tanh_fast(a[i + 3] + ca.w);
-            g[i] = sigmoid_fast(g[i] + cg.x); g[i + 1] = sigmoid_fast(g[i + 1] + cg.y);
-            g[i + 2] = sigmoid_fast(g[i + 2] + cg.z); g[i + 3] = sigmoid_fast(g[i + 3] + cg.w);
+            for (int i = 0; i < 16; i += 4) {
+                const float4 ca = __ldg(reinterpret_cast<const float4*>(cond_row + c0 + i));
+                const float4 cg = __ldg(reinterpret_cast<const float4*>(cond_row + H + c0 + i));
+                a[i] += ca.x; a[i + 1] += ca.y; a[i + 2] += ca.z; a[i + 3] += ca.w;
+                g[i] += cg.x; g[i + 1] += cg.y; g[i + 2] += cg.z; g[i + 3] += cg.w;
+            }
+        }
+        if (trk_row) {                                   // WNP: cond_layer1(track) squeezed, rank 1 in time (modules.py:320-336)
+            const float pa = trk_row[(p.cs_base + c0) / p.cs_div], pg = trk_row[(p.cs_base + H + c0) / p.cs_div];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                a[i] += fmaf(ctl->cw[c0 + i], pa, ctl->cb[c0 + i]);
+                g[i] += fmaf(ctl->cw[H + c0 + i], pg, ctl->cb[H + c0 + i]);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            a[i] = live ? tanh_fast(a[i]) : 0.f;
+            g[i] = live ? sigmoid_fast(g[i]) : 0.f;
         }
         if (p.ts_save && t_ok) {
             row_store_bf16x16(p.ts_save, H2, c0, io, a);
@@ -262,10 +283,10 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const float4 bb = *reinterpret_cast<const float4*>(&ctl->bias_rs[c0 + 4 * i]);
-                v[4 * i] = (v[4 * i] + bb.x + x[4 * i]) * mk;
-                v[4 * i + 1] = (v[4 * i + 1] + bb.y + x[4 * i + 1]) * mk;
-                v[4 * i + 2] = (v[4 * i + 2] + bb.z + x[4 * i + 2]) * mk;
-                v[4 * i + 3] = (v[4 * i + 3] + bb.w + x[4 * i + 3]) * mk;
+                v[4 * i] = live ? v[4 * i] + bb.x + x[4 * i] : 0.f;
+                v[4 * i + 1] = live ? v[4 * i + 1] + bb.y + x[4 * i + 1] : 0.f;
+                v[4 * i + 2] = live ? v[4 * i + 2] + bb.z + x[4 * i + 2] : 0.f;
+                v[4 * i + 3] = live ? v[4 * i + 3] + bb.w + x[4 * i + 3] : 0.f;
             }
             row_store_f32x16(p.h_out_f32, H, c0, io, v);
             stage_bf16x16_sw128(stage_out, stage_bytes, r, c0, v);
@@ -281,8 +302,9 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
         }
         if (p.last) {                                     // WN output = skip * mask (modules.py:171), operand of `end`
 #pragma unroll
-            for (int i = 0; i < 16; ++i) sk[i] *= mk;
+            for (int i = 0; i < 16; ++i) sk[i] = live ? sk[i] : 0.f;
             stage_bf16x16_sw128(stage_out, stage_bytes, r, c0, sk);
+            if (p.h_out_f32_last) row_store_f32x16(p.h_out_f32_last, H, c0, io, sk);   // fp32 master for a chained WN
         } else {
             row_store_f32x16(p.skip_f32, H, c0, io, sk);
         }
