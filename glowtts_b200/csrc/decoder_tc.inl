@@ -19,9 +19,11 @@ struct TcAct {             // byte offsets inside one block's activation set
 };
 struct TcLayout {          // byte offsets in the workspace
     size_t mask_sq, x_len, winv, icld, we, pack, X, act, hf[2], skipf, bwd, total;
+    size_t hdr, off, row_b, row_fr;      // varlen packing plan (pack.cu): {0, n_rows}, off[B+1], row_b[P], row_fr[P]; mask_sq = mask_p[P]
+    int G, P;                            // gap rows behind every utterance, packed row capacity (multiple of 128)
     size_t we_floats, x_bytes;
     int n_pack, n_act, n_x;
-    TcPack P;
+    TcPack P_;
     TcAct A;
     // backward temporaries
     size_t b_dZ, b_dM, b_dend, b_drs, b_dxin, b_lstride, b_dgate, b_dhf[2], b_dh0, b_wpart;   // b_drs / b_dxin: one per layer, b_lstride apart
@@ -36,11 +38,19 @@ static int tc_supported(const Dims& D) {
 static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout* L) {
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 1024); return o; };
-    const size_t nq = D.nq;
-    const size_t nqp = (size_t)D.B * ((D.Tq + 127) / 128) * 128;     // rows of the tile-private buffers (whole 128-frame tiles)
+    // Inside the bf16 path the batch is ONE packed sequence of P rows (pack.cu): valid frames of every utterance, each
+    // followed by G zero rows (G = the widest halo of any WN layer), dead rows up to P.
+    L->G = (D.K / 2) * ipow(D.dr, D.L - 1);
+    L->P = (int)(((size_t)(D.B > 0 ? D.B : 1) * (D.Tq + L->G) + 127) / 128 * 128);
+    const size_t nq = (size_t)L->P;
+    const size_t nqp = nq;                                           // rows of the tile-private buffers (whole 128-frame tiles)
     const int H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
     L->mask_sq = take(nq * 4);
     L->x_len = take((size_t)D.B * 4);
+    L->hdr = take(16);
+    L->off = take((size_t)(D.B + 1) * 4);
+    L->row_b = take(nq * 4);
+    L->row_fr = take(nq * 4);
     L->winv = take((size_t)D.NB * 64 * 4);
     L->icld = take((size_t)D.NB * 4);
     L->we_floats = L32.weff_block;
@@ -48,7 +58,7 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     // packed weights
     size_t w = 0;
     auto wtake = [&](size_t n) { size_t o = w; w = align_up(w + n, 512); return o; };
-    TcPack& P = L->P;
+    TcPack& P = L->P_;
     P.start = wtake((size_t)H * pad64(Ch));
     for (int i = 0; i < D.L; ++i) P.in[i] = wtake((size_t)K * 2 * H * H);
     for (int i = 0; i < D.L; ++i) P.rs[i] = wtake((size_t)((i < D.L - 1) ? 2 * H : H) * H);
@@ -103,7 +113,7 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
 static int tc_pack_all(const Dims& D, const TcLayout& L, const gtk_block_params* blocks, bf16* pk_base, int with_transposed,
                        cudaStream_t st) {
     const int H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
-    const TcPack& Q = L.P;
+    const TcPack& Q = L.P_;
     static thread_local tc::FoldPackJobs J;
     J.n = 0;
     bf16* pk = pk_base;
@@ -146,22 +156,38 @@ static int tc_flow_consts(const Dims& D, const TcLayout& L, const gtk_block_para
     return GTK_OK;
 }
 
-// start -> WN -> end(+affine) of one block.  xc = mixed block input (t-major fp32), zout = block output.
+// Device views of the packing plan inside the workspace.
+struct TcPlan {
+    int* hdr; int* off; int* row_b; int* row_fr; float* mask_p; float* x_len;
+    const int* n_rows() const { return hdr + 1; }
+};
+static TcPlan tc_plan(const TcLayout& L, unsigned char* ws) {
+    TcPlan q;
+    q.hdr = reinterpret_cast<int*>(ws + L.hdr); q.off = reinterpret_cast<int*>(ws + L.off);
+    q.row_b = reinterpret_cast<int*>(ws + L.row_b); q.row_fr = reinterpret_cast<int*>(ws + L.row_fr);
+    q.mask_p = reinterpret_cast<float*>(ws + L.mask_sq); q.x_len = reinterpret_cast<float*>(ws + L.x_len);
+    return q;
+}
+
+// start -> WN -> end(+affine) of one block on the packed rows.  xc = mixed block input (t-major fp32 [C, P]),
+// zout = block output.
 static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout& L, const gtk_block_params& P, const bf16* pk,
-                       const float* xc, float* zout, float* logdet, const float* mask, unsigned char* act, unsigned char* ws,
+                       const float* xc, float* zout, float* logdet, const TcPlan& pl, unsigned char* act, unsigned char* ws,
                        int reverse, int save, int blk, cudaStream_t st) {
-    const int B = D.B, T = D.Tq, H = D.H, C = D.C, Ch = D.C / 2;
-    const TcPack& Q = L.P;
+    const int B = 1, T = L.P, H = D.H, C = D.C, Ch = D.C / 2;
+    const float* mask = pl.mask_p;
+    const TcPack& Q = L.P_;
     const TcAct& A = L.A;
     bf16* a0 = reinterpret_cast<bf16*>(act + A.a0);
     float* hf[2] = {reinterpret_cast<float*>(ws + L.hf[0]), reinterpret_cast<float*>(ws + L.hf[1])};
     float* skipf = reinterpret_cast<float*>(ws + L.skipf);
-    GTK_TRY(tc::frames_from_tmajor(xc, a0, B, C, T, 0, Ch, pad64(Ch), st));
+    GTK_TRY(tc::frames_from_tmajor(xc, a0, B, C, T, 0, Ch, pad64(Ch), st, pl.n_rows()));
     {
         tc::ConvTcParams p;
         memset(&p, 0, sizeof(p));
         p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = pad64(Ch) / 64; p.N = H;
         p.bias = P.start_b; p.mask = mask; p.mask_out = 1;
+        p.n_rows = pl.n_rows();
         p.tile_layout = 1;
         p.out_f32 = hf[0]; p.ld_f32 = H;
         p.out_bf16 = reinterpret_cast<bf16*>(act + A.h[0]); p.ld_bf16 = H;
@@ -175,6 +201,7 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
         p.tile_layout = 1;
         p.bias_in = P.in_b[i]; p.bias_rs = P.rs_b[i];
         p.cond = P.cond ? P.cond + (size_t)i * 2 * H : nullptr; p.cond_bstride = (size_t)2 * H * D.L;
+        p.n_rows = pl.n_rows(); p.row_b = pl.row_b; p.row_fr = pl.row_fr;
         p.mask = mask;
         p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, i);
         p.h_f32 = hf[i & 1]; p.h_out_f32 = hf[(i + 1) & 1];
@@ -190,6 +217,7 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
         memset(&p, 0, sizeof(p));
         p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = H / 64; p.N = C;
         p.bias = P.end_b; p.mask = mask;
+        p.n_rows = pl.n_rows(); p.row_b = pl.row_b;
         p.aff_x = xc; p.aff_z = zout; p.aff_logdet = reverse ? nullptr : logdet;
         p.aff_logs_save = save ? reinterpret_cast<float*>(act + A.logs) : nullptr;
         p.aff_reverse = reverse; p.aff_sigmoid_scale = d->sigmoid_scale;
@@ -210,26 +238,27 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     GTK_CUDA(cudaMemsetAsync(logdet, 0, sizeof(float) * D.B, st));
     if (D.Tq == 0) return GTK_OK;
     unsigned char* ws = static_cast<unsigned char*>(workspace);
-    float* msq = reinterpret_cast<float*>(ws + L.mask_sq);
-    float* x_len = reinterpret_cast<float*>(ws + L.x_len);
-    float* we = reinterpret_cast<float*>(ws + L.we);
+    const TcPlan pl = tc_plan(L, ws);
     GTK_TRY(tc_pack_all(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), train, st));
-    GTK_TRY(flow::squeeze(x, mask, reinterpret_cast<float*>(ws + L.X), msq, D.B, D.Cin, D.T, D.n, 0, st));
-    GTK_TRY(flow::mask_len(msq, x_len, D.B, D.Tq, st));
-    GTK_TRY(tc_flow_consts(D, L, blocks, ws, x_len, logdet, st));      // W^-1, log|det W|, the constant logdet terms
+    GTK_TRY(flow::pack_plan(mask, D.B, D.T, D.n, D.Tq, L.G, L.P, pl.hdr, pl.off, pl.row_b, pl.row_fr, pl.mask_p, pl.x_len, st));
+    GTK_TRY(flow::squeeze_pack(x, pl.off, pl.row_b, pl.mask_p, reinterpret_cast<float*>(ws + L.X), D.Cin, D.T, D.n, L.P, st));
+    GTK_TRY(tc_flow_consts(D, L, blocks, ws, pl.x_len, logdet, st));   // W^-1, log|det W|, the constant logdet terms
+    if (train)     // guard rows behind the last tile in use of the conv inputs the weight gradient reads with a tap shift
+        GTK_TRY(tc::zero_guard_rows(reinterpret_cast<bf16*>(ws + L.act + L.A.h[0]), D.L > 1 ? L.A.h[1] - L.A.h[0] : 0, D.L,
+                                    L.A.total, D.NB, D.H, pl.n_rows(), 64, L.P, st));
     for (int blk = 0; blk < D.NB; ++blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
         unsigned char* act = ws + L.act + (size_t)(train ? blk : 0) * L.A.total;
-        bf16* pk = reinterpret_cast<bf16*>(ws + L.pack) + (size_t)blk * L.P.total;
+        bf16* pk = reinterpret_cast<bf16*>(ws + L.pack) + (size_t)blk * L.P_.total;
         const float* xin = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? blk : (blk & 1)) * L.x_bytes);
         float* xout = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? blk + 1 : ((blk + 1) & 1)) * L.x_bytes);
         float* xmix = reinterpret_cast<float*>(act + L.A.xmix);
-        GTK_TRY(flow::mix(xin, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, xmix, D.B, D.C, D.Tq, 0, st));
-        GTK_TRY(tc_coupling(d, D, L, P, pk, xmix, xout, logdet, msq, act, ws, 0, train, blk, st));
+        GTK_TRY(flow::mix(xin, pl.mask_p, P.an_logs, P.an_bias, P.ic_weight, D.NS, xmix, 1, D.C, L.P, 0, st, pl.n_rows()));
+        GTK_TRY(tc_coupling(d, D, L, P, pk, xmix, xout, logdet, pl, act, ws, 0, train, blk, st));
     }
     const float* xfin = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? D.NB : (D.NB & 1)) * L.x_bytes);
-    GTK_TRY(flow::unsqueeze(xfin, msq, z, nullptr, D.B, D.C, D.Tq, D.n, 0, st));
+    GTK_TRY(flow::unsqueeze_unpack(xfin, pl.off, z, D.B, D.Cin, D.Tq * D.n, D.n, L.G, L.P, st));
     return GTK_OK;
 }
 
@@ -243,35 +272,27 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     if (ws_bytes < L.total) { set_error("decoder_reverse(bf16): workspace %zu < %zu", ws_bytes, L.total); return GTK_ERR_WORKSPACE; }
     if (D.B == 0 || D.Tq == 0) return GTK_OK;
     unsigned char* ws = static_cast<unsigned char*>(workspace);
-    float* msq = reinterpret_cast<float*>(ws + L.mask_sq);
-    float* we = reinterpret_cast<float*>(ws + L.we);
+    const TcPlan pl = tc_plan(L, ws);
     float* xa = reinterpret_cast<float*>(ws + L.X);
     float* xb = reinterpret_cast<float*>(ws + L.X + L.x_bytes);
     unsigned char* act = ws + L.act;
     GTK_TRY(tc_pack_all(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), 0, st));
-    GTK_TRY(flow::squeeze(z, mask, xa, msq, D.B, D.Cin, D.T, D.n, 0, st));
+    GTK_TRY(flow::pack_plan(mask, D.B, D.T, D.n, D.Tq, L.G, L.P, pl.hdr, pl.off, pl.row_b, pl.row_fr, pl.mask_p, pl.x_len, st));
+    GTK_TRY(flow::squeeze_pack(z, pl.off, pl.row_b, pl.mask_p, xa, D.Cin, D.T, D.n, L.P, st));
     GTK_TRY(tc_flow_consts(D, L, blocks, ws, nullptr, nullptr, st));
     for (int blk = D.NB - 1; blk >= 0; --blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
         float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
-        const bf16* pk = reinterpret_cast<const bf16*>(ws + L.pack) + (size_t)blk * L.P.total;
-        GTK_TRY(tc_coupling(d, D, L, P, pk, xa, xb, nullptr, msq, act, ws, 1, 0, blk, st));
-        GTK_TRY(flow::mix(xb, msq, P.an_logs, P.an_bias, winv, D.NS, xa, D.B, D.C, D.Tq, 1, st));
+        const bf16* pk = reinterpret_cast<const bf16*>(ws + L.pack) + (size_t)blk * L.P_.total;
+        GTK_TRY(tc_coupling(d, D, L, P, pk, xa, xb, nullptr, pl, act, ws, 1, 0, blk, st));
+        GTK_TRY(flow::mix(xb, pl.mask_p, P.an_logs, P.an_bias, winv, D.NS, xa, 1, D.C, L.P, 1, st, pl.n_rows()));
     }
-    GTK_TRY(flow::unsqueeze(xa, msq, x, nullptr, D.B, D.C, D.Tq, D.n, 0, st));
+    GTK_TRY(flow::unsqueeze_unpack(xa, pl.off, x, D.B, D.Cin, D.Tq * D.n, D.n, L.G, L.P, st));
     return GTK_OK;
 }
 
 // ------------------------------------------------------------------------------------------ backward
-// Weight gradient of a (possibly weight-normed) conv from frame operands, accumulated into (dg, dv) or dv alone.
-static int tc_wgrad_param(const float* g, const float* v, float* dg, float* dv, float* part, const bf16* dy, int ld_y, int cols_y,
-                          const bf16* x, int ld_x, int cols_x, int B, int T, int M, int Cin, int K, int dil, cudaStream_t st) {
-    if (!dv) return GTK_OK;
-    if (g) GTK_REQUIRE(dg != nullptr, "weight_g gradient pointer missing");
-    return tc::wgrad_tc_param(dy, ld_y, cols_y, x, ld_x, cols_x, g, v, dg, dv, part, B, T, M, Cin, K, dil, st);
-}
-
 static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_params* blocks, const gtk_block_grads* grads,
                        const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace, size_t ws_bytes,
                        int blk_hi, int blk_lo, cudaStream_t st) {
@@ -283,15 +304,17 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     make_tc_layout(D, L32, 1, &L);
     if (ws_bytes < L.total) { set_error("decoder_backward(bf16): workspace %zu < %zu", ws_bytes, L.total); return GTK_ERR_WORKSPACE; }
     if (D.B == 0 || D.T == 0) return GTK_OK;
-    if (first && (D.Tq * D.n != D.T || D.Tq == 0)) GTK_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)D.B * D.Cin * D.T, st));
-    if (D.Tq == 0) return GTK_OK;
+    if (D.Tq == 0) {
+        if (first) GTK_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)D.B * D.Cin * D.T, st));
+        return GTK_OK;
+    }
+    (void)mask;                                          // the plan the forward left in the workspace has the lengths
 
     unsigned char* ws = static_cast<unsigned char*>(workspace);
-    const float* msq = reinterpret_cast<const float*>(ws + L.mask_sq);
-    const float* x_len = reinterpret_cast<const float*>(ws + L.x_len);
-    const int B = D.B, T = D.Tq, H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
+    const TcPlan pl = tc_plan(L, ws);
+    const float* msq = pl.mask_p;
+    const int B = 1, T = L.P, H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
     const int ldC = pad64(C), ldCh = pad64(Ch);
-    const long long rows = (long long)B * T;
     float* dZ = reinterpret_cast<float*>(ws + L.b_dZ);
     float* dM = reinterpret_cast<float*>(ws + L.b_dM);
     bf16* dend = reinterpret_cast<bf16*>(ws + L.b_dend);
@@ -302,13 +325,13 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     bf16* dh0 = reinterpret_cast<bf16*>(ws + L.b_dh0);
     float* wpart = reinterpret_cast<float*>(ws + L.b_wpart);   // stream-K partial tiles of the weight gradients
 
-    if (first) GTK_TRY(flow::squeeze(dz, msq, dZ, nullptr, B, D.Cin, D.Tq * D.n, D.n, 1, st));
+    if (first) GTK_TRY(flow::squeeze_pack(dz, pl.off, pl.row_b, pl.mask_p, dZ, D.Cin, D.Tq * D.n, D.n, L.P, st));
     if (first) {   // gradients of the constant logdet terms of every block, one launch (they only need dlogdet and the saved W^-1)
         static thread_local flow::FlowConstGrads FG;
         for (int k0 = 0; k0 < D.NB; k0 += flow::FLOW_CONST_MAX_BLOCKS) {
             FG.n = min(flow::FLOW_CONST_MAX_BLOCKS, D.NB - k0);
             for (int k = 0; k < FG.n; ++k) { FG.dlogs[k] = grads[k0 + k].an_logs; FG.dW[k] = grads[k0 + k].ic_weight; }
-            GTK_TRY(flow::logdet_const_bwd_all(dlogdet, x_len, B, FG, C, reinterpret_cast<const float*>(ws + L.winv) + (size_t)k0 * 64,
+            GTK_TRY(flow::logdet_const_bwd_all(dlogdet, pl.x_len, D.B, FG, C, reinterpret_cast<const float*>(ws + L.winv) + (size_t)k0 * 64,
                                                D.NS, st));
         }
     }
@@ -317,11 +340,10 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         const gtk_block_params& P = blocks[blk];
         const gtk_block_grads& G = grads[blk];
         unsigned char* act = ws + L.act + (size_t)blk * L.A.total;
-        const bf16* pk = reinterpret_cast<const bf16*>(ws + L.pack) + (size_t)blk * L.P.total;
-        const TcPack& Q = L.P;
+        const bf16* pk = reinterpret_cast<const bf16*>(ws + L.pack) + (size_t)blk * L.P_.total;
+        const TcPack& Q = L.P_;
         const TcAct& A = L.A;
         const float* xin_blk = reinterpret_cast<const float*>(ws + L.X + (size_t)blk * L.x_bytes);
-        const float* winv = reinterpret_cast<const float*>(ws + L.winv) + (size_t)blk * 64;
         const float* xmix = reinterpret_cast<const float*>(act + A.xmix);
         const bf16* a0 = reinterpret_cast<const bf16*>(act + A.a0);
         const bf16* skip_bf = reinterpret_cast<const bf16*>(act + A.skip_bf);
@@ -331,13 +353,13 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         tc::WgradGroupJob jobs[tc::WGG_MAX_JOBS];
         int n_jobs = 0, n_tiles = 0;
         auto flush = [&]() -> int {
-            int rc = n_jobs ? tc::wgrad_group_launch(jobs, n_jobs, B, T, wpart, st) : GTK_OK;
+            int rc = n_jobs ? tc::wgrad_group_launch(jobs, n_jobs, B, T, wpart, pl.n_rows(), st) : GTK_OK;
             n_jobs = 0; n_tiles = 0;
             return rc;
         };
         auto queue = [&](const float* g, const float* v, float* dg, float* dv, float* db, const bf16* dy, int ld_y, int cols_y,
                          const bf16* x, int ld_x, int cols_x, int M, int Cin, int Kk, int dil) -> int {
-            if (!dv) return db ? tc::colsum_frames(dy, ld_y, M, 1, rows, db, 0, st) : GTK_OK;
+            if (!dv) return db ? tc::colsum_frames_seg(dy, ld_y, M, 1, pl.hdr, db, 0, st) : GTK_OK;
             if (g && !dg) { set_error("decoder_backward(bf16): weight_g gradient pointer missing"); return GTK_ERR_INVALID; }
             const int tiles = ((M + 127) / 128) * Kk;
             if (n_jobs == tc::WGG_MAX_JOBS || n_tiles + tiles > tc::WGG_MAX_TILES) GTK_TRY(flush());
@@ -350,7 +372,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
 
         // affine coupling + end conv
         GTK_TRY(tc::affine_bwd_frames(xmix, reinterpret_cast<const float*>(act + A.logs), msq, dZ, dlogdet, dend, ldC, dM, B, C, T,
-                                      d->sigmoid_scale, st));
+                                      d->sigmoid_scale, pl.row_b, pl.n_rows(), st));
         GTK_TRY(queue(nullptr, P.end_w, nullptr, G.end_w, G.end_b, dend, ldC, ldC, skip_bf, H, H, C, H, 1, 1));
         {
             // d(skip) feeds the res_skip gradient of EVERY layer: written into columns [H, 2H) of all per-layer buffers
@@ -358,6 +380,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
             memset(&p, 0, sizeof(p));
             p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = ldC / 64; p.N = H;
             p.mask = msq; p.mask_out = 1;
+            p.n_rows = pl.n_rows();
             p.out_bf16 = drs_of(0) + H; p.ld_bf16 = 2 * H;
             p.rep_bf16 = D.L; p.rep_stride = L.b_lstride / 2;
             GTK_TRY(tc::conv_tc_launch(dend, ldC, pk + Q.t_end, p, tc::EPI_PLAIN, st));
@@ -371,65 +394,68 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
             const bf16* acts = reinterpret_cast<const bf16*>(act + A.acts[i]);
             const bf16* h_i = reinterpret_cast<const bf16*>(act + A.h[i]);
             const bool want_dcond = P.cond && G.cond;
+            // the conditioning enters after the dropout: with both active the un-scaled gate gradient is kept as well
+            bf16* dpre = (want_dcond && d->p_dropout > 0.f) ? dgate : nullptr;
             GTK_TRY(queue(P.rs_g[i], P.rs_v[i], G.rs_g[i], G.rs_v[i], G.rs_b[i], drs_i, 2 * H, RS, acts, H, H, RS, H, 1, 1));
             GTK_TRY(queue(P.in_g[i], P.in_v[i], G.in_g[i], G.in_v[i], G.in_b[i], dxin, 2 * H, 2 * H, h_i, H, H, 2 * H, H, K, dil));
-            if (!want_dcond && tc::wn_bwd_supported(H, K, dil)) {
+            if (tc::wn_bwd_supported(H, K, dil)) {
                 // res_skip data gradient -> gate backward -> in_layer data gradient in ONE kernel (wn_bwd_tc.cu)
                 tc::WnBwdParams p;
                 memset(&p, 0, sizeof(p));
                 p.B = B; p.T = T; p.H = H; p.RS = RS; p.taps = K; p.dil = dil;
                 p.mask = msq; p.ts = ts;
+                p.n_rows = pl.n_rows(); p.row_fr = pl.row_fr; p.dpre = dpre;
                 p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, i);
                 p.resid_f32 = (i < D.L - 1) ? dhf[(i + 1) & 1] : nullptr;
                 p.out_f32 = dhf[i & 1];
                 GTK_TRY(tc::wn_bwd_layer_launch(drs_i, 2 * H, pk + Q.t_rs[i], pk + Q.t_in[i], dxin, i > 0 ? drs_of(i - 1) : dh0,
                                                 i > 0 ? 2 * H : H, p, st));
-                continue;
-            }
-            // res_skip 1x1: data gradient fused with the gate backward
-            {
-                tc::ConvTcParams p;
-                memset(&p, 0, sizeof(p));
-                p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = pad64(RS) / 64; p.N = H;
-                p.mask = msq;
-                p.tile_layout = 1;
-                p.ts = ts; p.out_bf16 = dxin; p.ld_bf16 = 2 * H;
-                p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, i);
-                // the conditioning enters after the dropout: with both active keep the un-scaled gate gradient too
-                if (want_dcond && d->p_dropout > 0.f) p.out2_bf16 = dgate;
-                GTK_TRY(tc::conv_tc_launch(drs_i, 2 * H, pk + Q.t_rs[i], p, tc::EPI_GATE_BWD, st));
-            }
-            if (want_dcond)
-                GTK_TRY(tc::colsum_frames(d->p_dropout > 0.f ? dgate : dxin, 2 * H, 2 * H, B, T, G.cond + (size_t)i * 2 * H,
-                                          (size_t)2 * H * D.L, st));
-            // in_layer dilated conv
-            {
-                tc::ConvTcParams p;
-                memset(&p, 0, sizeof(p));
-                p.B = B; p.T = T; p.taps = K; p.dil = dil; p.n_k = 2 * H / 64; p.N = H;
-                p.mask = msq; p.mask_out = 1;
-                p.tile_layout = 1;
-                if (i < D.L - 1) { p.resid_f32 = dhf[(i + 1) & 1]; p.ld_resid = H; p.mask_resid = 1; }
-                p.out_f32 = dhf[i & 1]; p.ld_f32 = H;
-                if (i > 0) { p.out_bf16 = drs_of(i - 1); p.ld_bf16 = 2 * H; }
-                else       { p.out_bf16 = dh0; p.ld_bf16 = H; }
-                GTK_TRY(tc::conv_tc_launch(dxin, 2 * H, pk + Q.t_in[i], p, tc::EPI_PLAIN, st));
-            }
+            } else {
+                {   // res_skip 1x1: data gradient fused with the gate backward
+                    tc::ConvTcParams p;
+                    memset(&p, 0, sizeof(p));
+                    p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = pad64(RS) / 64; p.N = H;
+                    p.mask = msq;
+                    p.n_rows = pl.n_rows(); p.row_fr = pl.row_fr;
+                    p.tile_layout = 1;
+                    p.ts = ts; p.out_bf16 = dxin; p.ld_bf16 = 2 * H;
+                    p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, i);
+                    p.out2_bf16 = dpre;
+                    GTK_TRY(tc::conv_tc_launch(drs_i, 2 * H, pk + Q.t_rs[i], p, tc::EPI_GATE_BWD, st));
                 }
+                {   // in_layer dilated conv
+                    tc::ConvTcParams p;
+                    memset(&p, 0, sizeof(p));
+                    p.B = B; p.T = T; p.taps = K; p.dil = dil; p.n_k = 2 * H / 64; p.N = H;
+                    p.mask = msq; p.mask_out = 1;
+                    p.n_rows = pl.n_rows();
+                    p.tile_layout = 1;
+                    if (i < D.L - 1) { p.resid_f32 = dhf[(i + 1) & 1]; p.ld_resid = H; p.mask_resid = 1; }
+                    p.out_f32 = dhf[i & 1]; p.ld_f32 = H;
+                    if (i > 0) { p.out_bf16 = drs_of(i - 1); p.ld_bf16 = 2 * H; }
+                    else       { p.out_bf16 = dh0; p.ld_bf16 = H; }
+                    GTK_TRY(tc::conv_tc_launch(dxin, 2 * H, pk + Q.t_in[i], p, tc::EPI_PLAIN, st));
+                }
+            }
+            if (want_dcond)      // d cond_layer(g)[b, n] = sum over the utterance's rows of the gate-input gradient
+                GTK_TRY(tc::colsum_frames_seg(dpre ? dpre : dxin, 2 * H, 2 * H, D.B, pl.off, G.cond + (size_t)i * 2 * H,
+                                              (size_t)2 * H * D.L, st));
+        }
         // start conv: h0 = (W x0 + b) * mask   (dh0 is already masked)
         GTK_TRY(queue(P.start_g, P.start_v, G.start_g, G.start_v, G.start_b, dh0, H, H, a0, ldCh, ldCh, H, Ch, 1, 1));
         {
             tc::ConvTcParams p;
             memset(&p, 0, sizeof(p));
             p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = H / 64; p.N = Ch;
+            p.n_rows = pl.n_rows();
             p.resid_tm = dZ; p.out_tm = dM; p.tm_C = C; p.tm_c0 = 0;
             GTK_TRY(tc::conv_tc_launch(dh0, H, pk + Q.t_start, p, tc::EPI_PLAIN, st));
         }
         GTK_TRY(flush());
         // ActNorm + InvConvNear (fp32)
         GTK_TRY(flow::mix_bwd(xin_blk, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, dM, dZ, G.an_logs, G.an_bias, G.ic_weight, B,
-                              C, T, st));
+                              C, T, st, pl.n_rows()));
     }
-    if (last) GTK_TRY(flow::unsqueeze(dZ, msq, dx, nullptr, B, C, T, D.n, D.T, st));
+    if (last) GTK_TRY(flow::unsqueeze_unpack(dZ, pl.off, dx, D.B, D.Cin, D.T, D.n, L.G, L.P, st));
     return GTK_OK;
 }

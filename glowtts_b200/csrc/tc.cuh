@@ -152,8 +152,8 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
 // out[g * out_gstride + n] += sum of rows [seg[g], seg[g + 1]) (device-resident bounds) of frames in[.., n]
 int colsum_frames_seg(const __nv_bfloat16* in, int ld, int n_cols, int groups, const int* seg, float* out, size_t out_gstride,
                       cudaStream_t st);
-int zero_guard_rows(__nv_bfloat16* base, size_t stride_bytes, int n_buf, int ld, const int* n_rows, int n_guard, int T,
-                    cudaStream_t st);
+int zero_guard_rows(__nv_bfloat16* base, size_t stride_bytes, int n_buf, size_t stride2_bytes, int n_buf2, int ld,
+                    const int* n_rows, int n_guard, int T, cudaStream_t st);
 int colsum_frames(const __nv_bfloat16* in, int ld, int n_cols, int groups, long long rows_per_group, float* out, size_t out_gstride,
                   cudaStream_t st);
 int affine_bwd_frames(const float* x, const float* logs_raw, const float* mask, const float* dz, const float* dlogdet,

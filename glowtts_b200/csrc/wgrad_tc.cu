@@ -297,20 +297,21 @@ int colsum_frames_seg(const __nv_bfloat16* in, int ld, int n_cols, int groups, c
 // Varlen packing: kernels never write behind the last 128-row tile in use, but the weight-gradient GEMM reads the conv
 // input up to (K/2) dil rows past its last k-step; those rows only ever meet zero output-gradient rows, and 0 x garbage
 // must not be 0 x NaN.
-__global__ void zero_guard_rows_kernel(unsigned char* base, size_t stride, int ld, const int* __restrict__ n_rows, int n_guard,
-                                       int T) {
+__global__ void zero_guard_rows_kernel(unsigned char* base, size_t stride, size_t stride2, int ld, const int* __restrict__ n_rows,
+                                       int n_guard, int T) {
     const int r0 = (*n_rows + 127) & ~127;
     const int rows = min(n_guard, T - r0);
     if (rows <= 0) return;
-    uint4* dst = reinterpret_cast<uint4*>(base + (size_t)blockIdx.x * stride + (size_t)r0 * ld * 2);
+    uint4* dst = reinterpret_cast<uint4*>(base + (size_t)blockIdx.x * stride + (size_t)blockIdx.y * stride2 + (size_t)r0 * ld * 2);
     const int n16 = rows * ld * 2 / 16;
     for (int i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = make_uint4(0u, 0u, 0u, 0u);
 }
-int zero_guard_rows(__nv_bfloat16* base, size_t stride_bytes, int n_buf, int ld, const int* n_rows, int n_guard, int T,
-                    cudaStream_t st) {
+int zero_guard_rows(__nv_bfloat16* base, size_t stride_bytes, int n_buf, size_t stride2_bytes, int n_buf2, int ld,
+                    const int* n_rows, int n_guard, int T, cudaStream_t st) {
     GTK_REQUIRE(base && n_rows && ld % 8 == 0, "bad args");
-    if (n_buf == 0 || n_guard == 0) return GTK_OK;
-    zero_guard_rows_kernel<<<n_buf, 256, 0, st>>>(reinterpret_cast<unsigned char*>(base), stride_bytes, ld, n_rows, n_guard, T);
+    if (n_buf == 0 || n_buf2 == 0 || n_guard == 0) return GTK_OK;
+    zero_guard_rows_kernel<<<dim3(n_buf, n_buf2), 256, 0, st>>>(reinterpret_cast<unsigned char*>(base), stride_bytes, stride2_bytes,
+                                                               ld, n_rows, n_guard, T);
     return check_launch("zero_guard_rows");
 }
 

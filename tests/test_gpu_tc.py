@@ -90,9 +90,12 @@ def test_fused_wn_layer_matches_torch(last, use_cond):
               ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
     torch.cuda.synchronize()
     tol = dict(rtol=1e-2, atol=1e-2)
-    np.testing.assert_allclose(ts[:, :, :H].float().cpu().numpy(), tt.permute(0, 2, 1).cpu().numpy(), **tol)
-    np.testing.assert_allclose(ts[:, :, H:].float().cpu().numpy(), ss.permute(0, 2, 1).cpu().numpy(), **tol)
-    np.testing.assert_allclose(ac.float().cpu().numpy(), acts.permute(0, 2, 1).cpu().numpy(), **tol)
+    # Masked frames: the reference's values there never reach an output (x * mask, output * mask: modules.py:166,171);
+    # the kernel writes exact zeros for them, so the comparison is over the valid frames (and zeros are checked below).
+    mk3 = mask[:, :, None]
+    np.testing.assert_allclose(ts[:, :, :H].float().cpu().numpy(), (tt.permute(0, 2, 1) * mk3).cpu().numpy(), **tol)
+    np.testing.assert_allclose(ts[:, :, H:].float().cpu().numpy(), (ss.permute(0, 2, 1) * mk3).cpu().numpy(), **tol)
+    np.testing.assert_allclose(ac.float().cpu().numpy(), (acts.permute(0, 2, 1) * mk3).cpu().numpy(), **tol)
     if last:
         want = (skip_prev + rs.permute(0, 2, 1)) * mask[:, :, None]
         np.testing.assert_allclose(skip16.float().cpu().numpy(), want.cpu().numpy(), rtol=2e-2, atol=2e-2)
@@ -101,7 +104,7 @@ def test_fused_wn_layer_matches_torch(last, use_cond):
         np.testing.assert_allclose(h_out32.cpu().numpy(), want_h.cpu().numpy(), rtol=5e-3, atol=5e-3)
         np.testing.assert_allclose(h_out16.float().cpu().numpy(), want_h.cpu().numpy(), rtol=2e-2, atol=2e-2)
         want_s = skip_prev + rs[:, H:].permute(0, 2, 1)
-        np.testing.assert_allclose(skip32.cpu().numpy(), want_s.cpu().numpy(), rtol=5e-3, atol=5e-3)
+        np.testing.assert_allclose((skip32 * mk3).cpu().numpy(), (want_s * mk3).cpu().numpy(), rtol=5e-3, atol=5e-3)
 
 
 def _decoders(cfg, seed, end_std=0.05):
