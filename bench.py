@@ -477,7 +477,8 @@ def workload_config(world, precision, launch="cuda_graph"):
                         "mels, ragged lengths",
             "batch_per_gpu": B_PER_GPU, "global_batch": B_PER_GPU * world, "t_text": T_TEXT, "t_mel": T_MEL,
             "precision": precision, "p_dropout_dec": CFG["p_dropout_dec"], "launch": launch,
-            "l2": "per-step working set (activation workspace ~2.4 GB) exceeds the 126 MB L2",
+            "l2": "per-step working set (activation workspace > 1 GB) exceeds the 126 MB L2",
+            "layout": "varlen-packed rows inside the decoder (no work on padding frames)",
             "parallelism": f"dp{world} (batch sharded, one flat-gradient NCCL all-reduce per step)" if world > 1 else "single GPU"}
 
 
@@ -548,6 +549,7 @@ def main():
     from glowtts_b200.distributed import sum_over_ranks
     frames_total, cells_total = sum_over_ranks(run.frames, device), sum_over_ranks(run.cells, device)
     run_frames, run_h2d, run_graphed = run.frames, run.h2d_bytes, run.graphed is not None
+    run_rows = int((run.host[1] // CFG["n_sqz"] + (CFG["kernel_size"] // 2) * CFG["dilation_rate"] ** (CFG["n_layers"] - 1)).sum())
 
     # ---- secondary legs, at EVERY N (all ranks run them: the timings are reduced over the ranks).  MAS and the reverse
     # flow shard by utterance with no collective ("replicas only"), so these curves should be linear; configs[3] is the
@@ -584,7 +586,9 @@ def main():
         # dominant kernel: the fused WaveNet layer (k=5 dilated conv GEMM + gate + res/skip 1x1 GEMM, wn_tc.cu);
         # fp32 path: the k=5 CUDA-core convolution.  Algorithmic flops = valid (unpadded) squeezed frames only.
         sq_frames_valid = run_frames // CFG["n_sqz"]
-        sq_frames_padded = B_PER_GPU * (T_MEL // 2)
+        # rows the tensor-core kernels really run: the decoder works on the varlen-packed batch (pack.cu): valid squeezed
+        # frames + G = 2 gap rows per utterance, rounded up to whole 128-row tiles
+        sq_frames_padded = (run_rows + 127) // 128 * 128
         H, K, L = CFG["hidden_channels"], CFG["kernel_size"], CFG["n_layers"]
         if "wn_layer_tc" in prof:
             # dominant = the fused WaveNet-layer kernel that takes more of the step: forward (k=5 conv GEMM -> gate ->
