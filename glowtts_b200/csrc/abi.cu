@@ -150,6 +150,11 @@ int gtk_mas_forward(const float* value, const int32_t* t_xs, const int32_t* t_ys
     return mas::forward(value, t_xs, t_ys, path, dur_out, idx_out, B, T_x, T_y, workspace, workspace_bytes, force_generic, ST);
 }
 
+size_t gtk_mas_static_scratch_bytes(void) { return mas::static_scratch_bytes(); }
+int gtk_mas_forward_static(const float* value, const int32_t* t_xs, const int32_t* t_ys, float* path, int32_t* dur_out,
+                           int32_t* idx_out, int B, int T_x, int T_y, void* stream) {
+    return mas::forward_static(value, t_xs, t_ys, path, dur_out, idx_out, B, T_x, T_y, ST);
+}
 int gtk_mas_fused_supported(int D, int T_x, int T_y, int has_x_logs) { return mas::fused_supported(D, T_x, T_y, has_x_logs); }
 int gtk_mas_fused_logp(const float* z, const float* x_m, const float* x_logs, const int32_t* t_xs, const int32_t* t_ys,
                        float* path, int32_t* dur_out, int32_t* idx_out, float* logp_out, int B, int D, int T_x, int T_y,

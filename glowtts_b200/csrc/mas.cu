@@ -20,6 +20,7 @@
 // ((v_prev > v_cur) ? v_prev : v_cur), -1e9 sentinels at x==y and (x==0,y>0), 0 at
 // (0,0), tie => stay.  Cells outside the reference's band are computed but never
 // consumed by an in-band cell, so the lower band clip is not needed.
+#include <mutex>
 #include "common.cuh"
 #include "ops.h"
 #include "tc.cuh"
@@ -1168,6 +1169,54 @@ int forward(const float* value, const int* t_xs, const int* t_ys, float* path, i
     ProfScope prof("mas_generic", stream);
     mas_generic_kernel<<<B, GEN_NT, smem, stream>>>(p, static_cast<uint32_t*>(workspace));
     return check_launch("mas_generic_kernel");
+}
+
+// ------------------------------------------------------------------------------------------ allocation-free variant
+// gtk_mas_forward_static: the generic kernel (the one MAS kernel that needs scratch memory: its decision words live in
+// global memory) with the scratch in a file-scope device array instead of a caller-provided workspace, for callers that
+// cannot allocate (CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library
+// holds MAS_STATIC_SCRATCH_BYTES until exit.  All calls share the array: calls that overlap on the GPU (different
+// streams) race.  Nothing in it has to start at zero -- the kernel writes every decision word before the backtrack reads
+// it -- so stale contents of an earlier call are harmless.
+constexpr size_t MAS_STATIC_SCRATCH_BYTES = 8u << 20;           // 8 MiB = B * T_y * ceil(T_x / 32) * 4 bytes at most
+static __device__ __align__(256) unsigned char g_mas_static_scratch[MAS_STATIC_SCRATCH_BYTES];
+
+size_t static_scratch_bytes() { return MAS_STATIC_SCRATCH_BYTES; }
+
+// Device address of the scratch array on the CURRENT device.  In host code `g_mas_static_scratch` is only a stand-in
+// symbol, not a device address: it must go through cudaGetSymbolAddress, once per device, with that device current.
+static int static_scratch_ptr(void** out) {
+    constexpr int MAX_DEV = 64;
+    static void* ptrs[MAX_DEV] = {nullptr};
+    static std::mutex mu;
+    int dev = 0;
+    GTK_CUDA(cudaGetDevice(&dev));
+    GTK_REQUIRE(dev >= 0 && dev < MAX_DEV, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        GTK_CUDA(cudaGetSymbolAddress(&p, g_mas_static_scratch));
+        GTK_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned null");
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return GTK_OK;
+}
+
+int forward_static(const float* value, const int* t_xs, const int* t_ys, float* path, int* dur_out, int* idx_out, int B,
+                   int T_x, int T_y, cudaStream_t stream) {
+    GTK_REQUIRE(B >= 0 && T_x >= 0 && T_y >= 0, "negative size");
+    if (B == 0) return GTK_OK;
+    const size_t need = (size_t)B * T_y * ceil_div(T_x, 32) * sizeof(uint32_t);
+    if (need > MAS_STATIC_SCRATCH_BYTES) {
+        set_error("mas_forward_static: B * T_y * ceil(T_x / 32) * 4 = %zu bytes exceeds the built-in scratch of %zu bytes; "
+                  "use gtk_mas_forward with a caller-provided workspace", need, MAS_STATIC_SCRATCH_BYTES);
+        return GTK_ERR_WORKSPACE;
+    }
+    void* scratch = nullptr;
+    int rc = static_scratch_ptr(&scratch);
+    if (rc) return rc;
+    return forward(value, t_xs, t_ys, path, dur_out, idx_out, B, T_x, T_y, scratch, MAS_STATIC_SCRATCH_BYTES, /*generic*/ 1, stream);
 }
 
 int lengths_from_mask(const float* mask, int* t_xs, int* t_ys, int B, int T_x, int T_y, cudaStream_t stream) {

@@ -9,6 +9,9 @@ namespace mas {
 size_t workspace_bytes(int B, int T_x, int T_y);
 int forward(const float* value, const int* t_xs, const int* t_ys, float* path, int* dur_out, int* idx_out, int B, int T_x,
             int T_y, void* workspace, size_t workspace_bytes_given, int force_generic, cudaStream_t stream);
+size_t static_scratch_bytes();
+int forward_static(const float* value, const int* t_xs, const int* t_ys, float* path, int* dur_out, int* idx_out, int B, int T_x,
+                   int T_y, cudaStream_t stream);
 int fused_supported(int D, int T_x, int T_y, int has_logs);
 int fused_forward(const float* z, const float* x_m, const int* t_xs, const int* t_ys, float* path, int* dur_out, int* idx_out,
                   float* logp_out, int B, int D, int T_x, int T_y, cudaStream_t stream);

@@ -62,6 +62,19 @@ int gtk_mas_forward(const float* value, const int32_t* t_xs, const int32_t* t_ys
                     int32_t* idx_out, int B, int T_x, int T_y, void* workspace, size_t workspace_bytes,
                     int force_generic, void* stream);
 
+/* Allocation-free variant of gtk_mas_forward.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same inputs, outputs and results as gtk_mas_forward(force_generic = 1), but the
+ * decision-bit scratch the generic kernel needs is a file-scope device array inside the library (csrc/mas.cu) instead
+ * of a caller workspace; the call performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ * Limit: B * T_y * ceil(T_x / 32) * 4 <= gtk_mas_static_scratch_bytes() (8 MiB, held by every GPU that loads the
+ * library until exit); larger shapes return an error (gtk_last_error() says so) -- use gtk_mas_forward.  All calls share
+ * the one array (it keeps the last call's contents; nothing in it needs to start at zero): calls that overlap on the
+ * GPU, e.g. on different streams, race. */
+size_t gtk_mas_static_scratch_bytes(void);
+int gtk_mas_forward_static(const float* value, const int32_t* t_xs, const int32_t* t_ys, float* path, int32_t* dur_out,
+                           int32_t* idx_out, int B, int T_x, int T_y, void* stream);
+
 /* Fused variant: models.py:1076-1083 (logp construction + maximum_path) in ONE kernel -- the [B,T_x,T_y] value tensor
  * is computed tile by tile on the tensor cores inside the MAS CTA (3xTF32 mma.sync) and never exists in HBM.
  * Covers mean_only models (x_logs == NULL; all configs/base*.json) with D == 80, T_x <= 256, T_y % 4 == 0;
