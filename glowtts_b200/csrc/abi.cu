@@ -345,6 +345,36 @@ int gtk_tc_wn_bwd_layer(const void* drs_bf16, int ld_drs, const void* wrs_t, con
                                    static_cast<__nv_bfloat16*>(out_bf16), ld_out, p, ST);
 }
 
+int gtk_cond_layers(const float* const* weight_g, const float* const* weight_v, const float* const* bias, int n_blocks,
+                    const float* g, float* cond, int B, int G, int N, void* stream) {
+    GTK_REQUIRE(weight_v && n_blocks >= 1 && n_blocks <= flow::COND_MAX_BLOCKS, "1..32 blocks per call");
+    flow::CondJobs J;
+    memset(&J, 0, sizeof(J));
+    J.n = n_blocks;
+    for (int k = 0; k < n_blocks; ++k) {
+        GTK_REQUIRE(weight_v[k] != nullptr, "null weight");
+        J.g[k] = weight_g ? weight_g[k] : nullptr; J.v[k] = weight_v[k]; J.b[k] = bias ? bias[k] : nullptr;
+    }
+    return flow::cond_all(J, g, cond, B, G, N, ST);
+}
+int gtk_cond_layers_bwd(const float* const* weight_g, const float* const* weight_v, int n_blocks, const float* g,
+                        const float* dcond, float* const* d_weight_g, float* const* d_weight_v, float* const* d_bias, float* dg,
+                        int B, int G, int N, void* stream) {
+    GTK_REQUIRE(weight_v && n_blocks >= 1 && n_blocks <= flow::COND_MAX_BLOCKS, "1..32 blocks per call");
+    flow::CondJobs J;
+    flow::CondGrads D;
+    memset(&J, 0, sizeof(J));
+    memset(&D, 0, sizeof(D));
+    J.n = D.n = n_blocks;
+    for (int k = 0; k < n_blocks; ++k) {
+        GTK_REQUIRE(weight_v[k] != nullptr, "null weight");
+        J.g[k] = weight_g ? weight_g[k] : nullptr; J.v[k] = weight_v[k];
+        D.g[k] = d_weight_g ? d_weight_g[k] : nullptr; D.v[k] = d_weight_v ? d_weight_v[k] : nullptr;
+        D.b[k] = d_bias ? d_bias[k] : nullptr;
+    }
+    return flow::cond_all_bwd(J, D, g, dcond, dg, B, G, N, ST);
+}
+
 size_t gtk_decoder_workspace_bytes(const gtk_decoder_desc* d, int train) { return decoder::workspace_bytes(d, train); }
 int gtk_decoder_forward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const float* x, const float* mask, float* z,
                         float* logdet, void* workspace, size_t workspace_bytes, int train, void* stream) {

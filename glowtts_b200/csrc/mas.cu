@@ -37,7 +37,7 @@ constexpr float NEG = -1e9f;             // max_neg_val default of maximum_path_
 
 struct Params {
     const float* value;   // [B, T_x, T_y] fp32, y fastest
-    float* path;          // [B, T_x, T_y] fp32 out (fully written: zeros + ones)
+    float* path;          // [B, T_x, T_y] fp32 out (fully written: zeros + ones), or null: durations / index only
     const int* t_xs;      // [B]
     const int* t_ys;      // [B]
     int* dur_out;         // [B, T_x] or null: frames per token  (= attn.sum(2), models.py:1085)
@@ -92,7 +92,8 @@ __device__ __forceinline__ void emit_path(const Params& p, float* __restrict__ p
         if (valid && x < t_x) {
             start = ys[x];
             end = (x + 1 < t_x) ? ys[x + 1] : t_y;
-            for (int y = start; y < end; ++y) pplane[(size_t)x * p.T_y + y] = 1.0f;
+            if (pplane)
+                for (int y = start; y < end; ++y) pplane[(size_t)x * p.T_y + y] = 1.0f;
             if (p.idx_out)
                 for (int y = start; y < end; ++y) p.idx_out[(size_t)b * p.T_y + y] = x;
         }
@@ -126,7 +127,8 @@ __global__ void __launch_bounds__(NT, 1) mas_kernel(const Params p) {
     const int n_iter = max(n_tiles, 1);
     const size_t plane_elems = (size_t)p.T_x * p.T_y;
     const float* __restrict__ vplane = p.value + (size_t)b * plane_elems;
-    float* __restrict__ pplane = p.path + (size_t)b * plane_elems;
+    float* __restrict__ pplane = p.path ? p.path + (size_t)b * plane_elems : nullptr;   // null: index + durations only
+    const size_t fill_elems = p.path ? plane_elems : 0;
 
     if (tid == 0) {
         for (int s = 0; s < MAX_STAGES; ++s) {
@@ -188,8 +190,8 @@ __global__ void __launch_bounds__(NT, 1) mas_kernel(const Params p) {
         // zero-fill geometry: [head scalars][nvec float4][tail scalars]
         const uintptr_t addr = reinterpret_cast<uintptr_t>(pplane);
         size_t head = ((16 - (addr & 15)) & 15) / 4;
-        if (head > plane_elems) head = plane_elems;
-        const size_t nvec = (plane_elems - head) / 4;
+        if (head > fill_elems) head = fill_elems;
+        const size_t nvec = (fill_elems - head) / 4;
         const size_t tail0 = head + nvec * 4;
         float4* pv = reinterpret_cast<float4*>(pplane + head);
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -252,7 +254,7 @@ __global__ void __launch_bounds__(NT, 1) mas_kernel(const Params p) {
             for (size_t i = lo + ht; i < hi; i += HT) pv[i] = z4;
             if (it == 0) {
                 if ((size_t)ht < head) pplane[ht] = 0.f;
-                for (size_t i = tail0 + ht; i < plane_elems; i += HT) pplane[i] = 0.f;
+                for (size_t i = tail0 + ht; i < fill_elems; i += HT) pplane[i] = 0.f;
             }
         }
     }
@@ -562,7 +564,8 @@ __global__ void __launch_bounds__(NT, 1) mas_wave_kernel(const __grid_constant__
     const int n_tiles = valid ? (t_y + YT - 1) / YT : 0;
     const int n_act = valid ? (t_x + BAND - 1) / BAND : 0;      // DP warps with rows below t_x
     const size_t plane_elems = (size_t)p.T_x * p.T_y;
-    float* __restrict__ pplane = p.path + (size_t)b * plane_elems;
+    float* __restrict__ pplane = p.path ? p.path + (size_t)b * plane_elems : nullptr;   // null: index + durations only
+    const size_t fill_elems = p.path ? plane_elems : 0;
 
     if (tid == 0) {
         for (int w = 0; w < NDP; ++w) {
@@ -606,14 +609,14 @@ __global__ void __launch_bounds__(NT, 1) mas_wave_kernel(const __grid_constant__
         constexpr int HT = NT - 32 * (NDP + 1);
         const uintptr_t addr = reinterpret_cast<uintptr_t>(pplane);
         size_t head = ((16 - (addr & 15)) & 15) / 4;
-        if (head > plane_elems) head = plane_elems;
-        const size_t nvec = (plane_elems - head) / 4;
+        if (head > fill_elems) head = fill_elems;
+        const size_t nvec = (fill_elems - head) / 4;
         const size_t tail0 = head + nvec * 4;
         float4* pv = reinterpret_cast<float4*>(pplane + head);
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
         for (size_t i = ht; i < nvec; i += HT) pv[i] = z4;
         if ((size_t)ht < head) pplane[ht] = 0.f;
-        for (size_t i = tail0 + ht; i < plane_elems; i += HT) pplane[i] = 0.f;
+        for (size_t i = tail0 + ht; i < fill_elems; i += HT) pplane[i] = 0.f;
     }
     __syncthreads();
     if (tid == 0) mas_stamp(4);
@@ -702,7 +705,8 @@ __global__ void __launch_bounds__(F_NT, 1) mas_fused_kernel(const __grid_constan
     const int n_iter = max(n_tiles, 1);
     const int n_act = valid ? (t_x + BAND - 1) / BAND : 0;
     const size_t plane_elems = (size_t)p.T_x * p.T_y;
-    float* __restrict__ pplane = p.path + (size_t)b * plane_elems;
+    float* __restrict__ pplane = p.path ? p.path + (size_t)b * plane_elems : nullptr;   // null: index + durations only
+    const size_t fill_elems = p.path ? plane_elems : 0;
 
     if (tid == 0) {
         for (int w = 0; w < NDP; ++w) {
@@ -739,8 +743,8 @@ __global__ void __launch_bounds__(F_NT, 1) mas_fused_kernel(const __grid_constan
         constexpr int HT = 32 * F_NMMA;
         const uintptr_t addr = reinterpret_cast<uintptr_t>(pplane);
         size_t head = ((16 - (addr & 15)) & 15) / 4;
-        if (head > plane_elems) head = plane_elems;
-        const size_t nvec = (plane_elems - head) / 4;
+        if (head > fill_elems) head = fill_elems;
+        const size_t nvec = (fill_elems - head) / 4;
         const size_t tail0 = head + nvec * 4;
         float4* pv = reinterpret_cast<float4*>(pplane + head);
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -886,7 +890,7 @@ __global__ void __launch_bounds__(F_NT, 1) mas_fused_kernel(const __grid_constan
             for (size_t i = lo + ht; i < hi; i += HT) pv[i] = z4;
             if (it == 0) {
                 if ((size_t)ht < head) pplane[ht] = 0.f;
-                for (size_t i = tail0 + ht; i < plane_elems; i += HT) pplane[i] = 0.f;
+                for (size_t i = tail0 + ht; i < fill_elems; i += HT) pplane[i] = 0.f;
             }
         }
     }
@@ -927,10 +931,11 @@ __global__ void __launch_bounds__(GEN_NT, 1) mas_generic_kernel(const Params p, 
     const bool valid = (t_x >= 1) && (t_y >= t_x);
     const size_t plane_elems = (size_t)p.T_x * p.T_y;
     const float* __restrict__ vplane = p.value + (size_t)b * plane_elems;
-    float* __restrict__ pplane = p.path + (size_t)b * plane_elems;
+    float* __restrict__ pplane = p.path ? p.path + (size_t)b * plane_elems : nullptr;   // null: index + durations only
+    const size_t fill_elems = p.path ? plane_elems : 0;
     uint32_t* wsb = ws + (size_t)b * p.T_y * W;
 
-    for (size_t i = tid; i < plane_elems; i += GEN_NT) pplane[i] = 0.f;
+    for (size_t i = tid; i < fill_elems; i += GEN_NT) pplane[i] = 0.f;
     if (p.dur_out) for (int x = tid; x < p.T_x; x += GEN_NT) p.dur_out[(size_t)b * p.T_x + x] = 0;
     if (p.idx_out) for (int y = tid; y < p.T_y; y += GEN_NT) p.idx_out[(size_t)b * p.T_y + y] = -1;
     for (int x = tid; x < p.T_x; x += GEN_NT) qa[x] = 0.f;
@@ -959,7 +964,7 @@ __global__ void __launch_bounds__(GEN_NT, 1) mas_generic_kernel(const Params p, 
     if (tid == 0) {
         int index = t_x - 1, cnt = 0;
         for (int y = t_y - 1; y >= 0; --y) {
-            pplane[(size_t)index * p.T_y + y] = 1.0f;
+            if (pplane) pplane[(size_t)index * p.T_y + y] = 1.0f;
             if (p.idx_out) p.idx_out[(size_t)b * p.T_y + y] = index;
             ++cnt;
             if (index != 0 && ((wsb[(size_t)y * W + (index >> 5)] >> (index & 31)) & 1u)) {
@@ -1107,7 +1112,8 @@ int forward(const float* value, const int* t_xs, const int* t_ys, float* path, i
     GTK_REQUIRE(B >= 0 && T_x >= 0 && T_y >= 0, "negative size");
     if (B == 0) return GTK_OK;
     GTK_REQUIRE(t_xs && t_ys, "null pointer");
-    GTK_REQUIRE((value && path) || T_x == 0 || T_y == 0, "null pointer");
+    GTK_REQUIRE(value || T_x == 0 || T_y == 0, "null pointer");
+    GTK_REQUIRE(path || dur_out || idx_out, "no output requested");
     if (T_x == 0 || T_y == 0) {
         if (dur_out && B * T_x > 0) GTK_CUDA(cudaMemsetAsync(dur_out, 0, sizeof(int) * (size_t)B * T_x, stream));
         if (idx_out && B * T_y > 0) GTK_CUDA(cudaMemsetAsync(idx_out, 0xff, sizeof(int) * (size_t)B * T_y, stream));

@@ -94,6 +94,13 @@ int mle_loss_fwd(const float* z, const float* m, const float* logs, const float*
 int mle_loss_bwd(const float* z, const float* m, const float* logs, const float* acc4, const float* gloss, float* dz,
                  float* dm, float* dlogs, float* dlogdet, int B, int C, int T, cudaStream_t st);
 int gather_tokens(const float* src, const int* idx, float* out, int B, int C, int T_x, int T_y, cudaStream_t st);
+// WN.cond_layer(g) of every block in one launch (cond.cu)
+constexpr int COND_MAX_BLOCKS = 32;
+struct CondJobs { const float* g[COND_MAX_BLOCKS]; const float* v[COND_MAX_BLOCKS]; const float* b[COND_MAX_BLOCKS]; int n; };
+struct CondGrads { float* g[COND_MAX_BLOCKS]; float* v[COND_MAX_BLOCKS]; float* b[COND_MAX_BLOCKS]; int n; };
+int cond_all(const CondJobs& J, const float* g, float* cond, int B, int G, int N, cudaStream_t st);
+int cond_all_bwd(const CondJobs& J, const CondGrads& D, const float* g, const float* dcond, float* dg, int B, int G, int N,
+                 cudaStream_t st);
 }  // namespace flow
 
 namespace conv {

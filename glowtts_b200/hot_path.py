@@ -47,11 +47,12 @@ def train_hot_path(decoder, y, y_lengths, x_m, x_logs, x_lengths, g=None, return
         lp = ops.logp(x_m.detach(), None if x_logs is None else x_logs.detach(), z.detach())
         t_xs = x_lengths.to(torch.int32)
         t_ys = y_lengths.to(torch.int32)
+        # the kernel only reads cells inside [0,t_x) x [0,t_y), so value*mask (__init__.py:11) need not be materialised
         if return_attn:
-            x_mask = sequence_mask(x_lengths, x_m.shape[2]).to(y.dtype)
-            lp = lp * (x_mask[:, :, None] * z_mask)                                      # __init__.py:11
-        # the kernel only reads cells inside [0,t_x) x [0,t_y), so value*mask need not be materialised
-        attn, dur, idx = ops.mas_path(lp, t_xs, t_ys)
+            attn, dur, idx = ops.mas_path(lp, t_xs, t_ys)
+        else:
+            attn = None                                    # nobody reads the [B,T_x,T_y] float path: do not write it
+            dur, idx = ops.mas_index(lp, t_xs, t_ys)
     z_m = ops.gather_tokens(x_m, idx, T_y)
     z_logs = None if x_logs is None else ops.gather_tokens(x_logs, idx, T_y)
     loss = commons.mle_loss(z, z_m, z_logs, logdet, z_mask)

@@ -86,7 +86,13 @@ class FlowSpecDecoder(nn.Module):
     def _cond(self, g: Optional[torch.Tensor]):
         if g is None or self.gin_channels == 0:
             return None
-        return torch.stack([self.flows[3 * b + 2].wn.conditioning(g) for b in range(self.n_blocks)], 0)
+        # cond_layer(g) of all blocks (weight-norm fold, GEMM, bias) in ONE library launch, [NB, B, 2HL]
+        layers = [self.flows[3 * b + 2].wn.cond_layer for b in range(self.n_blocks)]
+        folded = layers[0].folded
+        ws = []
+        for l in layers:
+            ws += [l.weight, l.bias] if folded else [l.weight_g, l.weight_v, l.bias]
+        return ops.cond_layers(g.reshape(g.shape[0], -1).to(torch.float32), ws, self.n_blocks, folded)
 
     def forward(self, x, x_mask, g=None, emo=None, pitch=None, energy=None, reverse=False):
         if pitch is not None or energy is not None:

@@ -203,8 +203,9 @@ class WN(nn.Module):
         """cond_layer(g) (modules.py:148-149): g [B,gin,1] -> [B, 2H*L] (a [2HL x gin] x [gin x B] GEMM)."""
         if g is None:
             return None
-        w = self.cond_layer.effective_weight().squeeze(-1)
-        return torch.addmm(self.cond_layer.bias, g.reshape(g.shape[0], -1).to(w.dtype), w.t())
+        l = self.cond_layer
+        ws = [l.weight, l.bias] if l.folded else [l.weight_g, l.weight_v, l.bias]
+        return ops.cond_layers(g.reshape(g.shape[0], -1).to(torch.float32), ws, 1, l.folded)[0]
 
     def forward(self, x, x_mask=None, g=None, **kwargs):
         H = self.hidden_channels

@@ -86,6 +86,29 @@ def _(value, t_xs, t_ys, force_generic=0):
             value.new_empty((B, T_y), dtype=torch.int32))
 
 
+@torch.library.custom_op(f"{NS}::mas_index", mutates_args=(), device_types="cuda")
+def mas_index(value: Tensor, t_xs: Tensor, t_ys: Tensor) -> Tuple[Tensor, Tensor]:
+    """core.pyx:9-45 without the [B,T_x,T_y] path plane (gtk_mas_forward with path = NULL): -> (durations i32 [B,T_x],
+    index i32 [B,T_y]).  What the training step needs (models.py:1085, 1118-1119 as a gather): the float path is
+    never written, so the kernel's HBM traffic is the 4 B/cell read of `value`."""
+    value = _chk(value, "value")
+    t_xs = _chk(t_xs, "t_xs", torch.int32)
+    t_ys = _chk(t_ys, "t_ys", torch.int32)
+    B, T_x, T_y = value.shape
+    dur = torch.empty(B, T_x, dtype=torch.int32, device=value.device)
+    idx = torch.empty(B, T_y, dtype=torch.int32, device=value.device)
+    ws_bytes = _lib.load().gtk_mas_workspace_bytes(B, T_x, T_y)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=value.device) if ws_bytes else None
+    _lib.call("gtk_mas_forward", _p(value), _p(t_xs), _p(t_ys), None, _p(dur), _p(idx), B, T_x, T_y, _p(ws), ws_bytes, 0, _stream())
+    return dur, idx
+
+
+@mas_index.register_fake
+def _(value, t_xs, t_ys):
+    B, T_x, T_y = value.shape
+    return value.new_empty((B, T_x), dtype=torch.int32), value.new_empty((B, T_y), dtype=torch.int32)
+
+
 def mas_fused_supported(D: int, T_x: int, T_y: int, has_x_logs: bool) -> bool:
     """Whether gtk_mas_fused_logp covers this shape (mean_only, D == 80, T_x <= 256, T_y % 4 == 0)."""
     return bool(_lib.load().gtk_mas_fused_supported(int(D), int(T_x), int(T_y), int(has_x_logs)))
@@ -907,6 +930,88 @@ def _dec_bwd(ctx, dz, dlogdet, dws):
 
 decoder_forward.register_autograd(_dec_bwd, setup_context=_dec_setup)
 decoder_forward_flat.register_autograd(_decf_bwd, setup_context=_decf_setup)
+
+
+# =============================================================================== speaker conditioning
+def _ptr_array(ts: Sequence[Optional[Tensor]]):
+    arr = (ctypes.c_void_p * len(ts))()
+    for i, t in enumerate(ts):
+        arr[i] = None if t is None else t.data_ptr()
+    return arr
+
+
+@torch.library.custom_op(f"{NS}::cond_layers", mutates_args=(), device_types="cuda")
+def cond_layers(g: Tensor, weights: List[Tensor], n_blocks: int, folded: bool) -> Tensor:
+    """WN.cond_layer(g) (modules.py:148-149) of every coupling block in one launch.  g [B,G]; weights = per block
+    (weight_g [N,1,1], weight_v [N,G,1], bias [N]) -- or (weight [N,G,1], bias [N]) when folded -- flattened.
+    -> cond [n_blocks, B, N]."""
+    g = _chk(g, "g")
+    weights = _chk_list(weights, "cond weights")
+    per = 2 if folded else 3
+    B, G = g.shape
+    wv = [weights[per * k + (0 if folded else 1)] for k in range(n_blocks)]
+    wg = None if folded else [weights[per * k] for k in range(n_blocks)]
+    bs = [weights[per * k + per - 1] for k in range(n_blocks)]
+    N = wv[0].shape[0]
+    cond = torch.empty(n_blocks, B, N, dtype=g.dtype, device=g.device)
+    _lib.call("gtk_cond_layers", None if wg is None else _ptr_array(wg), _ptr_array(wv), _ptr_array(bs), n_blocks, _p(g), _p(cond),
+              B, G, N, _stream())
+    return cond
+
+
+@cond_layers.register_fake
+def _(g, weights, n_blocks, folded):
+    return g.new_empty((n_blocks, g.shape[0], weights[1 if not folded else 0].shape[0]))
+
+
+@torch.library.custom_op(f"{NS}::cond_layers_bwd", mutates_args=(), device_types="cuda")
+def cond_layers_bwd(g: Tensor, weights: List[Tensor], n_blocks: int, folded: bool, dcond: Tensor) -> Tuple[Tensor, Tensor]:
+    """-> (dg [B,G], flat gradient of `weights` in order, each padded to a multiple of 4 floats: ops.grad_layout)."""
+    g, dcond = _chk(g, "g"), _chk(dcond, "dcond")
+    weights = _chk_list(weights, "cond weights")
+    per = 2 if folded else 3
+    B, G = g.shape
+    offs, sizes, tot = grad_layout(weights)
+    flat = torch.empty(tot, dtype=g.dtype, device=g.device)
+    views = [flat[o:o + n] for o, n in zip(offs, sizes)]
+    wv = [weights[per * k + (0 if folded else 1)] for k in range(n_blocks)]
+    wg = None if folded else [weights[per * k] for k in range(n_blocks)]
+    dwv = [views[per * k + (0 if folded else 1)] for k in range(n_blocks)]
+    dwg = None if folded else [views[per * k] for k in range(n_blocks)]
+    dbs = [views[per * k + per - 1] for k in range(n_blocks)]
+    N = wv[0].shape[0]
+    dg = torch.zeros_like(g)
+    _lib.call("gtk_cond_layers_bwd", None if wg is None else _ptr_array(wg), _ptr_array(wv), n_blocks, _p(g), _p(dcond),
+              None if dwg is None else _ptr_array(dwg), _ptr_array(dwv), _ptr_array(dbs), _p(dg), B, G, N, _stream())
+    return dg, flat
+
+
+@cond_layers_bwd.register_fake
+def _(g, weights, n_blocks, folded, dcond):
+    return torch.empty_like(g), g.new_empty((grad_layout(weights)[2],))
+
+
+def _cond_setup(ctx, inputs, output):
+    g, weights, n_blocks, folded = inputs
+    ctx.save_for_backward(g, *weights)
+    ctx.n_blocks, ctx.folded = n_blocks, folded
+
+
+def _cond_bwd(ctx, dcond):
+    g, *weights = ctx.saved_tensors
+    dg, flat = cond_layers_bwd(g, list(weights), ctx.n_blocks, ctx.folded, dcond.contiguous())
+    group = _GRAD_SYNC["group"]
+    if group is not None and _world(group) > 1:
+        # data-parallel training: the conditioner's gradients are not part of the decoder's flat buffer, so they are
+        # averaged here -- one collective for all blocks (DDP reduces every parameter: train_ms_emo_lang_pitch.py:166)
+        from .distributed import sync_flat_grad
+        sync_flat_grad(flat, group)
+    offs, sizes, _ = grad_layout(weights)
+    grads = [flat[o:o + n].view(w.shape) for o, n, w in zip(offs, sizes, weights)]
+    return dg, grads, None, None
+
+
+cond_layers.register_autograd(_cond_bwd, setup_context=_cond_setup)
 
 
 # =============================================================================== coupling-block pieces

@@ -54,7 +54,9 @@ size_t gtk_mas_workspace_bytes(int B, int T_x, int T_y);
 
 /* Replaces maximum_path_c / maximum_path_each (monotonic_align/core.pyx:9-45) and the host
  * round trip of monotonic_align/__init__.py:11-21.  value [B,T_x,T_y] is NOT modified.
- * path [B,T_x,T_y] is fully written (0/1).  dur_out [B,T_x] (frames per token = attn.sum(2),
+ * path [B,T_x,T_y] is fully written (0/1); path may be NULL when only the alignment's consumers are wanted (durations
+ * and the per-frame index; the training step gathers the prior with the index instead of the attn^T matmul,
+ * models.py:1118-1119), which halves the kernel's HBM traffic to the 4 B/cell read.  dur_out [B,T_x] (frames per token = attn.sum(2),
  * models.py:1085) and idx_out [B,T_y] (token per frame, -1 beyond t_y) are optional (NULL).
  * Bit-exact with core.pyx for the same fp32 value; utterances with t_x > t_y (undefined
  * behaviour in the reference) or empty lengths produce an all-zero path. */
@@ -220,6 +222,19 @@ int gtk_tc_wn_bwd_layer(const void* drs_bf16, int ld_drs, const void* wrs_t, con
                         const float* mask, const float* resid_tp, float* out_tp, void* dxin_bf16, void* out_bf16,
                         int ld_out, int B, int T, int H, int RS, int K, int dil, float drop_p,
                         unsigned long long drop_seed, void* stream);
+
+/* WN.cond_layer(g) (modules.py:122-124, 148-149: a weight-normed 1x1 conv gin_channels -> 2*H*L applied to the speaker
+ * embedding g [B, G, 1]) of n_blocks coupling blocks in ONE launch: cond[k][b][n] = bias_k[n] + sum_c W_k[n][c] g[b][c],
+ * W_k = weight_g_k[n] * weight_v_k[n][:] / ||weight_v_k[n][:]|| (pass weight_g == NULL, or a NULL entry, for a conv whose
+ * weight norm was removed).  weight_g / weight_v / bias: host arrays of n_blocks (<= 32) DEVICE pointers ([N], [N, G],
+ * [N]); g [B, G]; cond [n_blocks, B, N] (the layout gtk_block_params.cond expects per block).  G <= 512. */
+int gtk_cond_layers(const float* const* weight_g, const float* const* weight_v, const float* const* bias, int n_blocks,
+                    const float* g, float* cond, int B, int G, int N, void* stream);
+/* Its backward: dcond [n_blocks, B, N] -> d_weight_g / d_weight_v / d_bias (host arrays of device pointers, WRITTEN) and
+ * dg [B, G] (ACCUMULATED with atomics: zero it first; may be NULL). */
+int gtk_cond_layers_bwd(const float* const* weight_g, const float* const* weight_v, int n_blocks, const float* g,
+                        const float* dcond, float* const* d_weight_g, float* const* d_weight_v, float* const* d_bias, float* dg,
+                        int B, int G, int N, void* stream);
 
 /* ---- whole decoder (models.py:719-789) --------------------------------------------------- */
 typedef struct gtk_decoder_desc {

@@ -233,3 +233,18 @@ def test_fused_wrapper_routes_uncovered_shapes_through_logp_then_mas():
     assert torch.equal(path, want)
     with pytest.raises(RuntimeError):
         ops.mas_fused_logp(z, x_m, t_xs, t_ys)
+
+
+@pytest.mark.parametrize("shape", [(32, 180, 860), (3, 33, 65), (2, 600, 700)])
+def test_index_only_mode_matches_full_mode(shape):
+    """gtk_mas_forward with path = NULL (ops.mas_index): same durations and per-frame index as the full call, on the
+    TMA, helper-warp and generic kernels."""
+    from glowtts_b200 import ops
+    b, tx, ty = shape
+    value, mask, t_xs, t_ys = helpers.mas_case(b, tx, ty, 900 + tx, ragged=True, quantised=True)
+    v = torch.from_numpy(value).cuda()
+    xs, ys = torch.from_numpy(t_xs).cuda(), torch.from_numpy(t_ys).cuda()
+    path, dur, idx = ops.mas_path(v, xs, ys)
+    dur2, idx2 = ops.mas_index(v, xs, ys)
+    assert torch.equal(dur, dur2) and torch.equal(idx, idx2)
+    assert torch.equal(path.sum(2).to(torch.int32), dur2)
