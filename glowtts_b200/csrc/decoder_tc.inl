@@ -99,7 +99,7 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
         L->b_lstride = align_up((size_t)2 * H * nq * 2, 1024);      // per-layer copies: the grouped weight-gradient
         L->b_drs = take(L->b_lstride * D.L);                         // launch at the end of the block reads them all
         L->b_dxin = take(L->b_lstride * D.L);
-        L->b_dgate = take((size_t)2 * H * nq * 2);
+        L->b_dgate = take(L->b_lstride * D.L);                      // per layer too: their column sums run once per block
         L->b_dhf[0] = take((size_t)H * nqp * 4);
         L->b_dhf[1] = take((size_t)H * nqp * 4);
         L->b_dh0 = take((size_t)H * nq * 2);
@@ -395,7 +395,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
             const bf16* h_i = reinterpret_cast<const bf16*>(act + A.h[i]);
             const bool want_dcond = P.cond && G.cond;
             // the conditioning enters after the dropout: with both active the un-scaled gate gradient is kept as well
-            bf16* dpre = (want_dcond && d->p_dropout > 0.f) ? dgate : nullptr;
+            bf16* dpre = (want_dcond && d->p_dropout > 0.f) ? dgate + (size_t)i * (L.b_lstride / 2) : nullptr;
             GTK_TRY(queue(P.rs_g[i], P.rs_v[i], G.rs_g[i], G.rs_v[i], G.rs_b[i], drs_i, 2 * H, RS, acts, H, H, RS, H, 1, 1));
             GTK_TRY(queue(P.in_g[i], P.in_v[i], G.in_g[i], G.in_v[i], G.in_b[i], dxin, 2 * H, 2 * H, h_i, H, H, 2 * H, H, K, dil));
             if (tc::wn_bwd_supported(H, K, dil)) {
@@ -437,10 +437,10 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                     GTK_TRY(tc::conv_tc_launch(dxin, 2 * H, pk + Q.t_in[i], p, tc::EPI_PLAIN, st));
                 }
             }
-            if (want_dcond)      // d cond_layer(g)[b, n] = sum over the utterance's rows of the gate-input gradient
-                GTK_TRY(tc::colsum_frames_seg(dpre ? dpre : dxin, 2 * H, 2 * H, D.B, pl.off, G.cond + (size_t)i * 2 * H,
-                                              (size_t)2 * H * D.L, st));
         }
+        if (P.cond && G.cond)   // d cond_layer(g)[b, layer, n] = sum over the utterance's rows of the gate-input gradient, all layers
+            GTK_TRY(tc::colsum_frames_seg(d->p_dropout > 0.f ? dgate : dxin_of(0), 2 * H, 2 * H, D.B, pl.off, G.cond,
+                                          (size_t)2 * H * D.L, st, D.L, L.b_lstride / 2, (size_t)2 * H));
         // start conv: h0 = (W x0 + b) * mask   (dh0 is already masked)
         GTK_TRY(queue(P.start_g, P.start_v, G.start_g, G.start_v, G.start_b, dh0, H, H, a0, ldCh, ldCh, H, Ch, 1, 1));
         {

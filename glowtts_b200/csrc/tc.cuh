@@ -150,8 +150,9 @@ size_t wgrad_group_workspace_bytes();
 // n_rows: null, or (varlen packing, B == 1) device pointer to hdr[1] of the packing plan {0, n_rows}: rows in use
 int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, const int* n_rows, cudaStream_t st);
 // out[g * out_gstride + n] += sum of rows [seg[g], seg[g + 1]) (device-resident bounds) of frames in[.., n]
+// n_buf > 1: the same reduction over n_buf buffers buf_stride ELEMENTS apart, outputs out_bstride floats apart
 int colsum_frames_seg(const __nv_bfloat16* in, int ld, int n_cols, int groups, const int* seg, float* out, size_t out_gstride,
-                      cudaStream_t st);
+                      cudaStream_t st, int n_buf = 1, size_t buf_stride = 0, size_t out_bstride = 0);
 int zero_guard_rows(__nv_bfloat16* base, size_t stride_bytes, int n_buf, size_t stride2_bytes, int n_buf2, int ld,
                     const int* n_rows, int n_guard, int T, cudaStream_t st);
 int colsum_frames(const __nv_bfloat16* in, int ld, int n_cols, int groups, long long rows_per_group, float* out, size_t out_gstride,

@@ -264,32 +264,61 @@ int colsum_frames(const __nv_bfloat16* in, int ld, int n_cols, int groups, long 
 }
 
 // The same with device-resident group bounds (varlen packing: utterance b = rows [off[b], off[b+1]); whole batch =
-// {0, n_rows}).  grid.y = groups * SEG_SPLITS row slices.
-constexpr int SEG_SPLITS = 8;
-__global__ void colsum_frames_seg_kernel(const __nv_bfloat16* __restrict__ in, int ld, int n_cols, const int* __restrict__ seg,
-                                         float* __restrict__ out, size_t out_gstride) {
+// {0, n_rows}), vectorised: a thread owns 8 consecutive columns (one 16-byte load per row) and every 8th row of its
+// slice; grid (column blocks of 256, groups * SEG_SPLITS row slices, n_buf buffers `buf_stride` elements apart whose
+// outputs are `out_bstride` floats apart -- the L per-layer gradients of a coupling block in one launch).
+constexpr int SEG_SPLITS = 8, SEG_RL = 8;
+__global__ void __launch_bounds__(256) colsum_frames_seg_kernel(const __nv_bfloat16* __restrict__ in, int ld, int n_cols,
+                                                                const int* __restrict__ seg, float* __restrict__ out,
+                                                                size_t out_gstride, size_t buf_stride, size_t out_bstride) {
     const int g = blockIdx.y / SEG_SPLITS, rs = blockIdx.y % SEG_SPLITS;
-    const int n = blockIdx.x * 64 + (threadIdx.x & 63);
-    const int rl = threadIdx.x >> 6;
+    const int cv = threadIdx.x & 31, rl = threadIdx.x >> 5;          // 32 column vectors x 8 row lanes
+    const int n0 = (blockIdx.x * 32 + cv) * 8;
+    in += (size_t)blockIdx.z * buf_stride;
+    out += (size_t)blockIdx.z * out_bstride;
     const long long lo = seg[g], len = (long long)seg[g + 1] - lo;
     const long long r_lo = lo + len * rs / SEG_SPLITS, r_hi = lo + len * (rs + 1) / SEG_SPLITS;
-    float acc = 0.f;
-    if (n < n_cols)
-        for (long long r = r_lo + rl; r < r_hi; r += 4) acc += __bfloat162float(in[(size_t)r * ld + n]);
-    __shared__ float red[256];
-    red[threadIdx.x] = acc;
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    const bool vec = (ld % 8 == 0) && n0 + 8 <= n_cols;
+    if (n0 < n_cols) {
+        for (long long r = r_lo + rl; r < r_hi; r += SEG_RL) {
+            const __nv_bfloat16* src = in + (size_t)r * ld + n0;
+            if (vec) {
+                const uint4 q = *reinterpret_cast<const uint4*>(src);
+                const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
+                    acc[2 * i] += __low2float(h);
+                    acc[2 * i + 1] += __high2float(h);
+                }
+            } else {
+                for (int i = 0; i < 8 && n0 + i < n_cols; ++i) acc[i] += __bfloat162float(src[i]);
+            }
+        }
+    }
+    __shared__ float red[SEG_RL][32][9];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) red[rl][cv][i] = acc[i];
     __syncthreads();
-    if (rl == 0 && n < n_cols) {
-        const float s = red[threadIdx.x] + red[threadIdx.x + 64] + red[threadIdx.x + 128] + red[threadIdx.x + 192];
+    for (int e = threadIdx.x; e < 256; e += 256) {
+        const int c = e >> 3, i = e & 7, n = (blockIdx.x * 32 + c) * 8 + i;
+        if (n >= n_cols) continue;
+        float s = 0.f;
+#pragma unroll
+        for (int q = 0; q < SEG_RL; ++q) s += red[q][c][i];
         if (s != 0.f) atomicAdd(out + (size_t)g * out_gstride + n, s);
     }
 }
 int colsum_frames_seg(const __nv_bfloat16* in, int ld, int n_cols, int groups, const int* seg, float* out, size_t out_gstride,
-                      cudaStream_t st) {
-    GTK_REQUIRE(in && out && seg, "null");
+                      cudaStream_t st, int n_buf, size_t buf_stride, size_t out_bstride) {
+    GTK_REQUIRE(in && out && seg && n_buf >= 1, "null");
     if (groups == 0 || n_cols == 0) return GTK_OK;
-    dim3 grid(ceil_div(n_cols, 64), groups * SEG_SPLITS);
-    colsum_frames_seg_kernel<<<grid, 256, 0, st>>>(in, ld, n_cols, seg, out, out_gstride);
+    dim3 grid(ceil_div(n_cols, 256), groups * SEG_SPLITS, n_buf);
+    ProfScope prof("colsum_seg", st);
+    colsum_frames_seg_kernel<<<grid, 256, 0, st>>>(in, ld, n_cols, seg, out, out_gstride, buf_stride, out_bstride);
     return check_launch("colsum_frames_seg");
 }
 
