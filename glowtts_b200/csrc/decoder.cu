@@ -7,7 +7,10 @@
 //  * Weight norm is folded on device once per call; its backward is fused behind each weight gradient.
 //  * precision 0 runs every contraction in fp32 on CUDA cores (exact-parity path);
 //    precision 1 routes the WN / start / end contractions to the bf16 tcgen05 kernels (conv_tc.cu).
+#include <stdlib.h>
 #include <string.h>
+
+#include <mutex>
 
 #include "tc.cuh"
 #include "ops.h"
@@ -184,6 +187,55 @@ static int coupling_net(const Dims& D, const Layout& L, const gtk_block_params& 
     GTK_TRY(conv::pack_weight(P.end_w, wp, C, H, 1, 0, st));
     GTK_TRY(conv(act + L.a_skip, 0, wp, P.end_b, mask, nullptr, 0, act + L.a_end, 0, B, H, C, T, 1, 1, 0, 0, 0, st));
     return GTK_OK;
+}
+
+// Internal side stream of the bf16 backward: the weight gradients of block k (one persistent stream-K launch + reduce) run
+// on it while the data-gradient chain of block k - 1 runs on the caller's stream.  The chain launches fewer CTAs than the
+// GPU has SMs (one 128-row tile each), so the two fill the machine together.  Created once per device, lowest priority (the
+// chain is the critical path); joined back into the caller's stream before the backward call returns, so the call stays
+// stream-ordered for the caller -- and capturable: the side stream enters a CUDA-graph capture through the fork event
+// and leaves it through the join.  OFF by default (GTK_WGRAD_OVERLAP=1 turns it on): measured on B200 at configs[1] it
+// LOSES -- 5.29 ms / step against 4.75 ms (profiles/wgrad_overlap_r02.txt) -- because the stream-K weight gradient
+// (~490 MB of operand reads per block) and the fused layer kernels are both L2-bandwidth bound, so they contend
+// instead of filling each other's idle SMs.
+struct SideStream {
+    cudaStream_t s;
+    cudaEvent_t fork[2], done[2];
+};
+static int side_stream(SideStream** out) {
+    constexpr int MAX_DEV = 64;
+    static SideStream* tab[MAX_DEV] = {nullptr};
+    static std::mutex mu;
+    *out = nullptr;
+    static int enabled = -1;
+    if (enabled < 0) { const char* e = getenv("GTK_WGRAD_OVERLAP"); enabled = (e && e[0] == '1') ? 1 : 0; }
+    if (!enabled) return GTK_OK;
+    int dev = 0;
+    GTK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEV) return GTK_OK;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!tab[dev]) {
+        SideStream* ss = new SideStream();
+        int lo = 0, hi = 0;
+        GTK_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));          // lo = least priority (numerically greatest)
+        GTK_CUDA(cudaStreamCreateWithPriority(&ss->s, cudaStreamNonBlocking, lo));
+        for (int i = 0; i < 2; ++i) {
+            GTK_CUDA(cudaEventCreateWithFlags(&ss->fork[i], cudaEventDisableTiming));
+            GTK_CUDA(cudaEventCreateWithFlags(&ss->done[i], cudaEventDisableTiming));
+        }
+        tab[dev] = ss;
+    }
+    *out = tab[dev];
+    return GTK_OK;
+}
+static int wgrad_overlap_ctas() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("GTK_WGRAD_CTAS");
+        v = e ? atoi(e) : 0;
+        if (v <= 0) v = max(16, sm_count() * 2 / 5);     // ~60 of 148: what a ragged B=32 batch's 128-row tiles leave idle
+    }
+    return v;
 }
 
 #include "decoder_tc.inl"

@@ -27,6 +27,8 @@ struct TcLayout {          // byte offsets in the workspace
     TcAct A;
     // backward temporaries
     size_t b_dZ, b_dM, b_dend, b_drs, b_dxin, b_lstride, b_dgate, b_dhf[2], b_dh0, b_wpart;   // b_drs / b_dxin: one per layer, b_lstride apart
+    size_t b_pstride;                    // b_dend .. b_dh0 exist twice (block parity), b_pstride bytes apart: the weight
+                                         // gradients of block k read them on the side stream while block k - 1 writes its own
 };
 
 static int tc_supported(const Dims& D) {
@@ -95,14 +97,19 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     if (train) {
         L->b_dZ = take((size_t)C * nq * 4);
         L->b_dM = take((size_t)C * nq * 4);
-        L->b_dend = take((size_t)pad64(C) * nq * 2);
         L->b_lstride = align_up((size_t)2 * H * nq * 2, 1024);      // per-layer copies: the grouped weight-gradient
-        L->b_drs = take(L->b_lstride * D.L);                         // launch at the end of the block reads them all
-        L->b_dxin = take(L->b_lstride * D.L);
-        L->b_dgate = take(L->b_lstride * D.L);                      // per layer too: their column sums run once per block
+        for (int par = 0; par < 2; ++par) {                          // launch at the end of the block reads them all
+            const size_t o0 = off;
+            const size_t o_dend = take((size_t)pad64(C) * nq * 2);
+            const size_t o_drs = take(L->b_lstride * D.L);
+            const size_t o_dxin = take(L->b_lstride * D.L);
+            const size_t o_dgate = take(L->b_lstride * D.L);        // per layer too: their column sums run once per block
+            const size_t o_dh0 = take((size_t)H * nq * 2);
+            if (par == 0) { L->b_dend = o_dend; L->b_drs = o_drs; L->b_dxin = o_dxin; L->b_dgate = o_dgate; L->b_dh0 = o_dh0; }
+            else L->b_pstride = o0 - L->b_dend;
+        }
         L->b_dhf[0] = take((size_t)H * nqp * 4);
         L->b_dhf[1] = take((size_t)H * nqp * 4);
-        L->b_dh0 = take((size_t)H * nq * 2);
         L->b_wpart = take(tc::wgrad_group_workspace_bytes());
     }
     L->total = off;
@@ -317,13 +324,11 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     const int ldC = pad64(C), ldCh = pad64(Ch);
     float* dZ = reinterpret_cast<float*>(ws + L.b_dZ);
     float* dM = reinterpret_cast<float*>(ws + L.b_dM);
-    bf16* dend = reinterpret_cast<bf16*>(ws + L.b_dend);
-    auto drs_of = [&](int i) { return reinterpret_cast<bf16*>(ws + L.b_drs + (size_t)i * L.b_lstride); };
-    auto dxin_of = [&](int i) { return reinterpret_cast<bf16*>(ws + L.b_dxin + (size_t)i * L.b_lstride); };
-    bf16* dgate = reinterpret_cast<bf16*>(ws + L.b_dgate);
     float* dhf[2] = {reinterpret_cast<float*>(ws + L.b_dhf[0]), reinterpret_cast<float*>(ws + L.b_dhf[1])};
-    bf16* dh0 = reinterpret_cast<bf16*>(ws + L.b_dh0);
     float* wpart = reinterpret_cast<float*>(ws + L.b_wpart);   // stream-K partial tiles of the weight gradients
+    SideStream* side = nullptr;
+    GTK_TRY(side_stream(&side));
+    bool side_used[2] = {false, false};
 
     if (first) GTK_TRY(flow::squeeze_pack(dz, pl.off, pl.row_b, pl.mask_p, dZ, D.Cin, D.Tq * D.n, D.n, L.P, st));
     if (first) {   // gradients of the constant logdet terms of every block, one launch (they only need dlogdet and the saved W^-1)
@@ -347,19 +352,36 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         const float* xmix = reinterpret_cast<const float*>(act + A.xmix);
         const bf16* a0 = reinterpret_cast<const bf16*>(act + A.a0);
         const bf16* skip_bf = reinterpret_cast<const bf16*>(act + A.skip_bf);
+        // the gradient temporaries the weight-gradient launch reads: one set per block parity
+        const int par = blk & 1;
+        unsigned char* wp = ws + (size_t)par * L.b_pstride;
+        bf16* dend = reinterpret_cast<bf16*>(wp + L.b_dend);
+        auto drs_of = [&](int i) { return reinterpret_cast<bf16*>(wp + L.b_drs + (size_t)i * L.b_lstride); };
+        auto dxin_of = [&](int i) { return reinterpret_cast<bf16*>(wp + L.b_dxin + (size_t)i * L.b_lstride); };
+        bf16* dgate = reinterpret_cast<bf16*>(wp + L.b_dgate);
+        bf16* dh0 = reinterpret_cast<bf16*>(wp + L.b_dh0);
+        // the weight gradients of block blk + 2 (same parity) must have finished reading this set
+        if (side && side_used[par]) GTK_CUDA(cudaStreamWaitEvent(st, side->done[par], 0));
 
         // Weight / bias gradients of the whole block are queued here and run as ONE stream-K launch after the
-        // data-gradient chain (which is the critical path and keeps every dY it produced).
+        // data-gradient chain (which is the critical path and keeps every dY it produced) -- on the side stream, i.e.
+        // concurrently with the NEXT block's chain; the last block of the call has nothing to hide behind and gets all SMs.
         tc::WgradGroupJob jobs[tc::WGG_MAX_JOBS];
         int n_jobs = 0, n_tiles = 0;
+        cudaStream_t wst = side ? side->s : st;
         auto flush = [&]() -> int {
-            int rc = n_jobs ? tc::wgrad_group_launch(jobs, n_jobs, B, T, wpart, pl.n_rows(), st) : GTK_OK;
+            if (!n_jobs) return GTK_OK;
+            if (side) {
+                GTK_CUDA(cudaEventRecord(side->fork[par], st));
+                GTK_CUDA(cudaStreamWaitEvent(side->s, side->fork[par], 0));
+            }
+            int rc = tc::wgrad_group_launch(jobs, n_jobs, B, T, wpart, pl.n_rows(), wst, (side && blk > blk_lo) ? wgrad_overlap_ctas() : 0);
             n_jobs = 0; n_tiles = 0;
             return rc;
         };
         auto queue = [&](const float* g, const float* v, float* dg, float* dv, float* db, const bf16* dy, int ld_y, int cols_y,
                          const bf16* x, int ld_x, int cols_x, int M, int Cin, int Kk, int dil) -> int {
-            if (!dv) return db ? tc::colsum_frames_seg(dy, ld_y, M, 1, pl.hdr, db, 0, st) : GTK_OK;
+            if (!dv) return db ? tc::colsum_frames_seg(dy, ld_y, M, 1, pl.hdr, db, 0, st) : GTK_OK;   // (no caller leaves dv null)
             if (g && !dg) { set_error("decoder_backward(bf16): weight_g gradient pointer missing"); return GTK_ERR_INVALID; }
             const int tiles = ((M + 127) / 128) * Kk;
             if (n_jobs == tc::WGG_MAX_JOBS || n_tiles + tiles > tc::WGG_MAX_TILES) GTK_TRY(flush());
@@ -438,9 +460,6 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 }
             }
         }
-        if (P.cond && G.cond)   // d cond_layer(g)[b, layer, n] = sum over the utterance's rows of the gate-input gradient, all layers
-            GTK_TRY(tc::colsum_frames_seg(d->p_dropout > 0.f ? dgate : dxin_of(0), 2 * H, 2 * H, D.B, pl.off, G.cond,
-                                          (size_t)2 * H * D.L, st, D.L, L.b_lstride / 2, (size_t)2 * H));
         // start conv: h0 = (W x0 + b) * mask   (dh0 is already masked)
         GTK_TRY(queue(P.start_g, P.start_v, G.start_g, G.start_v, G.start_b, dh0, H, H, a0, ldCh, ldCh, H, Ch, 1, 1));
         {
@@ -452,10 +471,16 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
             GTK_TRY(tc::conv_tc_launch(dh0, H, pk + Q.t_start, p, tc::EPI_PLAIN, st));
         }
         GTK_TRY(flush());
+        if (P.cond && G.cond)   // d cond_layer(g)[b, layer, n] = sum over the utterance's rows of the gate-input gradient, all layers
+            GTK_TRY(tc::colsum_frames_seg(d->p_dropout > 0.f ? dgate : dxin_of(0), 2 * H, 2 * H, D.B, pl.off, G.cond,
+                                          (size_t)2 * H * D.L, wst, D.L, L.b_lstride / 2, (size_t)2 * H));
+        if (side) { GTK_CUDA(cudaEventRecord(side->done[par], side->s)); side_used[par] = true; }
         // ActNorm + InvConvNear (fp32)
         GTK_TRY(flow::mix_bwd(xin_blk, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, dM, dZ, G.an_logs, G.an_bias, G.ic_weight, B,
                               C, T, st, pl.n_rows()));
     }
     if (last) GTK_TRY(flow::unsqueeze_unpack(dZ, pl.off, dx, D.B, D.Cin, D.T, D.n, L.G, L.P, st));
+    for (int par = 0; par < 2; ++par)      // join: every gradient of this call is complete in the caller's stream order
+        if (side && side_used[par]) GTK_CUDA(cudaStreamWaitEvent(st, side->done[par], 0));
     return GTK_OK;
 }

@@ -148,7 +148,9 @@ struct WgradGroupJob {
 };
 size_t wgrad_group_workspace_bytes();
 // n_rows: null, or (varlen packing, B == 1) device pointer to hdr[1] of the packing plan {0, n_rows}: rows in use
-int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, const int* n_rows, cudaStream_t st);
+// max_ctas > 0 caps the persistent grid (a launch that overlaps other kernels must not claim every SM)
+int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, const int* n_rows, cudaStream_t st,
+                       int max_ctas = 0);
 // out[g * out_gstride + n] += sum of rows [seg[g], seg[g + 1]) (device-resident bounds) of frames in[.., n]
 // n_buf > 1: the same reduction over n_buf buffers buf_stride ELEMENTS apart, outputs out_bstride floats apart
 int colsum_frames_seg(const __nv_bfloat16* in, int ld, int n_cols, int groups, const int* seg, float* out, size_t out_gstride,

@@ -291,7 +291,8 @@ static int tmap_frames(CUtensorMap* out, const __nv_bfloat16* base, int ld, int 
     return make_tmap_bf16(out, base, 3, dims, strides, box, true);
 }
 
-int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, const int* n_rows, cudaStream_t st) {
+int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, const int* n_rows, cudaStream_t st,
+                       int max_ctas) {
     GTK_REQUIRE(jobs && n_jobs >= 1 && n_jobs <= WGG_MAX_JOBS && part_ws, "bad job list");
     if ((long long)B * T == 0) return GTK_OK;
     static thread_local GgParams P;                 // ~12 KB of kernel parameters, rebuilt per launch
@@ -342,7 +343,8 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     // stream-K cut: tile i covers [pos_i, pos_i + w_i S) on a line of length U; CTA c owns [c U / G, (c+1) U / G)
     long long U = 0;
     for (int i = 0; i < n_tiles; ++i) U += w_tile[i] * S;
-    const int G = (int)min((long long)min(sm_count(), WGG_MAX_CTAS), (long long)n_tiles * S);
+    int G = (int)min((long long)min(sm_count(), WGG_MAX_CTAS), (long long)n_tiles * S);
+    if (max_ctas > 0 && G > max_ctas) G = max_ctas;     // overlapped launch: leave the other SMs to the data-gradient chain
     int n_seg = 0, slot = 0, c = 0;
     long long pos = 0;
     for (int i = 0; i < n_tiles; ++i) {
