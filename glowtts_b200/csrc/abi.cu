@@ -305,6 +305,7 @@ int gtk_tc_colsum(const void* in_bf16, int ld, int n_cols, int groups, long long
 int gtk_debug_mas_trace(unsigned long long* out, int n_ctas) { return mas::trace_read(out, n_ctas); }
 int gtk_debug_mas_wait(long long* out, int n_ctas) { return mas::wait_read(out, n_ctas); }
 int gtk_debug_wn_trace(unsigned long long* out, int n_ctas) { return tc::wn_trace_read(out, n_ctas); }
+int gtk_debug_wn_wait(long long* out, int n_ctas) { return tc::wn_wait_read(out, n_ctas); }
 int gtk_debug_wb_trace(unsigned long long* out, int n_ctas) { return tc::wb_trace_read(out, n_ctas); }
 int gtk_debug_conv_trace_select(int epilogue, int taps) { tc::conv_trace_select(epilogue, taps); return GTK_OK; }
 int gtk_debug_conv_trace(unsigned long long* out, int n_ctas) { return tc::conv_trace_read(out, n_ctas); }

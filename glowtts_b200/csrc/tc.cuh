@@ -85,6 +85,7 @@ struct WnLayerParams {
     int n_sqz, cs_div;             // phase of channel n: (cs_base + n) / cs_div  (cs_div = 2HL / n_sqz)
     int cs_base;                   // layer * 2H
     float* h_out_f32_last;         // last layer: masked WN output also as fp32 tile-private master (input of a chained WN)
+    int dbg_noshift;               // instrumented builds: 1 = every tap reads the un-shifted tile (timing experiments only)
     const float* mask;             // [B, T]
     float drop_p;
     DropSeed drop_seed;
@@ -120,6 +121,7 @@ int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat1
                         __nv_bfloat16* dxin, __nv_bfloat16* out_bf16, int ld_out, WnBwdParams p, cudaStream_t st);
 
 int wn_trace_read(unsigned long long* out, int n_ctas);
+int wn_wait_read(long long* out, int n_ctas);
 int wb_trace_read(unsigned long long* out, int n_ctas);
 void conv_trace_select(int epi, int taps);
 int conv_trace_read(unsigned long long* out, int n_ctas);
