@@ -123,6 +123,7 @@ int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat1
 int wn_trace_read(unsigned long long* out, int n_ctas);
 int wn_wait_read(long long* out, int n_ctas);
 int wb_trace_read(unsigned long long* out, int n_ctas);
+int wb_wait_read(long long* out, int n_ctas);
 void conv_trace_select(int epi, int taps);
 int conv_trace_read(unsigned long long* out, int n_ctas);
 int conv_wait_read(long long* out, int n_ctas);

@@ -46,8 +46,15 @@ __device__ __forceinline__ unsigned long long wb_timer() {
         const int cta_ = blockIdx.y * gridDim.x + blockIdx.x;                               \
         if (threadIdx.x == 128 && cta_ < WB_TRACE_CTAS) g_wb_trace[cta_ * 7 + (i)] = wb_timer(); \
     } while (0)
+// SM cycles per CTA: [MMA thread waiting for weight stages in GEMM b, MMA thread GEMM-b total, producer waiting for free
+// stages in GEMM b, producer GEMM-b total]
+__device__ long long g_wb_wait[WB_TRACE_CTAS * 4];
+#define WB_CLK() clock64()
+#define WB_WAIT_STORE(i, v) do { const int cta_ = blockIdx.y * gridDim.x + blockIdx.x; if (cta_ < WB_TRACE_CTAS) g_wb_wait[cta_ * 4 + (i)] = (v); } while (0)
 #else
 #define WB_TRACE(i) do { } while (0)
+#define WB_CLK() 0ll
+#define WB_WAIT_STORE(i, v) do { } while (0)
 #endif
 
 // RowIo of frame f of utterance b for the tile-private tensors (addressed by frame, whatever the tiling of the kernel)
@@ -214,14 +221,20 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
 
     // ---------------------------------------------------------------- GEMM b: taps = row-shifted views of the smem tile
     if (warp == 0 && lane == 0) {
+        long long w_prod = 0;
+        const long long p0 = WB_CLK();
         for (int it = n_sb; it < n_b; ++it) {
             const int s = it % n_sb, use = it / n_sb;
+            const long long c0 = WB_CLK();
             mbar_wait(&ctl->empty_b[s], use & 1);
+            w_prod += WB_CLK() - c0;
             const int j = it / nkb, kc = it % nkb;
             mbar_arrive_expect_tx(&ctl->full_b[s], (uint32_t)sb_bytes);
             tma_load_3d_multicast(ring + (size_t)s * sb_bytes + (size_t)cta_rank * (H / WB_CL) * 128, &tmWin, &ctl->full_b[s],
                                   kc * KC, (int)cta_rank * (H / WB_CL), j, cl_mask);
         }
+        WB_WAIT_STORE(2, w_prod);
+        WB_WAIT_STORE(3, WB_CLK() - p0);
     } else if (warp == 1 && lane == 0) {
         mbar_wait(&ctl->acts_ready, 0);
         tc_fence_after();
@@ -231,9 +244,13 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
             for (int kc = 0; kc < nkb; ++kc) tma_store_3d(&tmDxin, smem + (size_t)kc * A_BYTES + halo * 128, kc * KC, t0, b);
             tma_store_commit();
         }
+        long long w_mma = 0;
+        const long long m0 = WB_CLK();
         for (int it = 0; it < n_b; ++it) {
             const int s = it % n_sb, use = it / n_sb;
+            const long long c0 = WB_CLK();
             mbar_wait(&ctl->full_b[s], use & 1);
+            w_mma += WB_CLK() - c0;
             tc_fence_after();
             const int j = it / nkb, kc = it % nkb;
             const uint64_t adesc = umma_desc_kmajor_sw128(smem_u32(smem + (size_t)kc * A_BYTES) + (uint32_t)(j * p.dil) * 128u);
@@ -244,6 +261,8 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
             umma_commit_multicast(&ctl->empty_b[s], cl_mask);
         }
         umma_commit(&ctl->acc_full);
+        WB_WAIT_STORE(0, w_mma);
+        WB_WAIT_STORE(1, WB_CLK() - m0);
     }
     __syncwarp();
 
@@ -295,6 +314,11 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
 }
 
 #ifdef GTK_INSTRUMENT
+int wb_wait_read(long long* out, int n_ctas) {
+    GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= WB_TRACE_CTAS, "n_ctas");
+    GTK_CUDA(cudaMemcpyFromSymbol(out, g_wb_wait, size_t(n_ctas) * 4 * sizeof(long long)));
+    return GTK_OK;
+}
 int wb_trace_read(unsigned long long* out, int n_ctas) {
     GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= WB_TRACE_CTAS, "n_ctas");
     GTK_CUDA(cudaMemcpyFromSymbol(out, g_wb_trace, size_t(n_ctas) * 7 * sizeof(unsigned long long)));

@@ -44,8 +44,15 @@ __device__ __forceinline__ unsigned long long gtimer() {
         const int cta_ = blockIdx.y * gridDim.x + blockIdx.x;                           \
         if (threadIdx.x == 128 && cta_ < WN_TRACE_CTAS) g_wn_trace[cta_ * 6 + (i)] = gtimer(); \
     } while (0)
+// SM cycles per CTA: [MMA thread waiting for operand stages in GEMM 1, MMA thread GEMM-1 total, producer waiting for free
+// stages, producer total]
+__device__ long long g_wn_wait[WN_TRACE_CTAS * 4];
+#define WN_CLK() clock64()
+#define WN_WAIT_STORE(i, v) do { const int cta_ = blockIdx.y * gridDim.x + blockIdx.x; if (cta_ < WN_TRACE_CTAS) g_wn_wait[cta_ * 4 + (i)] = (v); } while (0)
 #else
 #define WN_TRACE(i) do { } while (0)
+#define WN_CLK() 0ll
+#define WN_WAIT_STORE(i, v) do { } while (0)
 #endif
 
 __global__ void __launch_bounds__(EPI_NT, 1)
@@ -108,9 +115,14 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
             tma_load_3d(sb + (size_t)H * KC * 2, &tmWin, &ctl->full[it], kc * KC, H, j);
         }
         pdl_wait();
+        long long w_prod = 0;
+        const long long p0 = WN_CLK();
         for (int it = 0; it < n_all; ++it) {
             const int s = it % WN_STAGES, use = it / WN_STAGES;
+            if (it == n1) { WN_WAIT_STORE(2, w_prod); WN_WAIT_STORE(3, WN_CLK() - p0); }
+            const long long c0 = WN_CLK();
             if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
+            w_prod += WN_CLK() - c0;
             unsigned char* sa = smem + (size_t)s * stage_bytes;
             unsigned char* sb = sa + A_BYTES;
             if (it < n1) {
@@ -129,9 +141,13 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
             }
         }
     } else if (warp == 1 && lane == 0) {
+        long long w_mma = 0;
+        const long long m0 = WN_CLK();
         for (int it = 0; it < n1; ++it) {
             const int s = it % WN_STAGES, use = it / WN_STAGES;
+            const long long c0 = WN_CLK();
             mbar_wait(&ctl->full[s], use & 1);
+            w_mma += WN_CLK() - c0;
             tc_fence_after();
             const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
             const uint32_t sb = sa + A_BYTES;
@@ -147,6 +163,8 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
             umma_commit(&ctl->empty[s]);
         }
         umma_commit(&ctl->acc_full);                     // GEMM 1 done -> epilogue 1 may read TMEM
+        WN_WAIT_STORE(0, w_mma);
+        WN_WAIT_STORE(1, WN_CLK() - m0);
     }
     __syncwarp();
 
@@ -325,9 +343,9 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
 }
 
 #ifdef GTK_INSTRUMENT
-int wn_wait_read(long long* out, int n_ctas) {      // (wait counters exist in the N-chunked experiment kernel only)
-    GTK_REQUIRE(out && n_ctas >= 0, "n_ctas");
-    memset(out, 0, size_t(n_ctas) * 4 * sizeof(long long));
+int wn_wait_read(long long* out, int n_ctas) {
+    GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= WN_TRACE_CTAS, "n_ctas");
+    GTK_CUDA(cudaMemcpyFromSymbol(out, g_wn_wait, size_t(n_ctas) * 4 * sizeof(long long)));
     return GTK_OK;
 }
 int wn_trace_read(unsigned long long* out, int n_ctas) {

@@ -18,6 +18,8 @@ int gtk_debug_wn_trace(unsigned long long* out, int n_ctas);
 /* Debug: SM cycles per CTA of the last fused WN-layer launch: out[cta * 4 + {MMA thread waiting for weight stages during
  * GEMM 1, MMA thread GEMM-1 total, TMA producer waiting for free stages, producer total}]. */
 int gtk_debug_wn_wait(long long* out, int n_ctas);
+/* The same for GEMM b (the k = 5 data gradient) of the fused layer-backward kernel. */
+int gtk_debug_wb_wait(long long* out, int n_ctas);
 /* Debug: DP-warp phase stamps of the last TMA-path MAS launch: out[cta * 6 + {start, first tile landed, DP done,
  * backtrack done, barrier passed, end}] (globaltimer ns).  Synchronises the device. */
 int gtk_debug_mas_trace(unsigned long long* out, int n_ctas);
