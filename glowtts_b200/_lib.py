@@ -27,7 +27,9 @@ class DecoderDesc(ctypes.Structure):
         "B", "in_channels", "T", "n_sqz", "hidden", "kernel_size", "dilation_rate", "n_layers",
         "n_blocks", "n_split", "sigmoid_scale", "precision")] + [("p_dropout", ctypes.c_float),
                                                                  ("seed", ctypes.c_ulonglong),
-                                                                 ("seed_dev", ctypes.c_void_p)]
+                                                                 ("seed_dev", ctypes.c_void_p),
+                                                                 ("energy", ctypes.c_void_p), ("pitch", ctypes.c_void_p),
+                                                                 ("d_energy", ctypes.c_void_p), ("d_pitch", ctypes.c_void_p)]
 
 
 _BLOCK_FIELDS = ("an_logs", "an_bias", "ic_weight", "start_g", "start_v", "start_b",
@@ -35,9 +37,15 @@ _BLOCK_FIELDS = ("an_logs", "an_bias", "ic_weight", "start_g", "start_v", "start
 _ARRAY_FIELDS = ("in_g", "in_v", "in_b", "rs_g", "rs_v", "rs_b")
 
 
+class WnpParams(ctypes.Structure):
+    """gtk_wnp_params / gtk_wnp_grads."""
+    _fields_ = [(n, _f32p * GTK_MAX_LAYERS) for n in _ARRAY_FIELDS] + [(n, _f32p) for n in ("c1_g", "c1_v", "c1_b")]
+
+
 class BlockParams(ctypes.Structure):
     """gtk_block_params; gtk_block_grads has the same member order and types."""
-    _fields_ = [(n, (_f32p * GTK_MAX_LAYERS) if n in _ARRAY_FIELDS else _f32p) for n in _BLOCK_FIELDS]
+    _fields_ = [(n, (_f32p * GTK_MAX_LAYERS) if n in _ARRAY_FIELDS else _f32p) for n in _BLOCK_FIELDS] + [
+        ("wn_energy", WnpParams), ("wn_pitch", WnpParams)]
 
 
 BlockGrads = BlockParams

@@ -58,9 +58,26 @@ class CouplingBlock(nn.Module):
         self.wn_pitch.remove_weight_norm()
 
 
-def block_param_list(actnorm, invconv, coupling):
+def _wnp_param_list(wnp, folded):
+    """wn_energy / wn_pitch tensors in decoder_forward order (ops.py: after end_b when cfg[13] is set)."""
+    out, c1 = [], wnp.cond_layer1
+    if folded:
+        for grp in (wnp.in_layers, wnp.res_skip_layers):
+            out += [l.weight for l in grp]
+            out += [l.bias for l in grp]
+        out += [c1.weight, c1.bias]
+    else:
+        for grp in (wnp.in_layers, wnp.res_skip_layers):
+            out += [l.weight_g for l in grp]
+            out += [l.weight_v for l in grp]
+            out += [l.bias for l in grp]
+        out += [c1.weight_g, c1.weight_v, c1.bias]
+    return out
+
+
+def block_param_list(actnorm, invconv, coupling, prosody=False):
     """Tensors of one (ActNorm, InvConvNear, CouplingBlock) triple in decoder_forward order, and whether
-    the WaveNet's weight norm has been folded (store_inverse)."""
+    the WaveNet's weight norm has been folded (store_inverse).  prosody: the wn_energy / wn_pitch tensors follow."""
     wn = coupling.wn
     folded = wn.in_layers[0].folded
     out = [actnorm.logs.view(-1), actnorm.bias.view(-1), invconv.weight]
@@ -78,4 +95,6 @@ def block_param_list(actnorm, invconv, coupling):
             out += [l.weight_v for l in grp]
             out += [l.bias for l in grp]
     out += [coupling.end.weight, coupling.end.bias]
+    if prosody:
+        out += _wnp_param_list(coupling.wn_energy, folded) + _wnp_param_list(coupling.wn_pitch, folded)
     return out, folded

@@ -24,6 +24,7 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 struct Dims {
     int B, Cin, T, n, C, Tq, H, K, L, NB, NS, dr;
     size_t nq;   // B * Tq
+    int n_wn, wn_id[3];   // WaveNets chained in every coupling block (attentions.py:155-160): 0 = wn, 1 = wn_energy, 2 = wn_pitch
 };
 
 static int make_dims(const gtk_decoder_desc* d, Dims* o) {
@@ -41,6 +42,14 @@ static int make_dims(const gtk_decoder_desc* d, Dims* o) {
     o->dr = d->dilation_rate;
     o->nq = (size_t)o->B * o->Tq;
     GTK_REQUIRE(o->C % o->NS == 0 && o->C % 2 == 0, "channels % n_split != 0 (modules.py:637)");
+    o->n_wn = 1; o->wn_id[0] = 0; o->wn_id[1] = o->wn_id[2] = -1;
+    if (d->energy || d->pitch) {
+        GTK_REQUIRE(d->precision == 1, "pitch / energy conditioned blocks run on the bf16 path (precision 1); the fp32 path composes them from the module-level ops");
+        GTK_REQUIRE((2 * o->H * o->L) % (16 * o->n) == 0, "2 * hidden * n_layers / n_sqz must be a multiple of 16");
+        GTK_REQUIRE(o->n <= 4, "n_sqz <= 4 with pitch / energy tracks");
+        if (d->energy) o->wn_id[o->n_wn++] = 1;
+        if (d->pitch) o->wn_id[o->n_wn++] = 2;
+    }
     return GTK_OK;
 }
 

@@ -9,17 +9,41 @@ typedef __nv_bfloat16 bf16;
 
 static inline int pad64(int n) { return (n + 63) / 64 * 64; }
 
-struct TcPack {            // bf16 element offsets inside one block's packed-weight set
-    size_t start, in[GTK_MAX_LAYERS], rs[GTK_MAX_LAYERS], end;          // forward operands
-    size_t t_start, t_in[GTK_MAX_LAYERS], t_rs[GTK_MAX_LAYERS], t_end;  // data-gradient operands
+constexpr int TC_MAX_WN = 3;                       // wn, wn_energy, wn_pitch
+static inline int LI(int w, int i) { return w * GTK_MAX_LAYERS + i; }      // (chain slot of the WaveNet, layer)
+struct TcPack {            // bf16 element offsets inside one block's packed-weight set; per-layer entries indexed LI(w, i)
+    size_t start, in[TC_MAX_WN * GTK_MAX_LAYERS], rs[TC_MAX_WN * GTK_MAX_LAYERS], end;          // forward operands
+    size_t t_start, t_in[TC_MAX_WN * GTK_MAX_LAYERS], t_rs[TC_MAX_WN * GTK_MAX_LAYERS], t_end;  // data-gradient operands
     size_t total;
 };
 struct TcAct {             // byte offsets inside one block's activation set
-    size_t xmix, a0, h[GTK_MAX_LAYERS], ts[GTK_MAX_LAYERS], acts[GTK_MAX_LAYERS], skip_bf, logs, total;
+    size_t xmix, a0, h[TC_MAX_WN * GTK_MAX_LAYERS], ts[TC_MAX_WN * GTK_MAX_LAYERS], acts[TC_MAX_WN * GTK_MAX_LAYERS],
+        skip_bf[TC_MAX_WN], logs, total;
 };
+// Parameters / gradient destinations of the WaveNet in chain slot w of a block
+struct WnW {
+    const float* const* in_g; const float* const* in_v; const float* const* in_b;
+    const float* const* rs_g; const float* const* rs_v; const float* const* rs_b;
+    const float* c1_g; const float* c1_v; const float* c1_b;
+};
+struct WnG {
+    float* const* in_g; float* const* in_v; float* const* in_b; float* const* rs_g; float* const* rs_v; float* const* rs_b;
+    float* c1_g; float* c1_v; float* c1_b;
+};
+static WnW wn_weights(const gtk_block_params& P, int id) {
+    if (id == 0) return WnW{P.in_g, P.in_v, P.in_b, P.rs_g, P.rs_v, P.rs_b, nullptr, nullptr, nullptr};
+    const gtk_wnp_params& Q = id == 1 ? P.wn_energy : P.wn_pitch;
+    return WnW{Q.in_g, Q.in_v, Q.in_b, Q.rs_g, Q.rs_v, Q.rs_b, Q.c1_g, Q.c1_v, Q.c1_b};
+}
+static WnG wn_grads(const gtk_block_grads& P, int id) {
+    if (id == 0) return WnG{P.in_g, P.in_v, P.in_b, P.rs_g, P.rs_v, P.rs_b, nullptr, nullptr, nullptr};
+    const gtk_wnp_grads& Q = id == 1 ? P.wn_energy : P.wn_pitch;
+    return WnG{Q.in_g, Q.in_v, Q.in_b, Q.rs_g, Q.rs_v, Q.rs_b, Q.c1_g, Q.c1_v, Q.c1_b};
+}
 struct TcLayout {          // byte offsets in the workspace
     size_t mask_sq, x_len, winv, icld, we, pack, X, act, hf[2], skipf, bwd, total;
     size_t hdr, off, row_b, row_fr;      // varlen packing plan (pack.cu): {0, n_rows}, off[B+1], row_b[P], row_fr[P]; mask_sq = mask_p[P]
+    size_t trk[TC_MAX_WN], dtrk[TC_MAX_WN];   // packed pitch / energy samples [P, n_sqz] of chain slots >= 1, and their gradients
     int G, P;                            // gap rows behind every utterance, packed row capacity (multiple of 128)
     size_t we_floats, x_bytes;
     int n_pack, n_act, n_x;
@@ -53,6 +77,7 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     L->off = take((size_t)(D.B + 1) * 4);
     L->row_b = take(nq * 4);
     L->row_fr = take(nq * 4);
+    for (int w = 1; w < D.n_wn; ++w) { L->trk[w] = take(nq * D.n * 4); L->dtrk[w] = train ? take(nq * D.n * 4) : 0; }
     L->winv = take((size_t)D.NB * 64 * 4);
     L->icld = take((size_t)D.NB * 4);
     L->we_floats = L32.weff_block;
@@ -62,12 +87,16 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     auto wtake = [&](size_t n) { size_t o = w; w = align_up(w + n, 512); return o; };
     TcPack& P = L->P_;
     P.start = wtake((size_t)H * pad64(Ch));
-    for (int i = 0; i < D.L; ++i) P.in[i] = wtake((size_t)K * 2 * H * H);
-    for (int i = 0; i < D.L; ++i) P.rs[i] = wtake((size_t)((i < D.L - 1) ? 2 * H : H) * H);
+    for (int w = 0; w < D.n_wn; ++w) {
+        for (int i = 0; i < D.L; ++i) P.in[LI(w, i)] = wtake((size_t)K * 2 * H * H);
+        for (int i = 0; i < D.L; ++i) P.rs[LI(w, i)] = wtake((size_t)((i < D.L - 1) ? 2 * H : H) * H);
+    }
     P.end = wtake((size_t)C * H);
     P.t_start = wtake((size_t)Ch * H);
-    for (int i = 0; i < D.L; ++i) P.t_in[i] = wtake((size_t)K * H * 2 * H);
-    for (int i = 0; i < D.L; ++i) P.t_rs[i] = wtake((size_t)H * pad64((i < D.L - 1) ? 2 * H : H));
+    for (int w = 0; w < D.n_wn; ++w) {
+        for (int i = 0; i < D.L; ++i) P.t_in[LI(w, i)] = wtake((size_t)K * H * 2 * H);
+        for (int i = 0; i < D.L; ++i) P.t_rs[LI(w, i)] = wtake((size_t)H * pad64((i < D.L - 1) ? 2 * H : H));
+    }
     P.t_end = wtake((size_t)H * pad64(C));
     P.total = w;
     L->n_pack = D.NB;            // all blocks are packed by one launch up front
@@ -82,10 +111,13 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     TcAct& A = L->A;
     A.xmix = atake((size_t)C * nq * 4);
     A.a0 = atake((size_t)pad64(Ch) * nq * 2);
-    for (int i = 0; i < D.L; ++i) A.h[i] = atake((size_t)H * nq * 2);
-    for (int i = 0; i < D.L; ++i) A.ts[i] = atake((size_t)2 * H * nqp * 2);     // tile-private layout: whole tiles
-    for (int i = 0; i < D.L; ++i) A.acts[i] = atake((size_t)H * nq * 2);
-    A.skip_bf = atake((size_t)H * nq * 2);
+    for (int w = 0; w < D.n_wn; ++w) {
+        // h[w][0] of a chained WaveNet IS the masked output of the one before it (skip_bf[w - 1])
+        for (int i = 0; i < D.L; ++i) A.h[LI(w, i)] = atake((size_t)H * nq * 2);
+        for (int i = 0; i < D.L; ++i) A.ts[LI(w, i)] = atake((size_t)2 * H * nqp * 2);     // tile-private layout: whole tiles
+        for (int i = 0; i < D.L; ++i) A.acts[LI(w, i)] = atake((size_t)H * nq * 2);
+        A.skip_bf[w] = atake((size_t)H * nq * 2);
+    }
     A.logs = atake((size_t)Ch * nq * 4);
     A.total = a;
     L->n_act = train ? D.NB : 1;
@@ -101,9 +133,9 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
         for (int par = 0; par < 2; ++par) {                          // launch at the end of the block reads them all
             const size_t o0 = off;
             const size_t o_dend = take((size_t)pad64(C) * nq * 2);
-            const size_t o_drs = take(L->b_lstride * D.L);
-            const size_t o_dxin = take(L->b_lstride * D.L);
-            const size_t o_dgate = take(L->b_lstride * D.L);        // per layer too: their column sums run once per block
+            const size_t o_drs = take(L->b_lstride * D.L * D.n_wn);         // layer i of chain slot w: index w * L + i
+            const size_t o_dxin = take(L->b_lstride * D.L * D.n_wn);
+            const size_t o_dgate = take(L->b_lstride * D.L * D.n_wn);       // per layer too: their column sums run once per block
             const size_t o_dh0 = take((size_t)H * nq * 2);
             if (par == 0) { L->b_dend = o_dend; L->b_drs = o_drs; L->b_dxin = o_dxin; L->b_dgate = o_dgate; L->b_dh0 = o_dh0; }
             else L->b_pstride = o0 - L->b_dend;
@@ -132,13 +164,17 @@ static int tc_pack_all(const Dims& D, const TcLayout& L, const gtk_block_params*
     for (int blk = 0; blk < D.NB; ++blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
-        if (J.n + 2 + 2 * D.L > tc::FOLD_PACK_MAX_JOBS) { GTK_TRY(tc::fold_pack(J, st)); J.n = 0; }
+        if (J.n + 2 + 2 * D.L * D.n_wn > tc::FOLD_PACK_MAX_JOBS) { GTK_TRY(tc::fold_pack(J, st)); J.n = 0; }
         pk = pk_base + (size_t)blk * Q.total;
         add(P.start_g, P.start_v, Q.start, Q.t_start, H, Ch, 1, pad64(Ch), H);
-        for (int i = 0; i < D.L; ++i) {
-            const int RS = (i < D.L - 1) ? 2 * H : H;
-            add(P.in_g[i], P.in_v[i], Q.in[i], Q.t_in[i], 2 * H, H, K, H, 2 * H);
-            add(P.rs_g[i], P.rs_v[i], Q.rs[i], Q.t_rs[i], RS, H, 1, H, pad64(RS));
+        for (int w = 0; w < D.n_wn; ++w) {
+            const WnW W = wn_weights(P, D.wn_id[w]);
+            for (int i = 0; i < D.L; ++i) {
+                const int RS = (i < D.L - 1) ? 2 * H : H;
+                GTK_REQUIRE(W.in_v[i] && W.in_b[i] && W.rs_v[i] && W.rs_b[i] && (w == 0 || (W.c1_v && W.c1_b)), "null WaveNet parameter");
+                add(W.in_g[i], W.in_v[i], Q.in[LI(w, i)], Q.t_in[LI(w, i)], 2 * H, H, K, H, 2 * H);
+                add(W.rs_g[i], W.rs_v[i], Q.rs[LI(w, i)], Q.t_rs[LI(w, i)], RS, H, 1, H, pad64(RS));
+            }
         }
         add(nullptr, P.end_w, Q.end, Q.t_end, C, H, 1, H, pad64(C));
     }
@@ -200,24 +236,39 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
         p.out_bf16 = reinterpret_cast<bf16*>(act + A.h[0]); p.ld_bf16 = H;
         GTK_TRY(tc::conv_tc_launch(a0, pad64(Ch), pk + Q.start, p, tc::EPI_PLAIN, st));
     }
-    for (int i = 0; i < D.L; ++i) {
-        tc::WnLayerParams p;
-        memset(&p, 0, sizeof(p));
-        p.B = B; p.T = T; p.H = H; p.RS = (i < D.L - 1) ? 2 * H : H; p.taps = D.K; p.dil = ipow(D.dr, i);
-        p.first = (i == 0); p.last = (i == D.L - 1);
-        p.tile_layout = 1;
-        p.bias_in = P.in_b[i]; p.bias_rs = P.rs_b[i];
-        p.cond = P.cond ? P.cond + (size_t)i * 2 * H : nullptr; p.cond_bstride = (size_t)2 * H * D.L;
-        p.n_rows = pl.n_rows(); p.row_b = pl.row_b; p.row_fr = pl.row_fr;
-        p.mask = mask;
-        p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, i);
-        p.h_f32 = hf[i & 1]; p.h_out_f32 = hf[(i + 1) & 1];
-        p.h_out_bf16 = (i < D.L - 1) ? reinterpret_cast<bf16*>(act + A.h[i + 1]) : nullptr;
-        p.skip_f32 = skipf;
-        p.skip_out_bf16 = reinterpret_cast<bf16*>(act + A.skip_bf);
-        p.ts_save = save ? reinterpret_cast<bf16*>(act + A.ts[i]) : nullptr;
-        p.acts_save = save ? reinterpret_cast<bf16*>(act + A.acts[i]) : nullptr;
-        GTK_TRY(tc::wn_layer_launch(reinterpret_cast<const bf16*>(act + A.h[i]), pk + Q.in[i], pk + Q.rs[i], p, st));
+    // wn -> wn_energy -> wn_pitch (attentions.py:155-160): a chained WaveNet reads the masked output of the one before it
+    // (bf16 operand = skip_bf of that slot, fp32 master = the residual buffer its last layer left).
+    int cur = 0;                                          // which of the two fp32 residual buffers holds the layer input
+    for (int w = 0; w < D.n_wn; ++w) {
+        const WnW W = wn_weights(P, D.wn_id[w]);
+        for (int i = 0; i < D.L; ++i) {
+            tc::WnLayerParams p;
+            memset(&p, 0, sizeof(p));
+            p.B = B; p.T = T; p.H = H; p.RS = (i < D.L - 1) ? 2 * H : H; p.taps = D.K; p.dil = ipow(D.dr, i);
+            p.first = (i == 0); p.last = (i == D.L - 1);
+            p.tile_layout = 1;
+            p.bias_in = W.in_b[i]; p.bias_rs = W.rs_b[i];
+            if (w == 0) { p.cond = P.cond ? P.cond + (size_t)i * 2 * H : nullptr; p.cond_bstride = (size_t)2 * H * D.L; }
+            else {                                        // modules.WNP: cond_layer1 on the un-squeezed track, squeezed (modules.py:320-322)
+                p.trk = reinterpret_cast<const float*>(ws + L.trk[w]);
+                p.cw_g = W.c1_g; p.cw_v = W.c1_v; p.cb = W.c1_b;
+                p.n_sqz = D.n; p.cs_div = 2 * H * D.L / D.n; p.cs_base = i * 2 * H;
+            }
+            p.n_rows = pl.n_rows(); p.row_b = pl.row_b; p.row_fr = pl.row_fr;
+            p.mask = mask;
+            p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, w * D.L + i);
+            p.h_f32 = hf[cur]; p.h_out_f32 = hf[cur ^ 1];
+            p.h_out_bf16 = (i < D.L - 1) ? reinterpret_cast<bf16*>(act + A.h[LI(w, i + 1)]) : nullptr;
+            p.skip_f32 = skipf;
+            p.skip_out_bf16 = reinterpret_cast<bf16*>(act + A.skip_bf[w]);
+            if (p.last && w + 1 < D.n_wn) p.h_out_f32_last = hf[cur ^ 1];
+            p.ts_save = save ? reinterpret_cast<bf16*>(act + A.ts[LI(w, i)]) : nullptr;
+            p.acts_save = save ? reinterpret_cast<bf16*>(act + A.acts[LI(w, i)]) : nullptr;
+            const bf16* h_in = (i == 0 && w > 0) ? reinterpret_cast<const bf16*>(act + A.skip_bf[w - 1])
+                                                 : reinterpret_cast<const bf16*>(act + A.h[LI(w, i)]);
+            GTK_TRY(tc::wn_layer_launch(h_in, pk + Q.in[LI(w, i)], pk + Q.rs[LI(w, i)], p, st));
+            cur ^= 1;
+        }
     }
     {
         tc::ConvTcParams p;
@@ -228,7 +279,7 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
         p.aff_x = xc; p.aff_z = zout; p.aff_logdet = reverse ? nullptr : logdet;
         p.aff_logs_save = save ? reinterpret_cast<float*>(act + A.logs) : nullptr;
         p.aff_reverse = reverse; p.aff_sigmoid_scale = d->sigmoid_scale;
-        GTK_TRY(tc::conv_tc_launch(reinterpret_cast<const bf16*>(act + A.skip_bf), H, pk + Q.end, p, tc::EPI_AFFINE, st));
+        GTK_TRY(tc::conv_tc_launch(reinterpret_cast<const bf16*>(act + A.skip_bf[D.n_wn - 1]), H, pk + Q.end, p, tc::EPI_AFFINE, st));
     }
     return GTK_OK;
 }
@@ -249,10 +300,18 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     GTK_TRY(tc_pack_all(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), train, st));
     GTK_TRY(flow::pack_plan(mask, D.B, D.T, D.n, D.Tq, L.G, L.P, pl.hdr, pl.off, pl.row_b, pl.row_fr, pl.mask_p, pl.x_len, st));
     GTK_TRY(flow::squeeze_pack(x, pl.off, pl.row_b, pl.mask_p, reinterpret_cast<float*>(ws + L.X), D.Cin, D.T, D.n, L.P, st));
+    for (int w = 1; w < D.n_wn; ++w)
+        GTK_TRY(flow::pack_track(D.wn_id[w] == 1 ? d->energy : d->pitch, pl.off, pl.row_b, pl.mask_p,
+                                 reinterpret_cast<float*>(ws + L.trk[w]), D.T, D.n, L.P, st));
     GTK_TRY(tc_flow_consts(D, L, blocks, ws, pl.x_len, logdet, st));   // W^-1, log|det W|, the constant logdet terms
     if (train)     // guard rows behind the last tile in use of the conv inputs the weight gradient reads with a tap shift
-        GTK_TRY(tc::zero_guard_rows(reinterpret_cast<bf16*>(ws + L.act + L.A.h[0]), D.L > 1 ? L.A.h[1] - L.A.h[0] : 0, D.L,
-                                    L.A.total, D.NB, D.H, pl.n_rows(), 64, L.P, st));
+        for (int w = 0; w < D.n_wn; ++w) {
+            GTK_TRY(tc::zero_guard_rows(reinterpret_cast<bf16*>(ws + L.act + L.A.h[LI(w, 0)]), D.L > 1 ? L.A.h[1] - L.A.h[0] : 0, D.L,
+                                        L.A.total, D.NB, D.H, pl.n_rows(), 64, L.P, st));
+            if (w + 1 < D.n_wn)
+                GTK_TRY(tc::zero_guard_rows(reinterpret_cast<bf16*>(ws + L.act + L.A.skip_bf[w]), 0, 1, L.A.total, D.NB, D.H,
+                                            pl.n_rows(), 64, L.P, st));
+        }
     for (int blk = 0; blk < D.NB; ++blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
@@ -286,6 +345,9 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     GTK_TRY(tc_pack_all(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), 0, st));
     GTK_TRY(flow::pack_plan(mask, D.B, D.T, D.n, D.Tq, L.G, L.P, pl.hdr, pl.off, pl.row_b, pl.row_fr, pl.mask_p, pl.x_len, st));
     GTK_TRY(flow::squeeze_pack(z, pl.off, pl.row_b, pl.mask_p, xa, D.Cin, D.T, D.n, L.P, st));
+    for (int w = 1; w < D.n_wn; ++w)
+        GTK_TRY(flow::pack_track(D.wn_id[w] == 1 ? d->energy : d->pitch, pl.off, pl.row_b, pl.mask_p,
+                                 reinterpret_cast<float*>(ws + L.trk[w]), D.T, D.n, L.P, st));
     GTK_TRY(tc_flow_consts(D, L, blocks, ws, nullptr, nullptr, st));
     for (int blk = D.NB - 1; blk >= 0; --blk) {
         const gtk_block_params& P = blocks[blk];
@@ -331,6 +393,8 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     bool side_used[2] = {false, false};
 
     if (first) GTK_TRY(flow::squeeze_pack(dz, pl.off, pl.row_b, pl.mask_p, dZ, D.Cin, D.Tq * D.n, D.n, L.P, st));
+    if (first)
+        for (int w = 1; w < D.n_wn; ++w) GTK_CUDA(cudaMemsetAsync(ws + L.dtrk[w], 0, (size_t)L.P * D.n * sizeof(float), st));
     if (first) {   // gradients of the constant logdet terms of every block, one launch (they only need dlogdet and the saved W^-1)
         static thread_local flow::FlowConstGrads FG;
         for (int k0 = 0; k0 < D.NB; k0 += flow::FLOW_CONST_MAX_BLOCKS) {
@@ -351,14 +415,14 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         const float* xin_blk = reinterpret_cast<const float*>(ws + L.X + (size_t)blk * L.x_bytes);
         const float* xmix = reinterpret_cast<const float*>(act + A.xmix);
         const bf16* a0 = reinterpret_cast<const bf16*>(act + A.a0);
-        const bf16* skip_bf = reinterpret_cast<const bf16*>(act + A.skip_bf);
+        const bf16* skip_bf = reinterpret_cast<const bf16*>(act + A.skip_bf[D.n_wn - 1]);     // input of the `end` conv
         // the gradient temporaries the weight-gradient launch reads: one set per block parity
         const int par = blk & 1;
         unsigned char* wp = ws + (size_t)par * L.b_pstride;
         bf16* dend = reinterpret_cast<bf16*>(wp + L.b_dend);
-        auto drs_of = [&](int i) { return reinterpret_cast<bf16*>(wp + L.b_drs + (size_t)i * L.b_lstride); };
-        auto dxin_of = [&](int i) { return reinterpret_cast<bf16*>(wp + L.b_dxin + (size_t)i * L.b_lstride); };
-        bf16* dgate = reinterpret_cast<bf16*>(wp + L.b_dgate);
+        auto drs_of = [&](int w, int i) { return reinterpret_cast<bf16*>(wp + L.b_drs + (size_t)(w * D.L + i) * L.b_lstride); };
+        auto dxin_of = [&](int w, int i) { return reinterpret_cast<bf16*>(wp + L.b_dxin + (size_t)(w * D.L + i) * L.b_lstride); };
+        auto dgate_of = [&](int w, int i) { return reinterpret_cast<bf16*>(wp + L.b_dgate + (size_t)(w * D.L + i) * L.b_lstride); };
         bf16* dh0 = reinterpret_cast<bf16*>(wp + L.b_dh0);
         // the weight gradients of block blk + 2 (same parity) must have finished reading this set
         if (side && side_used[par]) GTK_CUDA(cudaStreamWaitEvent(st, side->done[par], 0));
@@ -403,23 +467,27 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
             p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = ldC / 64; p.N = H;
             p.mask = msq; p.mask_out = 1;
             p.n_rows = pl.n_rows();
-            p.out_bf16 = drs_of(0) + H; p.ld_bf16 = 2 * H;
+            p.out_bf16 = drs_of(D.n_wn - 1, 0) + H; p.ld_bf16 = 2 * H;           // ... of the LAST WaveNet of the chain
             p.rep_bf16 = D.L; p.rep_stride = L.b_lstride / 2;
             GTK_TRY(tc::conv_tc_launch(dend, ldC, pk + Q.t_end, p, tc::EPI_PLAIN, st));
         }
+        for (int w = D.n_wn - 1; w >= 0; --w) {
+        const WnW W = wn_weights(P, D.wn_id[w]);
+        const WnG Gw = wn_grads(G, D.wn_id[w]);
         for (int i = D.L - 1; i >= 0; --i) {
             const int RS = (i < D.L - 1) ? 2 * H : H;
             const int dil = ipow(D.dr, i);
-            const bf16* drs_i = (i < D.L - 1) ? drs_of(i) : drs_of(i) + H;     // [dh_{i+1} mask | dskip]  or  dskip
-            bf16* dxin = dxin_of(i);
-            const bf16* ts = reinterpret_cast<const bf16*>(act + A.ts[i]);
-            const bf16* acts = reinterpret_cast<const bf16*>(act + A.acts[i]);
-            const bf16* h_i = reinterpret_cast<const bf16*>(act + A.h[i]);
-            const bool want_dcond = P.cond && G.cond;
+            const bf16* drs_i = (i < D.L - 1) ? drs_of(w, i) : drs_of(w, i) + H;     // [dh_{i+1} mask | dskip]  or  dskip
+            bf16* dxin = dxin_of(w, i);
+            const bf16* ts = reinterpret_cast<const bf16*>(act + A.ts[LI(w, i)]);
+            const bf16* acts = reinterpret_cast<const bf16*>(act + A.acts[LI(w, i)]);
+            const bf16* h_i = (i == 0 && w > 0) ? reinterpret_cast<const bf16*>(act + A.skip_bf[w - 1])
+                                                : reinterpret_cast<const bf16*>(act + A.h[LI(w, i)]);
+            const bool want_dcond = w > 0 || (P.cond && G.cond);
             // the conditioning enters after the dropout: with both active the un-scaled gate gradient is kept as well
-            bf16* dpre = (want_dcond && d->p_dropout > 0.f) ? dgate + (size_t)i * (L.b_lstride / 2) : nullptr;
-            GTK_TRY(queue(P.rs_g[i], P.rs_v[i], G.rs_g[i], G.rs_v[i], G.rs_b[i], drs_i, 2 * H, RS, acts, H, H, RS, H, 1, 1));
-            GTK_TRY(queue(P.in_g[i], P.in_v[i], G.in_g[i], G.in_v[i], G.in_b[i], dxin, 2 * H, 2 * H, h_i, H, H, 2 * H, H, K, dil));
+            bf16* dpre = (want_dcond && d->p_dropout > 0.f) ? dgate_of(w, i) : nullptr;
+            GTK_TRY(queue(W.rs_g[i], W.rs_v[i], Gw.rs_g[i], Gw.rs_v[i], Gw.rs_b[i], drs_i, 2 * H, RS, acts, H, H, RS, H, 1, 1));
+            GTK_TRY(queue(W.in_g[i], W.in_v[i], Gw.in_g[i], Gw.in_v[i], Gw.in_b[i], dxin, 2 * H, 2 * H, h_i, H, H, 2 * H, H, K, dil));
             if (tc::wn_bwd_supported(H, K, dil)) {
                 // res_skip data gradient -> gate backward -> in_layer data gradient in ONE kernel (wn_bwd_tc.cu)
                 tc::WnBwdParams p;
@@ -427,11 +495,11 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 p.B = B; p.T = T; p.H = H; p.RS = RS; p.taps = K; p.dil = dil;
                 p.mask = msq; p.ts = ts;
                 p.n_rows = pl.n_rows(); p.row_fr = pl.row_fr; p.dpre = dpre;
-                p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, i);
+                p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, w * D.L + i);
                 p.resid_f32 = (i < D.L - 1) ? dhf[(i + 1) & 1] : nullptr;
                 p.out_f32 = dhf[i & 1];
-                GTK_TRY(tc::wn_bwd_layer_launch(drs_i, 2 * H, pk + Q.t_rs[i], pk + Q.t_in[i], dxin, i > 0 ? drs_of(i - 1) : dh0,
-                                                i > 0 ? 2 * H : H, p, st));
+                GTK_TRY(tc::wn_bwd_layer_launch(drs_i, 2 * H, pk + Q.t_rs[LI(w, i)], pk + Q.t_in[LI(w, i)], dxin,
+                                                i > 0 ? drs_of(w, i - 1) : dh0, i > 0 ? 2 * H : H, p, st));
             } else {
                 {   // res_skip 1x1: data gradient fused with the gate backward
                     tc::ConvTcParams p;
@@ -441,9 +509,9 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                     p.n_rows = pl.n_rows(); p.row_fr = pl.row_fr;
                     p.tile_layout = 1;
                     p.ts = ts; p.out_bf16 = dxin; p.ld_bf16 = 2 * H;
-                    p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, i);
+                    p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, w * D.L + i);
                     p.out2_bf16 = dpre;
-                    GTK_TRY(tc::conv_tc_launch(drs_i, 2 * H, pk + Q.t_rs[i], p, tc::EPI_GATE_BWD, st));
+                    GTK_TRY(tc::conv_tc_launch(drs_i, 2 * H, pk + Q.t_rs[LI(w, i)], p, tc::EPI_GATE_BWD, st));
                 }
                 {   // in_layer dilated conv
                     tc::ConvTcParams p;
@@ -454,11 +522,20 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                     p.tile_layout = 1;
                     if (i < D.L - 1) { p.resid_f32 = dhf[(i + 1) & 1]; p.ld_resid = H; p.mask_resid = 1; }
                     p.out_f32 = dhf[i & 1]; p.ld_f32 = H;
-                    if (i > 0) { p.out_bf16 = drs_of(i - 1); p.ld_bf16 = 2 * H; }
+                    if (i > 0) { p.out_bf16 = drs_of(w, i - 1); p.ld_bf16 = 2 * H; }
                     else       { p.out_bf16 = dh0; p.ld_bf16 = H; }
-                    GTK_TRY(tc::conv_tc_launch(dxin, 2 * H, pk + Q.t_in[i], p, tc::EPI_PLAIN, st));
+                    GTK_TRY(tc::conv_tc_launch(dxin, 2 * H, pk + Q.t_in[LI(w, i)], p, tc::EPI_PLAIN, st));
                 }
             }
+        }
+        if (w > 0) {
+            // modules.WNP: gradients of cond_layer1 and of the pitch / energy track from the layers' gate-input gradients,
+            // then d(input of this WaveNet) = d(masked output of the one before it) = the d(skip) operand of all ITS layers
+            GTK_TRY(tc::wnp_cond_bwd(d->p_dropout > 0.f ? dgate_of(w, 0) : dxin_of(w, 0), L.b_lstride / 2, D.L, 2 * H,
+                                     reinterpret_cast<const float*>(ws + L.trk[w]), D.n, 2 * H * D.L / D.n, W.c1_g, W.c1_v, Gw.c1_g,
+                                     Gw.c1_v, Gw.c1_b, reinterpret_cast<float*>(ws + L.dtrk[w]), pl.n_rows(), T, st));
+            GTK_TRY(tc::frames_fanout(dh0, H, drs_of(w - 1, 0) + H, 2 * H, L.b_lstride / 2, D.L, H, pl.n_rows(), T, st));
+        }
         }
         // start conv: h0 = (W x0 + b) * mask   (dh0 is already masked)
         GTK_TRY(queue(P.start_g, P.start_v, G.start_g, G.start_v, G.start_b, dh0, H, H, a0, ldCh, ldCh, H, Ch, 1, 1));
@@ -472,7 +549,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         }
         GTK_TRY(flush());
         if (P.cond && G.cond)   // d cond_layer(g)[b, layer, n] = sum over the utterance's rows of the gate-input gradient, all layers
-            GTK_TRY(tc::colsum_frames_seg(d->p_dropout > 0.f ? dgate : dxin_of(0), 2 * H, 2 * H, D.B, pl.off, G.cond,
+            GTK_TRY(tc::colsum_frames_seg(d->p_dropout > 0.f ? dgate_of(0, 0) : dxin_of(0, 0), 2 * H, 2 * H, D.B, pl.off, G.cond,
                                           (size_t)2 * H * D.L, wst, D.L, L.b_lstride / 2, (size_t)2 * H));
         if (side) { GTK_CUDA(cudaEventRecord(side->done[par], side->s)); side_used[par] = true; }
         // ActNorm + InvConvNear (fp32)
@@ -480,6 +557,11 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                               C, T, st, pl.n_rows()));
     }
     if (last) GTK_TRY(flow::unsqueeze_unpack(dZ, pl.off, dx, D.B, D.Cin, D.T, D.n, L.G, L.P, st));
+    if (last)
+        for (int w = 1; w < D.n_wn; ++w) {
+            float* dtrack = D.wn_id[w] == 1 ? d->d_energy : d->d_pitch;
+            if (dtrack) GTK_TRY(flow::unpack_track(reinterpret_cast<const float*>(ws + L.dtrk[w]), pl.off, dtrack, D.B, D.T, D.n, L.G, st));
+        }
     for (int par = 0; par < 2; ++par)      // join: every gradient of this call is complete in the caller's stream order
         if (side && side_used[par]) GTK_CUDA(cudaStreamWaitEvent(st, side->done[par], 0));
     return GTK_OK;

@@ -80,10 +80,11 @@ struct WnLayerParams {
     const int* row_fr;
     // time-varying rank-1 conditioner of WNP (modules.py:320-322, 353-362): pre += cw[n] * trk[row * n_sqz + phase(n)] + cb[n]
     const float* trk;              // [T, n_sqz] packed pitch / energy samples of each row, or null
-    const float* cw;               // [2H] cond_layer1 effective weight of this layer's channels
-    const float* cb;               // [2H] cond_layer1 bias of this layer's channels
-    int n_sqz, cs_div;             // phase of channel n: (cs_base + n) / cs_div  (cs_div = 2HL / n_sqz)
-    int cs_base;                   // layer * 2H
+    const float* cw_g;             // cond_layer1.weight_g [C1] (null: weight norm removed), C1 = 2HL / n_sqz
+    const float* cw_v;             // cond_layer1.weight_v (or .weight) [C1]: effective weight g v / |v|
+    const float* cb;               // cond_layer1.bias [C1]
+    int n_sqz, cs_div;             // squeezed channel cs_base + n reads sample (cs_base + n) / cs_div of the row's n_sqz
+    int cs_base;                   // samples through conv channel (cs_base + n) % cs_div;  cs_div = C1, cs_base = layer * 2H
     float* h_out_f32_last;         // last layer: masked WN output also as fp32 tile-private master (input of a chained WN)
     int dbg_noshift;               // instrumented builds: 1 = every tap reads the un-shifted tile (timing experiments only)
     const float* mask;             // [B, T]
@@ -158,6 +159,11 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
 // n_buf > 1: the same reduction over n_buf buffers buf_stride ELEMENTS apart, outputs out_bstride floats apart
 int colsum_frames_seg(const __nv_bfloat16* in, int ld, int n_cols, int groups, const int* seg, float* out, size_t out_gstride,
                       cudaStream_t st, int n_buf = 1, size_t buf_stride = 0, size_t out_bstride = 0);
+// WNP conditioner backward (wgrad_tc.cu): dpre = L bf16 frame buffers [T, 2H] `lstride` elements apart
+int wnp_cond_bwd(const __nv_bfloat16* dpre, size_t lstride, int L, int H2, const float* trk, int n_sqz, int C1, const float* c1_g,
+                 const float* c1_v, float* d_g, float* d_v, float* d_b, float* dtrk, const int* n_rows, int T, cudaStream_t st);
+int frames_fanout(const __nv_bfloat16* src, int ld_src, __nv_bfloat16* dst, int ld_dst, size_t dst_stride, int n_dst, int cols,
+                  const int* n_rows, int T, cudaStream_t st);
 int zero_guard_rows(__nv_bfloat16* base, size_t stride_bytes, int n_buf, size_t stride2_bytes, int n_buf2, int ld,
                     const int* n_rows, int n_guard, int T, cudaStream_t st);
 int colsum_frames(const __nv_bfloat16* in, int ld, int n_cols, int groups, long long rows_per_group, float* out, size_t out_gstride,

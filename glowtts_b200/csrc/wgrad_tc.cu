@@ -344,5 +344,134 @@ int zero_guard_rows(__nv_bfloat16* base, size_t stride_bytes, int n_buf, size_t 
     return check_launch("zero_guard_rows");
 }
 
+// ---------------------------------------------------------------------------------- WNP conditioner gradients
+// Backward of the time-varying conditioner of modules.WNP (modules.py:320-336, 353-362) from the gate-input gradients
+// dpre [rows, 2H] (bf16 frames) of its L layers (buffers `lstride` elements apart):
+//   cond[row, layer, n] = w[c] trk[row, s] + b[c],   cch = layer 2H + n,  s = cch / C1,  c = cch % C1,   w = g v / |v|
+//   d b[c] += sum_rows dpre ;  d w[c] += sum_rows dpre trk[row, s]  (-> d weight_g = d w sign(v), d weight_v = 0; or d weight
+//   when the norm was removed) ;  d trk[row, s] += sum_{layer, n} dpre w[c]   (accumulated over blocks, plain +=: one
+//   thread owns a row's sample).  One CTA = 32 rows, a warp = 4 of them; a lane owns column vectors of 8.
+constexpr int WC_NT = 256, WC_ROWS = 32;
+__global__ void __launch_bounds__(WC_NT) wnp_cond_bwd_kernel(const __nv_bfloat16* __restrict__ dpre, size_t lstride, int L, int H2,
+                                                             const float* __restrict__ trk, int n_sqz, int C1,
+                                                             const float* __restrict__ c1_g, const float* __restrict__ c1_v,
+                                                             float* __restrict__ d_g, float* __restrict__ d_v, float* __restrict__ d_b,
+                                                             const int* __restrict__ n_rows) {
+    __shared__ float red_b[WC_NT / 32][512], red_w[WC_NT / 32][512];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row0 = blockIdx.x * WC_ROWS;
+    if (row0 >= *n_rows) return;
+    const int nvec = H2 / 8;                               // 16-byte column vectors per row (<= 64)
+    for (int l = 0; l < L; ++l) {
+        const __nv_bfloat16* src = dpre + (size_t)l * lstride;
+        for (int v0 = 0; v0 < nvec; v0 += 32) {            // column vectors lane + v0
+            const int vec = v0 + lane;
+            if (vec >= nvec) continue;
+            const int n0 = vec * 8;
+            const int s = (l * H2 + n0) / C1;              // 8 consecutive squeezed channels share s (C1 % 16 == 0)
+            float ab[8], aw[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) ab[i] = aw[i] = 0.f;
+#pragma unroll
+            for (int q = 0; q < WC_ROWS / 8; ++q) {
+                const int row = row0 + warp + 8 * q;
+                if (row >= *n_rows) continue;
+                const uint4 qv = *reinterpret_cast<const uint4*>(src + (size_t)row * H2 + n0);
+                const uint32_t u[4] = {qv.x, qv.y, qv.z, qv.w};
+                const float tv = trk[(size_t)row * n_sqz + s];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&u[i]);
+                    const float a = __low2float(h), bq = __high2float(h);
+                    ab[2 * i] += a; ab[2 * i + 1] += bq;
+                    aw[2 * i] = fmaf(a, tv, aw[2 * i]); aw[2 * i + 1] = fmaf(bq, tv, aw[2 * i + 1]);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { red_b[warp][n0 + i] = ab[i]; red_w[warp][n0 + i] = aw[i]; }
+        }
+        __syncthreads();
+        for (int n = threadIdx.x; n < H2; n += WC_NT) {
+            float sb = 0.f, sw = 0.f;
+#pragma unroll
+            for (int w8 = 0; w8 < WC_NT / 32; ++w8) { sb += red_b[w8][n]; sw += red_w[w8][n]; }
+            const int cch = l * H2 + n, s = cch / C1, c = cch - s * C1;
+            if (sb != 0.f) atomicAdd(d_b + c, sb);
+            if (sw != 0.f) {
+                if (c1_g) atomicAdd(d_g + c, sw * (c1_v[c] < 0.f ? -1.f : 1.f));
+                else atomicAdd(d_v + c, sw);
+            }
+        }
+        __syncthreads();
+    }
+}
+// d trk[row, s] += sum_{layer, n in phase s} dpre[row, n] w[c]: one warp per row, lanes stride the 2H L columns.
+__global__ void __launch_bounds__(256) wnp_row_bwd_kernel(const __nv_bfloat16* __restrict__ dpre, size_t lstride, int L, int H2,
+                                                          int n_sqz, int C1, const float* __restrict__ c1_g,
+                                                          const float* __restrict__ c1_v, float* __restrict__ dtrk,
+                                                          const int* __restrict__ n_rows) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= *n_rows) return;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const int nvec = H2 / 8;
+    for (int l = 0; l < L; ++l) {
+        const __nv_bfloat16* src = dpre + (size_t)l * lstride + (size_t)row * H2;
+        for (int vec = lane; vec < nvec; vec += 32) {
+            const int n0 = vec * 8, cch = l * H2 + n0, s = cch / C1, c0 = cch - s * C1;
+            const uint4 qv = *reinterpret_cast<const uint4*>(src + n0);
+            const uint32_t u[4] = {qv.x, qv.y, qv.z, qv.w};
+            float part = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&u[i]);
+                const float v0 = c1_v[c0 + 2 * i], v1 = c1_v[c0 + 2 * i + 1];
+                const float w0 = c1_g ? c1_g[c0 + 2 * i] * (v0 < 0.f ? -1.f : 1.f) : v0;
+                const float w1 = c1_g ? c1_g[c0 + 2 * i + 1] * (v1 < 0.f ? -1.f : 1.f) : v1;
+                part = fmaf(__low2float(h), w0, part);
+                part = fmaf(__high2float(h), w1, part);
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[q] += (q == s) ? part : 0.f;
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc[q] = warp_sum(acc[q]);
+    if (lane < n_sqz) dtrk[(size_t)row * n_sqz + lane] += acc[lane == 0 ? 0 : lane == 1 ? 1 : lane == 2 ? 2 : 3];
+}
+int wnp_cond_bwd(const __nv_bfloat16* dpre, size_t lstride, int L, int H2, const float* trk, int n_sqz, int C1, const float* c1_g,
+                 const float* c1_v, float* d_g, float* d_v, float* d_b, float* dtrk, const int* n_rows, int T, cudaStream_t st) {
+    GTK_REQUIRE(dpre && trk && c1_v && d_b && dtrk && n_rows, "null");
+    GTK_REQUIRE(H2 % 8 == 0 && H2 <= 512 && n_sqz >= 1 && n_sqz <= 4 && C1 % 16 == 0, "shape");
+    GTK_REQUIRE(c1_g ? d_g != nullptr : d_v != nullptr, "conditioner weight gradient pointer missing");
+    if (T == 0) return GTK_OK;
+    wnp_cond_bwd_kernel<<<ceil_div(T, WC_ROWS), WC_NT, 0, st>>>(dpre, lstride, L, H2, trk, n_sqz, C1, c1_g, c1_v, d_g, d_v, d_b, n_rows);
+    int rc = check_launch("wnp_cond_bwd");
+    if (rc) return rc;
+    wnp_row_bwd_kernel<<<ceil_div(T, 8), 256, 0, st>>>(dpre, lstride, L, H2, n_sqz, C1, c1_g, c1_v, dtrk, n_rows);
+    return check_launch("wnp_row_bwd");
+}
+
+// dst_k[row, c] = src[row, c] for k < n_dst destinations `dst_stride` elements apart (bf16 frames, 8 columns per thread):
+// the data gradient of a chained WaveNet's input is the d(skip) operand of every layer of the WaveNet before it.
+__global__ void __launch_bounds__(256) frames_fanout_kernel(const __nv_bfloat16* __restrict__ src, int ld_src, __nv_bfloat16* dst,
+                                                            int ld_dst, size_t dst_stride, int n_dst, int cols,
+                                                            const int* __restrict__ n_rows, int T) {
+    const int nv = cols / 8;
+    const long long lim = n_rows ? (long long)min(T, (*n_rows + 127) & ~127) : (long long)T;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < lim * nv; i += (long long)gridDim.x * blockDim.x) {
+        const long long row = i / nv;
+        const int v = (int)(i - row * nv);
+        const uint4 q = *reinterpret_cast<const uint4*>(src + (size_t)row * ld_src + v * 8);
+        for (int k = 0; k < n_dst; ++k) *reinterpret_cast<uint4*>(dst + (size_t)k * dst_stride + (size_t)row * ld_dst + v * 8) = q;
+    }
+}
+int frames_fanout(const __nv_bfloat16* src, int ld_src, __nv_bfloat16* dst, int ld_dst, size_t dst_stride, int n_dst, int cols,
+                  const int* n_rows, int T, cudaStream_t st) {
+    GTK_REQUIRE(src && dst && cols % 8 == 0 && ld_src % 8 == 0 && ld_dst % 8 == 0, "bad args");
+    if (T == 0 || n_dst == 0) return GTK_OK;
+    frames_fanout_kernel<<<min(1024, ceil_div(T * (cols / 8), 256)), 256, 0, st>>>(src, ld_src, dst, ld_dst, dst_stride, n_dst, cols, n_rows, T);
+    return check_launch("frames_fanout");
+}
+
 }  // namespace tc
 }  // namespace gtk

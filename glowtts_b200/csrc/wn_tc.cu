@@ -83,8 +83,15 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     {
         for (int i = threadIdx.x; i < H2; i += EPI_NT) {
             ctl->bias_in[i] = p.bias_in[i];
-            ctl->cw[i] = p.trk ? p.cw[i] : 0.f;
-            ctl->cb[i] = p.trk ? p.cb[i] : 0.f;
+            float cwv = 0.f, cbv = 0.f;
+            if (p.trk) {                                 // WNP conditioner of channel i (modules.py:320-322, 353-362)
+                const int c = (p.cs_base + i) % p.cs_div;
+                const float v = p.cw_v[c];
+                cwv = p.cw_g ? p.cw_g[c] * (v < 0.f ? -1.f : 1.f) : v;      // weight norm of a 1-element row: g v / |v|
+                cbv = p.cb[c];
+            }
+            ctl->cw[i] = cwv;
+            ctl->cb[i] = cbv;
         }
         for (int i = threadIdx.x; i < RS; i += EPI_NT) ctl->bias_rs[i] = p.bias_rs[i];
     }
@@ -363,6 +370,8 @@ int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, con
     GTK_REQUIRE(p.taps >= 1 && (p.taps & 1) && p.dil >= 1, "bad conv shape");
     GTK_REQUIRE(p.last ? (p.RS == p.H && p.skip_out_bf16) : (p.RS == 2 * p.H && p.h_f32 && p.h_out_f32 && p.h_out_bf16), "layer outputs");
     GTK_REQUIRE(p.first || p.skip_f32, "skip accumulator");
+    GTK_REQUIRE(!p.trk || (p.cw_v && p.cb && p.n_sqz >= 1 && p.cs_div >= 16 && p.cs_div % 16 == 0),
+                "time-varying conditioner arguments (2 H L / n_sqz must be a multiple of 16)");
     GTK_REQUIRE(p.last || p.skip_f32, "skip accumulator");
     if (p.B == 0 || p.T == 0) return GTK_OK;
     const int H = p.H;

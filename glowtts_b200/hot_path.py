@@ -34,15 +34,30 @@ def sequence_mask(length: torch.Tensor, max_length: int) -> torch.Tensor:
     return torch.arange(max_length, device=length.device)[None, :] < length[:, None]
 
 
-def train_hot_path(decoder, y, y_lengths, x_m, x_logs, x_lengths, g=None, return_attn=False) -> HotPathOut:
+def normalize_track(track: torch.Tensor, T_y: int) -> torch.Tensor:
+    """models.py:1057-1073: a raw pitch / energy track [B,1,T] (0 = unvoiced / silence) -> log(track), zeros kept zero,
+    cut to T_y frames."""
+    t = track.reshape(track.shape[0], track.shape[-1])[:, :T_y]
+    zero = t == 0.0
+    out = torch.log(torch.clamp(t, min=torch.finfo(t.dtype).tiny))
+    return out.masked_fill(zero, 0.0).unsqueeze(1)
+
+
+def train_hot_path(decoder, y, y_lengths, x_m, x_logs, x_lengths, g=None, return_attn=False, pitch=None,
+                   energy=None) -> HotPathOut:
     """y [B,80,T_y] mel, y_lengths [B] (multiples of n_sqz, models.py:1052-1053), x_m / x_logs [B,80,T_x]
-    (x_logs None = mean_only), x_lengths [B]."""
+    (x_logs None = mean_only), x_lengths [B]; pitch / energy: raw per-frame tracks [B,1,T_y] of the live fork
+    (models.py:1057-1075), None when the model is trained without them."""
     n = decoder.n_sqz
     T_y = (y.shape[2] // n) * n
     y = y[:, :, :T_y]
     y_lengths = torch.div(y_lengths, n, rounding_mode="floor") * n                      # models.py:1052 (preprocess), on device
     z_mask = sequence_mask(y_lengths, T_y).to(y.dtype).unsqueeze(1)                     # models.py:1054
-    z, logdet = decoder(y, z_mask, g=g)
+    if pitch is not None or energy is not None:
+        z, logdet = decoder(y, z_mask, g=g, pitch=None if pitch is None else normalize_track(pitch, T_y),
+                            energy=None if energy is None else normalize_track(energy, T_y))
+    else:
+        z, logdet = decoder(y, z_mask, g=g)
     with torch.no_grad():
         lp = ops.logp(x_m.detach(), None if x_logs is None else x_logs.detach(), z.detach())
         t_xs = x_lengths.to(torch.int32)
@@ -122,9 +137,10 @@ class GraphedTrainStep:
         self.launches = _lib.launch_count() - n0           # library kernels per replay
 
     def _eager(self, dry: bool = False) -> HotPathOut:
-        y, y_len, x_m, x_len = self.static
+        y, y_len, x_m, x_len, *tracks = self.static      # optionally followed by (pitch, energy) raw tracks [B,1,T_y]
+        pitch, energy = tracks if tracks else (None, None)
         self.optimizer.zero_grad(set_to_none=True)
-        out = train_hot_path(self.decoder, y, y_len, x_m, self.x_logs, x_len, self.g)
+        out = train_hot_path(self.decoder, y, y_len, x_m, self.x_logs, x_len, self.g, pitch=pitch, energy=energy)
         out.loss.backward()
         if not dry:
             self.optimizer.step()

@@ -41,13 +41,13 @@ class FlowSpecDecoder(nn.Module):
                 sigmoid_scale=sigmoid_scale, n_sqz=n_sqz))
 
     # ---------------------------------------------------------------- fused call plumbing
-    def _cfg(self, folded: bool):
+    def _cfg(self, folded: bool, prosody: bool = False):
         # nn.Dropout(p_dropout) on the WN in_layer outputs (modules.py:120,153) is active in training mode only.
         drop = self.training and self.p_dropout > 0
         return [self.in_channels, self.n_sqz, self.hidden_channels, self.kernel_size, self.dilation_rate,
                 self.n_layers, self.n_blocks, self.n_split, int(bool(self.sigmoid_scale)),
                 {"fp32": 0, "bf16": 1}[self.precision], int(folded),
-                int(round(self.p_dropout * 1e6)) if drop else 0, 0]
+                int(round(self.p_dropout * 1e6)) if drop else 0, 0, int(prosody)]
 
     _SEED_STEP = 0x9E3779B97F4A7C15 - (1 << 64)      # odd 64-bit increment (as a signed int64)
 
@@ -74,10 +74,10 @@ class FlowSpecDecoder(nn.Module):
             self._drop_state = st
         return int(st.item()) & 0xFFFFFFFFFFFFFFFF
 
-    def _params(self):
+    def _params(self, prosody: bool = False):
         out, folded = [], None
         for b in range(self.n_blocks):
-            p, f = attentions.block_param_list(self.flows[3 * b], self.flows[3 * b + 1], self.flows[3 * b + 2])
+            p, f = attentions.block_param_list(self.flows[3 * b], self.flows[3 * b + 1], self.flows[3 * b + 2], prosody)
             assert folded is None or folded == f
             folded = f
             out += p
@@ -95,30 +95,32 @@ class FlowSpecDecoder(nn.Module):
         return ops.cond_layers(g.reshape(g.shape[0], -1).to(torch.float32), ws, self.n_blocks, folded)
 
     def forward(self, x, x_mask, g=None, emo=None, pitch=None, energy=None, reverse=False):
-        if pitch is not None or energy is not None:
-            # live-fork configuration (three WaveNets per coupling block): flow by flow through the module-level ops
+        prosody = pitch is not None or energy is not None
+        if prosody and self.precision != "bf16":
+            # live-fork configuration (three WaveNets per coupling block) on the exact-parity fp32 path: flow by flow
+            # through the module-level ops; the bf16 path runs the chain inside the fused call (attentions.py:155-160)
             return self._forward_unfused(x, x_mask, g, reverse, pitch=pitch, energy=energy)
         for b in range(self.n_blocks):          # data-dependent init, if requested (init.py:17-23)
             if not self.flows[3 * b].initialized:
-                return self._forward_unfused(x, x_mask, g, reverse)
-        params, folded = self._params()
+                return self._forward_unfused(x, x_mask, g, reverse, pitch=pitch, energy=energy)
+        params, folded = self._params(prosody)
         mask2 = x_mask.reshape(x_mask.shape[0], x_mask.shape[-1]).to(torch.float32)
         cond = self._cond(g)
-        cfg = self._cfg(folded)
+        cfg = self._cfg(folded, prosody)
         seed = self._next_seed(x.device)
         if reverse:
             with torch.no_grad():
-                return ops.decoder_reverse(x, mask2, [p.detach() for p in params], cond, cfg, seed), None
+                return ops.decoder_reverse(x, mask2, [p.detach() for p in params], cond, cfg, seed, energy, pitch), None
         train = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params))
         if train and not folded and all(p.requires_grad for p in params):
-            flat, offsets = self._ensure_flat(params)
-            z, logdet, _ = ops.decoder_forward_flat(x, mask2, flat, offsets, cond, cfg, True, seed)
+            flat, offsets = self._ensure_flat(params, prosody)
+            z, logdet, _ = ops.decoder_forward_flat(x, mask2, flat, offsets, cond, cfg, True, seed, energy, pitch)
         else:
-            z, logdet, _ = ops.decoder_forward(x, mask2, params, cond, cfg, train, seed)
+            z, logdet, _ = ops.decoder_forward(x, mask2, params, cond, cfg, train, seed, energy, pitch)
         return z, logdet
 
     # ---------------------------------------------------------------- flat parameter storage (training)
-    def _ensure_flat(self, params):
+    def _ensure_flat(self, params, prosody: bool = False):
         """Keep every decoder parameter as a view into ONE fp32 buffer (like DDP/FSDP flat buffers): the fused call
         takes the buffer, autograd returns ONE gradient tensor, and `p.grad` of the named parameters become views of
         it (no per-parameter copies).  Rebuilt lazily if the module was moved (.to()/.cuda()) or reloaded."""
@@ -136,30 +138,33 @@ class FlowSpecDecoder(nn.Module):
                                    "from flat_parameters() (or move the module before creating it)")
             with torch.no_grad():
                 buf = torch.zeros(total, dtype=torch.float32, device=params[0].device)
-                owners = self._param_owners()
+                owners = self._param_owners(prosody)
                 for p, o, n in zip(params, offs, sizes):
                     buf[o:o + n].copy_(p.detach().reshape(-1))
                     owners[p.data_ptr()].data = buf[o:o + n].view(owners[p.data_ptr()].shape)
             flat = buf.requires_grad_(True)
             flat.register_post_accumulate_grad_hook(self._scatter_flat_grad)
             self._flat, self._flat_offs, self._flat_sizes = flat, offs, sizes
-            self._flat_params = [owners_p for owners_p in self._ordered_owners()]
+            self._flat_params = [owners_p for owners_p in self._ordered_owners(prosody)]
+            self._flat_prosody = prosody
         return self._flat, self._flat_offs
 
-    def flat_parameters(self):
+    def flat_parameters(self, prosody: bool = False):
         """Parameters for the optimizer with the fused decoder weights as ONE tensor: [flat buffer] + every parameter
-        that is not part of it (e.g. the WN cond_layers).  The named parameters stay views of the buffer, so
+        that is not part of it (e.g. the WN cond_layers; with prosody=False also the wn_energy / wn_pitch WaveNets, which
+        then take no part in the fused call -- pass prosody=True when training with pitch / energy tracks on the bf16
+        path).  The named parameters stay views of the buffer, so
         state_dict()/checkpoints are unchanged; an elementwise optimizer (Adam, AdamW, SGD) then runs one multi-tensor
         launch instead of ~40 and reads the gradient the backward kernels wrote in place (no scatter)."""
-        params, folded = self._params()
+        params, folded = self._params(prosody)
         if folded:
             raise RuntimeError("glowtts_b200: weight norm was removed (store_inverse/remove_weight_norm); nothing to train")
-        flat, _ = self._ensure_flat(params)
+        flat, _ = self._ensure_flat(params, prosody)
         self._keep_flat_grad = True
-        inside = {id(p) for p in self._ordered_owners()}
+        inside = {id(p) for p in self._ordered_owners(prosody)}
         return [flat] + [p for p in self.parameters() if id(p) not in inside]
 
-    def _ordered_owners(self):
+    def _ordered_owners(self, prosody: bool = False):
         """nn.Parameters in decoder_forward order (ActNorm logs/bias are [1,C,1] parameters passed as [C] views)."""
         out = []
         for b in range(self.n_blocks):
@@ -168,10 +173,15 @@ class FlowSpecDecoder(nn.Module):
             for grp in (cb.wn.in_layers, cb.wn.res_skip_layers):
                 out += [l.weight_g for l in grp] + [l.weight_v for l in grp] + [l.bias for l in grp]
             out += [cb.end.weight, cb.end.bias]
+            for wnp in ((cb.wn_energy, cb.wn_pitch) if prosody else ()):
+                for grp in (wnp.in_layers, wnp.res_skip_layers):
+                    out += [l.weight_g for l in grp] + [l.weight_v for l in grp] + [l.bias for l in grp]
+                c1 = wnp.cond_layer1
+                out += [c1.weight_g, c1.weight_v, c1.bias]
         return out
 
-    def _param_owners(self):
-        return {p.data_ptr(): p for p in self._ordered_owners()}
+    def _param_owners(self, prosody: bool = False):
+        return {p.data_ptr(): p for p in self._ordered_owners(prosody)}
 
     def _scatter_flat_grad(self, flat):
         if getattr(self, "_keep_flat_grad", False):

@@ -574,18 +574,45 @@ def _(duration, mask):
 
 # =============================================================================== whole decoder
 # cfg = [in_channels, n_sqz, hidden, kernel_size, dilation_rate, n_layers, n_blocks, n_split, sigmoid_scale,
-#        precision, wn_folded]
+#        precision, wn_folded, p_dropout (ppm), host seed, prosody]
 # params: per block, in this order (g entries absent when wn_folded):
 #   an_logs, an_bias, ic_weight, start_g, start_v, start_b, in_g*L, in_v*L, in_b*L, rs_g*L, rs_v*L, rs_b*L, end_w, end_b
+# and, when cfg[13] (prosody: the fork's wn_energy / wn_pitch WaveNets, attentions.py:114-117, 155-160) is set, after end_b:
+#   for wn_energy, then wn_pitch:  in_g*L, in_v*L, in_b*L, rs_g*L, rs_v*L, rs_b*L, cond_layer1 g, v, b
 CFG_LEN = 11
 
 
-def params_per_block(n_layers: int, wn_folded: bool) -> int:
-    return (7 + 4 * n_layers) if wn_folded else (8 + 6 * n_layers)
+def params_per_wnp(n_layers: int, wn_folded: bool) -> int:
+    return (4 * n_layers + 2) if wn_folded else (6 * n_layers + 3)
 
 
-def _desc(cfg: Sequence[int], B: int, T: int, seed: Optional[Tensor] = None) -> DecoderDesc:
+def params_per_block(n_layers: int, wn_folded: bool, prosody: bool = False) -> int:
+    base = (7 + 4 * n_layers) if wn_folded else (8 + 6 * n_layers)
+    return base + (2 * params_per_wnp(n_layers, wn_folded) if prosody else 0)
+
+
+def _prosody(cfg: Sequence[int]) -> bool:
+    return len(cfg) > 13 and bool(cfg[13])
+
+
+def _track(t: Optional[Tensor], name: str, B: int, T: int) -> Optional[Tensor]:
+    """A pitch / energy track as the library reads it: fp32 [B, T] (a [B,1,T'] track with T' >= T is cut, models.py:1059)."""
+    if t is None:
+        return None
+    t = t.reshape(t.shape[0], t.shape[-1])
+    if t.shape[0] != B or t.shape[1] < T:
+        raise RuntimeError(f"glowtts_b200: {name} must be [B, T] with B={B}, T>={T}; got {tuple(t.shape)}")
+    if t.shape[1] != T:
+        t = t[:, :T]
+    return _chk(t.contiguous(), name)
+
+
+def _desc(cfg: Sequence[int], B: int, T: int, seed: Optional[Tensor] = None, energy: Optional[Tensor] = None,
+          pitch: Optional[Tensor] = None, d_energy: Optional[Tensor] = None, d_pitch: Optional[Tensor] = None) -> DecoderDesc:
     d = DecoderDesc()
+    if (energy is not None or pitch is not None) and not _prosody(cfg):
+        raise RuntimeError("glowtts_b200: pitch / energy tracks need cfg[13] = 1 and the wn_energy / wn_pitch parameters")
+    d.energy, d.pitch, d.d_energy, d.d_pitch = _p(energy), _p(pitch), _p(d_energy), _p(d_pitch)
     d.B, d.T = B, T
     (d.in_channels, d.n_sqz, d.hidden, d.kernel_size, d.dilation_rate, d.n_layers, d.n_blocks, d.n_split,
      d.sigmoid_scale, d.precision) = [int(v) for v in cfg[:10]]
@@ -618,7 +645,7 @@ def dropout_scale(seed: int, block: int, layer: int, p: float, B: int, T: int, C
 def _blocks(cfg: Sequence[int], tensors: Sequence[Optional[Tensor]], cond: Optional[Tensor]):
     """Fill an array of gtk_block_params (or gtk_block_grads) from the flat tensor list."""
     L, NB, folded = int(cfg[5]), int(cfg[6]), bool(cfg[10])
-    per = params_per_block(L, folded)
+    per = params_per_block(L, folded, _prosody(cfg))
     if len(tensors) != per * NB:
         raise RuntimeError(f"glowtts_b200: expected {per * NB} decoder tensors, got {len(tensors)}")
     arr = (BlockParams * NB)()
@@ -634,6 +661,14 @@ def _blocks(cfg: Sequence[int], tensors: Sequence[Optional[Tensor]], cond: Optio
             for i in range(L):
                 fld[i] = None if (folded and name.endswith("_g")) else ptr(next(it))
         P.end_w, P.end_b = ptr(next(it)), ptr(next(it))
+        if _prosody(cfg):
+            for W in (P.wn_energy, P.wn_pitch):
+                for name in ("in_g", "in_v", "in_b", "rs_g", "rs_v", "rs_b"):
+                    fld = getattr(W, name)
+                    for i in range(L):
+                        fld[i] = None if (folded and name.endswith("_g")) else ptr(next(it))
+                W.c1_g = None if folded else ptr(next(it))
+                W.c1_v, W.c1_b = ptr(next(it)), ptr(next(it))
         P.cond = None if cond is None else cond[b].data_ptr()
     return arr
 
@@ -663,15 +698,17 @@ def _chk_list(ts: Sequence[Tensor], name: str) -> List[Tensor]:
 
 @torch.library.custom_op(f"{NS}::decoder_forward", mutates_args=(), device_types="cuda")
 def decoder_forward(x: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], cfg: List[int],
-                    train: bool, seed: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
-    """FlowSpecDecoder.forward(reverse=False) (models.py:765-785).  x [B,in,T], mask [B,T], cond [NB,B,2H*L] or None
-    -> (z [B,in,(T//n)*n], logdet [B], workspace kept for the backward)."""
+                    train: bool, seed: Optional[Tensor] = None, energy: Optional[Tensor] = None,
+                    pitch: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
+    """FlowSpecDecoder.forward(reverse=False) (models.py:765-785).  x [B,in,T], mask [B,T], cond [NB,B,2H*L] or None,
+    energy / pitch [B,T] or None (the fork's per-frame tracks, bf16 path) -> (z [B,in,(T//n)*n], logdet [B], workspace
+    kept for the backward)."""
     x = _chk(x, "x")
     B, Cin, T = x.shape
     mask = _chk(_fit_mask(mask, T), "mask")
     params = _chk_list(params, "params")
     cond = _opt(cond, "cond")
-    d = _desc(cfg, B, T, seed)
+    d = _desc(cfg, B, T, seed, _track(energy, "energy", B, T), _track(pitch, "pitch", B, T))
     lib = _lib.load()
     ws_bytes = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), int(train))
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
@@ -687,7 +724,7 @@ def decoder_forward(x: Tensor, mask: Tensor, params: List[Tensor], cond: Optiona
 
 
 @decoder_forward.register_fake
-def _(x, mask, params, cond, cfg, train, seed=None):
+def _(x, mask, params, cond, cfg, train, seed=None, energy=None, pitch=None):
     B, Cin, T = x.shape
     n = cfg[1]
     return x.new_empty((B, Cin, (T // n) * n)), x.new_empty((B,)), x.new_empty((0,), dtype=torch.uint8)
@@ -695,14 +732,14 @@ def _(x, mask, params, cond, cfg, train, seed=None):
 
 @torch.library.custom_op(f"{NS}::decoder_reverse", mutates_args=(), device_types="cuda")
 def decoder_reverse(z: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], cfg: List[int],
-                    seed: Optional[Tensor] = None) -> Tensor:
+                    seed: Optional[Tensor] = None, energy: Optional[Tensor] = None, pitch: Optional[Tensor] = None) -> Tensor:
     """FlowSpecDecoder.forward(reverse=True) (models.py:765-785)."""
     z = _chk(z, "z")
     B, Cin, T = z.shape
     mask = _chk(_fit_mask(mask, T), "mask")
     params = _chk_list(params, "params")
     cond = _opt(cond, "cond")
-    d = _desc(cfg, B, T, seed)
+    d = _desc(cfg, B, T, seed, _track(energy, "energy", B, T), _track(pitch, "pitch", B, T))
     lib = _lib.load()
     ws_bytes = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), 0)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=z.device)
@@ -714,7 +751,7 @@ def decoder_reverse(z: Tensor, mask: Tensor, params: List[Tensor], cond: Optiona
 
 
 @decoder_reverse.register_fake
-def _(z, mask, params, cond, cfg, seed=None):
+def _(z, mask, params, cond, cfg, seed=None, energy=None, pitch=None):
     B, Cin, T = z.shape
     n = cfg[1]
     return z.new_empty((B, Cin, (T // n) * n))
@@ -722,13 +759,17 @@ def _(z, mask, params, cond, cfg, seed=None):
 
 @torch.library.custom_op(f"{NS}::decoder_backward", mutates_args=(), device_types="cuda")
 def decoder_backward(dz: Tensor, dlogdet: Tensor, mask: Tensor, params: List[Tensor], cond: Optional[Tensor], ws: Tensor,
-                     cfg: List[int], T: int, seed: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
-    """Backward of decoder_forward(train=True) -> (dx [B,in,T], flat parameter grads (see grad_layout), dcond)."""
+                     cfg: List[int], T: int, seed: Optional[Tensor] = None, energy: Optional[Tensor] = None,
+                     pitch: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
+    """Backward of decoder_forward(train=True) -> (dx [B,in,T], flat parameter grads (see grad_layout), dcond,
+    d energy [B,T], d pitch [B,T]; empty tensors where the input was None)."""
     dz, dlogdet, mask = _chk(dz, "dz"), _chk(dlogdet, "dlogdet"), _chk(_fit_mask(mask, T), "mask")
     params = _chk_list(params, "params")
     cond = _opt(cond, "cond")
     B, Cin = dz.shape[0], dz.shape[1]
-    d = _desc(cfg, B, T, seed)
+    energy, pitch = _track(energy, "energy", B, T), _track(pitch, "pitch", B, T)
+    d_energy, d_pitch = _track_grads(dz, energy, pitch)
+    d = _desc(cfg, B, T, seed, energy, pitch, d_energy if energy is not None else None, d_pitch if pitch is not None else None)
     dx = torch.empty(B, Cin, T, dtype=dz.dtype, device=dz.device)
     # one flat zero-initialised gradient buffer, viewed per parameter (one memset instead of ~430)
     offs, sizes, tot = grad_layout(params)
@@ -739,13 +780,24 @@ def decoder_backward(dz: Tensor, dlogdet: Tensor, mask: Tensor, params: List[Ten
     gblocks = _blocks(cfg, grads, dcond if cond is not None else None)
     _lib.call("gtk_decoder_backward", ctypes.byref(d), blocks, gblocks, _p(mask), _p(dz), _p(dlogdet), _p(dx), _p(ws),
               ws.numel(), _stream())
-    return dx, flat, dcond
+    return dx, flat, dcond, d_energy, d_pitch
+
+
+def _track_grads(like: Tensor, energy: Optional[Tensor], pitch: Optional[Tensor]) -> Tuple[Tensor, Tensor]:
+    return (torch.empty_like(energy) if energy is not None else like.new_empty(0),
+            torch.empty_like(pitch) if pitch is not None else like.new_empty(0))
+
+
+def _track_fake(like, t, B, T):
+    return like.new_empty((B, T)) if t is not None else like.new_empty(0)
 
 
 @decoder_backward.register_fake
-def _(dz, dlogdet, mask, params, cond, ws, cfg, T, seed=None):
-    return (dz.new_empty((dz.shape[0], dz.shape[1], T)), dz.new_empty((grad_layout(params)[2],)),
-            torch.empty_like(cond) if cond is not None else dz.new_empty(0))
+def _(dz, dlogdet, mask, params, cond, ws, cfg, T, seed=None, energy=None, pitch=None):
+    B = dz.shape[0]
+    return (dz.new_empty((B, dz.shape[1], T)), dz.new_empty((grad_layout(params)[2],)),
+            torch.empty_like(cond) if cond is not None else dz.new_empty(0), _track_fake(dz, energy, B, T),
+            _track_fake(dz, pitch, B, T))
 
 
 _GRAD_SYNC = {"group": None, "segments": int(os.environ.get("GTK_GRAD_SYNC_SEGMENTS", "3"))}
@@ -764,14 +816,15 @@ def _flat_ptrs(flat: Tensor, offsets: Sequence[int]) -> List[int]:
 
 @torch.library.custom_op(f"{NS}::decoder_forward_flat", mutates_args=(), device_types="cuda")
 def decoder_forward_flat(x: Tensor, mask: Tensor, flat: Tensor, offsets: List[int], cond: Optional[Tensor], cfg: List[int],
-                         train: bool, seed: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
+                         train: bool, seed: Optional[Tensor] = None, energy: Optional[Tensor] = None,
+                         pitch: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
     """decoder_forward with the parameters given as one flat buffer + element offsets (same order as `params`)."""
     x = _chk(x, "x")
     B, Cin, T = x.shape
     mask = _chk(_fit_mask(mask, T), "mask")
     flat = _chk(flat, "flat")
     cond = _opt(cond, "cond")
-    d = _desc(cfg, B, T, seed)
+    d = _desc(cfg, B, T, seed, _track(energy, "energy", B, T), _track(pitch, "pitch", B, T))
     lib = _lib.load()
     ws_bytes = lib.gtk_decoder_workspace_bytes(ctypes.byref(d), int(train))
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
@@ -787,7 +840,7 @@ def decoder_forward_flat(x: Tensor, mask: Tensor, flat: Tensor, offsets: List[in
 
 
 @decoder_forward_flat.register_fake
-def _(x, mask, flat, offsets, cond, cfg, train, seed=None):
+def _(x, mask, flat, offsets, cond, cfg, train, seed=None, energy=None, pitch=None):
     B, Cin, T = x.shape
     n = cfg[1]
     return x.new_empty((B, Cin, (T // n) * n)), x.new_empty((B,)), x.new_empty((0,), dtype=torch.uint8)
@@ -795,13 +848,16 @@ def _(x, mask, flat, offsets, cond, cfg, train, seed=None):
 
 @torch.library.custom_op(f"{NS}::decoder_backward_flat", mutates_args=(), device_types="cuda")
 def decoder_backward_flat(dz: Tensor, dlogdet: Tensor, mask: Tensor, flat: Tensor, offsets: List[int], cond: Optional[Tensor],
-                          ws: Tensor, cfg: List[int], T: int, seed: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
-    """-> (dx, d flat (same layout as flat), dcond)."""
+                          ws: Tensor, cfg: List[int], T: int, seed: Optional[Tensor] = None, energy: Optional[Tensor] = None,
+                          pitch: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
+    """-> (dx, d flat (same layout as flat), dcond, d energy, d pitch)."""
     dz, dlogdet, mask = _chk(dz, "dz"), _chk(dlogdet, "dlogdet"), _chk(_fit_mask(mask, T), "mask")
     flat = _chk(flat, "flat")
     cond = _opt(cond, "cond")
     B, Cin = dz.shape[0], dz.shape[1]
-    d = _desc(cfg, B, T, seed)
+    energy, pitch = _track(energy, "energy", B, T), _track(pitch, "pitch", B, T)
+    d_energy, d_pitch = _track_grads(dz, energy, pitch)
+    d = _desc(cfg, B, T, seed, energy, pitch, d_energy if energy is not None else None, d_pitch if pitch is not None else None)
     dx = torch.empty(B, Cin, T, dtype=dz.dtype, device=dz.device)
     dflat = torch.zeros_like(flat)
     dcond = torch.zeros_like(cond) if cond is not None else dz.new_empty(0)
@@ -809,18 +865,21 @@ def decoder_backward_flat(dz: Tensor, dlogdet: Tensor, mask: Tensor, flat: Tenso
     gblocks = _blocks(cfg, _flat_ptrs(dflat, offsets), dcond if cond is not None else None)
     _lib.call("gtk_decoder_backward", ctypes.byref(d), blocks, gblocks, _p(mask), _p(dz), _p(dlogdet), _p(dx), _p(ws),
               ws.numel(), _stream())
-    return dx, dflat, dcond
+    return dx, dflat, dcond, d_energy, d_pitch
 
 
 @decoder_backward_flat.register_fake
-def _(dz, dlogdet, mask, flat, offsets, cond, ws, cfg, T, seed=None):
-    return (dz.new_empty((dz.shape[0], dz.shape[1], T)), torch.empty_like(flat),
-            torch.empty_like(cond) if cond is not None else dz.new_empty(0))
+def _(dz, dlogdet, mask, flat, offsets, cond, ws, cfg, T, seed=None, energy=None, pitch=None):
+    B = dz.shape[0]
+    return (dz.new_empty((B, dz.shape[1], T)), torch.empty_like(flat),
+            torch.empty_like(cond) if cond is not None else dz.new_empty(0), _track_fake(dz, energy, B, T),
+            _track_fake(dz, pitch, B, T))
 
 
 def decoder_backward_flat_overlapped(dz: Tensor, dlogdet: Tensor, mask: Tensor, flat: Tensor, offsets: List[int],
                                      cond: Optional[Tensor], ws: Tensor, cfg: List[int], T: int, seed: Optional[Tensor],
-                                     group, n_segments: int = 3) -> Tuple[Tensor, Tensor, Tensor]:
+                                     group, n_segments: int = 3, energy: Optional[Tensor] = None,
+                                     pitch: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
     """decoder_backward_flat for data-parallel training: the backward is issued as `n_segments` block ranges
     (gtk_decoder_backward_range) and the flat-gradient slice of each finished range is all-reduced (averaged, as DDP does:
     train_ms_emo_lang_pitch.py:166) asynchronously while the next range computes; only the last range's collective is
@@ -830,13 +889,15 @@ def decoder_backward_flat_overlapped(dz: Tensor, dlogdet: Tensor, mask: Tensor, 
     flat = _chk(flat, "flat")
     cond = _opt(cond, "cond")
     B, Cin = dz.shape[0], dz.shape[1]
-    d = _desc(cfg, B, T, seed)
+    energy, pitch = _track(energy, "energy", B, T), _track(pitch, "pitch", B, T)
+    d_energy, d_pitch = _track_grads(dz, energy, pitch)
+    d = _desc(cfg, B, T, seed, energy, pitch, d_energy if energy is not None else None, d_pitch if pitch is not None else None)
     dx = torch.empty(B, Cin, T, dtype=dz.dtype, device=dz.device)
     dflat = torch.zeros_like(flat)
     dcond = torch.zeros_like(cond) if cond is not None else dz.new_empty(0)
     blocks = _blocks(cfg, _flat_ptrs(flat, offsets), cond)
     gblocks = _blocks(cfg, _flat_ptrs(dflat, offsets), dcond if cond is not None else None)
-    nb, ppb = int(cfg[6]), params_per_block(int(cfg[5]), False)
+    nb, ppb = int(cfg[6]), params_per_block(int(cfg[5]), False, _prosody(cfg))
     sync = group is not None and _world(group) > 1         # group None: segmentation only (tests)
     world = dist.get_world_size(group) if sync else 1
     avg = sync and dist.get_backend(group) == "nccl"
@@ -857,20 +918,20 @@ def decoder_backward_flat_overlapped(dz: Tensor, dlogdet: Tensor, mask: Tensor, 
         w.wait()                  # stream-ordered for NCCL: the current stream waits, the host does not
     if sync and not avg:
         dflat.div_(world)
-    return dx, dflat, dcond
+    return dx, dflat, dcond, d_energy, d_pitch
 
 
 def _decf_setup(ctx, inputs, output):
-    x, mask, flat, offsets, cond, cfg, train, seed = inputs
+    x, mask, flat, offsets, cond, cfg, train, seed, energy, pitch = inputs
     ctx.set_materialize_grads(False)       # the activation workspace output has no gradient: do not zero-fill GBs for it
-    ctx.save_for_backward(mask, cond, output[2], flat, seed)
+    ctx.save_for_backward(mask, cond, output[2], flat, seed, energy, pitch)
     ctx.cfg, ctx.T, ctx.train, ctx.has_cond, ctx.offsets = list(cfg), x.shape[2], train, cond is not None, list(offsets)
 
 
 def _decf_bwd(ctx, dz, dlogdet, dws):
     if not ctx.train:
         raise RuntimeError("glowtts_b200: decoder_forward was run with train=False; no activations were kept")
-    mask, cond, ws, flat, seed = ctx.saved_tensors
+    mask, cond, ws, flat, seed, energy, pitch = ctx.saved_tensors
     B = mask.shape[0]
     if dz is None:
         Tz = (ctx.T // ctx.cfg[1]) * ctx.cfg[1]
@@ -881,14 +942,25 @@ def _decf_bwd(ctx, dz, dlogdet, dws):
     if group is not None and _world(group) > 1:
         # data-parallel training (train_ms_emo_lang_pitch.py:166 DDP): the flat gradient is all-reduced range by range,
         # overlapped with the rest of the backward
-        dx, dflat, dcond = decoder_backward_flat_overlapped(dz.contiguous(), dlogdet.contiguous(), mask, flat, ctx.offsets, cond,
-                                                            ws, ctx.cfg, ctx.T, seed, group, _GRAD_SYNC["segments"])
+        dx, dflat, dcond, de, dp = decoder_backward_flat_overlapped(dz.contiguous(), dlogdet.contiguous(), mask, flat, ctx.offsets,
+                                                                    cond, ws, ctx.cfg, ctx.T, seed, group,
+                                                                    _GRAD_SYNC["segments"], energy, pitch)
     else:
-        dx, dflat, dcond = decoder_backward_flat(dz.contiguous(), dlogdet.contiguous(), mask, flat, ctx.offsets, cond, ws,
-                                                 ctx.cfg, ctx.T, seed)
-    return dx, None, dflat, None, (dcond if ctx.has_cond else None), None, None, None
+        dx, dflat, dcond, de, dp = decoder_backward_flat(dz.contiguous(), dlogdet.contiguous(), mask, flat, ctx.offsets, cond, ws,
+                                                         ctx.cfg, ctx.T, seed, energy, pitch)
+    return (dx, None, dflat, None, (dcond if ctx.has_cond else None), None, None, None,
+            _track_like(de, energy), _track_like(dp, pitch))
 
 
+
+
+def _track_like(d: Tensor, t: Optional[Tensor]) -> Optional[Tensor]:
+    """Gradient of a track in the shape autograd saw ([B,T'] or [B,1,T'], possibly longer than the T the decoder used)."""
+    if t is None:
+        return None
+    out = d.new_zeros(t.shape)
+    out.reshape(t.shape[0], t.shape[-1])[:, :d.shape[1]].copy_(d)
+    return out
 
 
 def set_grad_sync(group, segments: Optional[int] = None) -> None:
@@ -901,23 +973,24 @@ def set_grad_sync(group, segments: Optional[int] = None) -> None:
 
 
 def _dec_setup(ctx, inputs, output):
-    x, mask, params, cond, cfg, train, seed = inputs
+    x, mask, params, cond, cfg, train, seed, energy, pitch = inputs
     ctx.set_materialize_grads(False)
-    ctx.save_for_backward(mask, cond, output[2], seed, *params)
+    ctx.save_for_backward(mask, cond, output[2], seed, energy, pitch, *params)
     ctx.cfg, ctx.T, ctx.train, ctx.has_cond = list(cfg), x.shape[2], train, cond is not None
 
 
 def _dec_bwd(ctx, dz, dlogdet, dws):
     if not ctx.train:
         raise RuntimeError("glowtts_b200: decoder_forward was run with train=False; no activations were kept")
-    mask, cond, ws, seed, *params = ctx.saved_tensors
+    mask, cond, ws, seed, energy, pitch, *params = ctx.saved_tensors
     B = mask.shape[0]
     if dz is None:
         Tz = (ctx.T // ctx.cfg[1]) * ctx.cfg[1]
         dz = torch.zeros(B, ctx.cfg[0], Tz, dtype=mask.dtype, device=mask.device)
     if dlogdet is None:
         dlogdet = torch.zeros(B, dtype=mask.dtype, device=mask.device)
-    dx, flat, dcond = decoder_backward(dz.contiguous(), dlogdet.contiguous(), mask, list(params), cond, ws, ctx.cfg, ctx.T, seed)
+    dx, flat, dcond, de, dp = decoder_backward(dz.contiguous(), dlogdet.contiguous(), mask, list(params), cond, ws, ctx.cfg,
+                                               ctx.T, seed, energy, pitch)
     if _GRAD_SYNC["group"] is not None:
         # data-parallel training (train_ms_emo_lang_pitch.py:166 DDP): ONE NCCL all-reduce over the flat
         # gradient buffer the backward kernels wrote, averaged over ranks as DDP does.
@@ -925,7 +998,7 @@ def _dec_bwd(ctx, dz, dlogdet, dws):
         sync_flat_grad(flat, _GRAD_SYNC["group"])
     offs, sizes, _ = grad_layout(params)
     grads = [flat[o:o + n].view(p.shape) for o, n, p in zip(offs, sizes, params)]
-    return dx, None, grads, (dcond if ctx.has_cond else None), None, None, None
+    return dx, None, grads, (dcond if ctx.has_cond else None), None, None, None, _track_like(de, energy), _track_like(dp, pitch)
 
 
 decoder_forward.register_autograd(_dec_bwd, setup_context=_dec_setup)

@@ -255,7 +255,32 @@ typedef struct gtk_decoder_desc {
     const unsigned long long* seed_dev;   /* if not NULL the per-call seed is read from this DEVICE address by the
                                            * kernels instead (`seed` is ignored): a captured CUDA graph then picks up a
                                            * fresh seed on every replay */
+    /* The fork's pitch / energy conditioned coupling blocks (attentions.py:155-160: wn -> wn_energy -> wn_pitch, modules.WNP
+     * modules.py:272-362), bf16 path.  energy / pitch: [B, T] tracks on the un-squeezed time axis, or NULL = that WaveNet is
+     * the identity (modules.py:323-324).  d_energy / d_pitch: [B, T] gradients of the tracks, WRITTEN by the backward, or NULL. */
+    const float* energy;
+    const float* pitch;
+    float* d_energy;
+    float* d_pitch;
 } gtk_decoder_desc;
+
+/* Parameters of one modules.WNP (wn_energy / wn_pitch of a coupling block); all NULL when unused. */
+typedef struct gtk_wnp_params {
+    const float* in_g[GTK_MAX_LAYERS];    /* ....in_layers.{i}.weight_g [2H] */
+    const float* in_v[GTK_MAX_LAYERS];    /* ....in_layers.{i}.weight_v [2H, H, K] */
+    const float* in_b[GTK_MAX_LAYERS];    /* ....in_layers.{i}.bias [2H] */
+    const float* rs_g[GTK_MAX_LAYERS];    /* ....res_skip_layers.{i}.weight_g [RS_i] */
+    const float* rs_v[GTK_MAX_LAYERS];    /* ....res_skip_layers.{i}.weight_v [RS_i, H, 1] */
+    const float* rs_b[GTK_MAX_LAYERS];    /* ....res_skip_layers.{i}.bias [RS_i] */
+    const float* c1_g;                    /* ....cond_layer1.weight_g [2HL/n_sqz] (NULL after remove_weight_norm) */
+    const float* c1_v;                    /* ....cond_layer1.weight_v (or .weight) [2HL/n_sqz, 1, 1] */
+    const float* c1_b;                    /* ....cond_layer1.bias [2HL/n_sqz] */
+} gtk_wnp_params;
+typedef struct gtk_wnp_grads {
+    float* in_g[GTK_MAX_LAYERS]; float* in_v[GTK_MAX_LAYERS]; float* in_b[GTK_MAX_LAYERS];
+    float* rs_g[GTK_MAX_LAYERS]; float* rs_v[GTK_MAX_LAYERS]; float* rs_b[GTK_MAX_LAYERS];
+    float* c1_g; float* c1_v; float* c1_b;
+} gtk_wnp_grads;
 
 /* Parameters of one (ActNorm, InvConvNear, CouplingBlock) triple; state_dict names in comments.
  * Weight-normed convs take (weight_g, weight_v); after remove_weight_norm pass weight as *_v and NULL as *_g. */
@@ -275,6 +300,8 @@ typedef struct gtk_block_params {
     const float* end_w;                   /* ....end.weight [C, H, 1] */
     const float* end_b;                   /* ....end.bias [C] */
     const float* cond;                    /* wn.cond_layer(g) output [B, 2H*L] or NULL (modules.py:148-149) */
+    gtk_wnp_params wn_energy;             /* flows.{3b+2}.wn_energy.* (used when gtk_decoder_desc.energy != NULL) */
+    gtk_wnp_params wn_pitch;              /* flows.{3b+2}.wn_pitch.*  (used when gtk_decoder_desc.pitch != NULL) */
 } gtk_block_params;
 
 /* Gradient destinations, same shapes as the parameters; ACCUMULATED into (zero them once per step). */
@@ -285,6 +312,8 @@ typedef struct gtk_block_grads {
     float* rs_g[GTK_MAX_LAYERS]; float* rs_v[GTK_MAX_LAYERS]; float* rs_b[GTK_MAX_LAYERS];
     float* end_w; float* end_b;
     float* cond;                          /* [B, 2H*L] or NULL */
+    gtk_wnp_grads wn_energy;
+    gtk_wnp_grads wn_pitch;
 } gtk_block_grads;
 
 /* train != 0: activations are kept in the workspace for gtk_decoder_backward. */

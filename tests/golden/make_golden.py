@@ -106,15 +106,22 @@ PROSODY_CASES = {
     "flow_tiny_pe": (dict(helpers.TINY_CFG, gin_channels=6), 25, 3, 14, 35, True, True, True),
     "flow_tiny_p": (helpers.TINY_CFG, 26, 2, 12, 36, False, True, False),
 }
+PROSODY_H64_CASES = {
+    # round 2: tensor-core-capable widths (hidden 64) so that the fused 3-WN chain of the bf16 path has reference fixtures
+    "flow_h64_pe": (dict(in_channels=16, hidden_channels=64, kernel_size=3, dilation_rate=2, n_blocks=2, n_layers=3,
+                         n_split=4, n_sqz=2, gin_channels=8), 45, 3, 280, 46, True, True, True),
+    "flow_h64_p": (dict(in_channels=16, hidden_channels=64, kernel_size=5, dilation_rate=1, n_blocks=2, n_layers=3,
+                        n_split=4, n_sqz=2, gin_channels=0), 47, 2, 300, 48, False, True, False),
+}
 
 
 prosody_inputs = helpers.prosody_inputs
 
 
-def gen_flow_prosody(ref):
+def gen_flow_prosody(ref, cases=None):
     """FlowSpecDecoder with pitch / energy tracks: every coupling block runs wn -> wn_energy -> wn_pitch
     (attentions.py:155-160, modules.WNP)."""
-    for name, (cfg, sd_seed, b, t, in_seed, use_g, use_p, use_e) in PROSODY_CASES.items():
+    for name, (cfg, sd_seed, b, t, in_seed, use_g, use_p, use_e) in (cases or PROSODY_CASES).items():
         dec = ref.models.FlowSpecDecoder(cfg["in_channels"], cfg["hidden_channels"], cfg["kernel_size"],
                                          cfg["dilation_rate"], cfg["n_blocks"], cfg["n_layers"], p_dropout=0.0,
                                          n_split=cfg["n_split"], n_sqz=cfg["n_sqz"], gin_channels=cfg["gin_channels"])
@@ -126,15 +133,26 @@ def gen_flow_prosody(ref):
         y = y.clone().requires_grad_(True)
         if pitch is not None:
             pitch = pitch.clone().requires_grad_(True)
+        if energy is not None and cases is not None:
+            energy = energy.clone().requires_grad_(True)
         z, logdet = dec(y, mask, g=g, pitch=pitch, energy=energy, reverse=False)
         loss = ref.commons.mle_loss(z, torch.zeros_like(z), torch.zeros_like(z), logdet, mask)
         loss.backward()
-        sel = {"grad:" + k: p.grad.detach().numpy() for k, p in dec.named_parameters() if p.grad is not None}
+        sel = {}
+        for k, p in dec.named_parameters():
+            if p.grad is None:
+                continue
+            a = p.grad.detach().numpy()
+            if cases is not None and a.size > 4096:
+                a = a.reshape(-1)[:: max(1, a.size // 2048)]    # strided sample keeps the file small
+            sel["grad:" + k] = a
         with torch.no_grad():
             y_rev, _ = dec(z.detach(), mask, g=g, pitch=pitch, energy=energy, reverse=True)
             dec.store_inverse()
             y_rev2, _ = dec(z.detach(), mask, g=g, pitch=pitch, energy=energy, reverse=True)
         extra = {} if pitch is None else {"dpitch": pitch.grad.numpy()}
+        if energy is not None and energy.grad is not None:
+            extra["denergy"] = energy.grad.numpy()
         np.savez_compressed(os.path.join(HERE, name + ".npz"),
                             sd_seed=sd_seed, b=b, t=t, in_seed=in_seed, use_g=use_g, use_pitch=use_p, use_energy=use_e,
                             z=z.detach().numpy(), logdet=logdet.detach().numpy(), loss=loss.item(),
@@ -292,7 +310,11 @@ if __name__ == "__main__":
     if "--prosody-only" in sys.argv:       # add the 3-WN fixtures without touching the older files
         gen_flow_prosody(ref)
         sys.exit(0)
+    if "--prosody-h64-only" in sys.argv:   # round 2: the hidden-64 3-WN fixtures
+        gen_flow_prosody(ref, PROSODY_H64_CASES)
+        sys.exit(0)
     gen_flow_prosody(ref)
+    gen_flow_prosody(ref, PROSODY_H64_CASES)
     gen_round2(ref)
     gen_mas()
     gen_modules(ref)

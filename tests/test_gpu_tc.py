@@ -364,8 +364,8 @@ def test_segmented_backward_equals_one_call_backward(precision, segments):
         gen = torch.Generator(device="cuda").manual_seed(3)
         dz = torch.randn(z.shape, device="cuda", generator=gen) * mask
         dld = torch.randn(logdet.shape, device="cuda", generator=gen)
-        dx0, df0, _ = ops.decoder_backward_flat(dz, dld, mask2, flat, offsets, None, ws, c, y.shape[2], None)
-        dx1, df1, _ = ops.decoder_backward_flat_overlapped(dz, dld, mask2, flat, offsets, None, ws, c, y.shape[2], None, None, segments)
+        dx0, df0, *_ = ops.decoder_backward_flat(dz, dld, mask2, flat, offsets, None, ws, c, y.shape[2], None)
+        dx1, df1, *_ = ops.decoder_backward_flat_overlapped(dz, dld, mask2, flat, offsets, None, ws, c, y.shape[2], None, None, segments)
     assert torch.allclose(dx0, dx1, rtol=1e-5, atol=1e-6)
     assert torch.allclose(df0, df1, rtol=1e-5, atol=1e-6)
     assert df0.abs().sum().item() > 0
