@@ -140,15 +140,21 @@ def build_decoder(device, precision, gin=0):
 class Runner:
     """Holds the resident model/optimizer and runs one step, device-resident or end to end."""
 
-    def __init__(self, device, world, precision, graph=False, gin=0):
+    def __init__(self, device, world, precision, graph=False, gin=0, prosody=False):
         from glowtts_b200 import ops
         self.device, self.world = device, world
         self.dec = build_decoder(device, precision, gin)
         # train_ms_emo_lang_pitch.py:126-130 AdamW; the decoder hands its weights over as one flat tensor
-        self.opt = torch.optim.AdamW(self.dec.flat_parameters(), lr=1e-4, fused=True, capturable=graph)
+        self.opt = torch.optim.AdamW(self.dec.flat_parameters(prosody=prosody), lr=1e-4, fused=True, capturable=graph)
         self.graphed = None
         gen = torch.Generator().manual_seed(SEED + int(os.environ.get("RANK", "0")))
         self.host = synth_batch(B_PER_GPU, gen, len_gen=torch.Generator().manual_seed(SEED))
+        if prosody:
+            # the live fork's per-frame tracks (models.py:1057-1075): raw F0 in Hz with unvoiced frames at 0, raw energy
+            pitch = torch.rand(B_PER_GPU, 1, T_MEL, generator=gen) * 300 + 60
+            pitch = pitch * (torch.rand(B_PER_GPU, 1, T_MEL, generator=gen) > 0.3)
+            energy = torch.rand(B_PER_GPU, 1, T_MEL, generator=gen) * 4 + 0.05
+            self.host += [pitch.pin_memory(), energy.pin_memory()]
         self.dev = [t.to(device) for t in self.host]
         # configs[3] (base_blank_ms.json): speaker embedding g [B, gin, 1] (models.py:1040-1041), resident
         self.g = (torch.randn(B_PER_GPU, gin, 1, generator=gen).to(device) if gin else None)
@@ -168,9 +174,10 @@ class Runner:
 
     def step(self, batch):
         from glowtts_b200.hot_path import train_hot_path
-        y, y_len, x_m, x_len = batch
+        y, y_len, x_m, x_len, *tracks = batch
+        pitch, energy = tracks if tracks else (None, None)
         self.opt.zero_grad(set_to_none=True)
-        out = train_hot_path(self.dec, y, y_len, x_m, None, x_len, g=self.g)
+        out = train_hot_path(self.dec, y, y_len, x_m, None, x_len, g=self.g, pitch=pitch, energy=energy)
         out.loss.backward()
         self.opt.step()
         return out.loss
@@ -367,6 +374,50 @@ def multispeaker_step(device, world, precision, graph, steps, warmup):
     out = {"workload": "configs[3]: base_blank_ms.json train step (gin_channels=256 speaker conditioning), B=32 per GPU",
            "n_gpus": world, "ms_per_step": ms / steps, "mel_frames_per_s": frames / (ms / steps * 1e-3),
            "launch": "cuda_graph" if run.graphed is not None else "eager"}
+    del run
+    torch.cuda.empty_cache()
+    return out
+
+
+def prosody_step(device, world, precision, graph, steps, warmup, ms_plain):
+    """The live fork's train step: every coupling block chains wn -> wn_energy -> wn_pitch
+    (attentions.py:155-160) inside the fused call, pitch / energy tracks copied with the batch; same B=32 per GPU.
+    FLOPs: the three WaveNets of a block (3 x 4 layers) + start / end convs, forward, per squeezed frame."""
+    run = Runner(device, world, precision, graph=graph, prosody=True)
+    for _ in range(max(warmup, 3)):
+        run.step_e2e()
+    ms = timed(run.step_resident, steps, world)
+    ms_e2e = timed(run.step_e2e, steps, world)
+    from glowtts_b200 import _lib
+    from glowtts_b200.distributed import sum_over_ranks
+    frames = sum_over_ranks(run.frames, device)
+    out = {"workload": "live-fork train step: 3 WaveNets per coupling block (wn, wn_energy, wn_pitch) with per-frame pitch / "
+                       "energy tracks, B=32 per GPU, otherwise configs[1]",
+           "n_gpus": world, "ms_per_step": ms / steps, "mel_frames_per_s": frames / (ms / steps * 1e-3),
+           "e2e_ms_per_step": ms_e2e / steps, "h2d_bytes_per_step": run.h2d_bytes,
+           "vs_one_wavenet_step": (ms / steps) / ms_plain if ms_plain else None,
+           "launch": "cuda_graph" if run.graphed is not None else "eager",
+           "gpu_launches_per_step": run.graphed.launches if run.graphed is not None else None}
+    if world == 1:
+        # roofline of the fused layer kernels in THIS step (event profiler, eager pass)
+        _lib.prof_enable(True)
+        for _ in range(2):
+            run.step(run.dev)
+        torch.cuda.synchronize()
+        prof = _lib.prof_read()
+        _lib.prof_enable(False)
+        H, K, L = CFG["hidden_channels"], CFG["kernel_size"], CFG["n_layers"]
+        flop_layer = (2.0 * (2 * H * H * K) + 2.0 * H * H * (2 * (L - 1) + 1) / L) * (run.frames // CFG["n_sqz"])
+        pk = peaks()
+        for tag in ("wn_layer_tc", "wn_bwd_layer_tc"):
+            n_l, ms_l = prof.get(tag, (0, 0.0))
+            if ms_l > 0:
+                out[tag] = {"launches_per_step": n_l / 2, "ms_per_launch": ms_l / n_l,
+                            "tflops": flop_layer * n_l / (ms_l * 1e-3) / 1e12,
+                            "frac_of_sustained_bf16_peak": flop_layer * n_l / (ms_l * 1e-3) / 1e12 / pk["tc_sustained"]}
+        fwd_flop_frame = CFG["n_blocks"] * (FLOP_PER_SQ_FRAME_FWD + 2 * 2 * (4 * (384 * 192 * 5) + 3 * (384 * 192) + 192 * 192))
+        out["mflop_per_sq_frame_fwd"] = fwd_flop_frame / 1e6
+        out["step_tflops"] = 3.0 * fwd_flop_frame * (run.frames // CFG["n_sqz"]) / (ms / steps * 1e-3) / 1e12
     del run
     torch.cuda.empty_cache()
     return out
@@ -579,6 +630,9 @@ def main():
         leg("mas_stress_index_only", lambda: mas_alone(device, steps=5, B=b_stress, TX=400, TY=2000, n_buf=1, world=world,
                                                        want_path=False, name=f"configs[4]: B=512 over {world} GPU(s)"))
     leg("multispeaker", lambda: multispeaker_step(device, world, args.precision, not args.no_graph, args.steps, args.warmup))
+    if args.precision == "bf16":
+        leg("prosody", lambda: prosody_step(device, world, args.precision, not args.no_graph, args.steps, args.warmup,
+                                            ms_res / args.steps))
 
     if rank == 0:
         pk = peaks()

@@ -256,7 +256,7 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
             }
             p.n_rows = pl.n_rows(); p.row_b = pl.row_b; p.row_fr = pl.row_fr;
             p.mask = mask;
-            p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, w * D.L + i);
+            p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, D.wn_id[w] * D.L + i);
             p.h_f32 = hf[cur]; p.h_out_f32 = hf[cur ^ 1];
             p.h_out_bf16 = (i < D.L - 1) ? reinterpret_cast<bf16*>(act + A.h[LI(w, i + 1)]) : nullptr;
             p.skip_f32 = skipf;
@@ -495,7 +495,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 p.B = B; p.T = T; p.H = H; p.RS = RS; p.taps = K; p.dil = dil;
                 p.mask = msq; p.ts = ts;
                 p.n_rows = pl.n_rows(); p.row_fr = pl.row_fr; p.dpre = dpre;
-                p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, w * D.L + i);
+                p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, D.wn_id[w] * D.L + i);
                 p.resid_f32 = (i < D.L - 1) ? dhf[(i + 1) & 1] : nullptr;
                 p.out_f32 = dhf[i & 1];
                 GTK_TRY(tc::wn_bwd_layer_launch(drs_i, 2 * H, pk + Q.t_rs[LI(w, i)], pk + Q.t_in[LI(w, i)], dxin,
@@ -509,7 +509,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                     p.n_rows = pl.n_rows(); p.row_fr = pl.row_fr;
                     p.tile_layout = 1;
                     p.ts = ts; p.out_bf16 = dxin; p.ld_bf16 = 2 * H;
-                    p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, w * D.L + i);
+                    p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, D.wn_id[w] * D.L + i);
                     p.out2_bf16 = dpre;
                     GTK_TRY(tc::conv_tc_launch(drs_i, 2 * H, pk + Q.t_rs[LI(w, i)], p, tc::EPI_GATE_BWD, st));
                 }

@@ -195,9 +195,10 @@ def wn(sd: SD, prefix: str, x: Tensor, x_mask: Tensor, g: Optional[Tensor], hidd
 
 
 def wnp(sd: SD, prefix: str, x: Tensor, x_mask: Tensor, g1: Optional[Tensor], hidden: int,
-        dilation_rate: int, n_layers: int, n_sqz: int = 2) -> Tensor:
+        dilation_rate: int, n_layers: int, n_sqz: int = 2, drop=None) -> Tensor:
     """modules.py:316-343 + 353-362: identity when g1 is None; otherwise the WN body
-    with a time-varying conditioner cond_layer1(g1) squeezed by n_sqz."""
+    with a time-varying conditioner cond_layer1(g1) squeezed by n_sqz.  `drop(layer, x_in)` stands for self.drop
+    (modules.py:331), as in wn()."""
     if g1 is None:
         return x
     cond = _conv(sd, prefix + ".cond_layer1", g1)
@@ -206,6 +207,8 @@ def wnp(sd: SD, prefix: str, x: Tensor, x_mask: Tensor, g1: Optional[Tensor], hi
     out = torch.zeros_like(x)
     for i in range(n_layers):
         x_in = _conv(sd, f"{prefix}.in_layers.{i}", x, dilation=dilation_rate**i)
+        if drop is not None:
+            x_in = drop(i, x_in)
         acts = fused_add_tanh_sigmoid_multiply(x_in, cond[:, 2 * hidden * i : 2 * hidden * (i + 1)], hidden)
         rs = _conv(sd, f"{prefix}.res_skip_layers.{i}", acts)
         if i < n_layers - 1:
@@ -229,8 +232,10 @@ def coupling(sd: SD, prefix: str, x: Tensor, x_mask: Tensor, *, hidden: int, dil
         energy = energy.unsqueeze(1)
     h = _conv(sd, prefix + ".start", x0) * x_mask
     h = wn(sd, prefix + ".wn", h, x_mask, g, hidden, dilation_rate, n_layers, drop)
-    h = wnp(sd, prefix + ".wn_energy", h, x_mask, energy, hidden, dilation_rate, n_layers, n_sqz)
-    h = wnp(sd, prefix + ".wn_pitch", h, x_mask, pitch, hidden, dilation_rate, n_layers, n_sqz)
+    # the drop hook numbers the layers of the three WaveNets 0..L-1 (wn), L..2L-1 (wn_energy), 2L..3L-1 (wn_pitch)
+    sub = lambda k: None if drop is None else (lambda i, v: drop(k * n_layers + i, v))
+    h = wnp(sd, prefix + ".wn_energy", h, x_mask, energy, hidden, dilation_rate, n_layers, n_sqz, sub(1))
+    h = wnp(sd, prefix + ".wn_pitch", h, x_mask, pitch, hidden, dilation_rate, n_layers, n_sqz, sub(2))
     out = _conv(sd, prefix + ".end", h)
     m, logs = out[:, : c // 2], out[:, c // 2 :]
     if sigmoid_scale:
