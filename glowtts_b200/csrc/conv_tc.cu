@@ -126,15 +126,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     else __syncthreads();
     tc_fence_after();
     // PDL: the producer thread requests the weight tiles of its first stages before pdl_wait() (see wn_tc.cu)
-    const bool is_producer = (warp == 0 && lane == 0);
+    const bool is_producer = (warp == 0);
     if (!is_producer) pdl_wait();
     const uint32_t tmem = ctl->tmem_base;
     CONV_TRACE(1);
 
+    // Whole warp in the uniform loops, ONE ELECTED lane issues the TMA / MMA instructions: their descriptors stay in
+    // uniform registers (under `if (lane == 0)` every one is wrapped in an R2UR waterfall loop, profiles/mma_issue_r02.txt)
     if (warp == 0) {
-        if (lane == 0) {
-            tma_prefetch_desc(&tmA);
-            tma_prefetch_desc(&tmB);
+        {
+            if (elect_one()) {
+                tma_prefetch_desc(&tmA);
+                tma_prefetch_desc(&tmB);
+            }
             long long w_empty = 0;
             auto load_weights = [&](int s, int j, int kc) {
                 unsigned char* sb = smem + (size_t)s * stage_bytes + A_BYTES;
@@ -150,7 +154,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
             };
             const int n_pre = min(p.stages, n_iter);
-            for (int it = 0; it < n_pre; ++it) load_weights(it, it / p.n_k, it % p.n_k);
+            if (elect_one())
+                for (int it = 0; it < n_pre; ++it) load_weights(it, it / p.n_k, it % p.n_k);
+            __syncwarp();
             pdl_wait();
             for (int it = 0; it < n_iter; ++it) {
                 const int s = it % p.stages, use = it / p.stages;
@@ -161,15 +167,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
                 const int j = it / p.n_k, kc = it % p.n_k;
                 unsigned char* sa = smem + (size_t)s * stage_bytes;
-                if (it >= n_pre) load_weights(s, j, kc);
-                tma_load_3d(sa, &tmA, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
+                if (elect_one()) {
+                    if (it >= n_pre) load_weights(s, j, kc);
+                    tma_load_3d(sa, &tmA, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
+                }
+                __syncwarp();
             }
             #ifdef GTK_INSTRUMENT
             if (p.trace) { const int cta_ = blockIdx.y * gridDim.x + blockIdx.x; if (cta_ < CONV_TRACE_CTAS) g_conv_wait[cta_ * 2] = w_empty; }
 #endif
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {
+            const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
             const uint32_t idesc = umma_idesc_bf16(BT, p.NW);
             long long w_full = 0;
             for (int it = 0; it < n_iter; ++it) {
@@ -180,28 +190,31 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 tc_fence_after();
                 const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
                 const uint32_t sb = sa + A_BYTES;
-                const uint64_t adesc = umma_desc_kmajor_sw128(sa);
-                // Back-to-back MMAs into ONE accumulator serialise on its read-modify-write latency (measured: 127 ns
-                // instead of 77 ns per 128x192x16 MMA).  With N <= 256 the k16 steps alternate between two accumulators
-                // (TMEM columns 0.. and 256..), which the epilogue adds.
-                if (dual) {
-                    const uint64_t bdesc = umma_desc_kmajor_sw128(sb);
+                if (elect_one()) {
+                    const uint64_t adesc = umma_desc_kmajor_sw128(sa);
+                    // Back-to-back MMAs into ONE accumulator serialise on its read-modify-write latency.  With N <= 256 the
+                    // k16 steps alternate between two accumulators (TMEM columns 0.. and 256..), which the epilogue adds.
+                    if (dual) {
+                        const uint64_t bdesc = umma_desc_kmajor_sw128(sb);
 #pragma unroll
-                    for (int k = 0; k < KC / 16; ++k)
-                        umma_bf16(tmem + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, it != 0 || k >= 2);
-                } else {
+                        for (int k = 0; k < KC / 16; ++k)
+                            umma_bf16(tm + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, it != 0 || k >= 2);
+                    } else {
 #pragma unroll
-                    for (int k = 0; k < KC / 16; ++k) {
-                        for (int ch = 0; ch < p.NCH; ++ch) {
-                            const uint64_t bdesc = umma_desc_kmajor_sw128(sb + ch * p.NW * KC * 2);
-                            umma_bf16(tmem + ch * p.NW, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0);
+                        for (int k = 0; k < KC / 16; ++k) {
+                            for (int ch = 0; ch < p.NCH; ++ch) {
+                                const uint64_t bdesc = umma_desc_kmajor_sw128(sb + ch * p.NW * KC * 2);
+                                umma_bf16(tm + ch * p.NW, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0);
+                            }
                         }
                     }
+                    if constexpr (CL > 1) umma_commit_multicast(&ctl->empty[s], (uint16_t)((1u << CL) - 1));
+                    else umma_commit(&ctl->empty[s]);
                 }
-                if constexpr (CL > 1) umma_commit_multicast(&ctl->empty[s], (uint16_t)((1u << CL) - 1));
-                else umma_commit(&ctl->empty[s]);
+                __syncwarp();
             }
-            umma_commit(&ctl->acc_full);
+            if (elect_one()) umma_commit(&ctl->acc_full);
+            __syncwarp();
             #ifdef GTK_INSTRUMENT
             if (p.trace) { const int cta_ = blockIdx.y * gridDim.x + blockIdx.x; if (cta_ < CONV_TRACE_CTAS) g_conv_wait[cta_ * 2 + 1] = w_full; }
 #endif

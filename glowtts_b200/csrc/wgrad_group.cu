@@ -4,7 +4,15 @@
 //   dW_q[m][c][j] = sum_{b,t} dY_q[b, t, m] * X_q[b, t + (j - K_q/2) dil_q, c]          for every conv q of the block
 //   db_q[m]       = sum_{b,t} dY_q[b, t, m]                                             (a column of ones appended to X_q)
 //
-// Work = (conv, 128-row M tile, tap) tiles x (utterance, 64-frame chunk) k-steps.  All tiles of all convs are laid
+// Work = tiles x (utterance, 64-frame chunk) k-steps.  A tile is
+//   * (conv, 128-row M tile, tap) with all X columns: the default.  One tile per tap, each fetching dY and a shifted
+//     copy of X: ~490 MB of L2 -> SM traffic per coupling block, which is what bounds it (profiles/wgrad_overlap_r02.txt);
+//   * opt-in (GTK_WGRAD_ALL_TAPS=1), k > 1 convs: "all-taps" tiles (conv, 128-row M tile, 64-column block of X) with EVERY
+//     tap inside: the X rows [t0 - halo, t0 + 64 + halo) are staged ONCE per k-step and tap j is a row-shifted MN-major
+//     descriptor on them (the 128-byte swizzle is a function of the shared-memory address only), one TMEM accumulator of
+//     64 columns per tap.  Less than half the traffic, but N = 64 MMAs run at ~74 cycles each: no faster overall
+//     (profiles/mma_issue_r02.txt).
+// All tiles of all convs are laid
 // end to end (weighted by the bytes one k-step stages) and cut into `grid` equal contiguous shares, one per SM
 // ("stream-K"): no wave quantisation, no per-conv launch, and each CTA writes at most a few partial tiles.  A CTA
 // walks its segments with one TMA producer thread, one MMA thread and four epilogue warps; two 256-column TMEM
@@ -14,6 +22,7 @@
 // {64 channels x 64 frames} SWIZZLE_128B boxes, the conv tap being a shifted (zero-filled) box of X -- as in
 // wgrad_tc.cu.  The bias gradient rides along as X block 3 = [1, 0, 0, ...] written once to shared memory.
 // The reduce kernel sums a tile's partial slots and finishes weight norm (dg, dv) and the bias gradient per row.
+#include <stdlib.h>
 #include <string.h>
 
 #include "tc.cuh"
@@ -27,12 +36,16 @@ constexpr int GG_BOX = GG_TK * 128;              // bytes of one {64 ch, 64 fram
 constexpr int GG_STAGES = 4;
 constexpr int GG_STAGE_BYTES = 6 * GG_BOX;       // 2 dY boxes (128 rows of M) + up to 4 X boxes (N <= 256)
 constexpr int GG_ONES_BLK = 3;                   // X block that holds the ones column (never written by TMA)
-constexpr int GG_SLOT_FLOATS = 128 * 256;        // one partial tile
+constexpr int GG_SLOT_COLS = 512;                // one partial tile: 128 rows x up to 512 accumulator columns
+constexpr int GG_SLOT_FLOATS = 128 * GG_SLOT_COLS;
+constexpr int GG_ALL_TAPS = 0xFF;                // GgTile::tap of an all-taps tile
+constexpr int GG_CB = 64;                        // X columns of an all-taps tile = accumulator columns per tap
 
 struct GgJobDev {
     int taps, dil, n_blk, ones;                  // n_blk = real 64-column blocks of X; ones: bias gradient wanted
+    int halo;                                    // (taps / 2) * dil: rows staged either side of a k-step (all-taps tiles)
 };
-struct GgTile { unsigned char job, m_tile, tap, pad; };
+struct GgTile { unsigned char job, m_tile, tap, cblk; };   // tap == GG_ALL_TAPS: every tap, X columns [64 cblk, 64 cblk + 64)
 struct GgSeg { unsigned short tile, s_lo, s_hi, slot; };
 struct GgCta { unsigned short seg0, nseg; };
 
@@ -45,6 +58,7 @@ struct GgParams {
     GgSeg seg[WGG_MAX_SEGS];
     GgCta cta[WGG_MAX_CTAS];
     CUtensorMap tmY[WGG_MAX_JOBS], tmX[WGG_MAX_JOBS];
+    CUtensorMap tmXh[WGG_MAX_JOBS];              // X with a {64 columns, 64 + 2 halo rows} box (all-taps tiles)
 };
 
 struct GgCtl {
@@ -87,64 +101,108 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
     const uint32_t tmem = ctl->tmem_base;
 
     if (warp == 0) {
-        if (lane == 0) {
-            int it = 0;
-            for (int sg = 0; sg < me.nseg; ++sg) {
-                const GgSeg S = p.seg[me.seg0 + sg];
-                const GgTile Tl = p.tile[S.tile];
-                const GgJobDev J = p.job[Tl.job];
-                const CUtensorMap* tmX = &p.tmX[Tl.job];
-                const CUtensorMap* tmY = &p.tmY[Tl.job];
-                const int m0 = Tl.m_tile * 128;
-                const int shift = ((int)Tl.tap - J.taps / 2) * J.dil;
-                const uint32_t bytes = (uint32_t)(2 + J.n_blk) * GG_BOX;
-                const int s_lo = GG_SCALE(S.s_lo), s_hi = GG_SCALE(S.s_hi);
-                for (int step = s_lo; step < s_hi; ++step, ++it) {
-                    const int s = it % GG_STAGES, use = it / GG_STAGES;
-                    if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
-                    const int b = step / p.chunks_t, t0 = (step % p.chunks_t) * GG_TK;
-                    unsigned char* sa = smem + (size_t)s * GG_STAGE_BYTES;
-                    unsigned char* sb = sa + 2 * GG_BOX;
+        // TMA producer: whole warp in the uniform loops, one elected lane issues (see the MMA warp)
+        int it = 0;
+        for (int sg = 0; sg < me.nseg; ++sg) {
+            const GgSeg S = p.seg[me.seg0 + sg];
+            const GgTile Tl = p.tile[S.tile];
+            const GgJobDev J = p.job[Tl.job];
+            const CUtensorMap* tmX = &p.tmX[Tl.job];
+            const CUtensorMap* tmY = &p.tmY[Tl.job];
+            const int m0 = Tl.m_tile * 128;
+            const bool all_taps = Tl.tap == GG_ALL_TAPS;
+            const int shift = all_taps ? -J.halo : ((int)Tl.tap - J.taps / 2) * J.dil;
+            const uint32_t bytes = all_taps ? (uint32_t)(2 * GG_BOX + (GG_TK + 2 * J.halo) * 128) : (uint32_t)(2 + J.n_blk) * GG_BOX;
+            const int s_lo = GG_SCALE(S.s_lo), s_hi = GG_SCALE(S.s_hi);
+            for (int step = s_lo; step < s_hi; ++step, ++it) {
+                const int s = it % GG_STAGES, use = it / GG_STAGES;
+                if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
+                const int b = step / p.chunks_t, t0 = (step % p.chunks_t) * GG_TK;
+                unsigned char* sa = smem + (size_t)s * GG_STAGE_BYTES;
+                unsigned char* sb = sa + 2 * GG_BOX;
+                if (elect_one()) {
                     mbar_arrive_expect_tx(&ctl->full[s], bytes);
                     tma_load_3d(sa, tmY, &ctl->full[s], m0, t0, b);
                     tma_load_3d(sa + GG_BOX, tmY, &ctl->full[s], m0 + 64, t0, b);
-                    for (int nb = 0; nb < J.n_blk; ++nb)
-                        tma_load_3d(sb + (size_t)nb * GG_BOX, tmX, &ctl->full[s], nb * 64, t0 + shift, b);
+                    if (all_taps) {
+                        tma_load_3d(sb, &p.tmXh[Tl.job], &ctl->full[s], Tl.cblk * GG_CB, t0 + shift, b);
+                    } else {
+                        for (int nb = 0; nb < J.n_blk; ++nb)
+                            tma_load_3d(sb + (size_t)nb * GG_BOX, tmX, &ctl->full[s], nb * 64, t0 + shift, b);
+                    }
                 }
+                __syncwarp();
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            int it = 0, ne = 0;                            // ne: non-empty segments so far (accumulator hand-shake parity)
-            for (int sg = 0; sg < me.nseg; ++sg) {
-                const GgSeg S = p.seg[me.seg0 + sg];
-                const GgTile Tl = p.tile[S.tile];
-                const GgJobDev J = p.job[Tl.job];
-                const int s_lo = GG_SCALE(S.s_lo), s_hi = GG_SCALE(S.s_hi);
-                if (s_hi <= s_lo) continue;
-                const int N = (J.ones && Tl.tap == 0) ? (GG_ONES_BLK + 1) * 64 : J.n_blk * 64;
-                const uint32_t idesc = umma_idesc_bf16(128, N, 1, 1);
-                // Two accumulators (TMEM columns 0.. and 256..) take alternate k16 steps: back-to-back MMAs into one
-                // accumulator serialise on its read-modify-write latency.  The epilogue adds them; the next segment
-                // starts when it has drained both (segments are ~100 k-steps long, the drain is a few per cent).
-                if (ne > 0) { mbar_wait(&ctl->acc_empty[0], (ne - 1) & 1); tc_fence_after(); }
+        // MMA issue.  The WHOLE warp walks the (warp-uniform) loops and one elected lane issues: the descriptors then live
+        // in uniform registers.  Under `if (lane == 0)` the compiler cannot prove uniformity and wraps every tcgen05.mma in
+        // an R2UR waterfall loop (~15 instructions, >100 cycles per MMA: profiles/mma_issue_r02.txt).
+        const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
+        int it = 0, ne = 0;                            // ne: non-empty segments so far (accumulator hand-shake parity)
+        for (int sg = 0; sg < me.nseg; ++sg) {
+            const GgSeg S = p.seg[me.seg0 + sg];
+            const GgTile Tl = p.tile[S.tile];
+            const GgJobDev J = p.job[Tl.job];
+            const int s_lo = GG_SCALE(S.s_lo), s_hi = GG_SCALE(S.s_hi);
+            if (s_hi <= s_lo) continue;
+            if (ne > 0) { mbar_wait(&ctl->acc_empty[0], (ne - 1) & 1); tc_fence_after(); }
+            if (Tl.tap == GG_ALL_TAPS) {
+                // one accumulator per tap (columns [64 j, 64 j + 64)): independent MMA chains by construction; the bias
+                // gradient (ones column) takes 16 more columns on the tile of X block 0
+                const uint32_t idesc_t = umma_idesc_bf16(128, GG_CB, 1, 1), idesc_1 = umma_idesc_bf16(128, 16, 1, 1);
+                const bool ones = J.ones && Tl.cblk == 0;
                 for (int step = s_lo; step < s_hi; ++step, ++it) {
                     const int s = it % GG_STAGES, use = it / GG_STAGES;
                     mbar_wait(&ctl->full[s], use & 1);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + (size_t)s * GG_STAGE_BYTES);
                     const uint32_t sb = sa + 2 * GG_BOX;
+                    if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < GG_TK / 16; ++k) {
-                        const uint64_t adesc = umma_desc_mnmajor_sw128(sa + k * 2048, GG_BOX, 1024);
-                        const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + k * 2048, GG_BOX, 1024);
-                        umma_bf16(tmem + (k & 1) * 256, adesc, bdesc, idesc, (step != s_lo) || k >= 2);
+                        for (int k = 0; k < GG_TK / 16; ++k) {
+                            const uint64_t adesc = umma_desc_mnmajor_sw128(sa + k * 2048, GG_BOX, 1024);
+                            const bool acc = (step != s_lo) || k > 0;
+                            for (int j = 0; j < J.taps; ++j) {
+                                const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + (uint32_t)(j * J.dil) * 128u + k * 2048, GG_BOX, 1024);
+                                umma_bf16(tm + j * GG_CB, adesc, bdesc, idesc_t, acc);
+                            }
+                            if (ones) {
+                                const uint64_t bdesc = umma_desc_mnmajor_sw128(sa + (2 + GG_ONES_BLK) * GG_BOX + k * 2048, GG_BOX, 1024);
+                                umma_bf16(tm + J.taps * GG_CB, adesc, bdesc, idesc_1, acc);
+                            }
+                        }
+                        umma_commit(&ctl->empty[s]);
                     }
-                    umma_commit(&ctl->empty[s]);
+                    __syncwarp();
                 }
-                umma_commit(&ctl->acc_full[0]);
-                ++ne;
+            } else {
+                const int N = (J.ones && Tl.tap == 0) ? (GG_ONES_BLK + 1) * 64 : J.n_blk * 64;
+                const uint32_t idesc = umma_idesc_bf16(128, N, 1, 1);
+                // Two accumulators (TMEM columns 0.. and 256..) take alternate k16 steps: back-to-back MMAs into one
+                // accumulator serialise on its read-modify-write latency.  The epilogue adds them; the next segment
+                // starts when it has drained both (segments are ~100 k-steps long, the drain is a few per cent).
+                for (int step = s_lo; step < s_hi; ++step, ++it) {
+                    const int s = it % GG_STAGES, use = it / GG_STAGES;
+                    mbar_wait(&ctl->full[s], use & 1);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + (size_t)s * GG_STAGE_BYTES);
+                    const uint32_t sb = sa + 2 * GG_BOX;
+                    if (elect_one()) {
+#pragma unroll
+                        for (int k = 0; k < GG_TK / 16; ++k) {
+                            const uint64_t adesc = umma_desc_mnmajor_sw128(sa + k * 2048, GG_BOX, 1024);
+                            const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + k * 2048, GG_BOX, 1024);
+                            umma_bf16(tm + (k & 1) * 256, adesc, bdesc, idesc, (step != s_lo) || k >= 2);
+                        }
+                        umma_commit(&ctl->empty[s]);
+                    }
+                    __syncwarp();
+                }
             }
+            if (elect_one()) umma_commit(&ctl->acc_full[0]);
+            __syncwarp();
+            ++ne;
         }
     } else if (warp >= 4) {
         const int q = warp & 3;
@@ -153,27 +211,31 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
             const GgSeg S = p.seg[me.seg0 + sg];
             const GgTile Tl = p.tile[S.tile];
             const GgJobDev J = p.job[Tl.job];
-            float* prow = p.part + (size_t)S.slot * GG_SLOT_FLOATS + (size_t)(q * 32 + lane) * 256;
+            float* prow = p.part + (size_t)S.slot * GG_SLOT_FLOATS + (size_t)(q * 32 + lane) * GG_SLOT_COLS;
+            const bool all_taps = Tl.tap == GG_ALL_TAPS;
+            const int n_cols = all_taps ? J.taps * GG_CB : J.n_blk * 64;             // weight-gradient columns of the tile
+            const bool ones = J.ones && (all_taps ? Tl.cblk == 0 : Tl.tap == 0);
+            const int ones_col = all_taps ? J.taps * GG_CB : GG_ONES_BLK * 64;
             if (GG_SCALE(S.s_hi) <= GG_SCALE(S.s_lo)) {              // empty share: its partial tile is zero
-                for (int c0 = 0; c0 < J.n_blk * 64; c0 += 4) *reinterpret_cast<float4*>(prow + c0) = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (J.ones && Tl.tap == 0) prow[GG_ONES_BLK * 64] = 0.f;
+                for (int c0 = 0; c0 < n_cols; c0 += 4) *reinterpret_cast<float4*>(prow + c0) = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (ones) prow[ones_col] = 0.f;
                 continue;
             }
             mbar_wait(&ctl->acc_full[0], ne & 1);
             ++ne;
             tc_fence_after();
             const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
-            for (int c0 = 0; c0 < J.n_blk * 64; c0 += 16) {
+            for (int c0 = 0; c0 < n_cols; c0 += 16) {
                 float v[16];
-                tmem_ld16_dual(trow + c0, true, v);
+                tmem_ld16_dual(trow + c0, !all_taps, v);
                 float4* o4 = reinterpret_cast<float4*>(prow + c0);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
             }
-            if (J.ones && Tl.tap == 0) {
+            if (ones) {
                 float v[16];
-                tmem_ld16_dual(trow + GG_ONES_BLK * 64, true, v);
-                prow[GG_ONES_BLK * 64] = v[0];
+                tmem_ld16_dual(trow + ones_col, !all_taps, v);
+                prow[ones_col] = v[0];
             }
             tc_fence_before();
             __syncwarp();
@@ -196,6 +258,7 @@ struct GgRedJob {
     float* dv;
     float* db;                 // bias gradient [M] or null
     int M, Cin, taps, tile0, row0, ones;
+    int n_cblk;                // > 0: all-taps tiles, tile = tile0 + m_tile * n_cblk + c / 64, column = 64 tap + c % 64
 };
 struct GgRedParams {
     const float* part;
@@ -222,7 +285,7 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
     const float* __restrict__ vrow = J.v + (size_t)m * R;
     float* __restrict__ dvrow = J.dv + (size_t)m * R;
     const bool wn = J.g != nullptr;
-    const float* part_row = p.part + (size_t)r * 256;
+    const float* part_row = p.part + (size_t)r * GG_SLOT_COLS;
     float ss = 0.f, dd = 0.f;
     for (int e0 = threadIdx.x; e0 < R; e0 += 4 * GG_RED_NT) {
         float acc[4], vv[4];
@@ -233,8 +296,8 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
             acc[u] = 0.f; vv[u] = 0.f; idx[u] = -1;
             if (e < R) {
                 const int j = e / Cin, c = e - j * Cin;        // c fastest: coalesced reads of the partial tiles
-                const int tile = J.tile0 + m_tile * taps + j;
-                const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + c;
+                const int tile = J.n_cblk ? J.tile0 + m_tile * J.n_cblk + c / GG_CB : J.tile0 + m_tile * taps + j;
+                const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + (J.n_cblk ? j * GG_CB + c % GG_CB : c);
                 const int ns = p.nslot[tile];
                 idx[u] = c * taps + j;
                 if (wn) vv[u] = vrow[idx[u]];
@@ -256,8 +319,8 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
             }
     }
     if (J.db && J.ones && threadIdx.x == GG_RED_NT - 1) {
-        const int tile = J.tile0 + m_tile * taps;
-        const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + GG_ONES_BLK * 64;
+        const int tile = J.tile0 + m_tile * (J.n_cblk ? J.n_cblk : taps);
+        const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + (J.n_cblk ? taps * GG_CB : GG_ONES_BLK * 64);
         float acc = 0.f;
         for (int s = 0; s < p.nslot[tile]; ++s) acc += src[(size_t)s * GG_SLOT_FLOATS];
         J.db[m] += acc;
@@ -284,10 +347,10 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
 // ------------------------------------------------------------------------------------------ host
 size_t wgrad_group_workspace_bytes() { return (size_t)(WGG_MAX_CTAS + WGG_MAX_TILES) * GG_SLOT_FLOATS * sizeof(float); }
 
-static int tmap_frames(CUtensorMap* out, const __nv_bfloat16* base, int ld, int cols, int T, int B) {
+static int tmap_frames(CUtensorMap* out, const __nv_bfloat16* base, int ld, int cols, int T, int B, int box_rows = GG_TK) {
     const uint64_t dims[3] = {(uint64_t)cols, (uint64_t)T, (uint64_t)B};
     const uint64_t strides[2] = {(uint64_t)ld * 2, (uint64_t)ld * 2 * T};
-    const uint32_t box[3] = {64, GG_TK, 1};
+    const uint32_t box[3] = {64, (uint32_t)box_rows, 1};
     return make_tmap_bf16(out, base, 3, dims, strides, box, true);
 }
 
@@ -305,9 +368,18 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     const int S = B * P.chunks_t;
     GTK_REQUIRE(S <= 65535, "too many k-steps for the segment table");
 
+    // all-taps tiles (opt-in, GTK_WGRAD_ALL_TAPS=1): k > 1, the per-tap accumulators (+ 16 bias columns) fit the 512 TMEM
+    // columns, the staged X rows fit the three X boxes of a stage.  Measured on the bench workload (B200, round 2,
+    // profiles/mma_issue_r02.txt): L2 -> SM traffic 490 -> 223 MB per coupling block, but an N = 64 MMA costs ~74 cycles
+    // (its tensor-pipe time is 32), so the kernel ends up at the same time as the per-tap tiles (0.74 vs 0.70 ms per
+    // step).  Per-tap stays the default; N = 96 column blocks (two boxes per stage) are the next thing to try.
+    static const bool all_taps_on = getenv("GTK_WGRAD_ALL_TAPS") && atoi(getenv("GTK_WGRAD_ALL_TAPS")) != 0;
+    auto all_taps = [&](const WgradGroupJob& J) {
+        return all_taps_on && J.K > 1 && J.K * GG_CB + 16 <= GG_SLOT_COLS && GG_TK + 2 * (J.K / 2) * J.dil <= 3 * GG_TK;
+    };
     bool ones_ok = true;
-    for (int q = 0; q < n_jobs; ++q) ones_ok = ones_ok && ceil_div(jobs[q].Cin, 64) <= GG_ONES_BLK;
-    int n_tiles = 0, rows = 0;
+    for (int q = 0; q < n_jobs; ++q) ones_ok = ones_ok && (all_taps(jobs[q]) || ceil_div(jobs[q].Cin, 64) <= GG_ONES_BLK);
+    int n_tiles = 0, rows = 0, rc_at = 0;
     size_t max_row = 0;
     long long w_tile[WGG_MAX_TILES];
     for (int q = 0; q < n_jobs; ++q) {
@@ -317,8 +389,13 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
         GTK_REQUIRE(J.ld_y % 8 == 0 && J.ld_x % 8 == 0 && J.cols_x >= J.Cin, "frame pitch");
         GTK_REQUIRE(J.cols_y >= J.M, "dY columns");
         GgJobDev& D = P.job[q];
-        D.taps = J.K; D.dil = J.dil; D.n_blk = ceil_div(J.Cin, 64);
+        D.taps = J.K; D.dil = J.dil; D.n_blk = ceil_div(J.Cin, 64); D.halo = (J.K / 2) * J.dil;
         D.ones = (J.db && ones_ok) ? 1 : 0;
+        const bool at = all_taps(J);
+        if (at) {
+            rc_at = tmap_frames(&P.tmXh[q], J.x, J.ld_x, J.cols_x, T, B, GG_TK + 2 * D.halo);
+            if (rc_at) return rc_at;
+        }
         int rc = tmap_frames(&P.tmY[q], J.dy, J.ld_y, J.cols_y, T, B);
         if (rc) return rc;
         rc = tmap_frames(&P.tmX[q], J.x, J.ld_x, J.cols_x, T, B);
@@ -326,15 +403,26 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
         GgRedJob& Q = R.job[q];
         Q.g = J.g; Q.v = J.v; Q.dg = J.dg; Q.dv = J.dv; Q.db = J.db;
         Q.M = J.M; Q.Cin = J.Cin; Q.taps = J.K; Q.tile0 = n_tiles; Q.row0 = rows; Q.ones = D.ones;
+        Q.n_cblk = at ? D.n_blk : 0;
         rows += J.M;
         max_row = max(max_row, (size_t)J.Cin * J.K * sizeof(float));
         const int m_tiles = ceil_div(J.M, 128);
-        GTK_REQUIRE(n_tiles + m_tiles * J.K <= WGG_MAX_TILES && m_tiles <= 255 && J.K <= 255, "too many tiles in one group");
+        const int per_m = at ? D.n_blk : J.K;
+        GTK_REQUIRE(n_tiles + m_tiles * per_m <= WGG_MAX_TILES && m_tiles <= 255 && J.K < GG_ALL_TAPS, "too many tiles in one group");
+        // tile weight = tensor-pipe cycles of one k16 step (what bounds the kernel once the operands are not re-fetched per
+        // tap): max(N / 2, 48) per MMA of N columns -- below N = 96 the shared-memory operand reads set the pace
         for (int mt = 0; mt < m_tiles; ++mt)
-            for (int j = 0; j < J.K; ++j) {
+            for (int j = 0; j < per_m; ++j) {
                 GgTile& Tl = P.tile[n_tiles];
-                Tl.job = (unsigned char)q; Tl.m_tile = (unsigned char)mt; Tl.tap = (unsigned char)j;
-                w_tile[n_tiles] = 2 + ((D.ones && j == 0) ? GG_ONES_BLK + 1 : D.n_blk);    // boxes staged per k-step
+                Tl.job = (unsigned char)q; Tl.m_tile = (unsigned char)mt;
+                if (at) {
+                    Tl.tap = (unsigned char)GG_ALL_TAPS; Tl.cblk = (unsigned char)j;
+                    w_tile[n_tiles] = (long long)J.K * 48 + ((D.ones && j == 0) ? 16 : 0);
+                } else {
+                    Tl.tap = (unsigned char)j; Tl.cblk = 0;
+                    const int N = ((D.ones && j == 0) ? GG_ONES_BLK + 1 : D.n_blk) * 64;
+                    w_tile[n_tiles] = max(N / 2, 48);
+                }
                 ++n_tiles;
             }
     }
@@ -344,7 +432,11 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     long long U = 0;
     for (int i = 0; i < n_tiles; ++i) U += w_tile[i] * S;
     int G = (int)min((long long)min(sm_count(), WGG_MAX_CTAS), (long long)n_tiles * S);
-    if (max_ctas > 0 && G > max_ctas) G = max_ctas;     // overlapped launch: leave the other SMs to the data-gradient chain
+    // Overlapped launch (side stream): leave the other SMs to the data-gradient chain -- and take them as whole TPCs
+    // (clusters of 2): the fused layer kernels launch as CTA pairs, which need both SMs of a TPC free.
+    const bool paired = max_ctas > 0;
+    if (paired && G > max_ctas) G = max_ctas;
+    if (paired && G > 1) G &= ~1;
     int n_seg = 0, slot = 0, c = 0;
     long long pos = 0;
     for (int i = 0; i < n_tiles; ++i) {
@@ -373,6 +465,18 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     GTK_CUDA(cudaFuncSetAttribute(wgrad_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     {
         ProfScope prof("wgrad_group", st);
+        if (paired && G > 1) {
+            cudaLaunchConfig_t cfg;
+            memset(&cfg, 0, sizeof(cfg));
+            cfg.gridDim = dim3(G); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+            cudaLaunchAttribute attr[2];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+            cfg.attrs = attr; cfg.numAttrs = 2;
+            GTK_CUDA(cudaLaunchKernelEx(&cfg, wgrad_group_kernel, P));
+        } else
         GTK_CUDA(launch_pdl(wgrad_group_kernel, dim3(G), dim3(NTHREADS), smem, st, P));
         int rc = check_launch("wgrad_group");
         if (rc) return rc;

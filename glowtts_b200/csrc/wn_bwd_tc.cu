@@ -106,32 +106,39 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
     cluster_sync_all();                                        // the peer's barriers exist before anything is multicast
     tc_fence_after();
     // PDL: the producer thread requests the res_skip weight tiles of its first stages before pdl_wait() (see wn_tc.cu)
-    const bool is_producer = (warp == 0 && lane == 0);
+    const bool is_producer = (warp == 0);
     if (!is_producer) pdl_wait();
     const uint32_t tmem = ctl->tmem_base;
     const uint32_t idesc = umma_idesc_bf16(BT, H);
     WB_TRACE(1);
 
-    // ---------------------------------------------------------------- TMA producer
-    if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tmDrs);
-        tma_prefetch_desc(&tmWrs);
-        tma_prefetch_desc(&tmWin);
+    // ---------------------------------------------------------------- TMA producer.  Whole warp in the uniform loops, ONE
+    // ELECTED lane issues (TMA and MMA descriptors stay in uniform registers; see wn_tc.cu / profiles/mma_issue_r02.txt)
+    if (warp == 0) {
         const int n_pre = min(n_sa, nka);
-        for (int kc = 0; kc < n_pre; ++kc) {
-            mbar_arrive_expect_tx(&ctl->full[kc], (uint32_t)sa_bytes);
-            tma_load_2d(ring + (size_t)kc * sa_bytes + A_BYTES, &tmWrs, &ctl->full[kc], kc * KC, 0);
+        if (elect_one()) {
+            tma_prefetch_desc(&tmDrs);
+            tma_prefetch_desc(&tmWrs);
+            tma_prefetch_desc(&tmWin);
+            for (int kc = 0; kc < n_pre; ++kc) {
+                mbar_arrive_expect_tx(&ctl->full[kc], (uint32_t)sa_bytes);
+                tma_load_2d(ring + (size_t)kc * sa_bytes + A_BYTES, &tmWrs, &ctl->full[kc], kc * KC, 0);
+            }
         }
+        __syncwarp();
         pdl_wait();
         for (int kc = 0; kc < nka; ++kc) {
             const int s = kc % n_sa, use = kc / n_sa;
             if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
             unsigned char* sa = ring + (size_t)s * sa_bytes;
-            if (kc >= n_pre) {
-                mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)sa_bytes);
-                tma_load_2d(sa + A_BYTES, &tmWrs, &ctl->full[s], kc * KC, 0);
+            if (elect_one()) {
+                if (kc >= n_pre) {
+                    mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)sa_bytes);
+                    tma_load_2d(sa + A_BYTES, &tmWrs, &ctl->full[s], kc * KC, 0);
+                }
+                tma_load_3d(sa, &tmDrs, &ctl->full[s], kc * KC, t0 - halo, b);
             }
-            tma_load_3d(sa, &tmDrs, &ctl->full[s], kc * KC, t0 - halo, b);
+            __syncwarp();
         }
         // The ring is re-cut into weight-only stages for GEMM b.  Each CTA of the pair fetches half of the rows of every
         // weight tile and the TMA multicasts them into both shared memories; a stage may be written once BOTH CTAs have
@@ -141,25 +148,34 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
         for (int it = 0; it < min(n_sb, n_b); ++it) {
             mbar_wait(&ctl->empty_b[it], 0);
             const int j = it / nkb, kc = it % nkb;
-            mbar_arrive_expect_tx(&ctl->full_b[it], (uint32_t)sb_bytes);
-            tma_load_3d_multicast(ring + (size_t)it * sb_bytes + (size_t)cta_rank * (H / WB_CL) * 128, &tmWin, &ctl->full_b[it],
-                                  kc * KC, (int)cta_rank * (H / WB_CL), j, cl_mask);
+            if (elect_one()) {
+                mbar_arrive_expect_tx(&ctl->full_b[it], (uint32_t)sb_bytes);
+                tma_load_3d_multicast(ring + (size_t)it * sb_bytes + (size_t)cta_rank * (H / WB_CL) * 128, &tmWin,
+                                      &ctl->full_b[it], kc * KC, (int)cta_rank * (H / WB_CL), j, cl_mask);
+            }
+            __syncwarp();
         }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1) {
         // ---------------------------------------------------------------- GEMM a
+        const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
         for (int kc = 0; kc < nka; ++kc) {
             const int s = kc % n_sa, use = kc / n_sa;
             mbar_wait(&ctl->full[s], use & 1);
             tc_fence_after();
             const uint32_t sa = smem_u32(ring + (size_t)s * sa_bytes);
-            const uint64_t adesc = umma_desc_kmajor_sw128(sa), bdesc = umma_desc_kmajor_sw128(sa + A_BYTES);
+            if (elect_one()) {
+                const uint64_t adesc = umma_desc_kmajor_sw128(sa), bdesc = umma_desc_kmajor_sw128(sa + A_BYTES);
 #pragma unroll
-            for (int k = 0; k < KC / 16; ++k)                  // two accumulators take alternate k16 steps (conv_tc.cu)
-                umma_bf16(tmem + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, kc != 0 || k >= 2);
-            umma_commit(&ctl->empty[s]);
+                for (int k = 0; k < KC / 16; ++k)              // two accumulators take alternate k16 steps (conv_tc.cu)
+                    umma_bf16(tm + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, kc != 0 || k >= 2);
+                umma_commit(&ctl->empty[s]);
+            }
+            __syncwarp();
         }
-        umma_commit(&ctl->acc_full);
-        for (int s = 0; s < n_sb; ++s) umma_commit_multicast(&ctl->empty_b[s], cl_mask);   // ring free on this CTA
+        if (elect_one()) {
+            umma_commit(&ctl->acc_full);
+            for (int s = 0; s < n_sb; ++s) umma_commit_multicast(&ctl->empty_b[s], cl_mask);   // ring free on this CTA
+        }
     }
     __syncwarp();
 
@@ -220,7 +236,7 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
     }
 
     // ---------------------------------------------------------------- GEMM b: taps = row-shifted views of the smem tile
-    if (warp == 0 && lane == 0) {
+    if (warp == 0) {
         long long w_prod = 0;
         const long long p0 = WB_CLK();
         for (int it = n_sb; it < n_b; ++it) {
@@ -229,21 +245,26 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
             mbar_wait(&ctl->empty_b[s], use & 1);
             w_prod += WB_CLK() - c0;
             const int j = it / nkb, kc = it % nkb;
-            mbar_arrive_expect_tx(&ctl->full_b[s], (uint32_t)sb_bytes);
-            tma_load_3d_multicast(ring + (size_t)s * sb_bytes + (size_t)cta_rank * (H / WB_CL) * 128, &tmWin, &ctl->full_b[s],
-                                  kc * KC, (int)cta_rank * (H / WB_CL), j, cl_mask);
+            if (elect_one()) {
+                mbar_arrive_expect_tx(&ctl->full_b[s], (uint32_t)sb_bytes);
+                tma_load_3d_multicast(ring + (size_t)s * sb_bytes + (size_t)cta_rank * (H / WB_CL) * 128, &tmWin,
+                                      &ctl->full_b[s], kc * KC, (int)cta_rank * (H / WB_CL), j, cl_mask);
+            }
+            __syncwarp();
         }
         WB_WAIT_STORE(2, w_prod);
         WB_WAIT_STORE(3, WB_CLK() - p0);
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1) {
+        const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
         mbar_wait(&ctl->acts_ready, 0);
         tc_fence_after();
         // d(xin) of the OWNED frames [t0, t0 + tile_out) for the weight-gradient launch: rows halo.. of the tile (a TMA
         // store must not start at a negative coordinate; the swizzle is address-based, so a row-offset source is fine)
-        if (t0 < p.T) {
+        if (lane == 0 && t0 < p.T) {
             for (int kc = 0; kc < nkb; ++kc) tma_store_3d(&tmDxin, smem + (size_t)kc * A_BYTES + halo * 128, kc * KC, t0, b);
             tma_store_commit();
         }
+        __syncwarp();
         long long w_mma = 0;
         const long long m0 = WB_CLK();
         for (int it = 0; it < n_b; ++it) {
@@ -253,14 +274,19 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
             w_mma += WB_CLK() - c0;
             tc_fence_after();
             const int j = it / nkb, kc = it % nkb;
-            const uint64_t adesc = umma_desc_kmajor_sw128(smem_u32(smem + (size_t)kc * A_BYTES) + (uint32_t)(j * p.dil) * 128u);
-            const uint64_t bdesc = umma_desc_kmajor_sw128(smem_u32(ring + (size_t)s * sb_bytes));
+            const uint32_t a_addr = smem_u32(smem + (size_t)kc * A_BYTES) + (uint32_t)(j * p.dil) * 128u;
+            const uint32_t b_addr = smem_u32(ring + (size_t)s * sb_bytes);
+            if (elect_one()) {
+                const uint64_t adesc = umma_desc_kmajor_sw128(a_addr), bdesc = umma_desc_kmajor_sw128(b_addr);
 #pragma unroll
-            for (int k = 0; k < KC / 16; ++k)
-                umma_bf16(tmem + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, it != 0 || k >= 2);
-            umma_commit_multicast(&ctl->empty_b[s], cl_mask);
+                for (int k = 0; k < KC / 16; ++k)
+                    umma_bf16(tm + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, it != 0 || k >= 2);
+                umma_commit_multicast(&ctl->empty_b[s], cl_mask);
+            }
+            __syncwarp();
         }
-        umma_commit(&ctl->acc_full);
+        if (elect_one()) umma_commit(&ctl->acc_full);
+        __syncwarp();
         WB_WAIT_STORE(0, w_mma);
         WB_WAIT_STORE(1, WB_CLK() - m0);
     }

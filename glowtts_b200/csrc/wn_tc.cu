@@ -102,25 +102,34 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     // PDL: everything the previous kernel of the stream wrote (h, skip) may be touched only after pdl_wait().  The TMA
     // producer thread first requests the WEIGHT tiles of its first stages (packed long before the previous kernel
     // started), so they are in flight while the previous kernel drains, and waits afterwards.
-    const bool is_producer = (warp == 0 && lane == 0);
+    const bool is_producer = (warp == 0);
     if (!is_producer) pdl_wait();
     const uint32_t tmem = ctl->tmem_base;
     const uint32_t idesc = umma_idesc_bf16(BT, H);
+    const int n_lo = min(H2, 256), n_hi = H2 - n_lo;          // GEMM-1 column split of a k16 step (see the MMA warp)
+    const uint32_t idesc_lo = umma_idesc_bf16(BT, n_lo), idesc_hi = umma_idesc_bf16(BT, n_hi > 0 ? n_hi : 16);
     WN_TRACE(1);
 
-    // ---------------------------------------------------------------- roles during GEMM 1 (one lane each)
-    if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tmH);
-        tma_prefetch_desc(&tmWin);
-        tma_prefetch_desc(&tmWrs);
+    // ---------------------------------------------------------------- roles during GEMM 1.  The whole warp walks the
+    // (warp-uniform) loops and ONE ELECTED lane issues the TMA / MMA instructions: their descriptors then live in uniform
+    // registers.  Under `if (lane == 0)` the compiler cannot prove uniformity and wraps every tcgen05.mma / TMA in an R2UR
+    // waterfall loop, ~15 instructions and > 100 cycles each -- more than the 96-cycle tensor-pipe time of one
+    // 128 x 192 x 16 MMA, i.e. GEMM 1 was bound by instruction issue (profiles/mma_issue_r02.txt).
+    if (warp == 0) {
         const int n_pre = min(WN_STAGES, n1);
-        for (int it = 0; it < n_pre; ++it) {             // weights of the first stages: independent of the previous kernel
-            unsigned char* sb = smem + (size_t)it * stage_bytes + A_BYTES;
-            const int j = it / n_kh, kc = it % n_kh;
-            mbar_arrive_expect_tx(&ctl->full[it], (uint32_t)(A_BYTES + H2 * KC * 2));
-            tma_load_3d(sb, &tmWin, &ctl->full[it], kc * KC, 0, j);
-            tma_load_3d(sb + (size_t)H * KC * 2, &tmWin, &ctl->full[it], kc * KC, H, j);
+        if (elect_one()) {
+            tma_prefetch_desc(&tmH);
+            tma_prefetch_desc(&tmWin);
+            tma_prefetch_desc(&tmWrs);
+            for (int it = 0; it < n_pre; ++it) {         // weights of the first stages: independent of the previous kernel
+                unsigned char* sb = smem + (size_t)it * stage_bytes + A_BYTES;
+                const int j = it / n_kh, kc = it % n_kh;
+                mbar_arrive_expect_tx(&ctl->full[it], (uint32_t)(A_BYTES + H2 * KC * 2));
+                tma_load_3d(sb, &tmWin, &ctl->full[it], kc * KC, 0, j);
+                tma_load_3d(sb + (size_t)H * KC * 2, &tmWin, &ctl->full[it], kc * KC, H, j);
+            }
         }
+        __syncwarp();
         pdl_wait();
         long long w_prod = 0;
         const long long p0 = WN_CLK();
@@ -132,22 +141,26 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
             w_prod += WN_CLK() - c0;
             unsigned char* sa = smem + (size_t)s * stage_bytes;
             unsigned char* sb = sa + A_BYTES;
-            if (it < n1) {
-                const int j = it / n_kh, kc = it % n_kh;
-                if (it >= n_pre) {
-                    mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(A_BYTES + H2 * KC * 2));
-                    tma_load_3d(sb, &tmWin, &ctl->full[s], kc * KC, 0, j);
-                    tma_load_3d(sb + (size_t)H * KC * 2, &tmWin, &ctl->full[s], kc * KC, H, j);
+            if (elect_one()) {
+                if (it < n1) {
+                    const int j = it / n_kh, kc = it % n_kh;
+                    if (it >= n_pre) {
+                        mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(A_BYTES + H2 * KC * 2));
+                        tma_load_3d(sb, &tmWin, &ctl->full[s], kc * KC, 0, j);
+                        tma_load_3d(sb + (size_t)H * KC * 2, &tmWin, &ctl->full[s], kc * KC, H, j);
+                    }
+                    tma_load_3d(sa, &tmH, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
+                } else {
+                    const int kc = it - n1;             // the A slot of this stage is written by epilogue 1
+                    mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(RS * KC * 2));
+                    tma_load_2d(sb, &tmWrs, &ctl->full[s], kc * KC, 0);
+                    if (RS > H) tma_load_2d(sb + (size_t)H * KC * 2, &tmWrs, &ctl->full[s], kc * KC, H);
                 }
-                tma_load_3d(sa, &tmH, &ctl->full[s], kc * KC, t0 + (j - p.taps / 2) * p.dil, b);
-            } else {
-                const int kc = it - n1;                 // the A slot of this stage is written by epilogue 1
-                mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(RS * KC * 2));
-                tma_load_2d(sb, &tmWrs, &ctl->full[s], kc * KC, 0);
-                if (RS > H) tma_load_2d(sb + (size_t)H * KC * 2, &tmWrs, &ctl->full[s], kc * KC, H);
             }
+            __syncwarp();
         }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1) {
+        const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
         long long w_mma = 0;
         const long long m0 = WN_CLK();
         for (int it = 0; it < n1; ++it) {
@@ -158,18 +171,24 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
             tc_fence_after();
             const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
             const uint32_t sb = sa + A_BYTES;
-            const uint64_t adesc = umma_desc_kmajor_sw128(sa);
+            if (elect_one()) {
+                // The 2H gate columns of a k16 step go out as one MMA of N = min(2H, 256) and, beyond 256, one of
+                // N = 2H - 256 (H = 192: 256 + 128), NOT as a tanh and a sigmoid MMA of N = H each.  Measured
+                // (profiles/mma_issue_r02.txt): an accumulator accepts its next MMA ~193 cycles after the previous one, so
+                // two N = 192 chains run at 127 cycles per MMA (254 per k16 step), while the 256 | 128 pair keeps the tensor
+                // pipe busy for 128 + 64 = 192 cycles per step -- exactly the accumulators' turn-around.
+                const uint64_t adesc = umma_desc_kmajor_sw128(sa), bdesc = umma_desc_kmajor_sw128(sb);
 #pragma unroll
-            for (int k = 0; k < KC / 16; ++k) {
-#pragma unroll
-                for (int ch = 0; ch < 2; ++ch) {
-                    const uint64_t bdesc = umma_desc_kmajor_sw128(sb + ch * H * KC * 2);
-                    umma_bf16(tmem + ch * H, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0);
+                for (int k = 0; k < KC / 16; ++k) {
+                    umma_bf16(tm, adesc + 2 * k, bdesc + 2 * k, idesc_lo, (it | k) != 0);
+                    if (n_hi) umma_bf16(tm + 256, adesc + 2 * k, bdesc + 2 * k + (256 * KC * 2 >> 4), idesc_hi, (it | k) != 0);
                 }
+                umma_commit(&ctl->empty[s]);
             }
-            umma_commit(&ctl->empty[s]);
+            __syncwarp();
         }
-        umma_commit(&ctl->acc_full);                     // GEMM 1 done -> epilogue 1 may read TMEM
+        if (elect_one()) umma_commit(&ctl->acc_full);    // GEMM 1 done -> epilogue 1 may read TMEM
+        __syncwarp();
         WN_WAIT_STORE(0, w_mma);
         WN_WAIT_STORE(1, WN_CLK() - m0);
     }
@@ -258,7 +277,8 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
     WN_TRACE(3);
 
     // ---- GEMM 2 (res_skip 1x1): issued by warp 1 once every thread has delivered its gate outputs
-    if (warp == 1 && lane == 0) {
+    if (warp == 1) {
+        const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
         mbar_wait(&ctl->acts_ready, 0);                  // acts are in the A slots, the xin columns are free again
         tc_fence_after();
         for (int it = n1; it < n_all; ++it) {
@@ -267,18 +287,21 @@ wn_layer_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
             tc_fence_after();
             const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
             const uint32_t sb = sa + A_BYTES;
-            const uint64_t adesc = umma_desc_kmajor_sw128(sa);
-            const int nch = RS > H ? 2 : 1;
+            if (elect_one()) {
+                const uint64_t adesc = umma_desc_kmajor_sw128(sa), bdesc = umma_desc_kmajor_sw128(sb);
+                const int r_lo = min(RS, 256), r_hi = RS - r_lo;       // same column split as GEMM 1
+                const uint32_t id_lo = umma_idesc_bf16(BT, r_lo), id_hi = umma_idesc_bf16(BT, r_hi > 0 ? r_hi : 16);
 #pragma unroll
-            for (int k = 0; k < KC / 16; ++k) {
-                for (int ch = 0; ch < nch; ++ch) {
-                    const uint64_t bdesc = umma_desc_kmajor_sw128(sb + ch * H * KC * 2);
-                    umma_bf16(tmem + ch * H, adesc + 2 * k, bdesc + 2 * k, idesc, (it != n1) || (k != 0));
+                for (int k = 0; k < KC / 16; ++k) {
+                    umma_bf16(tm, adesc + 2 * k, bdesc + 2 * k, id_lo, (it != n1) || (k != 0));
+                    if (r_hi) umma_bf16(tm + 256, adesc + 2 * k, bdesc + 2 * k + (256 * KC * 2 >> 4), id_hi, (it != n1) || (k != 0));
                 }
             }
+            __syncwarp();
         }
-        umma_commit(&ctl->acc_full);
-        if (p.acts_save) {                               // bf16 gate output for the res_skip weight gradient
+        if (elect_one()) umma_commit(&ctl->acc_full);
+        __syncwarp();
+        if (lane == 0 && p.acts_save) {                  // bf16 gate output for the res_skip weight gradient
             for (int kc = 0; kc < n_kh; ++kc)
                 tma_store_3d(&tmActs, smem + (size_t)((n1 + kc) % WN_STAGES) * stage_bytes, kc * KC, t0, b);
             tma_store_commit();

@@ -206,3 +206,41 @@ def test_prosody_dropout_training_step_graphed():
     # same seeds -> same dropout masks -> same trajectory (up to the summation order of the atomic reductions)
     assert np.allclose(losses[0], losses[1], rtol=1e-5), losses
     assert losses[0][-1] < losses[0][0], losses[0]
+
+
+def test_all_taps_weight_gradient_tiles_match_per_tap(tmp_path):
+    """GTK_WGRAD_ALL_TAPS=1 (wgrad_group.cu: every tap of a k > 1 conv inside one tile, row-shifted MN-major descriptors on
+    one staged X tile) gives the same parameter gradients as the default per-tap tiles.  The switch is read once per
+    process, so each mode runs in its own interpreter."""
+    import subprocess
+    import sys
+    script = r'''
+import sys, numpy as np, torch
+sys.path.insert(0, "tests")
+import helpers
+from glowtts_b200 import models, commons
+cfg = dict(in_channels=16, hidden_channels=192, kernel_size=5, dilation_rate=1, n_blocks=2, n_layers=2, n_split=4, n_sqz=2, gin_channels=0)
+dec = models.FlowSpecDecoder(16, 192, 5, 1, 2, 2, p_dropout=0.0, n_split=4, n_sqz=2, precision="bf16")
+dec.load_state_dict(helpers.make_state_dict(cfg, 91), strict=True)
+dec = dec.cuda()
+gen = torch.Generator().manual_seed(92)
+B, T = 3, 900
+lengths = torch.tensor([900, 640, 258])
+mask = (torch.arange(T)[None, :] < lengths[:, None]).float().unsqueeze(1).cuda()
+y = torch.randn(B, 16, T, generator=gen).cuda() * mask
+z, ld = dec(y, mask)
+commons.mle_loss(z, None, None, ld, mask).backward()
+np.savez(sys.argv[1], **{k: p.grad.cpu().numpy() for k, p in dec.named_parameters() if p.grad is not None})
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for mode in ("0", "1"):
+        out = str(tmp_path / f"g{mode}.npz")
+        env = dict(os.environ, GTK_WGRAD_ALL_TAPS=mode)
+        subprocess.run([sys.executable, "-c", script, out], check=True, cwd=root, env=env, timeout=600)
+        outs.append(np.load(out))
+    a, b = outs
+    assert set(a.files) == set(b.files) and len(a.files) > 20
+    for k in a.files:
+        ref = np.abs(a[k]).max()
+        assert np.abs(a[k] - b[k]).max() <= 2e-3 * ref + 1e-7, (k, float(np.abs(a[k] - b[k]).max()), float(ref))
