@@ -67,6 +67,38 @@ class ClockSampler:
         self.index = index
 
     def start(self):
+        # NVML from a polling thread (5 ms period: the timed region of a default run is ~0.1 s, too short for nvidia-smi's
+        # loop mode to deliver more than a sample or two); nvidia-smi -lms as the fallback
+        self.nvml_rows, self._stop = [], False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+                h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid if not uuid.startswith("GPU-") else uuid).encode())
+            except Exception:
+                h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            bits = {"hw_slowdown": pynvml.nvmlClocksThrottleReasonHwSlowdown,
+                    "hw_thermal_slowdown": pynvml.nvmlClocksThrottleReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": pynvml.nvmlClocksThrottleReasonSwThermalSlowdown,
+                    "sw_power_cap": pynvml.nvmlClocksThrottleReasonSwPowerCap}
+
+            def poll():
+                while not self._stop:
+                    try:
+                        sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                        rs = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                        self.nvml_rows.append((float(sm), float(mx), [n for n, b in bits.items() if rs & b]))
+                    except Exception:
+                        pass
+                    time.sleep(0.005)
+            self.thread = threading.Thread(target=poll, daemon=True)
+            self.thread.start()
+            self.proc = "nvml"
+            return
+        except Exception:
+            self.nvml_rows = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -83,6 +115,14 @@ class ClockSampler:
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        if self.proc == "nvml":
+            self._stop = True
+            self.thread.join(timeout=1)
+            sm = sorted(r[0] for r in self.nvml_rows)
+            reasons = sorted({n for r in self.nvml_rows for n in r[2]})
+            med = sm[len(sm) * 3 // 4] if sm else None
+            return {"sm_mhz": med, "sm_max_mhz": self.nvml_rows[0][1] if self.nvml_rows else None, "reasons": reasons,
+                    "samples": len(sm), "source": "nvml, 5 ms polling during the timed region"}
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
