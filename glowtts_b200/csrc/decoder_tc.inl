@@ -51,6 +51,7 @@ struct TcLayout {          // byte offsets in the workspace
     TcAct A;
     // backward temporaries
     size_t b_dZ, b_dM, b_dend, b_drs, b_dxin, b_lstride, b_dgate, b_dhf[2], b_dh0, b_wpart;   // b_drs / b_dxin: one per layer, b_lstride apart
+    int wpart_cap;                       // stream-K launches whose partial tiles fit b_wpart (deferred reduce)
     size_t b_pstride;                    // b_dend .. b_dh0 exist twice (block parity), b_pstride bytes apart: the weight
                                          // gradients of block k read them on the side stream while block k - 1 writes its own
 };
@@ -142,7 +143,9 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
         }
         L->b_dhf[0] = take((size_t)H * nqp * 4);
         L->b_dhf[1] = take((size_t)H * nqp * 4);
-        L->b_wpart = take(tc::wgrad_group_workspace_bytes());
+        // partial tiles of the stream-K weight-gradient launches of one backward call, reduced by ONE launch at its end
+        L->wpart_cap = min(tc::WGG_MAX_DEFER, D.NB * D.n_wn);
+        L->b_wpart = take(tc::wgrad_group_workspace_bytes() * (size_t)L->wpart_cap);
     }
     L->total = off;
 }
@@ -391,6 +394,8 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     SideStream* side = nullptr;
     GTK_TRY(side_stream(&side));
     bool side_used[2] = {false, false};
+    // main-stream weight gradients: all stream-K launches of this call share ONE reduce launch at its end
+    tc::WgradReduceBatch* rbatch = side ? nullptr : tc::wgrad_reduce_batch(wpart, L.wpart_cap);
 
     if (first) GTK_TRY(flow::squeeze_pack(dz, pl.off, pl.row_b, pl.mask_p, dZ, D.Cin, D.Tq * D.n, D.n, L.P, st));
     if (first)
@@ -439,7 +444,8 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 GTK_CUDA(cudaEventRecord(side->fork[par], st));
                 GTK_CUDA(cudaStreamWaitEvent(side->s, side->fork[par], 0));
             }
-            int rc = tc::wgrad_group_launch(jobs, n_jobs, B, T, wpart, pl.n_rows(), wst, (side && blk > blk_lo) ? wgrad_overlap_ctas() : 0);
+            int rc = tc::wgrad_group_launch(jobs, n_jobs, B, T, wpart, pl.n_rows(), wst, (side && blk > blk_lo) ? wgrad_overlap_ctas() : 0,
+                                            rbatch);
             n_jobs = 0; n_tiles = 0;
             return rc;
         };
@@ -556,6 +562,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         GTK_TRY(flow::mix_bwd(xin_blk, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, dM, dZ, G.an_logs, G.an_bias, G.ic_weight, B,
                               C, T, st, pl.n_rows()));
     }
+    GTK_TRY(tc::wgrad_group_reduce_flush(rbatch, st));      // weight norm + accumulation of every weight gradient of this call
     if (last) GTK_TRY(flow::unsqueeze_unpack(dZ, pl.off, dx, D.B, D.Cin, D.T, D.n, L.G, L.P, st));
     if (last)
         for (int w = 1; w < D.n_wn; ++w) {

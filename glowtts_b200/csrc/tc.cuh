@@ -150,11 +150,20 @@ struct WgradGroupJob {
     float* db;                 // += bias gradient [M], or null
     int M, Cin, K, dil;
 };
-size_t wgrad_group_workspace_bytes();
+size_t wgrad_group_workspace_bytes();               // partial tiles of ONE launch (worst case)
+// Deferred reduce: the stream-K launches of several coupling blocks write their partial tiles side by side into one
+// workspace of `capacity` launches x wgrad_group_workspace_bytes(), and ONE reduce launch finishes them all
+// (wgrad_group_reduce_flush) -- the per-block reduce is a latency-bound kernel of 2.7 waves, twelve of them cost 0.36 ms
+// per step.  The batch is host state owned by the caller for the duration of one backward call.
+struct WgradReduceBatch;
+WgradReduceBatch* wgrad_reduce_batch(float* part_ws, int capacity);     // thread-local object, reset
+int wgrad_group_reduce_flush(WgradReduceBatch* rb, cudaStream_t st);
 // n_rows: null, or (varlen packing, B == 1) device pointer to hdr[1] of the packing plan {0, n_rows}: rows in use
 // max_ctas > 0 caps the persistent grid (a launch that overlaps other kernels must not claim every SM)
+// defer: null = reduce right after the stream-K launch (part_ws = one launch's workspace); else append to the batch
 int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, const int* n_rows, cudaStream_t st,
-                       int max_ctas = 0);
+                       int max_ctas = 0, WgradReduceBatch* defer = nullptr);
+constexpr int WGG_MAX_DEFER = 14;                   // launches per reduce batch (kernel parameter space)
 // out[g * out_gstride + n] += sum of rows [seg[g], seg[g + 1]) (device-resident bounds) of frames in[.., n]
 // n_buf > 1: the same reduction over n_buf buffers buf_stride ELEMENTS apart, outputs out_bstride floats apart
 int colsum_frames_seg(const __nv_bfloat16* in, int ld, int n_cols, int groups, const int* seg, float* out, size_t out_gstride,

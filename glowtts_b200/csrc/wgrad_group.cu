@@ -272,15 +272,30 @@ struct GgRedParams {
 // The kernel is latency-bound (a few dependent L2 round trips per block), so every thread issues all the loads of its
 // (up to four) row elements -- partial slots four at a time, plus v -- before consuming any of them.
 constexpr int GG_RED_NT = 256;
-__global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __grid_constant__ GgRedParams p) {
+struct GgRedMulti {
+    int n;
+    int row_end[WGG_MAX_DEFER];                    // cumulative output rows of launch k
+    GgRedParams r[WGG_MAX_DEFER];
+};
+struct WgradReduceBatch {
+    GgRedMulti M;
+    float* part_ws;
+    int capacity;
+    size_t max_row;
+};
+__global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __grid_constant__ GgRedMulti pm) {
     extern __shared__ float row[];                 // [Cin * taps] reduced dW row, torch order (c, j)
     __shared__ float red[2][GG_RED_NT / 32];
     pdl_trigger();
     pdl_wait();                                    // the stream-K partial tiles are complete and visible
+    int k = 0;
+    while (k + 1 < pm.n && (int)blockIdx.x >= pm.row_end[k]) ++k;
+    const GgRedParams& p = pm.r[k];
+    const int brow = (int)blockIdx.x - (k ? pm.row_end[k - 1] : 0);
     int q = 0;
-    while (q + 1 < p.n_jobs && (int)blockIdx.x >= p.job[q + 1].row0) ++q;
+    while (q + 1 < p.n_jobs && brow >= p.job[q + 1].row0) ++q;
     const GgRedJob& J = p.job[q];
-    const int m = blockIdx.x - J.row0, Cin = J.Cin, taps = J.taps, R = Cin * taps;
+    const int m = brow - J.row0, Cin = J.Cin, taps = J.taps, R = Cin * taps;
     const int m_tile = m >> 7, r = m & 127;
     const float* __restrict__ vrow = J.v + (size_t)m * R;
     float* __restrict__ dvrow = J.dv + (size_t)m * R;
@@ -354,12 +369,32 @@ static int tmap_frames(CUtensorMap* out, const __nv_bfloat16* base, int ld, int 
     return make_tmap_bf16(out, base, 3, dims, strides, box, true);
 }
 
+WgradReduceBatch* wgrad_reduce_batch(float* part_ws, int capacity) {
+    static thread_local WgradReduceBatch rb;
+    rb.M.n = 0; rb.part_ws = part_ws; rb.capacity = max(1, min(capacity, WGG_MAX_DEFER)); rb.max_row = 0;
+    return &rb;
+}
+
+int wgrad_group_reduce_flush(WgradReduceBatch* rb, cudaStream_t st) {
+    if (!rb || rb->M.n == 0) return GTK_OK;
+    const int rows = rb->M.row_end[rb->M.n - 1];
+    ProfScope prof("wgrad_group_reduce", st);
+    GTK_CUDA(launch_pdl(wgrad_group_reduce_kernel, dim3(rows), dim3(GG_RED_NT), rb->max_row, st, rb->M));
+    rb->M.n = 0; rb->max_row = 0;
+    return check_launch("wgrad_group_reduce");
+}
+
 int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, float* part_ws, const int* n_rows, cudaStream_t st,
-                       int max_ctas) {
+                       int max_ctas, WgradReduceBatch* defer) {
     GTK_REQUIRE(jobs && n_jobs >= 1 && n_jobs <= WGG_MAX_JOBS && part_ws, "bad job list");
     if ((long long)B * T == 0) return GTK_OK;
     static thread_local GgParams P;                 // ~12 KB of kernel parameters, rebuilt per launch
-    static thread_local GgRedParams R;
+    static thread_local GgRedMulti R1;              // immediate mode: a batch of one
+    if (defer && defer->M.n == defer->capacity) { int rc = wgrad_group_reduce_flush(defer, st); if (rc) return rc; }
+    if (defer) part_ws = defer->part_ws + (size_t)defer->M.n * (wgrad_group_workspace_bytes() / sizeof(float));
+    GgRedMulti& RM = defer ? defer->M : R1;
+    if (!defer) RM.n = 0;
+    GgRedParams& R = RM.r[RM.n];
     memset(&P, 0, sizeof(P));
     memset(&R, 0, sizeof(R));
     GTK_REQUIRE(!n_rows || B == 1, "packed rows are one long sequence");
@@ -481,9 +516,13 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
         int rc = check_launch("wgrad_group");
         if (rc) return rc;
     }
-    {
+    RM.row_end[RM.n] = (RM.n ? RM.row_end[RM.n - 1] : 0) + rows;
+    ++RM.n;
+    if (defer) {
+        defer->max_row = max(defer->max_row, max_row);
+    } else {
         ProfScope prof("wgrad_group_reduce", st);
-        GTK_CUDA(launch_pdl(wgrad_group_reduce_kernel, dim3(rows), dim3(GG_RED_NT), (size_t)max_row, st, R));
+        GTK_CUDA(launch_pdl(wgrad_group_reduce_kernel, dim3(rows), dim3(GG_RED_NT), (size_t)max_row, st, RM));
         int rc = check_launch("wgrad_group_reduce");
         if (rc) return rc;
     }
