@@ -15,8 +15,9 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIBDIR = os.path.join(HERE, "lib")
-OBJDIR = os.path.join(HERE, "build")
+# GTK_LIBDIR / GTK_OBJDIR: build a variant (e.g. GTK_EXTRA_CFLAGS=-DGTK_INSTRUMENT) beside the product library
+LIBDIR = os.environ.get("GTK_LIBDIR") or os.path.join(HERE, "lib")
+OBJDIR = os.environ.get("GTK_OBJDIR") or os.path.join(HERE, "build")
 LIB = os.path.join(LIBDIR, "libglowtts_b200.so")
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

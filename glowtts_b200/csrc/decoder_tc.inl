@@ -41,7 +41,8 @@ static WnG wn_grads(const gtk_block_grads& P, int id) {
     return WnG{Q.in_g, Q.in_v, Q.in_b, Q.rs_g, Q.rs_v, Q.rs_b, Q.c1_g, Q.c1_v, Q.c1_b};
 }
 struct TcLayout {          // byte offsets in the workspace
-    size_t mask_sq, x_len, winv, icld, we, pack, X, act, hf[2], skipf, bwd, total;
+    size_t mask_sq, x_len, winv, icld, we, pack, X, act, hf[2], hx, skipf, bwd, total;
+    int stack, st_lead, st_halo, st_out;  // wn_stack.cu covers this WaveNet shape: window geometry
     size_t hdr, off, row_b, row_fr;      // varlen packing plan (pack.cu): {0, n_rows}, off[B+1], row_b[P], row_fr[P]; mask_sq = mask_p[P]
     size_t trk[TC_MAX_WN], dtrk[TC_MAX_WN];   // packed pitch / energy samples [P, n_sqz] of chain slots >= 1, and their gradients
     int G, P;                            // gap rows behind every utterance, packed row capacity (multiple of 128)
@@ -71,6 +72,9 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     L->P = (int)(((size_t)(D.B > 0 ? D.B : 1) * (D.Tq + L->G) + 127) / 128 * 128);
     const size_t nq = (size_t)L->P;
     const size_t nqp = nq;                                           // rows of the tile-private buffers (whole 128-frame tiles)
+    L->stack = tc::wn_stack_geometry(D.H, D.K, D.dr, D.L, pad64(D.C / 2) / 64, &L->st_lead, &L->st_halo, &L->st_out) ? 1 : 0;
+    // window-private fp32 masters of the stack kernel: overlapping 128-row windows, tile_out owned rows each
+    const size_t nqm = L->stack ? max(nqp, tc::wn_stack_master_rows(L->P, L->st_out)) : nqp;
     const int H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
     L->mask_sq = take(nq * 4);
     L->x_len = take((size_t)D.B * 4);
@@ -123,9 +127,10 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     A.total = a;
     L->n_act = train ? D.NB : 1;
     L->act = take(a * L->n_act);
-    L->hf[0] = take((size_t)H * nqp * 4);
+    L->hf[0] = take((size_t)H * nqm * 4);
     L->hf[1] = take((size_t)H * nqp * 4);
-    L->skipf = take((size_t)H * nqp * 4);
+    L->hx = (L->stack && D.n_wn > 2) ? take((size_t)H * nqp * 4) : 0;   // second fp32 exchange buffer between chained WaveNets
+    L->skipf = take((size_t)H * nqm * 4);
     L->bwd = off;
     if (train) {
         L->b_dZ = take((size_t)C * nq * 4);
@@ -228,6 +233,49 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
     float* hf[2] = {reinterpret_cast<float*>(ws + L.hf[0]), reinterpret_cast<float*>(ws + L.hf[1])};
     float* skipf = reinterpret_cast<float*>(ws + L.skipf);
     GTK_TRY(tc::frames_from_tmajor(xc, a0, B, C, T, 0, Ch, pad64(Ch), st, pl.n_rows()));
+    const bool stack = L.stack && tc::wn_stack_enabled();
+    if (stack) {
+        // start conv + every layer of a WaveNet in ONE launch per WaveNet (wn_stack.cu); a chained WaveNet reads the
+        // masked output of the one before it (bf16 operand + fp32 master through the frame-addressed exchange buffers)
+        float* hxb[2] = {hf[1], L.hx ? reinterpret_cast<float*>(ws + L.hx) : hf[1]};
+        for (int w = 0; w < D.n_wn; ++w) {
+            const WnW W = wn_weights(P, D.wn_id[w]);
+            tc::WnStackIo io;
+            memset(&io, 0, sizeof(io));
+            tc::WnStackParams p;
+            memset(&p, 0, sizeof(p));
+            p.B = B; p.T = T; p.H = H; p.taps = D.K; p.L = D.L;
+            p.save = save;
+            p.n_rows = pl.n_rows(); p.row_b = pl.row_b; p.row_fr = pl.row_fr; p.mask = mask;
+            p.drop_p = d->p_dropout;
+            p.hf = hf[0]; p.skipf = skipf;
+            if (w == 0) {
+                p.has_start = 1; p.n_ks = pad64(Ch) / 64; p.bias_start = P.start_b;
+                io.a0 = a0; io.ld_a0 = pad64(Ch); io.wstart = pk + Q.start;
+                p.cond_bstride = (size_t)2 * H * D.L;
+            } else {                                      // modules.WNP: cond_layer1 on the un-squeezed track, squeezed (modules.py:320-322)
+                io.hin = reinterpret_cast<const bf16*>(act + A.skip_bf[w - 1]);
+                p.h_in_f32 = hxb[(w - 1) & 1];
+                p.trk = reinterpret_cast<const float*>(ws + L.trk[w]);
+                p.cw_g = W.c1_g; p.cw_v = W.c1_v; p.cb = W.c1_b;
+                p.n_sqz = D.n; p.cs_div = 2 * H * D.L / D.n;
+            }
+            if (w + 1 < D.n_wn) p.h_out_f32_last = hxb[w & 1];
+            io.skip_out = reinterpret_cast<bf16*>(act + A.skip_bf[w]);
+            for (int i = 0; i < D.L; ++i) {
+                tc::WnStackLayer& ly = p.layer[i];
+                ly.bias_in = W.in_b[i]; ly.bias_rs = W.rs_b[i];
+                ly.cond = (w == 0 && P.cond) ? P.cond + (size_t)i * 2 * H : nullptr;
+                ly.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, D.wn_id[w] * D.L + i);
+                ly.ts_save = save ? reinterpret_cast<bf16*>(act + A.ts[LI(w, i)]) : nullptr;
+                ly.RS = (i < D.L - 1) ? 2 * H : H; ly.dil = ipow(D.dr, i); ly.cs_base = i * 2 * H;
+                io.win[i] = pk + Q.in[LI(w, i)]; io.wrs[i] = pk + Q.rs[LI(w, i)];
+                io.hsave[i] = (i == 0 && w > 0) ? nullptr : reinterpret_cast<bf16*>(act + A.h[LI(w, i)]);
+                io.acts[i] = reinterpret_cast<bf16*>(act + A.acts[LI(w, i)]);
+            }
+            GTK_TRY(tc::wn_stack_launch(io, p, st));
+        }
+    } else {
     {
         tc::ConvTcParams p;
         memset(&p, 0, sizeof(p));
@@ -273,6 +321,7 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
             cur ^= 1;
         }
     }
+    }   // layer-by-layer path
     {
         tc::ConvTcParams p;
         memset(&p, 0, sizeof(p));

@@ -101,6 +101,58 @@ struct WnLayerParams {
 int wn_layer_launch(const __nv_bfloat16* h_bf16, const __nv_bfloat16* win_p, const __nv_bfloat16* wrs_p, WnLayerParams p,
                     cudaStream_t st);
 
+// A whole WaveNet (start conv + every layer) in one launch (wn_stack.cu): windows of 128 rows with a recomputed halo.
+constexpr int WS_MAX_LAYERS = 4;
+constexpr int WS_STAGES = 3;
+struct WnStackLayer {
+    const float* bias_in;          // [2H]
+    const float* bias_rs;          // [RS]
+    const float* cond;             // this layer's slice of cond_layer(g): cond[b * cond_bstride + n], or null
+    DropSeed drop_seed;
+    __nv_bfloat16* ts_save;        // [rows, 2H] tanh | sigmoid, tile-private layout addressed by frame, or null
+    int RS, dil, cs_base;          // cs_base = layer * 2H (WNP conditioner channel offset)
+};
+struct WnStackParams {
+    int B, T, H, taps, L;
+    int lead, halo_tot, tile_out;  // filled by wn_stack_launch
+    int has_start, n_ks;           // 1: the window is start(x0) (n_ks k-chunks of padded input channels); 0: it is loaded from hin
+    int save;                      // training: h_l and the gate outputs of the owned rows are stored
+    const float* bias_start;       // [H]
+    size_t cond_bstride;
+    const int* n_rows;             // varlen packing (pack.cu)
+    const int* row_b;
+    const int* row_fr;
+    const float* mask;             // [B, T]
+    float drop_p;
+    const float* trk;              // WNP (see WnLayerParams)
+    const float* cw_g;
+    const float* cw_v;
+    const float* cb;
+    int n_sqz, cs_div;
+    float* hf;                     // window-private fp32 masters: wn_stack_master_rows(T, tile_out) * B rows of H floats
+    float* skipf;
+    const float* h_in_f32;         // !has_start: fp32 master of the input, tile-private layout addressed by frame
+    float* h_out_f32_last;         // masked WN output as fp32 (same layout) for a chained WaveNet, or null
+    WnStackLayer layer[WS_MAX_LAYERS];
+};
+struct WnStackMaps {
+    CUtensorMap a0, wstart, hin, skip_out, win[WS_MAX_LAYERS], wrs[WS_MAX_LAYERS], hsave[WS_MAX_LAYERS], acts[WS_MAX_LAYERS];
+};
+struct WnStackIo {                 // bf16 operands / outputs, frames [B, T, H] unless noted
+    const __nv_bfloat16* a0; int ld_a0;          // x0 frames [B, T, ld_a0] (has_start)
+    const __nv_bfloat16* wstart;                 // [H][n_ks * 64]
+    const __nv_bfloat16* hin;                    // window input (!has_start)
+    const __nv_bfloat16* win[WS_MAX_LAYERS];     // [taps][2H][H]
+    const __nv_bfloat16* wrs[WS_MAX_LAYERS];     // [RS][H]
+    __nv_bfloat16* hsave[WS_MAX_LAYERS];         // h_l (save)
+    __nv_bfloat16* acts[WS_MAX_LAYERS];          // gate output of layer l (save)
+    __nv_bfloat16* skip_out;                     // masked WN output
+};
+bool wn_stack_geometry(int H, int K, int dr, int L, int n_ks, int* lead, int* halo_tot, int* tile_out);
+bool wn_stack_enabled();                         // GTK_WN_STACK != 0
+size_t wn_stack_master_rows(int T, int tile_out);
+int wn_stack_launch(const WnStackIo& io, WnStackParams p, cudaStream_t st);
+
 // Backward of one WaveNet layer fused into one kernel (wn_bwd_tc.cu).
 struct WnBwdParams {
     int B, T, H, RS, taps, dil;
@@ -124,6 +176,8 @@ int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat1
 int wn_trace_read(unsigned long long* out, int n_ctas);
 int wn_wait_read(long long* out, int n_ctas);
 int wb_trace_read(unsigned long long* out, int n_ctas);
+int ws_trace_read(unsigned long long* out, int n_ctas);
+int ws_wait_read(long long* out, int n_ctas);
 int wb_wait_read(long long* out, int n_ctas);
 void conv_trace_select(int epi, int taps);
 int conv_trace_read(unsigned long long* out, int n_ctas);
@@ -397,6 +451,15 @@ struct RowIo {
     int r;             // row inside the tile (== TMEM lane)
     size_t frame;      // b * T + t (frame-major row)
 };
+// RowIo of frame f of utterance b for the tile-private tensors (addressed by frame, whatever the tiling of the kernel)
+__device__ __forceinline__ RowIo frame_io(int b, int f, int T) {
+    RowIo io;
+    io.tp = 1;
+    io.tile_id = b * ((T + BT - 1) / BT) + (f >> 7);
+    io.r = f & 127;
+    io.frame = (size_t)b * T + f;
+    return io;
+}
 __device__ __forceinline__ void row_load_f32x16(const float* base, int ld, int c0, const RowIo& io, float (&v)[16]) {
     const float4* s;
     size_t step;

@@ -57,15 +57,6 @@ __device__ long long g_wb_wait[WB_TRACE_CTAS * 4];
 #define WB_WAIT_STORE(i, v) do { } while (0)
 #endif
 
-// RowIo of frame f of utterance b for the tile-private tensors (addressed by frame, whatever the tiling of the kernel)
-__device__ __forceinline__ RowIo frame_io(int b, int f, int T) {
-    RowIo io;
-    io.tp = 1;
-    io.tile_id = b * ((T + BT - 1) / BT) + (f >> 7);
-    io.r = f & 127;
-    io.frame = (size_t)b * T + f;
-    return io;
-}
 
 __global__ void __launch_bounds__(EPI_NT, 1)
 wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_constant__ CUtensorMap tmWrs,

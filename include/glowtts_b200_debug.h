@@ -27,6 +27,11 @@ int gtk_debug_mas_trace(unsigned long long* out, int n_ctas);
 int gtk_debug_mas_wait(long long* out, int n_ctas);
 /* Debug: the fused layer-backward kernel: out[cta * 7 + {start, setup, GEMM a, epilogue a, GEMM b, epilogue b, end}]. */
 int gtk_debug_wb_trace(unsigned long long* out, int n_ctas);
+/* Debug: the whole-WaveNet kernel (wn_stack.cu): out[cta * 24 + {0 start, 1 prologue done, 2 start-conv epilogue done,
+ * per layer l: 3+4l GEMM 1 complete, 4+4l epilogue 1 done, 5+4l GEMM 2 complete, 6+4l epilogue 2 done, 3+4L end}];
+ * wait: out[cta * 8 + l] = SM cycles the MMA warp waited for weight stages in GEMM 1 of layer l, [4 + l] = that GEMM 1. */
+int gtk_debug_ws_trace(unsigned long long* out, int n_ctas);
+int gtk_debug_ws_wait(long long* out, int n_ctas);
 /* Debug: the same for the plain tcgen05 conv kernel.  Select which launches record (epilogue 0 plain / 1 gate-bwd /
  * 2 affine, and the tap count; -1 = none), run, then read out[cta * 5 + {start, setup done, accumulator complete,
  * epilogue math done, stores issued}] of the last selected launch.  Synchronises the device. */
