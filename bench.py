@@ -45,7 +45,8 @@ SEED = 1234  # configs/base.json:5
 NCU_TRAFFIC = {"mas configs[0]": 19.9e6,    # profiles/ncu_mas_cfg1_r01.csv: 19.89 MB read (value), 0 written (the 19.8 MB path stays in L2)
                "mas configs[4] on one GPU": 3.383e9,   # profiles/ncu_mas_cfg5_r01.csv: 1.728 GB read + 1.655 GB written (algorithmic 3.277 GB)
                "wn_layer_tc": 23.05e6,      # profiles/ncu_wn_layer_r01.txt: (16.89 + 0.82 MB, 27.50 + 0.89 MB) -> mean bytes / launch
-               "wn_bwd_layer_tc": 33.0e6}   # profiles/ncu_wn_bwd_layer_r01.txt: 32.78 MB read + 0.2 MB written per launch
+               "wn_bwd_layer_tc": 33.0e6,   # profiles/ncu_wn_bwd_layer_r01.txt: 32.78 MB read + 0.2 MB written per launch
+               "wn_stack_tc": None}
 
 
 def peaks():
@@ -449,12 +450,13 @@ def prosody_step(device, world, precision, graph, steps, warmup, ms_plain):
         H, K, L = CFG["hidden_channels"], CFG["kernel_size"], CFG["n_layers"]
         flop_layer = (2.0 * (2 * H * H * K) + 2.0 * H * H * (2 * (L - 1) + 1) / L) * (run.frames // CFG["n_sqz"])
         pk = peaks()
-        for tag in ("wn_layer_tc", "wn_bwd_layer_tc"):
+        # the whole-WaveNet forward kernel (wn_stack.cu) runs all L layers of one WaveNet per launch
+        for tag, fl in (("wn_stack_tc", flop_layer * L), ("wn_layer_tc", flop_layer), ("wn_bwd_layer_tc", flop_layer)):
             n_l, ms_l = prof.get(tag, (0, 0.0))
             if ms_l > 0:
                 out[tag] = {"launches_per_step": n_l / 2, "ms_per_launch": ms_l / n_l,
-                            "tflops": flop_layer * n_l / (ms_l * 1e-3) / 1e12,
-                            "frac_of_sustained_bf16_peak": flop_layer * n_l / (ms_l * 1e-3) / 1e12 / pk["tc_sustained"]}
+                            "tflops": fl * n_l / (ms_l * 1e-3) / 1e12,
+                            "frac_of_sustained_bf16_peak": fl * n_l / (ms_l * 1e-3) / 1e12 / pk["tc_sustained"]}
         fwd_flop_frame = CFG["n_blocks"] * (FLOP_PER_SQ_FRAME_FWD + 2 * 2 * (4 * (384 * 192 * 5) + 3 * (384 * 192) + 192 * 192))
         out["mflop_per_sq_frame_fwd"] = fwd_flop_frame / 1e6
         out["step_tflops"] = 3.0 * fwd_flop_frame * (run.frames // CFG["n_sqz"]) / (ms / steps * 1e-3) / 1e12
@@ -684,12 +686,15 @@ def main():
         # frames + G = 2 gap rows per utterance, rounded up to whole 128-row tiles
         sq_frames_padded = (run_rows + 127) // 128 * 128
         H, K, L = CFG["hidden_channels"], CFG["kernel_size"], CFG["n_layers"]
-        if "wn_layer_tc" in prof:
-            # dominant = the fused WaveNet-layer kernel that takes more of the step: forward (k=5 conv GEMM -> gate ->
-            # res/skip GEMM) or backward (res/skip data gradient -> gate backward -> k=5 data gradient): same GEMM shapes.
-            tag = max(("wn_layer_tc", "wn_bwd_layer_tc"), key=lambda t: prof.get(t, (0, 0.0))[1])
-            # per frame: 2H x (H K) conv + RS x H res/skip, RS = 2H except the last layer of a block (H); mean over layers
+        if "wn_layer_tc" in prof or "wn_stack_tc" in prof:
+            # dominant = the fused WaveNet kernel that takes more of the step: forward (k=5 conv GEMM -> gate -> res/skip
+            # GEMM; wn_stack.cu runs the start conv and all L layers of a WaveNet in one launch, wn_tc.cu one layer) or
+            # backward (res/skip data gradient -> gate backward -> k=5 data gradient, one layer per launch): same GEMM shapes.
+            tag = max(("wn_stack_tc", "wn_layer_tc", "wn_bwd_layer_tc"), key=lambda t: prof.get(t, (0, 0.0))[1])
+            # per frame and layer: 2H x (H K) conv + RS x H res/skip, RS = 2H except the last layer of a block (H); mean over layers
             flop_per_frame = 2.0 * (2 * H * H * K) + 2.0 * H * H * (2 * (L - 1) + 1) / L
+            if tag == "wn_stack_tc":                        # L layers + the start 1x1 conv (in_channels * n_sqz / 2 -> H)
+                flop_per_frame = flop_per_frame * L + 2.0 * H * (CFG["in_channels"] * CFG["n_sqz"] // 2)
         else:
             tag = "conv_f32_kN"
             flop_per_frame = 2.0 * (2 * H * H * K)

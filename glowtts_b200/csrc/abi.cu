@@ -310,6 +310,7 @@ int gtk_debug_wb_wait(long long* out, int n_ctas) { return tc::wb_wait_read(out,
 int gtk_debug_wb_trace(unsigned long long* out, int n_ctas) { return tc::wb_trace_read(out, n_ctas); }
 int gtk_debug_ws_trace(unsigned long long* out, int n_ctas) { return tc::ws_trace_read(out, n_ctas); }
 int gtk_debug_ws_wait(long long* out, int n_ctas) { return tc::ws_wait_read(out, n_ctas); }
+int gtk_debug_gg_wait(long long* out, int n_ctas) { return tc::gg_wait_read(out, n_ctas); }
 int gtk_debug_conv_trace_select(int epilogue, int taps) { tc::conv_trace_select(epilogue, taps); return GTK_OK; }
 int gtk_debug_conv_trace(unsigned long long* out, int n_ctas) { return tc::conv_trace_read(out, n_ctas); }
 int gtk_debug_conv_wait(long long* out, int n_ctas) { return tc::conv_wait_read(out, n_ctas); }

@@ -234,6 +234,7 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
     float* skipf = reinterpret_cast<float*>(ws + L.skipf);
     GTK_TRY(tc::frames_from_tmajor(xc, a0, B, C, T, 0, Ch, pad64(Ch), st, pl.n_rows()));
     const bool stack = L.stack && tc::wn_stack_enabled();
+    const bool end_in_stack = stack && tc::wn_stack_end_ok(H, C) && !(getenv("GTK_WN_STACK_END") && getenv("GTK_WN_STACK_END")[0] == '0');
     if (stack) {
         // start conv + every layer of a WaveNet in ONE launch per WaveNet (wn_stack.cu); a chained WaveNet reads the
         // masked output of the one before it (bf16 operand + fp32 master through the frame-addressed exchange buffers)
@@ -261,6 +262,12 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
                 p.n_sqz = D.n; p.cs_div = 2 * H * D.L / D.n;
             }
             if (w + 1 < D.n_wn) p.h_out_f32_last = hxb[w & 1];
+            else if (end_in_stack) {                      // `end` + affine coupling on the resident WN output
+                p.has_end = 1; p.C_end = C; p.bias_end = P.end_b; io.wend = pk + Q.end;
+                p.aff_x = xc; p.aff_z = zout; p.aff_logdet = reverse ? nullptr : logdet;
+                p.aff_logs_save = save ? reinterpret_cast<float*>(act + A.logs) : nullptr;
+                p.aff_reverse = reverse; p.aff_sigmoid_scale = d->sigmoid_scale;
+            }
             io.skip_out = reinterpret_cast<bf16*>(act + A.skip_bf[w]);
             for (int i = 0; i < D.L; ++i) {
                 tc::WnStackLayer& ly = p.layer[i];
@@ -322,7 +329,7 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
         }
     }
     }   // layer-by-layer path
-    {
+    if (!end_in_stack) {
         tc::ConvTcParams p;
         memset(&p, 0, sizeof(p));
         p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = H / 64; p.N = C;

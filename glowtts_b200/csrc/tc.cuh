@@ -133,10 +133,19 @@ struct WnStackParams {
     float* skipf;
     const float* h_in_f32;         // !has_start: fp32 master of the input, tile-private layout addressed by frame
     float* h_out_f32_last;         // masked WN output as fp32 (same layout) for a chained WaveNet, or null
+    // `end` 1x1 conv + affine coupling (attentions.py:170-183) on the resident WN output (last WaveNet of a block); see
+    // ConvTcParams EPI_AFFINE for the meaning of the aff_* fields.  has_end: the bf16 WN output is stored only when save
+    int has_end, C_end;            // C_end = in_channels * n_sqz (output channels of `end`, a multiple of 32, <= 256)
+    const float* bias_end;         // [C_end]
+    const float* aff_x;
+    float* aff_z;
+    float* aff_logdet;
+    float* aff_logs_save;
+    int aff_reverse, aff_sigmoid_scale;
     WnStackLayer layer[WS_MAX_LAYERS];
 };
 struct WnStackMaps {
-    CUtensorMap a0, wstart, hin, skip_out, win[WS_MAX_LAYERS], wrs[WS_MAX_LAYERS], hsave[WS_MAX_LAYERS], acts[WS_MAX_LAYERS];
+    CUtensorMap a0, wstart, hin, skip_out, wend, win[WS_MAX_LAYERS], wrs[WS_MAX_LAYERS], hsave[WS_MAX_LAYERS], acts[WS_MAX_LAYERS];
 };
 struct WnStackIo {                 // bf16 operands / outputs, frames [B, T, H] unless noted
     const __nv_bfloat16* a0; int ld_a0;          // x0 frames [B, T, ld_a0] (has_start)
@@ -147,9 +156,11 @@ struct WnStackIo {                 // bf16 operands / outputs, frames [B, T, H] 
     __nv_bfloat16* hsave[WS_MAX_LAYERS];         // h_l (save)
     __nv_bfloat16* acts[WS_MAX_LAYERS];          // gate output of layer l (save)
     __nv_bfloat16* skip_out;                     // masked WN output
+    const __nv_bfloat16* wend;                   // [C_end][H] (has_end)
 };
 bool wn_stack_geometry(int H, int K, int dr, int L, int n_ks, int* lead, int* halo_tot, int* tile_out);
 bool wn_stack_enabled();                         // GTK_WN_STACK != 0
+bool wn_stack_end_ok(int H, int C_end);
 size_t wn_stack_master_rows(int T, int tile_out);
 int wn_stack_launch(const WnStackIo& io, WnStackParams p, cudaStream_t st);
 
@@ -178,6 +189,7 @@ int wn_wait_read(long long* out, int n_ctas);
 int wb_trace_read(unsigned long long* out, int n_ctas);
 int ws_trace_read(unsigned long long* out, int n_ctas);
 int ws_wait_read(long long* out, int n_ctas);
+int gg_wait_read(long long* out, int n_ctas);
 int wb_wait_read(long long* out, int n_ctas);
 void conv_trace_select(int epi, int taps);
 int conv_trace_read(unsigned long long* out, int n_ctas);

@@ -34,7 +34,9 @@ namespace tc {
 constexpr int GG_TK = 64;                        // frames per k-step
 constexpr int GG_BOX = GG_TK * 128;              // bytes of one {64 ch, 64 frames} box
 constexpr int GG_STAGES = 4;
-constexpr int GG_STAGE_BYTES = 6 * GG_BOX;       // 2 dY boxes (128 rows of M) + up to 4 X boxes (N <= 256)
+constexpr int GG_PAIR_ROWS = 8;                  // extra X rows a stage can hold: a tap PAIR shares one staged X tile when dil <= 8
+constexpr int GG_XSTRIDE = (GG_TK + GG_PAIR_ROWS) * 128;   // bytes between the 64-column X blocks of a stage (9 swizzle atoms)
+constexpr int GG_STAGE_BYTES = 2 * GG_BOX + 4 * GG_XSTRIDE;   // 2 dY boxes (128 rows of M) + up to 4 X blocks (N <= 256)
 constexpr int GG_ONES_BLK = 3;                   // X block that holds the ones column (never written by TMA)
 constexpr int GG_SLOT_COLS = 512;                // one partial tile: 128 rows x up to 512 accumulator columns
 constexpr int GG_SLOT_FLOATS = 128 * GG_SLOT_COLS;
@@ -45,7 +47,11 @@ struct GgJobDev {
     int taps, dil, n_blk, ones;                  // n_blk = real 64-column blocks of X; ones: bias gradient wanted
     int halo;                                    // (taps / 2) * dil: rows staged either side of a k-step (all-taps tiles)
 };
-struct GgTile { unsigned char job, m_tile, tap, cblk; };   // tap == GG_ALL_TAPS: every tap, X columns [64 cblk, 64 cblk + 64)
+// tap == GG_ALL_TAPS: every tap, X columns [64 cblk, 64 cblk + 64); otherwise taps [tap, tap + cblk] (cblk = 0 or 1) with all
+// X columns: a PAIR of taps shares the dY tile and ONE staged X tile of 64 + dil rows (tap + 1 is a row-shifted MN-major
+// descriptor on it) and owns one 256-column accumulator per tap -- the same two independent MMA chains as a single-tap
+// tile (which alternates its k16 steps between the two accumulators), for half the L2 -> SM operand traffic per MMA
+struct GgTile { unsigned char job, m_tile, tap, cblk; };
 struct GgSeg { unsigned short tile, s_lo, s_hi, slot; };
 struct GgCta { unsigned short seg0, nseg; };
 
@@ -58,7 +64,8 @@ struct GgParams {
     GgSeg seg[WGG_MAX_SEGS];
     GgCta cta[WGG_MAX_CTAS];
     CUtensorMap tmY[WGG_MAX_JOBS], tmX[WGG_MAX_JOBS];
-    CUtensorMap tmXh[WGG_MAX_JOBS];              // X with a {64 columns, 64 + 2 halo rows} box (all-taps tiles)
+    CUtensorMap tmXh[WGG_MAX_JOBS];              // X with a {64 columns, 64 + 2 halo rows} box (all-taps tiles),
+                                                 // or {64 columns, 64 + dil rows} (tap pairs)
 };
 
 struct GgCtl {
@@ -66,12 +73,30 @@ struct GgCtl {
     uint32_t tmem_base;
 };
 
+// Instrumented builds (-DGTK_INSTRUMENT): SM cycles per CTA of the last launch: [0] MMA warp waiting for operand stages,
+// [1] waiting for the drain of the previous segment, [2] MMA warp total, [3] k-steps, [4] segments, [5] kernel entry ->
+// MMA warp start (pdl wait + setup), [6] producer waiting for free stages, [7] drain warps total drain cycles (warp 4)
+#ifdef GTK_INSTRUMENT
+__device__ long long g_gg_wait[WGG_MAX_CTAS * 8];
+#define GG_CLK() clock64()
+#define GG_STORE(i, v) do { g_gg_wait[blockIdx.x * 8 + (i)] = (v); } while (0)
+int gg_wait_read(long long* out, int n_ctas) {
+    GTK_REQUIRE(out && n_ctas >= 0 && n_ctas <= WGG_MAX_CTAS, "n_ctas");
+    GTK_CUDA(cudaMemcpyFromSymbol(out, g_gg_wait, size_t(n_ctas) * 8 * sizeof(long long)));
+    return GTK_OK;
+}
+#else
+#define GG_CLK() 0ll
+#define GG_STORE(i, v) do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_constant__ GgParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     GgCtl* ctl = reinterpret_cast<GgCtl*>(smem + (size_t)GG_STAGES * GG_STAGE_BYTES);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const GgCta me = p.cta[blockIdx.x];
+    const long long k_t0 = GG_CLK();
     pdl_trigger();
     // The host cut every tile's k-steps [0, S_max) into contiguous shares.  With packed rows only the first S_val steps
     // hold data: every segment boundary is rescaled by S_val / S_max (monotone, so the segments still tile [0, S_val)
@@ -91,7 +116,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
         const int s = i / (GG_TK * 8), r = (i / 8) % GG_TK, ch = i % 8;
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
         if (ch == (r & 7)) v.x = 0x3F80u;        // bf16 1.0 in the low half-word = channel 0
-        *reinterpret_cast<uint4*>(smem + (size_t)s * GG_STAGE_BYTES + (2 + GG_ONES_BLK) * GG_BOX + r * 128 + ch * 16) = v;
+        *reinterpret_cast<uint4*>(smem + (size_t)s * GG_STAGE_BYTES + 2 * GG_BOX + GG_ONES_BLK * GG_XSTRIDE + r * 128 + ch * 16) = v;
     }
     fence_proxy_async_smem();
     tc_fence_before();
@@ -103,6 +128,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
     if (warp == 0) {
         // TMA producer: whole warp in the uniform loops, one elected lane issues (see the MMA warp)
         int it = 0;
+        long long w_free = 0;
         for (int sg = 0; sg < me.nseg; ++sg) {
             const GgSeg S = p.seg[me.seg0 + sg];
             const GgTile Tl = p.tile[S.tile];
@@ -112,11 +138,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
             const int m0 = Tl.m_tile * 128;
             const bool all_taps = Tl.tap == GG_ALL_TAPS;
             const int shift = all_taps ? -J.halo : ((int)Tl.tap - J.taps / 2) * J.dil;
-            const uint32_t bytes = all_taps ? (uint32_t)(2 * GG_BOX + (GG_TK + 2 * J.halo) * 128) : (uint32_t)(2 + J.n_blk) * GG_BOX;
+            const bool pair = !all_taps && Tl.cblk != 0;
+            const uint32_t bytes = all_taps ? (uint32_t)(2 * GG_BOX + (GG_TK + 2 * J.halo) * 128)
+                                 : pair ? (uint32_t)(2 * GG_BOX + J.n_blk * (GG_TK + J.dil) * 128) : (uint32_t)(2 + J.n_blk) * GG_BOX;
+            const CUtensorMap* tmXs = pair ? &p.tmXh[Tl.job] : tmX;
             const int s_lo = GG_SCALE(S.s_lo), s_hi = GG_SCALE(S.s_hi);
             for (int step = s_lo; step < s_hi; ++step, ++it) {
                 const int s = it % GG_STAGES, use = it / GG_STAGES;
+                const long long c0 = GG_CLK();
                 if (use > 0) mbar_wait(&ctl->empty[s], (use - 1) & 1);
+                w_free += GG_CLK() - c0;
                 const int b = step / p.chunks_t, t0 = (step % p.chunks_t) * GG_TK;
                 unsigned char* sa = smem + (size_t)s * GG_STAGE_BYTES;
                 unsigned char* sb = sa + 2 * GG_BOX;
@@ -128,25 +159,31 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
                         tma_load_3d(sb, &p.tmXh[Tl.job], &ctl->full[s], Tl.cblk * GG_CB, t0 + shift, b);
                     } else {
                         for (int nb = 0; nb < J.n_blk; ++nb)
-                            tma_load_3d(sb + (size_t)nb * GG_BOX, tmX, &ctl->full[s], nb * 64, t0 + shift, b);
+                            tma_load_3d(sb + (size_t)nb * GG_XSTRIDE, tmXs, &ctl->full[s], nb * 64, t0 + shift, b);
                     }
                 }
                 __syncwarp();
             }
         }
+        GG_STORE(6, w_free);
     } else if (warp == 1) {
         // MMA issue.  The WHOLE warp walks the (warp-uniform) loops and one elected lane issues: the descriptors then live
         // in uniform registers.  Under `if (lane == 0)` the compiler cannot prove uniformity and wraps every tcgen05.mma in
         // an R2UR waterfall loop (~15 instructions, >100 cycles per MMA: profiles/mma_issue_r02.txt).
         const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
         int it = 0, ne = 0;                            // ne: non-empty segments so far (accumulator hand-shake parity)
+        long long w_full = 0, w_drain = 0;
+        const long long m_t0 = GG_CLK();
+        GG_STORE(5, m_t0 - k_t0);
         for (int sg = 0; sg < me.nseg; ++sg) {
             const GgSeg S = p.seg[me.seg0 + sg];
             const GgTile Tl = p.tile[S.tile];
             const GgJobDev J = p.job[Tl.job];
             const int s_lo = GG_SCALE(S.s_lo), s_hi = GG_SCALE(S.s_hi);
             if (s_hi <= s_lo) continue;
-            if (ne > 0) { mbar_wait(&ctl->acc_empty[0], (ne - 1) & 1); tc_fence_after(); }
+            { const long long c0 = GG_CLK();
+              if (ne > 0) { mbar_wait(&ctl->acc_empty[0], (ne - 1) & 1); tc_fence_after(); }
+              w_drain += GG_CLK() - c0; }
             if (Tl.tap == GG_ALL_TAPS) {
                 // one accumulator per tap (columns [64 j, 64 j + 64)): independent MMA chains by construction; the bias
                 // gradient (ones column) takes 16 more columns on the tile of X block 0
@@ -164,13 +201,38 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
                             const uint64_t adesc = umma_desc_mnmajor_sw128(sa + k * 2048, GG_BOX, 1024);
                             const bool acc = (step != s_lo) || k > 0;
                             for (int j = 0; j < J.taps; ++j) {
-                                const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + (uint32_t)(j * J.dil) * 128u + k * 2048, GG_BOX, 1024);
+                                const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + (uint32_t)(j * J.dil) * 128u + k * 2048, GG_XSTRIDE, 1024);
                                 umma_bf16(tm + j * GG_CB, adesc, bdesc, idesc_t, acc);
                             }
                             if (ones) {
-                                const uint64_t bdesc = umma_desc_mnmajor_sw128(sa + (2 + GG_ONES_BLK) * GG_BOX + k * 2048, GG_BOX, 1024);
+                                const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + GG_ONES_BLK * GG_XSTRIDE + k * 2048, GG_XSTRIDE, 1024);
                                 umma_bf16(tm + J.taps * GG_CB, adesc, bdesc, idesc_1, acc);
                             }
+                        }
+                        umma_commit(&ctl->empty[s]);
+                    }
+                    __syncwarp();
+                }
+            } else if (Tl.cblk != 0) {
+                // tap pair: accumulator 0 = tap `tap` (with the ones column when tap == 0), accumulator 1 = tap + 1 read
+                // dil rows further down the same staged X tile
+                const int N0 = (J.ones && Tl.tap == 0) ? (GG_ONES_BLK + 1) * 64 : J.n_blk * 64;
+                const uint32_t idesc0 = umma_idesc_bf16(128, N0, 1, 1), idesc1 = umma_idesc_bf16(128, J.n_blk * 64, 1, 1);
+                for (int step = s_lo; step < s_hi; ++step, ++it) {
+                    const int s = it % GG_STAGES, use = it / GG_STAGES;
+                    mbar_wait(&ctl->full[s], use & 1);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + (size_t)s * GG_STAGE_BYTES);
+                    const uint32_t sb = sa + 2 * GG_BOX;
+                    if (elect_one()) {
+#pragma unroll
+                        for (int k = 0; k < GG_TK / 16; ++k) {
+                            const uint64_t adesc = umma_desc_mnmajor_sw128(sa + k * 2048, GG_BOX, 1024);
+                            const uint64_t b0 = umma_desc_mnmajor_sw128(sb + k * 2048, GG_XSTRIDE, 1024);
+                            const uint64_t b1 = umma_desc_mnmajor_sw128(sb + (uint32_t)J.dil * 128u + k * 2048, GG_XSTRIDE, 1024);
+                            const bool acc = (step != s_lo) || k > 0;
+                            umma_bf16(tm, adesc, b0, idesc0, acc);
+                            umma_bf16(tm + 256, adesc, b1, idesc1, acc);
                         }
                         umma_commit(&ctl->empty[s]);
                     }
@@ -184,7 +246,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
                 // starts when it has drained both (segments are ~100 k-steps long, the drain is a few per cent).
                 for (int step = s_lo; step < s_hi; ++step, ++it) {
                     const int s = it % GG_STAGES, use = it / GG_STAGES;
+                    const long long c0 = GG_CLK();
                     mbar_wait(&ctl->full[s], use & 1);
+                    w_full += GG_CLK() - c0;
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + (size_t)s * GG_STAGE_BYTES);
                     const uint32_t sb = sa + 2 * GG_BOX;
@@ -192,7 +256,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
 #pragma unroll
                         for (int k = 0; k < GG_TK / 16; ++k) {
                             const uint64_t adesc = umma_desc_mnmajor_sw128(sa + k * 2048, GG_BOX, 1024);
-                            const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + k * 2048, GG_BOX, 1024);
+                            const uint64_t bdesc = umma_desc_mnmajor_sw128(sb + k * 2048, GG_XSTRIDE, 1024);
                             umma_bf16(tm + (k & 1) * 256, adesc, bdesc, idesc, (step != s_lo) || k >= 2);
                         }
                         umma_commit(&ctl->empty[s]);
@@ -204,43 +268,52 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
             __syncwarp();
             ++ne;
         }
+        GG_STORE(0, w_full); GG_STORE(1, w_drain); GG_STORE(2, GG_CLK() - m_t0); GG_STORE(3, (long long)it); GG_STORE(4, (long long)ne);
     } else if (warp >= 4) {
         const int q = warp & 3;
         int ne = 0;
+        long long t_drain = 0;
         for (int sg = 0; sg < me.nseg; ++sg) {
             const GgSeg S = p.seg[me.seg0 + sg];
             const GgTile Tl = p.tile[S.tile];
             const GgJobDev J = p.job[Tl.job];
             float* prow = p.part + (size_t)S.slot * GG_SLOT_FLOATS + (size_t)(q * 32 + lane) * GG_SLOT_COLS;
             const bool all_taps = Tl.tap == GG_ALL_TAPS;
-            const int n_cols = all_taps ? J.taps * GG_CB : J.n_blk * 64;             // weight-gradient columns of the tile
+            const bool pair = !all_taps && Tl.cblk != 0;
+            const int n_cols = all_taps ? J.taps * GG_CB : J.n_blk * 64;             // weight-gradient columns of the tile (per tap)
             const bool ones = J.ones && (all_taps ? Tl.cblk == 0 : Tl.tap == 0);
             const int ones_col = all_taps ? J.taps * GG_CB : GG_ONES_BLK * 64;
             if (GG_SCALE(S.s_hi) <= GG_SCALE(S.s_lo)) {              // empty share: its partial tile is zero
                 for (int c0 = 0; c0 < n_cols; c0 += 4) *reinterpret_cast<float4*>(prow + c0) = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (pair)
+                    for (int c0 = 0; c0 < n_cols; c0 += 4) *reinterpret_cast<float4*>(prow + 256 + c0) = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (ones) prow[ones_col] = 0.f;
                 continue;
             }
             mbar_wait(&ctl->acc_full[0], ne & 1);
             ++ne;
             tc_fence_after();
+            const long long d0 = GG_CLK();
             const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
-            for (int c0 = 0; c0 < n_cols; c0 += 16) {
-                float v[16];
-                tmem_ld16_dual(trow + c0, !all_taps, v);
-                float4* o4 = reinterpret_cast<float4*>(prow + c0);
+            for (int half = 0; half < (pair ? 2 : 1); ++half)      // a pair keeps tap + 1 in accumulator columns 256..
+                for (int c0 = 0; c0 < n_cols; c0 += 16) {
+                    float v[16];
+                    tmem_ld16_dual(trow + half * 256 + c0, !all_taps && !pair, v);
+                    float4* o4 = reinterpret_cast<float4*>(prow + half * 256 + c0);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-            }
+                    for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                }
             if (ones) {
                 float v[16];
-                tmem_ld16_dual(trow + ones_col, !all_taps, v);
+                tmem_ld16_dual(trow + ones_col, !all_taps && !pair, v);
                 prow[ones_col] = v[0];
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&ctl->acc_empty[0]);
+            t_drain += GG_CLK() - d0;
         }
+        if (warp == 4 && lane == 0) GG_STORE(7, t_drain);
     }
     tc_fence_before();
     __syncthreads();
@@ -259,6 +332,7 @@ struct GgRedJob {
     float* db;                 // bias gradient [M] or null
     int M, Cin, taps, tile0, row0, ones;
     int n_cblk;                // > 0: all-taps tiles, tile = tile0 + m_tile * n_cblk + c / 64, column = 64 tap + c % 64
+    int n_grp;                 // > 0: tap pairs, n_grp tiles per m_tile: tile = tile0 + m_tile * n_grp + tap / 2, column = 256 (tap % 2) + c
 };
 struct GgRedParams {
     const float* part;
@@ -311,8 +385,10 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
             acc[u] = 0.f; vv[u] = 0.f; idx[u] = -1;
             if (e < R) {
                 const int j = e / Cin, c = e - j * Cin;        // c fastest: coalesced reads of the partial tiles
-                const int tile = J.n_cblk ? J.tile0 + m_tile * J.n_cblk + c / GG_CB : J.tile0 + m_tile * taps + j;
-                const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + (J.n_cblk ? j * GG_CB + c % GG_CB : c);
+                const int tile = J.n_cblk ? J.tile0 + m_tile * J.n_cblk + c / GG_CB
+                               : J.n_grp ? J.tile0 + m_tile * J.n_grp + (j >> 1) : J.tile0 + m_tile * taps + j;
+                const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS +
+                                   (J.n_cblk ? j * GG_CB + c % GG_CB : J.n_grp ? (j & 1) * 256 + c : c);
                 const int ns = p.nslot[tile];
                 idx[u] = c * taps + j;
                 if (wn) vv[u] = vrow[idx[u]];
@@ -334,7 +410,7 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
             }
     }
     if (J.db && J.ones && threadIdx.x == GG_RED_NT - 1) {
-        const int tile = J.tile0 + m_tile * (J.n_cblk ? J.n_cblk : taps);
+        const int tile = J.tile0 + m_tile * (J.n_cblk ? J.n_cblk : J.n_grp ? J.n_grp : taps);
         const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + (J.n_cblk ? taps * GG_CB : GG_ONES_BLK * 64);
         float acc = 0.f;
         for (int s = 0; s < p.nslot[tile]; ++s) acc += src[(size_t)s * GG_SLOT_FLOATS];
@@ -412,6 +488,11 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     auto all_taps = [&](const WgradGroupJob& J) {
         return all_taps_on && J.K > 1 && J.K * GG_CB + 16 <= GG_SLOT_COLS && GG_TK + 2 * (J.K / 2) * J.dil <= 3 * GG_TK;
     };
+    // tap pairs (opt-in, GTK_WGRAD_TAP_PAIRS=1): k > 1 and the dil extra rows fit the staged X block.  Measured on the bench
+    // workload (B200, round 2): operand traffic per coupling block 490 -> ~310 MB, kernel 0.67 -> 0.71 ms per step (the
+    // partial tiles double): per-tap tiles stay the default.
+    static const bool pairs_on = getenv("GTK_WGRAD_TAP_PAIRS") && atoi(getenv("GTK_WGRAD_TAP_PAIRS")) != 0;
+    auto tap_pairs = [&](const WgradGroupJob& J) { return pairs_on && !all_taps(J) && J.K > 1 && J.dil <= GG_PAIR_ROWS; };
     bool ones_ok = true;
     for (int q = 0; q < n_jobs; ++q) ones_ok = ones_ok && (all_taps(jobs[q]) || ceil_div(jobs[q].Cin, 64) <= GG_ONES_BLK);
     int n_tiles = 0, rows = 0, rc_at = 0;
@@ -426,9 +507,9 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
         GgJobDev& D = P.job[q];
         D.taps = J.K; D.dil = J.dil; D.n_blk = ceil_div(J.Cin, 64); D.halo = (J.K / 2) * J.dil;
         D.ones = (J.db && ones_ok) ? 1 : 0;
-        const bool at = all_taps(J);
-        if (at) {
-            rc_at = tmap_frames(&P.tmXh[q], J.x, J.ld_x, J.cols_x, T, B, GG_TK + 2 * D.halo);
+        const bool at = all_taps(J), tp = tap_pairs(J);
+        if (at || tp) {
+            rc_at = tmap_frames(&P.tmXh[q], J.x, J.ld_x, J.cols_x, T, B, at ? GG_TK + 2 * D.halo : GG_TK + J.dil);
             if (rc_at) return rc_at;
         }
         int rc = tmap_frames(&P.tmY[q], J.dy, J.ld_y, J.cols_y, T, B);
@@ -439,24 +520,29 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
         Q.g = J.g; Q.v = J.v; Q.dg = J.dg; Q.dv = J.dv; Q.db = J.db;
         Q.M = J.M; Q.Cin = J.Cin; Q.taps = J.K; Q.tile0 = n_tiles; Q.row0 = rows; Q.ones = D.ones;
         Q.n_cblk = at ? D.n_blk : 0;
+        Q.n_grp = tp ? (J.K + 1) / 2 : 0;
         rows += J.M;
         max_row = max(max_row, (size_t)J.Cin * J.K * sizeof(float));
         const int m_tiles = ceil_div(J.M, 128);
-        const int per_m = at ? D.n_blk : J.K;
+        const int per_m = at ? D.n_blk : tp ? (J.K + 1) / 2 : J.K;
         GTK_REQUIRE(n_tiles + m_tiles * per_m <= WGG_MAX_TILES && m_tiles <= 255 && J.K < GG_ALL_TAPS, "too many tiles in one group");
-        // tile weight = tensor-pipe cycles of one k16 step (what bounds the kernel once the operands are not re-fetched per
-        // tap): max(N / 2, 48) per MMA of N columns -- below N = 96 the shared-memory operand reads set the pace
+        // tile weight = measured cycles of one k16 step: with two accumulator chains an MMA of ANY N <= 256 is accepted every
+        // ~128 cycles (profiles/mma_issue_r02.txt), so a single-tap tile costs 128 per k16 step whatever its width and a tap
+        // pair 256; five chains of N = 64 (all-taps) ~74 each.  (Round-2 ncu capture of the kernel with weights N / 2:
+        // sm cycles active 68 k of 99 k elapsed -- CTAs whose share was made of narrow tiles got up to twice the k-steps.)
         for (int mt = 0; mt < m_tiles; ++mt)
             for (int j = 0; j < per_m; ++j) {
                 GgTile& Tl = P.tile[n_tiles];
                 Tl.job = (unsigned char)q; Tl.m_tile = (unsigned char)mt;
                 if (at) {
                     Tl.tap = (unsigned char)GG_ALL_TAPS; Tl.cblk = (unsigned char)j;
-                    w_tile[n_tiles] = (long long)J.K * 48 + ((D.ones && j == 0) ? 16 : 0);
+                    w_tile[n_tiles] = (long long)J.K * 76 + ((D.ones && j == 0) ? 76 : 0);
+                } else if (tp) {
+                    Tl.tap = (unsigned char)(2 * j); Tl.cblk = (unsigned char)((2 * j + 1 < J.K) ? 1 : 0);
+                    w_tile[n_tiles] = Tl.cblk ? 256 : 128;
                 } else {
                     Tl.tap = (unsigned char)j; Tl.cblk = 0;
-                    const int N = ((D.ones && j == 0) ? GG_ONES_BLK + 1 : D.n_blk) * 64;
-                    w_tile[n_tiles] = max(N / 2, 48);
+                    w_tile[n_tiles] = 128;
                 }
                 ++n_tiles;
             }

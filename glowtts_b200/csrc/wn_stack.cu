@@ -89,7 +89,8 @@ wn_stack_kernel(const __grid_constant__ WnStackMaps tm, const __grid_constant__ 
     unsigned char* ring = tile + (size_t)n_kh * pitch;
     float* cst = reinterpret_cast<float*>(ring + (size_t)WS_STAGES * stage_bytes);   // [L][bias_in | bias_rs | cw | cb][2H], bias_start[H]
     float* c_start = cst + (size_t)L * 4 * H2;
-    WsCtl* ctl = reinterpret_cast<WsCtl*>(c_start + H);
+    float* c_end = c_start + H;                                          // bias of `end` [256]
+    WsCtl* ctl = reinterpret_cast<WsCtl*>(c_end + 256);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wi = blockIdx.x, b = blockIdx.y;
@@ -101,7 +102,8 @@ wn_stack_kernel(const __grid_constant__ WnStackMaps tm, const __grid_constant__ 
 
     const int n_s = p.has_start ? p.n_ks : 0;                           // operand stages of the start conv
     const int n1 = p.taps * n_kh, n_l = n1 + n_kh;                      // ... of GEMM 1, of one layer
-    const int total = n_s + L * n_l;
+    const int n_lay = n_s + L * n_l;                                    // ... up to and including the last layer
+    const int total = n_lay + (p.has_end ? n_kh : 0);                   // + the `end` conv
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < WS_STAGES; ++s) { mbar_init(&ctl->full[s], 1); mbar_init(&ctl->empty[s], 1); }
@@ -127,6 +129,8 @@ wn_stack_kernel(const __grid_constant__ WnStackMaps tm, const __grid_constant__ 
         c[2 * H2 + i] = cwv;
         c[3 * H2 + i] = cbv;
     }
+    if (p.has_end)
+        for (int i = threadIdx.x; i < p.C_end; i += EPI_NT) c_end[i] = p.bias_end[i];
     if (p.has_start) {
         for (int i = threadIdx.x; i < H; i += EPI_NT) c_start[i] = p.bias_start[i];
         // the lead-in / lead-out rows are only ever read (by the outermost taps): give them a finite value once
@@ -150,6 +154,11 @@ wn_stack_kernel(const __grid_constant__ WnStackMaps tm, const __grid_constant__ 
         if (it < n_s) {
             mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(A_BYTES + H * KC * 2));
             tma_load_2d(sb + A_BYTES, &tm.wstart, &ctl->full[s], it * KC, 0);
+            return;
+        }
+        if (it >= n_lay) {                              // `end` weights: [C_end rows][64 channels] per k-chunk
+            mbar_arrive_expect_tx(&ctl->full[s], (uint32_t)(p.C_end * KC * 2));
+            tma_load_2d(sb, &tm.wend, &ctl->full[s], (it - n_lay) * KC, 0);
             return;
         }
         const int x = it - n_s, l = x / n_l, y = x - l * n_l;
@@ -425,7 +434,7 @@ wn_stack_kernel(const __grid_constant__ WnStackMaps tm, const __grid_constant__ 
         mbar_wait(&ctl->acc_full, acc_n & 1); ++acc_n;
         tc_fence_after();
         WS_TRACE(5 + 4 * l);
-        if (is_prod && !last) issue_upto(min(total, end_l + WS_STAGES));    // GEMM 2 has released the ring: does not block
+        if (is_prod) issue_upto(min(total, end_l + WS_STAGES));             // GEMM 2 has released the ring: does not block
         for (int cc = ch_lo; cc < ch_hi; ++cc) {
             const int c0 = cc * 16;
             float v[16], sk[16];
@@ -472,16 +481,101 @@ wn_stack_kernel(const __grid_constant__ WnStackMaps tm, const __grid_constant__ 
         WS_TRACE(6 + 4 * l);
     }
 
-    // ------------------------------------------------------------------ masked WN output of the owned rows
+    // ------------------------------------------------------------------ masked WN output of the owned rows; `end` conv +
+    // affine coupling on the resident tile (conv_tc.cu EPI_AFFINE, same sums: two accumulators take alternate k16 steps)
     if (is_mma) {
+        const uint32_t tmw = __shfl_sync(0xffffffffu, tmem, 0);
         mbar_wait(&ctl->tile_ready, tr_n & 1);
         tc_fence_after();
-        if (lane == 0) {
+        if (lane == 0 && (!p.has_end || p.save)) {        // with `end` in the kernel only the weight gradient reads it
             for (int kc = 0; kc < n_kh; ++kc) tma_store_3d(&tm.skip_out, tile + (size_t)kc * pitch + own_src, kc * KC, t_own, b);
             tma_store_commit();
-            tma_store_wait_read();                        // shared memory must outlive the bulk reads
         }
         __syncwarp();
+        if (p.has_end) {
+            const uint32_t idesc = umma_idesc_bf16(BT, p.C_end);
+            for (int kc = 0; kc < n_kh; ++kc, ++it_m) {
+                const int s = it_m % WS_STAGES, use = it_m / WS_STAGES;
+                mbar_wait(&ctl->full[s], use & 1);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(tile + (size_t)kc * pitch) + (uint32_t)p.lead * 128u;
+                const uint32_t sb = smem_u32(ring + (size_t)s * stage_bytes);
+                if (elect_one()) {
+                    const uint64_t adesc = umma_desc_kmajor_sw128(sa), bdesc = umma_desc_kmajor_sw128(sb);
+#pragma unroll
+                    for (int k = 0; k < KC / 16; ++k)
+                        umma_bf16(tmw + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, kc != 0 || k >= 2);
+                }
+                __syncwarp();
+            }
+            if (elect_one()) umma_commit(&ctl->acc_full);
+            __syncwarp();
+        }
+        if (lane == 0) tma_store_wait_read();             // shared memory must outlive the bulk reads
+        __syncwarp();
+    }
+    __syncwarp();
+    if (p.has_end) {
+        const int Ch = p.C_end / 2, C = p.C_end;
+        float ld_sum = 0.f;
+        const int nck = Ch / 16;
+        mbar_wait(&ctl->acc_full, acc_n & 1); ++acc_n;
+        tc_fence_after();
+        for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
+            const int c0 = cc * 16;
+            float m[16], lg[16];
+            tmem_ld16_dual(trow + c0, true, m);
+            tmem_ld16_dual(trow + Ch + c0, true, lg);
+            if (!own) continue;
+            const float* __restrict__ ax = p.aff_x;
+            float* __restrict__ az = p.aff_z;
+            const size_t o0 = ((size_t)b * C + c0) * p.T + t, o1 = o0 + (size_t)Ch * p.T;
+            float x0[16], x1[16], lsave[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) { x0[i] = ax[o0 + (size_t)i * p.T]; x1[i] = ax[o1 + (size_t)i * p.T]; }
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const int c = c0 + i;
+                float mm = m[i] + c_end[c];
+                float ll = lg[i] + c_end[Ch + c];
+                lsave[i] = ll;                             // raw end-conv output (pre sigmoid_scale), as the fp32 path keeps it
+                if (p.aff_sigmoid_scale) ll = __logf(1e-6f + sigmoid_f(ll + 2.f));
+                az[o0 + (size_t)i * p.T] = x0[i];
+                if (p.aff_reverse) {
+                    az[o1 + (size_t)i * p.T] = live ? (x1[i] - mm) * __expf(-ll) : 0.f;
+                } else {
+                    az[o1 + (size_t)i * p.T] = live ? mm + __expf(ll) * x1[i] : 0.f;
+                    ld_sum += live ? ll : 0.f;
+                }
+            }
+            if (p.aff_logs_save) {
+                float4* o4 = reinterpret_cast<float4*>(p.aff_logs_save + frame * Ch + c0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) o4[i] = make_float4(lsave[4 * i], lsave[4 * i + 1], lsave[4 * i + 2], lsave[4 * i + 3]);
+            }
+        }
+        if (!p.aff_reverse && p.aff_logdet) {
+            if (!own) ld_sum = 0.f;
+            if (p.row_b) {
+                // packed rows: the owned live rows of a warp usually belong to one utterance; at a boundary each lane adds
+                // its own
+                const int ub = (own && live) ? p.row_b[frame] : -1;
+                const unsigned act = __ballot_sync(0xffffffffu, ub >= 0);
+                if (act) {
+                    const int ub0 = __shfl_sync(0xffffffffu, ub, __ffs(act) - 1);
+                    if (__all_sync(0xffffffffu, ub < 0 || ub == ub0)) {
+                        ld_sum = warp_sum(ld_sum);
+                        if (lane == 0 && ld_sum != 0.f) atomicAdd(p.aff_logdet + ub0, ld_sum);
+                    } else if (ub >= 0 && ld_sum != 0.f) {
+                        atomicAdd(p.aff_logdet + ub, ld_sum);
+                    }
+                }
+            } else {
+                ld_sum = warp_sum(ld_sum);
+                if (lane == 0) atomicAdd(p.aff_logdet + b, ld_sum);
+            }
+        }
+        tc_fence_before();
     }
     __syncthreads();
     WS_TRACE(3 + 4 * L);
@@ -495,7 +589,7 @@ static size_t ws_smem_bytes(int H, int L, int lead) {
     const int n_kh = H / KC;
     const size_t pitch = ((size_t)(BT + 2 * lead) * 128 + 1023) & ~(size_t)1023;
     const size_t stage = (size_t)((2 * H * KC * 2) > (A_BYTES + H * KC * 2) ? (2 * H * KC * 2) : (A_BYTES + H * KC * 2));
-    return (size_t)n_kh * pitch + WS_STAGES * stage + ((size_t)L * 4 * 2 * H + H) * sizeof(float) + sizeof(WsCtl) + 1024;
+    return (size_t)n_kh * pitch + WS_STAGES * stage + ((size_t)L * 4 * 2 * H + H + 256) * sizeof(float) + sizeof(WsCtl) + 1024;
 }
 
 // Window geometry of a WaveNet with L layers, kernel K, dilation rate dr; false if the stack kernel does not cover it.
@@ -509,6 +603,12 @@ bool wn_stack_geometry(int H, int K, int dr, int L, int n_ks, int* lead, int* ha
     if (halo_tot) *halo_tot = (int)tot;
     if (tile_out) *tile_out = BT - 2 * (int)tot;
     return true;
+}
+
+// `end` + affine inside the kernel: the C_end weight rows of a k-chunk must fit a ring stage
+bool wn_stack_end_ok(int H, int C_end) {
+    const int stage = (2 * H * KC * 2) > (A_BYTES + H * KC * 2) ? (2 * H * KC * 2) : (A_BYTES + H * KC * 2);
+    return C_end % 32 == 0 && C_end >= 32 && C_end <= 256 && C_end * KC * 2 <= stage;
 }
 
 static bool stack_env_on() {
@@ -577,6 +677,14 @@ int wn_stack_launch(const WnStackIo& io, WnStackParams p, cudaStream_t st) {
         }
     }
     GTK_TRY(frames_map(&tm.skip_out, io.skip_out, H, H, p.tile_out));
+    if (p.has_end) {
+        GTK_REQUIRE(io.wend && p.bias_end && p.aff_x && p.aff_z && wn_stack_end_ok(H, p.C_end),
+                    "`end` conv arguments (in_channels * n_sqz must be a multiple of 32 and fit a ring stage)");
+        const uint64_t dims[2] = {(uint64_t)H, (uint64_t)p.C_end};
+        const uint64_t strides[1] = {(uint64_t)H * 2};
+        const uint32_t box[2] = {KC, (uint32_t)p.C_end};
+        GTK_TRY(make_tmap_bf16(&tm.wend, io.wend, 2, dims, strides, box, true));
+    }
     GTK_CUDA(cudaFuncSetAttribute(wn_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(ceil_div(p.T, p.tile_out), p.B);
     ProfScope prof("wn_stack_tc", st);

@@ -32,6 +32,10 @@ int gtk_debug_wb_trace(unsigned long long* out, int n_ctas);
  * wait: out[cta * 8 + l] = SM cycles the MMA warp waited for weight stages in GEMM 1 of layer l, [4 + l] = that GEMM 1. */
 int gtk_debug_ws_trace(unsigned long long* out, int n_ctas);
 int gtk_debug_ws_wait(long long* out, int n_ctas);
+/* Debug: stream-K weight-gradient kernel (wgrad_group.cu), SM cycles per CTA of the last launch: out[cta * 8 + {0 MMA warp
+ * waiting for operand stages, 1 waiting for the previous segment's drain, 2 MMA warp total, 3 k-steps, 4 segments, 5 kernel
+ * entry -> MMA warp start, 6 producer waiting for free stages, 7 drain time of warp 4}]. */
+int gtk_debug_gg_wait(long long* out, int n_ctas);
 /* Debug: the same for the plain tcgen05 conv kernel.  Select which launches record (epilogue 0 plain / 1 gate-bwd /
  * 2 affine, and the tap count; -1 = none), run, then read out[cta * 5 + {start, setup done, accumulator complete,
  * epilogue math done, stores issued}] of the last selected launch.  Synchronises the device. */

@@ -234,13 +234,15 @@ np.savez(sys.argv[1], **{k: p.grad.cpu().numpy() for k, p in dec.named_parameter
 '''
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     outs = []
-    for mode in ("0", "1"):
-        out = str(tmp_path / f"g{mode}.npz")
-        env = dict(os.environ, GTK_WGRAD_ALL_TAPS=mode)
+    # per-tap tiles (the default) | tap-pair tiles (two taps share one staged X tile) | all-taps tiles
+    for i, mode in enumerate((dict(), dict(GTK_WGRAD_TAP_PAIRS="1"), dict(GTK_WGRAD_ALL_TAPS="1"))):
+        out = str(tmp_path / f"g{i}.npz")
+        env = dict(os.environ, **mode)
         subprocess.run([sys.executable, "-c", script, out], check=True, cwd=root, env=env, timeout=600)
         outs.append(np.load(out))
-    a, b = outs
-    assert set(a.files) == set(b.files) and len(a.files) > 20
-    for k in a.files:
-        ref = np.abs(a[k]).max()
-        assert np.abs(a[k] - b[k]).max() <= 2e-3 * ref + 1e-7, (k, float(np.abs(a[k] - b[k]).max()), float(ref))
+    a = outs[0]
+    for b in outs[1:]:
+        assert set(a.files) == set(b.files) and len(a.files) > 20
+        for k in a.files:
+            ref = np.abs(a[k]).max()
+            assert np.abs(a[k] - b[k]).max() <= 2e-3 * ref + 1e-7, (k, float(np.abs(a[k] - b[k]).max()), float(ref))

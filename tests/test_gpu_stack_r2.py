@@ -81,8 +81,9 @@ def test_stack_kernel_is_bit_identical_to_layer_kernels(name, cfg, lengths, p_dr
     a = _run(cfg, sd, y, mask, cond, pitch, energy, p_dropout, stack=True)
     b = _run(cfg, sd, y, mask, cond, pitch, energy, p_dropout, stack=False)
     n_wn = 3 if prosody else 1
-    # the stack path is one launch per WaveNet instead of 1 + L
-    assert b["n_fwd"] - a["n_fwd"] == cfg["n_blocks"] * (cfg["n_layers"] * n_wn + 1 - n_wn), (a["n_fwd"], b["n_fwd"])
+    # the stack path is one launch per WaveNet instead of start + L layers, and `end` + the affine coupling ride in the
+    # last WaveNet's launch
+    assert b["n_fwd"] - a["n_fwd"] == cfg["n_blocks"] * (cfg["n_layers"] * n_wn + 2 - n_wn), (a["n_fwd"], b["n_fwd"])
     assert torch.isfinite(a["z"]).all()
     for k in ("z", "y_rev", "dy"):
         assert torch.equal(a[k], b[k]), (name, k, float((a[k] - b[k]).abs().max()))
