@@ -440,6 +440,16 @@ __device__ __forceinline__ void load_bf16x16(const __nv_bfloat16* src, float (&v
     }
 }
 
+__device__ __forceinline__ void unpack_bf16x16(const uint4& a, const uint4& b, float (&v)[16]) {
+    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
+        v[2 * i] = __low2float(h);
+        v[2 * i + 1] = __high2float(h);
+    }
+}
+
 // accumulator split over two TMEM column ranges (base and base + 256): load both halves and add
 __device__ __forceinline__ void tmem_ld16_dual(uint32_t taddr, bool dual, float (&v)[16]) {
     tmem_ld16(taddr, v);

@@ -42,6 +42,10 @@ constexpr int GG_SLOT_COLS = 512;                // one partial tile: 128 rows x
 constexpr int GG_SLOT_FLOATS = 128 * GG_SLOT_COLS;
 constexpr int GG_ALL_TAPS = 0xFF;                // GgTile::tap of an all-taps tile
 constexpr int GG_CB = 64;                        // X columns of an all-taps tile = accumulator columns per tap
+// Stream-K share weights = measured SM cycles of one k-step (profiles/gg_trace_r02.py, B200): a single-tap tile is bound
+// by the latency of its operand stage under full-chip load (~820 cycles for 40 KB, the MMA warp waits 45 % of the time),
+// a tap pair by its eight MMAs on two accumulator chains (~1060 cycles, it never waits for operands)
+constexpr int GG_W_SINGLE = 100, GG_W_PAIR = 130;
 
 struct GgJobDev {
     int taps, dil, n_blk, ones;                  // n_blk = real 64-column blocks of X; ones: bias gradient wanted
@@ -488,10 +492,8 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     auto all_taps = [&](const WgradGroupJob& J) {
         return all_taps_on && J.K > 1 && J.K * GG_CB + 16 <= GG_SLOT_COLS && GG_TK + 2 * (J.K / 2) * J.dil <= 3 * GG_TK;
     };
-    // tap pairs (opt-in, GTK_WGRAD_TAP_PAIRS=1): k > 1 and the dil extra rows fit the staged X block.  Measured on the bench
-    // workload (B200, round 2): operand traffic per coupling block 490 -> ~310 MB, kernel 0.67 -> 0.71 ms per step (the
-    // partial tiles double): per-tap tiles stay the default.
-    static const bool pairs_on = getenv("GTK_WGRAD_TAP_PAIRS") && atoi(getenv("GTK_WGRAD_TAP_PAIRS")) != 0;
+    // tap pairs (default, GTK_WGRAD_TAP_PAIRS=0 disables): k > 1 and the dil extra rows fit the staged X block
+    static const bool pairs_on = !(getenv("GTK_WGRAD_TAP_PAIRS") && atoi(getenv("GTK_WGRAD_TAP_PAIRS")) == 0);
     auto tap_pairs = [&](const WgradGroupJob& J) { return pairs_on && !all_taps(J) && J.K > 1 && J.dil <= GG_PAIR_ROWS; };
     bool ones_ok = true;
     for (int q = 0; q < n_jobs; ++q) ones_ok = ones_ok && (all_taps(jobs[q]) || ceil_div(jobs[q].Cin, 64) <= GG_ONES_BLK);
@@ -539,10 +541,10 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
                     w_tile[n_tiles] = (long long)J.K * 76 + ((D.ones && j == 0) ? 76 : 0);
                 } else if (tp) {
                     Tl.tap = (unsigned char)(2 * j); Tl.cblk = (unsigned char)((2 * j + 1 < J.K) ? 1 : 0);
-                    w_tile[n_tiles] = Tl.cblk ? 256 : 128;
+                    w_tile[n_tiles] = Tl.cblk ? GG_W_PAIR : GG_W_SINGLE;
                 } else {
                     Tl.tap = (unsigned char)j; Tl.cblk = 0;
-                    w_tile[n_tiles] = 128;
+                    w_tile[n_tiles] = GG_W_SINGLE;
                 }
                 ++n_tiles;
             }

@@ -186,17 +186,34 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
         const bool own = in_t && r >= halo && r < halo + tile_out;      // tiles overlap by the halo: owned frames only
         __nv_bfloat16* dpre_row = (p.dpre && own) ? p.dpre + ((size_t)b * p.T + f) * H2 : nullptr;
         const unsigned long long dseed = p.drop_p > 0.f ? drop_resolve(p.drop_seed) : 0ull;
+        // The saved tanh | sigmoid of this thread's columns (written by the forward pass long ago: they come from HBM) are
+        // requested BEFORE the wait for GEMM a, so their latency hides under it (H <= 192: at most 3 chunks per thread).
+        constexpr int WB_MAXC = 3;
+        const int cc_lo = nck * part / EPI_PARTS, cc_hi = nck * (part + 1) / EPI_PARTS;
+        uint4 pre[WB_MAXC][4];
+#pragma unroll
+        for (int i = 0; i < WB_MAXC; ++i) {
+            if (ok && cc_lo + i < cc_hi) {
+                const int c0 = (cc_lo + i) * 16;
+                const uint4* st = reinterpret_cast<const uint4*>(p.ts) + ((size_t)io.tile_id * (H2 >> 3) + (c0 >> 3)) * 128 + io.r;
+                const uint4* ss4 = reinterpret_cast<const uint4*>(p.ts) + ((size_t)io.tile_id * (H2 >> 3) + ((H + c0) >> 3)) * 128 + io.r;
+                pre[i][0] = __ldg(st); pre[i][1] = __ldg(st + 128); pre[i][2] = __ldg(ss4); pre[i][3] = __ldg(ss4 + 128);
+            }
+        }
         mbar_wait(&ctl->acc_full, 0);
         tc_fence_after();
         WB_TRACE(2);
-        for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
+#pragma unroll
+        for (int ci = 0; ci < WB_MAXC; ++ci) {
+            const int cc = cc_lo + ci;
+            if (cc >= cc_hi) break;
             const int c0 = cc * 16;
             float d[16], dt[16], ds[16];
             tmem_ld16_dual(trow + c0, true, d);
             if (ok) {
                 float tt[16], ss[16];
-                row_load_bf16x16(p.ts, H2, c0, io, tt);
-                row_load_bf16x16(p.ts, H2, H + c0, io, ss);
+                unpack_bf16x16(pre[ci][0], pre[ci][1], tt);
+                unpack_bf16x16(pre[ci][2], pre[ci][3], ss);
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
                     dt[i] = d[i] * ss[i] * (1.f - tt[i] * tt[i]);
@@ -290,17 +307,28 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
         const RowIo io = frame_io(b, ok ? f : 0, p.T);
         const float mk = (p.mask && ok) ? p.mask[(size_t)b * p.T + f] : 1.f;
         const bool live = mk != 0.f;
+        // the fp32 carry of the layer above is requested before the wait for GEMM b (it was complete at kernel start)
+        constexpr int WB_MAXC = 3;
+        const int cc_lo = nck * part / EPI_PARTS, cc_hi = nck * (part + 1) / EPI_PARTS;
+        float xpre[WB_MAXC][16];
+        if (p.resid_f32 && ok) {
+#pragma unroll
+            for (int i = 0; i < WB_MAXC; ++i)
+                if (cc_lo + i < cc_hi) row_load_f32x16(p.resid_f32, H, (cc_lo + i) * 16, io, xpre[i]);
+        }
         mbar_wait(&ctl->acc_full, 1);
         tc_fence_after();
         WB_TRACE(4);
-        for (int cc = nck * part / EPI_PARTS; cc < nck * (part + 1) / EPI_PARTS; ++cc) {
+#pragma unroll
+        for (int ci = 0; ci < WB_MAXC; ++ci) {
+            const int cc = cc_lo + ci;
+            if (cc >= cc_hi) break;
             const int c0 = cc * 16;
             float v[16];
             tmem_ld16_dual(trow + c0, true, v);
             if (!ok) continue;
             if (p.resid_f32) {
-                float x[16];
-                row_load_f32x16(p.resid_f32, H, c0, io, x);
+                float (&x)[16] = xpre[ci];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) v[i] = live ? v[i] + x[i] : 0.f;     // resid and output both masked (modules.py:166)
             } else {

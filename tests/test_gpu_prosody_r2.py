@@ -234,8 +234,8 @@ np.savez(sys.argv[1], **{k: p.grad.cpu().numpy() for k, p in dec.named_parameter
 '''
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     outs = []
-    # per-tap tiles (the default) | tap-pair tiles (two taps share one staged X tile) | all-taps tiles
-    for i, mode in enumerate((dict(), dict(GTK_WGRAD_TAP_PAIRS="1"), dict(GTK_WGRAD_ALL_TAPS="1"))):
+    # per-tap tiles | tap-pair tiles (the default: two taps share one staged X tile) | all-taps tiles
+    for i, mode in enumerate((dict(GTK_WGRAD_TAP_PAIRS="0"), dict(), dict(GTK_WGRAD_ALL_TAPS="1"))):
         out = str(tmp_path / f"g{i}.npz")
         env = dict(os.environ, **mode)
         subprocess.run([sys.executable, "-c", script, out], check=True, cwd=root, env=env, timeout=600)
