@@ -237,6 +237,34 @@ static int side_stream(SideStream** out) {
     *out = tab[dev];
     return GTK_OK;
 }
+// Auxiliary stream of the bf16 forward / reverse: the weight-norm fold + bf16 pack of blocks 1 .. NB-1 runs on it while the
+// caller's stream packs block 0, builds the packing plan and runs block 0 -- the packs are ~70 us of one launch that only
+// block k >= 1 needs.  Forked from and joined back into the caller's stream with events (capturable, stream-ordered for the
+// caller).  GTK_AUX_STREAM=0 keeps everything on the caller's stream.
+static int aux_stream(SideStream** out) {
+    constexpr int MAX_DEV = 64;
+    static SideStream* tab[MAX_DEV] = {nullptr};
+    static std::mutex mu;
+    *out = nullptr;
+    static int enabled = -1;
+    if (enabled < 0) { const char* e = getenv("GTK_AUX_STREAM"); enabled = (e && e[0] == '0') ? 0 : 1; }
+    if (!enabled) return GTK_OK;
+    int dev = 0;
+    GTK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEV) return GTK_OK;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!tab[dev]) {
+        SideStream* ss = new SideStream();
+        GTK_CUDA(cudaStreamCreateWithFlags(&ss->s, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            GTK_CUDA(cudaEventCreateWithFlags(&ss->fork[i], cudaEventDisableTiming));
+            GTK_CUDA(cudaEventCreateWithFlags(&ss->done[i], cudaEventDisableTiming));
+        }
+        tab[dev] = ss;
+    }
+    *out = tab[dev];
+    return GTK_OK;
+}
 static int wgrad_overlap_ctas() {
     static int v = -1;
     if (v < 0) {

@@ -158,7 +158,7 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
 // weight-norm fold + bf16 operand packs (zero padding included) of EVERY block in one launch (a second one only
 // if the model has more than FOLD_PACK_MAX_JOBS conv weights).
 static int tc_pack_all(const Dims& D, const TcLayout& L, const gtk_block_params* blocks, bf16* pk_base, int with_transposed,
-                       cudaStream_t st) {
+                       cudaStream_t st, int blk_lo = 0, int blk_hi = -1) {
     const int H = D.H, C = D.C, Ch = D.C / 2, K = D.K;
     const TcPack& Q = L.P_;
     static thread_local tc::FoldPackJobs J;
@@ -169,7 +169,8 @@ static int tc_pack_all(const Dims& D, const TcLayout& L, const gtk_block_params*
         j.g = g; j.v = v; j.fwd = pk + fwd; j.tr = with_transposed ? pk + tr : nullptr;
         j.M = M; j.Cin = Cin; j.K = Kk; j.rows_f = M; j.cols_f = cols_f; j.rows_t = Cin; j.cols_t = cols_t; j.groups = 0;
     };
-    for (int blk = 0; blk < D.NB; ++blk) {
+    if (blk_hi < 0) blk_hi = D.NB;
+    for (int blk = blk_lo; blk < blk_hi; ++blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
         if (J.n + 2 + 2 * D.L * D.n_wn > tc::FOLD_PACK_MAX_JOBS) { GTK_TRY(tc::fold_pack(J, st)); J.n = 0; }
@@ -186,7 +187,24 @@ static int tc_pack_all(const Dims& D, const TcLayout& L, const gtk_block_params*
         }
         add(nullptr, P.end_w, Q.end, Q.t_end, C, H, 1, H, pad64(C));
     }
-    return tc::fold_pack(J, st);
+    return J.n ? tc::fold_pack(J, st) : GTK_OK;
+}
+
+// Packs of the first block to run on the caller's stream, the others on the auxiliary stream (decoder.cu: aux_stream);
+// *join is set to the event the caller's stream must wait for before it runs any other block (null: nothing to wait for).
+static int tc_pack_split(const Dims& D, const TcLayout& L, const gtk_block_params* blocks, bf16* pk_base, int with_transposed,
+                         int first_blk, cudaStream_t st, cudaEvent_t** join) {
+    *join = nullptr;
+    SideStream* ax = nullptr;
+    GTK_TRY(aux_stream(&ax));
+    if (!ax || D.NB < 2) return tc_pack_all(D, L, blocks, pk_base, with_transposed, st);
+    GTK_CUDA(cudaEventRecord(ax->fork[0], st));
+    GTK_CUDA(cudaStreamWaitEvent(ax->s, ax->fork[0], 0));
+    if (first_blk > 0) GTK_TRY(tc_pack_all(D, L, blocks, pk_base, with_transposed, ax->s, 0, first_blk));
+    if (first_blk + 1 < D.NB) GTK_TRY(tc_pack_all(D, L, blocks, pk_base, with_transposed, ax->s, first_blk + 1, D.NB));
+    GTK_CUDA(cudaEventRecord(ax->done[0], ax->s));
+    *join = &ax->done[0];
+    return tc_pack_all(D, L, blocks, pk_base, with_transposed, st, first_blk, first_blk + 1);
 }
 
 // W^-1 / log|det W| of every block (+ the constant part of logdet when logdet != null), one launch per 32 blocks.
@@ -356,7 +374,8 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     if (D.Tq == 0) return GTK_OK;
     unsigned char* ws = static_cast<unsigned char*>(workspace);
     const TcPlan pl = tc_plan(L, ws);
-    GTK_TRY(tc_pack_all(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), train, st));
+    cudaEvent_t* packs_done = nullptr;
+    GTK_TRY(tc_pack_split(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), train, 0, st, &packs_done));
     GTK_TRY(flow::pack_plan(mask, D.B, D.T, D.n, D.Tq, L.G, L.P, pl.hdr, pl.off, pl.row_b, pl.row_fr, pl.mask_p, pl.x_len, st));
     GTK_TRY(flow::squeeze_pack(x, pl.off, pl.row_b, pl.mask_p, reinterpret_cast<float*>(ws + L.X), D.Cin, D.T, D.n, L.P, st));
     for (int w = 1; w < D.n_wn; ++w)
@@ -374,6 +393,7 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     for (int blk = 0; blk < D.NB; ++blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
+        if (blk == 1 && packs_done) GTK_CUDA(cudaStreamWaitEvent(st, *packs_done, 0));
         unsigned char* act = ws + L.act + (size_t)(train ? blk : 0) * L.A.total;
         bf16* pk = reinterpret_cast<bf16*>(ws + L.pack) + (size_t)blk * L.P_.total;
         const float* xin = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? blk : (blk & 1)) * L.x_bytes);
@@ -401,7 +421,8 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     float* xa = reinterpret_cast<float*>(ws + L.X);
     float* xb = reinterpret_cast<float*>(ws + L.X + L.x_bytes);
     unsigned char* act = ws + L.act;
-    GTK_TRY(tc_pack_all(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), 0, st));
+    cudaEvent_t* packs_done = nullptr;
+    GTK_TRY(tc_pack_split(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), 0, D.NB - 1, st, &packs_done));
     GTK_TRY(flow::pack_plan(mask, D.B, D.T, D.n, D.Tq, L.G, L.P, pl.hdr, pl.off, pl.row_b, pl.row_fr, pl.mask_p, pl.x_len, st));
     GTK_TRY(flow::squeeze_pack(z, pl.off, pl.row_b, pl.mask_p, xa, D.Cin, D.T, D.n, L.P, st));
     for (int w = 1; w < D.n_wn; ++w)
@@ -411,6 +432,7 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     for (int blk = D.NB - 1; blk >= 0; --blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
+        if (blk == D.NB - 2 && packs_done) GTK_CUDA(cudaStreamWaitEvent(st, *packs_done, 0));
         float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
         const bf16* pk = reinterpret_cast<const bf16*>(ws + L.pack) + (size_t)blk * L.P_.total;
         GTK_TRY(tc_coupling(d, D, L, P, pk, xa, xb, nullptr, pl, act, ws, 1, 0, blk, st));
