@@ -349,7 +349,7 @@ struct GgRedParams {
 // modules.py:124,131,141):  dg[m] += <dW_m, v_m>/||v_m||,  dv_m += g_m/||v_m|| (dW_m - v_m <dW_m, v_m>/||v_m||^2).
 // The kernel is latency-bound (a few dependent L2 round trips per block), so every thread issues all the loads of its
 // (up to four) row elements -- partial slots four at a time, plus v -- before consuming any of them.
-constexpr int GG_RED_NT = 256;
+constexpr int GG_RED_NT = 128;
 struct GgRedMulti {
     int n;
     int row_end[WGG_MAX_DEFER];                    // cumulative output rows of launch k
@@ -380,13 +380,15 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
     const bool wn = J.g != nullptr;
     const float* part_row = p.part + (size_t)r * GG_SLOT_COLS;
     float ss = 0.f, dd = 0.f;
+    // pass 1: partial slots -> reduced row in shared memory, torch order (the partial tiles are read c-fastest = coalesced;
+    // v is NOT touched here: indexed c * taps + j it would be a stride-taps read, 5x the sectors for the k = 5 convs)
     for (int e0 = threadIdx.x; e0 < R; e0 += 4 * GG_RED_NT) {
-        float acc[4], vv[4];
+        float acc[4];
         int idx[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int e = e0 + u * GG_RED_NT;
-            acc[u] = 0.f; vv[u] = 0.f; idx[u] = -1;
+            acc[u] = 0.f; idx[u] = -1;
             if (e < R) {
                 const int j = e / Cin, c = e - j * Cin;        // c fastest: coalesced reads of the partial tiles
                 const int tile = J.n_cblk ? J.tile0 + m_tile * J.n_cblk + c / GG_CB
@@ -395,7 +397,6 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
                                    (J.n_cblk ? j * GG_CB + c % GG_CB : J.n_grp ? (j & 1) * 256 + c : c);
                 const int ns = p.nslot[tile];
                 idx[u] = c * taps + j;
-                if (wn) vv[u] = vrow[idx[u]];
                 for (int s = 0; s < ns; s += 4) {
                     const float a0 = src[(size_t)s * GG_SLOT_FLOATS];
                     const float a1 = (s + 1 < ns) ? src[(size_t)(s + 1) * GG_SLOT_FLOATS] : 0.f;
@@ -407,11 +408,7 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-            if (idx[u] >= 0) {
-                row[idx[u]] = acc[u];
-                ss += vv[u] * vv[u];
-                dd += vv[u] * acc[u];
-            }
+            if (idx[u] >= 0) row[idx[u]] = acc[u];
     }
     if (J.db && J.ones && threadIdx.x == GG_RED_NT - 1) {
         const int tile = J.tile0 + m_tile * (J.n_cblk ? J.n_cblk : J.n_grp ? J.n_grp : taps);
@@ -420,16 +417,21 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
         for (int s = 0; s < p.nslot[tile]; ++s) acc += src[(size_t)s * GG_SLOT_FLOATS];
         J.db[m] += acc;
     }
-    if (wn) {                                       // both row sums with one barrier pair
-        ss = warp_sum(ss);
-        dd = warp_sum(dd);
-        if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = ss; red[1][threadIdx.x >> 5] = dd; }
-    }
     __syncthreads();
     if (!wn) {
         for (int e = threadIdx.x; e < R; e += GG_RED_NT) dvrow[e] += row[e];
         return;
     }
+    // pass 2 (coalesced, torch order): <v, v> and <dW, v> of the row
+    for (int e = threadIdx.x; e < R; e += GG_RED_NT) {
+        const float vv = vrow[e];
+        ss += vv * vv;
+        dd += vv * row[e];
+    }
+    ss = warp_sum(ss);
+    dd = warp_sum(dd);
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = ss; red[1][threadIdx.x >> 5] = dd; }
+    __syncthreads();
     ss = 0.f; dd = 0.f;
 #pragma unroll
     for (int w = 0; w < GG_RED_NT / 32; ++w) { ss += red[0][w]; dd += red[1][w]; }
