@@ -22,6 +22,7 @@
 // consumed by an in-band cell, so the lower band clip is not needed.
 #include <mutex>
 #include "common.cuh"
+#include <stdlib.h>
 #include "ops.h"
 #include "tc.cuh"
 
@@ -45,6 +46,8 @@ struct Params {
     int B, T_x, T_y;
     int n_stages;
     int vec4;             // 1: value rows are 16-byte aligned (T_y % 4 == 0 and base aligned)
+    uint32_t* bits_ws;    // wavefront kernel: decision words [B][T_y / 32][ROWW] in GLOBAL memory (null: shared memory);
+                          // opt-in experiment, see plan_wave
 };
 
 template <int XPT>
@@ -552,9 +555,10 @@ __global__ void __launch_bounds__(NT, 1) mas_wave_kernel(const __grid_constant__
 
     WaveCtl* ctl = reinterpret_cast<WaveCtl*>(smem_raw);
     int* ys = reinterpret_cast<int*>(smem_raw + sizeof(WaveCtl));
-    uint32_t* bitsT = reinterpret_cast<uint32_t*>(ys + ROWW + 4);
+    uint32_t* bits_smem = reinterpret_cast<uint32_t*>(ys + ROWW + 4);
+    uint32_t* bitsT = p.bits_ws ? p.bits_ws + (size_t)blockIdx.x * NYB * ROWW : bits_smem;
     float* tiles = reinterpret_cast<float*>(
-        (reinterpret_cast<uintptr_t>(bitsT + (size_t)NYB * ROWW) + 127) & ~static_cast<uintptr_t>(127));
+        (reinterpret_cast<uintptr_t>(bits_smem + (p.bits_ws ? 0 : (size_t)NYB * ROWW)) + 127) & ~static_cast<uintptr_t>(127));
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.x;
@@ -1014,26 +1018,49 @@ static int plan_fast(int T_x, int T_y, int* xpt_out) {
     return 0;
 }
 
+static size_t wave_bits_bytes(int B, int T_x, int T_y) {
+    return (size_t)B * ceil_div(T_y, YT) * ((T_x + 3) & ~3) * sizeof(uint32_t);
+}
+static int plan_wave(int T_x, int T_y, int* xpt_out, int* bits_global);
 size_t workspace_bytes(int B, int T_x, int T_y) {
-    int xpt;
-    if (plan_fast(T_x, T_y, &xpt) > 0) return 0;
-    return (size_t)B * T_y * ceil_div(T_x, 32) * sizeof(uint32_t);
+    int xpt, bg = 1;
+    const size_t wave = (T_y % 4 == 0 && plan_wave(T_x, T_y, &xpt, &bg) > 0 && bg) ? wave_bits_bytes(B, T_x, T_y) : 0;
+    if (plan_fast(T_x, T_y, &xpt) > 0) return wave;
+    return max(wave, (size_t)B * T_y * ceil_div(T_x, 32) * sizeof(uint32_t));
 }
 
 // TMA wavefront path: text rows per lane of each of the NDP DP warps.
-static size_t wave_smem_bytes(int T_x, int T_y, int stages) {
+static size_t wave_smem_bytes(int T_x, int T_y, int stages, int bits_global = 0) {
     const size_t roww = (size_t)((T_x + 3) & ~3);
     const size_t nyb = (T_y + YT - 1) / YT;
     const size_t rb = ceil_div(T_x, TBOX);
-    return sizeof(WaveCtl) + (roww + 4) * 4 + nyb * roww * 4 + 128 + (size_t)stages * rb * TBOX_BYTES;
+    return sizeof(WaveCtl) + (roww + 4) * 4 + (bits_global ? 0 : nyb * roww * 4) + 128 + (size_t)stages * rb * TBOX_BYTES;
 }
-static int plan_wave(int T_x, int T_y, int* xpt_out) {
-    const int xpt = max(1, ceil_div(T_x, 32 * NDP));
+// *bits_global: in = the caller can provide the global decision-word workspace; out = the plan uses it (when the bits in
+// shared memory would leave fewer than 3 value stages and moving them out buys at least one more)
+static int plan_wave(int T_x, int T_y, int* xpt_out, int* bits_global) {
+    int xpt = max(1, ceil_div(T_x, 32 * NDP));
+    {   // experiment switch: at least this many text rows per lane (fewer, longer DP warps)
+        static const int min_xpt = getenv("GTK_MAS_MIN_XPT") ? atoi(getenv("GTK_MAS_MIN_XPT")) : 0;
+        if (min_xpt > xpt) xpt = min(min_xpt, TMA_MAX_XPT);
+    }
     *xpt_out = xpt;
+    const int can_global = *bits_global;
+    *bits_global = 0;
     if (xpt > TMA_MAX_XPT || T_y % 4 != 0) return 0;
-    for (int s = TMA_MAX_STAGES; s >= 2; --s)
-        if (wave_smem_bytes(T_x, T_y, s) <= SMEM_LIMIT) return s;
-    return 0;
+    int s_smem = 0, s_glob = 0;
+    for (int s = TMA_MAX_STAGES; s >= 2 && !s_smem; --s)
+        if (wave_smem_bytes(T_x, T_y, s) <= SMEM_LIMIT) s_smem = s;
+    // opt-in (GTK_MAS_GLOBAL_BITS=1).  Measured on B200, B = 512 x 400 x 2000: three stages with the bits in L2 run 844 us
+    // against 781 us with two stages and the bits in shared memory -- the single-thread backtrack pays L2 latency per batch
+    // of rows and the extra stage buys nothing: the kernel is not bound by the bytes in flight.
+    static const bool glob_on = getenv("GTK_MAS_GLOBAL_BITS") && atoi(getenv("GTK_MAS_GLOBAL_BITS")) != 0;
+    if (can_global && glob_on && s_smem < 3) {
+        for (int s = TMA_MAX_STAGES; s >= 2 && !s_glob; --s)
+            if (wave_smem_bytes(T_x, T_y, s, 1) <= SMEM_LIMIT) s_glob = s;
+        if (s_glob > s_smem) { *bits_global = 1; return s_glob; }
+    }
+    return s_smem;
 }
 
 // Fused logp + MAS path: smem = wavefront layout + the z ring.
@@ -1079,7 +1106,7 @@ int fused_forward(const float* z, const float* x_m, const int* t_xs, const int* 
     }
     Params p;
     p.value = nullptr; p.path = path; p.t_xs = t_xs; p.t_ys = t_ys; p.dur_out = dur_out; p.idx_out = idx_out;
-    p.B = B; p.T_x = T_x; p.T_y = T_y; p.n_stages = stages; p.vec4 = 1;
+    p.B = B; p.T_x = T_x; p.T_y = T_y; p.n_stages = stages; p.vec4 = 1; p.bits_ws = nullptr;
     CUtensorMap tm;
     const uint64_t dims[3] = {(uint64_t)T_y, (uint64_t)D, (uint64_t)B};
     const uint64_t strides[2] = {(uint64_t)T_y * 4, (uint64_t)T_y * 4 * D};
@@ -1125,16 +1152,19 @@ int forward(const float* value, const int* t_xs, const int* t_ys, float* path, i
     p.vec4 = ((T_y % 4) == 0) && ((reinterpret_cast<uintptr_t>(value) & 15) == 0);
     int xpt = 0;
     // force_generic: 0 = pick the fastest applicable path, 1 = generic kernel, 2 = helper-warp fast path (no TMA)
-    const int tma_stages = (force_generic == 0 && p.vec4) ? plan_wave(T_x, T_y, &xpt) : 0;
+    int bits_global = (workspace && workspace_bytes_given >= wave_bits_bytes(B, T_x, T_y)) ? 1 : 0;
+    const int tma_stages = (force_generic == 0 && p.vec4) ? plan_wave(T_x, T_y, &xpt, &bits_global) : 0;
+    p.bits_ws = nullptr;
     if (tma_stages > 0) {
         p.n_stages = tma_stages;
+        if (bits_global) p.bits_ws = static_cast<uint32_t*>(workspace);
         CUtensorMap tm;
         const uint64_t dims[3] = {(uint64_t)T_y, (uint64_t)T_x, (uint64_t)B};
         const uint64_t strides[2] = {(uint64_t)T_y * 4, (uint64_t)T_y * 4 * T_x};
         const uint32_t box[3] = {TP, TBOX, 1};
         int rc = tc::make_tmap_f32(&tm, value, 3, dims, strides, box);
         if (rc) return rc;
-        const size_t smem = wave_smem_bytes(T_x, T_y, tma_stages);
+        const size_t smem = wave_smem_bytes(T_x, T_y, tma_stages, bits_global);
         switch (xpt) {
 #define GTK_MAS_CASE(N) case N: return launch_wave<N>(p, tm, smem, stream);
             GTK_MAS_CASE(1) GTK_MAS_CASE(2) GTK_MAS_CASE(3) GTK_MAS_CASE(4) GTK_MAS_CASE(5) GTK_MAS_CASE(6)
