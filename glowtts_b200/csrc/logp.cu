@@ -8,7 +8,7 @@
 // rounding of the reference's two matmuls.
 #include <stdlib.h>
 
-#include "common.cuh"
+#include "tc.cuh"
 #include "ops.h"
 
 namespace gtk {
@@ -280,6 +280,172 @@ __global__ void __launch_bounds__(TNT, 2) logp_tc_kernel(const float* __restrict
         }
 }
 
+
+// -------------------------------------------------------------------------------------------------
+// tcgen05 logp (round 2): the same 3xTF32 contraction on the 5th-generation tensor cores.  One 128 (text) x 128 (frames)
+// output tile per CTA, fp32 accumulator in TMEM (128 columns: three CTAs share an SM).  The operands are COMPUTED by the
+// CTA (scaled means, squares, hi / lo split), so the threads stage them, not TMA: thread = one row (threads 0..127 text
+// rows of A, 128..255 frames of B), walking k in chunks of 32: 32 coalesced global loads (lanes = consecutive rows), the
+// hi / lo split, sixteen 16-byte stores into K-major SWIZZLE_128B tiles (32 fp32 per 128-byte row, 16-byte chunks XOR-ed
+// with row % 8 -- the layout conv_tc.cu's bf16 tiles have) for A_hi, A_lo, B_hi, B_lo.  One elected lane then issues, per
+// k8 step,  D += A_lo B_hi;  D += A_hi B_lo;  D += A_hi B_hi   (tcgen05.mma.kind::tf32, M = N = 128, K = 8; hi = upper
+// 19 bits = exactly a tf32, lo = v - hi), while the threads already load the next chunk into registers; the 64 KB staging
+// area is rewritten once the MMAs have completed.  The row owners also sum the per-token / per-frame constants over d in
+// a fixed order.  Drain: warp = TMEM lane quarter x frame half, thread = text row, 64 consecutive frames.
+constexpr int UX = 128, UY = 128, UNT = 256;
+constexpr int U_KC = 32;                          // fp32 elements per swizzle row = k per pass
+constexpr int U_TILE = UX * 128;                  // bytes of one [128 rows x 32 fp32] tile
+
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, bool accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"((uint32_t)accumulate)
+        : "memory");
+}
+
+struct LogpUmmaCtl {
+    uint64_t mma_done;
+    uint32_t tmem_base;
+    float crow[UX], zq[UY];
+};
+
+template <bool MEAN_ONLY>
+__global__ void __launch_bounds__(UNT, 3) logp_umma_kernel(const float* __restrict__ x_m, const float* __restrict__ x_logs,
+                                                        const float* __restrict__ z, float* __restrict__ out, int D, int T_x,
+                                                        int T_y) {
+    extern __shared__ __align__(1024) unsigned char usm_raw[];
+    unsigned char* usm = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(usm_raw) + 1023) & ~uintptr_t(1023));
+    unsigned char* a_hi = usm;
+    unsigned char* a_lo = a_hi + U_TILE;
+    unsigned char* b_hi = a_lo + U_TILE;
+    unsigned char* b_lo = b_hi + U_TILE;
+    LogpUmmaCtl* ctl = reinterpret_cast<LogpUmmaCtl*>(b_lo + U_TILE);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int y0 = blockIdx.x * UY, x0 = blockIdx.y * UX, b = blockIdx.z;
+    const int KT = MEAN_ONLY ? D : 2 * D;
+    const int n_chunks = (KT + U_KC - 1) / U_KC;
+
+    // this thread's row: text row x0 + row of A, or frame y0 + row of B
+    const bool is_b = tid >= UX;
+    const int row = is_b ? tid - UX : tid;
+    const int g = (is_b ? y0 : x0) + row, g_n = is_b ? T_y : T_x;
+    const bool ok = g < g_n;
+    const float* src = (is_b ? z + (size_t)b * D * T_y : x_m + (size_t)b * D * T_x) + (ok ? g : 0);
+    const float* lsrc = (MEAN_ONLY || is_b) ? nullptr : x_logs + (size_t)b * D * T_x + (ok ? g : 0);
+
+    if (tid == 0) { mbar_init(&ctl->mma_done, 1); mbar_fence_init(); }
+    if (warp == 0) tc::tmem_alloc<128>(&ctl->tmem_base);
+
+    float cst = 0.f;                                  // A: per-token constant; B (mean_only): sum_d z^2
+    float v[U_KC];
+    auto load_chunk = [&](int c) {                    // operand values k = 32 c .. 32 c + 31 of this row (and the constants)
+#pragma unroll
+        for (int i = 0; i < U_KC; ++i) {
+            const int k = c * U_KC + i;
+            float val = 0.f;
+            if (ok && k < KT) {
+                const int d = (MEAN_ONLY || k < D) ? k : k - D;
+                const float a = __ldg(src + (size_t)d * g_n);
+                if (is_b) {
+                    val = (MEAN_ONLY || k < D) ? a : a * a;
+                    if (MEAN_ONLY) cst = fmaf(a, a, cst);
+                } else if (MEAN_ONLY) {
+                    val = a;
+                    cst = fmaf(a, a, cst);
+                } else {
+                    const float l = __ldg(lsrc + (size_t)d * g_n);
+                    const float sc = expf(-2.f * l);
+                    val = (k < D) ? a * sc : -0.5f * sc;
+                    if (k < D) cst += -0.918938533204672742f - l - 0.5f * a * a * sc;
+                }
+            }
+            v[i] = val;
+        }
+    };
+    load_chunk(0);
+    const uint32_t idesc = umma_idesc_tf32(UX, UY);
+    unsigned char* t_hi = is_b ? b_hi : a_hi;
+    unsigned char* t_lo = is_b ? b_lo : a_lo;
+    for (int c = 0; c < n_chunks; ++c) {
+        if (c > 0) mbar_wait(&ctl->mma_done, (c - 1) & 1);          // the MMAs of the previous chunk have read the staging area
+#pragma unroll
+        for (int sl = 0; sl < U_KC / 4; ++sl) {
+            uint32_t h[4], l[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { h[i] = tf32_hi(v[4 * sl + i]); l[i] = tf32_lo(v[4 * sl + i], h[i]); }
+            const size_t off = (size_t)row * 128 + (size_t)((sl ^ (row & 7)) << 4);
+            *reinterpret_cast<uint4*>(t_hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4*>(t_lo + off) = make_uint4(l[0], l[1], l[2], l[3]);
+        }
+        if (c + 1 == n_chunks) {
+            if (is_b) ctl->zq[row] = MEAN_ONLY ? -0.5f * cst : 0.f;
+            else ctl->crow[row] = MEAN_ONLY ? -0.5f * cst - (float)D * 0.918938533204672742f : cst;
+        }
+        tc::fence_proxy_async_smem();
+        tc::tc_fence_before();
+        __syncthreads();
+        tc::tc_fence_after();
+        if (warp == 1) {
+            const uint32_t tmem = ctl->tmem_base;
+            if (tc::elect_one()) {
+                const uint64_t ah = tc::umma_desc_kmajor_sw128(smem_u32(a_hi)), al = tc::umma_desc_kmajor_sw128(smem_u32(a_lo));
+                const uint64_t bh = tc::umma_desc_kmajor_sw128(smem_u32(b_hi)), bl = tc::umma_desc_kmajor_sw128(smem_u32(b_lo));
+#pragma unroll
+                for (int k = 0; k < U_KC / 8; ++k) {              // K = 8 per tf32 MMA = 32 bytes = 2 descriptor units
+                    umma_tf32(tmem, al + 2 * k, bh + 2 * k, idesc, (c | k) != 0);
+                    umma_tf32(tmem, ah + 2 * k, bl + 2 * k, idesc, true);
+                    umma_tf32(tmem, ah + 2 * k, bh + 2 * k, idesc, true);
+                }
+                tc::umma_commit(&ctl->mma_done);
+            }
+            __syncwarp();
+        }
+        if (c + 1 < n_chunks) load_chunk(c + 1);      // in flight while the tensor core works
+    }
+    mbar_wait(&ctl->mma_done, (n_chunks - 1) & 1);
+    tc::tc_fence_after();
+    // ---- drain: warp w owns TMEM lanes 32 (w % 4) .. (text rows) and frames 64 (w / 4) ..
+    {
+        const uint32_t tmem = ctl->tmem_base;
+        const int q = warp & 3, half = warp >> 2;
+        const int r = q * 32 + lane, x = x0 + r;
+        const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 64);
+        const float c = ctl->crow[r];
+        float* orow = out + ((size_t)b * T_x + (x < T_x ? x : 0)) * T_y + y0 + half * 64;
+        const bool vec = ((T_y & 3) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float w[16];
+            tc::tmem_ld16(trow + 16 * j, w);
+            if (x >= T_x) continue;
+            const int yy = half * 64 + 16 * j;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) w[i] += c + ctl->zq[yy + i];
+            if (vec && y0 + yy + 16 <= T_y) {
+                float4* o4 = reinterpret_cast<float4*>(orow + 16 * j);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) o4[i] = make_float4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (y0 + yy + i < T_y) orow[16 * j + i] = w[i];
+            }
+        }
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc::tc_fence_after();
+        tc::tmem_dealloc<128>(ctl->tmem_base);
+    }
+}
+
+static size_t logp_umma_smem() { return (size_t)4 * U_TILE + sizeof(LogpUmmaCtl) + 1024; }
+
 static size_t logp_tc_smem(int D, bool mean_only) {
     const int KT = mean_only ? D : 2 * D;
     return sizeof(float) * ((size_t)KT * AP + (size_t)KT * BP + (mean_only ? 0 : (size_t)D * TX) + TX + TY);
@@ -289,6 +455,26 @@ int forward(const float* x_m, const float* x_logs, const float* z, float* out, i
             cudaStream_t st) {
     GTK_REQUIRE(x_m && z && out, "null");
     if ((long long)B * T_x * T_y == 0) return GTK_OK;
+    // tcgen05 kind::tf32 kernel: mean_only models (every configs/base*.json; 33 us at B = 32, 180 x 860, the same as the
+    // mma.sync kernel it replaces there), and general models the mma.sync kernel does not cover.  With x_logs the row-owner
+    // staging pays 2 D expf per text row on 128 of the 256 threads (141 us against 52 us): those shapes stay on the
+    // mma.sync kernel.  GTK_LOGP_UMMA=1 forces tcgen05 everywhere, GTK_LOGP_LEGACY=1 / GTK_LOGP_FFMA=1 the older kernels.
+    const bool legacy_ok = D % 8 == 0 && D >= 8 && D <= TC_MAX_D;
+    if (D >= 1 && D <= 256 && !getenv("GTK_LOGP_FFMA") && !getenv("GTK_LOGP_LEGACY") &&
+        (x_logs == nullptr || !legacy_ok || getenv("GTK_LOGP_UMMA"))) {
+        const bool mo = x_logs == nullptr;
+        const size_t smem = logp_umma_smem();
+        dim3 grid(ceil_div(T_y, UY), ceil_div(T_x, UX), B);
+        ProfScope prof("logp", st);
+        if (mo) {
+            GTK_CUDA(cudaFuncSetAttribute(logp_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            logp_umma_kernel<true><<<grid, UNT, smem, st>>>(x_m, x_logs, z, out, D, T_x, T_y);
+        } else {
+            GTK_CUDA(cudaFuncSetAttribute(logp_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            logp_umma_kernel<false><<<grid, UNT, smem, st>>>(x_m, x_logs, z, out, D, T_x, T_y);
+        }
+        return check_launch("logp_umma");
+    }
     if (D % 8 == 0 && D >= 8 && D <= TC_MAX_D && !getenv("GTK_LOGP_FFMA")) {
         const bool mo = x_logs == nullptr;
         const size_t smem = logp_tc_smem(D, mo);

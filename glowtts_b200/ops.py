@@ -902,7 +902,13 @@ def decoder_backward_flat_overlapped(dz: Tensor, dlogdet: Tensor, mask: Tensor, 
     world = dist.get_world_size(group) if sync else 1
     avg = sync and dist.get_backend(group) == "nccl"
     n_segments = max(1, min(int(n_segments), nb))
-    bounds = [nb * k // n_segments for k in range(n_segments + 1)]          # block index boundaries, ascending
+    # block index boundaries, ascending.  The ranges run from the last block down, so range 0 is the one whose collective
+    # nothing can hide: it gets half a share (12 blocks, 3 segments: blocks 11..7 | 6..2 | 1..0)
+    if n_segments > 1:
+        last = max(1, nb // (2 * n_segments))
+        bounds = [0] + [last + (nb - last) * k // (n_segments - 1) for k in range(n_segments)]
+    else:
+        bounds = [0, nb]
     works = []
     for k in range(n_segments - 1, -1, -1):                                   # ranges from the last block down
         lo, hi = bounds[k], bounds[k + 1] - 1
