@@ -220,6 +220,29 @@ def test_logp_matches_oracle_and_feeds_mas(mean_only):
     assert agree > 0.97                                              # path agreement under 1e-4 logp noise
 
 
+@pytest.mark.parametrize("kernel", ["umma", "legacy", "ffma"])
+@pytest.mark.parametrize("mean_only,B,D,TX,TY", [(True, 3, 80, 180, 860), (False, 2, 80, 37, 101), (True, 2, 80, 129, 258),
+                                                (False, 2, 24, 200, 131), (True, 2, 17, 5, 33)])
+def test_logp_kernels_match_oracle(kernel, mean_only, B, D, TX, TY):
+    """Every logp kernel (tcgen05 kind::tf32 3xTF32 -- the default for mean_only models --, mma.sync 3xTF32, FFMA) against
+    the oracle restatement of models.py:1076-1082: tile seams (T_x > 128, T_y > 128), ragged edges (T_y % 4 != 0), k-chunk
+    padding (D = 17, 24) and both mean_only settings."""
+    from glowtts_b200 import commons
+    gen = torch.Generator().manual_seed(18)
+    x_m = torch.randn(B, D, TX, generator=gen) * 0.7
+    x_logs = torch.zeros(B, D, TX) if mean_only else torch.randn(B, D, TX, generator=gen) * 0.2
+    z = torch.randn(B, D, TY, generator=gen)
+    want = oflow.logp(x_m.double(), x_logs.double(), z.double())
+    env = {"umma": "GTK_LOGP_UMMA", "legacy": "GTK_LOGP_LEGACY", "ffma": "GTK_LOGP_FFMA"}[kernel]
+    os.environ[env] = "1"
+    try:
+        got = commons.logp(x_m.cuda(), None if mean_only else x_logs.cuda(), z.cuda())
+    finally:
+        os.environ.pop(env, None)
+    err = float((got.cpu().double() - want).abs().max())
+    assert err <= 4e-6 * float(want.abs().max()) + 1e-5, (kernel, err, float(want.abs().max()))
+
+
 def test_standalone_coupling_block_and_wn_match_oracle():
     from glowtts_b200 import attentions
     cfg = dict(helpers.TINY_CFG, n_blocks=1, gin_channels=4, kernel_size=3, dilation_rate=2, n_layers=3)
