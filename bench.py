@@ -553,7 +553,8 @@ def run_reference(args):
     cfg = workload_config(1, "f32", "eager-cpu")
     cfg.update({"batch_per_step": b, "batch_per_gpu": None, "global_batch": b, "device": "host CPU",
                 "parallelism": f"{threads} CPU threads (torch intra-op); no GPU",
-                "l2": "n/a (CPU arm)", "kind": "oracle port of the reference modules + reference core.pyx"})
+                "l2": "n/a (CPU arm)", "layout": "padded [B, C, T] tensors, as the reference computes them",
+                "kind": "oracle port of the reference modules + reference core.pyx"})
     print(json.dumps({
         "impl": "reference", "metric": "train_hot_path_mel_frames_per_s", "value": val, "unit": "mel frames/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_sum / args.steps * 1e3,

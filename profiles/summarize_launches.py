@@ -8,12 +8,16 @@ import sys
 lines = [l for l in open(sys.argv[1]) if not l.startswith("==")]
 rows = list(csv.DictReader(lines))
 names = [r["Kernel Name"] for r in rows]
-sq = [i for i, n in enumerate(names) if "squeeze_kernel" in n and "unsqueeze" not in n]
-# each step has a forward squeeze and a backward one; argv[2] = k picks the k-th step from the end (0 = last, which
-# may be cut off by ncu's -c limit)
+# a step starts at the forward pack-plan kernel (round 2: varlen packing; round 1 lists: the forward squeeze kernel)
+sq = [i for i, n in enumerate(names) if "pack_plan_kernel" in n]
+per_step = 1
+if not sq:
+    sq = [i for i, n in enumerate(names) if "squeeze_kernel" in n and "unsqueeze" not in n]
+    per_step = 2
+# argv[2] = k picks the k-th step from the end (0 = last, which may be cut off by ncu's -c limit)
 k = int(sys.argv[2]) if len(sys.argv) > 2 else 0
-start = sq[-2 - 2 * k] if len(sq) >= 2 + 2 * k else 0
-end = sq[-2 * k] if k > 0 else len(rows)
+start = sq[-per_step * (1 + k)] if len(sq) >= per_step * (1 + k) else 0
+end = sq[-per_step * k] if k > 0 else len(rows)
 sel = rows[start:end]
 agg = collections.defaultdict(lambda: [0, 0.0])
 for r in sel:
