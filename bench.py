@@ -46,7 +46,7 @@ NCU_TRAFFIC = {"mas configs[0]": 19.9e6,    # profiles/ncu_mas_cfg1_r01.csv: 19.
                "mas configs[4] on one GPU": 3.383e9,   # profiles/ncu_mas_cfg5_r01.csv: 1.728 GB read + 1.655 GB written (algorithmic 3.277 GB)
                "wn_layer_tc": 23.05e6,      # profiles/ncu_wn_layer_r01.txt: (16.89 + 0.82 MB, 27.50 + 0.89 MB) -> mean bytes / launch
                "wn_bwd_layer_tc": 33.0e6,   # profiles/ncu_wn_bwd_layer_r01.txt: 32.78 MB read + 0.2 MB written per launch
-               "wn_stack_tc": None}
+               "wn_stack_tc": 54.1e6}       # profiles/ncu_wn_stack_r02.txt: 13.1 MB read + 41.0 MB written per launch (training saves)
 
 
 def peaks():
