@@ -310,7 +310,7 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
 struct LogpUmmaCtl {
     uint64_t mma_done;
     uint32_t tmem_base;
-    float crow[UX], zq[UY];
+    float crow[UX], crow2[UX], zq[UY];      // per-token constant (two partial sums, added in a fixed order), per-frame constant
 };
 
 template <bool MEAN_ONLY>
@@ -326,64 +326,90 @@ __global__ void __launch_bounds__(UNT, 3) logp_umma_kernel(const float* __restri
     LogpUmmaCtl* ctl = reinterpret_cast<LogpUmmaCtl*>(b_lo + U_TILE);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int y0 = blockIdx.x * UY, x0 = blockIdx.y * UX, b = blockIdx.z;
-    const int KT = MEAN_ONLY ? D : 2 * D;
-    const int n_chunks = (KT + U_KC - 1) / U_KC;
-
-    // this thread's row: text row x0 + row of A, or frame y0 + row of B
-    const bool is_b = tid >= UX;
-    const int row = is_b ? tid - UX : tid;
-    const int g = (is_b ? y0 : x0) + row, g_n = is_b ? T_y : T_x;
-    const bool ok = g < g_n;
-    const float* src = (is_b ? z + (size_t)b * D * T_y : x_m + (size_t)b * D * T_x) + (ok ? g : 0);
-    const float* lsrc = (MEAN_ONLY || is_b) ? nullptr : x_logs + (size_t)b * D * T_x + (ok ? g : 0);
+    // k layout.  mean_only: k = d, chunks of 32.  General models: chunk c holds d = 16 c .. 16 c + 15 twice -- slots [0, 16) =
+    // (m s)(d) against z(d), slots [16, 32) = (-0.5 s)(d) against z^2(d) -- so that exp(-2 logs) is evaluated once per (row, d).
+    const int n_chunks = MEAN_ONLY ? (D + U_KC - 1) / U_KC : (D + 15) / 16;
 
     if (tid == 0) { mbar_init(&ctl->mma_done, 1); mbar_fence_init(); }
     if (warp == 0) tc::tmem_alloc<128>(&ctl->tmem_base);
 
-    float cst = 0.f;                                  // A: per-token constant; B (mean_only): sum_d z^2
-    float v[U_KC];
-    auto load_chunk = [&](int c) {                    // operand values k = 32 c .. 32 c + 31 of this row (and the constants)
+    // Thread <-> rows.  mean_only: thread = one row (threads 0..127 text rows of A, 128..255 frames of B), all 32 slots of
+    // a chunk.  General: thread = text row AND frame `tid % 128`, the 8 d's of half `tid / 128` of the chunk for both
+    // operands (the expf work is spread over all 256 threads).
+    const bool is_b = MEAN_ONLY && tid >= UX;
+    const int row = tid % UX, half = tid / UX;
+    const int gx = x0 + row, gy = y0 + row;
+    const bool okx = gx < T_x, oky = gy < T_y;
+    const float* srcm = x_m + (size_t)b * D * T_x + (okx ? gx : 0);
+    const float* srcl = MEAN_ONLY ? nullptr : x_logs + (size_t)b * D * T_x + (okx ? gx : 0);
+    const float* srcz = z + (size_t)b * D * T_y + (oky ? gy : 0);
+
+    float cst = 0.f;                                  // per-token constant (partial); mean_only B rows: sum_d z^2
+    float v[U_KC];                                    // general: v[0..15] = A values (m s | -0.5 s), v[16..31] = B values (z | z^2)
+    auto load_chunk = [&](int c) {
+        if constexpr (MEAN_ONLY) {
 #pragma unroll
-        for (int i = 0; i < U_KC; ++i) {
-            const int k = c * U_KC + i;
-            float val = 0.f;
-            if (ok && k < KT) {
-                const int d = (MEAN_ONLY || k < D) ? k : k - D;
-                const float a = __ldg(src + (size_t)d * g_n);
-                if (is_b) {
-                    val = (MEAN_ONLY || k < D) ? a : a * a;
-                    if (MEAN_ONLY) cst = fmaf(a, a, cst);
-                } else if (MEAN_ONLY) {
-                    val = a;
-                    cst = fmaf(a, a, cst);
-                } else {
-                    const float l = __ldg(lsrc + (size_t)d * g_n);
-                    const float sc = expf(-2.f * l);
-                    val = (k < D) ? a * sc : -0.5f * sc;
-                    if (k < D) cst += -0.918938533204672742f - l - 0.5f * a * a * sc;
+            for (int i = 0; i < U_KC; ++i) {
+                const int d = c * U_KC + i;
+                float val = 0.f;
+                if (d < D && (is_b ? oky : okx)) {
+                    val = __ldg((is_b ? srcz : srcm) + (size_t)d * (is_b ? T_y : T_x));
+                    cst = fmaf(val, val, cst);
                 }
+                v[i] = val;
             }
-            v[i] = val;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int d = c * 16 + half * 8 + i;
+                float ms = 0.f, hs = 0.f, zz = 0.f;
+                if (d < D) {
+                    if (okx) {
+                        const float m = __ldg(srcm + (size_t)d * T_x), l = __ldg(srcl + (size_t)d * T_x);
+                        const float sc = expf(-2.f * l);
+                        ms = m * sc;
+                        hs = -0.5f * sc;
+                        cst += -0.918938533204672742f - l - 0.5f * m * m * sc;
+                    }
+                    if (oky) zz = __ldg(srcz + (size_t)d * T_y);
+                }
+                v[i] = ms; v[8 + i] = hs; v[16 + i] = zz; v[24 + i] = zz * zz;
+            }
         }
+    };
+    auto put_quad = [&](unsigned char* t_hi, unsigned char* t_lo, int quad, const float* q) {
+        uint32_t h[4], l[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { h[i] = tf32_hi(q[i]); l[i] = tf32_lo(q[i], h[i]); }
+        const size_t off = (size_t)row * 128 + (size_t)((quad ^ (row & 7)) << 4);
+        *reinterpret_cast<uint4*>(t_hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(t_lo + off) = make_uint4(l[0], l[1], l[2], l[3]);
     };
     load_chunk(0);
     const uint32_t idesc = umma_idesc_tf32(UX, UY);
-    unsigned char* t_hi = is_b ? b_hi : a_hi;
-    unsigned char* t_lo = is_b ? b_lo : a_lo;
     for (int c = 0; c < n_chunks; ++c) {
         if (c > 0) mbar_wait(&ctl->mma_done, (c - 1) & 1);          // the MMAs of the previous chunk have read the staging area
+        if constexpr (MEAN_ONLY) {
 #pragma unroll
-        for (int sl = 0; sl < U_KC / 4; ++sl) {
-            uint32_t h[4], l[4];
+            for (int sl = 0; sl < U_KC / 4; ++sl) put_quad(is_b ? b_hi : a_hi, is_b ? b_lo : a_lo, sl, v + 4 * sl);
+        } else {
+            // slots [8 half, 8 half + 8) and [16 + 8 half, 16 + 8 half + 8) of both operands
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { h[i] = tf32_hi(v[4 * sl + i]); l[i] = tf32_lo(v[4 * sl + i], h[i]); }
-            const size_t off = (size_t)row * 128 + (size_t)((sl ^ (row & 7)) << 4);
-            *reinterpret_cast<uint4*>(t_hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
-            *reinterpret_cast<uint4*>(t_lo + off) = make_uint4(l[0], l[1], l[2], l[3]);
+            for (int u = 0; u < 2; ++u) {
+                put_quad(a_hi, a_lo, 2 * half + u, v + 4 * u);
+                put_quad(a_hi, a_lo, 4 + 2 * half + u, v + 8 + 4 * u);
+                put_quad(b_hi, b_lo, 2 * half + u, v + 16 + 4 * u);
+                put_quad(b_hi, b_lo, 4 + 2 * half + u, v + 24 + 4 * u);
+            }
         }
         if (c + 1 == n_chunks) {
-            if (is_b) ctl->zq[row] = MEAN_ONLY ? -0.5f * cst : 0.f;
-            else ctl->crow[row] = MEAN_ONLY ? -0.5f * cst - (float)D * 0.918938533204672742f : cst;
+            if constexpr (MEAN_ONLY) {
+                if (is_b) { ctl->zq[row] = -0.5f * cst; }
+                else { ctl->crow[row] = -0.5f * cst - (float)D * 0.918938533204672742f; ctl->crow2[row] = 0.f; }
+            } else {
+                if (half == 0) { ctl->crow[row] = cst; ctl->zq[row] = 0.f; }
+                else ctl->crow2[row] = cst;
+            }
         }
         tc::fence_proxy_async_smem();
         tc::tc_fence_before();
@@ -414,7 +440,7 @@ __global__ void __launch_bounds__(UNT, 3) logp_umma_kernel(const float* __restri
         const int q = warp & 3, half = warp >> 2;
         const int r = q * 32 + lane, x = x0 + r;
         const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 64);
-        const float c = ctl->crow[r];
+        const float c = ctl->crow[r] + ctl->crow2[r];
         float* orow = out + ((size_t)b * T_x + (x < T_x ? x : 0)) * T_y + y0 + half * 64;
         const bool vec = ((T_y & 3) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
 #pragma unroll
@@ -455,13 +481,9 @@ int forward(const float* x_m, const float* x_logs, const float* z, float* out, i
             cudaStream_t st) {
     GTK_REQUIRE(x_m && z && out, "null");
     if ((long long)B * T_x * T_y == 0) return GTK_OK;
-    // tcgen05 kind::tf32 kernel: mean_only models (every configs/base*.json; 33 us at B = 32, 180 x 860, the same as the
-    // mma.sync kernel it replaces there), and general models the mma.sync kernel does not cover.  With x_logs the row-owner
-    // staging pays 2 D expf per text row on 128 of the 256 threads (141 us against 52 us): those shapes stay on the
-    // mma.sync kernel.  GTK_LOGP_UMMA=1 forces tcgen05 everywhere, GTK_LOGP_LEGACY=1 / GTK_LOGP_FFMA=1 the older kernels.
-    const bool legacy_ok = D % 8 == 0 && D >= 8 && D <= TC_MAX_D;
-    if (D >= 1 && D <= 256 && !getenv("GTK_LOGP_FFMA") && !getenv("GTK_LOGP_LEGACY") &&
-        (x_logs == nullptr || !legacy_ok || getenv("GTK_LOGP_UMMA"))) {
+    // tcgen05 kind::tf32 kernel: the default (B = 32, 180 x 860 on B200: mean_only 33 us, general models 46 us against 52 us
+    // for the mma.sync kernel).  GTK_LOGP_LEGACY=1 selects the mma.sync kernel, GTK_LOGP_FFMA=1 the FFMA one.
+    if (D >= 1 && D <= 256 && !getenv("GTK_LOGP_FFMA") && !getenv("GTK_LOGP_LEGACY")) {
         const bool mo = x_logs == nullptr;
         const size_t smem = logp_umma_smem();
         dim3 grid(ceil_div(T_y, UY), ceil_div(T_x, UX), B);
