@@ -183,7 +183,6 @@ struct WnBwdParams {
     float* out_f32;                // fp32 carry written for the layer below (tile-private layout, ld = H)
     const int* n_rows;             // varlen packing (pack.cu), or null
     const int* row_fr;
-    int three_chains;              // set by the launcher: GEMM b on three accumulator chains (H = 192)
     __nv_bfloat16* dpre;           // [B,T,2H] frames or null: gate-input gradient BEFORE the dropout scale (what the
                                    // conditioners' gradients are reduced from when p_dropout > 0; == d(xin) when it is 0)
 };

@@ -101,8 +101,6 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
     if (!is_producer) pdl_wait();
     const uint32_t tmem = ctl->tmem_base;
     const uint32_t idesc = umma_idesc_bf16(BT, H);
-    const uint32_t idesc_128 = umma_idesc_bf16(BT, 128), idesc_64 = umma_idesc_bf16(BT, 64);
-    const bool three = (H == 192) && p.three_chains;    // GEMM b on three accumulator chains (see the MMA warp)
     WB_TRACE(1);
 
     // ---------------------------------------------------------------- TMA producer.  Whole warp in the uniform loops, ONE
@@ -288,27 +286,9 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
             const uint32_t b_addr = smem_u32(ring + (size_t)s * sb_bytes);
             if (elect_one()) {
                 const uint64_t adesc = umma_desc_kmajor_sw128(a_addr), bdesc = umma_desc_kmajor_sw128(b_addr);
-                if (three) {
-                    // H = 192: THREE accumulator chains instead of two (an accumulator accepts its next MMA only ~193 cycles
-                    // after the previous one: two chains of N = 192 run at ~147 cycles per k16 step against 96 of tensor-pipe
-                    // time).  S0 = columns [0, 192), S1 = [192, 384), S2 = [384, 512) holds output channels 0..127 only: k16
-                    // step n goes to S0, S1, or (n % 3 == 2) to S2 as N = 128 with its channels 128..191 as an N = 64 MMA into
-                    // S0 and S1 alternately.  Epilogue b adds the three.
 #pragma unroll
-                    for (int k = 0; k < KC / 16; ++k) {
-                        const int n = it * (KC / 16) + k, ph = n % 3;
-                        if (ph == 0) umma_bf16(tm, adesc + 2 * k, bdesc + 2 * k, idesc, n != 0);
-                        else if (ph == 1) umma_bf16(tm + 192, adesc + 2 * k, bdesc + 2 * k, idesc, n != 1);
-                        else {
-                            umma_bf16(tm + 384, adesc + 2 * k, bdesc + 2 * k, idesc_128, n != 2);
-                            umma_bf16(tm + (((n / 3) & 1) ? 192 : 0) + 128, adesc + 2 * k, bdesc + 2 * k + (128 * 128 >> 4), idesc_64, true);
-                        }
-                    }
-                } else {
-#pragma unroll
-                    for (int k = 0; k < KC / 16; ++k)
-                        umma_bf16(tm + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, it != 0 || k >= 2);
-                }
+                for (int k = 0; k < KC / 16; ++k)
+                    umma_bf16(tm + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idesc, it != 0 || k >= 2);
                 umma_commit_multicast(&ctl->empty_b[s], cl_mask);
             }
             __syncwarp();
@@ -345,17 +325,7 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
             if (cc >= cc_hi) break;
             const int c0 = cc * 16;
             float v[16];
-            if (three) {
-                tmem_ld16_sum(trow + c0, trow + 192 + c0, v);
-                if (c0 < 128) {
-                    float w3[16];
-                    tmem_ld16(trow + 384 + c0, w3);
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] += w3[i];
-                }
-            } else {
-                tmem_ld16_dual(trow + c0, true, v);
-            }
+            tmem_ld16_dual(trow + c0, true, v);
             if (!ok) continue;
             if (p.resid_f32) {
                 float (&x)[16] = xpre[ci];
@@ -408,12 +378,6 @@ int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat1
     GTK_REQUIRE(p.taps >= 1 && (p.taps & 1) && p.dil >= 1 && wn_bwd_supported(p.H, p.taps, p.dil), "conv shape not supported by the fused backward");
     GTK_REQUIRE(ld_drs % 8 == 0 && ld_out % 8 == 0 && ld_drs >= p.RS && ld_out >= p.H, "frame pitch");
     if (p.B == 0 || p.T == 0) return GTK_OK;
-    {   // GTK_WB_THREE_CHAINS=1: GEMM b on three accumulator chains (opt-in; read per call).  Measured on B200, bench workload:
-        // 1.76 ms per step against 1.59 ms for two chains -- the N = 128 + N = 64 MMAs of every third k16 step cost more
-        // issue time (~75-80 cycles each whatever their width) than the third chain saves in accumulator turn-around.
-        const char* e = getenv("GTK_WB_THREE_CHAINS");
-        p.three_chains = (e && e[0] == '1');
-    }
     const int H = p.H, halo = (p.taps / 2) * p.dil, tile_out = BT - 2 * halo;
     const int rs_pad = ceil_div(p.RS, KC) * KC;
     CUtensorMap tmDrs, tmWrs, tmWin, tmDxin, tmOut;
