@@ -41,7 +41,7 @@ static WnG wn_grads(const gtk_block_grads& P, int id) {
     return WnG{Q.in_g, Q.in_v, Q.in_b, Q.rs_g, Q.rs_v, Q.rs_b, Q.c1_g, Q.c1_v, Q.c1_b};
 }
 struct TcLayout {          // byte offsets in the workspace
-    size_t mask_sq, x_len, winv, icld, we, pack, X, act, hf[2], hx, skipf, xmix_alt, bwd, total;
+    size_t mask_sq, x_len, winv, icld, we, pack, X, act, hf[2], hx, skipf, bwd, total;
     int stack, st_lead, st_halo, st_out;  // wn_stack.cu covers this WaveNet shape: window geometry
     size_t hdr, off, row_b, row_fr;      // varlen packing plan (pack.cu): {0, n_rows}, off[B+1], row_b[P], row_fr[P]; mask_sq = mask_p[P]
     size_t trk[TC_MAX_WN], dtrk[TC_MAX_WN];   // packed pitch / energy samples [P, n_sqz] of chain slots >= 1, and their gradients
@@ -131,7 +131,6 @@ static void make_tc_layout(const Dims& D, const Layout& L32, int train, TcLayout
     L->hf[1] = take((size_t)H * nqp * 4);
     L->hx = (L->stack && D.n_wn > 2) ? take((size_t)H * nqp * 4) : 0;   // second fp32 exchange buffer between chained WaveNets
     L->skipf = take((size_t)H * nqm * 4);
-    L->xmix_alt = train ? 0 : take((size_t)C * nq * 4);     // inference forward: second mixed-input buffer (fused mix ping-pong)
     L->bwd = off;
     if (train) {
         L->b_dZ = take((size_t)C * nq * 4);
@@ -241,21 +240,9 @@ static TcPlan tc_plan(const TcLayout& L, unsigned char* ws) {
 
 // start -> WN -> end(+affine) of one block on the packed rows.  xc = mixed block input (t-major fp32 [C, P]),
 // zout = block output.
-// The mix (ActNorm + InvConvNear, or its inverse) the whole-WaveNet kernel applies to the coupling output in its affine
-// epilogue: forward = the NEXT block's mix, reverse = this block's inverse mix.  out == null: nothing fused.
-// Opt-in (GTK_WN_STACK_MIX=1): measured on B200 (B = 32, T = 860) it saves 11 launches per pass and no time -- step 4.29 ->
-// 4.33 ms, reverse flow 1.32 -> 1.34 ms: the mix then runs in the tail of a kernel that occupies 92 SMs instead of as a
-// 6 us kernel on all 148.  Results are bit-identical either way (tests/test_gpu_stack_r2.py runs both).
-struct TcMixNext { float* out; const float* logs; const float* bias; const float* M; int reverse; };
-static bool tc_mix_fusable(const Dims& D, const TcLayout& L) {
-    const char* e = getenv("GTK_WN_STACK_MIX");
-    return L.stack && tc::wn_stack_enabled() && tc::wn_stack_end_ok(D.H, D.C) && D.NS == 4 && D.C <= 256 &&
-           !(getenv("GTK_WN_STACK_END") && getenv("GTK_WN_STACK_END")[0] == '0') && (e && e[0] == '1');
-}
-
 static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout& L, const gtk_block_params& P, const bf16* pk,
                        const float* xc, float* zout, float* logdet, const TcPlan& pl, unsigned char* act, unsigned char* ws,
-                       int reverse, int save, int blk, cudaStream_t st, const TcMixNext* mixn = nullptr) {
+                       int reverse, int save, int blk, cudaStream_t st) {
     const int B = 1, T = L.P, H = D.H, C = D.C, Ch = D.C / 2;
     const float* mask = pl.mask_p;
     const TcPack& Q = L.P_;
@@ -298,10 +285,6 @@ static int tc_coupling(const gtk_decoder_desc* d, const Dims& D, const TcLayout&
                 p.aff_x = xc; p.aff_z = zout; p.aff_logdet = reverse ? nullptr : logdet;
                 p.aff_logs_save = save ? reinterpret_cast<float*>(act + A.logs) : nullptr;
                 p.aff_reverse = reverse; p.aff_sigmoid_scale = d->sigmoid_scale;
-                if (mixn && mixn->out) {
-                    p.mix_out = mixn->out; p.mix_logs = mixn->logs; p.mix_bias = mixn->bias; p.mix_M = mixn->M;
-                    p.mix_reverse = mixn->reverse;
-                }
             }
             io.skip_out = reinterpret_cast<bf16*>(act + A.skip_bf[w]);
             for (int i = 0; i < D.L; ++i) {
@@ -407,7 +390,6 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
                 GTK_TRY(tc::zero_guard_rows(reinterpret_cast<bf16*>(ws + L.act + L.A.skip_bf[w]), 0, 1, L.A.total, D.NB, D.H,
                                             pl.n_rows(), 64, L.P, st));
         }
-    const bool mix_fused = tc_mix_fusable(D, L);
     for (int blk = 0; blk < D.NB; ++blk) {
         const gtk_block_params& P = blocks[blk];
         GTK_TRY(check_block(D, P));
@@ -416,24 +398,9 @@ static int tc_forward(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
         bf16* pk = reinterpret_cast<bf16*>(ws + L.pack) + (size_t)blk * L.P_.total;
         const float* xin = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? blk : (blk & 1)) * L.x_bytes);
         float* xout = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? blk + 1 : ((blk + 1) & 1)) * L.x_bytes);
-        // mixed block input: per block when training; inference ping-pongs between two buffers (a fused mix writes the
-        // next block's input while other windows still read this one's)
-        auto xmix_of = [&](int k) {
-            return train ? reinterpret_cast<float*>(ws + L.act + (size_t)k * L.A.total + L.A.xmix)
-                         : ((k & 1) ? reinterpret_cast<float*>(ws + L.xmix_alt) : reinterpret_cast<float*>(ws + L.act + L.A.xmix));
-        };
-        float* xmix = xmix_of(blk);
-        if (blk == 0 || !mix_fused)
-            GTK_TRY(flow::mix(xin, pl.mask_p, P.an_logs, P.an_bias, P.ic_weight, D.NS, xmix, 1, D.C, L.P, 0, st, pl.n_rows()));
-        TcMixNext mixn = {nullptr, nullptr, nullptr, nullptr, 0};
-        if (mix_fused && blk + 1 < D.NB) {
-            const gtk_block_params& Pn = blocks[blk + 1];
-            GTK_TRY(check_block(D, Pn));
-            mixn.out = xmix_of(blk + 1); mixn.logs = Pn.an_logs; mixn.bias = Pn.an_bias; mixn.M = Pn.ic_weight;
-        }
-        // the un-mixed block output is read by the backward (training) and by the final unsqueeze (last block) only
-        float* zdst = (mixn.out && !train) ? nullptr : xout;
-        GTK_TRY(tc_coupling(d, D, L, P, pk, xmix, zdst, logdet, pl, act, ws, 0, train, blk, st, &mixn));
+        float* xmix = reinterpret_cast<float*>(act + L.A.xmix);
+        GTK_TRY(flow::mix(xin, pl.mask_p, P.an_logs, P.an_bias, P.ic_weight, D.NS, xmix, 1, D.C, L.P, 0, st, pl.n_rows()));
+        GTK_TRY(tc_coupling(d, D, L, P, pk, xmix, xout, logdet, pl, act, ws, 0, train, blk, st));
     }
     const float* xfin = reinterpret_cast<float*>(ws + L.X + (size_t)(train ? D.NB : (D.NB & 1)) * L.x_bytes);
     GTK_TRY(flow::unsqueeze_unpack(xfin, pl.off, z, D.B, D.Cin, D.Tq * D.n, D.n, L.G, L.P, st));
@@ -456,7 +423,6 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
     unsigned char* act = ws + L.act;
     cudaEvent_t* packs_done = nullptr;
     GTK_TRY(tc_pack_split(D, L, blocks, reinterpret_cast<bf16*>(ws + L.pack), 0, D.NB - 1, st, &packs_done));
-    const bool mix_fused = tc_mix_fusable(D, L);
     GTK_TRY(flow::pack_plan(mask, D.B, D.T, D.n, D.Tq, L.G, L.P, pl.hdr, pl.off, pl.row_b, pl.row_fr, pl.mask_p, pl.x_len, st));
     GTK_TRY(flow::squeeze_pack(z, pl.off, pl.row_b, pl.mask_p, xa, D.Cin, D.T, D.n, L.P, st));
     for (int w = 1; w < D.n_wn; ++w)
@@ -469,14 +435,8 @@ static int tc_reverse(const gtk_decoder_desc* d, const Dims& D, const gtk_block_
         if (blk == D.NB - 2 && packs_done) GTK_CUDA(cudaStreamWaitEvent(st, *packs_done, 0));
         float* winv = reinterpret_cast<float*>(ws + L.winv) + (size_t)blk * 64;
         const bf16* pk = reinterpret_cast<const bf16*>(ws + L.pack) + (size_t)blk * L.P_.total;
-        if (mix_fused) {       // coupling inverse + this block's inverse mix in one kernel: xa -> xb, then swap
-            TcMixNext mixn = {xb, P.an_logs, P.an_bias, winv, 1};
-            GTK_TRY(tc_coupling(d, D, L, P, pk, xa, nullptr, nullptr, pl, act, ws, 1, 0, blk, st, &mixn));
-            float* t = xa; xa = xb; xb = t;
-        } else {
-            GTK_TRY(tc_coupling(d, D, L, P, pk, xa, xb, nullptr, pl, act, ws, 1, 0, blk, st));
-            GTK_TRY(flow::mix(xb, pl.mask_p, P.an_logs, P.an_bias, winv, D.NS, xa, 1, D.C, L.P, 1, st, pl.n_rows()));
-        }
+        GTK_TRY(tc_coupling(d, D, L, P, pk, xa, xb, nullptr, pl, act, ws, 1, 0, blk, st));
+        GTK_TRY(flow::mix(xb, pl.mask_p, P.an_logs, P.an_bias, winv, D.NS, xa, 1, D.C, L.P, 1, st, pl.n_rows()));
     }
     GTK_TRY(flow::unsqueeze_unpack(xa, pl.off, x, D.B, D.Cin, D.Tq * D.n, D.n, L.G, L.P, st));
     return GTK_OK;

@@ -142,14 +142,6 @@ struct WnStackParams {
     float* aff_logdet;
     float* aff_logs_save;
     int aff_reverse, aff_sigmoid_scale;
-    // has_end, n_split = 4: ActNorm + InvConvNear of the NEXT flow block (forward; modules.py:584-599, 635-665) or the inverse
-    // mix of this block (reverse) applied to the coupling output in the same epilogue: mix_out[b, c, t] t-major.  aff_z may
-    // then be null (nobody reads the un-mixed output).  mix_M: [4][4] (W, or W^-1 in reverse); null pieces are skipped.
-    float* mix_out;
-    const float* mix_logs;
-    const float* mix_bias;
-    const float* mix_M;
-    int mix_reverse;
     WnStackLayer layer[WS_MAX_LAYERS];
 };
 struct WnStackMaps {

@@ -31,8 +31,6 @@
 namespace gtk {
 namespace tc {
 
-constexpr int WS_MIX_FLOATS = 256 + 256 + 16;
-
 struct WsCtl {
     uint64_t full[WS_STAGES], empty[WS_STAGES], acc_full, acts_ready, tile_ready, tile_tma;
     uint32_t tmem_base;
@@ -92,8 +90,7 @@ wn_stack_kernel(const __grid_constant__ WnStackMaps tm, const __grid_constant__ 
     float* cst = reinterpret_cast<float*>(ring + (size_t)WS_STAGES * stage_bytes);   // [L][bias_in | bias_rs | cw | cb][2H], bias_start[H]
     float* c_start = cst + (size_t)L * 4 * H2;
     float* c_end = c_start + H;                                          // bias of `end` [256]
-    float* c_mix = c_end + 256;                                          // fused mix: e^(+-logs) [256], bias [256], M [16]
-    WsCtl* ctl = reinterpret_cast<WsCtl*>(c_mix + WS_MIX_FLOATS);
+    WsCtl* ctl = reinterpret_cast<WsCtl*>(c_end + 256);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wi = blockIdx.x, b = blockIdx.y;
@@ -134,13 +131,6 @@ wn_stack_kernel(const __grid_constant__ WnStackMaps tm, const __grid_constant__ 
     }
     if (p.has_end)
         for (int i = threadIdx.x; i < p.C_end; i += EPI_NT) c_end[i] = p.bias_end[i];
-    if (p.mix_out) {                                  // ActNorm / InvConvNear constants of the fused mix (flow_pointwise.cu: mix_kernel)
-        for (int i = threadIdx.x; i < p.C_end; i += EPI_NT) {
-            c_mix[i] = p.mix_logs ? expf(p.mix_reverse ? -p.mix_logs[i] : p.mix_logs[i]) : 1.f;
-            c_mix[256 + i] = p.mix_bias ? p.mix_bias[i] : 0.f;
-        }
-        if (threadIdx.x < 16) c_mix[512 + threadIdx.x] = p.mix_M ? p.mix_M[threadIdx.x] : ((threadIdx.x / 4 == threadIdx.x % 4) ? 1.f : 0.f);
-    }
     if (p.has_start) {
         for (int i = threadIdx.x; i < H; i += EPI_NT) c_start[i] = p.bias_start[i];
         // the lead-in / lead-out rows are only ever read (by the outermost taps): give them a finite value once
@@ -550,36 +540,12 @@ wn_stack_kernel(const __grid_constant__ WnStackMaps tm, const __grid_constant__ 
                 float ll = lg[i] + c_end[Ch + c];
                 lsave[i] = ll;                             // raw end-conv output (pre sigmoid_scale), as the fp32 path keeps it
                 if (p.aff_sigmoid_scale) ll = __logf(1e-6f + sigmoid_f(ll + 2.f));
+                az[o0 + (size_t)i * p.T] = x0[i];
                 if (p.aff_reverse) {
-                    x1[i] = live ? (x1[i] - mm) * __expf(-ll) : 0.f;
+                    az[o1 + (size_t)i * p.T] = live ? (x1[i] - mm) * __expf(-ll) : 0.f;
                 } else {
-                    x1[i] = live ? mm + __expf(ll) * x1[i] : 0.f;
+                    az[o1 + (size_t)i * p.T] = live ? mm + __expf(ll) * x1[i] : 0.f;
                     ld_sum += live ? ll : 0.f;
-                }
-                if (az) { az[o0 + (size_t)i * p.T] = x0[i]; az[o1 + (size_t)i * p.T] = x1[i]; }
-            }
-            if (p.mix_out) {
-                // ActNorm + InvConvNear of the NEXT flow block (forward) / inverse mix of this block (reverse) on the coupling
-                // output, n_split = 4: group g = channels {2g, 2g+1} of either half (flow_pointwise.cu: mix_channel) -- all
-                // four live in this thread's chunk.  Same expressions as mix_kernel: bit-identical results.
-                float* __restrict__ mo = p.mix_out;
-#pragma unroll
-                for (int gi = 0; gi < 8; ++gi) {
-                    const int ca = c0 + 2 * gi;            // first-half channel of member 0
-                    float y[4];
-                    const float vin[4] = {x0[2 * gi], x0[2 * gi + 1], x1[2 * gi], x1[2 * gi + 1]};
-                    const int chn[4] = {ca, ca + 1, Ch + ca, Ch + ca + 1};
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        y[j] = (!p.mix_reverse && p.mix_logs) ? c_mix[256 + chn[j]] + c_mix[chn[j]] * vin[j] : vin[j];
-#pragma unroll
-                    for (int a = 0; a < 4; ++a) {
-                        float acc = 0.f;
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) acc += c_mix[512 + a * 4 + j] * y[j];
-                        if (p.mix_reverse && p.mix_logs) acc = (acc - c_mix[256 + chn[a]]) * c_mix[chn[a]];
-                        mo[((size_t)b * C + chn[a]) * p.T + t] = acc * mk;
-                    }
                 }
             }
             if (p.aff_logs_save) {
@@ -623,7 +589,7 @@ static size_t ws_smem_bytes(int H, int L, int lead) {
     const int n_kh = H / KC;
     const size_t pitch = ((size_t)(BT + 2 * lead) * 128 + 1023) & ~(size_t)1023;
     const size_t stage = (size_t)((2 * H * KC * 2) > (A_BYTES + H * KC * 2) ? (2 * H * KC * 2) : (A_BYTES + H * KC * 2));
-    return (size_t)n_kh * pitch + WS_STAGES * stage + ((size_t)L * 4 * 2 * H + H + 256 + WS_MIX_FLOATS) * sizeof(float) + sizeof(WsCtl) + 1024;
+    return (size_t)n_kh * pitch + WS_STAGES * stage + ((size_t)L * 4 * 2 * H + H + 256) * sizeof(float) + sizeof(WsCtl) + 1024;
 }
 
 // Window geometry of a WaveNet with L layers, kernel K, dilation rate dr; false if the stack kernel does not cover it.
@@ -712,7 +678,7 @@ int wn_stack_launch(const WnStackIo& io, WnStackParams p, cudaStream_t st) {
     }
     GTK_TRY(frames_map(&tm.skip_out, io.skip_out, H, H, p.tile_out));
     if (p.has_end) {
-        GTK_REQUIRE(io.wend && p.bias_end && p.aff_x && (p.aff_z || p.mix_out) && wn_stack_end_ok(H, p.C_end),
+        GTK_REQUIRE(io.wend && p.bias_end && p.aff_x && p.aff_z && wn_stack_end_ok(H, p.C_end),
                     "`end` conv arguments (in_channels * n_sqz must be a multiple of 32 and fit a ring stage)");
         const uint64_t dims[2] = {(uint64_t)H, (uint64_t)p.C_end};
         const uint64_t strides[1] = {(uint64_t)H * 2};
