@@ -269,26 +269,26 @@ def timed(fn, steps, world):
 
 
 def kernel_spans():
-    """Busy span (us) of the LAST launch of the fused WaveNet-layer kernels in the step that just ran, from the
-    globaltimer stamps every CTA leaves (first CTA past its preamble / griddepcontrol.wait -> last CTA done).  Unlike the
-    event-bracketed eager pass this is the kernel as it runs inside the replayed graph, overlapped launches included."""
-    import ctypes
-
-    import numpy as np
-    from glowtts_b200 import _lib
-    out = {}
-    n_ctas = B_PER_GPU * ((T_MEL // 2 + 127) // 128)
-    for tag, sym, n in (("wn_layer_tc", "gtk_debug_wn_trace", 6), ("wn_bwd_layer_tc", "gtk_debug_wb_trace", 7)):
-        try:
-            buf = (ctypes.c_ulonglong * (n_ctas * n))()
-            torch.cuda.synchronize()
-            _lib.call(sym, buf, n_ctas)
-            t = np.array(list(buf), dtype=np.int64).reshape(n_ctas, n)
-            t = t[t[:, 0] > 0]
-            out[tag] = float(t[:, n - 1].max() - t[:, 1].min()) / 1e3
-        except Exception as e:                              # debug entry points: never hide the main numbers
-            out[tag] = None
-    return out
+    """Busy span (us) of the LAST launch of the whole-WaveNet forward kernel and of the fused layer backward inside the
+    REPLAYED CUDA GRAPH of the step (first CTA past griddepcontrol.wait -> last CTA done), from the per-CTA globaltimer
+    stamps of the -DGTK_INSTRUMENT library variant (profiles/_instr, built by __graft_entry__.build()).  The product library
+    carries no stamps, so the measurement runs in a child process that loads the variant through GTK_LIB
+    (profiles/ws_span_in_graph.py).  Unlike the event-bracketed eager pass this is the kernel as it runs in the timed
+    region: PDL-overlapped prologue excluded, same clocks."""
+    root = os.path.dirname(os.path.abspath(__file__))
+    lib = os.path.join(root, "profiles", "_instr", "libglowtts_b200.so")
+    if not os.path.exists(lib):
+        return {}
+    try:
+        env = dict(os.environ, GTK_LIB=lib)
+        for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
+            env.pop(k, None)
+        out = subprocess.run([sys.executable, os.path.join(root, "profiles", "ws_span_in_graph.py"), "--json"], env=env,
+                             capture_output=True, text=True, timeout=240, cwd=root)
+        line = [l for l in out.stdout.splitlines() if l.startswith("{")][-1]
+        return json.loads(line)
+    except Exception:                                       # diagnostic: never hide the main numbers
+        return {}
 
 
 def mas_alone(device, steps=20, B=32, TX=T_TEXT, TY=T_MEL, n_buf=8, name="configs[0]", world=1, want_path=True):
@@ -627,7 +627,7 @@ def main():
     launches = _lib.launch_count() - n0
     if run.graphed is not None:                            # replays do not pass through the library's host counter
         launches = run.graphed.launches * args.steps
-    spans = kernel_spans() if rank == 0 else {}            # in-kernel stamps of the last graph-replayed launches
+    spans = {}
     ms_e2e = timed(run.step_e2e, args.steps, world)
     clk = clocks.stop() if rank == 0 else None
 
@@ -681,6 +681,8 @@ def main():
         leg("prosody", lambda: prosody_step(device, world, args.precision, not args.no_graph, args.steps, args.warmup,
                                             ms_res / args.steps))
 
+    if rank == 0 and world == 1 and run_graphed and args.precision == "bf16":
+        spans = kernel_spans()                             # child process with the instrumented library variant
     if rank == 0:
         pk = peaks()
         s_res, s_e2e = ms_res / args.steps * 1e-3, ms_e2e / args.steps * 1e-3
@@ -715,9 +717,11 @@ def main():
                        "behind a 12 ms device-side spin so that the stream never runs dry (no host launch latency inside a pair)",
                 "kernel_span_us_in_graph": spans.get(tag),
                 "frac_by_span": (flop_per_launch / (spans[tag] * 1e-6) / 1e12 / pk["tc_sustained"]) if spans.get(tag) else None,
-                "span_note": "busy span of the step's last launch of this kernel inside the replayed CUDA graph (PDL-overlapped "
-                             "launches), from per-CTA globaltimer stamps; the event-bracketed figure above includes launch "
-                             "and event overhead of the eager pass",
+                "span_note": "busy span of the step's last launch of this kernel inside the replayed CUDA graph (first CTA past "
+                             "griddepcontrol.wait -> last CTA done), per-CTA globaltimer stamps of the instrumented library "
+                             "variant in a child process; the event-bracketed figure above is the stand-alone launch, "
+                             "prologue and launch latency included",
+                "spans_us_in_graph": spans or None,
                 "by_tag_ms_per_step": {k: v[1] / max(prof_steps, 1) for k, v in sorted(prof.items())}}
         step_flop = 3.0 * FLOP_PER_SQ_FRAME_FWD * CFG["n_blocks"] * sq_frames_padded
         out = {

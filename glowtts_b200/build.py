@@ -42,8 +42,8 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
-def _compile(src, obj, verbose):
-    cmd = [NVCC, *ARCH, *CFLAGS, "-c", src, "-o", obj]
+def _compile(src, obj, verbose, extra=()):
+    cmd = [NVCC, *ARCH, *CFLAGS, *extra, "-c", src, "-o", obj]
     proc = subprocess.run(cmd, capture_output=True, text=True)
     log = proc.stdout + proc.stderr
     with open(obj + ".log", "w") as f:
@@ -55,27 +55,39 @@ def _compile(src, obj, verbose):
     return obj
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    os.makedirs(LIBDIR, exist_ok=True)
-    os.makedirs(OBJDIR, exist_ok=True)
+def build(force: bool = False, verbose: bool = False, libdir: str = None, objdir: str = None, extra_cflags=()) -> str:
+    libdir, objdir = libdir or LIBDIR, objdir or OBJDIR
+    lib = os.path.join(libdir, "libglowtts_b200.so")
+    os.makedirs(libdir, exist_ok=True)
+    os.makedirs(objdir, exist_ok=True)
     headers = _headers()
     jobs = []
     objs = []
     for src in _sources():
-        obj = os.path.join(OBJDIR, os.path.basename(src)[:-3] + ".o")
+        obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
         if force or _stale(obj, [src] + headers):
             jobs.append((src, obj))
     if jobs:
         with concurrent.futures.ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
-            for fut in [ex.submit(_compile, s, o, verbose) for s, o in jobs]:
+            for fut in [ex.submit(_compile, s, o, verbose, tuple(extra_cflags)) for s, o in jobs]:
                 fut.result()
-    if jobs or force or _stale(LIB, objs):
-        cmd = [NVCC, *ARCH, "-shared", "-o", LIB, *objs, "-cudart", "static"]
+    if jobs or force or _stale(lib, objs):
+        cmd = [NVCC, *ARCH, "-shared", "-o", lib, *objs, "-cudart", "static"]
         proc = subprocess.run(cmd, capture_output=True, text=True)
         if proc.returncode != 0:
             raise RuntimeError("link failed:\n" + proc.stdout + proc.stderr)
-    return LIB
+    return lib
+
+
+INSTR_DIR = os.path.join(os.path.dirname(HERE), "profiles", "_instr")
+
+
+def build_instrumented(force: bool = False) -> str:
+    """The -DGTK_INSTRUMENT variant (per-CTA globaltimer stamps, cycle counters, gtk_debug_* entry points) beside the
+    product library, in profiles/_instr/: loaded through GTK_LIB by the scripts under profiles/ and by bench.py's in-graph
+    kernel-span measurement.  Never loaded by the product path."""
+    return build(force=force, libdir=INSTR_DIR, objdir=os.path.join(INSTR_DIR, "build"), extra_cflags=("-DGTK_INSTRUMENT",))
 
 
 if __name__ == "__main__":
