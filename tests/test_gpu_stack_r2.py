@@ -59,11 +59,18 @@ def _run(cfg, sd, y, mask, cond, pitch, energy, p_dropout, stack):
         os.environ.pop("GTK_WN_STACK", None)
 
 
+ONE_LAYER = dict(in_channels=16, hidden_channels=64, kernel_size=5, dilation_rate=1, n_blocks=2, n_layers=1, n_split=4,
+                 n_sqz=2, gin_channels=0)
+DIL3 = dict(in_channels=32, hidden_channels=128, kernel_size=3, dilation_rate=3, n_blocks=1, n_layers=3, n_split=4,
+            n_sqz=2, gin_channels=0)       # halos 1, 3, 9: windows own 102 of 128 rows, 9 rows of slack either side
+
 CASES = [
     ("base", BASE, [860, 430, 612, 2, 256, 700], 0.0, False),
     ("base_cond_dropout", BASE_G, [300, 226, 1024, 58], 0.05, False),
     ("h128_dilated", H128_DIL, [700, 514, 2, 388, 130], 0.0, False),
     ("h64_pitch_energy", H64_PE, [700, 514, 2, 388, 130], 0.05, True),
+    ("one_layer", ONE_LAYER, [300, 2, 258, 64], 0.0, False),
+    ("dilation_3", DIL3, [612, 10, 430], 0.05, False),
 ]
 
 
