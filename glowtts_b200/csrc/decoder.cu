@@ -203,10 +203,12 @@ static int coupling_net(const Dims& D, const Layout& L, const gtk_block_params& 
 // GPU has SMs (one 128-row tile each), so the two fill the machine together.  Created once per device, lowest priority (the
 // chain is the critical path); joined back into the caller's stream before the backward call returns, so the call stays
 // stream-ordered for the caller -- and capturable: the side stream enters a CUDA-graph capture through the fork event
-// and leaves it through the join.  OFF by default (GTK_WGRAD_OVERLAP=1 turns it on): measured on B200 at configs[1] it
-// LOSES -- 5.29 ms / step against 4.75 ms (profiles/wgrad_overlap_r02.txt) -- because the stream-K weight gradient
-// (~490 MB of operand reads per block) and the fused layer kernels are both L2-bandwidth bound, so they contend
-// instead of filling each other's idle SMs.
+// and leaves it through the join.  Three modes (GTK_WGRAD_OVERLAP): 2 = the default, "semi" overlap: the weight gradients of
+// block k share the GPU only with the small memory-bound kernels between two blocks (mix_bwd of block k, affine_bwd_frames of
+// block k - 1) and the main stream joins before the first tensor-core kernel of block k - 1: 4.28 -> 4.20 ms per step.
+// 1 = full overlap with the next block's chain: measured on B200 at configs[1] it LOSES -- 5.29 ms / step against 4.75 ms
+// (profiles/wgrad_overlap_r02.txt; re-measured 4.60-4.96 vs 4.40) -- the stream-K weight gradient takes the idle SMs the
+// chain's next kernel needs for its early-resident CTAs, and both contend in L2.  0 = everything on the caller's stream.
 struct SideStream {
     cudaStream_t s;
     cudaEvent_t fork[2], done[2];
@@ -217,7 +219,7 @@ static int side_stream(SideStream** out) {
     static std::mutex mu;
     *out = nullptr;
     static int enabled = -1;
-    if (enabled < 0) { const char* e = getenv("GTK_WGRAD_OVERLAP"); enabled = (e && e[0] == '1') ? 1 : 0; }
+    if (enabled < 0) { const char* e = getenv("GTK_WGRAD_OVERLAP"); enabled = e ? ((e[0] == '1' || e[0] == '2') ? (e[0] - '0') : 0) : 2; }
     if (!enabled) return GTK_OK;
     int dev = 0;
     GTK_CUDA(cudaGetDevice(&dev));
@@ -264,6 +266,13 @@ static int aux_stream(SideStream** out) {
     }
     *out = tab[dev];
     return GTK_OK;
+}
+// GTK_WGRAD_OVERLAP=2: "semi" overlap -- the weight gradients of block k run on the side stream only while the main stream
+// runs the small memory-bound kernels between two blocks (mix_bwd of block k, affine_bwd_frames of block k - 1); the main
+// stream joins before the first tensor-core kernel of block k - 1.
+static bool wgrad_semi_overlap() {
+    const char* e = getenv("GTK_WGRAD_OVERLAP");
+    return !e || e[0] == '2';
 }
 static int wgrad_overlap_ctas() {
     static int v = -1;

@@ -473,7 +473,8 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     GTK_TRY(side_stream(&side));
     bool side_used[2] = {false, false};
     // main-stream weight gradients: all stream-K launches of this call share ONE reduce launch at its end
-    tc::WgradReduceBatch* rbatch = side ? nullptr : tc::wgrad_reduce_batch(wpart, L.wpart_cap);
+    const bool semi = side && wgrad_semi_overlap();
+    tc::WgradReduceBatch* rbatch = (side && !semi) ? nullptr : tc::wgrad_reduce_batch(wpart, L.wpart_cap);
 
     if (first) GTK_TRY(flow::squeeze_pack(dz, pl.off, pl.row_b, pl.mask_p, dZ, D.Cin, D.Tq * D.n, D.n, L.P, st));
     if (first)
@@ -522,8 +523,8 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 GTK_CUDA(cudaEventRecord(side->fork[par], st));
                 GTK_CUDA(cudaStreamWaitEvent(side->s, side->fork[par], 0));
             }
-            int rc = tc::wgrad_group_launch(jobs, n_jobs, B, T, wpart, pl.n_rows(), wst, (side && blk > blk_lo) ? wgrad_overlap_ctas() : 0,
-                                            rbatch);
+            int rc = tc::wgrad_group_launch(jobs, n_jobs, B, T, wpart, pl.n_rows(), wst,
+                                            (side && !semi && blk > blk_lo) ? wgrad_overlap_ctas() : 0, rbatch);
             n_jobs = 0; n_tiles = 0;
             return rc;
         };
@@ -544,6 +545,9 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         GTK_TRY(tc::affine_bwd_frames(xmix, reinterpret_cast<const float*>(act + A.logs), msq, dZ, dlogdet, dend, ldC, dM, B, C, T,
                                       d->sigmoid_scale, pl.row_b, pl.n_rows(), st));
         GTK_TRY(queue(nullptr, P.end_w, nullptr, G.end_w, G.end_b, dend, ldC, ldC, skip_bf, H, H, C, H, 1, 1));
+        // semi overlap: the weight gradients of the block above have had mix_bwd and affine_bwd_frames to hide behind; the
+        // tensor-core chain of this block wants the SMs to itself
+        if (semi && blk < blk_hi && side_used[(blk + 1) & 1]) GTK_CUDA(cudaStreamWaitEvent(st, side->done[(blk + 1) & 1], 0));
         {
             // d(skip) feeds the res_skip gradient of EVERY layer: written into columns [H, 2H) of all per-layer buffers
             tc::ConvTcParams p;
@@ -640,7 +644,9 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         GTK_TRY(flow::mix_bwd(xin_blk, msq, P.an_logs, P.an_bias, P.ic_weight, D.NS, dM, dZ, G.an_logs, G.an_bias, G.ic_weight, B,
                               C, T, st, pl.n_rows()));
     }
-    GTK_TRY(tc::wgrad_group_reduce_flush(rbatch, st));      // weight norm + accumulation of every weight gradient of this call
+    // weight norm + accumulation of every weight gradient of this call (semi overlap: behind the launches on the side stream)
+    GTK_TRY(tc::wgrad_group_reduce_flush(rbatch, semi ? side->s : st));
+    if (semi) { GTK_CUDA(cudaEventRecord(side->done[0], side->s)); side_used[0] = true; }
     if (last) GTK_TRY(flow::unsqueeze_unpack(dZ, pl.off, dx, D.B, D.Cin, D.T, D.n, L.G, L.P, st));
     if (last)
         for (int w = 1; w < D.n_wn; ++w) {
