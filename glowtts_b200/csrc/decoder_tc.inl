@@ -559,6 +559,9 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
             p.rep_bf16 = D.L; p.rep_stride = L.b_lstride / 2;
             GTK_TRY(tc::conv_tc_launch(dend, ldC, pk + Q.t_end, p, tc::EPI_PLAIN, st));
         }
+        const bool post_fused = tc::wn_bwd_supported(H, K, 1) && tc::wn_bwd_post_ok(H, Ch) &&
+                                !(getenv("GTK_WB_POST") && getenv("GTK_WB_POST")[0] == '0');
+        bool post_done = false;
         for (int w = D.n_wn - 1; w >= 0; --w) {
         const WnW W = wn_weights(P, D.wn_id[w]);
         const WnG Gw = wn_grads(G, D.wn_id[w]);
@@ -586,6 +589,10 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
                 p.drop_p = d->p_dropout; p.drop_seed = make_drop_seed(d->seed, d->seed_dev, blk, D.wn_id[w] * D.L + i);
                 p.resid_f32 = (i < D.L - 1) ? dhf[(i + 1) & 1] : nullptr;
                 p.out_f32 = dhf[i & 1];
+                if (i == 0 && w == 0 && post_fused) {      // data gradient of `start` in the same kernel (GEMM c)
+                    p.post_w = pk + Q.t_start; p.post_N = Ch; p.post_C = C; p.post_resid_tm = dZ; p.post_out_tm = dM;
+                    post_done = true;
+                }
                 GTK_TRY(tc::wn_bwd_layer_launch(drs_i, 2 * H, pk + Q.t_rs[LI(w, i)], pk + Q.t_in[LI(w, i)], dxin,
                                                 i > 0 ? drs_of(w, i - 1) : dh0, i > 0 ? 2 * H : H, p, st));
             } else {
@@ -627,7 +634,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         }
         // start conv: h0 = (W x0 + b) * mask   (dh0 is already masked)
         GTK_TRY(queue(P.start_g, P.start_v, G.start_g, G.start_v, G.start_b, dh0, H, H, a0, ldCh, ldCh, H, Ch, 1, 1));
-        {
+        if (!post_done) {
             tc::ConvTcParams p;
             memset(&p, 0, sizeof(p));
             p.B = B; p.T = T; p.taps = 1; p.dil = 1; p.n_k = H / 64; p.N = Ch;

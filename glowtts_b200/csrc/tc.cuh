@@ -175,10 +175,18 @@ struct WnBwdParams {
     float* out_f32;                // fp32 carry written for the layer below (tile-private layout, ld = H)
     const int* n_rows;             // varlen packing (pack.cu), or null
     const int* row_fr;
+    // layer 0 of the first WaveNet: the data gradient of the `start` 1x1 conv rides in the same kernel (GEMM c on the d(h_0)
+    // tile): post_out_tm[b, c, t] = post_resid_tm[b, c, t] + sum_n d(h_0)[t, n] W[n, c], c < post_N, t-major with post_C
+    // channels per utterance.  post_w = the data-gradient pack [post_N][H]; null: no fused conv.
+    const __nv_bfloat16* post_w;
+    int post_N, post_C;
+    const float* post_resid_tm;
+    float* post_out_tm;
     __nv_bfloat16* dpre;           // [B,T,2H] frames or null: gate-input gradient BEFORE the dropout scale (what the
                                    // conditioners' gradients are reduced from when p_dropout > 0; == d(xin) when it is 0)
 };
 bool wn_bwd_supported(int H, int taps, int dil);
+bool wn_bwd_post_ok(int H, int N);       // the fused `start` data gradient fits (N = in_channels * n_sqz / 2)
 // drs: [B,T,ld_drs] frames (columns [0,RS) = [d(h_next) mask | d(skip)]); wrs_t / win_t: data-gradient weight packs;
 // dxin: [B,T,2H] frames out; out_bf16: [B,T,ld_out] frames, columns [0,H) = d(h) mask out.
 int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat16* wrs_t, const __nv_bfloat16* win_t,

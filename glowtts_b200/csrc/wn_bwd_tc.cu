@@ -27,6 +27,7 @@ struct WbCtl {
     uint64_t full[WB_MAX_STAGES], empty[WB_MAX_STAGES];        // GEMM a ring
     uint64_t full_b[WB_MAX_STAGES], empty_b[WB_MAX_STAGES];    // GEMM b ring (same memory, re-cut; cluster-wide `empty`)
     uint64_t acc_full, acts_ready;
+    uint64_t full_c;                                           // weights of the fused `start` data gradient (GEMM c)
     uint32_t tmem_base;
 };
 constexpr int WB_CL = 2;                     // CTAs per cluster: every in_layer weight tile is fetched once per pair
@@ -61,7 +62,8 @@ __device__ long long g_wb_wait[WB_TRACE_CTAS * 4];
 __global__ void __launch_bounds__(EPI_NT, 1)
 wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_constant__ CUtensorMap tmWrs,
                     const __grid_constant__ CUtensorMap tmWin, const __grid_constant__ CUtensorMap tmDxin,
-                    const __grid_constant__ CUtensorMap tmOut, const WnBwdParams p) {
+                    const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmWpost,
+                    const WnBwdParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int H = p.H, H2 = 2 * p.H;
@@ -90,6 +92,7 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
         }
         mbar_init(&ctl->acc_full, 1);
         mbar_init(&ctl->acts_ready, EPI_NT);
+        mbar_init(&ctl->full_c, 1);
         mbar_fence_init();
     }
     if (warp == 2) tmem_alloc<512>(&ctl->tmem_base);
@@ -293,6 +296,8 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
             }
             __syncwarp();
         }
+        if (p.post_w && lane == 0) tma_store_wait_read();       // the d(xin) store has read the tile GEMM c's weights will overwrite
+        __syncwarp();
         if (elect_one()) umma_commit(&ctl->acc_full);
         __syncwarp();
         WB_WAIT_STORE(0, w_mma);
@@ -319,6 +324,17 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
         mbar_wait(&ctl->acc_full, 1);
         tc_fence_after();
         WB_TRACE(4);
+        if (p.post_w && warp == 0) {
+            // fused `start` data gradient (GEMM c): its weight chunks go where the d(xin) tile was, now that GEMM b has read
+            // it (and its TMA store too: the MMA warp waits for that store before it commits GEMM b); they land under this
+            // epilogue
+            if (elect_one()) {
+                const int chp = (p.post_N * 128 + 1023) & ~1023;
+                mbar_arrive_expect_tx(&ctl->full_c, (uint32_t)((H / KC) * p.post_N * 128));
+                for (int kc = 0; kc < H / KC; ++kc) tma_load_2d(smem + (size_t)kc * chp, &tmWpost, &ctl->full_c, kc * KC, 0);
+            }
+            __syncwarp();
+        }
 #pragma unroll
         for (int ci = 0; ci < WB_MAXC; ++ci) {
             const int cc = cc_lo + ci;
@@ -348,8 +364,74 @@ wn_bwd_layer_kernel(const __grid_constant__ CUtensorMap tmDrs, const __grid_cons
             for (int kc = 0; kc < H / KC; ++kc) tma_store_3d(&tmOut, ring + (size_t)kc * A_BYTES, kc * KC, t0, b);
             tma_store_commit();
         }
-        tma_store_wait_read();
     }
+    if (p.post_w) {
+        // ---------------------------------------------------------------- GEMM c + epilogue c: data gradient of the `start`
+        // 1x1 conv on the d(h_0) tile that sits in shared memory as an A operand (conv_tc.cu EPI_PLAIN with resid_tm / out_tm,
+        // same sums: two accumulators take alternate k16 steps): dM[c, t] = dZ[c, t] + sum_n d(h_0)[t, n] Wstart[n, c]
+        if (warp == 1) {
+            const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
+            mbar_wait(&ctl->full_c, 0);
+            tc_fence_after();
+            const int chp = (p.post_N * 128 + 1023) & ~1023;
+            const uint32_t idc = umma_idesc_bf16(BT, p.post_N);
+            if (elect_one()) {
+                for (int kc = 0; kc < H / KC; ++kc) {
+                    const uint64_t adesc = umma_desc_kmajor_sw128(smem_u32(ring + (size_t)kc * A_BYTES));
+                    const uint64_t bdesc = umma_desc_kmajor_sw128(smem_u32(smem + (size_t)kc * chp));
+#pragma unroll
+                    for (int k = 0; k < KC / 16; ++k)
+                        umma_bf16(tm + (k & 1) * 256, adesc + 2 * k, bdesc + 2 * k, idc, kc != 0 || k >= 2);
+                }
+                umma_commit(&ctl->acc_full);
+            }
+            __syncwarp();
+        }
+        const int f = t0 + r;
+        const bool ok = r < tile_out && f < p.T;
+        const int nck_c = p.post_N / 16;
+        // the residual (the other half's gradient, complete long before this kernel) is requested before the wait
+        const int cq_lo = nck_c * part / EPI_PARTS, cq_hi = nck_c * (part + 1) / EPI_PARTS;
+        constexpr int WB_PREC = 2;
+        float xc[WB_PREC][16];
+        if (p.post_resid_tm && ok) {
+#pragma unroll
+            for (int ci = 0; ci < WB_PREC; ++ci)
+                if (cq_lo + ci < cq_hi) {
+                    const size_t o0 = ((size_t)b * p.post_C + (cq_lo + ci) * 16) * p.T + f;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) xc[ci][i] = __ldg(p.post_resid_tm + o0 + (size_t)i * p.T);
+                }
+        }
+        mbar_wait(&ctl->acc_full, 0);                      // third completion of acc_full
+        tc_fence_after();
+        for (int cc = cq_lo; cc < cq_hi; ++cc) {
+            const int c0 = cc * 16;
+            float v[16];
+            tmem_ld16_dual(trow + c0, true, v);
+            if (!ok) continue;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] += 0.f;      // conv_tc adds its (absent) bias here
+            const size_t o0 = ((size_t)b * p.post_C + c0) * p.T + f;
+            if (p.post_resid_tm) {
+                if (cc - cq_lo < WB_PREC) {
+#pragma unroll
+                    for (int ci = 0; ci < WB_PREC; ++ci)
+                        if (ci == cc - cq_lo) {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) v[i] += xc[ci][i];
+                        }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] += p.post_resid_tm[o0 + (size_t)i * p.T];
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 16; ++i) p.post_out_tm[o0 + (size_t)i * p.T] = v[i];
+        }
+        tc_fence_before();
+    }
+    if (warp == 1 && lane == 0) tma_store_wait_read();
     WB_TRACE(6);
     cluster_sync_all();                                        // the peer's commits may still be arriving on our barriers
     if (warp == 2) {
@@ -371,6 +453,8 @@ int wb_trace_read(unsigned long long* out, int n_ctas) {
 }
 #endif
 
+bool wn_bwd_post_ok(int H, int N) { return N % 16 == 0 && N >= 16 && N <= 256 && (size_t)(H / KC) * ((N * 128 + 1023) & ~1023) <= (size_t)(2 * H / KC) * A_BYTES; }
+
 int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat16* wrs_t, const __nv_bfloat16* win_t,
                         __nv_bfloat16* dxin, __nv_bfloat16* out_bf16, int ld_out, WnBwdParams p, cudaStream_t st) {
     GTK_REQUIRE(drs && wrs_t && win_t && dxin && out_bf16 && p.ts && p.out_f32, "null");
@@ -380,7 +464,16 @@ int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat1
     if (p.B == 0 || p.T == 0) return GTK_OK;
     const int H = p.H, halo = (p.taps / 2) * p.dil, tile_out = BT - 2 * halo;
     const int rs_pad = ceil_div(p.RS, KC) * KC;
-    CUtensorMap tmDrs, tmWrs, tmWin, tmDxin, tmOut;
+    CUtensorMap tmDrs, tmWrs, tmWin, tmDxin, tmOut, tmWpost;
+    memset(&tmWpost, 0, sizeof(tmWpost));
+    if (p.post_w) {     // data-gradient pack of the `start` weight: [post_N rows (N)][H columns (K)]
+        GTK_REQUIRE(wn_bwd_post_ok(p.H, p.post_N) && p.post_out_tm && p.post_C >= p.post_N, "fused start data gradient arguments");
+        const uint64_t dims[2] = {(uint64_t)p.H, (uint64_t)p.post_N};
+        const uint64_t strides[1] = {(uint64_t)p.H * 2};
+        const uint32_t box[2] = {KC, (uint32_t)p.post_N};
+        int rc = make_tmap_bf16(&tmWpost, p.post_w, 2, dims, strides, box, true);
+        if (rc) return rc;
+    }
     {
         const uint64_t dims[3] = {(uint64_t)rs_pad, (uint64_t)p.T, (uint64_t)p.B};
         const uint64_t strides[2] = {(uint64_t)ld_drs * 2, (uint64_t)ld_drs * 2 * p.T};
@@ -430,7 +523,7 @@ int wn_bwd_layer_launch(const __nv_bfloat16* drs, int ld_drs, const __nv_bfloat1
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
     cfg.attrs = attr; cfg.numAttrs = 2;
-    GTK_CUDA(cudaLaunchKernelEx(&cfg, wn_bwd_layer_kernel, tmDrs, tmWrs, tmWin, tmDxin, tmOut, p));
+    GTK_CUDA(cudaLaunchKernelEx(&cfg, wn_bwd_layer_kernel, tmDrs, tmWrs, tmWin, tmDxin, tmOut, tmWpost, p));
     return check_launch("wn_bwd_layer_tc");
 }
 

@@ -103,3 +103,38 @@ def test_stack_kernel_is_bit_identical_to_layer_kernels(name, cfg, lengths, p_dr
     for k in b["grads"]:
         ga, gb = a["grads"][k].double(), b["grads"][k].double()
         assert float((ga - gb).norm()) <= 1e-5 * float(gb.norm()) + 1e-12, (name, k, float((ga - gb).abs().max()))
+
+
+@pytest.mark.parametrize("name,cfg,lengths,p_dropout,prosody", [CASES[0], CASES[3], CASES[5]],
+                         ids=[CASES[0][0], CASES[3][0], CASES[5][0]])
+def test_start_data_gradient_inside_the_layer_0_backward_is_bit_identical(name, cfg, lengths, p_dropout, prosody):
+    """The data gradient of the `start` 1x1 conv rides in the layer-0 launch of csrc/wn_bwd_tc.cu (GEMM c on the d(h_0) tile
+    in shared memory, same two-accumulator sums as csrc/conv_tc.cu): one launch fewer per coupling block and the same bits
+    as the separate conv (GTK_WB_POST=0)."""
+    from glowtts_b200 import _lib
+    sd = helpers.make_state_dict(cfg, 81)
+    B, T = len(lengths), max(lengths)
+    gen = torch.Generator().manual_seed(82)
+    lens = torch.tensor(lengths)
+    mask = (torch.arange(T)[None, :] < lens[:, None]).float().unsqueeze(1).cuda()
+    y = torch.randn(B, cfg["in_channels"], T, generator=gen).cuda() * mask
+    cond = torch.randn(B, cfg["gin_channels"], 1, generator=gen).cuda() if cfg["gin_channels"] else None
+    pitch = torch.randn(B, 1, T, generator=gen).cuda() if prosody else None
+    energy = torch.randn(B, T, generator=gen).cuda() if prosody else None
+    out = {}
+    for post in ("1", "0"):
+        os.environ["GTK_WB_POST"] = post
+        try:
+            n0 = _lib.launch_count()
+            out[post] = _run(cfg, sd, y, mask, cond, pitch, energy, p_dropout, stack=True)
+            out[post]["n"] = _lib.launch_count() - n0
+        finally:
+            os.environ.pop("GTK_WB_POST", None)
+    assert out["0"]["n"] - out["1"]["n"] == cfg["n_blocks"], (out["0"]["n"], out["1"]["n"])
+    assert torch.isfinite(out["1"]["dy"]).all()
+    assert torch.equal(out["1"]["dy"], out["0"]["dy"]), float((out["1"]["dy"] - out["0"]["dy"]).abs().max())
+    for k in out["0"]["extra"]:
+        assert torch.equal(out["1"]["extra"][k], out["0"]["extra"][k]), k
+    for k in out["0"]["grads"]:
+        ga, gb = out["1"]["grads"][k].double(), out["0"]["grads"][k].double()
+        assert float((ga - gb).norm()) <= 1e-5 * float(gb.norm()) + 1e-12, (name, k)
