@@ -224,6 +224,7 @@ struct WgradGroupJob {
     float* db;                 // += bias gradient [M], or null
     int M, Cin, K, dil;
 };
+bool wgrad_red_enabled();                           // shares ADD into one slot per tile (GTK_WGRAD_RED=0: one partial tile per share)
 size_t wgrad_group_workspace_bytes();               // partial tiles of ONE launch (worst case)
 // Deferred reduce: the stream-K launches of several coupling blocks write their partial tiles side by side into one
 // workspace of `capacity` launches x wgrad_group_workspace_bytes(), and ONE reduce launch finishes them all

@@ -62,7 +62,8 @@ struct GgCta { unsigned short seg0, nseg; };
 struct GgParams {
     int B, T, chunks_t;
     const int* n_rows;                           // varlen packing (B == 1): only rows [0, *n_rows) hold data, or null
-    float* part;                                 // [slots][128][256] fp32
+    float* part;                                 // [slots][128][512] fp32
+    int red;                                     // 1: ONE zeroed slot per tile, every share adds into it (red.global.add.v4.f32)
     GgJobDev job[WGG_MAX_JOBS];
     GgTile tile[WGG_MAX_TILES];
     GgSeg seg[WGG_MAX_SEGS];
@@ -288,6 +289,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
             const bool ones = J.ones && (all_taps ? Tl.cblk == 0 : Tl.tap == 0);
             const int ones_col = all_taps ? J.taps * GG_CB : GG_ONES_BLK * 64;
             if (GG_SCALE(S.s_hi) <= GG_SCALE(S.s_lo)) {              // empty share: its partial tile is zero
+                if (p.red) continue;                                 // ... and adds nothing to the tile's one slot
                 for (int c0 = 0; c0 < n_cols; c0 += 4) *reinterpret_cast<float4*>(prow + c0) = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (pair)
                     for (int c0 = 0; c0 < n_cols; c0 += 4) *reinterpret_cast<float4*>(prow + 256 + c0) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -304,13 +306,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_group_kernel(const __grid_c
                     float v[16];
                     tmem_ld16_dual(trow + half * 256 + c0, !all_taps && !pair, v);
                     float4* o4 = reinterpret_cast<float4*>(prow + half * 256 + c0);
+                    if (p.red) {
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                        for (int i = 0; i < 4; ++i)
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(o4 + i), "f"(v[4 * i]),
+                                         "f"(v[4 * i + 1]), "f"(v[4 * i + 2]), "f"(v[4 * i + 3]) : "memory");
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) o4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                    }
                 }
             if (ones) {
                 float v[16];
                 tmem_ld16_dual(trow + ones_col, !all_taps && !pair, v);
-                prow[ones_col] = v[0];
+                if (p.red) atomicAdd(prow + ones_col, v[0]);
+                else prow[ones_col] = v[0];
             }
             tc_fence_before();
             __syncwarp();
@@ -360,6 +370,7 @@ struct WgradReduceBatch {
     float* part_ws;
     int capacity;
     size_t max_row;
+    int zeroed[WGG_MAX_DEFER];                     // adding shares: tile slots of launch k that were zeroed ahead of time
 };
 __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __grid_constant__ GgRedMulti pm) {
     extern __shared__ float row[];                 // [Cin * taps] reduced dW row, torch order (c, j)
@@ -442,6 +453,8 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
 }
 
 // ------------------------------------------------------------------------------------------ host
+bool wgrad_red_enabled() { const char* e = getenv("GTK_WGRAD_RED"); return !(e && e[0] == '0'); }
+
 size_t wgrad_group_workspace_bytes() { return (size_t)(WGG_MAX_CTAS + WGG_MAX_TILES) * GG_SLOT_FLOATS * sizeof(float); }
 
 static int tmap_frames(CUtensorMap* out, const __nv_bfloat16* base, int ld, int cols, int T, int B, int box_rows = GG_TK) {
@@ -454,6 +467,7 @@ static int tmap_frames(CUtensorMap* out, const __nv_bfloat16* base, int ld, int 
 WgradReduceBatch* wgrad_reduce_batch(float* part_ws, int capacity) {
     static thread_local WgradReduceBatch rb;
     rb.M.n = 0; rb.part_ws = part_ws; rb.capacity = max(1, min(capacity, WGG_MAX_DEFER)); rb.max_row = 0;
+    memset(rb.zeroed, 0, sizeof(rb.zeroed));
     return &rb;
 }
 
@@ -463,6 +477,7 @@ int wgrad_group_reduce_flush(WgradReduceBatch* rb, cudaStream_t st) {
     ProfScope prof("wgrad_group_reduce", st);
     GTK_CUDA(launch_pdl(wgrad_group_reduce_kernel, dim3(rows), dim3(GG_RED_NT), rb->max_row, st, rb->M));
     rb->M.n = 0; rb->max_row = 0;
+    memset(rb->zeroed, 0, sizeof(rb->zeroed));
     return check_launch("wgrad_group_reduce");
 }
 
@@ -562,6 +577,12 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     const bool paired = max_ctas > 0;
     if (paired && G > max_ctas) G = max_ctas;
     if (paired && G > 1) G &= ~1;
+    // Adding shares (default, GTK_WGRAD_RED=0 restores one partial tile per share): every share of a tile adds its
+    // accumulator into the tile's ONE zeroed slot with vector reds, which merge in L2 -- the reduce kernel reads one tile
+    // instead of ~4 partial tiles per tile (its DRAM reads were 534 MB per step, profiles/wgrad_group_trace_r02.txt).  The
+    // price is the summation order: weight gradients differ in their last bits from run to run (like the bias gradients).
+    const bool red = wgrad_red_enabled();
+    P.red = red ? 1 : 0;
     int n_seg = 0, slot = 0, c = 0;
     long long pos = 0;
     for (int i = 0; i < n_tiles; ++i) {
@@ -578,9 +599,11 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
             Sg.tile = (unsigned short)i; Sg.s_lo = (unsigned short)s; Sg.s_hi = (unsigned short)s_hi; Sg.slot = (unsigned short)slot;
             if (P.cta[c].nseg == 0) P.cta[c].seg0 = (unsigned short)n_seg;
             ++P.cta[c].nseg;
-            ++n_seg; ++slot;
+            ++n_seg;
+            if (!red) ++slot;
             s = s_hi;
         }
+        if (red) ++slot;
         R.nslot[i] = (unsigned short)(slot - R.slot0[i]);
         pos += w * S;
     }
@@ -588,6 +611,14 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
 
     const size_t smem = (size_t)GG_STAGES * GG_STAGE_BYTES + sizeof(GgCtl) + 1024;
     GTK_CUDA(cudaFuncSetAttribute(wgrad_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (red) {
+        // the tile slots must be zero when the first share lands.  A batch zeroes the slots of its NEXT launch right behind
+        // this one (the stream is idle then: the memset stays off the path of the launch that needs it)
+        const size_t slot_bytes = (size_t)GG_SLOT_FLOATS * sizeof(float);
+        const int have = defer ? defer->zeroed[defer->M.n] : 0;
+        if (n_tiles > have)
+            GTK_CUDA(cudaMemsetAsync(part_ws + (size_t)have * GG_SLOT_FLOATS, 0, (size_t)(n_tiles - have) * slot_bytes, st));
+    }
     {
         ProfScope prof("wgrad_group", st);
         if (paired && G > 1) {
@@ -609,6 +640,11 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     RM.row_end[RM.n] = (RM.n ? RM.row_end[RM.n - 1] : 0) + rows;
     ++RM.n;
     if (defer) {
+        if (red && defer->M.n < defer->capacity) {
+            GTK_CUDA(cudaMemsetAsync(defer->part_ws + (size_t)defer->M.n * (wgrad_group_workspace_bytes() / sizeof(float)), 0,
+                                     (size_t)n_tiles * GG_SLOT_FLOATS * sizeof(float), st));
+            defer->zeroed[defer->M.n] = n_tiles;
+        }
         defer->max_row = max(defer->max_row, max_row);
     } else {
         ProfScope prof("wgrad_group_reduce", st);
