@@ -391,35 +391,71 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
     const bool wn = J.g != nullptr;
     const float* part_row = p.part + (size_t)r * GG_SLOT_COLS;
     float ss = 0.f, dd = 0.f;
-    // pass 1: partial slots -> reduced row in shared memory, torch order (the partial tiles are read c-fastest = coalesced;
-    // v is NOT touched here: indexed c * taps + j it would be a stride-taps read, 5x the sectors for the k = 5 convs)
-    for (int e0 = threadIdx.x; e0 < R; e0 += 4 * GG_RED_NT) {
-        float acc[4];
-        int idx[4];
+    // pass 1: partial slots -> reduced row in shared memory, torch order.  ncu (round 2): this kernel is bound by issue slots
+    // (71 % busy, XU pipe saturated by the per-element e / Cin; DRAM at 17 % of peak).  Per-tap and tap-pair tiles: taps in the
+    // outer loop (tile, slot base and slot count are uniform per tap), the threads cover c (Cin <= 256: two columns each),
+    // coalesced read-only loads of the tile rows.  v is NOT touched here (see pass 2).
+    if (!J.n_cblk) {
+        const int c0 = threadIdx.x, c1 = threadIdx.x + GG_RED_NT;
+        const bool ok0 = c0 < Cin, ok1 = c1 < Cin;
+        const int tbase = J.tile0 + m_tile * (J.n_grp ? J.n_grp : taps);
+        constexpr int JB = 5;                      // taps whose loads are issued back to back (one round trip for a k = 5 row)
+        for (int j0 = 0; j0 < taps; j0 += JB) {
+            float a0[JB], a1[JB];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int e = e0 + u * GG_RED_NT;
-            acc[u] = 0.f; idx[u] = -1;
-            if (e < R) {
-                const int j = e / Cin, c = e - j * Cin;        // c fastest: coalesced reads of the partial tiles
-                const int tile = J.n_cblk ? J.tile0 + m_tile * J.n_cblk + c / GG_CB
-                               : J.n_grp ? J.tile0 + m_tile * J.n_grp + (j >> 1) : J.tile0 + m_tile * taps + j;
-                const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS +
-                                   (J.n_cblk ? j * GG_CB + c % GG_CB : J.n_grp ? (j & 1) * 256 + c : c);
-                const int ns = p.nslot[tile];
-                idx[u] = c * taps + j;
-                for (int s = 0; s < ns; s += 4) {
-                    const float a0 = src[(size_t)s * GG_SLOT_FLOATS];
-                    const float a1 = (s + 1 < ns) ? src[(size_t)(s + 1) * GG_SLOT_FLOATS] : 0.f;
-                    const float a2 = (s + 2 < ns) ? src[(size_t)(s + 2) * GG_SLOT_FLOATS] : 0.f;
-                    const float a3 = (s + 3 < ns) ? src[(size_t)(s + 3) * GG_SLOT_FLOATS] : 0.f;
-                    acc[u] += (a0 + a1) + (a2 + a3);
+            for (int u = 0; u < JB; ++u) {
+                const int j = j0 + u;
+                a0[u] = 0.f; a1[u] = 0.f;
+                if (j < taps) {
+                    const int tile = tbase + (J.n_grp ? (j >> 1) : j);
+                    const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + (J.n_grp ? (j & 1) * 256 : 0);
+                    if (ok0) a0[u] = __ldg(src + c0);
+                    if (ok1) a1[u] = __ldg(src + c1);
+                    for (int sl = 1; sl < p.nslot[tile]; ++sl) {      // adding shares: one slot per tile, never taken
+                        src += GG_SLOT_FLOATS;
+                        if (ok0) a0[u] += __ldg(src + c0);
+                        if (ok1) a1[u] += __ldg(src + c1);
+                    }
                 }
             }
-        }
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
-            if (idx[u] >= 0) row[idx[u]] = acc[u];
+            for (int u = 0; u < JB; ++u) {
+                const int j = j0 + u;
+                if (j < taps && ok0) row[c0 * taps + j] = a0[u];
+                if (j < taps && ok1) row[c1 * taps + j] = a1[u];
+            }
+        }
+    } else {
+        // all-taps tiles (opt-in): element by element (the partial tiles are read c-fastest = coalesced;
+        // v is NOT touched here: indexed c * taps + j it would be a stride-taps read, 5x the sectors for the k = 5 convs)
+        for (int e0 = threadIdx.x; e0 < R; e0 += 4 * GG_RED_NT) {
+            float acc[4];
+            int idx[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int e = e0 + u * GG_RED_NT;
+                acc[u] = 0.f; idx[u] = -1;
+                if (e < R) {
+                    const int j = e / Cin, c = e - j * Cin;        // c fastest: coalesced reads of the partial tiles
+                    const int tile = J.n_cblk ? J.tile0 + m_tile * J.n_cblk + c / GG_CB
+                                   : J.n_grp ? J.tile0 + m_tile * J.n_grp + (j >> 1) : J.tile0 + m_tile * taps + j;
+                    const float* src = part_row + (size_t)p.slot0[tile] * GG_SLOT_FLOATS +
+                                       (J.n_cblk ? j * GG_CB + c % GG_CB : J.n_grp ? (j & 1) * 256 + c : c);
+                    const int ns = p.nslot[tile];
+                    idx[u] = c * taps + j;
+                    for (int s = 0; s < ns; s += 4) {
+                        const float a0 = src[(size_t)s * GG_SLOT_FLOATS];
+                        const float a1 = (s + 1 < ns) ? src[(size_t)(s + 1) * GG_SLOT_FLOATS] : 0.f;
+                        const float a2 = (s + 2 < ns) ? src[(size_t)(s + 2) * GG_SLOT_FLOATS] : 0.f;
+                        const float a3 = (s + 3 < ns) ? src[(size_t)(s + 3) * GG_SLOT_FLOATS] : 0.f;
+                        acc[u] += (a0 + a1) + (a2 + a3);
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (idx[u] >= 0) row[idx[u]] = acc[u];
+        }
     }
     if (J.db && J.ones && threadIdx.x == GG_RED_NT - 1) {
         const int tile = J.tile0 + m_tile * (J.n_cblk ? J.n_cblk : J.n_grp ? J.n_grp : taps);
