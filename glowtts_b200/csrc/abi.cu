@@ -98,6 +98,10 @@ int reverse(const gtk_decoder_desc* d, const gtk_block_params* blocks, const flo
 int backward(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads, const float* mask,
              const float* dz, const float* dlogdet, float* dx, void* workspace, size_t ws_bytes, int blk_hi, int blk_lo,
              cudaStream_t st);
+int backward_deferred(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads, const float* mask,
+                      const float* dz, const float* dlogdet, float* dx, void* workspace, size_t ws_bytes, int blk_hi, int blk_lo,
+                      cudaStream_t st);
+int backward_join_stream(cudaStream_t st);
 }  // namespace decoder
 }  // namespace gtk
 
@@ -400,5 +404,11 @@ int gtk_decoder_backward_range(const gtk_decoder_desc* d, const gtk_block_params
                                size_t workspace_bytes, int blk_hi, int blk_lo, void* stream) {
     return decoder::backward(d, blocks, grads, mask, dz, dlogdet, dx, workspace, workspace_bytes, blk_hi, blk_lo, ST);
 }
+int gtk_decoder_backward_range_deferred(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads,
+                                        const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace,
+                                        size_t workspace_bytes, int blk_hi, int blk_lo, void* stream) {
+    return decoder::backward_deferred(d, blocks, grads, mask, dz, dlogdet, dx, workspace, workspace_bytes, blk_hi, blk_lo, ST);
+}
+int gtk_decoder_backward_join(void* stream) { return decoder::backward_join_stream(ST); }
 
 }  // extern "C"

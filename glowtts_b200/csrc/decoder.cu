@@ -212,7 +212,12 @@ static int coupling_net(const Dims& D, const Layout& L, const gtk_block_params& 
 struct SideStream {
     cudaStream_t s;
     cudaEvent_t fork[2], done[2];
+    // deferred join of a backward RANGE (gtk_decoder_backward_range_deferred): the call leaves its last weight-gradient launch
+    // and its reduce running on the side stream; the next range picks the state up where an un-split backward would be
+    cudaEvent_t red_done;                          // behind the reduce of the last deferred range
+    bool carry, carry_used[2], red_pending;
 };
+static thread_local int g_defer_join = 0;          // set by backward_range_deferred() for the duration of one call
 static int side_stream(SideStream** out) {
     constexpr int MAX_DEV = 64;
     static SideStream* tab[MAX_DEV] = {nullptr};
@@ -234,6 +239,8 @@ static int side_stream(SideStream** out) {
             GTK_CUDA(cudaEventCreateWithFlags(&ss->fork[i], cudaEventDisableTiming));
             GTK_CUDA(cudaEventCreateWithFlags(&ss->done[i], cudaEventDisableTiming));
         }
+        GTK_CUDA(cudaEventCreateWithFlags(&ss->red_done, cudaEventDisableTiming));
+        ss->carry = false; ss->carry_used[0] = ss->carry_used[1] = false; ss->red_pending = false;
         tab[dev] = ss;
     }
     *out = tab[dev];
@@ -285,6 +292,14 @@ static int wgrad_overlap_ctas() {
 }
 
 #include "decoder_tc.inl"
+
+// gtk_decoder_backward_join: `stream` waits for what a deferred range left on the side stream (its weight gradients + reduce)
+static int backward_join(cudaStream_t stream) {
+    SideStream* side = nullptr;
+    GTK_TRY(side_stream(&side));
+    if (side && side->red_pending) GTK_CUDA(cudaStreamWaitEvent(stream, side->red_done, 0));
+    return GTK_OK;
+}
 
 static size_t tc_workspace_bytes(const Dims& D, int train) {
     Layout L32;
@@ -367,6 +382,18 @@ int reverse(const gtk_decoder_desc* d, const gtk_block_params* blocks, const flo
 }
 
 #include "decoder_bwd.inl"
+
+// backward() of a range that is not the last one, without the join of the internal side stream at its end (bf16 path with
+// the default side-stream weight gradients; any other configuration joins as backward() does)
+int backward_deferred(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads, const float* mask,
+                      const float* dz, const float* dlogdet, float* dx, void* workspace, size_t ws_bytes, int blk_hi, int blk_lo,
+                      cudaStream_t st) {
+    g_defer_join = 1;
+    const int rc = backward(d, blocks, grads, mask, dz, dlogdet, dx, workspace, ws_bytes, blk_hi, blk_lo, st);
+    g_defer_join = 0;
+    return rc;
+}
+int backward_join_stream(cudaStream_t st) { return backward_join(st); }
 
 }  // namespace decoder
 }  // namespace gtk

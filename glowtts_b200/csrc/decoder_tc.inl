@@ -474,6 +474,15 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     bool side_used[2] = {false, false};
     // main-stream weight gradients: all stream-K launches of this call share ONE reduce launch at its end
     const bool semi = side && wgrad_semi_overlap();
+    // Deferred join (gtk_decoder_backward_range_deferred, semi overlap only): a range that is not the last one returns with
+    // its last weight-gradient launch and its reduce still running on the side stream; the next range carries on as the
+    // un-split backward would -- it waits for that weight gradient before its first tensor-core kernel and never for the
+    // reduce (a range boundary then costs what a block boundary costs, not an exposed join: profiles/scaling_r02.txt)
+    const bool defer = semi && g_defer_join && !last;
+    const bool carried = semi && side->carry && !first;
+    if (carried) { side_used[0] = side->carry_used[0]; side_used[1] = side->carry_used[1]; }
+    if (side) side->carry = false;
+    if (side && first) side->red_pending = false;
     tc::WgradReduceBatch* rbatch = (side && !semi) ? nullptr : tc::wgrad_reduce_batch(wpart, L.wpart_cap);
 
     if (first) GTK_TRY(flow::squeeze_pack(dz, pl.off, pl.row_b, pl.mask_p, dZ, D.Cin, D.Tq * D.n, D.n, L.P, st));
@@ -547,7 +556,7 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
         GTK_TRY(queue(nullptr, P.end_w, nullptr, G.end_w, G.end_b, dend, ldC, ldC, skip_bf, H, H, C, H, 1, 1));
         // semi overlap: the weight gradients of the block above have had mix_bwd and affine_bwd_frames to hide behind; the
         // tensor-core chain of this block wants the SMs to itself
-        if (semi && blk < blk_hi && side_used[(blk + 1) & 1]) GTK_CUDA(cudaStreamWaitEvent(st, side->done[(blk + 1) & 1], 0));
+        if (semi && (blk < blk_hi || carried) && side_used[(blk + 1) & 1]) GTK_CUDA(cudaStreamWaitEvent(st, side->done[(blk + 1) & 1], 0));
         {
             // d(skip) feeds the res_skip gradient of EVERY layer: written into columns [H, 2H) of all per-layer buffers
             tc::ConvTcParams p;
@@ -653,6 +662,12 @@ static int tc_backward(const gtk_decoder_desc* d, const Dims& D, const gtk_block
     }
     // weight norm + accumulation of every weight gradient of this call (semi overlap: behind the launches on the side stream)
     GTK_TRY(tc::wgrad_group_reduce_flush(rbatch, semi ? side->s : st));
+    if (defer) {
+        GTK_CUDA(cudaEventRecord(side->red_done, side->s));
+        side->red_pending = true; side->carry = true;
+        side->carry_used[0] = side_used[0]; side->carry_used[1] = side_used[1];
+        return GTK_OK;                                 // no join: the caller orders consumers with gtk_decoder_backward_join
+    }
     if (semi) { GTK_CUDA(cudaEventRecord(side->done[0], side->s)); side_used[0] = true; }
     if (last) GTK_TRY(flow::unsqueeze_unpack(dZ, pl.off, dx, D.B, D.Cin, D.T, D.n, L.G, L.P, st));
     if (last)

@@ -876,6 +876,17 @@ def _(dz, dlogdet, mask, flat, offsets, cond, ws, cfg, T, seed=None, energy=None
             _track_fake(dz, pitch, B, T))
 
 
+_RANGE_STREAMS = {}
+
+
+def _range_stream(device):
+    """Helper stream per device from which the collective of a deferred backward range is issued."""
+    key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
+    if key not in _RANGE_STREAMS:
+        _RANGE_STREAMS[key] = torch.cuda.Stream(device=device)
+    return _RANGE_STREAMS[key]
+
+
 def decoder_backward_flat_overlapped(dz: Tensor, dlogdet: Tensor, mask: Tensor, flat: Tensor, offsets: List[int],
                                      cond: Optional[Tensor], ws: Tensor, cfg: List[int], T: int, seed: Optional[Tensor],
                                      group, n_segments: int = 3, energy: Optional[Tensor] = None,
@@ -903,21 +914,37 @@ def decoder_backward_flat_overlapped(dz: Tensor, dlogdet: Tensor, mask: Tensor, 
     avg = sync and dist.get_backend(group) == "nccl"
     n_segments = max(1, min(int(n_segments), nb))
     # block index boundaries, ascending.  The ranges run from the last block down, so range 0 is the one whose collective
-    # nothing can hide: it gets half a share (12 blocks, 3 segments: blocks 11..7 | 6..2 | 1..0)
+    # nothing can hide: it gets a quarter of a share (12 blocks, 3 segments: blocks 11..6 | 5..1 | 0)
     if n_segments > 1:
-        last = max(1, nb // (2 * n_segments))
+        last = max(1, nb // (4 * n_segments))
+        if os.environ.get("GTK_GRAD_SYNC_LAST"):              # blocks in the last (exposed) range, for sweeps
+            last = max(1, min(nb - n_segments + 1, int(os.environ["GTK_GRAD_SYNC_LAST"])))
         bounds = [0] + [last + (nb - last) * k // (n_segments - 1) for k in range(n_segments)]
     else:
         bounds = [0, nb]
     works = []
+    # Deferred join (GTK_RANGE_DEFER=0 disables): a range that is not the last one returns without joining the library's side
+    # stream (its last weight-gradient launch + its reduce); the collective is issued from a helper stream that waits for the
+    # caller's stream AND that side-stream work, so the next range's kernels never wait for a reduce.
+    defer = os.environ.get("GTK_RANGE_DEFER", "1") != "0" and dz.is_cuda
     for k in range(n_segments - 1, -1, -1):                                   # ranges from the last block down
         lo, hi = bounds[k], bounds[k + 1] - 1
-        _lib.call("gtk_decoder_backward_range", ctypes.byref(d), blocks, gblocks, _p(mask), _p(dz), _p(dlogdet), _p(dx),
-                  _p(ws), ws.numel(), hi, lo, _stream())
+        deferred = defer and lo > 0
+        _lib.call("gtk_decoder_backward_range_deferred" if deferred else "gtk_decoder_backward_range", ctypes.byref(d), blocks,
+                  gblocks, _p(mask), _p(dz), _p(dlogdet), _p(dx), _p(ws), ws.numel(), hi, lo, _stream())
         if not sync:
-            continue
+            continue                      # segmentation only: the last range joins the side stream
         e0 = int(offsets[lo * ppb])
         e1 = int(offsets[(hi + 1) * ppb]) if hi + 1 < nb else flat.numel()
+        if deferred:
+            helper = _range_stream(dz.device)
+            helper.wait_stream(torch.cuda.current_stream(dz.device))
+            _lib.call("gtk_decoder_backward_join", ctypes.c_void_p(helper.cuda_stream))
+            with torch.cuda.stream(helper):
+                works.append(dist.all_reduce(dflat[e0:e1], op=dist.ReduceOp.AVG if avg else dist.ReduceOp.SUM, group=group,
+                                             async_op=True))
+            dflat.record_stream(helper)
+            continue
         works.append(dist.all_reduce(dflat[e0:e1], op=dist.ReduceOp.AVG if avg else dist.ReduceOp.SUM, group=group,
                                      async_op=True))
     for w in works:

@@ -337,6 +337,18 @@ int gtk_decoder_backward(const gtk_decoder_desc* d, const gtk_block_params* bloc
 int gtk_decoder_backward_range(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads,
                                const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace,
                                size_t workspace_bytes, int blk_hi, int blk_lo, void* stream);
+/* gtk_decoder_backward_range for a range that is NOT the last one, returning without joining the library's internal side
+ * stream: the range's last weight-gradient launch and its reduce keep running there while the caller enqueues the next
+ * range, which carries on as the un-split backward would (a range boundary then costs what a block boundary costs).  A
+ * consumer of this range's parameter gradients -- the gradient all-reduce of DDP, train_ms_emo_lang_pitch.py:166 -- is
+ * ordered with gtk_decoder_backward_join(consumer_stream) AND an ordinary dependency on `stream` (bias / ActNorm gradients
+ * are written there).  The last range (blk_lo = 0, any of the two entry points) joins everything.  With the side stream off
+ * (GTK_WGRAD_OVERLAP=0/1, fp32 path) this is gtk_decoder_backward_range. */
+int gtk_decoder_backward_range_deferred(const gtk_decoder_desc* d, const gtk_block_params* blocks, const gtk_block_grads* grads,
+                                        const float* mask, const float* dz, const float* dlogdet, float* dx, void* workspace,
+                                        size_t workspace_bytes, int blk_hi, int blk_lo, void* stream);
+/* `stream` waits for the side-stream work of the last deferred range on the current device (no-op when there is none). */
+int gtk_decoder_backward_join(void* stream);
 
 #ifdef __cplusplus
 }

@@ -10,6 +10,8 @@ rows = list(csv.DictReader(lines))
 names = [r["Kernel Name"] for r in rows]
 # a step starts at the forward pack-plan kernel (round 2: varlen packing; round 1 lists: the forward squeeze kernel)
 sq = [i for i, n in enumerate(names) if "pack_plan_kernel" in n]
+# the weight packs of a step are enqueued (auxiliary stream) just before its pack-plan kernel: they belong to the step
+sq = [i - sum(1 for j in (i - 1, i - 2) if j >= 0 and "fold_pack" in names[j]) for i in sq]
 per_step = 1
 if not sq:
     sq = [i for i, n in enumerate(names) if "squeeze_kernel" in n and "unsqueeze" not in n]
