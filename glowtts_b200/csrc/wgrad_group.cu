@@ -344,7 +344,8 @@ struct GgRedJob {
     float* dg;
     float* dv;
     float* db;                 // bias gradient [M] or null
-    int M, Cin, taps, tile0, row0, ones;
+    int M, Cin, taps, tile0, row0, ones;       // row0: first block of this conv in the block-per-row launch (k > 1 convs)
+    int row0w;                 // first block in the warp-per-row launch (1x1 convs; four rows per block); a conv has rows in one
     int n_cblk;                // > 0: all-taps tiles, tile = tile0 + m_tile * n_cblk + c / 64, column = 64 tap + c % 64
     int n_grp;                 // > 0: tap pairs, n_grp tiles per m_tile: tile = tile0 + m_tile * n_grp + tap / 2, column = 256 (tap % 2) + c
 };
@@ -362,7 +363,8 @@ struct GgRedParams {
 constexpr int GG_RED_NT = 128;
 struct GgRedMulti {
     int n;
-    int row_end[WGG_MAX_DEFER];                    // cumulative output rows of launch k
+    int row_end[WGG_MAX_DEFER];                    // cumulative blocks of stream-K launch k in the block-per-row launch
+    int row_end_w[WGG_MAX_DEFER];                  // ... in the warp-per-row launch
     GgRedParams r[WGG_MAX_DEFER];
 };
 struct WgradReduceBatch {
@@ -372,6 +374,67 @@ struct WgradReduceBatch {
     size_t max_row;
     int zeroed[WGG_MAX_DEFER];                     // adding shares: tile slots of launch k that were zeroed ahead of time
 };
+// 1x1 convs (res_skip, start, end: half of a step's 38 784 rows, 15 % of its bytes): a WARP per output row, the row (<= 256
+// elements, already in torch order) stays in registers -- no shared memory, no block barrier, a quarter of the blocks.  Its own
+// kernel: inside the block-per-row kernel its 48 registers cost that kernel a third of its occupancy (4.066 against 4.054 ms).
+__global__ void __launch_bounds__(GG_RED_NT, 10) wgrad_group_reduce_rows_kernel(const __grid_constant__ GgRedMulti pm) {
+    pdl_trigger();
+    pdl_wait();
+    int k = 0;
+    while (k + 1 < pm.n && (int)blockIdx.x >= pm.row_end_w[k]) ++k;
+    const GgRedParams& p = pm.r[k];
+    const int brow = (int)blockIdx.x - (k ? pm.row_end_w[k - 1] : 0);
+    int q = 0;
+    while (q + 1 < p.n_jobs && brow >= p.job[q + 1].row0w) ++q;
+    const GgRedJob& J = p.job[q];
+    const int lane = threadIdx.x & 31;
+    const int m = (brow - J.row0w) * (GG_RED_NT / 32) + (threadIdx.x >> 5);
+    if (m >= J.M) return;
+    const int Cin = J.Cin, tile = J.tile0 + (m >> 7);
+    const float* src = p.part + (size_t)p.slot0[tile] * GG_SLOT_FLOATS + (size_t)(m & 127) * GG_SLOT_COLS;
+    const int ns = p.nslot[tile];
+    const float* __restrict__ vrow = J.v + (size_t)m * Cin;
+    float* __restrict__ dvrow = J.dv + (size_t)m * Cin;
+    const bool wn = J.g != nullptr;
+    float a[8], v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        const int c = lane + 32 * u;
+        const bool ok = c < Cin;
+        a[u] = ok ? __ldg(src + c) : 0.f;
+        v[u] = (wn && ok) ? __ldg(vrow + c) : 0.f;
+    }
+    for (int sl = 1; sl < ns; ++sl) {                          // adding shares: one slot per tile, never taken
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            if (lane + 32 * u < Cin) a[u] += __ldg(src + (size_t)sl * GG_SLOT_FLOATS + lane + 32 * u);
+    }
+    if (J.db && J.ones && lane == 31) {
+        float acc = 0.f;
+        for (int sl = 0; sl < ns; ++sl) acc += src[(size_t)sl * GG_SLOT_FLOATS + GG_ONES_BLK * 64];
+        J.db[m] += acc;
+    }
+    if (!wn) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            if (lane + 32 * u < Cin) dvrow[lane + 32 * u] += a[u];
+        return;
+    }
+    float ss = 0.f, dd = 0.f;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { ss += v[u] * v[u]; dd += v[u] * a[u]; }
+    ss = warp_sum(ss);
+    dd = warp_sum(dd);
+    ss = __shfl_sync(0xffffffffu, ss, 0);
+    dd = __shfl_sync(0xffffffffu, dd, 0);
+    const float nrm = sqrtf(ss);
+    const float sc = J.g[m] / nrm, proj = dd / ss;
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+        if (lane + 32 * u < Cin) dvrow[lane + 32 * u] += sc * (a[u] - v[u] * proj);
+    if (lane == 0) J.dg[m] += dd / nrm;
+}
+
 __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __grid_constant__ GgRedMulti pm) {
     extern __shared__ float row[];                 // [Cin * taps] reduced dW row, torch order (c, j)
     __shared__ float red[2][GG_RED_NT / 32];
@@ -489,6 +552,7 @@ __global__ void __launch_bounds__(GG_RED_NT) wgrad_group_reduce_kernel(const __g
 }
 
 // ------------------------------------------------------------------------------------------ host
+static bool wgrad_reduce_warp_rows() { const char* e = getenv("GTK_WGRAD_REDUCE_ROWS"); return !(e && e[0] == '0'); }
 bool wgrad_red_enabled() { const char* e = getenv("GTK_WGRAD_RED"); return !(e && e[0] == '0'); }
 
 size_t wgrad_group_workspace_bytes() { return (size_t)(WGG_MAX_CTAS + WGG_MAX_TILES) * GG_SLOT_FLOATS * sizeof(float); }
@@ -509,9 +573,13 @@ WgradReduceBatch* wgrad_reduce_batch(float* part_ws, int capacity) {
 
 int wgrad_group_reduce_flush(WgradReduceBatch* rb, cudaStream_t st) {
     if (!rb || rb->M.n == 0) return GTK_OK;
-    const int rows = rb->M.row_end[rb->M.n - 1];
+    const int rows = rb->M.row_end[rb->M.n - 1], rows_w = rb->M.row_end_w[rb->M.n - 1];
     ProfScope prof("wgrad_group_reduce", st);
-    GTK_CUDA(launch_pdl(wgrad_group_reduce_kernel, dim3(rows), dim3(GG_RED_NT), rb->max_row, st, rb->M));
+    if (rows > 0) {
+        GTK_CUDA(launch_pdl(wgrad_group_reduce_kernel, dim3(rows), dim3(GG_RED_NT), rb->max_row, st, rb->M));
+        if (rows_w > 0) { int rc = check_launch("wgrad_group_reduce"); if (rc) return rc; }
+    }
+    if (rows_w > 0) GTK_CUDA(launch_pdl(wgrad_group_reduce_rows_kernel, dim3(rows_w), dim3(GG_RED_NT), 0, st, rb->M));
     rb->M.n = 0; rb->max_row = 0;
     memset(rb->zeroed, 0, sizeof(rb->zeroed));
     return check_launch("wgrad_group_reduce");
@@ -550,7 +618,7 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
     auto tap_pairs = [&](const WgradGroupJob& J) { return pairs_on && !all_taps(J) && J.K > 1 && J.dil <= GG_PAIR_ROWS; };
     bool ones_ok = true;
     for (int q = 0; q < n_jobs; ++q) ones_ok = ones_ok && (all_taps(jobs[q]) || ceil_div(jobs[q].Cin, 64) <= GG_ONES_BLK);
-    int n_tiles = 0, rows = 0, rc_at = 0;
+    int n_tiles = 0, rows = 0, rows_w = 0, rc_at = 0;
     size_t max_row = 0;
     long long w_tile[WGG_MAX_TILES];
     for (int q = 0; q < n_jobs; ++q) {
@@ -573,10 +641,12 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
         if (rc) return rc;
         GgRedJob& Q = R.job[q];
         Q.g = J.g; Q.v = J.v; Q.dg = J.dg; Q.dv = J.dv; Q.db = J.db;
-        Q.M = J.M; Q.Cin = J.Cin; Q.taps = J.K; Q.tile0 = n_tiles; Q.row0 = rows; Q.ones = D.ones;
+        Q.M = J.M; Q.Cin = J.Cin; Q.taps = J.K; Q.tile0 = n_tiles; Q.row0 = rows; Q.row0w = rows_w; Q.ones = D.ones;
+        const bool warp_rows = J.K == 1 && !at && wgrad_reduce_warp_rows();
         Q.n_cblk = at ? D.n_blk : 0;
         Q.n_grp = tp ? (J.K + 1) / 2 : 0;
-        rows += J.M;
+        if (warp_rows) rows_w += ceil_div(J.M, GG_RED_NT / 32);
+        else rows += J.M;
         max_row = max(max_row, (size_t)J.Cin * J.K * sizeof(float));
         const int m_tiles = ceil_div(J.M, 128);
         const int per_m = at ? D.n_blk : tp ? (J.K + 1) / 2 : J.K;
@@ -674,6 +744,7 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
         if (rc) return rc;
     }
     RM.row_end[RM.n] = (RM.n ? RM.row_end[RM.n - 1] : 0) + rows;
+    RM.row_end_w[RM.n] = (RM.n ? RM.row_end_w[RM.n - 1] : 0) + rows_w;
     ++RM.n;
     if (defer) {
         if (red && defer->M.n < defer->capacity) {
@@ -684,7 +755,11 @@ int wgrad_group_launch(const WgradGroupJob* jobs, int n_jobs, int B, int T, floa
         defer->max_row = max(defer->max_row, max_row);
     } else {
         ProfScope prof("wgrad_group_reduce", st);
-        GTK_CUDA(launch_pdl(wgrad_group_reduce_kernel, dim3(rows), dim3(GG_RED_NT), (size_t)max_row, st, RM));
+        if (rows > 0) {
+            GTK_CUDA(launch_pdl(wgrad_group_reduce_kernel, dim3(rows), dim3(GG_RED_NT), (size_t)max_row, st, RM));
+            if (rows_w > 0) { int rc = check_launch("wgrad_group_reduce"); if (rc) return rc; }
+        }
+        if (rows_w > 0) GTK_CUDA(launch_pdl(wgrad_group_reduce_rows_kernel, dim3(rows_w), dim3(GG_RED_NT), 0, st, RM));
         int rc = check_launch("wgrad_group_reduce");
         if (rc) return rc;
     }
