@@ -280,7 +280,9 @@ def kernel_spans():
     if not os.path.exists(lib):
         return {}
     try:
-        env = dict(os.environ, GTK_LIB=lib)
+        # GTK_WB_POST=0: the step's last fused-layer-backward launch is layer 0 of block 0, which in the timed step also
+        # carries the d-`start` GEMM; the span is that of a plain layer launch, the one `flop_per_launch` describes
+        env = dict(os.environ, GTK_LIB=lib, GTK_WB_POST="0")
         for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
             env.pop(k, None)
         out = subprocess.run([sys.executable, os.path.join(root, "profiles", "ws_span_in_graph.py"), "--json"], env=env,
@@ -719,7 +721,8 @@ def main():
                 "frac_by_span": (flop_per_launch / (spans[tag] * 1e-6) / 1e12 / pk["tc_sustained"]) if spans.get(tag) else None,
                 "span_note": "busy span of the step's last launch of this kernel inside the replayed CUDA graph (first CTA past "
                              "griddepcontrol.wait -> last CTA done), per-CTA globaltimer stamps of the instrumented library "
-                             "variant in a child process; the event-bracketed figure above is the stand-alone launch, "
+                             "variant in a child process (with GTK_WB_POST=0: a plain layer launch, without the d-start GEMM that "
+                             "layer 0 carries in the timed step); the event-bracketed figure above is the stand-alone launch, "
                              "prologue and launch latency included",
                 "spans_us_in_graph": spans or None,
                 "by_tag_ms_per_step": {k: v[1] / max(prof_steps, 1) for k, v in sorted(prof.items())}}
