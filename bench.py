@@ -289,7 +289,9 @@ def kernel_spans():
                              capture_output=True, text=True, timeout=240, cwd=root)
         line = [l for l in out.stdout.splitlines() if l.startswith("{")][-1]
         return json.loads(line)
-    except Exception:                                       # diagnostic: never hide the main numbers
+    except Exception as e:                                  # diagnostic: never hide the main numbers, but say why
+        print(f"bench.py: no in-graph kernel spans ({e!r}); is profiles/_instr older than the library? "
+              "(__graft_entry__.build() rebuilds both)", file=sys.stderr)
         return {}
 
 
