@@ -45,7 +45,7 @@ SEED = 1234  # configs/base.json:5
 NCU_TRAFFIC = {"mas configs[0]": 19.9e6,    # profiles/ncu_mas_cfg1_r01.csv: 19.89 MB read (value), 0 written (the 19.8 MB path stays in L2)
                "mas configs[4] on one GPU": 3.383e9,   # profiles/ncu_mas_cfg5_r01.csv: 1.728 GB read + 1.655 GB written (algorithmic 3.277 GB)
                "wn_layer_tc": 23.05e6,      # profiles/ncu_wn_layer_r01.txt: (16.89 + 0.82 MB, 27.50 + 0.89 MB) -> mean bytes / launch
-               "wn_bwd_layer_tc": 33.0e6,   # profiles/ncu_wn_bwd_layer_r01.txt: 32.78 MB read + 0.2 MB written per launch
+               "wn_bwd_layer_tc": 24.9e6,   # profiles/ncu_wn_bwd_layer_r02.txt: 24.87 MB read + 0.01 MB written per launch (packed rows; r01: 33.0 MB)
                "wn_stack_tc": 54.1e6}       # profiles/ncu_wn_stack_r02.txt: 13.1 MB read + 41.0 MB written per launch (training saves)
 
 
