@@ -876,6 +876,19 @@ def _(dz, dlogdet, mask, flat, offsets, cond, ws, cfg, T, seed=None, energy=None
             _track_fake(dz, pitch, B, T))
 
 
+def range_bounds(nb: int, n_segments: int) -> List[int]:
+    """Block index boundaries, ascending, of the backward ranges of a data-parallel step: range k covers blocks
+    bounds[k] .. bounds[k + 1] - 1.  The ranges run from the last block down, so range 0 is the one whose collective nothing can
+    hide: it gets a quarter of a share (12 blocks, 3 segments: blocks 11..6 | 5..1 | 0); GTK_GRAD_SYNC_LAST=k sets its size."""
+    n_segments = max(1, min(int(n_segments), nb))
+    if n_segments == 1:
+        return [0, nb]
+    last = max(1, nb // (4 * n_segments))
+    if os.environ.get("GTK_GRAD_SYNC_LAST"):                  # blocks in the last (exposed) range, for sweeps
+        last = max(1, min(nb - n_segments + 1, int(os.environ["GTK_GRAD_SYNC_LAST"])))
+    return [0] + [last + (nb - last) * k // (n_segments - 1) for k in range(n_segments)]
+
+
 _RANGE_STREAMS = {}
 
 
@@ -913,15 +926,7 @@ def decoder_backward_flat_overlapped(dz: Tensor, dlogdet: Tensor, mask: Tensor, 
     world = dist.get_world_size(group) if sync else 1
     avg = sync and dist.get_backend(group) == "nccl"
     n_segments = max(1, min(int(n_segments), nb))
-    # block index boundaries, ascending.  The ranges run from the last block down, so range 0 is the one whose collective
-    # nothing can hide: it gets a quarter of a share (12 blocks, 3 segments: blocks 11..6 | 5..1 | 0)
-    if n_segments > 1:
-        last = max(1, nb // (4 * n_segments))
-        if os.environ.get("GTK_GRAD_SYNC_LAST"):              # blocks in the last (exposed) range, for sweeps
-            last = max(1, min(nb - n_segments + 1, int(os.environ["GTK_GRAD_SYNC_LAST"])))
-        bounds = [0] + [last + (nb - last) * k // (n_segments - 1) for k in range(n_segments)]
-    else:
-        bounds = [0, nb]
+    bounds = range_bounds(nb, n_segments)
     works = []
     # Deferred join (GTK_RANGE_DEFER=0 disables): a range that is not the last one returns without joining the library's side
     # stream (its last weight-gradient launch + its reduce); the collective is issued from a helper stream that waits for the

@@ -63,3 +63,23 @@ def test_gloo_world2_flat_gradient_sync(tmp_path):
     np.testing.assert_allclose(g["got"], g["want"], rtol=1e-6, atol=1e-8)
     np.testing.assert_array_equal(g["got"], g1["got"])                   # both ranks hold the same averaged buffer
     assert np.abs(g["got"]).max() > 0
+
+
+@pytest.mark.parametrize("nb,segs", [(12, 3), (12, 1), (12, 2), (12, 4), (12, 12), (12, 20), (5, 3), (5, 5), (2, 3), (1, 3)])
+def test_backward_range_bounds_tile_the_blocks(nb, segs, monkeypatch):
+    """ops.range_bounds: the block ranges of the overlapped data-parallel backward (issued from the last block down) tile
+    0..nb-1, none is empty, and the LAST range issued (blocks bounds[0]..bounds[1]-1, the only exposed collective) is the
+    smallest; GTK_GRAD_SYNC_LAST overrides its size within what the segment count allows."""
+    from glowtts_b200 import ops
+    monkeypatch.delenv("GTK_GRAD_SYNC_LAST", raising=False)
+    b = ops.range_bounds(nb, segs)
+    assert b[0] == 0 and b[-1] == nb and len(b) == min(max(segs, 1), nb) + 1
+    sizes = [hi - lo for lo, hi in zip(b, b[1:])]
+    assert all(s >= 1 for s in sizes) and sizes[0] == min(sizes)
+    if (nb, segs) == (12, 3):
+        assert b == [0, 1, 6, 12]                      # 11..6 | 5..1 | 0
+    monkeypatch.setenv("GTK_GRAD_SYNC_LAST", "2")
+    b2 = ops.range_bounds(nb, segs)
+    assert b2[0] == 0 and b2[-1] == nb and all(hi > lo for lo, hi in zip(b2, b2[1:]))
+    if len(b2) > 2:
+        assert b2[1] == min(2, nb - (len(b2) - 1) + 1)
